@@ -1,0 +1,97 @@
+"""Deterministic synthetic sparse matrices of the shapes BASELINE.json names.
+
+The reference's example matrices are missing blobs, so every
+config runs on a seeded stand-in.  All generators return a row-major-sorted COO pattern
+(row ascending, col ascending inside a row, no duplicates) as int64 numpy arrays -- the
+order the reference loader demands (struct.cc:125).
+"""
+import numpy as np
+
+
+def _rows_from_lengths(lengths):
+    return np.repeat(np.arange(len(lengths), dtype=np.int64), lengths)
+
+
+def _cols_for_lengths(rng, lengths, cols, weights=None):
+    """Distinct sorted column ids per row, vectorised: sample keys then dedupe per row."""
+    lengths = np.minimum(lengths, cols).astype(np.int64)
+    total = int(lengths.sum())
+    r = _rows_from_lengths(lengths)
+    if weights is None:
+        c = rng.integers(0, cols, size=total, dtype=np.int64)
+    else:
+        cdf = np.cumsum(weights)
+        cdf /= cdf[-1]
+        c = np.searchsorted(cdf, rng.random(total)).astype(np.int64)
+        c = np.minimum(c, cols - 1)
+    key = r * cols + c
+    key = np.unique(key)  # sorted, duplicates dropped (row lengths shrink slightly)
+    return key // cols, key % cols
+
+
+def synth_matrix(kind, rows, cols, seed=0, **p):
+    """Return (row, col) int64 arrays of a seeded synthetic pattern.
+
+    kinds: uniform(density) | ragged(mean_len, empty_frac) | lognormal(mean_len) |
+           powerlaw(avg_deg, alpha) | banded(half_bandwidth) | nm24()
+    """
+    rng = np.random.default_rng(0x6753 + seed)
+    if kind == "uniform":
+        density = p["density"]
+        if rows * cols <= (1 << 27):
+            mask = rng.random((rows, cols)) < density
+            r, c = np.nonzero(mask)
+            return r.astype(np.int64), c.astype(np.int64)
+        lengths = rng.binomial(cols, density, size=rows)
+        return _cols_for_lengths(rng, lengths, cols)
+    if kind == "ragged":
+        lengths = rng.geometric(1.0 / p["mean_len"], size=rows)
+        lengths[rng.random(rows) < p.get("empty_frac", 0.1)] = 0
+        lengths[rows - max(1, rows // 50):] = 0  # trailing empty rows (remove_empty_row_in_end path)
+        if rows > 8:
+            lengths[3] = min(cols, 5 * int(p["mean_len"]) + 70)  # one long row (> 64: several col-dir chunks)
+        return _cols_for_lengths(rng, lengths, cols)
+    if kind == "lognormal":
+        sigma = 0.9
+        mu = np.log(p["mean_len"]) - sigma * sigma / 2
+        lengths = np.maximum(1, rng.lognormal(mu, sigma, size=rows)).astype(np.int64)
+        return _cols_for_lengths(rng, lengths, cols)
+    if kind == "powerlaw":
+        alpha = p.get("alpha", 2.1)
+        u = rng.random(rows)
+        deg = np.floor((1.0 - u) ** (-1.0 / (alpha - 1.0))).astype(np.float64)
+        deg = np.minimum(deg, p.get("cap", max(8, cols // 10)))
+        deg *= p["avg_deg"] * rows / deg.sum()
+        lengths = np.maximum(0, np.round(deg)).astype(np.int64)
+        w = (np.arange(1, cols + 1, dtype=np.float64)) ** (-0.6)
+        w = w[rng.permutation(cols)]
+        return _cols_for_lengths(rng, lengths, cols, weights=w)
+    if kind == "banded":
+        hb = p["half_bandwidth"]
+        offs = np.arange(-hb, hb + 1, dtype=np.int64)
+        r = np.repeat(np.arange(rows, dtype=np.int64), len(offs))
+        c = r + np.tile(offs, rows)
+        ok = (c >= 0) & (c < cols)
+        return r[ok], c[ok]
+    if kind == "nm24":
+        # exactly 2 of every 4 consecutive columns kept (magnitude-chosen from random weights)
+        assert cols % 4 == 0
+        w = rng.random((rows, cols // 4, 4))
+        keep = np.argsort(-w, axis=2)[:, :, :2]
+        keep.sort(axis=2)
+        base = (np.arange(cols // 4, dtype=np.int64) * 4)[None, :, None]
+        c = (keep + base).reshape(rows, -1)
+        r = np.repeat(np.arange(rows, dtype=np.int64), c.shape[1])
+        return r, c.reshape(-1).astype(np.int64)
+    raise ValueError("unknown synthetic kind %r" % kind)
+
+
+def synth_values(nnz, seed=0, scale=0.02, dtype=np.float32):
+    """Pruned-weight-like values N(0, scale); reference mode uses all ones instead."""
+    rng = np.random.default_rng(0x7A11 + seed)
+    return (rng.standard_normal(nnz) * scale).astype(dtype)
+
+
+def synth_dense(k, n, seed=0, dtype=np.float32):
+    rng = np.random.default_rng(0xB0B + seed)
+    return rng.uniform(-1.0, 1.0, size=(k, n)).astype(dtype)

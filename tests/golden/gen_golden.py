@@ -1,0 +1,149 @@
+#!/usr/bin/env python3
+"""Generate golden transform_step fixtures by running the UNMODIFIED reference pipeline.
+
+TEST INFRASTRUCTURE ONLY.  Runs in the dev container (needs /root/reference and
+oracle/_ref/ref_harness, built by `make -C oracle ref`).  For every (matrix, family, N, S, C)
+case below it
+  1. writes the synthetic matrix as a 1-based, row-major-sorted COO text file
+     (the only input format the reference loader accepts, struct.cc:97-125),
+  2. runs the reference's own test_spmm_<family> operator chain (token_test.cc:1003-1582)
+     through oracle/ref_harness.cc, which dumps EVERY metadata array left in the
+     meta_data_set with the reference's own writer,
+  3. packs the dump into tests/golden/<case>.npz: one u64 (or f64 for nz_vals) array per
+     metadata key, plus "__dtypes__" (key -> compressed dtype chosen by the reference,
+     code_source_data.cc:383-416), "__registered__" (keys the reference's code generator
+     registered as kernel inputs = files in its data_source/<id>/ hand-off dir) and the
+     input COO itself.
+
+The .npz files are committed; /root/reference is not needed to run the tests.
+"""
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(os.path.dirname(HERE))
+REF = os.environ.get("GS_REFERENCE", "/root/reference")
+HARNESS = os.path.join(REPO, "oracle", "_ref", "ref_harness")
+
+sys.path.insert(0, REPO)
+from generalsparse_b200.synth import synth_matrix  # noqa: E402
+
+FAMILIES = ["thread_total", "warp_total", "warp_bitmap", "thread_bit_map", "warp_segment",
+            "block_total", "block_bitmap"]
+
+# (case name, generator kind, rows, cols, params, seed)
+MATRICES = [
+    ("tiny", "uniform", 64, 48, dict(density=0.085), 1),
+    ("ragged", "ragged", 200, 150, dict(mean_len=9.0, empty_frac=0.15), 2),
+    ("ig5like", "lognormal", 1500, 1300, dict(mean_len=37.4), 3),
+    ("ffnlike", "uniform", 344, 512, dict(density=0.30), 4),
+    ("powerlaw", "powerlaw", 3000, 3000, dict(avg_deg=20.0, alpha=2.1), 5),
+]
+
+# (family, N, sparse_coarsen, coarsen)
+def cases_for(mname):
+    out = []
+    for fam in FAMILIES:
+        out.append((fam, 8, 4 if fam == "thread_total" else 1, 1))
+    if mname in ("tiny", "ffnlike"):
+        out.append(("thread_total", 32, 8, 1))
+        out.append(("thread_total", 8, 2, 2))
+        out.append(("warp_segment", 32, 1, 1))
+        out.append(("warp_bitmap", 32, 1, 2))
+        out.append(("block_bitmap", 16, 1, 1))
+        out.append(("thread_bit_map", 4, 1, 1))
+    return out
+
+
+def write_mtx(path, rows, cols, r, c):
+    with open(path, "w") as f:
+        f.write("%%MatrixMarket matrix coordinate real general\n")
+        f.write("%d %d %d\n" % (rows, cols, len(r)))
+        for i in range(len(r)):
+            f.write("%d %d 1\n" % (r[i] + 1, c[i] + 1))
+
+
+def make_scratch():
+    d = tempfile.mkdtemp(prefix="gsref_")
+    cfg = json.load(open(os.path.join(REF, "global_config.json.bak")))
+    cfg.update(ROOT_PATH_STR=d, spmv_header_file=os.path.join(d, "spmm_header_top.code"), HALF=False, DATA_SET="")
+    json.dump(cfg, open(os.path.join(d, "global_config.json"), "w"))
+    shutil.copytree(os.path.join(REF, "arm_code"), os.path.join(d, "arm_code"))
+    os.makedirs(os.path.join(d, "data_source"))
+    return d
+
+
+def read_dump(dump_dir):
+    out, dtypes = {}, {}
+    for line in open(os.path.join(dump_dir, "INDEX")):
+        key, n, mem_t, comp_t = line.split()
+        txt = open(os.path.join(dump_dir, key)).read().split()
+        assert len(txt) == int(n), (key, len(txt), n)
+        if mem_t in ("FLOAT", "DOUBLE"):
+            out[key] = np.array([float(x) for x in txt], dtype=np.float64)
+        else:
+            out[key] = np.array([int(x) for x in txt], dtype=np.uint64)
+        dtypes[key] = comp_t
+    return out, dtypes
+
+
+def run_case(scratch, mtx, fam, n, s, c):
+    dump = os.path.join(scratch, "dump_%s_%d_%d_%d" % (fam, n, s, c))
+    shutil.rmtree(dump, ignore_errors=True)
+    p = subprocess.run([HARNESS, fam, mtx, str(n), str(s), str(c), dump], cwd=scratch,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if p.returncode != 0 or not os.path.isdir(dump):
+        return None, p.stdout[-2000:]
+    arrs, dtypes = read_dump(dump)
+    registered = []
+    if os.path.exists(dump + ".handoff"):
+        hand = open(dump + ".handoff").read().strip()
+        if os.path.isdir(hand):
+            registered = sorted(x for x in os.listdir(hand) if "_META_" in x)
+    cfg = json.load(open(os.path.join(scratch, "global_config.json")))
+    # operator / step records the reference prints (observable behaviour)
+    steps = [ln for ln in p.stdout.splitlines() if "::{" in ln or "operator" in ln]
+    return dict(arrs=arrs, dtypes=dtypes, registered=registered, vector_width=int(cfg["VECTOR_WIDTH"]),
+                steps=steps), p.stdout[-500:]
+
+
+def main():
+    only = sys.argv[1:]
+    scratch = make_scratch()
+    summary = {}
+    for mname, kind, rows, cols, params, seed in MATRICES:
+        if only and mname not in only:
+            continue
+        r, c = synth_matrix(kind, rows, cols, seed=seed, **params)
+        mtx = os.path.join(scratch, mname + ".mtx")
+        write_mtx(mtx, rows, cols, r, c)
+        for fam, n, s, co in cases_for(mname):
+            res, log = run_case(scratch, mtx, fam, n, s, co)
+            name = "%s__%s__N%d_S%d_C%d" % (mname, fam, n, s, co)
+            if res is None:
+                print("FAILED", name, "\n", log)
+                summary[name] = "reference aborted"
+                continue
+            payload = {k: v for k, v in res["arrs"].items()}
+            payload["__coo_row__"] = r.astype(np.int64)
+            payload["__coo_col__"] = c.astype(np.int64)
+            payload["__shape__"] = np.array([rows, cols], dtype=np.int64)
+            payload["__meta__"] = np.array(json.dumps(dict(
+                dtypes=res["dtypes"], registered=res["registered"], vector_width=res["vector_width"],
+                family=fam, N=n, S=s, C=co, steps=res["steps"], matrix=dict(kind=kind, rows=rows, cols=cols,
+                                                                              params=params, seed=seed))))
+            np.savez_compressed(os.path.join(HERE, name + ".npz"), **payload)
+            summary[name] = "%d arrays" % len(res["arrs"])
+            print(name, summary[name], "registered:", len(res["registered"]))
+    json.dump(summary, open(os.path.join(HERE, "SUMMARY.json"), "w"), indent=1, sort_keys=True)
+    shutil.rmtree(scratch, ignore_errors=True)
+
+
+if __name__ == "__main__":
+    main()
