@@ -1,0 +1,774 @@
+#include "steps.hpp"
+
+#include <algorithm>
+
+namespace gs {
+namespace steps {
+
+namespace {
+
+const char *level_tag(POS_TYPE p)
+{
+    switch (p) {
+    case TBLOCK_META: return "BMTB";
+    case WARP_META: return "BMW";
+    case THREAD_META: return "BMT";
+    default: return "GLOBAL";
+    }
+}
+
+void record(recs *rec, const std::string &name, int id, const std::string &extra = "")
+{
+    if (rec) rec->push_back(name + "::{name:\"" + name + "\",target_matrix_id:" + std::to_string(id) + extra + "}");
+}
+
+std::vector<uint64_t> row_nnz(const meta_data_set &ms, int id, uint64_t *row_num_out = nullptr)
+{
+    uint64_t row_num = ms.real_row_num(id);
+    const universal_array &r = ms.get(GLOBAL_META, "nz_row_indices", id);
+    if (row_num_out) *row_num_out = row_num;
+    return get_nnz_of_each_row_in_spec_range(r, 0, row_num - 1, 0, r.get_len() - 1);
+}
+
+universal_array vals_like(const universal_array &old, std::vector<double> v) { return universal_array(std::move(v), old.type); }
+
+void check_pad_rate(uint64_t after, uint64_t before, double bound, const char *who)
+{
+    // the reference asserts (aborts) when nnz_after/nnz_before >= PADDING_RATE_UP_BOUND
+    if ((double)after / (double)before >= bound)
+        throw Error(std::string(who) + ": current padding rate is " + std::to_string((double)after / (double)before) +
+                    ", higher than " + std::to_string(bound));
+}
+
+} // namespace
+
+// ------------------------------------------------------------------------------------------------ sort
+void get_row_order_by_length(meta_data_set &ms, int id, recs *rec)
+{
+    GS_REQUIRE(!ms.is_exist(GLOBAL_META, "original_nz_row_indices", id), "the sub-matrix is already sorted");
+    uint64_t row_num;
+    std::vector<uint64_t> len = row_nnz(ms, id, &row_num);
+    uint64_t max_len = *std::max_element(len.begin(), len.end());
+    // counting sort by length, longest first, stable inside a length class (get_row_order_by_length.cc:67-90)
+    std::vector<uint64_t> start(max_len + 2, 0);
+    for (uint64_t l : len) start[max_len - l + 1]++;
+    for (size_t i = 1; i < start.size(); i++) start[i] += start[i - 1];
+    std::vector<uint64_t> order(row_num);
+    for (uint64_t r = 0; r < row_num; r++) order[start[max_len - len[r]]++] = r;
+    ms.add_u(GLOBAL_META, "original_nz_row_indices", id, std::move(order));
+    record(rec, "get_row_order_by_length", id);
+}
+
+namespace {
+// CSR offsets of the current (row-sorted) stream over the logical row count end-begin+1
+std::vector<uint64_t> logical_rowptr(const meta_data_set &ms, int id, uint64_t *rows_out)
+{
+    uint64_t rows = ms.scalar(GLOBAL_META, "end_row_index", id) - ms.scalar(GLOBAL_META, "begin_row_index", id) + 1;
+    const universal_array &r = ms.get(GLOBAL_META, "nz_row_indices", id);
+    std::vector<uint64_t> n = get_nnz_of_each_row_in_spec_range(r, 0, rows - 1, 0, r.get_len() - 1);
+    std::vector<uint64_t> ptr(rows + 1, 0);
+    for (uint64_t i = 0; i < rows; i++) ptr[i + 1] = ptr[i] + n[i];
+    *rows_out = rows;
+    return ptr;
+}
+} // namespace
+
+void reorder_val_by_index(meta_data_set &ms, int id, recs *rec)
+{
+    uint64_t rows;
+    std::vector<uint64_t> ptr = logical_rowptr(ms, id, &rows);
+    const universal_array &order = ms.get(GLOBAL_META, "original_nz_row_indices", id);
+    GS_REQUIRE(order.get_len() == rows, "original_nz_row_indices length != row count");
+    const universal_array &old = ms.get(GLOBAL_META, "nz_vals", id);
+    std::vector<double> out;
+    out.reserve(old.f.size());
+    for (uint64_t nr = 0; nr < rows; nr++) {
+        uint64_t o = order.u[nr];
+        GS_REQUIRE(o < rows, "row order entry out of range");
+        out.insert(out.end(), old.f.begin() + ptr[o], old.f.begin() + ptr[o + 1]);
+    }
+    universal_array na = vals_like(old, std::move(out));
+    ms.replace(GLOBAL_META, "nz_vals", id, std::move(na));
+    record(rec, "reorder_val_by_index", id);
+}
+
+void reorder_col_by_index(meta_data_set &ms, int id, recs *rec)
+{
+    uint64_t rows;
+    std::vector<uint64_t> ptr = logical_rowptr(ms, id, &rows);
+    const universal_array &order = ms.get(GLOBAL_META, "original_nz_row_indices", id);
+    GS_REQUIRE(order.get_len() == rows, "original_nz_row_indices length != row count");
+    const universal_array &old = ms.get(GLOBAL_META, "nz_col_indices", id);
+    std::vector<uint64_t> out;
+    out.reserve(old.u.size());
+    for (uint64_t nr = 0; nr < rows; nr++) {
+        uint64_t o = order.u[nr];
+        GS_REQUIRE(o < rows, "row order entry out of range");
+        out.insert(out.end(), old.u.begin() + ptr[o], old.u.begin() + ptr[o + 1]);
+    }
+    ms.replace_u(GLOBAL_META, "nz_col_indices", id, std::move(out));
+    record(rec, "reorder_col_by_index", id);
+}
+
+void reorder_row_by_index(meta_data_set &ms, int id, recs *rec)
+{
+    uint64_t rows;
+    std::vector<uint64_t> ptr = logical_rowptr(ms, id, &rows);
+    const universal_array &order = ms.get(GLOBAL_META, "original_nz_row_indices", id);
+    GS_REQUIRE(order.get_len() == rows, "original_nz_row_indices length != row count");
+    std::vector<uint64_t> out;
+    out.reserve(ptr[rows]);
+    for (uint64_t nr = 0; nr < rows; nr++) {
+        uint64_t o = order.u[nr];
+        out.insert(out.end(), ptr[o + 1] - ptr[o], nr);
+    }
+    ms.replace_u(GLOBAL_META, "nz_row_indices", id, std::move(out));
+    record(rec, "reorder_row_by_index", id);
+}
+
+void remove_empty_row_in_end_of_sub_matrix(meta_data_set &ms, int id, recs *rec)
+{
+    uint64_t begin = ms.scalar(GLOBAL_META, "begin_row_index", id), end = ms.scalar(GLOBAL_META, "end_row_index", id);
+    uint64_t rows = end - begin + 1;
+    uint64_t max_row = ms.get(GLOBAL_META, "nz_row_indices", id).u.back();
+    GS_REQUIRE(max_row <= rows - 1, "row index past end_row_index");
+    if (max_row < rows - 1) ms.replace_u(GLOBAL_META, "end_row_index", id, {begin + max_row});
+    record(rec, "remove_empty_row_in_end_of_sub_matrix", id);
+}
+
+// --------------------------------------------------------------------------------------------- padding
+void modify_by_col_pad_in_sub_matrix(meta_data_set &ms, int id, uint64_t m, double bound, recs *rec)
+{
+    GS_REQUIRE(m >= 2, "multiple_of_each_row_size must be >= 2");
+    uint64_t row_num;
+    std::vector<uint64_t> len = row_nnz(ms, id, &row_num);
+    const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    const universal_array &C = ms.get(GLOBAL_META, "nz_col_indices", id);
+    const universal_array &V = ms.get(GLOBAL_META, "nz_vals", id);
+    uint64_t nnz = R.get_len(), after = nnz;
+    bool padded = false;
+    for (uint64_t i = 0; i < row_num; i++)
+        if (len[i] % m != 0) {
+            after += (len[i] / m + 1) * m - len[i];
+            check_pad_rate(after, nnz, bound, "modify_col_indices_by_col_pad_in_sub_matrix");
+            padded = true;
+        }
+    if (padded) {
+        std::vector<uint64_t> nr, nc;
+        std::vector<double> nv;
+        nr.reserve(after), nc.reserve(after), nv.reserve(after);
+        uint64_t p = 0;
+        for (uint64_t i = 0; i < row_num; i++) {
+            uint64_t l = len[i];
+            for (uint64_t k = 0; k < l; k++, p++) nr.push_back(i), nc.push_back(C.u[p]), nv.push_back(V.f[p]);
+            if (l % m != 0) {
+                uint64_t target = (l / m + 1) * m;
+                uint64_t last_col = nc.back();
+                for (uint64_t k = l; k < target; k++) nr.push_back(i), nc.push_back(last_col), nv.push_back(0.0);
+            }
+        }
+        universal_array va = vals_like(V, std::move(nv));
+        ms.replace_u(GLOBAL_META, "nz_col_indices", id, std::move(nc));
+        ms.replace(GLOBAL_META, "nz_vals", id, std::move(va));
+        ms.replace_u(GLOBAL_META, "nz_row_indices", id, std::move(nr));
+    }
+    std::string extra = ",multiple_of_each_row_size:" + std::to_string(m);
+    record(rec, "modify_col_indices_by_col_pad_in_sub_matrix", id, extra);
+    record(rec, "modify_vals_by_col_pad_in_sub_matrix", id, extra);
+    record(rec, "modify_row_indices_by_col_pad_in_sub_matrix", id, extra);
+}
+
+void modify_by_nnz_pad(meta_data_set &ms, int id, uint64_t target, double bound, recs *rec)
+{
+    GS_REQUIRE(target >= 1, "nnz_target must be >= 1");
+    universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    universal_array &C = ms.get(GLOBAL_META, "nz_col_indices", id);
+    universal_array &V = ms.get(GLOBAL_META, "nz_vals", id);
+    uint64_t nnz = C.get_len();
+    if (nnz % target != 0) {
+        uint64_t n2 = (nnz / target + 1) * target;
+        check_pad_rate(n2, nnz, bound, "modify_col_indices_by_nnz_pad");
+        C.u.resize(n2, C.u.back());
+        V.f.resize(n2, 0.0);
+        R.u.resize(n2, R.u.back());
+    }
+    std::string extra = ",nnz_target:" + std::to_string(target);
+    record(rec, "modify_col_indices_by_nnz_pad", id, extra);
+    record(rec, "modify_vals_by_nnz_pad", id, extra);
+    record(rec, "modify_row_indices_by_nnz_pad", id, extra);
+}
+
+void modify_by_row_pad_in_sub_matrix(meta_data_set &ms, int id, uint64_t multiple, double bound, recs *rec)
+{
+    GS_REQUIRE(multiple >= 1, "multiple must be >= 1");
+    // NB: this step uses the LOGICAL row count end-begin+1 (modify_row_indices_by_row_pad_in_sub_matrix.cc)
+    uint64_t rows = ms.scalar(GLOBAL_META, "end_row_index", id) - ms.scalar(GLOBAL_META, "begin_row_index", id) + 1;
+    universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    universal_array &C = ms.get(GLOBAL_META, "nz_col_indices", id);
+    universal_array &V = ms.get(GLOBAL_META, "nz_vals", id);
+    if (rows % multiple != 0) {
+        uint64_t added = (rows / multiple + 1) * multiple - rows;
+        uint64_t nnz = R.get_len();
+        check_pad_rate(nnz + added, nnz, bound, "modify_col_indices_by_row_pad_in_sub_matrix");
+        uint64_t last_col = C.u.back();
+        for (uint64_t i = 0; i < added; i++) {
+            C.u.push_back(last_col);
+            V.f.push_back(0.0);
+            R.u.push_back(rows + i);
+        }
+    }
+    std::string extra = ",multiple:" + std::to_string(multiple);
+    record(rec, "modify_col_indices_by_row_pad_in_sub_matrix", id, extra);
+    record(rec, "modify_vals_by_row_pad_in_sub_matrix", id, extra);
+    record(rec, "modify_row_indices_by_row_pad_in_sub_matrix", id, extra);
+}
+
+void modify_by_empty_pad_in_submatrix(meta_data_set &ms, int id, recs *rec)
+{
+    uint64_t row_num = ms.real_row_num(id);
+    const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    const universal_array &C = ms.get(GLOBAL_META, "nz_col_indices", id);
+    const universal_array &V = ms.get(GLOBAL_META, "nz_vals", id);
+    uint64_t nnz = R.get_len();
+    std::vector<uint64_t> nr, nc;
+    std::vector<double> nv;
+    bool padded = false;
+    for (uint64_t i = 0; i < nnz; i++) {
+        uint64_t r = R.u[i];
+        uint64_t next = (i == nnz - 1) ? row_num : R.u[i + 1];
+        nr.push_back(r), nc.push_back(C.u[i]), nv.push_back(V.f[i]);
+        // every empty row between r and next gets one explicit zero that reuses this entry's column
+        for (uint64_t e = r + 1; e < next; e++) {
+            nr.push_back(e), nc.push_back(C.u[i]), nv.push_back(0.0);
+            padded = true;
+        }
+    }
+    if (padded) {
+        universal_array va = vals_like(V, std::move(nv));
+        ms.replace_u(GLOBAL_META, "nz_col_indices", id, std::move(nc));
+        ms.replace(GLOBAL_META, "nz_vals", id, std::move(va));
+        ms.replace_u(GLOBAL_META, "nz_row_indices", id, std::move(nr));
+    }
+    record(rec, "modify_col_indices_by_empty_pad_in_submatrix", id);
+    record(rec, "modify_vals_by_empty_pad_in_submatrix", id);
+    record(rec, "modify_row_indices_by_empty_pad_in_submatrix", id);
+}
+
+// ---------------------------------------------------------------------------- fixed blocking, row direction
+static std::string row_dir_name(const char *what, POS_TYPE pos, const char *suffix)
+{
+    std::string lvl = pos == TBLOCK_META ? "BMTBs" : level_tag(pos);
+    return std::string("get_begin_") + what + "_of_" + lvl + "_after_fixed_blocking_in_row_direction" + suffix;
+}
+
+void get_begin_rows_after_fixed_blocking_in_row_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t b, recs *rec)
+{
+    GS_REQUIRE(b >= 1, "fixed_row_block_size must be >= 1");
+    uint64_t row_num = ms.real_row_num(id);
+    std::vector<uint64_t> v;
+    // [0, b, 2b, ..., row_num]; the BMT and BMW/BMTB reference loops give the same sequence
+    for (uint64_t r = 0; r < row_num; r += b) v.push_back(r);
+    v.push_back(row_num);
+    ms.add_u(pos, "first_row_indices", id, std::move(v));
+    record(rec, row_dir_name("rows", pos, pos == WARP_META ? "_without_BMTB" : ""), id, ",fixed_row_block_size:" + std::to_string(b));
+}
+
+void get_begin_nzs_after_fixed_blocking_in_row_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t b, recs *rec)
+{
+    GS_REQUIRE(b >= 1, "fixed_row_block_size must be >= 1");
+    uint64_t row_num;
+    std::vector<uint64_t> len = row_nnz(ms, id, &row_num);
+    std::vector<uint64_t> v{0};
+    uint64_t acc = 0;
+    for (uint64_t r = 0; r < row_num; r++) {
+        acc += len[r];
+        if ((r + 1) % b == 0 || r == row_num - 1) v.push_back(acc);
+    }
+    ms.add_u(pos, "first_nz_indices", id, std::move(v));
+    record(rec, row_dir_name("nzs", pos, pos == WARP_META ? "_without_BMTB" : ""), id, ",fixed_row_block_size:" + std::to_string(b));
+}
+
+void get_begin_rows_after_fixed_blocking_in_row_direction_in_parent(meta_data_set &ms, POS_TYPE pos, POS_TYPE parent, int id, uint64_t b, recs *rec)
+{
+    const universal_array &P = ms.get(parent, "first_row_indices", id);
+    std::vector<uint64_t> v;
+    for (uint64_t i = 0; i + 1 < P.get_len(); i++)
+        for (uint64_t r = P.u[i]; r < P.u[i + 1]; r += b) v.push_back(r);
+    v.push_back(P.u.back());
+    ms.add_u(pos, "first_row_indices", id, std::move(v));
+    record(rec, row_dir_name("rows", pos, parent == TBLOCK_META ? "_in_BMTB" : "_in_BMW"), id, ",fixed_row_block_size:" + std::to_string(b));
+}
+
+void get_begin_nzs_after_fixed_blocking_in_row_direction_in_parent(meta_data_set &ms, POS_TYPE pos, POS_TYPE parent, int id, uint64_t b, recs *rec)
+{
+    const universal_array &P = ms.get(parent, "first_row_indices", id);
+    std::vector<uint64_t> len = row_nnz(ms, id);
+    std::vector<uint64_t> v{0};
+    for (uint64_t i = 0; i + 1 < P.get_len(); i++)
+        for (uint64_t r0 = P.u[i]; r0 < P.u[i + 1]; r0 += b) {
+            uint64_t n = 0;
+            for (uint64_t r = r0; r < P.u[i + 1] && r < r0 + b; r++) n += len.at(r);
+            v.push_back(v.back() + n);
+        }
+    ms.add_u(pos, "first_nz_indices", id, std::move(v));
+    record(rec, row_dir_name("nzs", pos, parent == TBLOCK_META ? "_in_BMTB" : "_in_BMW"), id, ",fixed_row_block_size:" + std::to_string(b));
+}
+
+void get_begin_rows_after_fixed_blocking_in_row_direction_relative_to_parent(meta_data_set &ms, POS_TYPE pos, POS_TYPE parent, int id, uint64_t b, recs *rec)
+{
+    const universal_array &P = ms.get(parent, "first_row_indices", id);
+    std::vector<uint64_t> v;
+    for (uint64_t i = 0; i + 1 < P.get_len(); i++)
+        for (uint64_t r = P.u[i]; r < P.u[i + 1]; r += b) v.push_back(r - P.u[i]);
+    const char *sfx = parent == TBLOCK_META ? "_relative_to_BMTB" : "_relative_to_BMW";
+    ms.add_u(pos, std::string("first_row_indices") + sfx, id, std::move(v));
+    record(rec, row_dir_name("rows", pos, sfx), id, ",fixed_row_block_size:" + std::to_string(b));
+}
+
+void get_begin_nzs_after_fixed_blocking_in_row_direction_relative_to_parent(meta_data_set &ms, POS_TYPE pos, POS_TYPE parent, int id, uint64_t b, recs *rec)
+{
+    const universal_array &P = ms.get(parent, "first_row_indices", id);
+    std::vector<uint64_t> len = row_nnz(ms, id);
+    std::vector<uint64_t> v;
+    for (uint64_t i = 0; i + 1 < P.get_len(); i++) {
+        uint64_t n = 0;
+        for (uint64_t r = P.u[i]; r < P.u[i + 1]; r++) {
+            if ((r - P.u[i]) % b == 0) v.push_back(n);
+            n += len.at(r);
+        }
+    }
+    const char *sfx = parent == TBLOCK_META ? "_relative_to_BMTB" : "_relative_to_BMW";
+    ms.add_u(pos, std::string("first_nz_indices") + sfx, id, std::move(v));
+    record(rec, row_dir_name("nzs", pos, sfx), id, ",fixed_row_block_size:" + std::to_string(b));
+}
+
+static const char *first_child_name(POS_TYPE child) { return child == WARP_META ? "first_BMW_indices" : "first_BMT_indices"; }
+
+void get_begin_children_of_parent_after_blocking_in_row_direction(meta_data_set &ms, POS_TYPE child, POS_TYPE parent, int id, recs *rec)
+{
+    const universal_array &P = ms.get(parent, "first_row_indices", id);
+    const universal_array &Cc = ms.get(child, "first_row_indices", id);
+    std::vector<uint64_t> v{0};
+    uint64_t c = 0;
+    for (uint64_t i = 0; i + 1 < P.get_len(); i++) {
+        GS_REQUIRE(c < Cc.get_len() && Cc.u[c] == P.u[i], "child blocks do not start at the parent's first row");
+        uint64_t n = 0;
+        while (c < Cc.get_len() && Cc.u[c] < P.u[i + 1]) n++, c++;
+        v.push_back(v.back() + n);
+    }
+    ms.add_u(parent, first_child_name(child), id, std::move(v));
+    record(rec, child == WARP_META ? "get_begin_BMWs_of_BMTB_after_blocking_in_row_direction"
+                                   : "get_begin_BMTs_of_specific_parent_after_blocking_in_row_direction", id);
+}
+
+void get_begin_children_of_parent_after_blocking(meta_data_set &ms, POS_TYPE child, POS_TYPE parent, int id, recs *rec)
+{
+    const universal_array &P = ms.get(parent, "first_nz_indices", id);
+    const universal_array &Cc = ms.get(child, "first_nz_indices", id);
+    std::vector<uint64_t> v{0};
+    uint64_t c = 0;
+    for (uint64_t i = 0; i + 1 < P.get_len(); i++) {
+        GS_REQUIRE(c < Cc.get_len() && Cc.u[c] == P.u[i], "child blocks do not start at the parent's first non-zero");
+        uint64_t n = 0;
+        while (c < Cc.get_len() && Cc.u[c] < P.u[i + 1]) n++, c++;
+        v.push_back(v.back() + n);
+    }
+    ms.add_u(parent, first_child_name(child), id, std::move(v));
+    record(rec, child == WARP_META ? "get_begin_BMWs_of_BMTB_after_blocking" : "get_begin_BMTs_of_specific_parent_after_blocking", id);
+}
+
+// ---------------------------------------------------------------------------- fixed blocking, col direction
+void get_begin_rows_after_fixed_blocking_in_col_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t c, recs *rec)
+{
+    GS_REQUIRE(c >= 1, "col_size must be >= 1");
+    uint64_t row_num;
+    std::vector<uint64_t> len = row_nnz(ms, id, &row_num);
+    std::vector<uint64_t> v;
+    for (uint64_t r = 0; r < row_num; r++) v.insert(v.end(), (len[r] + c - 1) / c, r);
+    ms.add_u(pos, "first_row_indices_without_ending", id, std::move(v));
+    record(rec, std::string("get_begin_rows_of_") + level_tag(pos) + "_after_fixed_blocking_in_col_direction", id, ",col_size:" + std::to_string(c));
+}
+
+void get_begin_nzs_after_fixed_blocking_in_col_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t c, recs *rec)
+{
+    GS_REQUIRE(c >= 1, "col_size must be >= 1");
+    uint64_t row_num;
+    std::vector<uint64_t> len = row_nnz(ms, id, &row_num);
+    std::vector<uint64_t> v{0};
+    for (uint64_t r = 0; r < row_num; r++) {
+        uint64_t remain = len[r];
+        while (remain > 0) {
+            uint64_t take = remain < c ? remain : c;
+            v.push_back(v.back() + take);
+            remain -= take;
+        }
+    }
+    ms.add_u(pos, "first_nz_indices", id, std::move(v));
+    record(rec, std::string("get_begin_nzs_of_") + level_tag(pos) + "_after_fixed_blocking_in_col_direction", id, ",col_size:" + std::to_string(c));
+}
+
+// ---------------------------------------------------------------------------- fixed blocking, nnz direction
+void get_begin_rows_after_fixed_blocking_in_nnz_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t k, recs *rec)
+{
+    GS_REQUIRE(k >= 1, "nnz_per_block must be >= 1");
+    uint64_t row_num = ms.real_row_num(id);
+    const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    std::vector<uint64_t> v;
+    for (uint64_t i = 0; i < R.get_len(); i += k) v.push_back(R.u[i]);
+    v.push_back(row_num);
+    ms.add_u(pos, "first_row_indices", id, std::move(v));
+    record(rec, std::string("get_begin_rows_of_") + level_tag(pos) + "_after_fixed_blocking_in_nnz_direction", id, ",nnz_per_" + std::string(level_tag(pos)) + ":" + std::to_string(k));
+}
+
+void get_begin_nzs_after_fixed_blocking_in_nnz_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t k, recs *rec)
+{
+    GS_REQUIRE(k >= 1, "nnz_per_block must be >= 1");
+    uint64_t nnz = ms.get(GLOBAL_META, "nz_row_indices", id).get_len();
+    std::vector<uint64_t> v;
+    for (uint64_t i = 0; i < nnz; i += k) v.push_back(i);
+    v.push_back(nnz);
+    ms.add_u(pos, "first_nz_indices", id, std::move(v));
+    record(rec, std::string("get_begin_nzs_of_") + level_tag(pos) + "_after_fixed_blocking_in_nnz_direction", id, ",nnz_per_" + std::string(level_tag(pos)) + ":" + std::to_string(k));
+}
+
+// --------------------------------------------------------------------------------------------------- sizes
+void get_BMT_size_of_each_parent(meta_data_set &ms, POS_TYPE parent_pos, int id, bool row_direction_blocking, recs *rec)
+{
+    record(rec, "get_BMT_size_of_each_parent", id);
+    const universal_array &T = ms.get(THREAD_META, "first_nz_indices", id);
+    std::vector<uint64_t> out;
+    if (parent_pos == GLOBAL_META) {
+        uint64_t size = 0;
+        bool seen = false;
+        for (uint64_t t = 0; t + 1 < T.get_len(); t++) {
+            uint64_t s = T.u[t + 1] - T.u[t];
+            if (!seen) size = s, seen = true;
+            else if (s != size) return; // not uniform: the reference prints a note and emits nothing
+        }
+        GS_REQUIRE(seen, "no BMT");
+        out.push_back(size);
+    } else {
+        const universal_array &P = ms.get(parent_pos, "first_nz_indices", id);
+        const universal_array *FB = row_direction_blocking ? &ms.get(parent_pos, "first_BMT_indices", id) : nullptr;
+        uint64_t t = 0;
+        for (uint64_t p = 0; p + 1 < P.get_len(); p++) {
+            uint64_t lo = P.u[p], hi = P.u[p + 1];
+            GS_REQUIRE(t < T.get_len() && T.u[t] == lo, "BMT does not start at the parent block's first non-zero");
+            uint64_t size = 0;
+            bool seen = false;
+            uint64_t cur = T.u[t];
+            while (cur < hi) {
+                GS_REQUIRE(t + 1 < T.get_len(), "BMT offsets end inside a parent block");
+                uint64_t s = T.u[t + 1] - T.u[t];
+                if (!seen) size = s, seen = true;
+                else if (s != size) return;
+                t++;
+                cur = T.u[t];
+            }
+            if (FB && lo == hi)
+                while (t < FB->u[p + 1]) t++;
+            // (the reference asserts that at least one BMT was seen unless the parent is empty)
+            out.push_back(size);
+        }
+    }
+    ms.add_u(parent_pos, "BMT_size_of_each_blk", id, std::move(out));
+}
+
+// -------------------------------------------------------------------------------------- bit maps / segments
+static std::vector<uint8_t> row_start_bits(const universal_array &R)
+{
+    std::vector<uint8_t> bits(R.get_len());
+    bits[0] = 1;
+    for (uint64_t j = 1; j < R.get_len(); j++) bits[j] = R.u[j] != R.u[j - 1];
+    return bits;
+}
+
+void thread_bit_map(meta_data_set &ms, bool parent_flag, uint64_t parent_size, int id, recs *rec)
+{
+    const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    const universal_array &T = ms.get(THREAD_META, "first_nz_indices", id);
+    std::vector<uint8_t> bits = row_start_bits(R);
+    if (parent_flag) {
+        GS_REQUIRE(ms.is_exist(GLOBAL_META, "BMT_size_of_each_blk", id), "thread_bit_map with a parent needs uniform BMT sizes");
+        GS_REQUIRE(parent_size >= 1, "parent size");
+        uint64_t thread_size = T.u[1] - T.u[0];
+        // the first non-zero of every `parent_size`-th BMT starts a segment (thread_bit_map.cc: parent_flag loop;
+        // the reference loop may step one BMT past the end, which writes nothing observable)
+        for (uint64_t i = 0; i < bits.size() / thread_size + 1; i += parent_size)
+            if (i * thread_size < bits.size()) bits[i * thread_size] = 1;
+    }
+    std::vector<uint64_t> out;
+    out.reserve(T.get_len() - 1);
+    for (uint64_t i = 0; i + 1 < T.get_len(); i++) {
+        uint64_t lo = T.u[i], hi = T.u[i + 1];
+        GS_REQUIRE(hi - lo <= 64, "a BMT wider than 64 non-zeros does not fit the u64 bit map");
+        uint64_t map = 0;
+        for (uint64_t j = hi; j-- > lo;) map = (map << 1) | bits[j]; // LSB = first non-zero of the BMT
+        out.push_back(map);
+    }
+    ms.add_u(THREAD_META, "thread_bit_map", id, std::move(out));
+    record(rec, "thread_bit_map", id);
+}
+
+void parent_bit_map_of_thread(meta_data_set &ms, POS_TYPE pos, int id, uint64_t vector_width, recs *rec)
+{
+    const universal_array &F = ms.get(THREAD_META, "first_row_indices_without_ending", id);
+    std::vector<uint8_t> bits = row_start_bits(F);
+    std::vector<uint64_t> out;
+    POS_TYPE store = pos;
+    if (pos == WARP_META) {
+        GS_REQUIRE(vector_width >= 1 && vector_width <= 64, "VECTOR_WIDTH must be in 1..64");
+        for (uint64_t i = 0; i < bits.size(); i += vector_width) bits[i] = 1;
+        for (uint64_t i = 0; i < bits.size(); i += vector_width) {
+            uint64_t k = std::min<uint64_t>(i + vector_width, bits.size());
+            uint64_t map = 0;
+            for (uint64_t j = k; j-- > i;) map = (map << 1) | bits[j];
+            out.push_back(map);
+        }
+    } else if (pos == TBLOCK_META) {
+        const universal_array &FB = ms.get(TBLOCK_META, "first_BMT_indices", id);
+        for (uint64_t i = 0; i < FB.get_len(); i++)
+            if (FB.u[i] < bits.size()) bits[FB.u[i]] = 1; // the end sentinel falls one past the array in the reference
+        out.assign(bits.begin(), bits.end());
+        store = THREAD_META; // one 0/1 per BMT, stored at THREAD level (parent_bit_map_of_thread.cc: pos reassigned)
+    } else {
+        throw Error("parent_bit_map_of_thread: pos must be WARP_META or TBLOCK_META");
+    }
+    ms.add_u(store, "bit_map_of_thread", id, std::move(out));
+    record(rec, "parent_bit_map_of_thread", id);
+}
+
+void segment_empty_flag(meta_data_set &ms, POS_TYPE, uint64_t size, int id, recs *rec)
+{
+    GS_REQUIRE(size >= 1 && size <= 64, "segment_empty_flag packs at most 64 BMTs per word");
+    const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    const universal_array &T = ms.get(THREAD_META, "first_nz_indices", id);
+    std::vector<uint8_t> flag;
+    for (uint64_t j = 0; j + 1 < T.get_len(); j++) {
+        uint8_t f = 0;
+        for (uint64_t i = T.u[j] + 1; i < T.u[j + 1]; i++)
+            if (R.u[i] - R.u[i - 1] > 1) {
+                f = 1;
+                break;
+            }
+        flag.push_back(f);
+    }
+    std::vector<uint64_t> out;
+    for (uint64_t i = 0; i < flag.size(); i += size) {
+        uint64_t k = std::min<uint64_t>(i + size, flag.size());
+        uint64_t w = 0;
+        for (uint64_t j = k; j-- > i;) w = (w << 1) | flag[j];
+        out.push_back(w);
+    }
+    ms.add_u(THREAD_META, "segment_empty_flag", id, std::move(out));
+    record(rec, "segment_empty_flag", id);
+}
+
+void segment_empty_row_indices(meta_data_set &ms, POS_TYPE, int id, recs *rec)
+{
+    const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    const universal_array &T = ms.get(THREAD_META, "first_nz_indices", id);
+    std::vector<uint64_t> out;
+    for (uint64_t j = 0; j + 1 < T.get_len(); j++) {
+        uint64_t first_row = R.u[T.u[j]];
+        out.push_back(0);
+        for (uint64_t i = T.u[j] + 1; i < T.u[j + 1]; i++)
+            if (R.u[i] != R.u[i - 1]) out.push_back(R.u[i] - first_row);
+    }
+    ms.add_u(THREAD_META, "segment_empty_row_indices", id, std::move(out));
+    record(rec, "segment_empty_row_indices", id);
+}
+
+void segment_offset(meta_data_set &ms, bool parent_flag, uint64_t size, int id, recs *rec)
+{
+    const universal_array *B = nullptr;
+    if (ms.is_exist(THREAD_META, "thread_bit_map", id)) B = &ms.get(THREAD_META, "thread_bit_map", id);
+    else if (ms.is_exist(THREAD_META, "bit_map_of_thread", id)) B = &ms.get(THREAD_META, "bit_map_of_thread", id);
+    GS_REQUIRE(B != nullptr, "segment_offset needs thread_bit_map or bit_map_of_thread");
+    GS_REQUIRE(size >= 1, "size");
+    std::vector<uint64_t> out(B->get_len(), 0);
+    uint64_t count = 0, prev = 0;
+    for (uint64_t j = 1; j < B->get_len(); j++) {
+        if (B->u[j] == 0 && ((j % size != 0) || !parent_flag)) count++;
+        else {
+            out[prev] = count;
+            count = 0;
+            prev = j;
+        }
+    }
+    // NB: the run that reaches the end of the array is never written back (segment_offset.cc) -- kept
+    ms.add_u(THREAD_META, "segment_offset", id, std::move(out));
+    record(rec, "segment_offset", id);
+}
+
+void segment_ptr(meta_data_set &ms, POS_TYPE, int id, recs *rec)
+{
+    const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    const universal_array &T = ms.get(THREAD_META, "first_nz_indices", id);
+    std::vector<uint64_t> out{0};
+    uint64_t count = 0;
+    for (uint64_t j = 0; j + 2 < T.get_len(); j++) {
+        count++;
+        for (uint64_t i = T.u[j] + 1; i < T.u[j + 1]; i++)
+            if (R.u[i] != R.u[i - 1]) count++;
+        out.push_back(count);
+    }
+    ms.add_u(THREAD_META, "segment_ptr", id, std::move(out));
+    record(rec, "segment_ptr", id);
+}
+
+// -------------------------------------------------------------------------------------- merge-thread grouping
+static const universal_array &bmt_first_rows(const meta_data_set &ms, int id)
+{
+    if (ms.is_exist(THREAD_META, "first_row_indices", id)) return ms.get(THREAD_META, "first_row_indices", id);
+    return ms.get(THREAD_META, "first_row_indices_without_ending", id);
+}
+
+static std::vector<uint64_t> sample_with_last(const universal_array &A, uint64_t merge_num)
+{
+    GS_REQUIRE(merge_num >= 1, "merge_num must be >= 1");
+    std::vector<uint64_t> v;
+    for (uint64_t j = 0; j + 1 < A.get_len(); j += merge_num) v.push_back(A.u[j]);
+    v.push_back(A.u.back());
+    return v;
+}
+
+void get_begin_rows_after_merge_thread(meta_data_set &ms, POS_TYPE pos, uint64_t merge_num, int id, recs *rec)
+{
+    ms.add_u(pos, "first_row_indices", id, sample_with_last(bmt_first_rows(ms, id), merge_num));
+    record(rec, "get_begin_rows_after_merge_thread", id);
+}
+
+void get_begin_nzs_after_merge_thread(meta_data_set &ms, POS_TYPE pos, uint64_t merge_num, int id, recs *rec)
+{
+    ms.add_u(pos, "first_nz_indices", id, sample_with_last(ms.get(THREAD_META, "first_nz_indices", id), merge_num));
+    record(rec, "get_begin_nzs_after_merge_thread", id);
+}
+
+static std::vector<uint64_t> relative_in_groups(const universal_array &A, uint64_t merge_num)
+{
+    GS_REQUIRE(merge_num >= 1, "merge_num must be >= 1");
+    std::vector<uint64_t> v;
+    for (uint64_t j = 0; j + 1 < A.get_len(); j += merge_num)
+        for (uint64_t i = j; i < j + merge_num && i + 1 < A.get_len(); i++) v.push_back(A.u[i] - A.u[j]);
+    return v;
+}
+
+void get_begin_rows_relative_to_parent_after_merge_thread(meta_data_set &ms, POS_TYPE pos, uint64_t merge_num, int id, recs *rec)
+{
+    GS_REQUIRE(pos == WARP_META || pos == TBLOCK_META, "pos");
+    // stored at the PARENT level in the reference (get_begin_rows_relative_to_parent_after_merge_thread.cc)
+    ms.add_u(pos, pos == WARP_META ? "first_row_indices_relative_to_BMW" : "first_row_indices_relative_to_BMTB", id,
+             relative_in_groups(bmt_first_rows(ms, id), merge_num));
+    record(rec, "get_begin_rows_relative_to_parent_after_merge_thread", id);
+}
+
+void get_begin_nzs_relative_to_parent_after_merge_thread(meta_data_set &ms, POS_TYPE pos, uint64_t merge_num, int id, recs *rec)
+{
+    GS_REQUIRE(pos == WARP_META || pos == TBLOCK_META, "pos");
+    // stored at THREAD level in the reference (get_begin_nzs_relative_to_parent_after_merge_thread.cc)
+    ms.add_u(THREAD_META, pos == WARP_META ? "first_nz_indices_relative_to_BMW" : "first_nz_indices_relative_to_BMTB", id,
+             relative_in_groups(ms.get(THREAD_META, "first_nz_indices", id), merge_num));
+    record(rec, "get_begin_nzs_relative_to_parent_after_merge_thread", id);
+}
+
+void get_begin_BMTs_after_merge_thread(meta_data_set &ms, POS_TYPE pos, uint64_t merge_num, int id, recs *rec)
+{
+    GS_REQUIRE(merge_num >= 1, "merge_num must be >= 1");
+    uint64_t n = ms.get(THREAD_META, "first_nz_indices", id).get_len() - 1;
+    std::vector<uint64_t> v;
+    for (uint64_t j = 0; j < n; j += merge_num) v.push_back(j);
+    v.push_back(n);
+    ms.add_u(pos, "first_BMT_indices", id, std::move(v));
+    record(rec, "get_begin_BMTs_after_merge_thread", id);
+}
+
+// ------------------------------------------------------------------------------------------ balanced blocking
+std::vector<uint64_t> balanced_begin_rows(const std::vector<uint64_t> &len, uint64_t per)
+{
+    // greedy "whole rows until >= nnz_per_interval" (data_transform_common.cc:960-988)
+    std::vector<uint64_t> v{0};
+    uint64_t cnt = 0, rows = len.size();
+    for (uint64_t i = 0; i < rows; i++) {
+        cnt += len[i];
+        if (cnt >= per) v.push_back(i + 1), cnt = 0;
+    }
+    if (v.back() < rows) v.push_back(rows);
+    return v;
+}
+
+std::vector<uint64_t> balanced_begin_nzs(const std::vector<uint64_t> &len, uint64_t per)
+{
+    // data_transform_common.cc:934-958
+    std::vector<uint64_t> v{0};
+    uint64_t cnt = 0, total = 0;
+    for (uint64_t i = 0; i < len.size(); i++) {
+        cnt += len[i];
+        total += len[i];
+        if (cnt >= per) v.push_back(total), cnt = 0;
+    }
+    if (cnt != 0) v.push_back(total);
+    return v;
+}
+
+void get_begin_rows_after_nnz_blocking_in_row_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t per, recs *rec)
+{
+    GS_REQUIRE(per >= 1, "nnz_per_interval must be >= 1");
+    std::vector<uint64_t> len = row_nnz(ms, id);
+    ms.add_u(pos, "first_row_indices", id, balanced_begin_rows(len, per));
+    record(rec, std::string("get_begin_rows_of_") + level_tag(pos) + "_after_nnz_blocking_in_row_direction", id, ",nnz_per_interval:" + std::to_string(per));
+}
+
+void get_begin_nzs_after_nnz_blocking_in_row_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t per, recs *rec)
+{
+    GS_REQUIRE(per >= 1, "nnz_per_interval must be >= 1");
+    std::vector<uint64_t> len = row_nnz(ms, id);
+    ms.add_u(pos, "first_nz_indices", id, balanced_begin_nzs(len, per));
+    record(rec, std::string("get_begin_nzs_of_") + level_tag(pos) + "_after_nnz_blocking_in_row_direction", id, ",nnz_per_interval:" + std::to_string(per));
+}
+
+void remove_item_of_metadata(meta_data_set &ms, int id, const std::string &name, POS_TYPE pos, recs *rec)
+{
+    ms.remove(pos, name, id);
+    record(rec, "remove_item_of_metadata", id);
+}
+
+const std::vector<std::string> &covered_reference_step_names()
+{
+    static const std::vector<std::string> names = {
+        "get_row_order_by_length", "reorder_val_by_index", "reorder_col_by_index", "reorder_row_by_index",
+        "remove_empty_row_in_end_of_sub_matrix",
+        "modify_col_indices_by_col_pad_in_sub_matrix", "modify_vals_by_col_pad_in_sub_matrix", "modify_row_indices_by_col_pad_in_sub_matrix",
+        "modify_col_indices_by_nnz_pad", "modify_vals_by_nnz_pad", "modify_row_indices_by_nnz_pad",
+        "modify_col_indices_by_row_pad_in_sub_matrix", "modify_vals_by_row_pad_in_sub_matrix", "modify_row_indices_by_row_pad_in_sub_matrix",
+        "modify_col_indices_by_empty_pad_in_submatrix", "modify_vals_by_empty_pad_in_submatrix", "modify_row_indices_by_empty_pad_in_submatrix",
+        "get_begin_rows_of_BMTBs_after_fixed_blocking_in_row_direction", "get_begin_nzs_of_BMTBs_after_fixed_blocking_in_row_direction",
+        "get_begin_rows_of_BMW_after_fixed_blocking_in_row_direction_without_BMTB", "get_begin_nzs_of_BMW_after_fixed_blocking_in_row_direction_without_BMTB",
+        "get_begin_rows_of_BMW_after_fixed_blocking_in_row_direction_in_BMTB", "get_begin_nzs_of_BMW_after_fixed_blocking_in_row_direction_in_BMTB",
+        "get_begin_rows_of_BMW_after_fixed_blocking_in_row_direction_relative_to_BMTB", "get_begin_nzs_of_BMW_after_fixed_blocking_in_row_direction_relative_to_BMTB",
+        "get_begin_rows_of_BMT_after_fixed_blocking_in_row_direction", "get_begin_nzs_of_BMT_after_fixed_blocking_in_row_direction",
+        "get_begin_rows_of_BMT_after_fixed_blocking_in_row_direction_in_BMTB", "get_begin_nzs_of_BMT_after_fixed_blocking_in_row_direction_in_BMTB",
+        "get_begin_rows_of_BMT_after_fixed_blocking_in_row_direction_in_BMW", "get_begin_nzs_of_BMT_after_fixed_blocking_in_row_direction_in_BMW",
+        "get_begin_rows_of_BMT_after_fixed_blocking_in_row_direction_relative_to_BMTB", "get_begin_nzs_of_BMT_after_fixed_blocking_in_row_direction_relative_to_BMTB",
+        "get_begin_rows_of_BMT_after_fixed_blocking_in_row_direction_relative_to_BMW", "get_begin_nzs_of_BMT_after_fixed_blocking_in_row_direction_relative_to_BMW",
+        "get_begin_BMWs_of_BMTB_after_blocking_in_row_direction", "get_begin_BMTs_of_specific_parent_after_blocking_in_row_direction",
+        "get_begin_BMTs_of_specific_parent_after_blocking", "get_begin_BMWs_of_BMTB_after_blocking",
+        "get_begin_rows_of_BMT_after_fixed_blocking_in_col_direction", "get_begin_nzs_of_BMT_after_fixed_blocking_in_col_direction",
+        "get_begin_rows_of_BMW_after_fixed_blocking_in_col_direction", "get_begin_nzs_of_BMW_after_fixed_blocking_in_col_direction",
+        "get_begin_rows_of_BMTB_after_fixed_blocking_in_col_direction", "get_begin_nzs_of_BMTB_after_fixed_blocking_in_col_direction",
+        "get_begin_rows_of_BMT_after_fixed_blocking_in_nnz_direction", "get_begin_nzs_of_BMT_after_fixed_blocking_in_nnz_direction",
+        "get_begin_rows_of_BMW_after_fixed_blocking_in_nnz_direction", "get_begin_nzs_of_BMW_after_fixed_blocking_in_nnz_direction",
+        "get_begin_rows_of_BMTB_after_fixed_blocking_in_nnz_direction", "get_begin_nzs_of_BMTB_after_fixed_blocking_in_nnz_direction",
+        "get_BMT_size_of_each_parent",
+        "thread_bit_map", "parent_bit_map_of_thread", "segment_empty_flag", "segment_empty_row_indices", "segment_offset", "segment_ptr",
+        "get_begin_rows_after_merge_thread", "get_begin_nzs_after_merge_thread", "get_begin_rows_relative_to_parent_after_merge_thread",
+        "get_begin_nzs_relative_to_parent_after_merge_thread", "get_begin_BMTs_after_merge_thread",
+        "get_begin_rows_of_BMT_after_nnz_blocking_in_row_direction", "get_begin_nzs_of_BMT_after_nnz_blocking_in_row_direction",
+        "get_begin_rows_of_BMW_after_nnz_blocking_in_row_direction", "get_begin_nzs_of_BMW_after_nnz_blocking_in_row_direction",
+        "get_begin_rows_of_BMTB_after_nnz_blocking_in_row_direction", "get_begin_nzs_of_BMTB_after_nnz_blocking_in_row_direction",
+        "remove_item_of_metadata"};
+    return names;
+}
+
+} // namespace steps
+} // namespace gs
