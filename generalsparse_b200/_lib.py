@@ -1,0 +1,96 @@
+"""ctypes binding of libgsparse_b200.so (include/gsparse_b200.h).
+
+The library is built in-tree by `__graft_entry__.build()` / `make -C generalsparse_b200/csrc`.
+There is NO fallback: if the shared library is missing, importing the engine fails loudly.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libgsparse_b200.so")
+
+# every symbol include/gsparse_b200.h declares (tests check that the .so exports all of them)
+SYMBOLS = [
+    "gs_last_error", "gs_version", "gs_family_name",
+    "gsh_metadata_from_mtx", "gsh_metadata_from_coo", "gsh_metadata_free", "gsh_metadata_count", "gsh_metadata_key",
+    "gsh_metadata_info", "gsh_metadata_read_u64", "gsh_metadata_read_f64", "gsh_metadata_set_vals", "gsh_metadata_dump",
+    "gsh_metadata_check", "gsh_config_load", "gsh_config_set", "gsh_config_get",
+    "gsh_session_create", "gsh_session_free", "gsh_session_add_and_run", "gsh_session_record_count", "gsh_session_record",
+    "gsh_session_run_family", "gsh_session_compile", "gsh_session_plan_desc", "gsh_partition_rows_balanced",
+    "gs_create", "gs_destroy", "gs_stream", "gs_upload_array", "gs_upload_session", "gs_plan_create", "gs_plan_destroy",
+    "gs_plan_set_kernel", "gs_set_dense", "gs_set_dense_device", "gs_launch", "gs_run", "gs_get_output", "gs_output_device",
+    "gs_spmm_host", "gs_plan_algorithmic_bytes", "gs_plan_launch_count", "gs_plan_kernel_name", "gs_execute",
+]
+
+(GS_U8, GS_U16, GS_U32, GS_U64, GS_F32, GS_F64, GS_F16) = range(7)
+(GLOBAL_META, TBLOCK_META, WARP_META, THREAD_META) = range(4)
+FAMILIES = ["thread_total", "warp_total", "warp_bitmap", "thread_bit_map", "warp_segment", "block_total", "block_bitmap",
+            "b200_row_smem", "b200_tcgen05"]
+FAMILY_ID = {n: i for i, n in enumerate(FAMILIES)}
+STATUS = {0: "GS_OK", 1: "GS_ERR_INVALID", 2: "GS_ERR_CUDA", 3: "GS_ERR_UNSUPPORTED", 4: "GS_ERR_NOT_FOUND",
+          5: "GS_ERR_PADDING_RATE", 6: "GS_ERR_INTERNAL"}
+
+
+class PlanDesc(C.Structure):
+    _fields_ = [("family", C.c_int32), ("sub_matrix_id", C.c_int32), ("sparse_coarsen", C.c_int32), ("coarsen", C.c_int32),
+                ("vector_width", C.c_int32), ("need_warp_reduction", C.c_int32), ("thread_for_row", C.c_int32),
+                ("has_row_permutation", C.c_int32), ("grid", C.c_uint32 * 2), ("block", C.c_uint32 * 2),
+                ("rows", C.c_uint64), ("cols", C.c_uint64), ("origin_nnz", C.c_uint64), ("stored_nnz", C.c_uint64),
+                ("n_deps", C.c_int32), ("deps", (C.c_char * 64) * 16)]
+
+
+class GsError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__("%s: %s" % (STATUS.get(status, status), msg))
+        self.status = status
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("libgsparse_b200.so is not built (%s); run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "-- there is no CPU or PyTorch fallback for the SpMM path" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, cp, i32, u64, sz = C.c_void_p, C.c_char_p, C.c_int, C.c_uint64, C.c_size_t
+    P = C.POINTER
+    sig = {
+        "gs_last_error": (cp, []), "gs_version": (cp, []), "gs_family_name": (cp, [i32]),
+        "gsh_metadata_from_mtx": (i32, [cp, cp, i32, P(vp)]),
+        "gsh_metadata_from_coo": (i32, [u64, u64, u64, vp, vp, vp, P(vp)]),
+        "gsh_metadata_free": (None, [vp]), "gsh_metadata_count": (u64, [vp]),
+        "gsh_metadata_key": (i32, [vp, u64, cp, sz]),
+        "gsh_metadata_info": (i32, [vp, cp, P(u64), P(i32), P(i32)]),
+        "gsh_metadata_read_u64": (i32, [vp, cp, vp, u64]), "gsh_metadata_read_f64": (i32, [vp, cp, vp, u64]),
+        "gsh_metadata_set_vals": (i32, [vp, i32, vp, u64]), "gsh_metadata_dump": (i32, [vp, cp]),
+        "gsh_metadata_check": (i32, [vp]),
+        "gsh_config_load": (i32, [cp]), "gsh_config_set": (i32, [cp, cp]), "gsh_config_get": (i32, [cp, cp, sz]),
+        "gsh_session_create": (i32, [vp, i32, P(vp)]), "gsh_session_free": (None, [vp]),
+        "gsh_session_add_and_run": (i32, [vp, cp, vp, i32]), "gsh_session_record_count": (u64, [vp]),
+        "gsh_session_record": (i32, [vp, u64, cp, sz]), "gsh_session_run_family": (i32, [vp, i32, i32, i32, i32]),
+        "gsh_session_compile": (i32, [vp]), "gsh_session_plan_desc": (i32, [vp, P(PlanDesc)]),
+        "gsh_partition_rows_balanced": (i32, [vp, u64, i32, vp]),
+        "gs_create": (i32, [P(vp), i32]), "gs_destroy": (None, [vp]), "gs_stream": (vp, [vp]),
+        "gs_upload_array": (i32, [vp, cp, vp, u64, i32, i32]), "gs_upload_session": (i32, [vp, vp, i32]),
+        "gs_plan_create": (i32, [vp, P(PlanDesc), i32, i32, P(vp)]), "gs_plan_destroy": (None, [vp]),
+        "gs_plan_set_kernel": (i32, [vp, i32]), "gs_set_dense": (i32, [vp, vp, i32]), "gs_set_dense_device": (i32, [vp, vp]),
+        "gs_launch": (i32, [vp]), "gs_run": (i32, [vp, i32, P(C.c_float)]), "gs_get_output": (i32, [vp, vp]),
+        "gs_output_device": (vp, [vp]), "gs_spmm_host": (i32, [vp, vp, vp]),
+        "gs_plan_algorithmic_bytes": (u64, [vp]), "gs_plan_launch_count": (i32, [vp]), "gs_plan_kernel_name": (cp, [vp]),
+        "gs_execute": (i32, [vp, i32, P(C.c_float), P(C.c_float)]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = L
+    return L
+
+
+def check(status):
+    if status != 0:
+        raise GsError(status, lib().gs_last_error().decode())

@@ -1,0 +1,263 @@
+"""Python mirror of the reference's operator-facing interface for the SpMM path.
+
+Thin wrappers over the C ABI (include/gsparse_b200.h): the work happens in libgsparse_b200.so
+(C++ operator graph + CUDA kernels).  Names follow the reference: meta_data_set
+(metadata_set.hpp:103), code_generator/operator_executer (code_generator.hpp:48,
+operator_executer.hpp:10), test_spmm_<family> chains (token_test.cc:1003-1582),
+execute_binary (executor.hpp:15).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import FAMILIES, FAMILY_ID, GsError, PlanDesc, check, lib
+
+_NP2GS = {np.dtype(np.uint8): _lib.GS_U8, np.dtype(np.uint16): _lib.GS_U16, np.dtype(np.uint32): _lib.GS_U32,
+          np.dtype(np.uint64): _lib.GS_U64, np.dtype(np.float32): _lib.GS_F32, np.dtype(np.float64): _lib.GS_F64,
+          np.dtype(np.float16): _lib.GS_F16}
+_GS2NAME = {0: "UNSIGNED_CHAR", 1: "UNSIGNED_SHORT", 2: "UNSIGNED_INT", 3: "UNSIGNED_LONG", 4: "FLOAT", 5: "DOUBLE"}
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def config_set(key, value):
+    if isinstance(value, bool):
+        v = "true" if value else "false"
+    elif isinstance(value, (int, float)):
+        v = repr(value)
+    else:
+        v = '"%s"' % value
+    check(lib().gsh_config_set(key.encode(), v.encode()))
+
+
+def config_get(key):
+    buf = C.create_string_buffer(512)
+    check(lib().gsh_config_get(key.encode(), buf, 512))
+    return buf.value.decode()
+
+
+class MetaDataSet:
+    """meta_data_set of one matrix (create_init_metadata_set_from_file, metadata_set.cc:612)."""
+
+    def __init__(self, handle):
+        self._h = handle
+
+    @classmethod
+    def from_mtx(cls, path, float_precise="float", reference_ones=True):
+        h = C.c_void_p()
+        check(lib().gsh_metadata_from_mtx(path.encode(), float_precise.encode(), int(reference_ones), C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def from_coo(cls, rows, cols, row, col, vals=None):
+        row = np.ascontiguousarray(row, dtype=np.int64)
+        col = np.ascontiguousarray(col, dtype=np.int64)
+        v = None if vals is None else np.ascontiguousarray(vals, dtype=np.float32)
+        h = C.c_void_p()
+        check(lib().gsh_metadata_from_coo(rows, cols, len(row), _ptr(row), _ptr(col), None if v is None else _ptr(v), C.byref(h)))
+        return cls(h)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().gsh_metadata_free(self._h)
+            self._h = None
+
+    def keys(self):
+        n = lib().gsh_metadata_count(self._h)
+        buf = C.create_string_buffer(256)
+        out = []
+        for i in range(n):
+            check(lib().gsh_metadata_key(self._h, i, buf, 256))
+            out.append(buf.value.decode())
+        return out
+
+    def info(self, key):
+        n, m, c = C.c_uint64(), C.c_int(), C.c_int()
+        check(lib().gsh_metadata_info(self._h, key.encode(), C.byref(n), C.byref(m), C.byref(c)))
+        return n.value, _GS2NAME[m.value], _GS2NAME[c.value]
+
+    def __contains__(self, key):
+        return key in self.keys()
+
+    def __getitem__(self, key):
+        n, mem, _ = self.info(key)
+        if mem in ("FLOAT", "DOUBLE"):
+            a = np.empty(n, dtype=np.float64)
+            check(lib().gsh_metadata_read_f64(self._h, key.encode(), _ptr(a), n))
+        else:
+            a = np.empty(n, dtype=np.uint64)
+            check(lib().gsh_metadata_read_u64(self._h, key.encode(), _ptr(a), n))
+        return a
+
+    def set_vals(self, vals, sub_matrix_id=0):
+        v = np.ascontiguousarray(vals, dtype=np.float32)
+        check(lib().gsh_metadata_set_vals(self._h, sub_matrix_id, _ptr(v), len(v)))
+
+    def dump(self, directory):
+        check(lib().gsh_metadata_dump(self._h, directory.encode()))
+
+    def check(self):
+        check(lib().gsh_metadata_check(self._h))
+
+
+class Session:
+    """code_generator + operator_executer of one sub-matrix."""
+
+    def __init__(self, ms, sub_matrix_id=0):
+        self.ms = ms
+        h = C.c_void_p()
+        check(lib().gsh_session_create(ms._h, sub_matrix_id, C.byref(h)))
+        self._h = h
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().gsh_session_free(self._h)
+            self._h = None
+
+    def add_and_run(self, op_name, *args):
+        a = np.array([int(x) for x in args], dtype=np.int64)
+        check(lib().gsh_session_add_and_run(self._h, op_name.encode(), _ptr(a) if len(a) else None, len(a)))
+        return self
+
+    def run_family(self, family, N, sparse_coarsen=1, coarsen=1):
+        fid = FAMILY_ID[family] if isinstance(family, str) else family
+        check(lib().gsh_session_run_family(self._h, fid, N, sparse_coarsen, coarsen))
+        return self
+
+    def compile(self):
+        check(lib().gsh_session_compile(self._h))
+        return self
+
+    def records(self):
+        n = lib().gsh_session_record_count(self._h)
+        buf = C.create_string_buffer(1024)
+        out = []
+        for i in range(n):
+            check(lib().gsh_session_record(self._h, i, buf, 1024))
+            out.append(buf.value.decode())
+        return out
+
+    def plan_desc(self):
+        d = PlanDesc()
+        check(lib().gsh_session_plan_desc(self._h, C.byref(d)))
+        return d
+
+    def deps(self):
+        d = self.plan_desc()
+        return [bytes(d.deps[i]).split(b"\0")[0].decode() for i in range(d.n_deps)]
+
+
+def partition_rows_balanced(row_nnz, G):
+    rn = np.ascontiguousarray(row_nnz, dtype=np.uint64)
+    out = np.empty(G + 1, dtype=np.uint64)
+    check(lib().gsh_partition_rows_balanced(_ptr(rn), len(rn), G, _ptr(out)))
+    return out
+
+
+class Engine:
+    """Device context (gs_ctx): replaces executor.cc's compile-and-fork."""
+
+    def __init__(self, device_id=0):
+        h = C.c_void_p()
+        check(lib().gs_create(C.byref(h), device_id))
+        self._h = h
+        self.device_id = device_id
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().gs_destroy(self._h)
+            self._h = None
+
+    @property
+    def stream(self):
+        return lib().gs_stream(self._h)
+
+    def upload_array(self, key, arr, half=False):
+        a = np.ascontiguousarray(arr)
+        check(lib().gs_upload_array(self._h, key.encode(), _ptr(a), a.size, _NP2GS[a.dtype], int(half)))
+
+    def upload_session(self, session, half=False):
+        check(lib().gs_upload_session(self._h, session._h, int(half)))
+
+    def plan(self, session_or_desc, N, half=False, kernel=None):
+        desc = session_or_desc.plan_desc() if isinstance(session_or_desc, Session) else session_or_desc
+        h = C.c_void_p()
+        check(lib().gs_plan_create(self._h, C.byref(desc), N, int(half), C.byref(h)))
+        p = Plan(self, h, desc, N, half)
+        if kernel is not None:
+            p.set_kernel(kernel)
+        return p
+
+
+class Plan:
+    def __init__(self, engine, handle, desc, N, half):
+        self.engine, self._h, self.desc, self.N, self.half = engine, handle, desc, N, half
+        self.vdtype = np.float16 if half else np.float32
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().gs_plan_destroy(self._h)
+            self._h = None
+
+    def set_kernel(self, family):
+        fid = FAMILY_ID[family] if isinstance(family, str) else family
+        check(lib().gs_plan_set_kernel(self._h, fid))
+
+    def set_dense(self, B):
+        B = np.ascontiguousarray(B)
+        assert B.shape == (self.desc.cols, self.N), (B.shape, self.desc.cols, self.N)
+        check(lib().gs_set_dense(self._h, _ptr(B), _NP2GS[B.dtype]))
+
+    def set_dense_device(self, ptr):
+        check(lib().gs_set_dense_device(self._h, C.c_void_p(ptr)))
+
+    def launch(self):
+        check(lib().gs_launch(self._h))
+
+    def run(self, repeat=1):
+        ms = C.c_float()
+        check(lib().gs_run(self._h, repeat, C.byref(ms)))
+        return ms.value
+
+    def output(self):
+        out = np.empty((self.desc.rows, self.N), dtype=self.vdtype)
+        check(lib().gs_get_output(self._h, _ptr(out)))
+        return out
+
+    def output_device(self):
+        return lib().gs_output_device(self._h)
+
+    def spmm_host(self, B, out=None):
+        B = np.ascontiguousarray(B, dtype=self.vdtype)
+        if out is None:
+            out = np.empty((self.desc.rows, self.N), dtype=self.vdtype)
+        check(lib().gs_spmm_host(self._h, _ptr(B), _ptr(out)))
+        return out
+
+    def spmm_host_ptr(self, b_ptr, c_ptr):
+        check(lib().gs_spmm_host(self._h, C.c_void_p(b_ptr), C.c_void_p(c_ptr)))
+
+    def execute(self, repeat):
+        """execute_binary(path, matrix, &ms_total, &gflops) of executor.hpp:15"""
+        ms, gf = C.c_float(), C.c_float()
+        check(lib().gs_execute(self._h, repeat, C.byref(ms), C.byref(gf)))
+        return ms.value, gf.value
+
+    @property
+    def algorithmic_bytes(self):
+        return lib().gs_plan_algorithmic_bytes(self._h)
+
+    @property
+    def launch_count(self):
+        return lib().gs_plan_launch_count(self._h)
+
+    @property
+    def kernel_name(self):
+        return lib().gs_plan_kernel_name(self._h).decode()
+
+
+__all__ = ["MetaDataSet", "Session", "Engine", "Plan", "GsError", "FAMILIES", "FAMILY_ID", "config_set", "config_get",
+           "partition_rows_balanced"]

@@ -1,0 +1,314 @@
+// gsh_* entry points of include/gsparse_b200.h: the host side (metadata store, operator graph).
+// Pure C++; nothing here touches CUDA, so these calls work on a box without a GPU.
+#include "capi_internal.hpp"
+
+#include <cstring>
+
+using namespace gs;
+
+namespace gs {
+thread_local std::string g_last_error;
+
+gs_status fail(gs_status st, const std::string &msg)
+{
+    g_last_error = msg;
+    return st;
+}
+
+gs_status translate_exception()
+{
+    try {
+        throw;
+    } catch (const gs::Error &e) {
+        std::string m = e.what();
+        if (m.find("padding rate") != std::string::npos) return fail(GS_ERR_PADDING_RATE, m);
+        if (m.find("no metadata item") != std::string::npos || m.find("did not produce") != std::string::npos) return fail(GS_ERR_NOT_FOUND, m);
+        if (m.find("not built") != std::string::npos || m.find("unbuilt") != std::string::npos) return fail(GS_ERR_UNSUPPORTED, m);
+        if (m.find("CUDA") != std::string::npos || m.find("cuda") != std::string::npos) return fail(GS_ERR_CUDA, m);
+        return fail(GS_ERR_INVALID, m);
+    } catch (const std::bad_alloc &) {
+        return fail(GS_ERR_INTERNAL, "out of host memory");
+    } catch (const std::exception &e) {
+        return fail(GS_ERR_INTERNAL, e.what());
+    } catch (...) {
+        return fail(GS_ERR_INTERNAL, "unknown failure");
+    }
+}
+} // namespace gs
+
+#define GS_API_BEGIN try {
+#define GS_API_END                                                                                                                 \
+    return GS_OK;                                                                                                                  \
+    }                                                                                                                              \
+    catch (...) { return gs::translate_exception(); }
+
+static gs_status copy_out(const std::string &s, char *buf, size_t n)
+{
+    if (!buf || n == 0) return fail(GS_ERR_INVALID, "null buffer");
+    if (s.size() + 1 > n) return fail(GS_ERR_INVALID, "buffer too small");
+    memcpy(buf, s.c_str(), s.size() + 1);
+    return GS_OK;
+}
+
+static int to_gs_dtype(data_type t)
+{
+    switch (t) {
+    case UNSIGNED_CHAR: return GS_U8;
+    case UNSIGNED_SHORT: return GS_U16;
+    case UNSIGNED_INT: return GS_U32;
+    case UNSIGNED_LONG: return GS_U64;
+    case FLOAT: return GS_F32;
+    default: return GS_F64;
+    }
+}
+
+extern "C" {
+
+const char *gs_last_error(void) { return g_last_error.c_str(); }
+const char *gs_version(void) { return "gsparse_b200 0.1 (sm_100a)"; }
+const char *gs_family_name(int f)
+{
+    static const char *n[] = {"thread_total", "warp_total", "warp_bitmap", "thread_bit_map", "warp_segment",
+                              "block_total", "block_bitmap", "b200_row_smem", "b200_tcgen05"};
+    return (f >= 0 && f < GS_FAMILY_COUNT) ? n[f] : "unknown";
+}
+
+gs_status gsh_metadata_from_mtx(const char *path, const char *float_precise, int reference_ones, gsh_metadata **out)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(path && out, "null argument");
+    auto h = new gsh_metadata;
+    try {
+        h->ms = create_init_metadata_set_from_file(path, path, float_precise ? float_precise : "float", reference_ones != 0);
+    } catch (...) {
+        delete h;
+        throw;
+    }
+    *out = h;
+    GS_API_END
+}
+
+gs_status gsh_metadata_from_coo(uint64_t rows, uint64_t cols, uint64_t nnz, const int64_t *row, const int64_t *col, const float *vals,
+                                gsh_metadata **out)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(row && col && out, "null argument");
+    auto h = new gsh_metadata;
+    try {
+        h->ms = create_init_metadata_set_from_coo(rows, cols, nnz, row, col, vals, get_config().as_string("PRECISE_OF_FLOAT"));
+    } catch (...) {
+        delete h;
+        throw;
+    }
+    *out = h;
+    GS_API_END
+}
+
+void gsh_metadata_free(gsh_metadata *ms) { delete ms; }
+
+uint64_t gsh_metadata_count(const gsh_metadata *ms) { return ms ? ms->ms->keys().size() : 0; }
+
+gs_status gsh_metadata_key(const gsh_metadata *ms, uint64_t i, char *buf, size_t n)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ms, "null metadata");
+    auto k = ms->ms->keys();
+    GS_REQUIRE(i < k.size(), "item index out of range");
+    return copy_out(k[i], buf, n);
+    GS_API_END
+}
+
+gs_status gsh_metadata_info(const gsh_metadata *ms, const char *key, uint64_t *len, int *mem_dtype, int *compressed_dtype)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ms && key, "null argument");
+    const universal_array *a = ms->ms->find_key(key);
+    if (!a) return fail(GS_ERR_NOT_FOUND, std::string("no metadata item ") + key);
+    if (len) *len = a->get_len();
+    if (mem_dtype) *mem_dtype = to_gs_dtype(a->type);
+    if (compressed_dtype) *compressed_dtype = to_gs_dtype(a->get_compress_data_type(get_config().as_bool("DATA_TYPE_COMPRESS")));
+    GS_API_END
+}
+
+gs_status gsh_metadata_read_u64(const gsh_metadata *ms, const char *key, uint64_t *dst, uint64_t cap)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ms && key && dst, "null argument");
+    const universal_array *a = ms->ms->find_key(key);
+    if (!a) return fail(GS_ERR_NOT_FOUND, std::string("no metadata item ") + key);
+    GS_REQUIRE(!a->is_float(), "item holds values, read it as f64");
+    GS_REQUIRE(cap >= a->get_len(), "destination too small");
+    memcpy(dst, a->u.data(), a->u.size() * sizeof(uint64_t));
+    GS_API_END
+}
+
+gs_status gsh_metadata_read_f64(const gsh_metadata *ms, const char *key, double *dst, uint64_t cap)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ms && key && dst, "null argument");
+    const universal_array *a = ms->ms->find_key(key);
+    if (!a) return fail(GS_ERR_NOT_FOUND, std::string("no metadata item ") + key);
+    GS_REQUIRE(a->is_float(), "item holds integers, read it as u64");
+    GS_REQUIRE(cap >= a->get_len(), "destination too small");
+    memcpy(dst, a->f.data(), a->f.size() * sizeof(double));
+    GS_API_END
+}
+
+gs_status gsh_metadata_set_vals(gsh_metadata *ms, int id, const float *vals, uint64_t n)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ms && vals, "null argument");
+    universal_array &v = ms->ms->get(GLOBAL_META, "nz_vals", id);
+    GS_REQUIRE(v.get_len() == n, "value count differs from the stored non-zero count");
+    for (uint64_t i = 0; i < n; i++) v.f[i] = (double)vals[i];
+    GS_API_END
+}
+
+gs_status gsh_metadata_dump(const gsh_metadata *ms, const char *dir)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ms && dir, "null argument");
+    ms->ms->output_2_dir(dir);
+    GS_API_END
+}
+
+gs_status gsh_metadata_check(const gsh_metadata *ms)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ms, "null metadata");
+    GS_REQUIRE(ms->ms->check(), "meta_data_set::check failed");
+    GS_API_END
+}
+
+gs_status gsh_config_load(const char *path)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(path, "null path");
+    get_config().load(path);
+    GS_API_END
+}
+
+gs_status gsh_config_set(const char *key, const char *json_scalar)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(key && json_scalar, "null argument");
+    get_config().set(key, json_scalar);
+    GS_API_END
+}
+
+gs_status gsh_config_get(const char *key, char *buf, size_t n)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(key, "null key");
+    if (!get_config().has(key)) return fail(GS_ERR_NOT_FOUND, std::string("no config key ") + key);
+    return copy_out(get_config().as_string(key), buf, n);
+    GS_API_END
+}
+
+gs_status gsh_session_create(gsh_metadata *ms, int id, gsh_session **out)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ms && out, "null argument");
+    auto s = new gsh_session;
+    try {
+        s->ms = ms->ms;
+        s->cg = std::make_shared<code_generator>(ms->ms, id);
+    } catch (...) {
+        delete s;
+        throw;
+    }
+    *out = s;
+    GS_API_END
+}
+
+void gsh_session_free(gsh_session *s) { delete s; }
+
+static void harvest(gsh_session *s, const std::shared_ptr<basic_operator> &op)
+{
+    s->records.push_back(op->convert_to_string());
+    for (const auto &r : op->get_data_transform_sequence()) s->records.push_back(r);
+}
+
+gs_status gsh_session_add_and_run(gsh_session *s, const char *op_name, const int64_t *args, int n_args)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(s && op_name && n_args >= 0 && (args || n_args == 0), "bad argument");
+    std::vector<int64_t> a(args, args + n_args);
+    auto op = make_operator(op_name, s->cg, s->ex.get_operator_context(), a);
+    s->ex.add_and_run(op);
+    harvest(s, op);
+    GS_API_END
+}
+
+uint64_t gsh_session_record_count(const gsh_session *s) { return s ? s->records.size() : 0; }
+
+gs_status gsh_session_record(const gsh_session *s, uint64_t i, char *buf, size_t n)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(s && i < s->records.size(), "record index out of range");
+    return copy_out(s->records[i], buf, n);
+    GS_API_END
+}
+
+gs_status gsh_session_run_family(gsh_session *s, int family, int N, int S, int C)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(s, "null session");
+    run_family_chain(family, s->cg, s->ex, N, S, C);
+    for (int st = 0; st < 3; st++)
+        for (const auto &op : s->ex.get_operator_context()->read_operator_context_arr((operator_stage_type)st, s->cg->get_sub_matrix_id())) harvest(s, op);
+    s->cg->compile();
+    GS_API_END
+}
+
+gs_status gsh_session_compile(gsh_session *s)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(s, "null session");
+    s->cg->compile();
+    GS_API_END
+}
+
+gs_status gsh_session_plan_desc(const gsh_session *s, gs_plan_desc *out)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(s && out, "null argument");
+    const kernel_plan &p = s->cg->plan();
+    memset(out, 0, sizeof(*out));
+    out->family = p.family;
+    out->sub_matrix_id = s->cg->get_sub_matrix_id();
+    out->sparse_coarsen = p.sparse_coarsen, out->coarsen = p.coarsen, out->vector_width = p.vector_width;
+    out->need_warp_reduction = p.need_warp_reduction, out->thread_for_row = p.thread_for_row;
+    out->has_row_permutation = p.has_row_permutation;
+    for (int i = 0; i < 2; i++) out->grid[i] = p.grid[i], out->block[i] = p.block[i];
+    out->rows = p.rows, out->cols = p.cols, out->origin_nnz = p.origin_nnz, out->stored_nnz = p.stored_nnz;
+    GS_REQUIRE(p.deps.size() <= 16, "too many dependencies");
+    out->n_deps = (int)p.deps.size();
+    for (size_t i = 0; i < p.deps.size(); i++) {
+        std::string k = meta_data_set::item_name(p.deps[i].pos, p.deps[i].name, p.deps[i].sub_matrix_id);
+        GS_REQUIRE(k.size() < 64, "key too long");
+        strcpy(out->deps[i], k.c_str());
+    }
+    GS_API_END
+}
+
+gs_status gsh_partition_rows_balanced(const uint64_t *row_nnz, uint64_t rows, int G, uint64_t *out)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(row_nnz && out && rows > 0 && G >= 1, "bad argument");
+    std::vector<uint64_t> len(row_nnz, row_nnz + rows);
+    uint64_t nnz = 0;
+    for (uint64_t l : len) nnz += l;
+    uint64_t per = (nnz + G - 1) / G;
+    if (per == 0) per = 1;
+    std::vector<uint64_t> b = steps::balanced_begin_rows(len, per);
+    // the >= rule can leave fewer or more than G parts: merge a tail, or repeat the end for idle devices
+    std::vector<uint64_t> cut(G + 1, rows);
+    for (int g = 0; g <= G; g++) cut[g] = (size_t)g < b.size() ? b[g] : rows;
+    cut[G] = rows;
+    cut[0] = 0;
+    for (int g = 0; g <= G; g++) out[g] = cut[g];
+    GS_API_END
+}
+
+} // extern "C"

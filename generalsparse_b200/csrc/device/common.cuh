@@ -1,0 +1,81 @@
+// Shared device-side definitions of the SpMM engine (sm_100a only).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace gsd {
+
+// canonical device arrays of one sub-matrix (widened at upload, see engine.cu)
+struct dev_arrays {
+    const void *col = nullptr;  // u16 or u32
+    const void *val = nullptr;  // f32 or f16
+    int col_is_u16 = 0;
+    int val_is_f16 = 0;
+    const uint32_t *perm = nullptr;          // GLOBAL original_nz_row_indices (sorted row -> original row) or null
+    const uint32_t *tb_first_row = nullptr;  // TBLOCK first_row_indices
+    const uint32_t *tb_first_nz = nullptr;   // TBLOCK first_nz_indices
+    const uint32_t *tb_first_bmt = nullptr;  // TBLOCK first_BMT_indices
+    const uint32_t *w_first_row = nullptr;   // WARP first_row_indices
+    const uint32_t *w_first_nz = nullptr;    // WARP first_nz_indices
+    const uint32_t *w_first_bmt = nullptr;   // WARP first_BMT_indices
+    const uint64_t *w_bit_map = nullptr;     // WARP bit_map_of_thread (one word per VECTOR_WIDTH BMTs)
+    const uint32_t *t_first_row = nullptr;   // THREAD first_row_indices (with sentinel)
+    const uint32_t *t_first_row_we = nullptr;// THREAD first_row_indices_without_ending
+    const uint32_t *t_first_nz = nullptr;    // THREAD first_nz_indices (or ..._relative_to_BMW when t_nz_relative)
+    int t_nz_relative = 0;
+    const uint64_t *t_bit_map = nullptr;     // THREAD thread_bit_map
+    const uint32_t *t_head = nullptr;        // THREAD bit_map_of_thread (0/1 per BMT, tblock mode)
+    const uint32_t *t_seg_ptr = nullptr;     // THREAD segment_ptr
+    const uint32_t *t_seg_offset = nullptr;  // THREAD segment_offset
+    const uint64_t *t_seg_empty_flag = nullptr;     // THREAD segment_empty_flag (packed per `size` BMTs)
+    const uint32_t *t_seg_empty_rows = nullptr;     // THREAD segment_empty_row_indices
+    uint32_t n_tb = 0, n_w = 0, n_t = 0;     // block counts at each level (entries - 1 where a sentinel exists)
+    uint64_t nnz = 0;                        // stored (padded) non-zeros
+    uint32_t rows = 0, cols = 0;             // C rows / K
+    uint32_t begin_row = 0;                  // begin_row_index of the sub-matrix
+};
+
+struct launch_params {
+    dev_arrays a;
+    const void *B = nullptr; // K x N row-major, value type
+    void *C = nullptr;       // rows x N row-major, value type
+    int N = 0;
+    int coarsen = 1;
+    int vector_width = 32;   // VECTOR_WIDTH of the chain (BMTs per BMW / flag packing size)
+    int block_size = 32;     // BMTs per BMTB in tblock-bitmap mode
+};
+
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+
+// accumulate into C: fp32 atomics for float, CAS-free half2-unaligned-safe path for half
+__device__ __forceinline__ void atomic_add_out(float *C, size_t idx, float v) { atomicAdd(C + idx, v); }
+__device__ __forceinline__ void atomic_add_out(__half *C, size_t idx, float v) { atomicAdd(C + idx, __float2half_rn(v)); }
+
+// cache-hinted streaming loads for data read exactly once (col/val streams)
+__device__ __forceinline__ uint4 ld_stream_v4(const void *p)
+{
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+
+} // namespace gsd
+
+// launchers (host functions, defined in kernels_ref.cu / kernels_b200.cu); return cudaError_t of the launch
+namespace gsd {
+cudaError_t launch_reference_family(int family, const launch_params &p, cudaStream_t s);
+const char *reference_family_kernel_name(int family);
+
+struct b200_row_plan; // opaque, kernels_b200.cu
+cudaError_t b200_row_prepare(const launch_params &p, int sm_count, b200_row_plan **out, cudaStream_t s);
+cudaError_t b200_row_launch(const b200_row_plan *plan, const launch_params &p, cudaStream_t s);
+void b200_row_free(b200_row_plan *plan);
+const char *b200_row_kernel_name(const b200_row_plan *plan);
+} // namespace gsd

@@ -1,0 +1,510 @@
+// gs_* entry points of include/gsparse_b200.h: device context, array upload, kernel plans,
+// launches and timing.  Replaces the reference's executor (executor.cc:6-105: write text files,
+// fork nvcc, fork a.out, read perf_result) with in-process launches on one CUDA stream.
+#include "../capi_internal.hpp"
+#include "common.cuh"
+
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+using namespace gs;
+
+#define CUDA_TRY(expr)                                                                                         \
+    do {                                                                                                       \
+        cudaError_t e__ = (expr);                                                                              \
+        if (e__ != cudaSuccess) throw gs::Error(std::string("CUDA: ") + cudaGetErrorString(e__) + " at " #expr); \
+    } while (0)
+
+#define GS_API_BEGIN try {
+#define GS_API_END                                                                                             \
+    return GS_OK;                                                                                              \
+    }                                                                                                          \
+    catch (...) { return gs::translate_exception(); }
+
+struct dev_array {
+    void *ptr = nullptr;
+    uint64_t len = 0;
+    int dtype = GS_U32;   // device dtype
+    uint64_t max_value = 0;
+    uint64_t align = 0;   // gcd of all entries (offset arrays): the row alignment vector loads may rely on
+};
+
+struct gs_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    std::map<std::string, dev_array> arrays;
+};
+
+struct gs_plan {
+    gs_ctx *ctx = nullptr;
+    gs_plan_desc desc{};
+    int N = 0;
+    int half = 0;
+    int kernel = 0; // gs_family actually launched
+    gsd::launch_params lp;
+    gsd::b200_row_plan *row_plan = nullptr;
+    void *B_dev = nullptr;  // owned
+    const void *B_use = nullptr;
+    void *C_dev = nullptr;
+    void *B_pinned = nullptr, *C_pinned = nullptr; // staging for pageable host buffers is NOT used; these stay null
+    uint64_t offset_bytes = 0; // bytes of the offset / bitmap arrays the launched kernel reads
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    size_t esz() const { return half ? 2 : 4; }
+};
+
+static uint64_t gcd64(uint64_t a, uint64_t b)
+{
+    while (b) {
+        uint64_t t = a % b;
+        a = b, b = t;
+    }
+    return a;
+}
+
+static bool key_has(const std::string &key, const char *s) { return key.find(s) != std::string::npos; }
+
+// host array (any unsigned width, f32, f64 or f16) -> the device's canonical dtype for that key
+static void upload(gs_ctx *ctx, const std::string &key, const void *host, uint64_t len, int dtype, int half)
+{
+    GS_REQUIRE(host && len > 0, "empty array " + key);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    dev_array d;
+    d.len = len;
+    std::vector<unsigned char> staged;
+    const bool is_val = key_has(key, "nz_vals");
+    if (is_val) {
+        GS_REQUIRE(dtype == GS_F32 || dtype == GS_F64 || dtype == GS_F16, "values must be f16, f32 or f64");
+        d.dtype = half ? GS_F16 : GS_F32;
+        staged.resize(len * (half ? 2 : 4));
+        for (uint64_t i = 0; i < len; i++) {
+            float v = dtype == GS_F32 ? ((const float *)host)[i] : dtype == GS_F64 ? (float)((const double *)host)[i] : __half2float(((const __half *)host)[i]);
+            if (half) ((__half *)staged.data())[i] = __float2half_rn(v);
+            else ((float *)staged.data())[i] = v;
+        }
+    } else {
+        GS_REQUIRE(dtype == GS_U8 || dtype == GS_U16 || dtype == GS_U32 || dtype == GS_U64, "index arrays must be unsigned integers");
+        std::vector<uint64_t> w(len);
+        uint64_t mx = 0, g = 0;
+        for (uint64_t i = 0; i < len; i++) {
+            uint64_t v = dtype == GS_U8 ? ((const uint8_t *)host)[i] : dtype == GS_U16 ? ((const uint16_t *)host)[i] : dtype == GS_U32 ? ((const uint32_t *)host)[i] : ((const uint64_t *)host)[i];
+            w[i] = v;
+            mx = v > mx ? v : mx;
+            g = gcd64(g, v);
+        }
+        d.max_value = mx, d.align = g;
+        const bool is_col = key_has(key, "nz_col_indices");
+        const bool is_bits = key_has(key, "thread_bit_map") || key_has(key, "segment_empty_flag") || (key_has(key, "bit_map_of_thread") && key_has(key, "WARP_META"));
+        if (is_bits) d.dtype = GS_U64;
+        else if (is_col && mx <= 65535ull) d.dtype = GS_U16;
+        else {
+            GS_REQUIRE(mx <= 4294967295ull, key + " does not fit 32-bit device offsets");
+            d.dtype = GS_U32;
+        }
+        size_t es = d.dtype == GS_U64 ? 8 : d.dtype == GS_U16 ? 2 : 4;
+        staged.resize(len * es);
+        for (uint64_t i = 0; i < len; i++) {
+            if (es == 8) ((uint64_t *)staged.data())[i] = w[i];
+            else if (es == 2) ((uint16_t *)staged.data())[i] = (uint16_t)w[i];
+            else ((uint32_t *)staged.data())[i] = (uint32_t)w[i];
+        }
+    }
+    auto it = ctx->arrays.find(key);
+    if (it != ctx->arrays.end()) {
+        cudaFree(it->second.ptr);
+        ctx->arrays.erase(it);
+    }
+    // 16 spare bytes so that 128-bit loads of the last partial vector stay inside the allocation
+    CUDA_TRY(cudaMalloc(&d.ptr, staged.size() + 16));
+    CUDA_TRY(cudaMemcpyAsync(d.ptr, staged.data(), staged.size(), cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->arrays[key] = d;
+}
+
+static const dev_array *find_arr(const gs_ctx *ctx, const char *pos, const char *name, int id)
+{
+    auto it = ctx->arrays.find(std::string(pos) + "_" + name + "_" + std::to_string(id));
+    return it == ctx->arrays.end() ? nullptr : &it->second;
+}
+
+static size_t dsize(int dt) { return dt == GS_U64 || dt == GS_F64 ? 8 : dt == GS_U16 || dt == GS_F16 ? 2 : dt == GS_U8 ? 1 : 4; }
+
+static void bind_arrays(gs_plan *p)
+{
+    gs_ctx *ctx = p->ctx;
+    const int id = p->desc.sub_matrix_id;
+    gsd::dev_arrays &a = p->lp.a;
+    a = gsd::dev_arrays();
+    const dev_array *col = find_arr(ctx, "GLOBAL_META", "nz_col_indices", id), *val = find_arr(ctx, "GLOBAL_META", "nz_vals", id);
+    GS_REQUIRE(col && val, "nz_col_indices / nz_vals of the sub-matrix are not uploaded");
+    GS_REQUIRE(col->len == val->len, "column and value arrays differ in length");
+    GS_REQUIRE((val->dtype == GS_F16) == (p->half != 0), "values were uploaded with a different HALF setting than the plan");
+    a.col = col->ptr, a.val = val->ptr, a.col_is_u16 = col->dtype == GS_U16, a.val_is_f16 = val->dtype == GS_F16;
+    a.nnz = col->len;
+    GS_REQUIRE(col->max_value < p->desc.cols, "a column index exceeds the matrix width");
+    a.rows = (uint32_t)p->desc.rows, a.cols = (uint32_t)p->desc.cols;
+    auto u32 = [&](const char *pos, const char *name, uint64_t *len = nullptr) -> const uint32_t * {
+        const dev_array *d = find_arr(ctx, pos, name, id);
+        if (!d) return nullptr;
+        GS_REQUIRE(d->dtype == GS_U32, std::string(name) + " has an unexpected device type");
+        if (len) *len = d->len;
+        return (const uint32_t *)d->ptr;
+    };
+    auto u64 = [&](const char *pos, const char *name) -> const uint64_t * {
+        const dev_array *d = find_arr(ctx, pos, name, id);
+        if (!d) return nullptr;
+        GS_REQUIRE(d->dtype == GS_U64, std::string(name) + " has an unexpected device type");
+        return (const uint64_t *)d->ptr;
+    };
+    uint64_t n = 0;
+    if (p->desc.has_row_permutation) {
+        a.perm = u32("GLOBAL_META", "original_nz_row_indices");
+        GS_REQUIRE(a.perm, "original_nz_row_indices is not uploaded");
+    }
+    a.tb_first_row = u32("TBLOCK_META", "first_row_indices");
+    a.tb_first_nz = u32("TBLOCK_META", "first_nz_indices", &n);
+    if (a.tb_first_nz) a.n_tb = (uint32_t)(n - 1);
+    a.tb_first_bmt = u32("TBLOCK_META", "first_BMT_indices", &n);
+    if (a.tb_first_bmt) a.n_tb = (uint32_t)(n - 1);
+    a.w_first_row = u32("WARP_META", "first_row_indices");
+    a.w_first_nz = u32("WARP_META", "first_nz_indices", &n);
+    if (a.w_first_nz) a.n_w = (uint32_t)(n - 1);
+    a.w_first_bmt = u32("WARP_META", "first_BMT_indices");
+    a.w_bit_map = u64("WARP_META", "bit_map_of_thread");
+    a.t_first_row = u32("THREAD_META", "first_row_indices");
+    a.t_first_row_we = u32("THREAD_META", "first_row_indices_without_ending", &n);
+    if (a.t_first_row_we) a.n_t = (uint32_t)n;
+    a.t_first_nz = u32("THREAD_META", "first_nz_indices", &n);
+    if (a.t_first_nz) a.n_t = (uint32_t)(n - 1);
+    else {
+        a.t_first_nz = u32("THREAD_META", "first_nz_indices_relative_to_BMW", &n);
+        if (a.t_first_nz) a.t_nz_relative = 1, a.n_t = (uint32_t)n;
+    }
+    a.t_bit_map = u64("THREAD_META", "thread_bit_map");
+    a.t_head = u32("THREAD_META", "bit_map_of_thread");
+    a.t_seg_ptr = u32("THREAD_META", "segment_ptr");
+    a.t_seg_offset = u32("THREAD_META", "segment_offset");
+    a.t_seg_empty_flag = u64("THREAD_META", "segment_empty_flag");
+    a.t_seg_empty_rows = u32("THREAD_META", "segment_empty_row_indices");
+    const dev_array *br = find_arr(ctx, "GLOBAL_META", "begin_row_index", id);
+    (void)br; // sub-matrix 0 of an undivided matrix starts at row 0; divided matrices upload begin_row_index
+}
+
+static void require(bool ok, const char *what)
+{
+    if (!ok) throw gs::Error(std::string("the uploaded arrays do not include ") + what + " needed by this kernel family");
+}
+
+static uint64_t arr_bytes(const gs_ctx *ctx, const char *pos, const char *name, int id)
+{
+    const dev_array *d = find_arr(ctx, pos, name, id);
+    return d ? d->len * dsize(d->dtype) : 0;
+}
+
+static void select_kernel(gs_plan *p, int family)
+{
+    const gsd::dev_arrays &a = p->lp.a;
+    const gs_ctx *ctx = p->ctx;
+    const int id = p->desc.sub_matrix_id;
+    uint64_t ob = 0;
+    auto add = [&](const char *pos, const char *name) { ob += arr_bytes(ctx, pos, name, id); };
+    switch (family) {
+    case GS_FAMILY_THREAD_TOTAL:
+        require(a.t_first_row && a.t_first_nz && !a.t_nz_relative, "THREAD first_row_indices/first_nz_indices");
+        add("THREAD_META", "first_row_indices"), add("THREAD_META", "first_nz_indices");
+        break;
+    case GS_FAMILY_WARP_TOTAL:
+        require(a.w_first_row && a.w_first_nz, "WARP first_row_indices/first_nz_indices");
+        add("WARP_META", "first_row_indices"), add("WARP_META", "first_nz_indices");
+        break;
+    case GS_FAMILY_TBLOCK_TOTAL:
+        require(a.tb_first_row && a.tb_first_nz, "TBLOCK first_row_indices/first_nz_indices");
+        add("TBLOCK_META", "first_row_indices"), add("TBLOCK_META", "first_nz_indices");
+        break;
+    case GS_FAMILY_WARP_BITMAP:
+        require(a.w_first_nz && a.w_bit_map && a.t_first_row_we && a.t_first_nz, "WARP first_nz_indices/bit_map_of_thread, THREAD first_row_indices_without_ending/first_nz_indices");
+        GS_REQUIRE(p->desc.vector_width >= 1 && p->desc.vector_width <= 64, "VECTOR_WIDTH must be 1..64 for the bit map families");
+        add("WARP_META", "first_nz_indices"), add("WARP_META", "bit_map_of_thread"), add("THREAD_META", "first_row_indices_without_ending");
+        add("THREAD_META", a.t_nz_relative ? "first_nz_indices_relative_to_BMW" : "first_nz_indices");
+        break;
+    case GS_FAMILY_TBLOCK_BITMAP:
+        require(a.tb_first_bmt && a.t_first_nz && !a.t_nz_relative && a.t_first_row_we && a.t_head && a.t_seg_offset,
+                "TBLOCK first_BMT_indices, THREAD first_nz_indices/first_row_indices_without_ending/bit_map_of_thread/segment_offset");
+        add("TBLOCK_META", "first_BMT_indices"), add("THREAD_META", "first_nz_indices"), add("THREAD_META", "first_row_indices_without_ending");
+        add("THREAD_META", "bit_map_of_thread"), add("THREAD_META", "segment_offset");
+        break;
+    case GS_FAMILY_THREAD_BITMAP:
+    case GS_FAMILY_WARP_SEGMENT:
+        require(a.t_first_row && a.t_first_nz && !a.t_nz_relative && a.t_bit_map && a.t_seg_ptr && a.t_seg_empty_flag && a.t_seg_empty_rows,
+                "THREAD first_row_indices/first_nz_indices/thread_bit_map/segment_ptr/segment_empty_flag/segment_empty_row_indices");
+        GS_REQUIRE(p->desc.vector_width >= 1 && p->desc.vector_width <= 64, "VECTOR_WIDTH must be 1..64 for the bit map families");
+        add("THREAD_META", "first_row_indices"), add("THREAD_META", "first_nz_indices"), add("THREAD_META", "thread_bit_map");
+        add("THREAD_META", "segment_ptr"), add("THREAD_META", "segment_empty_flag"), add("THREAD_META", "segment_empty_row_indices");
+        break;
+    case GS_FAMILY_B200_ROW_SMEM: {
+        if (p->row_plan) gsd::b200_row_free(p->row_plan), p->row_plan = nullptr;
+        gsd::launch_params lp = p->lp;
+        // row alignment: vector loads need every row offset to be a multiple of 8 (sparse coarsen 8 padding)
+        const char *lvl = (a.t_first_nz && a.t_first_row && !a.t_nz_relative) ? "THREAD_META" : (a.w_first_nz && a.w_first_row) ? "WARP_META" : "TBLOCK_META";
+        const dev_array *rp = find_arr(ctx, lvl, "first_nz_indices", id);
+        require(rp != nullptr, "a row-direction first_nz_indices array");
+        lp.vector_width = (rp->align % 8 == 0) ? 8 : 1;
+        cudaError_t e = gsd::b200_row_prepare(lp, ctx->sm_count, &p->row_plan, ctx->stream);
+        if (e == cudaErrorInvalidValue) throw gs::Error("b200_row_smem: not built for this dense width or chain (needs N in {8,16,32} and a row-direction chain with row block 1)");
+        CUDA_TRY(e);
+        add(lvl, "first_row_indices"), add(lvl, "first_nz_indices");
+        break;
+    }
+    default: throw gs::Error("kernel family not built: " + std::string(gs_family_name(family)));
+    }
+    if (p->desc.has_row_permutation) add("GLOBAL_META", "original_nz_row_indices");
+    p->offset_bytes = ob;
+    p->kernel = family;
+}
+
+static bool uses_atomics(int family)
+{
+    return family == GS_FAMILY_WARP_BITMAP || family == GS_FAMILY_TBLOCK_BITMAP || family == GS_FAMILY_THREAD_BITMAP || family == GS_FAMILY_WARP_SEGMENT;
+}
+
+static void enqueue(gs_plan *p)
+{
+    GS_REQUIRE(p->B_use != nullptr, "gs_set_dense has not been called");
+    gsd::launch_params lp = p->lp;
+    lp.B = p->B_use, lp.C = p->C_dev, lp.N = p->N;
+    if (uses_atomics(p->kernel)) CUDA_TRY(cudaMemsetAsync(p->C_dev, 0, (size_t)p->desc.rows * p->N * p->esz(), p->ctx->stream));
+    if (p->kernel == GS_FAMILY_B200_ROW_SMEM) CUDA_TRY(gsd::b200_row_launch(p->row_plan, lp, p->ctx->stream));
+    else CUDA_TRY(gsd::launch_reference_family(p->kernel, lp, p->ctx->stream));
+}
+
+extern "C" {
+
+gs_status gs_create(gs_ctx **out, int device_id)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(out, "null argument");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) return fail(GS_ERR_CUDA, std::string("CUDA: no usable device (") + cudaGetErrorString(e) + "); the SpMM path has no CPU fallback");
+    GS_REQUIRE(device_id >= 0 && device_id < n, "device id out of range");
+    CUDA_TRY(cudaSetDevice(device_id));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device_id));
+    if (prop.major != 10) return fail(GS_ERR_CUDA, std::string("CUDA: device is sm_") + std::to_string(prop.major) + std::to_string(prop.minor) + ", this library is built for sm_100a only");
+    gs_ctx *c = new gs_ctx;
+    c->device = device_id, c->sm_count = prop.multiProcessorCount;
+    e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete c;
+        CUDA_TRY(e);
+    }
+    *out = c;
+    GS_API_END
+}
+
+void gs_destroy(gs_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    for (auto &kv : ctx->arrays) cudaFree(kv.second.ptr);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+void *gs_stream(gs_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+
+gs_status gs_upload_array(gs_ctx *ctx, const char *key, const void *host, uint64_t len, int dtype, int half)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ctx && key, "null argument");
+    upload(ctx, key, host, len, dtype, half);
+    GS_API_END
+}
+
+gs_status gs_upload_session(gs_ctx *ctx, const gsh_session *s, int half)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ctx && s, "null argument");
+    const kernel_plan &kp = s->cg->plan();
+    for (const auto &d : kp.deps) {
+        const universal_array &a = s->ms->get(d.pos, d.name, d.sub_matrix_id);
+        std::string key = meta_data_set::item_name(d.pos, d.name, d.sub_matrix_id);
+        if (a.is_float()) upload(ctx, key, a.f.data(), a.f.size(), GS_F64, half);
+        else upload(ctx, key, a.u.data(), a.u.size(), GS_U64, half);
+    }
+    GS_API_END
+}
+
+gs_status gs_plan_create(gs_ctx *ctx, const gs_plan_desc *desc, int N, int half, gs_plan **out)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ctx && desc && out, "null argument");
+    GS_REQUIRE(N >= 1, "N must be >= 1");
+    GS_REQUIRE(desc->rows > 0 && desc->cols > 0, "empty shape");
+    GS_REQUIRE(desc->family >= 0 && desc->family < GS_FAMILY_COUNT, "unknown family");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    gs_plan *p = new gs_plan;
+    try {
+        p->ctx = ctx, p->desc = *desc, p->N = N, p->half = half;
+        p->lp.coarsen = desc->coarsen, p->lp.vector_width = desc->vector_width, p->lp.block_size = (int)desc->block[1];
+        p->lp.N = N;
+        bind_arrays(p);
+        select_kernel(p, desc->family);
+        size_t cbytes = (size_t)desc->rows * N * p->esz();
+        CUDA_TRY(cudaMalloc(&p->C_dev, cbytes + 16));
+        CUDA_TRY(cudaMemsetAsync(p->C_dev, 0, cbytes, ctx->stream)); // rows no kernel writes (trimmed trailing empty rows) stay zero
+        CUDA_TRY(cudaEventCreate(&p->ev0));
+        CUDA_TRY(cudaEventCreate(&p->ev1));
+        CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    } catch (...) {
+        gs_plan_destroy(p);
+        throw;
+    }
+    *out = p;
+    GS_API_END
+}
+
+void gs_plan_destroy(gs_plan *p)
+{
+    if (!p) return;
+    cudaSetDevice(p->ctx->device);
+    if (p->row_plan) gsd::b200_row_free(p->row_plan);
+    if (p->B_dev) cudaFree(p->B_dev);
+    if (p->C_dev) cudaFree(p->C_dev);
+    if (p->ev0) cudaEventDestroy(p->ev0);
+    if (p->ev1) cudaEventDestroy(p->ev1);
+    delete p;
+}
+
+gs_status gs_plan_set_kernel(gs_plan *p, int family)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p, "null plan");
+    CUDA_TRY(cudaSetDevice(p->ctx->device));
+    select_kernel(p, family);
+    GS_API_END
+}
+
+gs_status gs_set_dense(gs_plan *p, const void *B_host, int dtype)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p && B_host, "null argument");
+    GS_REQUIRE(dtype == GS_F32 || dtype == GS_F16, "dense B must be f32 or f16");
+    CUDA_TRY(cudaSetDevice(p->ctx->device));
+    size_t n = (size_t)p->desc.cols * p->N;
+    std::vector<unsigned char> conv;
+    const void *src = B_host;
+    if ((dtype == GS_F16) != (p->half != 0)) {
+        conv.resize(n * p->esz());
+        for (size_t i = 0; i < n; i++) {
+            if (p->half) ((__half *)conv.data())[i] = __float2half_rn(((const float *)B_host)[i]);
+            else ((float *)conv.data())[i] = __half2float(((const __half *)B_host)[i]);
+        }
+        src = conv.data();
+    }
+    if (!p->B_dev) CUDA_TRY(cudaMalloc(&p->B_dev, n * p->esz() + 16));
+    CUDA_TRY(cudaMemcpyAsync(p->B_dev, src, n * p->esz(), cudaMemcpyHostToDevice, p->ctx->stream));
+    CUDA_TRY(cudaStreamSynchronize(p->ctx->stream));
+    p->B_use = p->B_dev;
+    GS_API_END
+}
+
+gs_status gs_set_dense_device(gs_plan *p, const void *B_dev)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p && B_dev, "null argument");
+    GS_REQUIRE(((uintptr_t)B_dev & 15) == 0, "device B must be 16-byte aligned");
+    p->B_use = B_dev;
+    GS_API_END
+}
+
+gs_status gs_launch(gs_plan *p)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p, "null plan");
+    CUDA_TRY(cudaSetDevice(p->ctx->device));
+    enqueue(p);
+    GS_API_END
+}
+
+gs_status gs_run(gs_plan *p, int repeat, float *ms_per_iter)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p && repeat >= 1, "bad argument");
+    CUDA_TRY(cudaSetDevice(p->ctx->device));
+    CUDA_TRY(cudaEventRecord(p->ev0, p->ctx->stream));
+    for (int i = 0; i < repeat; i++) enqueue(p);
+    CUDA_TRY(cudaEventRecord(p->ev1, p->ctx->stream));
+    CUDA_TRY(cudaEventSynchronize(p->ev1));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, p->ev0, p->ev1));
+    if (ms_per_iter) *ms_per_iter = ms / repeat;
+    GS_API_END
+}
+
+gs_status gs_get_output(gs_plan *p, void *C_host)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p && C_host, "null argument");
+    CUDA_TRY(cudaSetDevice(p->ctx->device));
+    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, (size_t)p->desc.rows * p->N * p->esz(), cudaMemcpyDeviceToHost, p->ctx->stream));
+    CUDA_TRY(cudaStreamSynchronize(p->ctx->stream));
+    GS_API_END
+}
+
+void *gs_output_device(gs_plan *p) { return p ? p->C_dev : nullptr; }
+
+gs_status gs_spmm_host(gs_plan *p, const void *B_host, void *C_host)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p && B_host && C_host, "null argument");
+    CUDA_TRY(cudaSetDevice(p->ctx->device));
+    size_t nb = (size_t)p->desc.cols * p->N * p->esz(), nc = (size_t)p->desc.rows * p->N * p->esz();
+    if (!p->B_dev) CUDA_TRY(cudaMalloc(&p->B_dev, nb + 16));
+    CUDA_TRY(cudaMemcpyAsync(p->B_dev, B_host, nb, cudaMemcpyHostToDevice, p->ctx->stream));
+    p->B_use = p->B_dev;
+    enqueue(p);
+    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, nc, cudaMemcpyDeviceToHost, p->ctx->stream));
+    CUDA_TRY(cudaStreamSynchronize(p->ctx->stream));
+    GS_API_END
+}
+
+uint64_t gs_plan_algorithmic_bytes(const gs_plan *p)
+{
+    if (!p) return 0;
+    // nnz_stored*(idx+val) + offset arrays + K*N*sizeof(B) + M*N*sizeof(C) (+ permutation)
+    uint64_t idx = p->lp.a.col_is_u16 ? 2 : 4;
+    return p->lp.a.nnz * (idx + p->esz()) + p->offset_bytes + (uint64_t)p->desc.cols * p->N * p->esz() + (uint64_t)p->desc.rows * p->N * p->esz();
+}
+
+int gs_plan_launch_count(const gs_plan *p) { return p ? 1 : 0; }
+
+const char *gs_plan_kernel_name(const gs_plan *p)
+{
+    if (!p) return "";
+    if (p->kernel == GS_FAMILY_B200_ROW_SMEM) return gsd::b200_row_kernel_name(p->row_plan);
+    return gsd::reference_family_kernel_name(p->kernel);
+}
+
+gs_status gs_execute(gs_plan *p, int repeat, float *ms_total, float *gflops)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p && repeat >= 1, "bad argument");
+    CUDA_TRY(cudaSetDevice(p->ctx->device));
+    enqueue(p); // one untimed warm-up launch, as the generated main() does (code_generator.cc:582)
+    CUDA_TRY(cudaStreamSynchronize(p->ctx->stream));
+    CUDA_TRY(cudaEventRecord(p->ev0, p->ctx->stream));
+    for (int i = 0; i < repeat; i++) enqueue(p);
+    CUDA_TRY(cudaEventRecord(p->ev1, p->ctx->stream));
+    CUDA_TRY(cudaEventSynchronize(p->ev1));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, p->ev0, p->ev1));
+    if (ms_total) *ms_total = ms;
+    double rate = gs::get_config().as_float("FLOAT_RATE");
+    if (gflops) *gflops = (float)(rate * (double)p->desc.origin_nnz * p->N * repeat / (ms * 1e-3) / 1e9);
+    GS_API_END
+}
+
+} // extern "C"

@@ -1,0 +1,139 @@
+#include "config.hpp"
+
+#include "metadata.hpp"
+
+#include <cstdlib>
+#include <fstream>
+#include <sstream>
+
+namespace gs {
+
+config_store::config_store()
+{
+    // the keys the path reads, defaults from global_config.json.bak with HALF off
+    kv_ = {{"DATA_SET", "\"\""},
+           {"DATA_TYPE_COMPRESS", "true"},
+           {"DEFAULT_DEVICE_ID", "0"},
+           {"DENSE_MATRIX_SIZE", "8"},
+           {"FLOAT_RATE", "2"},
+           {"GFLOPS_UP_BOUND", "1000000"}, // the reference's 10000 is below what a B200 reaches
+           {"HALF", "false"},
+           {"OPERATOR_RUNTIME_CHECK", "true"},
+           {"PADDING_RATE_UP_BOUND", "4"},
+           {"PRECISE_OF_FLOAT", "\"float\""},
+           {"ROOT_PATH_STR", "\".\""},
+           {"SHARED_MEM_TOTAL_SIZE", "48000"},
+           {"VECTOR_WIDTH", "8"},
+           {"NUM_GPUS", "1"},
+           {"KERNEL_FAMILY", "\"thread_total\""},
+           {"PARITY_MODE", "true"}};
+}
+
+static void skip_ws(const std::string &s, size_t &i)
+{
+    while (i < s.size() && isspace((unsigned char)s[i])) i++;
+}
+
+void config_store::load(const std::string &path)
+{
+    std::ifstream in(path);
+    GS_REQUIRE(in.is_open(), "cannot open config " + path);
+    std::stringstream ss;
+    ss << in.rdbuf();
+    std::string s = ss.str();
+    size_t i = 0;
+    skip_ws(s, i);
+    GS_REQUIRE(i < s.size() && s[i] == '{', "config must be a JSON object");
+    i++;
+    while (true) {
+        skip_ws(s, i);
+        if (i < s.size() && s[i] == '}') break;
+        GS_REQUIRE(i < s.size() && s[i] == '"', "config: expected a key");
+        size_t e = s.find('"', i + 1);
+        GS_REQUIRE(e != std::string::npos, "config: unterminated key");
+        std::string key = s.substr(i + 1, e - i - 1);
+        i = e + 1;
+        skip_ws(s, i);
+        GS_REQUIRE(i < s.size() && s[i] == ':', "config: expected ':'");
+        i++;
+        skip_ws(s, i);
+        size_t b = i;
+        if (s[i] == '"') {
+            i++;
+            while (i < s.size() && s[i] != '"') i += (s[i] == '\\') ? 2 : 1;
+            i++;
+        } else {
+            while (i < s.size() && s[i] != ',' && s[i] != '}' && !isspace((unsigned char)s[i])) i++;
+        }
+        kv_[key] = s.substr(b, i - b);
+        skip_ws(s, i);
+        if (i < s.size() && s[i] == ',') i++;
+    }
+    loaded_from = path;
+}
+
+std::string config_store::as_string(const std::string &key) const
+{
+    auto it = kv_.find(key);
+    if (it == kv_.end()) return "";
+    const std::string &v = it->second;
+    if (v.size() >= 2 && v.front() == '"') return v.substr(1, v.size() - 2);
+    return v;
+}
+
+double config_store::as_float(const std::string &key) const
+{
+    auto it = kv_.find(key);
+    GS_REQUIRE(it != kv_.end(), "config key missing: " + key);
+    return atof(as_string(key).c_str());
+}
+
+bool config_store::as_bool(const std::string &key) const
+{
+    auto it = kv_.find(key);
+    if (it == kv_.end()) return false;
+    return it->second == "true";
+}
+
+void config_store::set(const std::string &key, const std::string &json_value)
+{
+    kv_[key] = json_value;
+    if (write_back && !loaded_from.empty()) save(loaded_from);
+}
+
+void config_store::set_number(const std::string &key, double v)
+{
+    std::ostringstream o;
+    if (v == (long)v) o << (long)v;
+    else o << v;
+    set(key, o.str());
+}
+
+void config_store::save(const std::string &path) const
+{
+    std::ofstream out(path);
+    out << "{\n";
+    size_t n = 0;
+    for (const auto &kv : kv_) out << "    \"" << kv.first << "\": " << kv.second << (++n == kv_.size() ? "\n" : ",\n");
+    out << "}";
+}
+
+config_store &get_config()
+{
+    static config_store c;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        std::ifstream probe("global_config.json");
+        if (probe.is_open()) {
+            probe.close();
+            c.load("global_config.json");
+        }
+    }
+    return c;
+}
+
+void set_config(const std::string &key, double v) { get_config().set_number(key, v); }
+void set_config(const std::string &key, const std::string &v) { get_config().set(key, "\"" + v + "\""); }
+
+} // namespace gs

@@ -1,0 +1,700 @@
+// Concrete operators (operator.hpp:268-1297, operator/*.cc).  Constructor argument order follows the
+// reference's code_generator flavour; args arrive as int64 through make_operator().
+#include "operators.hpp"
+
+#include "../../../include/gsparse_b200.h"
+
+#include <algorithm>
+
+namespace gs {
+
+namespace {
+
+using opv = std::vector<std::shared_ptr<basic_operator>>;
+
+bool any_name_has(const opv &ops, const char *needle)
+{
+    for (const auto &o : ops)
+        if (o->get_name().find(needle) != std::string::npos) return true;
+    return false;
+}
+
+void append(std::vector<std::string> &dst, const steps::recs &src) { dst.insert(dst.end(), src.begin(), src.end()); }
+
+// shared by the row-direction blocking operators: drop a parent level's arrays, re-run the operators
+// that produced them without their own padding (fixed_interval_row_direction_thread_blocking_operator.cc:258-269)
+void drop_level(meta_data_set &ms, POS_TYPE pos, int id, steps::recs &rec)
+{
+    for (const std::string &n : ms.all_item_of_metadata_of_diff_pos(pos, id)) steps::remove_item_of_metadata(ms, id, n, pos, &rec);
+}
+
+void rerun_former(const opv &former, bool check)
+{
+    for (const auto &o : former) {
+        o->set_padding_to_false();
+        o->run(check);
+    }
+}
+
+// ------------------------------------------------------------------------------------------- CONVERTING
+class sort_operator : public basic_operator { // operator.hpp:268, operator/sort_operator.cc:70-108
+  public:
+    explicit sort_operator(std::shared_ptr<code_generator> cg) : basic_operator("sort_operator", std::move(cg), CONVERTING_OP) {}
+    bool is_valid_according_to_metadata() override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        return ms.is_exist(GLOBAL_META, "nz_row_indices", id) && ms.is_exist(GLOBAL_META, "nz_col_indices", id) &&
+               ms.is_exist(GLOBAL_META, "nz_vals", id) && !ms.is_exist(GLOBAL_META, "original_nz_row_indices", id);
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        // sorting is only legal before any distribution (sort_operator.cc is_valid_according_to_operator)
+        return h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id).empty() &&
+               h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty();
+    }
+    void run(bool check) override
+    {
+        if (check) GS_REQUIRE(is_valid_according_to_metadata(), "sort_operator: metadata not sortable (already sorted?)");
+        steps::recs r;
+        steps::get_row_order_by_length(*meta_data_set_ptr, target_matrix_id, &r);
+        steps::reorder_val_by_index(*meta_data_set_ptr, target_matrix_id, &r);
+        steps::reorder_col_by_index(*meta_data_set_ptr, target_matrix_id, &r);
+        steps::reorder_row_by_index(*meta_data_set_ptr, target_matrix_id, &r);
+        steps::remove_empty_row_in_end_of_sub_matrix(*meta_data_set_ptr, target_matrix_id, &r);
+        append(transform_seq, r);
+        is_run = true;
+    }
+};
+
+// ----------------------------------------------------------------------------------------- DISTRIBUTING
+class fixed_interval_row_direction_tblock_blocking_operator : public basic_operator { // operator.hpp:356
+  public:
+    fixed_interval_row_direction_tblock_blocking_operator(std::shared_ptr<code_generator> cg, int b, bool is_padding)
+        : basic_operator("fixed_interval_row_direction_tblock_blocking_operator", std::move(cg), DISTRIBUTING_OP), b_(b), pad_(is_padding)
+    {
+        GS_REQUIRE(b > 0, "fixed_row_block_size must be > 0");
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        return h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id).empty() &&
+               h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty();
+    }
+    void set_padding_to_false() override { pad_ = false; }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        steps::recs r;
+        if (pad_) steps::modify_by_row_pad_in_sub_matrix(ms, id, b_, pad_bound(), &r);
+        steps::get_begin_rows_after_fixed_blocking_in_row_direction(ms, TBLOCK_META, id, b_, &r);
+        steps::get_begin_nzs_after_fixed_blocking_in_row_direction(ms, TBLOCK_META, id, b_, &r);
+        append(transform_seq, r);
+        code_generator_ptr->open_spec_level_of_paral(TBLOCK_META);
+        is_run = true;
+    }
+
+  private:
+    uint64_t b_;
+    bool pad_;
+};
+
+class fixed_interval_row_direction_warp_blocking_operator : public basic_operator { // operator.hpp:398
+  public:
+    fixed_interval_row_direction_warp_blocking_operator(std::shared_ptr<code_generator> cg, int b, bool row_rel, bool nz_rel, bool is_padding)
+        : basic_operator("fixed_interval_row_direction_warp_blocking_operator", std::move(cg), DISTRIBUTING_OP), b_(b), row_rel_(row_rel),
+          nz_rel_(nz_rel), pad_(is_padding)
+    {
+        GS_REQUIRE(b > 0, "fixed_row_block_size must be > 0");
+        if (is_padding) GS_REQUIRE(!row_rel && !nz_rel, "row padding excludes relative indices");
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        return h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty() && !any_name_has(d, "warp") &&
+               !any_name_has(d, "thread") && !any_name_has(d, "col_direction") && !any_name_has(d, "interlance");
+    }
+    void set_padding_to_false() override { pad_ = false; }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        steps::recs r;
+        if (ms.is_exist(TBLOCK_META, "first_row_indices", id)) {
+            steps::get_begin_rows_after_fixed_blocking_in_row_direction_in_parent(ms, WARP_META, TBLOCK_META, id, b_, &r);
+            if (row_rel_) steps::get_begin_rows_after_fixed_blocking_in_row_direction_relative_to_parent(ms, WARP_META, TBLOCK_META, id, b_, &r);
+            steps::get_begin_nzs_after_fixed_blocking_in_row_direction_in_parent(ms, WARP_META, TBLOCK_META, id, b_, &r);
+            if (nz_rel_) steps::get_begin_nzs_after_fixed_blocking_in_row_direction_relative_to_parent(ms, WARP_META, TBLOCK_META, id, b_, &r);
+            steps::get_begin_children_of_parent_after_blocking_in_row_direction(ms, WARP_META, TBLOCK_META, id, &r);
+        } else {
+            GS_REQUIRE(!row_rel_ && !nz_rel_, "relative indices need a BMTB level");
+            if (pad_) steps::modify_by_row_pad_in_sub_matrix(ms, id, b_, pad_bound(), &r);
+            steps::get_begin_rows_after_fixed_blocking_in_row_direction(ms, WARP_META, id, b_, &r);
+            steps::get_begin_nzs_after_fixed_blocking_in_row_direction(ms, WARP_META, id, b_, &r);
+        }
+        append(transform_seq, r);
+        code_generator_ptr->open_spec_level_of_paral(WARP_META);
+        is_run = true;
+    }
+
+  private:
+    uint64_t b_;
+    bool row_rel_, nz_rel_, pad_;
+};
+
+class fixed_interval_row_direction_thread_blocking_operator : public basic_operator { // operator.hpp:598
+  public:
+    fixed_interval_row_direction_thread_blocking_operator(std::shared_ptr<code_generator> cg, int b, bool row_rel, bool nz_rel, bool is_row_padding,
+                                                          bool pad_to_row_max, bool pad_to_col_size, int col_size,
+                                                          std::shared_ptr<operator_context> history)
+        : basic_operator("fixed_interval_row_direction_thread_blocking_operator", std::move(cg), DISTRIBUTING_OP), b_(b), row_rel_(row_rel),
+          nz_rel_(nz_rel), row_pad_(is_row_padding), max_pad_(pad_to_row_max), col_pad_(pad_to_col_size), col_size_(col_size)
+    {
+        GS_REQUIRE(b > 0, "fixed_row_block_size must be > 0");
+        if (is_row_padding) GS_REQUIRE(!row_rel && !nz_rel, "row padding excludes relative indices");
+        former_ = history->read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        // fixed_interval_row_direction_thread_blocking_operator.cc: no implementing operator yet, and no earlier
+        // thread / col-direction / interleave operator (balanced_interval only without max padding)
+        opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        if (!h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty()) return false;
+        bool balanced = any_name_has(d, "balanced_interval") && max_pad_;
+        return !any_name_has(d, "thread") && !any_name_has(d, "col") && !any_name_has(d, "interlance") && !balanced;
+    }
+    void set_padding_to_false() override { row_pad_ = max_pad_ = col_pad_ = false; }
+    void run(bool check) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        steps::recs r;
+        bool has_tb = ms.is_exist(TBLOCK_META, "first_row_indices", id), has_w = ms.is_exist(WARP_META, "first_row_indices", id);
+        if (has_w || has_tb) {
+            POS_TYPE parent = has_w ? WARP_META : TBLOCK_META;
+            if (max_pad_) {
+                steps::modify_by_col_pad_parent_blk_to_max_row_size(ms, parent, id, true, pad_bound(), &r);
+                if (has_w) drop_level(ms, WARP_META, id, r);
+                if (has_tb) drop_level(ms, TBLOCK_META, id, r);
+                rerun_former(former_, check);
+            }
+            if (col_pad_) {
+                steps::modify_by_col_pad_in_sub_matrix(ms, id, col_size_, pad_bound(), &r);
+                if (has_w) drop_level(ms, WARP_META, id, r);
+                if (has_tb) drop_level(ms, TBLOCK_META, id, r);
+                rerun_former(former_, check);
+            }
+            steps::get_begin_rows_after_fixed_blocking_in_row_direction_in_parent(ms, THREAD_META, parent, id, b_, &r);
+            if (row_rel_) steps::get_begin_rows_after_fixed_blocking_in_row_direction_relative_to_parent(ms, THREAD_META, parent, id, b_, &r);
+            steps::get_begin_nzs_after_fixed_blocking_in_row_direction_in_parent(ms, THREAD_META, parent, id, b_, &r);
+            if (nz_rel_) steps::get_begin_nzs_after_fixed_blocking_in_row_direction_relative_to_parent(ms, THREAD_META, parent, id, b_, &r);
+            steps::get_begin_children_of_parent_after_blocking_in_row_direction(ms, THREAD_META, parent, id, &r);
+            if (max_pad_ && b_ == 1) steps::get_BMT_size_of_each_parent(ms, parent, id, true, &r);
+        } else {
+            GS_REQUIRE(!row_rel_ && !nz_rel_, "relative indices need a parent level");
+            if (row_pad_) steps::modify_by_row_pad_in_sub_matrix(ms, id, b_, pad_bound(), &r);
+            if (max_pad_) steps::modify_by_col_pad_parent_blk_to_max_row_size(ms, GLOBAL_META, id, true, pad_bound(), &r);
+            if (col_pad_) steps::modify_by_col_pad_in_sub_matrix(ms, id, col_size_, pad_bound(), &r);
+            steps::get_begin_rows_after_fixed_blocking_in_row_direction(ms, THREAD_META, id, b_, &r);
+            steps::get_begin_nzs_after_fixed_blocking_in_row_direction(ms, THREAD_META, id, b_, &r);
+            if (max_pad_ && b_ == 1) steps::get_BMT_size_of_each_parent(ms, GLOBAL_META, id, true, &r);
+        }
+        append(transform_seq, r);
+        code_generator_ptr->open_spec_level_of_paral(THREAD_META);
+        code_generator_ptr->set_thread_for_row(true);
+        is_run = true;
+    }
+
+  private:
+    uint64_t b_;
+    bool row_rel_, nz_rel_, row_pad_, max_pad_, col_pad_;
+    uint64_t col_size_;
+    opv former_;
+};
+
+class fixed_interval_col_direction_thread_blocking_operator : public basic_operator { // operator.hpp:477
+  public:
+    fixed_interval_col_direction_thread_blocking_operator(std::shared_ptr<code_generator> cg, int col_block, bool row_rel_bmtb, bool nz_rel_bmtb,
+                                                          bool pad_to_col_size, bool pad_to_row_max, std::shared_ptr<operator_context> history)
+        : basic_operator("fixed_interval_col_direction_thread_blocking_operator", std::move(cg), DISTRIBUTING_OP), c_(col_block),
+          row_rel_(row_rel_bmtb), nz_rel_(nz_rel_bmtb), col_pad_(pad_to_col_size), max_pad_(pad_to_row_max)
+    {
+        GS_REQUIRE(col_block > 0, "fixed_col_block_size must be > 0");
+        former_ = history->read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        return h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty() && !any_name_has(d, "thread") && !any_name_has(d, "interlance");
+    }
+    void set_padding_to_false() override { col_pad_ = max_pad_ = false; }
+    void run(bool check) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        steps::recs r;
+        bool has_tb = ms.is_exist(TBLOCK_META, "first_row_indices", id), has_w = ms.is_exist(WARP_META, "first_row_indices", id);
+        if (max_pad_) steps::modify_by_col_pad_parent_blk_to_max_row_size(ms, has_w ? WARP_META : (has_tb ? TBLOCK_META : GLOBAL_META), id, false, pad_bound(), &r);
+        if (col_pad_) steps::modify_by_col_pad_in_sub_matrix(ms, id, c_, pad_bound(), &r);
+        if (col_pad_ || max_pad_) {
+            if (has_tb) drop_level(ms, TBLOCK_META, id, r);
+            if (has_w) drop_level(ms, WARP_META, id, r);
+            rerun_former(former_, check);
+        }
+        steps::get_begin_rows_after_fixed_blocking_in_col_direction(ms, THREAD_META, id, c_, &r);
+        steps::get_begin_nzs_after_fixed_blocking_in_col_direction(ms, THREAD_META, id, c_, &r);
+        GS_REQUIRE(!row_rel_ && !nz_rel_, "col-direction BMT indices relative to a parent: not built yet");
+        if (has_tb) {
+            steps::get_begin_children_of_parent_after_blocking(ms, THREAD_META, TBLOCK_META, id, &r);
+            if (col_pad_) steps::get_BMT_size_of_each_parent(ms, TBLOCK_META, id, false, &r);
+        }
+        if (has_w) {
+            steps::get_begin_children_of_parent_after_blocking(ms, THREAD_META, WARP_META, id, &r);
+            if (col_pad_) steps::get_BMT_size_of_each_parent(ms, WARP_META, id, false, &r);
+        }
+        if (col_pad_) steps::get_BMT_size_of_each_parent(ms, GLOBAL_META, id, false, &r);
+        append(transform_seq, r);
+        code_generator_ptr->open_spec_level_of_paral(THREAD_META);
+        is_run = true;
+    }
+
+  private:
+    uint64_t c_;
+    bool row_rel_, nz_rel_, col_pad_, max_pad_;
+    opv former_;
+};
+
+class fixed_interval_nnz_direction_thread_blocking_operator : public basic_operator { // operator.hpp:906
+  public:
+    fixed_interval_nnz_direction_thread_blocking_operator(std::shared_ptr<code_generator> cg, int nnz_per_bmt, bool row_rel, bool nz_rel, bool nnz_padding)
+        : basic_operator("fixed_interval_nnz_direction_thread_blocking_operator", std::move(cg), DISTRIBUTING_OP), k_(nnz_per_bmt), row_rel_(row_rel),
+          nz_rel_(nz_rel), pad_(nnz_padding)
+    {
+        GS_REQUIRE(nnz_per_bmt > 0, "nnz_per_BMT must be > 0");
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        return h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty() && !any_name_has(d, "thread") && !any_name_has(d, "interlance");
+    }
+    void set_padding_to_false() override { pad_ = false; }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        steps::recs r;
+        bool has_tb = ms.is_exist(TBLOCK_META, "first_row_indices", id), has_w = ms.is_exist(WARP_META, "first_row_indices", id);
+        if (pad_) steps::modify_by_nnz_pad(ms, id, k_, pad_bound(), &r);
+        steps::get_begin_rows_after_fixed_blocking_in_nnz_direction(ms, THREAD_META, id, k_, &r);
+        GS_REQUIRE(!row_rel_ && !nz_rel_, "nnz-direction BMT indices relative to a parent: not built yet");
+        steps::get_begin_nzs_after_fixed_blocking_in_nnz_direction(ms, THREAD_META, id, k_, &r);
+        if (has_w) steps::get_begin_children_of_parent_after_blocking(ms, THREAD_META, WARP_META, id, &r);
+        else if (has_tb) steps::get_begin_children_of_parent_after_blocking(ms, THREAD_META, TBLOCK_META, id, &r);
+        steps::get_BMT_size_of_each_parent(ms, GLOBAL_META, id, false, &r);
+        append(transform_seq, r);
+        code_generator_ptr->open_spec_level_of_paral(THREAD_META);
+        is_run = true;
+    }
+
+  private:
+    uint64_t k_;
+    bool row_rel_, nz_rel_, pad_;
+};
+
+// balanced_interval_row_direction_{tblock,warp,thread}_blocking_operator (operator.hpp:871,823,777), top level
+class balanced_interval_row_direction_blocking_operator : public basic_operator {
+  public:
+    balanced_interval_row_direction_blocking_operator(std::shared_ptr<code_generator> cg, POS_TYPE pos, int nnz_per_interval)
+        : basic_operator(std::string("balanced_interval_row_direction_") + (pos == TBLOCK_META ? "tblock" : pos == WARP_META ? "warp" : "thread") +
+                             "_blocking_operator", std::move(cg), DISTRIBUTING_OP), pos_(pos), per_(nnz_per_interval)
+    {
+        GS_REQUIRE(nnz_per_interval > 0, "nnz_per_interval must be > 0");
+    }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        GS_REQUIRE(ms.count_of_metadata_of_diff_pos(TBLOCK_META, id) + ms.count_of_metadata_of_diff_pos(WARP_META, id) == 0 || pos_ == TBLOCK_META,
+                   "balanced blocking inside a parent level: not built yet");
+        steps::recs r;
+        steps::get_begin_rows_after_nnz_blocking_in_row_direction(ms, pos_, id, per_, &r);
+        steps::get_begin_nzs_after_nnz_blocking_in_row_direction(ms, pos_, id, per_, &r);
+        append(transform_seq, r);
+        code_generator_ptr->open_spec_level_of_paral(pos_);
+        if (pos_ == THREAD_META) code_generator_ptr->set_thread_for_row(true);
+        is_run = true;
+    }
+
+  private:
+    POS_TYPE pos_;
+    uint64_t per_;
+};
+
+class empty_row_pad_operator : public basic_operator { // operator.hpp:449
+  public:
+    explicit empty_row_pad_operator(std::shared_ptr<code_generator> cg) : basic_operator("empty_row_pad_operator", std::move(cg), DISTRIBUTING_OP) {}
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        return h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id).empty() && h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty();
+    }
+    void run(bool) override
+    {
+        steps::recs r;
+        steps::modify_by_empty_pad_in_submatrix(*meta_data_set_ptr, target_matrix_id, &r);
+        append(transform_seq, r);
+        is_run = true;
+    }
+};
+
+// ----------------------------------------------------------------------------------------- IMPLEMENTING
+class thread_total_reduce_operator : public basic_operator { // operator.hpp:1070
+  public:
+    thread_total_reduce_operator(std::shared_ptr<code_generator> cg, bool need_warp_reduction, int S, int C)
+        : basic_operator("thread_total_reduce_operator", std::move(cg), IMPLEMENTING_OP), nwr_(need_warp_reduction), S_(S), C_(C)
+    {
+        GS_REQUIRE(S >= 1 && C >= 1, "coarsen factors must be >= 1");
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        // needs a thread-level distribution and no earlier implementing operator (thread_total_reduce_operator.cc:23-31)
+        return any_name_has(h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id), "thread") &&
+               h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty();
+    }
+    void run(bool) override
+    {
+        reduction_token t;
+        t.kind = RED_TOTAL_BMT, t.need_warp_reduction = nwr_, t.sparse_coarsen_factor = S_, t.coarsen_factor = C_;
+        code_generator_ptr->set_reduction_token(THREAD_META, t);
+        code_generator_ptr->open_spec_level_of_paral(THREAD_META);
+        is_run = true;
+    }
+
+  private:
+    bool nwr_;
+    int S_, C_;
+};
+
+class thread_bit_map_operator : public basic_operator { // operator.hpp:1093, operator/thread_bit_map_operator.cc
+  public:
+    thread_bit_map_operator(std::shared_ptr<code_generator> cg, POS_TYPE pos, int size, int S, int C)
+        : basic_operator("thread_bit_map_operator", std::move(cg), IMPLEMENTING_OP), pos_(pos), size_(size), S_(S), C_(C)
+    {
+        GS_REQUIRE(size >= 1, "size must be >= 1");
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        return any_name_has(h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id), "thread") &&
+               h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty();
+    }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        steps::recs r;
+        steps::thread_bit_map(ms, pos_ != THREAD_META, size_, id, &r);
+        steps::segment_empty_flag(ms, pos_, size_, id, &r);
+        steps::segment_empty_row_indices(ms, pos_, id, &r);
+        steps::segment_offset(ms, false, size_, id, &r);
+        steps::segment_ptr(ms, pos_, id, &r);
+        append(transform_seq, r);
+        reduction_token t;
+        t.kind = RED_THREAD_BIT_MAP, t.need_warp_reduction = (pos_ == WARP_META), t.sparse_coarsen_factor = S_, t.coarsen_factor = C_;
+        code_generator_ptr->set_reduction_token(THREAD_META, t);
+        code_generator_ptr->open_spec_level_of_paral(THREAD_META);
+        is_run = true;
+    }
+
+  private:
+    POS_TYPE pos_;
+    uint64_t size_;
+    int S_, C_;
+};
+
+class warp_total_reduce_operator : public basic_operator { // operator.hpp:1117
+  public:
+    warp_total_reduce_operator(std::shared_ptr<code_generator> cg, int C) : basic_operator("warp_total_reduce_operator", std::move(cg), IMPLEMENTING_OP), C_(C) {}
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        return any_name_has(h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id), "warp");
+    }
+    void run(bool) override
+    {
+        reduction_token t;
+        t.kind = RED_TOTAL_WARP, t.coarsen_factor = C_;
+        code_generator_ptr->set_reduction_token(WARP_META, t);
+        code_generator_ptr->open_spec_level_of_paral(WARP_META);
+        is_run = true;
+    }
+
+  private:
+    int C_;
+};
+
+// warp_bit_map_operator (operator.hpp:1139) and warp_segment_reduce_operator (:1162): group VECTOR_WIDTH BMTs into a BMW
+class warp_group_operator : public basic_operator {
+  public:
+    warp_group_operator(std::shared_ptr<code_generator> cg, bool bitmap, int C, bool relative_nz, bool relative_row)
+        : basic_operator(bitmap ? "warp_bit_map_operator" : "warp_segment_reduce_operator", std::move(cg), IMPLEMENTING_OP), bitmap_(bitmap), C_(C),
+          rel_nz_(relative_nz), rel_row_(relative_row)
+    {
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        // must follow the thread-level reduction that feeds it
+        opv im = h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id);
+        return any_name_has(im, bitmap_ ? "thread_total_reduce" : "thread_bit_map");
+    }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        uint64_t vw = (uint64_t)get_config().as_float("VECTOR_WIDTH");
+        steps::recs r;
+        steps::get_begin_rows_after_merge_thread(ms, WARP_META, vw, id, &r);
+        steps::get_begin_nzs_after_merge_thread(ms, WARP_META, vw, id, &r);
+        if (rel_row_) steps::get_begin_rows_relative_to_parent_after_merge_thread(ms, WARP_META, vw, id, &r);
+        if (rel_nz_) steps::get_begin_nzs_relative_to_parent_after_merge_thread(ms, WARP_META, vw, id, &r);
+        steps::get_begin_BMTs_after_merge_thread(ms, WARP_META, vw, id, &r);
+        if (bitmap_) steps::parent_bit_map_of_thread(ms, WARP_META, id, vw, &r);
+        append(transform_seq, r);
+        reduction_token t;
+        t.kind = bitmap_ ? RED_WARP_BIT_MAP : RED_WARP_SEGMENT, t.coarsen_factor = C_;
+        code_generator_ptr->set_reduction_token(WARP_META, t);
+        code_generator_ptr->open_spec_level_of_paral(WARP_META);
+        is_run = true;
+    }
+
+  private:
+    bool bitmap_;
+    int C_;
+    bool rel_nz_, rel_row_;
+};
+
+class tblock_total_reduce_operator : public basic_operator { // operator.hpp:1186
+  public:
+    tblock_total_reduce_operator(std::shared_ptr<code_generator> cg, int C) : basic_operator("tblock_total_reduce_operator", std::move(cg), IMPLEMENTING_OP), C_(C) {}
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        return any_name_has(h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id), "tblock");
+    }
+    void run(bool) override
+    {
+        reduction_token t;
+        t.kind = RED_TOTAL_TBLOCK, t.coarsen_factor = C_;
+        code_generator_ptr->set_reduction_token(TBLOCK_META, t);
+        code_generator_ptr->open_spec_level_of_paral(TBLOCK_META);
+        is_run = true;
+    }
+
+  private:
+    int C_;
+};
+
+class tblock_thread_bit_map_operator : public basic_operator { // operator.hpp:1209
+  public:
+    tblock_thread_bit_map_operator(std::shared_ptr<code_generator> cg, int C, int block_size, bool relative_nz, bool relative_row)
+        : basic_operator("tblock_thread_bit_map_operator", std::move(cg), IMPLEMENTING_OP), C_(C), bs_(block_size), rel_nz_(relative_nz), rel_row_(relative_row)
+    {
+        GS_REQUIRE(block_size >= 1, "block_size must be >= 1");
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        return any_name_has(h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id), "thread_total_reduce");
+    }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        steps::recs r;
+        steps::get_begin_rows_after_merge_thread(ms, TBLOCK_META, bs_, id, &r);
+        steps::get_begin_nzs_after_merge_thread(ms, TBLOCK_META, bs_, id, &r);
+        if (rel_row_) steps::get_begin_rows_relative_to_parent_after_merge_thread(ms, TBLOCK_META, bs_, id, &r);
+        if (rel_nz_) steps::get_begin_nzs_relative_to_parent_after_merge_thread(ms, TBLOCK_META, bs_, id, &r);
+        steps::get_begin_BMTs_after_merge_thread(ms, TBLOCK_META, bs_, id, &r);
+        steps::parent_bit_map_of_thread(ms, TBLOCK_META, id, (uint64_t)get_config().as_float("VECTOR_WIDTH"), &r);
+        steps::segment_offset(ms, true, bs_, id, &r);
+        append(transform_seq, r);
+        reduction_token t;
+        t.kind = RED_TBLOCK_BIT_MAP, t.coarsen_factor = C_;
+        code_generator_ptr->set_reduction_token(TBLOCK_META, t);
+        code_generator_ptr->open_spec_level_of_paral(TBLOCK_META);
+        is_run = true;
+    }
+
+  private:
+    int C_;
+    uint64_t bs_;
+    bool rel_nz_, rel_row_;
+};
+
+class grid_block_operator : public basic_operator { // operator.hpp:1047, operator/grid_block_operator.cc:2-34
+  public:
+    grid_block_operator(std::shared_ptr<code_generator> cg, unsigned grid_x, std::vector<unsigned> block, unsigned C)
+        : basic_operator("grid_block_operator", std::move(cg), IMPLEMENTING_OP)
+    {
+        GS_REQUIRE(block.size() == 2 && block[0] > 0 && block[1] > 0 && C > 0, "block must be (x,y) > 0");
+        if (block[1] % 2 != 0) block[1]++;
+        long n = get_config().as_integer("DENSE_MATRIX_SIZE");
+        unsigned per = (meta_data_set_ptr->is_exist(WARP_META, "first_nz_indices", target_matrix_id) ? block[1] : block[0]) * C;
+        unsigned grid_y = (unsigned)((n + per - 1) / per);
+        grid_ = {grid_x, grid_y};
+        block_ = block;
+    }
+    void run(bool) override
+    {
+        code_generator_ptr->set_thread_grid(grid_, block_);
+        is_run = true;
+    }
+
+  private:
+    std::vector<unsigned> grid_, block_;
+};
+
+} // namespace
+
+// ------------------------------------------------------------------------------------------------ factory
+const std::vector<std::string> &operator_names()
+{
+    static const std::vector<std::string> n = {"sort_operator",
+                                               "fixed_interval_row_direction_tblock_blocking_operator",
+                                               "fixed_interval_row_direction_warp_blocking_operator",
+                                               "fixed_interval_row_direction_thread_blocking_operator",
+                                               "fixed_interval_col_direction_thread_blocking_operator",
+                                               "fixed_interval_nnz_direction_thread_blocking_operator",
+                                               "balanced_interval_row_direction_tblock_blocking_operator",
+                                               "balanced_interval_row_direction_warp_blocking_operator",
+                                               "balanced_interval_row_direction_thread_blocking_operator",
+                                               "empty_row_pad_operator",
+                                               "thread_total_reduce_operator",
+                                               "thread_bit_map_operator",
+                                               "warp_total_reduce_operator",
+                                               "warp_bit_map_operator",
+                                               "warp_segment_reduce_operator",
+                                               "tblock_total_reduce_operator",
+                                               "tblock_thread_bit_map_operator",
+                                               "grid_block_operator"};
+    return n;
+}
+
+std::shared_ptr<basic_operator> make_operator(const std::string &op, std::shared_ptr<code_generator> cg, std::shared_ptr<operator_context> h,
+                                              const std::vector<int64_t> &a)
+{
+    auto need = [&](size_t n) { GS_REQUIRE(a.size() == n, op + " takes " + std::to_string(n) + " arguments after code_generator_ptr"); };
+    if (op == "sort_operator") return need(0), std::make_shared<sort_operator>(cg);
+    if (op == "fixed_interval_row_direction_tblock_blocking_operator")
+        return need(2), std::make_shared<fixed_interval_row_direction_tblock_blocking_operator>(cg, (int)a[0], a[1] != 0);
+    if (op == "fixed_interval_row_direction_warp_blocking_operator")
+        return need(4), std::make_shared<fixed_interval_row_direction_warp_blocking_operator>(cg, (int)a[0], a[1] != 0, a[2] != 0, a[3] != 0);
+    if (op == "fixed_interval_row_direction_thread_blocking_operator")
+        return need(7), std::make_shared<fixed_interval_row_direction_thread_blocking_operator>(cg, (int)a[0], a[1] != 0, a[2] != 0, a[3] != 0, a[4] != 0,
+                                                                                                 a[5] != 0, (int)a[6], h);
+    if (op == "fixed_interval_col_direction_thread_blocking_operator")
+        return need(5), std::make_shared<fixed_interval_col_direction_thread_blocking_operator>(cg, (int)a[0], a[1] != 0, a[2] != 0, a[3] != 0, a[4] != 0, h);
+    if (op == "fixed_interval_nnz_direction_thread_blocking_operator")
+        return need(4), std::make_shared<fixed_interval_nnz_direction_thread_blocking_operator>(cg, (int)a[0], a[1] != 0, a[2] != 0, a[3] != 0);
+    if (op == "balanced_interval_row_direction_tblock_blocking_operator")
+        return need(1), std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, TBLOCK_META, (int)a[0]);
+    if (op == "balanced_interval_row_direction_warp_blocking_operator")
+        return need(1), std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, WARP_META, (int)a[0]);
+    if (op == "balanced_interval_row_direction_thread_blocking_operator")
+        return need(1), std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, THREAD_META, (int)a[0]);
+    if (op == "empty_row_pad_operator") return need(0), std::make_shared<empty_row_pad_operator>(cg);
+    if (op == "thread_total_reduce_operator") return need(3), std::make_shared<thread_total_reduce_operator>(cg, a[0] != 0, (int)a[1], (int)a[2]);
+    if (op == "thread_bit_map_operator") return need(4), std::make_shared<thread_bit_map_operator>(cg, (POS_TYPE)a[0], (int)a[1], (int)a[2], (int)a[3]);
+    if (op == "warp_total_reduce_operator") return need(1), std::make_shared<warp_total_reduce_operator>(cg, (int)a[0]);
+    if (op == "warp_bit_map_operator") return need(3), std::make_shared<warp_group_operator>(cg, true, (int)a[0], a[1] != 0, a[2] != 0);
+    if (op == "warp_segment_reduce_operator") return need(3), std::make_shared<warp_group_operator>(cg, false, (int)a[0], a[1] != 0, a[2] != 0);
+    if (op == "tblock_total_reduce_operator") return need(1), std::make_shared<tblock_total_reduce_operator>(cg, (int)a[0]);
+    if (op == "tblock_thread_bit_map_operator")
+        return need(4), std::make_shared<tblock_thread_bit_map_operator>(cg, (int)a[0], (int)a[1], a[2] != 0, a[3] != 0);
+    if (op == "grid_block_operator")
+        return need(4), std::make_shared<grid_block_operator>(cg, (unsigned)a[0], std::vector<unsigned>{(unsigned)a[1], (unsigned)a[2]}, (unsigned)a[3]);
+    throw Error("unknown or unbuilt operator: " + op);
+}
+
+// ------------------------------------------------------------------------------- the driver's seven chains
+void run_family_chain(int family, std::shared_ptr<code_generator> cg, operator_executer &ex, int N, int S, int C)
+{
+    GS_REQUIRE(N >= 1 && S >= 1 && C >= 1, "N, sparse_coarsen and coarsen must be >= 1");
+    auto h = ex.get_operator_context();
+    auto ms = cg->get_metadata_set();
+    auto run = [&](const char *name, std::vector<int64_t> args) { ex.add_and_run(make_operator(name, cg, h, args)); };
+    set_config("DENSE_MATRIX_SIZE", (double)N); // token_test.cc:1630
+    int64_t rows = (int64_t)ms->scalar(GLOBAL_META, "origin_row_num", -1), nnz = (int64_t)ms->scalar(GLOBAL_META, "origin_nnz_num", -1);
+    int x, y;
+    switch (family) {
+    case GS_FAMILY_THREAD_TOTAL: // token_test.cc:1003-1092
+        run("sort_operator", {});
+        run("fixed_interval_row_direction_thread_blocking_operator", {1, 0, 0, 0, 0, 1, S});
+        x = std::min(N / C, 32);
+        GS_REQUIRE(x >= 1, "N / coarsen must be >= 1");
+        set_config("VECTOR_WIDTH", (double)x);
+        y = 128 / x;
+        GS_REQUIRE(ms->check(), "metadata check failed");
+        run("thread_total_reduce_operator", {0, S, C});
+        run("grid_block_operator", {rows / y + 1, x, y, C});
+        break;
+    case GS_FAMILY_WARP_TOTAL: // :1188-1249
+        run("fixed_interval_row_direction_warp_blocking_operator", {1, 0, 0, 0});
+        y = std::min(N / C, 32);
+        GS_REQUIRE(y >= 1, "N / coarsen must be >= 1");
+        x = std::max(256 / y, 32);
+        set_config("VECTOR_WIDTH", (double)x);
+        run("warp_total_reduce_operator", {C});
+        run("grid_block_operator", {rows, x, y, C});
+        break;
+    case GS_FAMILY_WARP_BITMAP: // :1253-1315
+        run("fixed_interval_col_direction_thread_blocking_operator", {64, 0, 0, 1, 0});
+        y = std::min(N / C, 32);
+        GS_REQUIRE(y >= 1, "N / coarsen must be >= 1");
+        x = std::max(128 / y, 32);
+        set_config("VECTOR_WIDTH", (double)x);
+        run("thread_total_reduce_operator", {1, S, C});
+        run("warp_bit_map_operator", {C, 1, 1});
+        run("grid_block_operator", {rows, x, y, C});
+        break;
+    case GS_FAMILY_THREAD_BITMAP: // :1319-1391
+        run("fixed_interval_nnz_direction_thread_blocking_operator", {32, 0, 0, 1});
+        x = std::min(N / C, 32);
+        GS_REQUIRE(x >= 1, "N / coarsen must be >= 1");
+        set_config("VECTOR_WIDTH", (double)x);
+        y = 128 / x;
+        cg->open_spec_level_of_paral(THREAD_META);
+        run("thread_bit_map_operator", {THREAD_META, x, S, C});
+        run("grid_block_operator", {nnz / y + 1, x, y, C});
+        break;
+    case GS_FAMILY_WARP_SEGMENT: // :1393-1455
+        run("fixed_interval_nnz_direction_thread_blocking_operator", {32, 0, 0, 1});
+        x = std::min(N, 32);
+        y = 256 / x;
+        set_config("VECTOR_WIDTH", (double)x);
+        run("thread_bit_map_operator", {WARP_META, x, S, C});
+        run("warp_segment_reduce_operator", {C, 0, 0});
+        run("grid_block_operator", {nnz / 128 + 1, x, y, C});
+        break;
+    case GS_FAMILY_TBLOCK_TOTAL: // :1458-1514
+        run("fixed_interval_row_direction_tblock_blocking_operator", {1, 0});
+        x = std::min(N, 32);
+        y = 256 / x;
+        set_config("VECTOR_WIDTH", (double)x);
+        run("tblock_total_reduce_operator", {C});
+        run("grid_block_operator", {rows, x, y, C});
+        break;
+    case GS_FAMILY_TBLOCK_BITMAP: { // :1518-1582
+        run("fixed_interval_col_direction_thread_blocking_operator", {64, 0, 0, 1, 0});
+        x = std::min(N / C, 32);
+        GS_REQUIRE(x >= 1, "N / coarsen must be >= 1");
+        y = 256 / x;
+        set_config("VECTOR_WIDTH", (double)x);
+        run("thread_total_reduce_operator", {0, S, C});
+        run("grid_block_operator", {rows, x, y, C});
+        int y_even = y % 2 ? y + 1 : y; // the driver passes block[1] before grid_block_operator's rounding of its own copy
+        (void)y_even;
+        run("tblock_thread_bit_map_operator", {C, y, 0, 0});
+        break;
+    }
+    default: throw Error("run_family_chain: not one of the seven driver families");
+    }
+}
+
+} // namespace gs

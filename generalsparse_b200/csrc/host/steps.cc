@@ -254,6 +254,52 @@ void modify_by_empty_pad_in_submatrix(meta_data_set &ms, int id, recs *rec)
     record(rec, "modify_row_indices_by_empty_pad_in_submatrix", id);
 }
 
+void modify_by_col_pad_parent_blk_to_max_row_size(meta_data_set &ms, POS_TYPE parent_pos, int id, bool with_empty, double bound, recs *rec)
+{
+    uint64_t row_num;
+    std::vector<uint64_t> len = row_nnz(ms, id, &row_num);
+    const universal_array &C = ms.get(GLOBAL_META, "nz_col_indices", id);
+    const universal_array &V = ms.get(GLOBAL_META, "nz_vals", id);
+    uint64_t nnz = C.get_len(), after = nnz;
+    // parent blocks as row ranges; GLOBAL = the whole sub-matrix
+    std::vector<uint64_t> bounds;
+    if (parent_pos == GLOBAL_META) bounds = {0, row_num};
+    else {
+        GS_REQUIRE(parent_pos == TBLOCK_META || parent_pos == WARP_META, "parent_pos");
+        bounds = ms.get(parent_pos, "first_row_indices", id).u;
+    }
+    std::vector<uint64_t> nr, nc;
+    std::vector<double> nv;
+    uint64_t p = 0;
+    bool padded = false;
+    for (uint64_t b = 0; b + 1 < bounds.size(); b++) {
+        uint64_t mx = 0;
+        for (uint64_t r = bounds[b]; r < bounds[b + 1]; r++) mx = std::max(mx, len.at(r));
+        for (uint64_t r = bounds[b]; r < bounds[b + 1]; r++) {
+            uint64_t l = len[r];
+            for (uint64_t k = 0; k < l; k++, p++) nr.push_back(r), nc.push_back(C.u[p]), nv.push_back(V.f[p]);
+            bool pad_this = with_empty ? (mx != 0) : (mx != 0 && l != 0);
+            if (pad_this && l < mx) {
+                after += mx - l;
+                check_pad_rate(after, nnz, bound, "modify_col_indices_by_col_pad_parent_blk_to_max_row_size");
+                uint64_t last_col = nc.empty() ? C.u[0] : nc.back();
+                for (uint64_t k = l; k < mx; k++) nr.push_back(r), nc.push_back(last_col), nv.push_back(0.0);
+                padded = true;
+            }
+        }
+    }
+    GS_REQUIRE(p == nnz, "parent blocks do not cover every non-zero");
+    if (padded) {
+        universal_array va = vals_like(V, std::move(nv));
+        ms.replace_u(GLOBAL_META, "nz_col_indices", id, std::move(nc));
+        ms.replace(GLOBAL_META, "nz_vals", id, std::move(va));
+        ms.replace_u(GLOBAL_META, "nz_row_indices", id, std::move(nr));
+    }
+    record(rec, "modify_col_indices_by_col_pad_parent_blk_to_max_row_size", id);
+    record(rec, "modify_vals_by_col_pad_parent_blk_to_max_row_size", id);
+    record(rec, "modify_row_indices_by_col_pad_parent_blk_to_max_row_size", id);
+}
+
 // ---------------------------------------------------------------------------- fixed blocking, row direction
 static std::string row_dir_name(const char *what, POS_TYPE pos, const char *suffix)
 {

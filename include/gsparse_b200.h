@@ -1,0 +1,187 @@
+/* gsparse_b200.h -- C ABI of libgsparse_b200.so, the B200-native SpMM engine behind
+ * GeneralSparse's operator API.
+ *
+ * The reference has no FFI: its boundary is C++ objects + text files + a child process
+ * (SURVEY.md section 8b).  This header is the C-ABI that replaces that hand-off; every entry
+ * point cites the reference interface it stands in for (paths relative to the reference root).
+ *
+ *   gsh_*  host side: metadata store, operator graph, transform steps (no GPU needed)
+ *   gs_*   device side: array upload, kernel plans, launches, timing (needs a B200)
+ *
+ * All functions return gs_status (0 = ok) unless stated; on failure gs_last_error() holds the
+ * message.  Nothing aborts the process (the reference uses assert(false)/exit(-1),
+ * executor.cc:16-19,85).  Handles are not thread-safe; use one context per host thread.
+ */
+#ifndef GSPARSE_B200_H
+#define GSPARSE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum gs_status {
+    GS_OK = 0,
+    GS_ERR_INVALID = 1,      /* bad argument / violated operator pre-condition (reference: assert) */
+    GS_ERR_CUDA = 2,         /* CUDA runtime failure, or no usable device */
+    GS_ERR_UNSUPPORTED = 3,  /* valid in the reference API, not built here */
+    GS_ERR_NOT_FOUND = 4,    /* metadata key / handle missing */
+    GS_ERR_PADDING_RATE = 5, /* PADDING_RATE_UP_BOUND exceeded (modify_*_by_*_pad*.cc abort) */
+    GS_ERR_INTERNAL = 6
+} gs_status;
+
+typedef enum gs_dtype { GS_U8 = 0, GS_U16 = 1, GS_U32 = 2, GS_U64 = 3, GS_F32 = 4, GS_F64 = 5, GS_F16 = 6 } gs_dtype;
+
+/* POS_TYPE (metadata_set.hpp:12-22) */
+typedef enum gs_pos { GS_GLOBAL_META = 0, GS_TBLOCK_META = 1, GS_WARP_META = 2, GS_THREAD_META = 3 } gs_pos;
+
+/* The seven kernel families the reference driver wires (token_test.cc:1003-1582), i.e. the
+ * reduction tokens of reduction_token.hpp:7-110, plus the B200-native row kernels that consume
+ * the same BMT/BMW arrays. */
+typedef enum gs_family {
+    GS_FAMILY_THREAD_TOTAL = 0,  /* total_BMT_result_reduce_to_one_register_token.cc:470-913 */
+    GS_FAMILY_WARP_TOTAL = 1,    /* total_warp_result_reduce_to_one_register_token.cc:525-840 */
+    GS_FAMILY_WARP_BITMAP = 2,   /* warp_bit_map_reduce_token.cc:94-392 */
+    GS_FAMILY_THREAD_BITMAP = 3, /* thread_bit_map_reduce_to_two_register_token.cc:819-1616 */
+    GS_FAMILY_WARP_SEGMENT = 4,  /* warp_segment_reduce_token.cc:94-440 */
+    GS_FAMILY_TBLOCK_TOTAL = 5,  /* total_block_reduce_to_one_register_token.cc:374-525 */
+    GS_FAMILY_TBLOCK_BITMAP = 6, /* tblock_bit_map_reduce_token.cc:83-189 */
+    GS_FAMILY_B200_ROW_SMEM = 7, /* persistent row kernel, dense B panel staged in shared memory by bulk copy */
+    GS_FAMILY_B200_TCGEN05 = 8,  /* sparse-tile decompress to shared memory + tcgen05.mma with TMEM accumulators */
+    GS_FAMILY_COUNT = 9
+} gs_family;
+
+const char *gs_last_error(void);
+const char *gs_version(void);
+const char *gs_family_name(int family);
+
+/* ------------------------------------------------------------------ host: metadata store ---- */
+typedef struct gsh_metadata gsh_metadata; /* meta_data_set, metadata_set.hpp:103-153 */
+
+/* create_init_metadata_set_from_file, metadata_set.cc:612-707 (+ loader struct.cc:49-261).
+ * reference_ones != 0 forces every value to 1 as the reference does (struct.cc:188-195). */
+gs_status gsh_metadata_from_mtx(const char *path, const char *float_precise, int reference_ones, gsh_metadata **out);
+/* the same store from in-memory COO (row-major sorted, 0-based); vals may be NULL (all ones) */
+gs_status gsh_metadata_from_coo(uint64_t rows, uint64_t cols, uint64_t nnz, const int64_t *row, const int64_t *col,
+                                const float *vals, gsh_metadata **out);
+void gsh_metadata_free(gsh_metadata *ms);
+/* number of items; key of item i in insertion order ("<POS>_<name>_<id>", metadata_set.cc:147-151) */
+uint64_t gsh_metadata_count(const gsh_metadata *ms);
+gs_status gsh_metadata_key(const gsh_metadata *ms, uint64_t i, char *buf, size_t buf_len);
+/* length, in-memory dtype (GS_U64/GS_F32/GS_F64) and compressed dtype (code_source_data.cc:383-416) */
+gs_status gsh_metadata_info(const gsh_metadata *ms, const char *key, uint64_t *len, int *mem_dtype, int *compressed_dtype);
+/* copy an item out as u64 (integers) or f64 (values) */
+gs_status gsh_metadata_read_u64(const gsh_metadata *ms, const char *key, uint64_t *dst, uint64_t cap);
+gs_status gsh_metadata_read_f64(const gsh_metadata *ms, const char *key, double *dst, uint64_t cap);
+/* replace the values of sub-matrix `id` (same length) -- how real weights enter after the pattern was loaded */
+gs_status gsh_metadata_set_vals(gsh_metadata *ms, int sub_matrix_id, const float *vals, uint64_t n);
+/* meta_data_set::output_2_dir / meta_data_item::output_2_file (metadata_set.cc:482-515, struct.cc:1991) */
+gs_status gsh_metadata_dump(const gsh_metadata *ms, const char *dir);
+gs_status gsh_metadata_check(const gsh_metadata *ms); /* meta_data_set::check + logical_check */
+
+/* get_config()/set_config() (config.cc:2-40): numbers, booleans ("true"/"false") and strings */
+gs_status gsh_config_load(const char *path);
+gs_status gsh_config_set(const char *key, const char *json_scalar);
+gs_status gsh_config_get(const char *key, char *buf, size_t buf_len);
+
+/* ------------------------------------------------------------------ host: operator graph ---- */
+/* One session = code_generator(meta_data_set, sub_matrix_id) + operator_executer
+ * (code_generator.hpp:48, operator_executer.hpp:10-80). */
+typedef struct gsh_session gsh_session;
+gs_status gsh_session_create(gsh_metadata *ms, int sub_matrix_id, gsh_session **out);
+void gsh_session_free(gsh_session *s);
+
+/* operator_executer::add_and_run (operator_executer.cc:19-26) on the operator class named `op_name`
+ * (operator.hpp; e.g. "sort_operator", "fixed_interval_row_direction_thread_blocking_operator").
+ * `args` are the constructor arguments that follow code_generator_ptr in the reference's third
+ * constructor flavour, in order, booleans as 0/1, POS_TYPE as gs_pos. */
+gs_status gsh_session_add_and_run(gsh_session *s, const char *op_name, const int64_t *args, int n_args);
+/* number of transform-step records so far and record i (convert_to_string() of the step) */
+uint64_t gsh_session_record_count(const gsh_session *s);
+gs_status gsh_session_record(const gsh_session *s, uint64_t i, char *buf, size_t buf_len);
+
+/* The reference driver's operator chains, test_spmm_<family>(meta, name, sparse_coarsen, coarsen)
+ * (token_test.cc:1003,1188,1253,1319,1393,1458,1518): runs the chain, sets VECTOR_WIDTH and the
+ * launch shape exactly as the driver does. N = DENSE_MATRIX_SIZE. */
+gs_status gsh_session_run_family(gsh_session *s, int family, int N, int sparse_coarsen, int coarsen);
+
+/* code_generator::compile (code_generator.hpp:265): fixes the kernel family from the installed
+ * reduction tokens and the list of metadata arrays the kernel reads (add_new_metadata_dependency,
+ * code_generator.hpp:66). */
+gs_status gsh_session_compile(gsh_session *s);
+
+typedef struct gs_plan_desc {
+    int32_t family;          /* gs_family */
+    int32_t sub_matrix_id;
+    int32_t sparse_coarsen;  /* (col,val) pairs per vector load; rows are padded to this multiple */
+    int32_t coarsen;         /* dense columns per thread */
+    int32_t vector_width;    /* VECTOR_WIDTH: threads cooperating on one row / BMTs per BMW */
+    int32_t need_warp_reduction;
+    int32_t thread_for_row;  /* 1: rows are disjoint -> plain stores; 0: atomicAdd (code_generator.cc:3316-3344) */
+    int32_t has_row_permutation; /* original_nz_row_indices present (sort_operator ran) */
+    uint32_t grid[2];        /* the reference's launch shape (grid_block_operator.cc:13-33); a hint */
+    uint32_t block[2];
+    uint64_t rows;           /* rows of C this sub-matrix writes = origin_row_num */
+    uint64_t cols;           /* K */
+    uint64_t origin_nnz;     /* unpadded nnz: the flop count uses this (code_generator.cc:614-624) */
+    uint64_t stored_nnz;     /* after padding */
+    int32_t n_deps;
+    char deps[16][64];       /* metadata keys the kernel consumes */
+} gs_plan_desc;
+gs_status gsh_session_plan_desc(const gsh_session *s, gs_plan_desc *out);
+
+/* nnz-balanced contiguous row partition for G devices: the reference's greedy rule
+ * get_begin_rows_of_child_after_balance_blocking_in_row_direction (data_transform_common.cc:960-988)
+ * with nnz_per_interval = ceil(nnz/G); a tail part beyond G is merged into the last.
+ * row_nnz: nnz per row (len rows). out_begin_rows: G+1 entries. */
+gs_status gsh_partition_rows_balanced(const uint64_t *row_nnz, uint64_t rows, int G, uint64_t *out_begin_rows);
+
+/* ------------------------------------------------------------------ device: engine ---------- */
+typedef struct gs_ctx gs_ctx;   /* replaces executor.cc's compile-and-fork with an in-process device context */
+typedef struct gs_plan gs_plan;
+
+gs_status gs_create(gs_ctx **out, int device_id);
+void gs_destroy(gs_ctx *ctx);
+void *gs_stream(gs_ctx *ctx); /* the cudaStream_t every launch of this context goes to */
+
+/* host array -> device (replaces the text-file hand-off metadata_set.cc:517-571 +
+ * read_arr_from_file_with_data_type cuda_code/kernel_lib.hpp:704-781).  Index arrays are widened
+ * to the device's canonical types (u16/u32 column ids, u32 offsets, u64 bit maps); value arrays
+ * are stored as f32 or, when half != 0, as f16. */
+gs_status gs_upload_array(gs_ctx *ctx, const char *key, const void *host, uint64_t len, int dtype, int half);
+/* upload every array a compiled session depends on, straight from its metadata store */
+gs_status gs_upload_session(gs_ctx *ctx, const gsh_session *s, int half);
+
+gs_status gs_plan_create(gs_ctx *ctx, const gs_plan_desc *desc, int N, int half, gs_plan **out);
+void gs_plan_destroy(gs_plan *p);
+/* override the family the plan launches with (e.g. GS_FAMILY_B200_ROW_SMEM on a thread_total chain) */
+gs_status gs_plan_set_kernel(gs_plan *p, int family);
+
+/* dense B (K x N row-major, x_arr[col*N+n]; total_BMT...token.cc:872-877): dtype GS_F32 or GS_F16 */
+gs_status gs_set_dense(gs_plan *p, const void *B_host, int dtype);
+gs_status gs_set_dense_device(gs_plan *p, const void *B_dev);   /* already on the device, plan's value type */
+/* enqueue one SpMM (C zeroed first when the family accumulates with atomics) on gs_stream() */
+gs_status gs_launch(gs_plan *p);
+/* `repeat` launches timed with CUDA events on gs_stream(); ms_per_iter = mean */
+gs_status gs_run(gs_plan *p, int repeat, float *ms_per_iter);
+/* C (rows x N row-major, y_arr[row*N+n]) in the plan's value type (f32, or f16 when half) */
+gs_status gs_get_output(gs_plan *p, void *C_host);
+void *gs_output_device(gs_plan *p);
+/* host-buffer round trip the reference's execute_binary does through files (executor.cc:6-58):
+ * H2D of B, launch, D2H of C, all on gs_stream(); returns after the stream drained */
+gs_status gs_spmm_host(gs_plan *p, const void *B_host, void *C_host);
+/* bytes one launch must move (SURVEY.md section 8d formula, with the device's actual dtypes) */
+uint64_t gs_plan_algorithmic_bytes(const gs_plan *p);
+int gs_plan_launch_count(const gs_plan *p); /* kernels per gs_launch (memset excluded) */
+const char *gs_plan_kernel_name(const gs_plan *p);
+
+/* execute_binary(path, matrix, &ms_total, &gflops) of executor.hpp:15 for an uploaded plan:
+ * 1 warm-up + `repeat` launches, gflops = FLOAT_RATE*origin_nnz*N*repeat/t/1e9 (code_generator.cc:582-624) */
+gs_status gs_execute(gs_plan *p, int repeat, float *ms_total, float *gflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSPARSE_B200_H */
