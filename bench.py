@@ -1,0 +1,301 @@
+#!/usr/bin/env python3
+"""bench.py -- SpMM GFLOP/s (2*nnz*N/t) and % of the HBM roofline on B200.
+
+Workload (BASELINE.json configs[1]): synthetic pruned Llama-2-7B FFN weight 11008 x 4096, 70 %
+unstructured sparsity, HALF storage with fp32 accumulation, N dense columns (default 8; --n 16/32).
+A step = one SpMM C = A*B through the reference's thread_total operator chain (sort_operator ->
+row blocking with sparse-coarsen-8 padding -> thread_total_reduce) executed by the B200 row kernel.
+Successive steps use successive device copies of A (R copies, R*bytes(A) > L2) so every launch
+streams A from HBM.
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched under torchrun, one rank per GPU)
+  python bench.py --impl reference ...                     (the reference's own CPU SpMM on the host cores)
+
+Prints ONE JSON line (rank 0).  `value` = whole-job GFLOP/s with inputs resident in HBM; `e2e` = the
+same metric through gs_spmm_host (pinned host B -> H2D -> kernel -> D2H C inside the timed region).
+Multi-GPU: weak scaling -- the global matrix is G FFN-sized row blocks stacked (G*11008 x 4096), cut with
+the reference's nnz-balanced row rule, one block per rank; B replicated, C rows disjoint, no collective
+on the data path.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ROWS, COLS, DENSITY = 11008, 4096, 0.30
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n", type=int, default=8, help="dense width N (8, 16 or 32)")
+    ap.add_argument("--kernel", default="b200_row_smem")
+    ap.add_argument("--copies", type=int, default=0, help="device copies of A to rotate over (0 = enough to exceed L2 3x)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p))["hbm_gbs"], "measured"
+    return 6650.0, "fallback"
+
+
+def make_weight(seed):
+    from generalsparse_b200 import synth
+    r, c = synth.synth_matrix("uniform", ROWS, COLS, seed=seed, density=DENSITY)
+    v = synth.synth_values(len(r), seed=seed).astype(np.float16).astype(np.float32)
+    return r, c, v
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        inside = [r for (t, r) in self.rows if t0 <= t <= t1 + 0.06] or [r for (_, r) in self.rows]
+        if not inside:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no sample"]}
+        sm = sorted(float(r[0]) for r in inside)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in inside)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(inside[0][1]), "reasons": reasons, "samples": len(inside)}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU SpMM (spmm_reference_host, cuda_code/kernel_lib.hpp:859-881,
+    compiled from /root/reference into oracle/_ref when it was built; else the oracle port) on all host threads."""
+    if rank != 0:
+        return
+    from generalsparse_b200 import oracle_check as oc
+    r, c, v = make_weight(1)
+    N = args.n
+    B = np.random.default_rng(7).uniform(-1, 1, (COLS, N)).astype(np.float32)
+    indptr = oc.csr_from_coo(ROWS, r)
+    cores = os.cpu_count() or 1
+    if oc.ref_lib() is not None:
+        kind = "reference"
+        fn = lambda: oc.ref_spmm_f32(ROWS, N, COLS, indptr, c, v, B, threads=cores)
+    else:
+        kind = "port"
+        fn = lambda: oc.oracle_spmm_f32(ROWS, N, indptr, c, v, B, mt=True)
+    steps = max(1, min(args.steps, 200))
+    for _ in range(max(1, min(args.warmup, 3))):
+        fn()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        fn()
+    dt = (time.perf_counter() - t0) / steps
+    gf = 2.0 * len(r) * N / dt / 1e9
+    line = {"impl": "reference", "metric": "SpMM GFLOP/s (2*nnz*N/t)", "value": gf, "unit": "GFLOP/s", "n_gpus": args.gpus, "steps": steps,
+            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "pruned Llama-2-7B FFN weight 11008x4096, 70%% unstructured, N=%d (CPU: fp32)" % N, "nnz": int(len(r))},
+            "cpu_baseline": {"value": gf, "unit": "GFLOP/s", "cores": cores, "kind": kind,
+                             "sample": "the whole 11008x4096 matrix, %d passes, all host threads over row chunks" % steps},
+            "e2e": {"value": gf, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    from generalsparse_b200 import api
+
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    N, half = args.n, True
+    hbm_peak, peak_src = peaks()
+
+    # ---- the global matrix: `world` FFN-sized blocks stacked; this rank's nnz-balanced row block ------------------------
+    blocks = [make_weight(1 + g) for g in range(world)]
+    row_nnz = np.concatenate([np.bincount(b[0], minlength=ROWS) for b in blocks]).astype(np.uint64)
+    cuts = api.partition_rows_balanced(row_nnz, world)
+    lo, hi = int(cuts[rank]), int(cuts[rank + 1])
+    g_rows = np.concatenate([b[0] + g * ROWS for g, b in enumerate(blocks)])
+    sel = (g_rows >= lo) & (g_rows < hi)
+    r = (g_rows[sel] - lo).astype(np.int64)
+    c = np.concatenate([b[1] for b in blocks])[sel]
+    v = np.concatenate([b[2] for b in blocks])[sel]
+    my_rows = hi - lo
+    nnz = int(len(r))
+    del blocks, g_rows, sel
+
+    # ---- the reference's operator chain (token_test.cc:1003-1092) with sparse coarsen 8 -------------------------------
+    t_host0 = time.perf_counter()
+    ms = api.MetaDataSet.from_coo(my_rows, COLS, r, c, v)
+    sess = api.Session(ms).run_family("thread_total", N, 8, 1)
+    host_pipeline_s = time.perf_counter() - t_host0
+    eng = api.Engine(local)
+    desc = sess.plan_desc()
+    bytes_a = desc.stored_nnz * 4
+    copies = args.copies or max(2, int(3 * 126e6 / bytes_a) + 1)
+    plans = []
+    B_host = torch.empty((COLS, N), dtype=torch.float16).pin_memory()
+    B_host.copy_(torch.from_numpy(np.random.default_rng(7).uniform(-1, 1, (COLS, N)).astype(np.float16)))
+    C_host = torch.empty((desc.rows, N), dtype=torch.float16).pin_memory()
+    for k in range(copies):
+        eng.upload_session(sess, half=half, as_id=k)
+        p = eng.plan(sess, N, half=half, kernel=args.kernel, sub_matrix_id=k)
+        p.set_dense(B_host.numpy())
+        plans.append(p)
+    stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local))
+
+    # ---- parity gate on the timed configuration (oracle = checker only) ------------------------------------------------
+    parity = None
+    if rank == 0:
+        from generalsparse_b200 import oracle_check as oc
+        plans[0].run(1)
+        C = plans[0].output().astype(np.float64)
+        indptr = oc.csr_from_coo(my_rows, r)
+        Bf = B_host.numpy().astype(np.float32)
+        ref = oc.oracle_spmm_f64acc(my_rows, N, indptr, c, v, Bf)
+        absrow = oc.oracle_spmm_absrow(my_rows, N, indptr, c, v, Bf)
+        err = np.abs(C - ref)
+        parity = {"max_rel_err_vs_f64": float((err / np.maximum(np.abs(ref), 1e-2 * absrow + 1e-30)).max()), "tolerance": 1e-2,
+                  "ok": bool((err <= 1e-2 * np.abs(ref) + 1e-2 * absrow).all())}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(steps):
+            fn(i)
+        e1.record(stream)
+        e1.synchronize()
+        barrier()
+        ms_ = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms_, op=dist.ReduceOp.MAX)
+        return float(ms_.item())
+
+    launch = lambda i: plans[i % copies].launch()
+    for i in range(max(3, args.warmup)):
+        launch(i)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.15)
+    t0 = time.time()
+    ms_total = timed(launch, args.steps)
+    # keep the device under the same load long enough for nvidia-smi to see it (not part of the reported time)
+    sustain_steps = max(args.steps, int(0.5 / max(ms_total / args.steps * 1e-3, 1e-6)))
+    ms_sustain = timed(launch, min(sustain_steps, 200000))
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+
+    # ---- e2e: pinned host B -> device, kernel, C -> pinned host, every step ---------------------------------------------
+    bp, cp = B_host.data_ptr(), C_host.data_ptr()
+    e2e_fn = lambda i: plans[i % copies].spmm_host_ptr(bp, cp)
+    for i in range(3):
+        e2e_fn(i)
+    e2e_steps = max(10, min(args.steps, 500))
+    barrier()
+    tw0 = time.perf_counter()
+    for i in range(e2e_steps):
+        e2e_fn(i)  # returns after the stream drained: the D2H result is on the host
+    torch.cuda.synchronize()
+    e2e_s = torch.tensor([time.perf_counter() - tw0], device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_s.item())
+
+    nnz_all = torch.tensor([desc.origin_nnz], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(nnz_all)
+    nnz_all = float(nnz_all.item())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    ms_step = ms_total / args.steps
+    value = 2.0 * nnz_all * N / (ms_step * 1e-3) / 1e9
+    alg_bytes = plans[0].algorithmic_bytes
+    achieved = alg_bytes / (ms_step * 1e-3) / 1e9
+    line = {
+        "metric": "SpMM GFLOP/s (2*nnz*N/t)", "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 storage, f32 accumulate",
+        "data": "synthetic",
+        "config": {"workload": "pruned Llama-2-7B FFN weight 11008x4096 per GPU, 70%% unstructured, N=%d, HALF, thread_total chain (sort, S=8 pad) on the B200 row kernel" % N,
+                   "rows_per_gpu": int(desc.rows), "cols": COLS, "nnz_per_gpu": int(desc.origin_nnz), "stored_nnz_per_gpu": int(desc.stored_nnz),
+                   "kernel": plans[0].kernel_name, "l2": "steps rotate over %d device copies of A (%.0f MB > 126 MB L2)" % (copies, copies * bytes_a / 1e6),
+                   "partition": "nnz-balanced row blocks (balanced_interval rule), B replicated, C rows disjoint, no collective",
+                   "host_pipeline_s": round(host_pipeline_s, 3)},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                     "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)" if peak_src == "measured" else "fallback 6650", "algorithmic_bytes_per_launch": int(alg_bytes),
+                     "sustained_ms_per_step": ms_sustain / min(sustain_steps, 200000)},
+        "e2e": {"value": 2.0 * nnz_all * N * e2e_steps / e2e_s / 1e9, "unit": "GFLOP/s", "h2d_bytes_per_step": int(COLS * N * 2),
+                "d2h_bytes_per_step": int(desc.rows * N * 2), "ms_per_step": e2e_s / e2e_steps * 1e3, "steps": e2e_steps},
+        "gpu_launches": args.steps * plans[0].launch_count, "clocks": clocks, "parity": parity,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        from generalsparse_b200 import oracle_check as oc
+        indptr = oc.csr_from_coo(my_rows, r)
+        Bf = B_host.numpy().astype(np.float32)
+        cores = os.cpu_count() or 1
+        if oc.ref_lib() is not None:
+            kind, fn = "reference", (lambda: oc.ref_spmm_f32(my_rows, N, COLS, indptr, c, v, Bf, threads=cores))
+        else:
+            kind, fn = "port", (lambda: oc.oracle_spmm_f32(my_rows, N, indptr, c, v, Bf, mt=True))
+        fn()
+        best = 1e30
+        for _ in range(5):
+            tc = time.perf_counter()
+            fn()
+            best = min(best, time.perf_counter() - tc)
+        line["cpu_baseline"] = {"value": 2.0 * nnz * N / best / 1e9, "unit": "GFLOP/s", "cores": cores, "kind": kind,
+                                "sample": "the whole 11008x4096 matrix, best of 5 passes, fp32, all host threads over row chunks"}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

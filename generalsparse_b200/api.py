@@ -179,11 +179,13 @@ class Engine:
         a = np.ascontiguousarray(arr)
         check(lib().gs_upload_array(self._h, key.encode(), _ptr(a), a.size, _NP2GS[a.dtype], int(half)))
 
-    def upload_session(self, session, half=False):
-        check(lib().gs_upload_session(self._h, session._h, int(half)))
+    def upload_session(self, session, half=False, as_id=-1):
+        check(lib().gs_upload_session_as(self._h, session._h, int(half), as_id))
 
-    def plan(self, session_or_desc, N, half=False, kernel=None):
+    def plan(self, session_or_desc, N, half=False, kernel=None, sub_matrix_id=None):
         desc = session_or_desc.plan_desc() if isinstance(session_or_desc, Session) else session_or_desc
+        if sub_matrix_id is not None:
+            desc.sub_matrix_id = sub_matrix_id
         h = C.c_void_p()
         check(lib().gs_plan_create(self._h, C.byref(desc), N, int(half), C.byref(h)))
         p = Plan(self, h, desc, N, half)

@@ -323,14 +323,16 @@ gs_status gs_upload_array(gs_ctx *ctx, const char *key, const void *host, uint64
     GS_API_END
 }
 
-gs_status gs_upload_session(gs_ctx *ctx, const gsh_session *s, int half)
+gs_status gs_upload_session(gs_ctx *ctx, const gsh_session *s, int half) { return gs_upload_session_as(ctx, s, half, -1); }
+
+gs_status gs_upload_session_as(gs_ctx *ctx, const gsh_session *s, int half, int as_id)
 {
     GS_API_BEGIN
     GS_REQUIRE(ctx && s, "null argument");
     const kernel_plan &kp = s->cg->plan();
     for (const auto &d : kp.deps) {
         const universal_array &a = s->ms->get(d.pos, d.name, d.sub_matrix_id);
-        std::string key = meta_data_set::item_name(d.pos, d.name, d.sub_matrix_id);
+        std::string key = meta_data_set::item_name(d.pos, d.name, as_id >= 0 ? as_id : d.sub_matrix_id);
         if (a.is_float()) upload(ctx, key, a.f.data(), a.f.size(), GS_F64, half);
         else upload(ctx, key, a.u.data(), a.u.size(), GS_U64, half);
     }

@@ -1,0 +1,140 @@
+// token_test <matrix.mtx> <N> -- the reference driver's CLI (token_test.cc:1625-1847) on the B200 engine.
+//
+// Same positional arguments, same CWD convention (./global_config.json is honoured when present), same
+// stdout lines ("<matrix> <gflops>" and "<matrix> : min time: <sec/iter>", token_test.cc:1086,1844).
+// The reference's main runs test_spmm_thread_total(meta, name, 4, 1) (token_test.cc:1656-1657); that is the
+// default here too.  Extra flags after the two positionals:
+//   --family <thread_total|warp_total|warp_bitmap|thread_bit_map|warp_segment|block_total|block_bitmap>
+//   --sparse-coarsen S  --coarsen C   the two integers every test_spmm_* takes
+//   --kernel b200_row_smem            launch the B200 row kernel on a row-direction chain
+//   --half                            HALF storage (global_config.json "HALF": true does the same)
+//   --values                          keep the file's values (the reference forces every value to 1)
+//   --repeat R                        timed launches (reference: 10000)
+//   --dump <dir>                      write every metadata array as text, one value per line (struct.cc:1991)
+//   --no-parity                       skip the host check (the reference always checks, code_generator.cc:631-638)
+// The host check is the reference's own: all-ones B, C[i][j] must equal the row's sum of values exactly in
+// reference mode; it reads C back and compares on the host -- it is a check, not a compute fallback.
+#include "../../include/gsparse_b200.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+static void die(const char *what)
+{
+    fprintf(stderr, "token_test: %s: %s\n", what, gs_last_error());
+    exit(1);
+}
+#define OK(call)                 \
+    do {                         \
+        if ((call) != GS_OK) die(#call); \
+    } while (0)
+
+int main(int argc, char **argv)
+{
+    if (argc < 3) {
+        fprintf(stderr, "usage: %s <matrix.mtx> <N> [--family F] [--sparse-coarsen S] [--coarsen C] [--kernel K] [--half] [--values] [--repeat R] [--dump DIR] [--no-parity]\n", argv[0]);
+        return 2;
+    }
+    std::string mtx = argv[1];
+    int N = atoi(argv[2]);
+    std::string family = "thread_total", kernel, dump;
+    int S = 4, C = 1, repeat = 10000;
+    bool half = false, values = false, parity = true;
+    for (int i = 3; i < argc; i++) {
+        std::string a = argv[i];
+        auto next = [&]() -> const char * { return i + 1 < argc ? argv[++i] : ""; };
+        if (a == "--family") family = next();
+        else if (a == "--sparse-coarsen") S = atoi(next());
+        else if (a == "--coarsen") C = atoi(next());
+        else if (a == "--kernel") kernel = next();
+        else if (a == "--half") half = true;
+        else if (a == "--values") values = true;
+        else if (a == "--repeat") repeat = atoi(next());
+        else if (a == "--dump") dump = next();
+        else if (a == "--no-parity") parity = false;
+        else if (a == "--gpus") next(); // multi-GPU runs go through bench.py / torchrun: one process per GPU
+        else {
+            fprintf(stderr, "token_test: unknown flag %s\n", a.c_str());
+            return 2;
+        }
+    }
+    FILE *cfg = fopen("global_config.json", "r");
+    if (cfg) {
+        fclose(cfg);
+        OK(gsh_config_load("global_config.json"));
+        char buf[64];
+        if (gsh_config_get("HALF", buf, sizeof buf) == GS_OK && std::string(buf) == "true") half = true;
+    }
+    int fam = -1;
+    for (int f = 0; f < 7; f++)
+        if (family == gs_family_name(f)) fam = f;
+    if (fam < 0) {
+        fprintf(stderr, "token_test: unknown family %s\n", family.c_str());
+        return 2;
+    }
+
+    gsh_metadata *ms = nullptr;
+    OK(gsh_metadata_from_mtx(mtx.c_str(), "float", values ? 0 : 1, &ms));
+    printf("finish read file\n");
+    gsh_session *s = nullptr;
+    OK(gsh_session_create(ms, 0, &s));
+    OK(gsh_session_run_family(s, fam, N, S, C));
+    for (uint64_t i = 0; i < gsh_session_record_count(s); i++) {
+        char buf[1024];
+        if (gsh_session_record(s, i, buf, sizeof buf) == GS_OK) printf("%s\n", buf);
+    }
+    if (!dump.empty()) OK(gsh_metadata_dump(ms, dump.c_str()));
+
+    gs_plan_desc desc;
+    OK(gsh_session_plan_desc(s, &desc));
+    gs_ctx *ctx = nullptr;
+    OK(gs_create(&ctx, 0));
+    OK(gs_upload_session(ctx, s, half));
+    gs_plan *plan = nullptr;
+    OK(gs_plan_create(ctx, &desc, N, half, &plan));
+    if (!kernel.empty()) {
+        int k = -1;
+        for (int f = 0; f < GS_FAMILY_COUNT; f++)
+            if (kernel == gs_family_name(f)) k = f;
+        if (k < 0 || gs_plan_set_kernel(plan, k) != GS_OK) die("--kernel");
+    }
+    std::vector<float> B((size_t)desc.cols * N, 1.0f); // x_arr := 1 (code_generator.cc:464-467)
+    OK(gs_set_dense(plan, B.data(), GS_F32));
+    float ms_total = 0, gflops = 0;
+    OK(gs_execute(plan, repeat, &ms_total, &gflops));
+
+    if (parity) {
+        // the reference's check: CSR x ones on the host, exact compare (cuda_code/kernel_lib.hpp:859-921)
+        uint64_t nnz = 0, rows = desc.rows;
+        OK(gsh_metadata_info(ms, "GLOBAL_META_nz_row_indices_0", &nnz, nullptr, nullptr));
+        std::vector<uint64_t> r(nnz), perm;
+        std::vector<double> v(nnz);
+        OK(gsh_metadata_read_u64(ms, "GLOBAL_META_nz_row_indices_0", r.data(), nnz));
+        OK(gsh_metadata_read_f64(ms, "GLOBAL_META_nz_vals_0", v.data(), nnz));
+        uint64_t plen = 0;
+        if (gsh_metadata_info(ms, "GLOBAL_META_original_nz_row_indices_0", &plen, nullptr, nullptr) == GS_OK) {
+            perm.resize(plen);
+            OK(gsh_metadata_read_u64(ms, "GLOBAL_META_original_nz_row_indices_0", perm.data(), plen));
+        }
+        std::vector<float> ref(rows, 0.0f);
+        for (uint64_t i = 0; i < nnz; i++) ref[perm.empty() ? r[i] : perm[r[i]]] += (float)v[i];
+        std::vector<unsigned char> out((size_t)rows * N * (half ? 2 : 4));
+        OK(gs_get_output(plan, out.data()));
+        long wrong = 0;
+        for (uint64_t i = 0; i < rows && !half; i++)
+            for (int j = 0; j < N; j++)
+                if (((float *)out.data())[i * N + j] != ref[i]) wrong++;
+        if (wrong) printf("wrong number:%ld\n", wrong);
+        else printf("correct\n");
+    }
+    printf("%s %g\n", mtx.c_str(), gflops);
+    printf("%s : min time: %g\n", mtx.c_str(), ms_total * 1e-3 / repeat);
+    gs_plan_destroy(plan);
+    gs_destroy(ctx);
+    gsh_session_free(s);
+    gsh_metadata_free(ms);
+    return 0;
+}

@@ -153,6 +153,9 @@ void *gs_stream(gs_ctx *ctx); /* the cudaStream_t every launch of this context g
 gs_status gs_upload_array(gs_ctx *ctx, const char *key, const void *host, uint64_t len, int dtype, int half);
 /* upload every array a compiled session depends on, straight from its metadata store */
 gs_status gs_upload_session(gs_ctx *ctx, const gsh_session *s, int half);
+/* the same, stored under sub-matrix id `as_id` (several matrices, or several copies of one, in one context);
+ * a plan reaches them by setting gs_plan_desc.sub_matrix_id = as_id */
+gs_status gs_upload_session_as(gs_ctx *ctx, const gsh_session *s, int half, int as_id);
 
 gs_status gs_plan_create(gs_ctx *ctx, const gs_plan_desc *desc, int N, int half, gs_plan **out);
 void gs_plan_destroy(gs_plan *p);
