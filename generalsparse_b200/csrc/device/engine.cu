@@ -330,6 +330,19 @@ gs_status gs_upload_session_as(gs_ctx *ctx, const gsh_session *s, int half, int 
     GS_API_BEGIN
     GS_REQUIRE(ctx && s, "null argument");
     const kernel_plan &kp = s->cg->plan();
+    // a session replaces the whole array set of its sub-matrix id: arrays of an earlier chain under the
+    // same id must not leak into the next plan's bindings
+    {
+        CUDA_TRY(cudaSetDevice(ctx->device));
+        const std::string suffix = "_" + std::to_string(as_id >= 0 ? as_id : s->cg->get_sub_matrix_id());
+        for (auto it = ctx->arrays.begin(); it != ctx->arrays.end();) {
+            const std::string &k = it->first;
+            if (k.size() > suffix.size() && k.compare(k.size() - suffix.size(), suffix.size(), suffix) == 0) {
+                cudaFree(it->second.ptr);
+                it = ctx->arrays.erase(it);
+            } else ++it;
+        }
+    }
     for (const auto &d : kp.deps) {
         const universal_array &a = s->ms->get(d.pos, d.name, d.sub_matrix_id);
         std::string key = meta_data_set::item_name(d.pos, d.name, as_id >= 0 ? as_id : d.sub_matrix_id);
