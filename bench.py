@@ -31,6 +31,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 ROWS, COLS, DENSITY = 11008, 4096, 0.30
+ROWS = int(os.environ.get("GS_BENCH_ROWS", ROWS))  # experiments only; the reported workload is 11008 rows
 
 
 def parse():

@@ -260,6 +260,141 @@ template <int NT, typename ColT, typename ValT, int VEC, bool SMEM> __global__ v
     }
 }
 
+// ---- pipelined variant ---------------------------------------------------------------------------------------------
+// v2 measured long_scoreboard as the dominant stall: one chunk of A per warp in flight is not enough to cover HBM
+// latency (profiles/r1_row_v2_summary.md).  Here the warp's whole work -- its rows, chunk after chunk -- is one flat
+// sequence, and D chunks (D x 1 KiB per warp) are kept in flight in registers across row boundaries.
+template <typename ColT, typename ValT> struct chunk_t {
+    uint4 c0, c1, v0, v1; // c1: u32 ids only; v1: f32 values only
+    uint32_t row, flags;  // flags: 1 lane active, 2 last chunk of its row, 4 chunk exists
+};
+
+template <typename ColT> __device__ __forceinline__ void unpack_cols(const uint4 &c0, const uint4 &c1, uint32_t (&c)[8]);
+template <> __device__ __forceinline__ void unpack_cols<uint16_t>(const uint4 &r, const uint4 &, uint32_t (&c)[8])
+{
+    c[0] = r.x & 0xffffu, c[1] = r.x >> 16, c[2] = r.y & 0xffffu, c[3] = r.y >> 16;
+    c[4] = r.z & 0xffffu, c[5] = r.z >> 16, c[6] = r.w & 0xffffu, c[7] = r.w >> 16;
+}
+template <> __device__ __forceinline__ void unpack_cols<uint32_t>(const uint4 &r0, const uint4 &r1, uint32_t (&c)[8])
+{
+    c[0] = r0.x, c[1] = r0.y, c[2] = r0.z, c[3] = r0.w, c[4] = r1.x, c[5] = r1.y, c[6] = r1.z, c[7] = r1.w;
+}
+
+struct cursor_t {
+    uint32_t r, hi, nz;   // row being loaded, its end, next chunk base
+    uint32_t nlo, nhi;    // offsets of the row after it (prefetched)
+};
+
+template <int NT, typename ColT, typename ValT, int D> __global__ void __launch_bounds__(832, 1) k_b200_row_pipe(row_args a)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bar;
+    constexpr int ROWB = NT * (int)sizeof(ValT);
+    constexpr bool SWZ = ROWB > 16 && ROWB <= 128;
+    const ColT *col = (const ColT *)a.col;
+    const ValT *val = (const ValT *)a.val;
+    const int lane = threadIdx.x & 31;
+    const uint32_t W = gridDim.x * (blockDim.x >> 5);
+
+    if (!SWZ && threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        mbar_expect_tx(&bar, a.b_bytes);
+        for (uint32_t off = 0; off < a.b_bytes; off += 32768u) {
+            uint32_t n = a.b_bytes - off < 32768u ? a.b_bytes - off : 32768u;
+            bulk_g2s(smem + off, (const unsigned char *)a.B + off, n, &bar);
+        }
+    }
+
+    cursor_t cur;
+    cur.r = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+    cur.nz = 0, cur.hi = 0, cur.nlo = 0, cur.nhi = 0;
+    if (cur.r < a.n_rows) cur.nz = a.rowptr[cur.r], cur.hi = a.rowptr[cur.r + 1];
+    if (cur.r + W < a.n_rows) cur.nlo = a.rowptr[cur.r + W], cur.nhi = a.rowptr[cur.r + W + 1];
+
+    auto load = [&](chunk_t<ColT, ValT> &st) {
+        if (cur.r >= a.n_rows) {
+            st.flags = 0;
+            return;
+        }
+        uint32_t base = cur.nz + lane * 8;
+        bool act = base < cur.hi;
+        if (act) {
+            st.c0 = ld_stream_v4(col + base);
+            if (sizeof(ColT) == 4) st.c1 = ld_stream_v4(col + base + 4);
+            st.v0 = ld_stream_v4(val + base);
+            if (sizeof(ValT) == 4) st.v1 = ld_stream_v4(val + base + 4);
+        }
+        bool last = cur.nz + 256 >= cur.hi;
+        st.row = cur.r;
+        st.flags = 4u | (last ? 2u : 0u) | (act ? 1u : 0u);
+        if (last) {
+            cur.r += W;
+            cur.nz = cur.nlo, cur.hi = cur.nhi;
+            if (cur.r + W < a.n_rows) cur.nlo = a.rowptr[cur.r + W], cur.nhi = a.rowptr[cur.r + W + 1];
+        } else {
+            cur.nz += 256;
+        }
+    };
+
+    chunk_t<ColT, ValT> st[D];
+#pragma unroll
+    for (int s = 0; s < D; s++) load(st[s]); // D chunks of A in flight before the panel has landed
+
+    if (SWZ) {
+        constexpr int P = ROWB / 16;
+        const uint4 *src = (const uint4 *)a.B;
+        uint32_t n_pieces = a.b_bytes >> 4;
+        for (uint32_t x = threadIdx.x; x < n_pieces; x += blockDim.x) *(uint4 *)(smem + piece_offset<ROWB, true>(x / P, x % P)) = __ldg(src + x);
+        __syncthreads();
+    } else {
+        __syncthreads();
+        mbar_wait(&bar, 0);
+    }
+
+    acc_t<NT> acc;
+#pragma unroll
+    for (int i = 0; i < NT; i++) acc.v[i] = 0.0f;
+    bool more = true;
+    while (more) {
+#pragma unroll
+        for (int s = 0; s < D; s++) {
+            const uint32_t fl = st[s].flags;
+            if (!(fl & 4u)) {
+                more = false;
+                break;
+            }
+            if (fl & 1u) {
+                uint32_t c[8];
+                unpack_cols<ColT>(st[s].c0, st[s].c1, c);
+                val8<ValT> v;
+                if (sizeof(ValT) == 4) {
+                    val8<float> *vf = (val8<float> *)&v;
+                    vf->r0 = st[s].v0, vf->r1 = st[s].v1;
+                } else {
+                    ((val8<__half> *)&v)->r = st[s].v0;
+                }
+                step8<NT, SWZ>(acc, c, v, smem);
+            }
+            const uint32_t row_done = st[s].row;
+            load(st[s]);
+            if (fl & 2u) {
+#pragma unroll
+                for (int i = 0; i < NT; i++) {
+#pragma unroll
+                    for (int d = 16; d >= 1; d >>= 1) acc.v[i] += __shfl_xor_sync(0xffffffffu, acc.v[i], d);
+                }
+                if (lane == 0) {
+                    uint32_t row = a.rowid[row_done];
+                    row = (a.perm ? a.perm[row] : row) + a.begin_row;
+                    store_out<NT>((ValT *)a.C, row, acc);
+                }
+#pragma unroll
+                for (int i = 0; i < NT; i++) acc.v[i] = 0.0f;
+            }
+        }
+    }
+}
+
 // ---- B200 layout pass -------------------------------------------------------------------------------------------------
 // Re-order the non-zeros INSIDE each row (SpMM is order-free inside a row) so that the 8 lanes of a quarter warp,
 // which execute one 128-bit LDS together, hold column ids that differ mod 8.  Lane l of a warp step owns positions

@@ -51,6 +51,26 @@ template <int NT, typename ColT, typename ValT> const void *pick_fn(int vec, boo
     return smem ? (const void *)k_b200_row<NT, ColT, ValT, 1, true> : (const void *)k_b200_row<NT, ColT, ValT, 1, false>;
 }
 
+template <int NT, typename ColT, typename ValT> const void *pick_pipe(int depth)
+{
+    switch (depth) {
+    case 2: return (const void *)k_b200_row_pipe<NT, ColT, ValT, 2>;
+    case 3: return (const void *)k_b200_row_pipe<NT, ColT, ValT, 3>;
+    case 4: return (const void *)k_b200_row_pipe<NT, ColT, ValT, 4>;
+    case 6: return (const void *)k_b200_row_pipe<NT, ColT, ValT, 6>;
+    default: return nullptr;
+    }
+}
+
+template <typename ColT, typename ValT> const void *pick_pipe_nt(int N, int depth)
+{
+    switch (N) {
+    case 8: return pick_pipe<8, ColT, ValT>(depth);
+    case 16: return pick_pipe<16, ColT, ValT>(depth);
+    default: return nullptr; // wider panels do not fit shared memory in fp16 x 4096 rows; the generic kernel handles them
+    }
+}
+
 template <typename ColT, typename ValT> const void *pick_nt(int N, int vec, bool smem)
 {
     switch (N) {
@@ -115,14 +135,24 @@ cudaError_t b200_row_prepare(const launch_params &p, int sm_count, b200_row_plan
     if (p.a.col_is_u16) fn = p.a.val_is_f16 ? pick_nt<uint16_t, __half>(p.N, pl->vec, pl->smem_b) : pick_nt<uint16_t, float>(p.N, pl->vec, pl->smem_b);
     else fn = p.a.val_is_f16 ? pick_nt<uint32_t, __half>(p.N, pl->vec, pl->smem_b) : pick_nt<uint32_t, float>(p.N, pl->vec, pl->smem_b);
     if (!fn) return fail(cudaErrorInvalidValue); // dense width not instantiated
+    // pipelined variant: rows padded to 8, panel in shared memory, D chunks of A per warp in flight
+    // (opt-in: measured slower than the plain kernel at every depth on C2, profiles/r1_row_v2_summary.md)
+    int depth = env_int("GS_ROW_DEPTH", 1), max_w = 32;
+    if (pl->vec == 8 && pl->smem_b && depth > 1) {
+        const void *pf = nullptr;
+        if (p.a.col_is_u16) pf = p.a.val_is_f16 ? pick_pipe_nt<uint16_t, __half>(p.N, depth) : pick_pipe_nt<uint16_t, float>(p.N, depth);
+        else pf = p.a.val_is_f16 ? pick_pipe_nt<uint32_t, __half>(p.N, depth) : pick_pipe_nt<uint32_t, float>(p.N, depth);
+        if (pf) fn = pf, max_w = 26; // __launch_bounds__(832): room for the in-flight chunks in registers
+        else depth = 1;
+    } else depth = 1;
     pl->fn = fn;
     cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem_bytes);
     if (e != cudaSuccess) return fail(e);
 
     // warps per CTA: the candidate in [16, 32] that wastes the fewest row slots; ties go to more warps
-    int best_w = 32;
+    int best_w = max_w;
     double best_eff = 0;
-    for (int w = 32; w >= 16; w--) {
+    for (int w = max_w; w >= 16; w--) {
         uint64_t warps = (uint64_t)sm_count * w;
         uint64_t rounds = (pl->n_rows + warps - 1) / warps;
         double eff = (double)pl->n_rows / (double)(rounds * warps);
@@ -141,8 +171,8 @@ cudaError_t b200_row_prepare(const launch_params &p, int sm_count, b200_row_plan
         else e = p.a.val_is_f16 ? rainbow<uint32_t, __half>(p, pl, s) : rainbow<uint32_t, float>(p, pl, s);
         if (e != cudaSuccess) return fail(e);
     }
-    snprintf(pl->name, sizeof pl->name, "k_b200_row<N%d,%s,%s,vec%d,%s%s,%dw>", p.N, p.a.col_is_u16 ? "u16" : "u32", p.a.val_is_f16 ? "f16" : "f32", pl->vec,
-             pl->smem_b ? "smem" : "gmem", do_rainbow ? "+rainbow" : "", best_w);
+    snprintf(pl->name, sizeof pl->name, "k_b200_row%s<N%d,%s,%s,vec%d,%s%s,%dw,d%d>", depth > 1 ? "_pipe" : "", p.N, p.a.col_is_u16 ? "u16" : "u32", p.a.val_is_f16 ? "f16" : "f32", pl->vec,
+             pl->smem_b ? "smem" : "gmem", do_rainbow ? "+rainbow" : "", best_w, depth);
     *out = pl;
     return cudaSuccess;
 }
