@@ -44,6 +44,7 @@ struct launch_params {
     int coarsen = 1;
     int vector_width = 32;   // VECTOR_WIDTH of the chain (BMTs per BMW / flag packing size)
     int block_size = 32;     // BMTs per BMTB in tblock-bitmap mode
+    bool pdl = false;        // the previous operation on the stream was a B200 row kernel launch (engine.cu)
 };
 
 template <typename T> __device__ __forceinline__ float to_f32(T v);

@@ -35,6 +35,14 @@ struct gs_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
+    // true while the last operation this library put on `stream` was a B200 row kernel launch: only then may the
+    // next row launch use programmatic dependent launch (it reads A and the panel before griddepcontrol.wait)
+    bool row_chain = false;
+    cudaStream_t mem_stream()
+    {
+        row_chain = false;
+        return stream;
+    }
     std::map<std::string, dev_array> arrays;
 };
 
@@ -118,7 +126,7 @@ static void upload(gs_ctx *ctx, const std::string &key, const void *host, uint64
     }
     // 16 spare bytes so that 128-bit loads of the last partial vector stay inside the allocation
     CUDA_TRY(cudaMalloc(&d.ptr, staged.size() + 16));
-    CUDA_TRY(cudaMemcpyAsync(d.ptr, staged.data(), staged.size(), cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(cudaMemcpyAsync(d.ptr, staged.data(), staged.size(), cudaMemcpyHostToDevice, ctx->mem_stream()));
     CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     ctx->arrays[key] = d;
 }
@@ -274,9 +282,15 @@ static void enqueue(gs_plan *p)
     GS_REQUIRE(p->B_use != nullptr, "gs_set_dense has not been called");
     gsd::launch_params lp = p->lp;
     lp.B = p->B_use, lp.C = p->C_dev, lp.N = p->N;
-    if (uses_atomics(p->kernel)) CUDA_TRY(cudaMemsetAsync(p->C_dev, 0, (size_t)p->desc.rows * p->N * p->esz(), p->ctx->stream));
-    if (p->kernel == GS_FAMILY_B200_ROW_SMEM) CUDA_TRY(gsd::b200_row_launch(p->row_plan, lp, p->ctx->stream));
-    else CUDA_TRY(gsd::launch_reference_family(p->kernel, lp, p->ctx->stream));
+    if (uses_atomics(p->kernel)) CUDA_TRY(cudaMemsetAsync(p->C_dev, 0, (size_t)p->desc.rows * p->N * p->esz(), p->ctx->mem_stream()));
+    if (p->kernel == GS_FAMILY_B200_ROW_SMEM) {
+        static const bool no_pdl = getenv("GS_NO_PDL") != nullptr;
+        lp.pdl = p->ctx->row_chain && !no_pdl;
+        CUDA_TRY(gsd::b200_row_launch(p->row_plan, lp, p->ctx->stream));
+        p->ctx->row_chain = true;
+    } else {
+        CUDA_TRY(gsd::launch_reference_family(p->kernel, lp, p->ctx->mem_stream()));
+    }
 }
 
 extern "C" {
@@ -369,7 +383,7 @@ gs_status gs_plan_create(gs_ctx *ctx, const gs_plan_desc *desc, int N, int half,
         select_kernel(p, desc->family);
         size_t cbytes = (size_t)desc->rows * N * p->esz();
         CUDA_TRY(cudaMalloc(&p->C_dev, cbytes + 16));
-        CUDA_TRY(cudaMemsetAsync(p->C_dev, 0, cbytes, ctx->stream)); // rows no kernel writes (trimmed trailing empty rows) stay zero
+        CUDA_TRY(cudaMemsetAsync(p->C_dev, 0, cbytes, ctx->mem_stream())); // rows no kernel writes (trimmed trailing empty rows) stay zero
         CUDA_TRY(cudaEventCreate(&p->ev0));
         CUDA_TRY(cudaEventCreate(&p->ev1));
         CUDA_TRY(cudaStreamSynchronize(ctx->stream));
@@ -420,7 +434,7 @@ gs_status gs_set_dense(gs_plan *p, const void *B_host, int dtype)
         src = conv.data();
     }
     if (!p->B_dev) CUDA_TRY(cudaMalloc(&p->B_dev, n * p->esz() + 16));
-    CUDA_TRY(cudaMemcpyAsync(p->B_dev, src, n * p->esz(), cudaMemcpyHostToDevice, p->ctx->stream));
+    CUDA_TRY(cudaMemcpyAsync(p->B_dev, src, n * p->esz(), cudaMemcpyHostToDevice, p->ctx->mem_stream()));
     CUDA_TRY(cudaStreamSynchronize(p->ctx->stream));
     p->B_use = p->B_dev;
     GS_API_END
@@ -464,7 +478,7 @@ gs_status gs_get_output(gs_plan *p, void *C_host)
     GS_API_BEGIN
     GS_REQUIRE(p && C_host, "null argument");
     CUDA_TRY(cudaSetDevice(p->ctx->device));
-    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, (size_t)p->desc.rows * p->N * p->esz(), cudaMemcpyDeviceToHost, p->ctx->stream));
+    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, (size_t)p->desc.rows * p->N * p->esz(), cudaMemcpyDeviceToHost, p->ctx->mem_stream()));
     CUDA_TRY(cudaStreamSynchronize(p->ctx->stream));
     GS_API_END
 }
@@ -478,10 +492,10 @@ gs_status gs_spmm_host(gs_plan *p, const void *B_host, void *C_host)
     CUDA_TRY(cudaSetDevice(p->ctx->device));
     size_t nb = (size_t)p->desc.cols * p->N * p->esz(), nc = (size_t)p->desc.rows * p->N * p->esz();
     if (!p->B_dev) CUDA_TRY(cudaMalloc(&p->B_dev, nb + 16));
-    CUDA_TRY(cudaMemcpyAsync(p->B_dev, B_host, nb, cudaMemcpyHostToDevice, p->ctx->stream));
+    CUDA_TRY(cudaMemcpyAsync(p->B_dev, B_host, nb, cudaMemcpyHostToDevice, p->ctx->mem_stream()));
     p->B_use = p->B_dev;
     enqueue(p);
-    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, nc, cudaMemcpyDeviceToHost, p->ctx->stream));
+    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, nc, cudaMemcpyDeviceToHost, p->ctx->mem_stream()));
     CUDA_TRY(cudaStreamSynchronize(p->ctx->stream));
     GS_API_END
 }

@@ -20,9 +20,12 @@
 //   * fp16 x fp16 products accumulate in fp32 with the mixed-precision FMA (fma.rn.f32.f16 -> FHFMA);
 //   * rows are disjoint, so C is written with plain 128-bit stores (no atomics, no memset).
 // HBM-bound byte work: nothing here is shaped like a GEMM.
-#include "b200_row.cuh"
+#include "b200_stream.cuh"
 
+#include <algorithm>
 #include <cstdio>
+#include <cstring>
+#include <vector>
 #include <cstdlib>
 #include <new>
 
@@ -39,6 +42,10 @@ struct b200_row_plan {
     const void *fn = nullptr;
     char name[96] = {0};
     void *col2 = nullptr, *val2 = nullptr; // B200 layout (owned); the reference-order arrays stay untouched
+    // stream schedule (b200_stream.cuh): per-warp ranges of the non-zero stream, computed once at plan time
+    bool stream = false;
+    uint32_t *w_nz = nullptr, *w_row = nullptr; // device, grid x (warps + 1) each (owned)
+    uint32_t bulk_panel = 0;
 };
 
 namespace {
@@ -110,6 +117,118 @@ int env_int(const char *name, int dflt)
     return v && *v ? atoi(v) : dflt;
 }
 
+// ---- stream schedule: kernel pickers, work partition, layout pass ------------------------------------------------
+template <int NT, typename ColT, typename ValT, int CTAS> const void *pick_stream_d(int depth)
+{
+    switch (depth) {
+    case 1: return (const void *)k_b200_stream<NT, ColT, ValT, 1, CTAS>;
+    case 2: return (const void *)k_b200_stream<NT, ColT, ValT, 2, CTAS>;
+    case 3: return (const void *)k_b200_stream<NT, ColT, ValT, 3, CTAS>;
+    default: return nullptr;
+    }
+}
+template <typename ColT, typename ValT> const void *pick_stream(int N, int depth, int ctas)
+{
+    if (N == 8) return ctas == 1 ? pick_stream_d<8, ColT, ValT, 1>(depth) : pick_stream_d<8, ColT, ValT, 2>(depth);
+    if (N == 16) return ctas == 1 ? pick_stream_d<16, ColT, ValT, 1>(depth) : pick_stream_d<16, ColT, ValT, 2>(depth);
+    return nullptr;
+}
+
+// CTA c owns the rows [cta_row[c], cta_row[c+1]): cut points at the row boundary nearest to c/n of the non-zeros.
+// Inside a CTA the 256-wide steps are dealt in equal runs to the warps; w_row holds, for every warp boundary, the
+// first row that starts at or after it (binary search over the CTA's rows).
+void stream_partition(const std::vector<uint32_t> &rp, uint32_t n_rows, int n_cta, int W, std::vector<uint32_t> &cta_row, std::vector<uint32_t> &w_nz,
+                      std::vector<uint32_t> &w_row)
+{
+    cta_row.assign(n_cta + 1, 0);
+    const uint64_t first = rp[0], total = rp[n_rows] - first;
+    for (int c = 1; c < n_cta; c++) {
+        uint64_t target = first + total * (uint64_t)c / (uint64_t)n_cta;
+        uint32_t r = (uint32_t)(std::lower_bound(rp.begin(), rp.begin() + n_rows + 1, (uint32_t)target) - rp.begin());
+        if (r > 0 && target - rp[r - 1] < rp[r] - target) r--;
+        cta_row[c] = std::max(std::min(r, n_rows), cta_row[c - 1]);
+    }
+    cta_row[n_cta] = n_rows;
+    w_nz.assign((size_t)n_cta * (W + 1), 0);
+    w_row.assign((size_t)n_cta * (W + 1), 0);
+    for (int c = 0; c < n_cta; c++) {
+        const uint32_t r0 = cta_row[c], r1 = cta_row[c + 1], nz0 = rp[r0], nz1 = rp[r1];
+        const uint32_t steps = (nz1 - nz0 + 255) / 256, per = (steps + W - 1) / W;
+        for (int w = 0; w <= W; w++) {
+            uint64_t st = std::min<uint64_t>(steps, (uint64_t)w * per);
+            uint32_t nz = (uint32_t)std::min<uint64_t>(nz1, nz0 + st * 256);
+            if (w == W) nz = nz1;
+            w_nz[(size_t)c * (W + 1) + w] = nz;
+            uint32_t r = (uint32_t)(std::lower_bound(rp.begin() + r0, rp.begin() + r1, nz) - rp.begin());
+            w_row[(size_t)c * (W + 1) + w] = w == W ? r1 : r;
+        }
+    }
+}
+
+template <typename ColT, typename ValT>
+cudaError_t rainbow_stream(const launch_params &p, b200_row_plan *pl, const std::vector<uint32_t> &cta_row, cudaStream_t s)
+{
+    size_t cb = p.a.nnz * sizeof(ColT) + 16, vb = p.a.nnz * sizeof(ValT) + 16;
+    void *tc = nullptr, *tv = nullptr;
+    uint32_t *d_cta = nullptr;
+    cudaError_t e;
+    if ((e = cudaMalloc(&pl->col2, cb)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&pl->val2, vb)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&tc, cb)) == cudaSuccess && (e = cudaMalloc(&tv, vb)) == cudaSuccess && (e = cudaMalloc(&d_cta, cta_row.size() * 4)) == cudaSuccess) {
+        cudaMemcpyAsync(pl->col2, p.a.col, cb - 16, cudaMemcpyDeviceToDevice, s);
+        cudaMemcpyAsync(pl->val2, p.a.val, vb - 16, cudaMemcpyDeviceToDevice, s);
+        cudaMemcpyAsync(d_cta, cta_row.data(), cta_row.size() * 4, cudaMemcpyHostToDevice, s);
+        k_rainbow_stream<ColT, ValT><<<(pl->n_rows + 63) / 64, 64, 0, s>>>((const ColT *)p.a.col, (const ValT *)p.a.val, (ColT *)pl->col2, (ValT *)pl->val2,
+                                                                            (ColT *)tc, (ValT *)tv, pl->rowptr, pl->n_rows, d_cta, (uint32_t)cta_row.size() - 1);
+        e = cudaStreamSynchronize(s);
+        if (e == cudaSuccess) e = cudaGetLastError();
+    }
+    cudaFree(tc), cudaFree(tv), cudaFree(d_cta);
+    return e;
+}
+
+// Returns cudaErrorNotSupported when the stream schedule does not apply (the caller falls back to one warp per row).
+cudaError_t stream_prepare(const launch_params &p, int sm_count, b200_row_plan *pl, cudaStream_t s)
+{
+    const int depth = env_int("GS_STREAM_DEPTH", 1), ctas = env_int("GS_STREAM_CTAS", 2);
+    const int W = env_int("GS_STREAM_WARPS", ctas == 1 ? 32 : 16);
+    if (ctas < 1 || ctas > 2 || W < 1 || W > (ctas == 1 ? 32 : 16)) return cudaErrorNotSupported;
+    const void *fn = nullptr;
+    if (p.a.col_is_u16) fn = p.a.val_is_f16 ? pick_stream<uint16_t, __half>(p.N, depth, ctas) : pick_stream<uint16_t, float>(p.N, depth, ctas);
+    else fn = p.a.val_is_f16 ? pick_stream<uint32_t, __half>(p.N, depth, ctas) : pick_stream<uint32_t, float>(p.N, depth, ctas);
+    if (!fn) return cudaErrorNotSupported;
+    if (pl->smem_bytes * ctas + 8192 > 227 * 1024) return cudaErrorNotSupported;
+
+    std::vector<uint32_t> rp(pl->n_rows + 1), cta_row, w_nz, w_row;
+    cudaError_t e = cudaMemcpyAsync(rp.data(), pl->rowptr, rp.size() * 4, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return e;
+    const int n_cta = sm_count * ctas;
+    stream_partition(rp, pl->n_rows, n_cta, W, cta_row, w_nz, w_row);
+    if ((e = cudaMalloc(&pl->w_nz, w_nz.size() * 4)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&pl->w_row, w_row.size() * 4)) != cudaSuccess) return e;
+    cudaMemcpyAsync(pl->w_nz, w_nz.data(), w_nz.size() * 4, cudaMemcpyHostToDevice, s);
+    cudaMemcpyAsync(pl->w_row, w_row.data(), w_row.size() * 4, cudaMemcpyHostToDevice, s);
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return e;
+
+    const bool do_rainbow = !env_int("GS_ROW_NO_RAINBOW", 0);
+    if (do_rainbow) {
+        if (p.a.col_is_u16) e = p.a.val_is_f16 ? rainbow_stream<uint16_t, __half>(p, pl, cta_row, s) : rainbow_stream<uint16_t, float>(p, pl, cta_row, s);
+        else e = p.a.val_is_f16 ? rainbow_stream<uint32_t, __half>(p, pl, cta_row, s) : rainbow_stream<uint32_t, float>(p, pl, cta_row, s);
+        if (e != cudaSuccess) return e;
+    }
+    if ((e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem_bytes)) != cudaSuccess) return e;
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, W * 32, pl->smem_bytes);
+    if (e != cudaSuccess) return e;
+    if (occ < ctas) return cudaErrorNotSupported;
+    pl->fn = fn, pl->stream = true, pl->grid = n_cta, pl->threads = W * 32;
+    pl->bulk_panel = env_int("GS_STREAM_BULK", 1) ? 1u : 0u;
+    snprintf(pl->name, sizeof pl->name, "k_b200_stream<N%d,%s,%s,d%d,%dx%dw%s,pdl>", p.N, p.a.col_is_u16 ? "u16" : "u32", p.a.val_is_f16 ? "f16" : "f32", depth, ctas, W,
+             do_rainbow ? ",+rainbow" : "");
+    return cudaSuccess;
+}
+
 } // namespace
 
 cudaError_t b200_row_prepare(const launch_params &p, int sm_count, b200_row_plan **out, cudaStream_t s)
@@ -135,6 +254,21 @@ cudaError_t b200_row_prepare(const launch_params &p, int sm_count, b200_row_plan
     if (p.a.col_is_u16) fn = p.a.val_is_f16 ? pick_nt<uint16_t, __half>(p.N, pl->vec, pl->smem_b) : pick_nt<uint16_t, float>(p.N, pl->vec, pl->smem_b);
     else fn = p.a.val_is_f16 ? pick_nt<uint32_t, __half>(p.N, pl->vec, pl->smem_b) : pick_nt<uint32_t, float>(p.N, pl->vec, pl->smem_b);
     if (!fn) return fail(cudaErrorInvalidValue); // dense width not instantiated
+
+    // stream schedule: rows padded to 8, panel in shared memory, rows long enough for 256-wide steps to pay
+    const char *sched = getenv("GS_ROW_SCHED");
+    const bool long_rows = pl->n_rows > 0 && p.a.nnz / pl->n_rows >= 64;
+    if (pl->vec == 8 && pl->smem_b && (sched ? strcmp(sched, "stream") == 0 : long_rows)) {
+        cudaError_t es = stream_prepare(p, sm_count, pl, s);
+        if (es == cudaSuccess) {
+            *out = pl;
+            return cudaSuccess;
+        }
+        if (es != cudaErrorNotSupported) return fail(es);
+        cudaGetLastError();
+        cudaFree(pl->col2), cudaFree(pl->val2), cudaFree(pl->w_nz), cudaFree(pl->w_row);
+        pl->col2 = pl->val2 = nullptr, pl->w_nz = pl->w_row = nullptr;
+    }
     // pipelined variant: rows padded to 8, panel in shared memory, D chunks of A per warp in flight
     // (opt-in: measured slower than the plain kernel at every depth on C2, profiles/r1_row_v2_summary.md)
     int depth = env_int("GS_ROW_DEPTH", 1), max_w = 32;
@@ -179,6 +313,24 @@ cudaError_t b200_row_prepare(const launch_params &p, int sm_count, b200_row_plan
 
 cudaError_t b200_row_launch(const b200_row_plan *pl, const launch_params &p, cudaStream_t s)
 {
+    if (pl->stream) {
+        row::stream_args a;
+        a.col = pl->col2 ? pl->col2 : p.a.col, a.val = pl->val2 ? pl->val2 : p.a.val, a.B = p.B, a.C = p.C;
+        a.rowptr = pl->rowptr, a.rowid = pl->rowid, a.perm = p.a.perm;
+        a.w_nz = pl->w_nz, a.w_row = pl->w_row;
+        a.n_rows = pl->n_rows, a.begin_row = p.a.begin_row, a.b_bytes = (uint32_t)pl->smem_bytes, a.bulk_panel = pl->bulk_panel;
+        void *args[] = {&a};
+        // programmatic dependent launch: only behind another launch of this kernel family on the same stream (the
+        // kernel reads A and the panel before griddepcontrol.wait, so whatever ran before must not have written them)
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof cfg);
+        cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(pl->threads), cfg.dynamicSmemBytes = pl->smem_bytes, cfg.stream = s;
+        cfg.attrs = attr, cfg.numAttrs = p.pdl ? 1 : 0;
+        return cudaLaunchKernelExC(&cfg, pl->fn, args);
+    }
     row::row_args a;
     a.col = pl->col2 ? pl->col2 : p.a.col, a.val = pl->val2 ? pl->val2 : p.a.val, a.B = p.B, a.C = p.C;
     a.rowptr = pl->rowptr, a.rowid = pl->rowid, a.perm = p.a.perm;
@@ -193,6 +345,8 @@ void b200_row_free(b200_row_plan *pl)
     if (!pl) return;
     if (pl->col2) cudaFree(pl->col2);
     if (pl->val2) cudaFree(pl->val2);
+    if (pl->w_nz) cudaFree(pl->w_nz);
+    if (pl->w_row) cudaFree(pl->w_row);
     delete pl;
 }
 const char *b200_row_kernel_name(const b200_row_plan *pl) { return pl ? pl->name : ""; }

@@ -117,7 +117,7 @@ def test_b200_row_kernel(engine, N, half, chain):
         S = 8 if chain == "thread_total" else 1
         B1 = np.ones((cols, N), dtype=np.float32)
         C, plan = _run(engine, chain, nrows, cols, rr, cc, None, B1, N, S, 1, half=half, kernel="b200_row_smem")
-        assert "k_b200_row" in plan.kernel_name
+        assert "k_b200_" in plan.kernel_name
         ref = oracle_spmm_f32(nrows, N, indptr, cc, np.ones(len(rr), np.float32), B1)
         assert np.array_equal(C.astype(np.float32), ref), plan.kernel_name
         vals = synth.synth_values(len(rr), seed=5)
