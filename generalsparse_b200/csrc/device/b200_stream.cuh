@@ -24,6 +24,7 @@ struct stream_args {
     const uint32_t *w_nz;  // grid x (W+1): first non-zero of each warp's range; entry W = end of the CTA's range
     const uint32_t *w_row; // grid x (W+1): first row that STARTS at or after w_nz; entry W = the CTA's row end
     uint32_t n_rows, begin_row, b_bytes, bulk_panel;
+    uint32_t pf; // > 0: also prefetch the A lines of step (D + pf) into L2
 };
 
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
@@ -75,9 +76,12 @@ template <int NT> __device__ __forceinline__ float warp_reduce_cols(acc_t<NT> &a
 __device__ __forceinline__ void store_c(__half *C, size_t idx, float s) { C[idx] = __float2half_rn(s); }
 __device__ __forceinline__ void store_c(float *C, size_t idx, float s) { C[idx] = s; }
 
-// NT = dense width, D = steps of A in flight per warp, CTAS = resident CTAs per SM the launch bounds allow.
-template <int NT, typename ColT, typename ValT, int D, int CTAS>
-__global__ void __launch_bounds__(CTAS == 1 ? 1024 : 512, CTAS) k_b200_stream(stream_args a)
+// NT = dense width, D = steps of A in flight per warp, SHAPE = resident CTAs per SM the launch bounds allow
+// (1: one CTA of <= 32 warps, 2: two CTAs of <= 16 warps; 64 registers per thread either way).
+// Dynamic shared memory: the dense panel, then the CTA's row table (rowptr slice + output row of every row) so
+// that the only long-latency loads inside the step loop are the A stream itself.
+template <int NT, typename ColT, typename ValT, int D, int SHAPE>
+__global__ void __launch_bounds__(SHAPE == 1 ? 1024 : 512, SHAPE) k_b200_stream(stream_args a)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(8) uint64_t bar;
@@ -93,9 +97,11 @@ __global__ void __launch_bounds__(CTAS == 1 ? 1024 : 512, CTAS) k_b200_stream(st
     const int my_col = lane / REP;
     const bool writer = (lane % REP) == 0;
 
-    const uint32_t slot = blockIdx.x * (W + 1) + warp;
-    const uint32_t nb = a.w_nz[slot], ne = a.w_nz[slot + 1];
-    const uint32_t r_own = a.w_row[slot], r_end = a.w_row[blockIdx.x * (W + 1) + W];
+    const uint32_t cta0 = blockIdx.x * (W + 1);
+    const uint32_t nb = a.w_nz[cta0 + warp], ne = a.w_nz[cta0 + warp + 1];
+    const uint32_t r0 = a.w_row[cta0], r_own = a.w_row[cta0 + warp], r_end = a.w_row[cta0 + W];
+    uint32_t *s_rp = (uint32_t *)(smem + a.b_bytes); // rowptr[r0 .. r_end]
+    uint32_t *s_out = s_rp + (r_end - r0 + 1);       // output row of r0 .. r_end - 1
 
     const bool bulk = !SWZ && a.bulk_panel;
     if (bulk && threadIdx.x == 0) {
@@ -112,32 +118,29 @@ __global__ void __launch_bounds__(CTAS == 1 ? 1024 : 512, CTAS) k_b200_stream(st
 #pragma unroll
     for (int s = 0; s < D; s++) q[s].load(col, val, nb + s * 256 + lane * 8, ne);
 
-    // row state: `cur` is the row the next non-zero belongs to
-    uint32_t cur = r_own;
-    bool is_head = false;
-    if (nb < ne && a.rowptr[r_own] > nb) cur = r_own - 1, is_head = true; // the range starts inside row r_own - 1
-    uint32_t cur_start = is_head ? 0u : a.rowptr[cur]; // (a head row starts before nb; only `< ne` is ever asked)
-    uint32_t hi = cur < a.n_rows ? a.rowptr[cur + 1] : ne;
-    uint32_t hi_next = cur + 2 <= a.n_rows ? a.rowptr[cur + 2] : ne;
-    auto out_row_of = [&](uint32_t r) -> uint32_t {
-        if (r >= a.n_rows) return 0;
-        uint32_t row = a.rowid[r];
-        return (a.perm ? a.perm[row] : row) + a.begin_row;
-    };
-    uint32_t out_row = out_row_of(cur);
+    for (uint32_t i = threadIdx.x; i <= r_end - r0; i += blockDim.x) {
+        s_rp[i] = a.rowptr[r0 + i];
+        if (i < r_end - r0) {
+            uint32_t row = a.rowid[r0 + i];
+            s_out[i] = (a.perm ? a.perm[row] : row) + a.begin_row;
+        }
+    }
     if (lane == 0) head_flag[warp] = 0;
-
-    if (bulk) {
-        __syncthreads();
-        mbar_wait(&bar, 0);
-    } else {
+    if (!bulk) {
         constexpr int P = ROWB / 16;
         const uint4 *src = (const uint4 *)a.B;
         uint32_t n_pieces = a.b_bytes >> 4;
         for (uint32_t x = threadIdx.x; x < n_pieces; x += blockDim.x) *(uint4 *)(smem + piece_offset<ROWB, SWZ>(x / P, x % P)) = __ldg(src + x);
-        __syncthreads();
     }
+    __syncthreads();
+    if (bulk) mbar_wait(&bar, 0);
     pdl_launch_dependents();
+
+    // row state: `cur` is the row the next non-zero belongs to, `hi` its end
+    uint32_t cur = r_own;
+    bool is_head = false;
+    if (nb < ne && s_rp[r_own - r0] > nb) cur = r_own - 1, is_head = true; // the range starts inside row r_own - 1
+    uint32_t hi = cur < r_end ? s_rp[cur + 1 - r0] : ne;
 
     acc_t<NT> acc;
 #pragma unroll
@@ -154,14 +157,8 @@ __global__ void __launch_bounds__(CTAS == 1 ? 1024 : 512, CTAS) k_b200_stream(st
             if (lane == 0) head_flag[warp] = 1;
         } else {
             if (!waited) pdl_wait(), waited = true;
-            if (writer) store_c(C, (size_t)out_row * NT + my_col, s);
+            if (writer) store_c(C, (size_t)s_out[cur - r0] * NT + my_col, s);
         }
-    };
-    auto next_row = [&]() {
-        cur++, is_head = false;
-        cur_start = hi, hi = hi_next;
-        hi_next = cur + 2 <= a.n_rows ? a.rowptr[cur + 2] : ne;
-        out_row = out_row_of(cur);
     };
 
     for (uint32_t base = nb; base < ne; base += 256u * D) {
@@ -171,6 +168,13 @@ __global__ void __launch_bounds__(CTAS == 1 ? 1024 : 512, CTAS) k_b200_stream(st
             if (b >= ne) break;
             const a_chunk<ColT, ValT> ch = q[s];
             q[s].load(col, val, b + 256u * D + lane * 8, ne);
+            if (a.pf) {
+                const uint32_t pp = b + 256u * (D + a.pf) + lane * 8;
+                if (pp < ne && (lane & 3) == 0) {
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(col + pp));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(val + pp));
+                }
+            }
             const uint32_t pos = b + lane * 8;
             const uint32_t step_end = b + 256u < ne ? b + 256u : ne;
             bool live = pos < step_end;
@@ -185,8 +189,11 @@ __global__ void __launch_bounds__(CTAS == 1 ? 1024 : 512, CTAS) k_b200_stream(st
                 if (hi > step_end || cur >= r_end) break; // the row goes on in the next step
                 finish();
                 live = live && pos >= hi;
-                next_row();
-                if (cur >= r_end || cur_start >= step_end) break;
+                const uint32_t next_start = hi;
+                cur++, is_head = false;
+                if (cur >= r_end) break;
+                hi = s_rp[cur + 1 - r0];
+                if (next_start >= step_end) break;
             }
         }
     }
@@ -194,7 +201,7 @@ __global__ void __launch_bounds__(CTAS == 1 ? 1024 : 512, CTAS) k_b200_stream(st
     // a row still open at the end of the range: either this warp owns it (it started here) or the whole range lies inside it
     float tail = 0.0f;
     bool own_tail = false;
-    if (nb < ne && cur < r_end && (is_head || cur_start < ne)) {
+    if (nb < ne && cur < r_end && (is_head || s_rp[cur - r0] < ne)) {
         tail = warp_reduce_cols<NT>(acc, lane);
         if (is_head) {
             if (writer) head_val[warp][my_col] = tail;
@@ -212,7 +219,7 @@ __global__ void __launch_bounds__(CTAS == 1 ? 1024 : 512, CTAS) k_b200_stream(st
             if (f == 1) break;
         }
         if (!waited) pdl_wait(), waited = true;
-        if (writer) store_c(C, (size_t)out_row * NT + my_col, tail);
+        if (writer) store_c(C, (size_t)s_out[cur - r0] * NT + my_col, tail);
         cur++;
     }
     // rows of this CTA that start at the very end of its range (trailing empty rows): the last warp zeroes them
@@ -220,7 +227,7 @@ __global__ void __launch_bounds__(CTAS == 1 ? 1024 : 512, CTAS) k_b200_stream(st
     if (warp == W - 1) {
         for (uint32_t r = cur + (lane / NT); r < r_end; r += REP) {
             if (!waited) pdl_wait(), waited = true;
-            store_c(C, (size_t)out_row_of(r) * NT + (lane % NT), 0.0f);
+            store_c(C, (size_t)s_out[r - r0] * NT + (lane % NT), 0.0f);
         }
     }
 }

@@ -45,7 +45,8 @@ struct b200_row_plan {
     // stream schedule (b200_stream.cuh): per-warp ranges of the non-zero stream, computed once at plan time
     bool stream = false;
     uint32_t *w_nz = nullptr, *w_row = nullptr; // device, grid x (warps + 1) each (owned)
-    uint32_t bulk_panel = 0;
+    uint32_t bulk_panel = 0, pf = 0;
+    size_t table_bytes = 0; // shared memory behind the panel: the largest CTA row table
 };
 
 namespace {
@@ -123,7 +124,6 @@ template <int NT, typename ColT, typename ValT, int CTAS> const void *pick_strea
     switch (depth) {
     case 1: return (const void *)k_b200_stream<NT, ColT, ValT, 1, CTAS>;
     case 2: return (const void *)k_b200_stream<NT, ColT, ValT, 2, CTAS>;
-    case 3: return (const void *)k_b200_stream<NT, ColT, ValT, 3, CTAS>;
     default: return nullptr;
     }
 }
@@ -190,12 +190,14 @@ cudaError_t rainbow_stream(const launch_params &p, b200_row_plan *pl, const std:
 // Returns cudaErrorNotSupported when the stream schedule does not apply (the caller falls back to one warp per row).
 cudaError_t stream_prepare(const launch_params &p, int sm_count, b200_row_plan *pl, cudaStream_t s)
 {
-    const int depth = env_int("GS_STREAM_DEPTH", 1), ctas = env_int("GS_STREAM_CTAS", 2);
-    const int W = env_int("GS_STREAM_WARPS", ctas == 1 ? 32 : 16);
-    if (ctas < 1 || ctas > 2 || W < 1 || W > (ctas == 1 ? 32 : 16)) return cudaErrorNotSupported;
+    const int depth = env_int("GS_STREAM_DEPTH", 1), shape = env_int("GS_STREAM_CTAS", 2);
+    if (shape < 1 || shape > 2) return cudaErrorNotSupported;
+    const int ctas = shape, max_w = shape == 1 ? 32 : 16;
+    const int W = env_int("GS_STREAM_WARPS", max_w);
+    if (W < 1 || W > max_w) return cudaErrorNotSupported;
     const void *fn = nullptr;
-    if (p.a.col_is_u16) fn = p.a.val_is_f16 ? pick_stream<uint16_t, __half>(p.N, depth, ctas) : pick_stream<uint16_t, float>(p.N, depth, ctas);
-    else fn = p.a.val_is_f16 ? pick_stream<uint32_t, __half>(p.N, depth, ctas) : pick_stream<uint32_t, float>(p.N, depth, ctas);
+    if (p.a.col_is_u16) fn = p.a.val_is_f16 ? pick_stream<uint16_t, __half>(p.N, depth, shape) : pick_stream<uint16_t, float>(p.N, depth, shape);
+    else fn = p.a.val_is_f16 ? pick_stream<uint32_t, __half>(p.N, depth, shape) : pick_stream<uint32_t, float>(p.N, depth, shape);
     if (!fn) return cudaErrorNotSupported;
     if (pl->smem_bytes * ctas + 8192 > 227 * 1024) return cudaErrorNotSupported;
 
@@ -205,6 +207,12 @@ cudaError_t stream_prepare(const launch_params &p, int sm_count, b200_row_plan *
     if (e != cudaSuccess) return e;
     const int n_cta = sm_count * ctas;
     stream_partition(rp, pl->n_rows, n_cta, W, cta_row, w_nz, w_row);
+    // the CTA's row table (rowptr slice + output rows) sits behind the panel in shared memory
+    uint32_t max_rows = 0;
+    for (int c = 0; c < n_cta; c++) max_rows = std::max(max_rows, cta_row[c + 1] - cta_row[c]);
+    pl->table_bytes = ((size_t)(2 * max_rows + 1) * 4 + 15) / 16 * 16;
+    if (pl->table_bytes > 16384 || (pl->smem_bytes + pl->table_bytes + 2048) * ctas > 227 * 1024) return cudaErrorNotSupported;
+    const size_t dyn = pl->smem_bytes + pl->table_bytes;
     if ((e = cudaMalloc(&pl->w_nz, w_nz.size() * 4)) != cudaSuccess) return e;
     if ((e = cudaMalloc(&pl->w_row, w_row.size() * 4)) != cudaSuccess) return e;
     cudaMemcpyAsync(pl->w_nz, w_nz.data(), w_nz.size() * 4, cudaMemcpyHostToDevice, s);
@@ -217,13 +225,14 @@ cudaError_t stream_prepare(const launch_params &p, int sm_count, b200_row_plan *
         else e = p.a.val_is_f16 ? rainbow_stream<uint32_t, __half>(p, pl, cta_row, s) : rainbow_stream<uint32_t, float>(p, pl, cta_row, s);
         if (e != cudaSuccess) return e;
     }
-    if ((e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem_bytes)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)) != cudaSuccess) return e;
     int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, W * 32, pl->smem_bytes);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, W * 32, dyn);
     if (e != cudaSuccess) return e;
     if (occ < ctas) return cudaErrorNotSupported;
     pl->fn = fn, pl->stream = true, pl->grid = n_cta, pl->threads = W * 32;
     pl->bulk_panel = env_int("GS_STREAM_BULK", 1) ? 1u : 0u;
+    pl->pf = (uint32_t)env_int("GS_STREAM_PF", 0);
     snprintf(pl->name, sizeof pl->name, "k_b200_stream<N%d,%s,%s,d%d,%dx%dw%s,pdl>", p.N, p.a.col_is_u16 ? "u16" : "u32", p.a.val_is_f16 ? "f16" : "f32", depth, ctas, W,
              do_rainbow ? ",+rainbow" : "");
     return cudaSuccess;
@@ -318,7 +327,7 @@ cudaError_t b200_row_launch(const b200_row_plan *pl, const launch_params &p, cud
         a.col = pl->col2 ? pl->col2 : p.a.col, a.val = pl->val2 ? pl->val2 : p.a.val, a.B = p.B, a.C = p.C;
         a.rowptr = pl->rowptr, a.rowid = pl->rowid, a.perm = p.a.perm;
         a.w_nz = pl->w_nz, a.w_row = pl->w_row;
-        a.n_rows = pl->n_rows, a.begin_row = p.a.begin_row, a.b_bytes = (uint32_t)pl->smem_bytes, a.bulk_panel = pl->bulk_panel;
+        a.n_rows = pl->n_rows, a.begin_row = p.a.begin_row, a.b_bytes = (uint32_t)pl->smem_bytes, a.bulk_panel = pl->bulk_panel, a.pf = pl->pf;
         void *args[] = {&a};
         // programmatic dependent launch: only behind another launch of this kernel family on the same stream (the
         // kernel reads A and the panel before griddepcontrol.wait, so whatever ran before must not have written them)
@@ -327,7 +336,7 @@ cudaError_t b200_row_launch(const b200_row_plan *pl, const launch_params &p, cud
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof cfg);
-        cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(pl->threads), cfg.dynamicSmemBytes = pl->smem_bytes, cfg.stream = s;
+        cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(pl->threads), cfg.dynamicSmemBytes = pl->smem_bytes + pl->table_bytes, cfg.stream = s;
         cfg.attrs = attr, cfg.numAttrs = p.pdl ? 1 : 0;
         return cudaLaunchKernelExC(&cfg, pl->fn, args);
     }

@@ -1,0 +1,12 @@
+J='import sys,json; d=json.loads(sys.stdin.read()); print(d["ms_per_step"], d["roofline"]["frac"], d["config"]["kernel"], d["parity"]["ok"])'
+run() { echo "== $*"; env "$@" timeout 300 python bench.py --steps 3000 --warmup 20 --no-cpu-baseline 2>&1 | tail -1 | python -c "$J"; }
+run X=1
+run GS_STREAM_PF=1
+run GS_STREAM_PF=2
+run GS_STREAM_PF=4
+run GS_STREAM_CTAS=3 GS_STREAM_DEPTH=2
+run GS_STREAM_CTAS=3 GS_STREAM_DEPTH=1
+run GS_STREAM_CTAS=4 GS_STREAM_DEPTH=2
+run GS_STREAM_CTAS=4 GS_STREAM_DEPTH=3
+run GS_STREAM_CTAS=3 GS_STREAM_DEPTH=2 GS_STREAM_PF=2
+run GS_STREAM_DEPTH=2 GS_STREAM_PF=2
