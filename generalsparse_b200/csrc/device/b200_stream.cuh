@@ -9,8 +9,11 @@
 //   * a row that crosses a warp boundary is finished through shared memory (its owner adds the partial sums of
 //     the following warps after one __syncthreads); CTAs own whole rows, so C needs no atomics and no memset;
 //   * D steps of A per warp are in flight in registers, across row boundaries;
-//   * programmatic dependent launch: the next launch's CTAs may become resident and stage their panel while this
-//     grid drains; nothing is written to C before griddepcontrol.wait.
+//   * the CTA's row table (rowptr slice, output row ids) and its rows of C live in shared memory, so the step loop
+//     issues no long-latency load but the A stream and C is written once, coalesced, at the end;
+//   * programmatic dependent launch: the next launch's CTAs become resident as soon as an SM has room, stage their
+//     panel and run their whole step loop while this grid drains; the only global stores of the kernel -- the C
+//     tile -- come after griddepcontrol.wait.
 #pragma once
 #include "b200_row.cuh"
 
@@ -76,12 +79,46 @@ template <int NT> __device__ __forceinline__ float warp_reduce_cols(acc_t<NT> &a
 __device__ __forceinline__ void store_c(__half *C, size_t idx, float s) { C[idx] = __float2half_rn(s); }
 __device__ __forceinline__ void store_c(float *C, size_t idx, float s) { C[idx] = s; }
 
+// One step of a lane: 8 non-zeros against the panel.  PRE (u16 ids, fp16, one 16-byte piece per dense row and
+// K * 16 <= 65536): the layout pass stored id * 16, i.e. the byte offset of the dense row inside the panel, so an
+// address is one mask or shift and the panel base folds into the LDS immediate.
+template <int NT, bool SWZ, bool PRE, typename ColT, typename ValT> struct gather8 {
+    static __device__ __forceinline__ void run(acc_t<NT> &acc, const a_chunk<ColT, ValT> &ch, const unsigned char *panel)
+    {
+        uint32_t c[8];
+        unpack_cols<ColT>(ch.c[0], ch.c[sizeof(ColT) / 2 - 1], c);
+        val8<ValT> v;
+        to_val8(ch, v);
+        step8<NT, SWZ>(acc, c, v, panel);
+    }
+};
+template <> struct gather8<8, false, true, uint16_t, __half> {
+    static __device__ __forceinline__ void run(acc_t<8> &acc, const a_chunk<uint16_t, __half> &ch, const unsigned char *panel)
+    {
+        const uint32_t cw[4] = {ch.c[0].x, ch.c[0].y, ch.c[0].z, ch.c[0].w}, vw[4] = {ch.v[0].x, ch.v[0].y, ch.v[0].z, ch.v[0].w};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint4 b0 = *(const uint4 *)(panel + (cw[j] & 0xffffu)), b1 = *(const uint4 *)(panel + (cw[j] >> 16));
+            unsigned short a0, a1, h0, h1;
+            split_h2(vw[j], a0, a1);
+            split_h2(b0.x, h0, h1), fma_h(acc.v[0], a0, h0), fma_h(acc.v[1], a0, h1);
+            split_h2(b0.y, h0, h1), fma_h(acc.v[2], a0, h0), fma_h(acc.v[3], a0, h1);
+            split_h2(b0.z, h0, h1), fma_h(acc.v[4], a0, h0), fma_h(acc.v[5], a0, h1);
+            split_h2(b0.w, h0, h1), fma_h(acc.v[6], a0, h0), fma_h(acc.v[7], a0, h1);
+            split_h2(b1.x, h0, h1), fma_h(acc.v[0], a1, h0), fma_h(acc.v[1], a1, h1);
+            split_h2(b1.y, h0, h1), fma_h(acc.v[2], a1, h0), fma_h(acc.v[3], a1, h1);
+            split_h2(b1.z, h0, h1), fma_h(acc.v[4], a1, h0), fma_h(acc.v[5], a1, h1);
+            split_h2(b1.w, h0, h1), fma_h(acc.v[6], a1, h0), fma_h(acc.v[7], a1, h1);
+        }
+    }
+};
+
 // NT = dense width, D = steps of A in flight per warp, SHAPE = resident CTAs per SM the launch bounds allow
 // (1: one CTA of <= 32 warps, 2: two CTAs of <= 16 warps; 64 registers per thread either way).
 // Dynamic shared memory: the dense panel, then the CTA's row table (rowptr slice + output row of every row) so
 // that the only long-latency loads inside the step loop are the A stream itself.
-template <int NT, typename ColT, typename ValT, int D, int SHAPE>
-__global__ void __launch_bounds__(SHAPE == 1 ? 1024 : 512, SHAPE) k_b200_stream(stream_args a)
+template <int NT, typename ColT, typename ValT, int D, int SHAPE, bool PRE>
+__global__ void __launch_bounds__(SHAPE == 1 ? 1024 : SHAPE == 2 ? 512 : 320, SHAPE) k_b200_stream(stream_args a)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(8) uint64_t bar;
@@ -102,6 +139,7 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 1024 : 512, SHAPE) k_b200_stream(
     const uint32_t r0 = a.w_row[cta0], r_own = a.w_row[cta0 + warp], r_end = a.w_row[cta0 + W];
     uint32_t *s_rp = (uint32_t *)(smem + a.b_bytes); // rowptr[r0 .. r_end]
     uint32_t *s_out = s_rp + (r_end - r0 + 1);       // output row of r0 .. r_end - 1
+    float *s_c = (float *)(s_out + (r_end - r0));    // the CTA's rows of C (fp32), stored once at the very end
 
     const bool bulk = !SWZ && a.bulk_panel;
     if (bulk && threadIdx.x == 0) {
@@ -125,6 +163,7 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 1024 : 512, SHAPE) k_b200_stream(
             s_out[i] = (a.perm ? a.perm[row] : row) + a.begin_row;
         }
     }
+    for (uint32_t i = threadIdx.x; i < (r_end - r0) * NT; i += blockDim.x) s_c[i] = 0.0f; // rows without non-zeros stay 0
     if (lane == 0) head_flag[warp] = 0;
     if (!bulk) {
         constexpr int P = ROWB / 16;
@@ -145,9 +184,9 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 1024 : 512, SHAPE) k_b200_stream(
     acc_t<NT> acc;
 #pragma unroll
     for (int i = 0; i < NT; i++) acc.v[i] = 0.0f;
-    bool waited = false;
 
-    // the row `cur` is complete: reduce over the lanes; a head row goes to shared memory, an owned row to C
+    // the row `cur` is complete: reduce over the lanes; a head row goes to its owner through head_val, an owned row
+    // to the CTA's C tile (nothing touches global C before griddepcontrol.wait at the very end)
     auto finish = [&]() {
         float s = warp_reduce_cols<NT>(acc, lane);
 #pragma unroll
@@ -155,9 +194,8 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 1024 : 512, SHAPE) k_b200_stream(
         if (is_head) {
             if (writer) head_val[warp][my_col] = s;
             if (lane == 0) head_flag[warp] = 1;
-        } else {
-            if (!waited) pdl_wait(), waited = true;
-            if (writer) store_c(C, (size_t)s_out[cur - r0] * NT + my_col, s);
+        } else if (writer) {
+            s_c[(cur - r0) * NT + my_col] = s;
         }
     };
 
@@ -179,13 +217,7 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 1024 : 512, SHAPE) k_b200_stream(
             const uint32_t step_end = b + 256u < ne ? b + 256u : ne;
             bool live = pos < step_end;
             for (;;) {
-                if (live && pos < hi) {
-                    uint32_t c[8];
-                    unpack_cols<ColT>(ch.c[0], ch.c[sizeof(ColT) / 2 - 1], c);
-                    val8<ValT> v;
-                    to_val8(ch, v);
-                    step8<NT, SWZ>(acc, c, v, smem);
-                }
+                if (live && pos < hi) gather8<NT, SWZ, PRE, ColT, ValT>::run(acc, ch, smem);
                 if (hi > step_end || cur >= r_end) break; // the row goes on in the next step
                 finish();
                 live = live && pos >= hi;
@@ -218,18 +250,12 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 1024 : 512, SHAPE) k_b200_stream(
             tail += head_val[w2][my_col];
             if (f == 1) break;
         }
-        if (!waited) pdl_wait(), waited = true;
-        if (writer) store_c(C, (size_t)s_out[cur - r0] * NT + my_col, tail);
-        cur++;
+        if (writer) s_c[(cur - r0) * NT + my_col] = tail;
     }
-    // rows of this CTA that start at the very end of its range (trailing empty rows): the last warp zeroes them
-    // (the last range ends on a row end, so `cur` is past every row that holds a non-zero)
-    if (warp == W - 1) {
-        for (uint32_t r = cur + (lane / NT); r < r_end; r += REP) {
-            if (!waited) pdl_wait(), waited = true;
-            store_c(C, (size_t)s_out[r - r0] * NT + (lane % NT), 0.0f);
-        }
-    }
+    __syncthreads();
+    // the CTA's rows of C: the only global stores of the kernel, after the previous grid on the stream has completed
+    pdl_wait();
+    for (uint32_t i = threadIdx.x; i < (r_end - r0) * NT; i += blockDim.x) store_c(C, (size_t)s_out[i / NT] * NT + (i % NT), s_c[i]);
 }
 
 // ---- B200 layout pass for the stream schedule ------------------------------------------------------------------------
@@ -241,7 +267,7 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 1024 : 512, SHAPE) k_b200_stream(
 // The row is bucket-sorted by col % 8 and dealt in 8 rounds; round t fills lane t of every quarter that has one.
 template <typename ColT, typename ValT>
 __global__ void k_rainbow_stream(const ColT *col, const ValT *val, ColT *col2, ValT *val2, ColT *tc, ValT *tv, const uint32_t *rowptr, uint32_t n_rows,
-                                 const uint32_t *cta_row, uint32_t n_cta)
+                                 const uint32_t *cta_row, uint32_t n_cta, uint32_t scale)
 {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_rows) return;
@@ -275,7 +301,7 @@ __global__ void k_rainbow_stream(const ColT *col, const ValT *val, ColT *col2, V
             if (cap <= t) continue;
             const uint32_t slot0 = i == 0 ? a : (qa + i) * 8;
             const uint32_t p = nz0 + (slot0 + t) * 8;
-            for (uint32_t j = 0; j < 8; j++, k++) col2[p + j] = tc[lo + k], val2[p + j] = tv[lo + k];
+            for (uint32_t j = 0; j < 8; j++, k++) col2[p + j] = (ColT)(tc[lo + k] * scale), val2[p + j] = tv[lo + k]; // scale 16: PRE ids
         }
     }
 }

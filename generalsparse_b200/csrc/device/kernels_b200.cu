@@ -119,11 +119,11 @@ int env_int(const char *name, int dflt)
 }
 
 // ---- stream schedule: kernel pickers, work partition, layout pass ------------------------------------------------
-template <int NT, typename ColT, typename ValT, int CTAS> const void *pick_stream_d(int depth)
+template <int NT, typename ColT, typename ValT, int CTAS, bool PRE = false> const void *pick_stream_d(int depth)
 {
     switch (depth) {
-    case 1: return (const void *)k_b200_stream<NT, ColT, ValT, 1, CTAS>;
-    case 2: return (const void *)k_b200_stream<NT, ColT, ValT, 2, CTAS>;
+    case 1: return (const void *)k_b200_stream<NT, ColT, ValT, 1, CTAS, PRE>;
+    case 2: return (const void *)k_b200_stream<NT, ColT, ValT, 2, CTAS, PRE>;
     default: return nullptr;
     }
 }
@@ -132,6 +132,13 @@ template <typename ColT, typename ValT> const void *pick_stream(int N, int depth
     if (N == 8) return ctas == 1 ? pick_stream_d<8, ColT, ValT, 1>(depth) : pick_stream_d<8, ColT, ValT, 2>(depth);
     if (N == 16) return ctas == 1 ? pick_stream_d<16, ColT, ValT, 1>(depth) : pick_stream_d<16, ColT, ValT, 2>(depth);
     return nullptr;
+}
+// PRE variant (pre-scaled column ids): N = 8, u16 ids, fp16, K * 16 <= 65536
+const void *pick_stream_pre(int depth, int ctas)
+{
+    return ctas == 1   ? pick_stream_d<8, uint16_t, __half, 1, true>(depth)
+           : ctas == 2 ? pick_stream_d<8, uint16_t, __half, 2, true>(depth)
+                       : pick_stream_d<8, uint16_t, __half, 3, true>(depth);
 }
 
 // CTA c owns the rows [cta_row[c], cta_row[c+1]): cut points at the row boundary nearest to c/n of the non-zeros.
@@ -166,7 +173,7 @@ void stream_partition(const std::vector<uint32_t> &rp, uint32_t n_rows, int n_ct
 }
 
 template <typename ColT, typename ValT>
-cudaError_t rainbow_stream(const launch_params &p, b200_row_plan *pl, const std::vector<uint32_t> &cta_row, cudaStream_t s)
+cudaError_t rainbow_stream(const launch_params &p, b200_row_plan *pl, const std::vector<uint32_t> &cta_row, uint32_t scale, cudaStream_t s)
 {
     size_t cb = p.a.nnz * sizeof(ColT) + 16, vb = p.a.nnz * sizeof(ValT) + 16;
     void *tc = nullptr, *tv = nullptr;
@@ -179,7 +186,7 @@ cudaError_t rainbow_stream(const launch_params &p, b200_row_plan *pl, const std:
         cudaMemcpyAsync(pl->val2, p.a.val, vb - 16, cudaMemcpyDeviceToDevice, s);
         cudaMemcpyAsync(d_cta, cta_row.data(), cta_row.size() * 4, cudaMemcpyHostToDevice, s);
         k_rainbow_stream<ColT, ValT><<<(pl->n_rows + 63) / 64, 64, 0, s>>>((const ColT *)p.a.col, (const ValT *)p.a.val, (ColT *)pl->col2, (ValT *)pl->val2,
-                                                                            (ColT *)tc, (ValT *)tv, pl->rowptr, pl->n_rows, d_cta, (uint32_t)cta_row.size() - 1);
+                                                                            (ColT *)tc, (ValT *)tv, pl->rowptr, pl->n_rows, d_cta, (uint32_t)cta_row.size() - 1, scale);
         e = cudaStreamSynchronize(s);
         if (e == cudaSuccess) e = cudaGetLastError();
     }
@@ -191,8 +198,8 @@ cudaError_t rainbow_stream(const launch_params &p, b200_row_plan *pl, const std:
 cudaError_t stream_prepare(const launch_params &p, int sm_count, b200_row_plan *pl, cudaStream_t s)
 {
     const int depth = env_int("GS_STREAM_DEPTH", 1), shape = env_int("GS_STREAM_CTAS", 2);
-    if (shape < 1 || shape > 2) return cudaErrorNotSupported;
-    const int ctas = shape, max_w = shape == 1 ? 32 : 16;
+    if (shape < 1 || shape > 3) return cudaErrorNotSupported; // (3 CTAs of 10 warps: pre-scaled variant only)
+    const int ctas = shape, max_w = shape == 1 ? 32 : shape == 2 ? 16 : 10;
     const int W = env_int("GS_STREAM_WARPS", max_w);
     if (W < 1 || W > max_w) return cudaErrorNotSupported;
     const void *fn = nullptr;
@@ -210,7 +217,7 @@ cudaError_t stream_prepare(const launch_params &p, int sm_count, b200_row_plan *
     // the CTA's row table (rowptr slice + output rows) sits behind the panel in shared memory
     uint32_t max_rows = 0;
     for (int c = 0; c < n_cta; c++) max_rows = std::max(max_rows, cta_row[c + 1] - cta_row[c]);
-    pl->table_bytes = ((size_t)(2 * max_rows + 1) * 4 + 15) / 16 * 16;
+    pl->table_bytes = ((size_t)(2 * max_rows + 1) * 4 + (size_t)max_rows * p.N * 4 + 15) / 16 * 16; // + the fp32 C tile
     if (pl->table_bytes > 16384 || (pl->smem_bytes + pl->table_bytes + 2048) * ctas > 227 * 1024) return cudaErrorNotSupported;
     const size_t dyn = pl->smem_bytes + pl->table_bytes;
     if ((e = cudaMalloc(&pl->w_nz, w_nz.size() * 4)) != cudaSuccess) return e;
@@ -220,9 +227,13 @@ cudaError_t stream_prepare(const launch_params &p, int sm_count, b200_row_plan *
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return e;
 
     const bool do_rainbow = !env_int("GS_ROW_NO_RAINBOW", 0);
+    // pre-scaled ids: the layout pass stores id * 16 (the byte offset of the dense row in the panel) when that fits u16
+    const bool pre = do_rainbow && p.N == 8 && p.a.col_is_u16 && p.a.val_is_f16 && (uint64_t)p.a.cols * 16 <= 65536 && !env_int("GS_STREAM_NO_PRE", 0);
+    if (pre) fn = pick_stream_pre(depth, shape);
     if (do_rainbow) {
-        if (p.a.col_is_u16) e = p.a.val_is_f16 ? rainbow_stream<uint16_t, __half>(p, pl, cta_row, s) : rainbow_stream<uint16_t, float>(p, pl, cta_row, s);
-        else e = p.a.val_is_f16 ? rainbow_stream<uint32_t, __half>(p, pl, cta_row, s) : rainbow_stream<uint32_t, float>(p, pl, cta_row, s);
+        const uint32_t sc = pre ? 16u : 1u;
+        if (p.a.col_is_u16) e = p.a.val_is_f16 ? rainbow_stream<uint16_t, __half>(p, pl, cta_row, sc, s) : rainbow_stream<uint16_t, float>(p, pl, cta_row, sc, s);
+        else e = p.a.val_is_f16 ? rainbow_stream<uint32_t, __half>(p, pl, cta_row, sc, s) : rainbow_stream<uint32_t, float>(p, pl, cta_row, sc, s);
         if (e != cudaSuccess) return e;
     }
     if ((e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)) != cudaSuccess) return e;
@@ -232,9 +243,9 @@ cudaError_t stream_prepare(const launch_params &p, int sm_count, b200_row_plan *
     if (occ < ctas) return cudaErrorNotSupported;
     pl->fn = fn, pl->stream = true, pl->grid = n_cta, pl->threads = W * 32;
     pl->bulk_panel = env_int("GS_STREAM_BULK", 1) ? 1u : 0u;
-    pl->pf = (uint32_t)env_int("GS_STREAM_PF", 0);
+    pl->pf = (uint32_t)env_int("GS_STREAM_PF", 2);
     snprintf(pl->name, sizeof pl->name, "k_b200_stream<N%d,%s,%s,d%d,%dx%dw%s,pdl>", p.N, p.a.col_is_u16 ? "u16" : "u32", p.a.val_is_f16 ? "f16" : "f32", depth, ctas, W,
-             do_rainbow ? ",+rainbow" : "");
+             pre ? ",+rainbow,pre16" : do_rainbow ? ",+rainbow" : "");
     return cudaSuccess;
 }
 
