@@ -54,6 +54,14 @@ def peaks():
     return 6650.0, "fallback"
 
 
+def traffic_bytes(N, half, world, args):
+    """DRAM bytes per launch from the committed ncu --set full capture of this workload (profiles/traffic.json), else None"""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not (os.path.exists(p) and N == 8 and half and ROWS == 11008 and args.kernel == "b200_row_smem"):
+        return None
+    return json.load(open(p)).get("C2_N8_half_thread_total_S8", {}).get("bytes")
+
+
 def make_weight(seed):
     from generalsparse_b200 import synth
     r, c = synth.synth_matrix("uniform", ROWS, COLS, seed=seed, density=DENSITY)
@@ -152,7 +160,8 @@ def main():
     # ---- the global matrix: `world` FFN-sized blocks stacked; this rank's nnz-balanced row block ------------------------
     blocks = [make_weight(1 + g) for g in range(world)]
     row_nnz = np.concatenate([np.bincount(b[0], minlength=ROWS) for b in blocks]).astype(np.uint64)
-    cuts = api.partition_rows_balanced(row_nnz, world)
+    from generalsparse_b200 import shard
+    cuts = shard.row_cuts(row_nnz, world)  # the same rule tests/test_partition_gloo.py covers on CPU
     lo, hi = int(cuts[rank]), int(cuts[rank + 1])
     g_rows = np.concatenate([b[0] + g * ROWS for g, b in enumerate(blocks)])
     sel = (g_rows >= lo) & (g_rows < hi)
@@ -269,7 +278,7 @@ def main():
                    "kernel": plans[0].kernel_name, "l2": "steps rotate over %d device copies of A (%.0f MB > 126 MB L2)" % (copies, copies * bytes_a / 1e6),
                    "partition": "nnz-balanced row blocks (balanced_interval rule), B replicated, C rows disjoint, no collective",
                    "host_pipeline_s": round(host_pipeline_s, 3)},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic_bytes(N, half, world, args),
                      "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)" if peak_src == "measured" else "fallback 6650", "algorithmic_bytes_per_launch": int(alg_bytes),
                      "sustained_ms_per_step": ms_sustain / min(sustain_steps, 200000)},
         "e2e": {"value": 2.0 * nnz_all * N * e2e_steps / e2e_s / 1e9, "unit": "GFLOP/s", "h2d_bytes_per_step": int(COLS * N * 2),
