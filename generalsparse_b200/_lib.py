@@ -19,7 +19,7 @@ SYMBOLS = [
     "gsh_session_run_family", "gsh_session_compile", "gsh_session_plan_desc", "gsh_partition_rows_balanced",
     "gs_create", "gs_destroy", "gs_stream", "gs_upload_array", "gs_upload_session", "gs_upload_session_as", "gs_plan_create", "gs_plan_destroy",
     "gs_plan_set_kernel", "gs_set_dense", "gs_set_dense_device", "gs_launch", "gs_run", "gs_get_output", "gs_output_device",
-    "gs_spmm_host", "gs_plan_algorithmic_bytes", "gs_plan_launch_count", "gs_plan_kernel_name", "gs_execute",
+    "gs_spmm_host", "gs_spmm_host_async", "gs_synchronize", "gs_plan_algorithmic_bytes", "gs_plan_launch_count", "gs_plan_kernel_name", "gs_execute",
 ]
 
 (GS_U8, GS_U16, GS_U32, GS_U64, GS_F32, GS_F64, GS_F16) = range(7)
@@ -80,6 +80,7 @@ def lib():
         "gs_plan_set_kernel": (i32, [vp, i32]), "gs_set_dense": (i32, [vp, vp, i32]), "gs_set_dense_device": (i32, [vp, vp]),
         "gs_launch": (i32, [vp]), "gs_run": (i32, [vp, i32, P(C.c_float)]), "gs_get_output": (i32, [vp, vp]),
         "gs_output_device": (vp, [vp]), "gs_spmm_host": (i32, [vp, vp, vp]),
+        "gs_spmm_host_async": (i32, [vp, vp, vp]), "gs_synchronize": (i32, [vp]),
         "gs_plan_algorithmic_bytes": (u64, [vp]), "gs_plan_launch_count": (i32, [vp]), "gs_plan_kernel_name": (cp, [vp]),
         "gs_execute": (i32, [vp, i32, P(C.c_float), P(C.c_float)]),
     }

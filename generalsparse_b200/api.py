@@ -175,6 +175,9 @@ class Engine:
     def stream(self):
         return lib().gs_stream(self._h)
 
+    def synchronize(self):
+        check(lib().gs_synchronize(self._h))
+
     def upload_array(self, key, arr, half=False):
         a = np.ascontiguousarray(arr)
         check(lib().gs_upload_array(self._h, key.encode(), _ptr(a), a.size, _NP2GS[a.dtype], int(half)))
@@ -241,6 +244,10 @@ class Plan:
 
     def spmm_host_ptr(self, b_ptr, c_ptr):
         check(lib().gs_spmm_host(self._h, C.c_void_p(b_ptr), C.c_void_p(c_ptr)))
+
+    def spmm_host_async_ptr(self, b_ptr, c_ptr):
+        """pinned host pointers; C is complete after Engine.synchronize()"""
+        check(lib().gs_spmm_host_async(self._h, C.c_void_p(b_ptr), C.c_void_p(c_ptr)))
 
     def execute(self, repeat):
         """execute_binary(path, matrix, &ms_total, &gflops) of executor.hpp:15"""

@@ -35,6 +35,7 @@ struct gs_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_in = nullptr, copy_out = nullptr; // gs_spmm_host_async: H2D and D2H beside the launch stream (lazy)
     // true while the last operation this library put on `stream` was a B200 row kernel launch: only then may the
     // next row launch use programmatic dependent launch (it reads A and the panel before griddepcontrol.wait)
     bool row_chain = false;
@@ -60,6 +61,7 @@ struct gs_plan {
     void *B_pinned = nullptr, *C_pinned = nullptr; // staging for pageable host buffers is NOT used; these stay null
     uint64_t offset_bytes = 0; // bytes of the offset / bitmap arrays the launched kernel reads
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev_b = nullptr, ev_k = nullptr, ev_c = nullptr; // async round trip: B landed, kernel done, C read back
     size_t esz() const { return half ? 2 : 4; }
 };
 
@@ -324,6 +326,8 @@ void gs_destroy(gs_ctx *ctx)
     cudaSetDevice(ctx->device);
     for (auto &kv : ctx->arrays) cudaFree(kv.second.ptr);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
+    if (ctx->copy_out) cudaStreamDestroy(ctx->copy_out);
     delete ctx;
 }
 
@@ -404,6 +408,9 @@ void gs_plan_destroy(gs_plan *p)
     if (p->C_dev) cudaFree(p->C_dev);
     if (p->ev0) cudaEventDestroy(p->ev0);
     if (p->ev1) cudaEventDestroy(p->ev1);
+    if (p->ev_b) cudaEventDestroy(p->ev_b);
+    if (p->ev_k) cudaEventDestroy(p->ev_k);
+    if (p->ev_c) cudaEventDestroy(p->ev_c);
     delete p;
 }
 
@@ -497,6 +504,51 @@ gs_status gs_spmm_host(gs_plan *p, const void *B_host, void *C_host)
     enqueue(p);
     CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, nc, cudaMemcpyDeviceToHost, p->ctx->mem_stream()));
     CUDA_TRY(cudaStreamSynchronize(p->ctx->stream));
+    GS_API_END
+}
+
+gs_status gs_spmm_host_async(gs_plan *p, const void *B_host, void *C_host)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p && B_host && C_host, "null argument");
+    gs_ctx *ctx = p->ctx;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    if (!ctx->copy_in) CUDA_TRY(cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking));
+    if (!ctx->copy_out) CUDA_TRY(cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
+    if (!p->ev_b) {
+        CUDA_TRY(cudaEventCreateWithFlags(&p->ev_b, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&p->ev_k, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&p->ev_c, cudaEventDisableTiming));
+        // order behind whatever the launch stream already holds for this plan
+        CUDA_TRY(cudaEventRecord(p->ev_k, ctx->stream));
+        CUDA_TRY(cudaEventRecord(p->ev_c, ctx->stream));
+    }
+    size_t nb = (size_t)p->desc.cols * p->N * p->esz(), nc = (size_t)p->desc.rows * p->N * p->esz();
+    if (!p->B_dev) CUDA_TRY(cudaMalloc(&p->B_dev, nb + 16));
+    // B of this plan: not before the plan's previous kernel has finished reading it
+    CUDA_TRY(cudaStreamWaitEvent(ctx->copy_in, p->ev_k, 0));
+    CUDA_TRY(cudaMemcpyAsync(p->B_dev, B_host, nb, cudaMemcpyHostToDevice, ctx->copy_in));
+    CUDA_TRY(cudaEventRecord(p->ev_b, ctx->copy_in));
+    p->B_use = p->B_dev;
+    // kernel: after B has landed and the plan's previous C has been read back
+    CUDA_TRY(cudaStreamWaitEvent(ctx->stream, p->ev_b, 0));
+    CUDA_TRY(cudaStreamWaitEvent(ctx->stream, p->ev_c, 0));
+    enqueue(p);
+    CUDA_TRY(cudaEventRecord(p->ev_k, ctx->stream));
+    CUDA_TRY(cudaStreamWaitEvent(ctx->copy_out, p->ev_k, 0));
+    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, nc, cudaMemcpyDeviceToHost, ctx->copy_out));
+    CUDA_TRY(cudaEventRecord(p->ev_c, ctx->copy_out));
+    GS_API_END
+}
+
+gs_status gs_synchronize(gs_ctx *ctx)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ctx, "null argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    if (ctx->copy_in) CUDA_TRY(cudaStreamSynchronize(ctx->copy_in));
+    if (ctx->copy_out) CUDA_TRY(cudaStreamSynchronize(ctx->copy_out));
     GS_API_END
 }
 

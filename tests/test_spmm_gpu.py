@@ -148,6 +148,31 @@ def test_host_roundtrip_and_execute(engine):
     assert plan.algorithmic_bytes > len(r) * 6
 
 
+def test_async_roundtrip_equals_blocking(engine):
+    """gs_spmm_host_async over several plans (copy-in / launch / copy-out streams chained by events) == gs_spmm_host;
+    back-to-back row-kernel launches also exercise programmatic dependent launch with different B per step"""
+    import torch
+    from generalsparse_b200 import api, synth
+    rows, cols, N = 1000, 4096, 8
+    r, c = _matrix("uniform", rows, cols, seed=31, density=0.1)
+    vals = synth.synth_values(len(r), seed=31).astype(np.float16).astype(np.float32)
+    ms = api.MetaDataSet.from_coo(rows, cols, r, c, vals)
+    s = api.Session(ms).run_family("thread_total", N, 8, 1)
+    plans = []
+    for k in range(3):
+        engine.upload_session(s, half=True, as_id=20 + k)
+        plans.append(engine.plan(s, N, half=True, kernel="b200_row_smem", sub_matrix_id=20 + k))
+    Bs = [torch.from_numpy(synth.synth_dense(cols, N, seed=40 + i).astype(np.float16)).pin_memory() for i in range(6)]
+    want = [plans[i % 3].spmm_host(Bs[i].numpy()) for i in range(6)]
+    outs = [torch.empty((rows, N), dtype=torch.float16).pin_memory() for _ in range(6)]
+    for rep in range(3):  # queue depth 6, three times over
+        for i in range(6):
+            plans[i % 3].spmm_host_async_ptr(Bs[i].data_ptr(), outs[i].data_ptr())
+    engine.synchronize()
+    for i in range(6):
+        assert np.array_equal(outs[i].numpy(), want[i]), i
+
+
 def test_errors_are_statuses_not_aborts(engine):
     from generalsparse_b200 import api
     rows, cols = 64, 48
