@@ -1,0 +1,316 @@
+// Device code of the B200 tile kernel (GS_FAMILY_B200_TCGEN05): sparse-tile decompress to shared memory + tcgen05.mma
+// with the accumulator in tensor memory.  Host side and the format: kernels_tile.cu, host/tile_format.hpp.
+//
+// Why a tensor-core path at all: at N >= 16 the gather kernels (b200_stream.cuh) are bound by the shared-memory data
+// pipe and the FMA pipe, not by HBM -- 13.5 M non-zeros x N=32 is 433 M fp32 FMAs and 433 MB of LDS traffic per launch,
+// 12 us and 23 us on 148 SMs against 8.4 us of HBM time.  A 30 %-dense 128 x 64 tile rebuilt in shared memory costs one
+// 2-byte store per non-zero whatever N is, and the contraction itself (2.9 GFLOP dense at N=32) is 2 us of tensor pipe.
+//
+// One persistent CTA per SM, 21 warps:
+//   warps 0-15  two producer groups of 8 warps, alternating tiles: zero the 16 KB image of A's tile (K-major, 128-byte
+//               swizzle), copy the 64 x N piece of B in the MN-major swizzled operand layout, scatter the tile's
+//               (offset, value) pairs with 2-byte stores (128-bit loads of 8 offsets + 8 values per lane, the next
+//               tile's loads issued before this tile's stores), fence to the async proxy, arrive on full[stage];
+//   warp 20     one elected lane issues 4 tcgen05.mma (M=128, N, K=16) per tile, commits to empty[stage], and to
+//               acc_full[] at the end of a row panel; two accumulators in TMEM alternate between panels;
+//   warps 16-19 epilogue: tcgen05.ld the accumulator (lane = row), convert, store the rows of C.
+// The tiles are dealt in equal contiguous runs to the CTAs (a run crosses row panels: stream-K).  A panel split over
+// several CTAs is summed by the CTA that holds its first tile, in k order, from fp32 partials the others leave in a
+// per-CTA workspace slot (release/acquire flag carrying the launch sequence number): no atomics, bit-reproducible.
+#pragma once
+#include "b200_stream.cuh"
+
+namespace gsd {
+namespace tile {
+
+using row::mbar_init;
+using row::smem_u32;
+
+constexpr int TM = 128, TK = 64, A_BYTES = TM * TK * 2;
+constexpr int GROUP_THREADS = 256, EPI_WARP0 = 16, MMA_WARP = 20, THREADS = 21 * 32;
+
+struct tile_args {
+    const uint32_t *tile_ptr; // n_tiles + 1
+    const uint16_t *off, *val;
+    const void *B;
+    void *C;
+    const uint32_t *out_row; // n_panels * 128 output rows of C, 0xffffffff = no row
+    float *ws;               // grid x 128 x N fp32 partial panels
+    uint32_t *flags;         // grid
+    uint32_t n_tiles, k_tiles, K, seq, ptr_cap;
+};
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(bar),
+                 "r"(parity)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) { asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory"); }
+__device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc),
+                 "r"(idesc), "r"(accumulate)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&r)[16])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]),
+                   "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void sts16(uint32_t addr, unsigned short v) { asm volatile("st.shared.b16 [%0], %1;" ::"r"(addr), "h"(v) : "memory"); }
+__device__ __forceinline__ void sts128(uint32_t addr, uint4 v) { asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); }
+__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(uint32_t *p, uint32_t v) { asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+
+// Shared-memory matrix descriptor (cute/arch/mma_sm100_desc.hpp, UMMA::SmemDescriptor): start address, leading and
+// stride byte offsets in 16-byte units, version 1, layout type in bits 61-63.
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout)
+{
+    return (uint64_t)((addr >> 4) & 0x3fffu) | ((uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16) | ((uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32) | (1ull << 46) |
+           ((uint64_t)layout << 61);
+}
+
+// geometry of the B operand (64 x N piece of the dense matrix, N contiguous = MN-major) for dense width N
+template <int N> struct b_geom {
+    static constexpr int ATOM_N = N < 64 ? N : 64;           // dense columns per swizzle atom
+    static constexpr int RB = ATOM_N * 2;                    // bytes of one k row inside an atom: 32 / 64 / 128
+    static constexpr int SWZ_MASK = RB / 16 - 1;             // 16-byte chunks per row - 1
+    static constexpr uint32_t LAYOUT = RB == 128 ? 2u : RB == 64 ? 4u : 6u; // SWIZZLE_128B / 64B / 32B
+    static constexpr int GROUPS = N / ATOM_N;                // atoms along N
+    static constexpr int GROUP_BYTES = TK * RB;              // one atom column: 64 k rows
+    static constexpr int BYTES = GROUPS * GROUP_BYTES;       // = 64 * N * 2
+    static constexpr int STAGE_BYTES = A_BYTES + (BYTES < 1024 ? 1024 : BYTES);
+    static constexpr int CHUNKS = BYTES / 16;
+    static constexpr int SBO = 8 * RB;                       // 8 k rows
+    static constexpr int K16_STEP = 16 * RB;                 // bytes between the K=16 slices of one tile
+    static constexpr int TMEM_COLS = 2 * N < 32 ? 32 : 2 * N;
+    // instruction descriptor (UMMA::InstrDescriptor): D fp32, A/B fp16, A K-major, B MN-major, N >> 3, M >> 4
+    static constexpr uint32_t IDESC = (1u << 4) | (1u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+};
+
+template <int N> constexpr int tile_stages() { return N <= 64 ? 8 : N == 128 ? 6 : 4; }
+
+template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_args a)
+{
+    using G = b_geom<N>;
+    constexpr int S = tile_stages<N>();
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * S + 4];
+    __shared__ uint32_t tmem_slot;
+    // 1024-byte alignment of the stage buffers (128-byte swizzle atoms)
+    const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    unsigned char *smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
+    uint32_t *s_ptr = (uint32_t *)(smem_al + (size_t)S * G::STAGE_BYTES); // the CTA's slice of tile_ptr
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t n_cta = gridDim.x, cta = blockIdx.x;
+    const uint32_t t0 = (uint32_t)((uint64_t)cta * a.n_tiles / n_cta), t1 = (uint32_t)((uint64_t)(cta + 1) * a.n_tiles / n_cta);
+    const uint32_t n_local = t1 - t0;
+    const uint32_t KT = a.k_tiles;
+
+    const uint32_t bar0 = smem_u32(bars);
+    auto full_bar = [&](uint32_t s) { return bar0 + 8u * s; };
+    auto empty_bar = [&](uint32_t s) { return bar0 + 8u * (S + s); };
+    auto accf_bar = [&](uint32_t b) { return bar0 + 8u * (2 * S + b); };
+    auto acce_bar = [&](uint32_t b) { return bar0 + 8u * (2 * S + 2 + b); };
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < S; s++) mbar_init(&bars[s], 8), mbar_init(&bars[S + s], 1);
+        mbar_init(&bars[2 * S], 1), mbar_init(&bars[2 * S + 1], 1);
+        mbar_init(&bars[2 * S + 2], 4), mbar_init(&bars[2 * S + 3], 4);
+    }
+    if (warp == MMA_WARP) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"((uint32_t)G::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    const bool ptr_in_smem = n_local + 1 <= a.ptr_cap;
+    if (ptr_in_smem)
+        for (uint32_t i = threadIdx.x; i <= n_local; i += blockDim.x) s_ptr[i] = a.tile_ptr[t0 + i];
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+    row::pdl_launch_dependents();
+
+    auto run_begin = [&](uint32_t it) { return ptr_in_smem ? s_ptr[it] : a.tile_ptr[t0 + it]; };
+
+    if (warp < EPI_WARP0) {
+        // ------------------------------------------------------------------------------------------ producers
+        const uint32_t g = warp >> 3, gt = threadIdx.x & (GROUP_THREADS - 1);
+        const uint4 *Bg = (const uint4 *)a.B;
+        uint4 o[2], v[2], nb[(G::CHUNKS + GROUP_THREADS - 1) / GROUP_THREADS];
+        constexpr int BCH = (G::CHUNKS + GROUP_THREADS - 1) / GROUP_THREADS;
+        uint32_t e0 = 0, e1 = 0;
+        auto load_tile = [&](uint32_t it) {
+            if (it >= n_local) return;
+            e0 = run_begin(it), e1 = run_begin(it + 1);
+#pragma unroll
+            for (int p = 0; p < 2; p++) {
+                const uint32_t e = e0 + p * 2048u + gt * 8u;
+                if (e < e1) o[p] = ld_stream_v4(a.off + e), v[p] = ld_stream_v4(a.val + e);
+            }
+            // this thread's 16-byte pieces of the 64 x N slice of B: piece x = k row x / (N/8), column chunk x % (N/8)
+            const uint32_t k0 = ((t0 + it) % KT) * TK;
+#pragma unroll
+            for (int j = 0; j < BCH; j++) {
+                const uint32_t x = gt + j * GROUP_THREADS, k = x / (N / 8);
+                nb[j] = make_uint4(0, 0, 0, 0);
+                if (x < (uint32_t)G::CHUNKS && k0 + k < a.K) nb[j] = __ldg(Bg + (size_t)(k0 + k) * (N / 8) + x % (N / 8));
+            }
+        };
+        load_tile(g);
+        for (uint32_t it = g; it < n_local; it += 2) {
+            const uint32_t s = it % S, ph = (it / S) & 1u;
+            const uint32_t abase = smem0 + s * G::STAGE_BYTES, bbase = abase + A_BYTES;
+            const uint4 co[2] = {o[0], o[1]}, cv[2] = {v[0], v[1]};
+            uint4 cb[BCH];
+#pragma unroll
+            for (int j = 0; j < BCH; j++) cb[j] = nb[j];
+            const uint32_t ce0 = e0, ce1 = e1;
+            load_tile(it + 2); // the group's next tile is in flight while this one is rebuilt
+            mbar_wait(empty_bar(s), ph ^ 1u);
+            // zero the image of A's tile, copy B's slice into the swizzled MN-major operand layout
+#pragma unroll
+            for (int j = 0; j < A_BYTES / 16 / GROUP_THREADS; j++) sts128(abase + (gt + j * GROUP_THREADS) * 16u, make_uint4(0, 0, 0, 0));
+#pragma unroll
+            for (int j = 0; j < BCH; j++) {
+                const uint32_t x = gt + j * GROUP_THREADS;
+                if (x < (uint32_t)G::CHUNKS) {
+                    const uint32_t k = x / (N / 8), c = x % (N / 8), grp = c / (G::ATOM_N / 8), cc = c % (G::ATOM_N / 8);
+                    const uint32_t swz = ((k * G::RB) >> 7) & G::SWZ_MASK;
+                    sts128(bbase + grp * G::GROUP_BYTES + k * G::RB + ((cc ^ swz) << 4), cb[j]);
+                }
+            }
+            bar_sync(1 + g, GROUP_THREADS);
+            auto scatter = [&](const uint4 &oo, const uint4 &vv) {
+                const uint32_t ow[4] = {oo.x, oo.y, oo.z, oo.w}, vw[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    sts16(abase + (ow[j] & 0xffffu), (unsigned short)(vw[j] & 0xffffu));
+                    sts16(abase + (ow[j] >> 16), (unsigned short)(vw[j] >> 16));
+                }
+            };
+#pragma unroll
+            for (int p = 0; p < 2; p++)
+                if (ce0 + p * 2048u + gt * 8u < ce1) scatter(co[p], cv[p]);
+            for (uint32_t e = ce0 + 4096u + gt * 8u; e < ce1; e += 2048u) scatter(ld_stream_v4(a.off + e), ld_stream_v4(a.val + e)); // > 4096 pairs: dense tiles
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(full_bar(s));
+        }
+    } else if (warp == MMA_WARP) {
+        // ------------------------------------------------------------------------------------------ MMA issue
+        if (lane == 0) {
+            uint32_t it = 0, seg = 0;
+            while (it < n_local) {
+                const uint32_t kt0 = (t0 + it) % KT, len = min(KT - kt0, n_local - it), ab = seg & 1u;
+                mbar_wait(acce_bar(ab), ((seg >> 1) & 1u) ^ 1u);
+                tc_fence_after();
+                const uint32_t d = tmem_base + ab * N;
+                for (uint32_t i = 0; i < len; i++, it++) {
+                    const uint32_t s = it % S, ph = (it / S) & 1u;
+                    mbar_wait(full_bar(s), ph);
+                    tc_fence_after();
+                    const uint32_t abase = smem0 + s * G::STAGE_BYTES, bbase = abase + A_BYTES;
+#pragma unroll
+                    for (int k = 0; k < TK / 16; k++) {
+                        const uint64_t ad = smem_desc(abase + k * 32, 16, 1024, 2u);
+                        const uint64_t bd = smem_desc(bbase + k * G::K16_STEP, G::GROUP_BYTES, G::SBO, G::LAYOUT);
+                        tc_mma_f16(d, ad, bd, G::IDESC, (i > 0 || k > 0) ? 1u : 0u);
+                    }
+                    tc_commit(empty_bar(s));
+                }
+                tc_commit(accf_bar(ab));
+                seg++;
+            }
+        }
+        __syncwarp();
+    } else {
+        // ------------------------------------------------------------------------------------------ epilogue
+        const uint32_t q = warp - EPI_WARP0, rip = q * 32 + lane, et = threadIdx.x - EPI_WARP0 * 32;
+        __half *C = (__half *)a.C;
+        bool waited = false;
+        uint32_t it = 0, seg = 0;
+        while (it < n_local) {
+            const uint32_t t = t0 + it, panel = t / KT, kt0 = t % KT, len = min(KT - kt0, n_local - it), ab = seg & 1u;
+            const bool partial_in = kt0 > 0;               // someone else owns the panel: leave a partial
+            const bool owner_wait = !partial_in && len < KT; // this CTA owns the panel and others hold its tail
+            mbar_wait(accf_bar(ab), (seg >> 1) & 1u);
+            tc_fence_after();
+            if (!waited) row::pdl_wait(), waited = true; // the first global store of this launch
+            const uint32_t taddr = tmem_base + ((q * 32u) << 16) + ab * N;
+            if (partial_in) {
+                float *slot = a.ws + ((size_t)cta * TM + rip) * N;
+#pragma unroll 1
+                for (int c = 0; c < N / 16; c++) {
+                    uint32_t r[16];
+                    tc_ld16(taddr + c * 16, r);
+#pragma unroll
+                    for (int j = 0; j < 4; j++) __stcg((uint4 *)(slot + c * 16) + j, make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]));
+                }
+                __threadfence();
+                bar_sync(3, 128);
+                if (et == 0) st_release(a.flags + cta, a.seq);
+            } else {
+                uint32_t c_last = cta; // contributors: the CTAs after this one whose first tile lies inside the panel
+                if (owner_wait) {
+                    const uint64_t panel_end = (uint64_t)(panel + 1) * KT;
+                    while (c_last + 1 < n_cta && (uint64_t)(c_last + 1) * a.n_tiles / n_cta < panel_end) c_last++;
+                    for (uint32_t c2 = cta + 1; c2 <= c_last; c2++)
+                        while (ld_acquire(a.flags + c2) != a.seq) __nanosleep(64);
+                }
+                const uint32_t orow = a.out_row[(size_t)panel * TM + rip];
+#pragma unroll 1
+                for (int c = 0; c < N / 16; c++) {
+                    uint32_t r[16];
+                    tc_ld16(taddr + c * 16, r);
+                    float f[16];
+#pragma unroll
+                    for (int j = 0; j < 16; j++) f[j] = __uint_as_float(r[j]);
+                    for (uint32_t c2 = cta + 1; c2 <= c_last; c2++) {
+                        const float4 *slot = (const float4 *)(a.ws + ((size_t)c2 * TM + rip) * N + c * 16);
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            const float4 x = __ldcg(slot + j);
+                            f[4 * j] += x.x, f[4 * j + 1] += x.y, f[4 * j + 2] += x.z, f[4 * j + 3] += x.w;
+                        }
+                    }
+                    if (orow != 0xffffffffu) {
+                        uint32_t h[8];
+#pragma unroll
+                        for (int j = 0; j < 8; j++) {
+                            __half2 p = __floats2half2_rn(f[2 * j], f[2 * j + 1]);
+                            h[j] = *(uint32_t *)&p;
+                        }
+                        uint4 *dst = (uint4 *)(C + (size_t)orow * N + c * 16);
+                        dst[0] = make_uint4(h[0], h[1], h[2], h[3]), dst[1] = make_uint4(h[4], h[5], h[6], h[7]);
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acce_bar(ab));
+            it += len, seg++;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)G::TMEM_COLS) : "memory");
+}
+
+} // namespace tile
+} // namespace gsd

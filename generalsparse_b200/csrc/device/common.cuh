@@ -79,4 +79,12 @@ cudaError_t b200_row_prepare(const launch_params &p, int sm_count, b200_row_plan
 cudaError_t b200_row_launch(const b200_row_plan *plan, const launch_params &p, cudaStream_t s);
 void b200_row_free(b200_row_plan *plan);
 const char *b200_row_kernel_name(const b200_row_plan *plan);
+
+struct b200_tile_plan; // opaque, kernels_tile.cu
+cudaError_t b200_tile_prepare(const launch_params &p, int sm_count, b200_tile_plan **out, cudaStream_t s);
+cudaError_t b200_tile_launch(b200_tile_plan *plan, const launch_params &p, cudaStream_t s);
+void b200_tile_free(b200_tile_plan *plan);
+const char *b200_tile_kernel_name(const b200_tile_plan *plan);
+uint64_t b200_tile_bytes(const b200_tile_plan *plan, uint64_t rows, uint64_t cols);
+uint64_t b200_tile_pairs(const b200_tile_plan *plan);
 } // namespace gsd

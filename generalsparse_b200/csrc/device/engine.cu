@@ -55,6 +55,7 @@ struct gs_plan {
     int kernel = 0; // gs_family actually launched
     gsd::launch_params lp;
     gsd::b200_row_plan *row_plan = nullptr;
+    gsd::b200_tile_plan *tile_plan = nullptr;
     void *B_dev = nullptr;  // owned
     const void *B_use = nullptr;
     void *C_dev = nullptr;
@@ -267,9 +268,17 @@ static void select_kernel(gs_plan *p, int family)
         add(lvl, "first_row_indices"), add(lvl, "first_nz_indices");
         break;
     }
+    case GS_FAMILY_B200_TCGEN05: {
+        if (p->tile_plan) gsd::b200_tile_free(p->tile_plan), p->tile_plan = nullptr;
+        GS_REQUIRE(p->half, "b200_tcgen05: the tensor-core path multiplies fp16 operands (HALF); fp32 values stay on the gather kernels");
+        cudaError_t e = gsd::b200_tile_prepare(p->lp, ctx->sm_count, &p->tile_plan, ctx->stream);
+        if (e == cudaErrorInvalidValue) throw gs::Error("b200_tcgen05: needs N in {16,32,64,128,256}, HALF values and a row-direction chain with row block 1");
+        CUDA_TRY(e);
+        break;
+    }
     default: throw gs::Error("kernel family not built: " + std::string(gs_family_name(family)));
     }
-    if (p->desc.has_row_permutation) add("GLOBAL_META", "original_nz_row_indices");
+    if (p->desc.has_row_permutation && family != GS_FAMILY_B200_TCGEN05) add("GLOBAL_META", "original_nz_row_indices");
     p->offset_bytes = ob;
     p->kernel = family;
 }
@@ -289,6 +298,11 @@ static void enqueue(gs_plan *p)
         static const bool no_pdl = getenv("GS_NO_PDL") != nullptr;
         lp.pdl = p->ctx->row_chain && !no_pdl;
         CUDA_TRY(gsd::b200_row_launch(p->row_plan, lp, p->ctx->stream));
+        p->ctx->row_chain = true;
+    } else if (p->kernel == GS_FAMILY_B200_TCGEN05) {
+        static const bool no_pdl = getenv("GS_NO_PDL") != nullptr;
+        lp.pdl = p->ctx->row_chain && !no_pdl;
+        CUDA_TRY(gsd::b200_tile_launch(p->tile_plan, lp, p->ctx->stream));
         p->ctx->row_chain = true;
     } else {
         CUDA_TRY(gsd::launch_reference_family(p->kernel, lp, p->ctx->mem_stream()));
@@ -404,6 +418,7 @@ void gs_plan_destroy(gs_plan *p)
     if (!p) return;
     cudaSetDevice(p->ctx->device);
     if (p->row_plan) gsd::b200_row_free(p->row_plan);
+    if (p->tile_plan) gsd::b200_tile_free(p->tile_plan);
     if (p->B_dev) cudaFree(p->B_dev);
     if (p->C_dev) cudaFree(p->C_dev);
     if (p->ev0) cudaEventDestroy(p->ev0);
@@ -556,6 +571,7 @@ uint64_t gs_plan_algorithmic_bytes(const gs_plan *p)
 {
     if (!p) return 0;
     // nnz_stored*(idx+val) + offset arrays + K*N*sizeof(B) + M*N*sizeof(C) (+ permutation)
+    if (p->kernel == GS_FAMILY_B200_TCGEN05) return gsd::b200_tile_bytes(p->tile_plan, p->desc.rows, p->desc.cols);
     uint64_t idx = p->lp.a.col_is_u16 ? 2 : 4;
     return p->lp.a.nnz * (idx + p->esz()) + p->offset_bytes + (uint64_t)p->desc.cols * p->N * p->esz() + (uint64_t)p->desc.rows * p->N * p->esz();
 }
@@ -566,6 +582,7 @@ const char *gs_plan_kernel_name(const gs_plan *p)
 {
     if (!p) return "";
     if (p->kernel == GS_FAMILY_B200_ROW_SMEM) return gsd::b200_row_kernel_name(p->row_plan);
+    if (p->kernel == GS_FAMILY_B200_TCGEN05) return gsd::b200_tile_kernel_name(p->tile_plan);
     return gsd::reference_family_kernel_name(p->kernel);
 }
 

@@ -1,0 +1,169 @@
+// Host side of the B200 tile kernel (GS_FAMILY_B200_TCGEN05): builds the tile stream of a row-direction chain once per
+// plan (host/tile_format.hpp), owns the device copies, the stream-K workspace and the launch.  Device code and the
+// design notes: b200_tile.cuh.
+#include "b200_tile.cuh"
+#include "../host/tile_format.hpp"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+namespace gsd {
+
+struct b200_tile_plan {
+    uint32_t *tile_ptr = nullptr, *out_row = nullptr, *flags = nullptr;
+    uint16_t *off = nullptr, *val = nullptr;
+    float *ws = nullptr;
+    uint32_t n_tiles = 0, k_tiles = 0, n_panels = 0, grid = 0, ptr_cap = 0, seq = 0;
+    uint64_t pairs = 0, nnz = 0;
+    size_t smem = 0;
+    const void *fn = nullptr;
+    int N = 0;
+    char name[96] = {0};
+};
+
+namespace {
+
+template <int N> void pick(const void *&fn, size_t &stage_bytes)
+{
+    fn = (const void *)tile::k_b200_tile<N>;
+    stage_bytes = (size_t)tile::tile_stages<N>() * tile::b_geom<N>::STAGE_BYTES;
+}
+
+int env_int(const char *name, int dflt)
+{
+    const char *v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+
+} // namespace
+
+cudaError_t b200_tile_prepare(const launch_params &p, int sm_count, b200_tile_plan **out, cudaStream_t s)
+{
+    *out = nullptr;
+    if (!p.a.val_is_f16) return cudaErrorInvalidValue; // kind::f16 operands; fp32 values stay on the gather kernels (tf32 would break the 1e-5 bound)
+    const uint32_t *rowptr = nullptr, *rowid = nullptr;
+    uint32_t n_rows = 0;
+    if (p.a.t_first_nz && p.a.t_first_row && !p.a.t_nz_relative) rowptr = p.a.t_first_nz, rowid = p.a.t_first_row, n_rows = p.a.n_t;
+    else if (p.a.w_first_nz && p.a.w_first_row) rowptr = p.a.w_first_nz, rowid = p.a.w_first_row, n_rows = p.a.n_w;
+    else if (p.a.tb_first_nz && p.a.tb_first_row) rowptr = p.a.tb_first_nz, rowid = p.a.tb_first_row, n_rows = p.a.n_tb;
+    else return cudaErrorInvalidValue;
+    b200_tile_plan *pl = new (std::nothrow) b200_tile_plan;
+    if (!pl) return cudaErrorMemoryAllocation;
+    auto fail = [&](cudaError_t e) {
+        b200_tile_free(pl);
+        return e;
+    };
+    size_t stage_bytes = 0;
+    switch (p.N) {
+    case 16: pick<16>(pl->fn, stage_bytes); break;
+    case 32: pick<32>(pl->fn, stage_bytes); break;
+    case 64: pick<64>(pl->fn, stage_bytes); break;
+    case 128: pick<128>(pl->fn, stage_bytes); break;
+    case 256: pick<256>(pl->fn, stage_bytes); break;
+    default: return fail(cudaErrorInvalidValue); // M=128 tcgen05.mma wants N % 16 == 0; N=8 stays on the stream kernel
+    }
+    pl->N = p.N;
+
+    // the chain's arrays back to the host, once
+    std::vector<uint32_t> rp(n_rows + 1), rid(n_rows), perm, colw(p.a.nnz);
+    std::vector<uint16_t> val(p.a.nnz);
+    cudaError_t e;
+    if ((e = cudaMemcpyAsync(rp.data(), rowptr, rp.size() * 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemcpyAsync(rid.data(), rowid, rid.size() * 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemcpyAsync(val.data(), p.a.val, val.size() * 2, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+    if (p.a.perm) {
+        perm.resize(p.a.rows);
+        if ((e = cudaMemcpyAsync(perm.data(), p.a.perm, perm.size() * 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+    }
+    if (p.a.col_is_u16) {
+        std::vector<uint16_t> c16(p.a.nnz);
+        if ((e = cudaMemcpyAsync(c16.data(), p.a.col, c16.size() * 2, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+        if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(e);
+        for (size_t i = 0; i < c16.size(); i++) colw[i] = c16[i];
+    } else {
+        if ((e = cudaMemcpyAsync(colw.data(), p.a.col, colw.size() * 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+        if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(e);
+    }
+    if (rp[n_rows] > p.a.nnz) return fail(cudaErrorInvalidValue);
+
+    gs::tile_stream ts;
+    try {
+        gs::build_tile_stream(rp.data(), colw.data(), val.data(), n_rows, p.a.cols, !env_int("GS_TILE_NO_BANK_ORDER", 0), ts);
+    } catch (...) {
+        return fail(cudaErrorInvalidValue);
+    }
+    pl->n_panels = ts.n_panels, pl->k_tiles = ts.k_tiles, pl->n_tiles = ts.n_panels * ts.k_tiles;
+    pl->pairs = ts.off.size(), pl->nnz = ts.nnz;
+    pl->grid = (uint32_t)std::min<uint64_t>((uint64_t)env_int("GS_TILE_CTAS", sm_count), pl->n_tiles);
+    if (pl->grid == 0 || (int)pl->grid > sm_count) return fail(cudaErrorInvalidValue); // the split-panel hand-off needs every CTA resident
+
+    std::vector<uint32_t> orow((size_t)ts.n_panels * gs::TILE_ROWS, 0xffffffffu);
+    for (uint32_t i = 0; i < n_rows; i++) {
+        const uint32_t r = rid[i];
+        if (p.a.perm && r >= perm.size()) return fail(cudaErrorInvalidValue);
+        orow[i] = (p.a.perm ? perm[r] : r) + p.a.begin_row;
+    }
+
+    const uint32_t per_cta = (pl->n_tiles + pl->grid - 1) / pl->grid + 1;
+    pl->ptr_cap = std::min<uint32_t>(per_cta + 1, 4096u); // the CTA's slice of tile_ptr sits behind the stages in shared memory
+    pl->smem = stage_bytes + 1024 + (size_t)pl->ptr_cap * 4;
+    if (pl->smem > 227 * 1024) pl->ptr_cap = 0, pl->smem = stage_bytes + 1024;
+
+    auto up = [&](void **dst, const void *src, size_t bytes) {
+        cudaError_t e2 = cudaMalloc(dst, bytes + 16);
+        if (e2 != cudaSuccess) return e2;
+        return bytes ? cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess;
+    };
+    if ((e = up((void **)&pl->tile_ptr, ts.tile_ptr.data(), ts.tile_ptr.size() * 4)) != cudaSuccess) return fail(e);
+    if ((e = up((void **)&pl->off, ts.off.data(), ts.off.size() * 2)) != cudaSuccess) return fail(e);
+    if ((e = up((void **)&pl->val, ts.val.data(), ts.val.size() * 2)) != cudaSuccess) return fail(e);
+    if ((e = up((void **)&pl->out_row, orow.data(), orow.size() * 4)) != cudaSuccess) return fail(e);
+    if ((e = cudaMalloc((void **)&pl->ws, (size_t)pl->grid * tile::TM * p.N * 4)) != cudaSuccess) return fail(e);
+    if ((e = cudaMalloc((void **)&pl->flags, (size_t)pl->grid * 4)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemsetAsync(pl->flags, 0, (size_t)pl->grid * 4, s)) != cudaSuccess) return fail(e);
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(e);
+    if ((e = cudaFuncSetAttribute(pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem)) != cudaSuccess) return fail(e);
+    snprintf(pl->name, sizeof pl->name, "k_b200_tile<N%d,f16,tcgen05 m128n%dk16,%d stages,streamK x%u%s,pdl>", p.N, p.N, p.N <= 64 ? 8 : p.N == 128 ? 6 : 4, pl->grid,
+             env_int("GS_TILE_NO_BANK_ORDER", 0) ? "" : ",bank-ordered");
+    *out = pl;
+    return cudaSuccess;
+}
+
+cudaError_t b200_tile_launch(b200_tile_plan *pl, const launch_params &p, cudaStream_t s)
+{
+    tile::tile_args a;
+    a.tile_ptr = pl->tile_ptr, a.off = pl->off, a.val = pl->val, a.B = p.B, a.C = p.C, a.out_row = pl->out_row;
+    a.ws = pl->ws, a.flags = pl->flags;
+    a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.K = p.a.cols, a.seq = ++pl->seq, a.ptr_cap = pl->ptr_cap;
+    void *args[] = {&a};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(tile::THREADS), cfg.dynamicSmemBytes = pl->smem, cfg.stream = s;
+    cfg.attrs = attr, cfg.numAttrs = p.pdl ? 1 : 0;
+    return cudaLaunchKernelExC(&cfg, pl->fn, args);
+}
+
+void b200_tile_free(b200_tile_plan *pl)
+{
+    if (!pl) return;
+    cudaFree(pl->tile_ptr), cudaFree(pl->out_row), cudaFree(pl->flags), cudaFree(pl->off), cudaFree(pl->val), cudaFree(pl->ws);
+    delete pl;
+}
+
+const char *b200_tile_kernel_name(const b200_tile_plan *pl) { return pl ? pl->name : ""; }
+
+// bytes one launch must move: the pair stream, the run starts, the output row table, B and C once each
+uint64_t b200_tile_bytes(const b200_tile_plan *pl, uint64_t rows, uint64_t cols)
+{
+    return pl->pairs * 4 + ((uint64_t)pl->n_tiles + 1) * 4 + (uint64_t)pl->n_panels * tile::TM * 4 + cols * pl->N * 2 + rows * pl->N * 2;
+}
+uint64_t b200_tile_pairs(const b200_tile_plan *pl) { return pl->pairs; }
+
+} // namespace gsd

@@ -182,3 +182,32 @@ def test_errors_are_statuses_not_aborts(engine):
     with pytest.raises(api.GsError) as ei:  # pad-to-64 on ~4 nnz rows: the reference aborts, we return a status
         s.run_family("warp_bitmap", 8, 1, 1)
     assert ei.value.status == 5
+
+
+@pytest.mark.parametrize("N", [16, 32, 64, 128, 256])
+@pytest.mark.parametrize("chain", ["thread_total", "warp_total"])
+def test_b200_tile_kernel(engine, N, chain):
+    """decompress-to-shared-memory + tcgen05 path (HALF): exact in reference mode, in tolerance on random values;
+    1000 x 4096 splits its 8 row panels over all CTAs (stream-K hand-off), 300 x 1000 has a ragged K tail and
+    empty rows, 130 x 70 is smaller than two tiles"""
+    from generalsparse_b200 import synth
+    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    mats = [("uniform", 1000, 4096, dict(density=0.1)), ("ragged", 300, 1000, dict(mean_len=20.0, empty_frac=0.2)), ("uniform", 130, 70, dict(density=0.3))]
+    for i, (kind, nrows, cols, kw) in enumerate(mats):
+        rr, cc = _matrix(kind, nrows, cols, seed=51 + i, **kw)
+        indptr = csr_from_coo(nrows, rr)
+        S = 8 if chain == "thread_total" else 1
+        B1 = np.ones((cols, N), dtype=np.float32)
+        C, plan = _run(engine, chain, nrows, cols, rr, cc, None, B1, N, S, 1, half=True, kernel="b200_tcgen05")
+        assert "k_b200_tile" in plan.kernel_name
+        ref = oracle_spmm_f32(nrows, N, indptr, cc, np.ones(len(rr), np.float32), B1)
+        assert np.array_equal(C.astype(np.float32), ref), plan.kernel_name
+        vals = synth.synth_values(len(rr), seed=5).astype(np.float16).astype(np.float32)
+        B = synth.synth_dense(cols, N, seed=5).astype(np.float16).astype(np.float32)
+        C, plan = _run(engine, chain, nrows, cols, rr, cc, vals, B, N, S, 1, half=True, kernel="b200_tcgen05")
+        ref = oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B)
+        absrow = oracle_spmm_absrow(nrows, N, indptr, cc, vals, B)
+        _check(C, ref, absrow * 1e-2, 1e-2)
+        # repeated launches (programmatic dependent launch, workspace and flag reuse) give the same bits
+        plan.run(5)
+        assert np.array_equal(plan.output(), C)
