@@ -6,11 +6,15 @@
 // 12 us and 23 us on 148 SMs against 8.4 us of HBM time.  A 30 %-dense 128 x 64 tile rebuilt in shared memory costs one
 // 2-byte store per non-zero whatever N is, and the contraction itself (2.9 GFLOP dense at N=32) is 2 us of tensor pipe.
 //
-// One persistent CTA per SM, 21 warps:
-//   warps 0-15  two producer groups of 8 warps, alternating tiles: zero the 16 KB image of A's tile (K-major, 128-byte
-//               swizzle), copy the 64 x N piece of B in the MN-major swizzled operand layout, scatter the tile's
-//               (offset, value) pairs with 2-byte stores (128-bit loads of 8 offsets + 8 values per lane, the next
-//               tile's loads issued before this tile's stores), fence to the async proxy, arrive on full[stage];
+// One persistent CTA per SM, 22 warps:
+//   warp 21     one lane runs ahead of everybody: bulk L2 prefetch of the pair runs 8 tiles ahead (UBLKPF), and, as
+//               soon as the tensor core has released a stage, one st.bulk that zeroes the 16 KB image of A's tile
+//               (UMEMSETS), then an arrive on zeroed[stage];
+//   warps 0-15  two producer groups of 8 warps, alternating tiles: copy the 64 x N piece of B in the MN-major swizzled
+//               operand layout, scatter the tile's (offset, value) pairs with 2-byte stores into the K-major
+//               128-byte-swizzled image (128-bit loads of 8 offsets + 8 values per lane; two register sets, so the next
+//               tile's loads are in flight while this tile is stored), fence to the async proxy, arrive on
+//               full[stage]; no barrier between the warps of a group;
 //   warp 20     one elected lane issues 4 tcgen05.mma (M=128, N, K=16) per tile, commits to empty[stage], and to
 //               acc_full[] at the end of a row panel; two accumulators in TMEM alternate between panels;
 //   warps 16-19 epilogue: tcgen05.ld the accumulator (lane = row), convert, store the rows of C.
@@ -27,7 +31,7 @@ using row::mbar_init;
 using row::smem_u32;
 
 constexpr int TM = 128, TK = 64, A_BYTES = TM * TK * 2;
-constexpr int GROUP_THREADS = 256, EPI_WARP0 = 16, MMA_WARP = 20, THREADS = 21 * 32;
+constexpr int GROUP_THREADS = 256, EPI_WARP0 = 16, MMA_WARP = 20, AHEAD_WARP = 21, THREADS = 22 * 32, PF_TILES = 8;
 
 struct tile_args {
     const uint32_t *tile_ptr; // n_tiles + 1
@@ -38,8 +42,31 @@ struct tile_args {
     float *ws;               // grid x 128 x N fp32 partial panels
     uint32_t *flags;         // grid
     uint32_t n_tiles, k_tiles, K, seq, ptr_cap;
+    uint32_t skip; // GS_TILE_SKIP (timing experiments, wrong results): 1 no scatter, 2 no zero fill, 4 no mma, 8 no B copy, 16 no pair loads, 32 no fence
+    unsigned long long *dbg; // GS_TILE_DEBUG: 8 (globaltimer, clock64) stamps per CTA, or null
 };
 
+__device__ __forceinline__ void stamp(const tile_args &a, int ev)
+{
+    if (a.dbg) {
+        unsigned long long g;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+        a.dbg[((size_t)blockIdx.x * 16 + ev) * 2] = g, a.dbg[((size_t)blockIdx.x * 16 + ev) * 2 + 1] = (unsigned long long)clock64();
+    }
+}
+
+__device__ __forceinline__ void counter(const tile_args &a, int ev, long long v)
+{
+    if (a.dbg) a.dbg[((size_t)blockIdx.x * 16 + ev) * 2] = 1, a.dbg[((size_t)blockIdx.x * 16 + ev) * 2 + 1] = (unsigned long long)v;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity);
+// timed wait: adds the cycles spent to acc (debug builds of the timeline only cost a clock read per wait)
+__device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity, long long &acc)
+{
+    long long t = clock64();
+    mbar_wait(bar, parity);
+    acc += clock64() - t;
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 {
     asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(bar),
@@ -67,6 +94,8 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&r)[16])
 }
 __device__ __forceinline__ void sts16(uint32_t addr, unsigned short v) { asm volatile("st.shared.b16 [%0], %1;" ::"r"(addr), "h"(v) : "memory"); }
 __device__ __forceinline__ void sts128(uint32_t addr, uint4 v) { asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); }
+__device__ __forceinline__ void smem_zero_bulk(uint32_t addr, uint32_t bytes) { asm volatile("st.bulk.weak.shared::cta [%0], %1, 0;" ::"r"(addr), "l"((uint64_t)bytes) : "memory"); }
+__device__ __forceinline__ void l2_prefetch_bulk(const void *p, uint32_t bytes) { asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory"); }
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
 {
@@ -109,7 +138,7 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
     using G = b_geom<N>;
     constexpr int S = tile_stages<N>();
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t bars[2 * S + 4];
+    __shared__ __align__(8) uint64_t bars[3 * S + 4];
     __shared__ uint32_t tmem_slot;
     // 1024-byte alignment of the stage buffers (128-byte swizzle atoms)
     const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -122,16 +151,18 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
     const uint32_t n_local = t1 - t0;
     const uint32_t KT = a.k_tiles;
 
+    if (threadIdx.x == 0) stamp(a, 0);
     const uint32_t bar0 = smem_u32(bars);
     auto full_bar = [&](uint32_t s) { return bar0 + 8u * s; };
     auto empty_bar = [&](uint32_t s) { return bar0 + 8u * (S + s); };
-    auto accf_bar = [&](uint32_t b) { return bar0 + 8u * (2 * S + b); };
-    auto acce_bar = [&](uint32_t b) { return bar0 + 8u * (2 * S + 2 + b); };
+    auto zeroed_bar = [&](uint32_t s) { return bar0 + 8u * (2 * S + s); };
+    auto accf_bar = [&](uint32_t b) { return bar0 + 8u * (3 * S + b); };
+    auto acce_bar = [&](uint32_t b) { return bar0 + 8u * (3 * S + 2 + b); };
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < S; s++) mbar_init(&bars[s], 8), mbar_init(&bars[S + s], 1);
-        mbar_init(&bars[2 * S], 1), mbar_init(&bars[2 * S + 1], 1);
-        mbar_init(&bars[2 * S + 2], 4), mbar_init(&bars[2 * S + 3], 4);
+        for (int s = 0; s < S; s++) mbar_init(&bars[s], 8), mbar_init(&bars[S + s], 1), mbar_init(&bars[2 * S + s], 1);
+        mbar_init(&bars[3 * S], 1), mbar_init(&bars[3 * S + 1], 1);
+        mbar_init(&bars[3 * S + 2], 4), mbar_init(&bars[3 * S + 3], 4);
     }
     if (warp == MMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"((uint32_t)G::TMEM_COLS) : "memory");
@@ -145,6 +176,7 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
     row::pdl_launch_dependents();
+    if (threadIdx.x == 0) stamp(a, 1);
 
     auto run_begin = [&](uint32_t it) { return ptr_in_smem ? s_ptr[it] : a.tile_ptr[t0 + it]; };
 
@@ -152,50 +184,53 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
         // ------------------------------------------------------------------------------------------ producers
         const uint32_t g = warp >> 3, gt = threadIdx.x & (GROUP_THREADS - 1);
         const uint4 *Bg = (const uint4 *)a.B;
-        uint4 o[2], v[2], nb[(G::CHUNKS + GROUP_THREADS - 1) / GROUP_THREADS];
-        constexpr int BCH = (G::CHUNKS + GROUP_THREADS - 1) / GROUP_THREADS;
-        uint32_t e0 = 0, e1 = 0;
-        auto load_tile = [&](uint32_t it) {
+        constexpr int BCH = (G::CHUNKS + GROUP_THREADS - 1) / GROUP_THREADS; // 16-byte pieces of B's slice per thread
+        constexpr bool PRE_B = BCH <= 2;                                     // B pieces travel with the pairs, one tile ahead
+        long long w_zeroed = 0, w_store = 0;
+        struct pre {
+            uint4 o[2], v[2], b[PRE_B ? BCH : 1];
+            uint32_t e0, e1;
+        };
+        // this thread's pieces of the 64 x N slice of B: piece x = k row x / (N/8), column chunk x % (N/8)
+        auto load_b = [&](uint32_t it, int j) {
+            const uint32_t k0 = ((t0 + it) % KT) * TK, x = gt + j * GROUP_THREADS, k = x / (N / 8);
+            uint4 r = make_uint4(0, 0, 0, 0);
+            if (x < (uint32_t)G::CHUNKS && k0 + k < a.K) r = __ldg(Bg + (size_t)(k0 + k) * (N / 8) + x % (N / 8));
+            return r;
+        };
+        auto load_tile = [&](pre &P, uint32_t it) {
             if (it >= n_local) return;
-            e0 = run_begin(it), e1 = run_begin(it + 1);
+            P.e0 = run_begin(it), P.e1 = run_begin(it + 1);
 #pragma unroll
             for (int p = 0; p < 2; p++) {
-                const uint32_t e = e0 + p * 2048u + gt * 8u;
-                if (e < e1) o[p] = ld_stream_v4(a.off + e), v[p] = ld_stream_v4(a.val + e);
+                const uint32_t e = P.e0 + p * 2048u + gt * 8u;
+                if (e < P.e1 && !(a.skip & 16u)) P.o[p] = ld_stream_v4(a.off + e), P.v[p] = ld_stream_v4(a.val + e);
             }
-            // this thread's 16-byte pieces of the 64 x N slice of B: piece x = k row x / (N/8), column chunk x % (N/8)
-            const uint32_t k0 = ((t0 + it) % KT) * TK;
+            if (PRE_B) {
 #pragma unroll
-            for (int j = 0; j < BCH; j++) {
-                const uint32_t x = gt + j * GROUP_THREADS, k = x / (N / 8);
-                nb[j] = make_uint4(0, 0, 0, 0);
-                if (x < (uint32_t)G::CHUNKS && k0 + k < a.K) nb[j] = __ldg(Bg + (size_t)(k0 + k) * (N / 8) + x % (N / 8));
+                for (int j = 0; j < BCH; j++) P.b[j] = load_b(it, j);
             }
         };
-        load_tile(g);
-        for (uint32_t it = g; it < n_local; it += 2) {
+        auto process = [&](const pre &P, uint32_t it) {
             const uint32_t s = it % S, ph = (it / S) & 1u;
             const uint32_t abase = smem0 + s * G::STAGE_BYTES, bbase = abase + A_BYTES;
-            const uint4 co[2] = {o[0], o[1]}, cv[2] = {v[0], v[1]};
-            uint4 cb[BCH];
+            uint4 lb[BCH];
+            if (!PRE_B) {
 #pragma unroll
-            for (int j = 0; j < BCH; j++) cb[j] = nb[j];
-            const uint32_t ce0 = e0, ce1 = e1;
-            load_tile(it + 2); // the group's next tile is in flight while this one is rebuilt
-            mbar_wait(empty_bar(s), ph ^ 1u);
-            // zero the image of A's tile, copy B's slice into the swizzled MN-major operand layout
-#pragma unroll
-            for (int j = 0; j < A_BYTES / 16 / GROUP_THREADS; j++) sts128(abase + (gt + j * GROUP_THREADS) * 16u, make_uint4(0, 0, 0, 0));
+                for (int j = 0; j < BCH; j++) lb[j] = load_b(it, j);
+            }
+            mbar_wait_t(zeroed_bar(s), ph, w_zeroed); // the stage is free and A's image is all zero
+            const long long tp = clock64();
+            // B's slice into the swizzled MN-major operand layout
 #pragma unroll
             for (int j = 0; j < BCH; j++) {
                 const uint32_t x = gt + j * GROUP_THREADS;
-                if (x < (uint32_t)G::CHUNKS) {
+                if (x < (uint32_t)G::CHUNKS && !(a.skip & 8u)) {
                     const uint32_t k = x / (N / 8), c = x % (N / 8), grp = c / (G::ATOM_N / 8), cc = c % (G::ATOM_N / 8);
                     const uint32_t swz = ((k * G::RB) >> 7) & G::SWZ_MASK;
-                    sts128(bbase + grp * G::GROUP_BYTES + k * G::RB + ((cc ^ swz) << 4), cb[j]);
+                    sts128(bbase + grp * G::GROUP_BYTES + k * G::RB + ((cc ^ swz) << 4), PRE_B ? P.b[j] : lb[j]);
                 }
             }
-            bar_sync(1 + g, GROUP_THREADS);
             auto scatter = [&](const uint4 &oo, const uint4 &vv) {
                 const uint32_t ow[4] = {oo.x, oo.y, oo.z, oo.w}, vw[4] = {vv.x, vv.y, vv.z, vv.w};
 #pragma unroll
@@ -206,37 +241,75 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
             };
 #pragma unroll
             for (int p = 0; p < 2; p++)
-                if (ce0 + p * 2048u + gt * 8u < ce1) scatter(co[p], cv[p]);
-            for (uint32_t e = ce0 + 4096u + gt * 8u; e < ce1; e += 2048u) scatter(ld_stream_v4(a.off + e), ld_stream_v4(a.val + e)); // > 4096 pairs: dense tiles
-            fence_async_smem();
+                if (P.e0 + p * 2048u + gt * 8u < P.e1 && !(a.skip & 1u)) scatter(P.o[p], P.v[p]);
+            for (uint32_t e = P.e0 + 4096u + gt * 8u; e < P.e1; e += 2048u) scatter(ld_stream_v4(a.off + e), ld_stream_v4(a.val + e)); // > 4096 pairs: dense tiles
+            if (!(a.skip & 32u)) fence_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(full_bar(s));
+            w_store += clock64() - tp;
+            if (it == 0 && threadIdx.x == 0) stamp(a, 2);
+        };
+        pre P0, P1;
+        load_tile(P0, g);
+        for (uint32_t it = g; it < n_local; it += 4) {
+            load_tile(P1, it + 2); // the group's next tile is in flight while this one is stored
+            process(P0, it);
+            if (it + 2 >= n_local) break;
+            load_tile(P0, it + 4);
+            process(P1, it + 2);
         }
+        if (gt == 0) counter(a, 8 + 2 * g, w_zeroed), counter(a, 9 + 2 * g, w_store);
     } else if (warp == MMA_WARP) {
         // ------------------------------------------------------------------------------------------ MMA issue
         if (lane == 0) {
             uint32_t it = 0, seg = 0;
+            long long w_full = 0, w_acce = 0;
             while (it < n_local) {
                 const uint32_t kt0 = (t0 + it) % KT, len = min(KT - kt0, n_local - it), ab = seg & 1u;
-                mbar_wait(acce_bar(ab), ((seg >> 1) & 1u) ^ 1u);
+                mbar_wait_t(acce_bar(ab), ((seg >> 1) & 1u) ^ 1u, w_acce);
                 tc_fence_after();
                 const uint32_t d = tmem_base + ab * N;
                 for (uint32_t i = 0; i < len; i++, it++) {
                     const uint32_t s = it % S, ph = (it / S) & 1u;
-                    mbar_wait(full_bar(s), ph);
+                    mbar_wait_t(full_bar(s), ph, w_full);
                     tc_fence_after();
+                    if (it == 0) stamp(a, 3);
                     const uint32_t abase = smem0 + s * G::STAGE_BYTES, bbase = abase + A_BYTES;
 #pragma unroll
                     for (int k = 0; k < TK / 16; k++) {
                         const uint64_t ad = smem_desc(abase + k * 32, 16, 1024, 2u);
                         const uint64_t bd = smem_desc(bbase + k * G::K16_STEP, G::GROUP_BYTES, G::SBO, G::LAYOUT);
-                        tc_mma_f16(d, ad, bd, G::IDESC, (i > 0 || k > 0) ? 1u : 0u);
+                        if (!(a.skip & 4u)) tc_mma_f16(d, ad, bd, G::IDESC, (i > 0 || k > 0) ? 1u : 0u);
                     }
                     tc_commit(empty_bar(s));
                 }
                 tc_commit(accf_bar(ab));
                 seg++;
             }
+            stamp(a, 4);
+            counter(a, 12, w_full), counter(a, 13, w_acce);
+        }
+        __syncwarp();
+    } else if (warp == AHEAD_WARP) {
+        // ------------------------------------------------------------------------------------------ L2 prefetch + zero fill
+        if (lane == 0) {
+            auto pf = [&](uint32_t it) {
+                if (it >= n_local) return;
+                const uint32_t e0 = run_begin(it), bytes = (run_begin(it + 1) - e0) * 2u;
+                if (bytes) l2_prefetch_bulk(a.off + e0, bytes), l2_prefetch_bulk(a.val + e0, bytes);
+            };
+            for (uint32_t it = 0; it < PF_TILES; it++) pf(it);
+            long long w_empty = 0, w_zero = 0;
+            for (uint32_t it = 0; it < n_local; it++) {
+                const uint32_t s = it % S, ph = (it / S) & 1u;
+                pf(it + PF_TILES);
+                mbar_wait_t(empty_bar(s), ph ^ 1u, w_empty); // the tensor core has finished reading the stage
+                const long long tz = clock64();
+                if (!(a.skip & 2u)) smem_zero_bulk(smem0 + s * G::STAGE_BYTES, A_BYTES);
+                mbar_arrive(zeroed_bar(s));
+                w_zero += clock64() - tz;
+            }
+            counter(a, 14, w_empty), counter(a, 15, w_zero);
         }
         __syncwarp();
     } else {
@@ -251,6 +324,7 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
             const bool owner_wait = !partial_in && len < KT; // this CTA owns the panel and others hold its tail
             mbar_wait(accf_bar(ab), (seg >> 1) & 1u);
             tc_fence_after();
+            if (et == 0 && it + len >= n_local) stamp(a, 7);
             if (!waited) row::pdl_wait(), waited = true; // the first global store of this launch
             const uint32_t taddr = tmem_base + ((q * 32u) << 16) + ab * N;
             if (partial_in) {
@@ -306,9 +380,11 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
             if (lane == 0) mbar_arrive(acce_bar(ab));
             it += len, seg++;
         }
+        if (et == 0) stamp(a, 5);
     }
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) stamp(a, 6);
     if (warp == MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)G::TMEM_COLS) : "memory");
 }
 

@@ -23,7 +23,9 @@ struct b200_tile_plan {
     const void *fn = nullptr;
     int N = 0;
     char name[96] = {0};
+    unsigned long long *dbg = nullptr; // GS_TILE_DEBUG: DBG_RING launches x grid x 8 stamps x 2
 };
+constexpr int DBG_RING = 16;
 
 namespace {
 
@@ -129,8 +131,44 @@ cudaError_t b200_tile_prepare(const launch_params &p, int sm_count, b200_tile_pl
     if ((e = cudaFuncSetAttribute(pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem)) != cudaSuccess) return fail(e);
     snprintf(pl->name, sizeof pl->name, "k_b200_tile<N%d,f16,tcgen05 m128n%dk16,%d stages,streamK x%u%s,pdl>", p.N, p.N, p.N <= 64 ? 8 : p.N == 128 ? 6 : 4, pl->grid,
              env_int("GS_TILE_NO_BANK_ORDER", 0) ? "" : ",bank-ordered");
+    if (env_int("GS_TILE_DEBUG", 0)) {
+        if ((e = cudaMalloc((void **)&pl->dbg, (size_t)DBG_RING * pl->grid * 32 * 8)) != cudaSuccess) return fail(e);
+        cudaMemset(pl->dbg, 0, (size_t)DBG_RING * pl->grid * 32 * 8);
+    }
     *out = pl;
     return cudaSuccess;
+}
+
+// GS_TILE_DEBUG: per-CTA time stamps of the last DBG_RING launches, relative to the first CTA start of the oldest one
+static void dump_debug(b200_tile_plan *pl, cudaStream_t s)
+{
+    cudaStreamSynchronize(s);
+    std::vector<unsigned long long> h((size_t)DBG_RING * pl->grid * 32);
+    cudaMemcpy(h.data(), pl->dbg, h.size() * 8, cudaMemcpyDeviceToHost);
+    static const char *ev[16] = {"entry", "setup done", "first tile stored", "first full seen", "last mma issued", "epilogue done", "all joined", "last acc ready",
+                                 "g0 wait zeroed", "g0 store", "g1 wait zeroed", "g1 store", "mma wait full", "mma wait acc_empty", "ahead wait empty", "ahead zero+arrive"};
+    unsigned long long base = ~0ull;
+    for (int L = 0; L < DBG_RING; L++)
+        for (uint32_t c = 0; c < pl->grid; c++) {
+            unsigned long long g = h[(((size_t)L * pl->grid + c) * 16 + 0) * 2];
+            if (g && g < base) base = g;
+        }
+    for (int L = DBG_RING - 2; L < DBG_RING; L++) {
+        const uint32_t slot = (pl->seq - (DBG_RING - 1 - L)) % DBG_RING;
+        fprintf(stderr, "[tile debug] launch seq %u\n", pl->seq - (DBG_RING - 1 - L));
+        for (int e = 0; e < 16; e++) {
+            std::vector<double> t, ck;
+            for (uint32_t c = 0; c < pl->grid; c++) {
+                const size_t i = (((size_t)slot * pl->grid + c) * 16 + e) * 2, i0 = (((size_t)slot * pl->grid + c) * 16 + 0) * 2;
+                if (!h[i]) continue;
+                t.push_back(e < 8 ? (double)(h[i] - base) * 1e-3 : 0.0), ck.push_back(e < 8 ? (double)(h[i + 1] - h[i0 + 1]) : (double)h[i + 1]);
+            }
+            if (t.empty()) continue;
+            std::sort(t.begin(), t.end()), std::sort(ck.begin(), ck.end());
+            fprintf(stderr, "  %-18s globaltimer us min %9.2f med %9.2f max %9.2f | cycles since entry min %8.0f med %8.0f max %8.0f (n=%zu)\n", ev[e], t.front(), t[t.size() / 2],
+                    t.back(), ck.front(), ck[ck.size() / 2], ck.back(), t.size());
+        }
+    }
 }
 
 cudaError_t b200_tile_launch(b200_tile_plan *pl, const launch_params &p, cudaStream_t s)
@@ -139,6 +177,8 @@ cudaError_t b200_tile_launch(b200_tile_plan *pl, const launch_params &p, cudaStr
     a.tile_ptr = pl->tile_ptr, a.off = pl->off, a.val = pl->val, a.B = p.B, a.C = p.C, a.out_row = pl->out_row;
     a.ws = pl->ws, a.flags = pl->flags;
     a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.K = p.a.cols, a.seq = ++pl->seq, a.ptr_cap = pl->ptr_cap;
+    a.skip = (uint32_t)env_int("GS_TILE_SKIP", 0);
+    a.dbg = pl->dbg ? pl->dbg + (size_t)(pl->seq % DBG_RING) * pl->grid * 32 : nullptr;
     void *args[] = {&a};
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -147,13 +187,15 @@ cudaError_t b200_tile_launch(b200_tile_plan *pl, const launch_params &p, cudaStr
     memset(&cfg, 0, sizeof cfg);
     cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(tile::THREADS), cfg.dynamicSmemBytes = pl->smem, cfg.stream = s;
     cfg.attrs = attr, cfg.numAttrs = p.pdl ? 1 : 0;
-    return cudaLaunchKernelExC(&cfg, pl->fn, args);
+    cudaError_t e = cudaLaunchKernelExC(&cfg, pl->fn, args);
+    if (pl->dbg && pl->seq == 100) dump_debug(pl, s);
+    return e;
 }
 
 void b200_tile_free(b200_tile_plan *pl)
 {
     if (!pl) return;
-    cudaFree(pl->tile_ptr), cudaFree(pl->out_row), cudaFree(pl->flags), cudaFree(pl->off), cudaFree(pl->val), cudaFree(pl->ws);
+    cudaFree(pl->tile_ptr), cudaFree(pl->out_row), cudaFree(pl->flags), cudaFree(pl->off), cudaFree(pl->val), cudaFree(pl->ws), cudaFree(pl->dbg);
     delete pl;
 }
 
