@@ -6,23 +6,28 @@
 // 12 us and 23 us on 148 SMs against 8.4 us of HBM time.  A 30 %-dense 128 x 64 tile rebuilt in shared memory costs one
 // 2-byte store per non-zero whatever N is, and the contraction itself (2.9 GFLOP dense at N=32) is 2 us of tensor pipe.
 //
-// One persistent CTA per SM, 22 warps:
-//   warp 21     one lane runs ahead of everybody: bulk L2 prefetch of the pair runs 8 tiles ahead (UBLKPF), and, as
+// One CTA per SM and launch, 16 warps x 64 registers, sized so that TWO CTAs fit an SM: with programmatic dependent launch the next
+// launch's CTAs become resident beside this launch's and their prologue, pipeline fill and first tiles overlap this
+// launch's tail (the split-panel hand-off below), which a 37-tile CTA otherwise pays in full every launch.
+//   warp 11     one lane runs ahead of everybody: bulk L2 prefetch of the pair runs 8 tiles ahead (UBLKPF), and, as
 //               soon as the tensor core has released a stage, one st.bulk that zeroes the 16 KB image of A's tile
-//               (UMEMSETS), then an arrive on zeroed[stage];
-//   warps 0-15  two producer groups of 8 warps, alternating tiles: copy the 64 x N piece of B in the MN-major swizzled
-//               operand layout, scatter the tile's (offset, value) pairs with 2-byte stores into the K-major
-//               128-byte-swizzled image (128-bit loads of 8 offsets + 8 values per lane; two register sets, so the next
-//               tile's loads are in flight while this tile is stored), fence to the async proxy, arrive on
-//               full[stage]; no barrier between the warps of a group;
-//   warp 20     one elected lane issues 4 tcgen05.mma (M=128, N, K=16) per tile, commits to empty[stage], and to
+//               (UMEMSETS) + an arrive on zeroed[stage], and the TMA load of the 64 x N piece of B (row-major in
+//               global memory = the MN-major operand layout; the tensor map applies the 32/64/128-byte swizzle),
+//               completing on full[stage];
+//   warps 0-9   producers, every warp on every tile and independent of the others (no CTA barrier in the loop):
+//               scatter the warp's share of the tile's (offset, value) pairs with 2-byte stores into the K-major 128-byte-swizzled image (128-bit
+//               loads of 8 offsets + 8 values per lane; two register sets, so the loads of the next tile are in
+//               flight while this tile is stored), fence to the async proxy, arrive on full[stage];
+//   warp 10     one elected lane issues 4 tcgen05.mma (M=128, N, K=16) per tile, commits to empty[stage], and to
 //               acc_full[] at the end of a row panel; two accumulators in TMEM alternate between panels;
-//   warps 16-19 epilogue: tcgen05.ld the accumulator (lane = row), convert, store the rows of C.
+//   warps 12-15 epilogue: tcgen05.ld the accumulator (lane = row), convert, store the rows of C.
 // The tiles are dealt in equal contiguous runs to the CTAs (a run crosses row panels: stream-K).  A panel split over
 // several CTAs is summed by the CTA that holds its first tile, in k order, from fp32 partials the others leave in a
 // per-CTA workspace slot (release/acquire flag carrying the launch sequence number): no atomics, bit-reproducible.
 #pragma once
 #include "b200_stream.cuh"
+
+#include <cuda.h> // CUtensorMap (the type only: the encoder is reached through cudaGetDriverEntryPoint)
 
 namespace gsd {
 namespace tile {
@@ -31,7 +36,9 @@ using row::mbar_init;
 using row::smem_u32;
 
 constexpr int TM = 128, TK = 64, A_BYTES = TM * TK * 2;
-constexpr int GROUP_THREADS = 256, EPI_WARP0 = 16, MMA_WARP = 20, AHEAD_WARP = 21, THREADS = 22 * 32, PF_TILES = 8;
+constexpr int PRODUCER_WARPS = 10, PRODUCER_THREADS = PRODUCER_WARPS * 32, MMA_WARP = 10, AHEAD_WARP = 11, EPI_WARP0 = 12, THREADS = 16 * 32, PF_TILES = 8;
+constexpr int PASS_PAIRS = PRODUCER_THREADS * 8; // pairs one sweep of the producer warps stores: 2560, above a 30 %-dense tile (2458 +- 41)
+constexpr int DEPTH = 2;                         // register sets of pairs per producer lane: DEPTH - 1 tiles are in flight while one is stored
 
 struct tile_args {
     const uint32_t *tile_ptr; // n_tiles + 1
@@ -96,6 +103,13 @@ __device__ __forceinline__ void sts16(uint32_t addr, unsigned short v) { asm vol
 __device__ __forceinline__ void sts128(uint32_t addr, uint4 v) { asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); }
 __device__ __forceinline__ void smem_zero_bulk(uint32_t addr, uint32_t bytes) { asm volatile("st.bulk.weak.shared::cta [%0], %1, 0;" ::"r"(addr), "l"((uint64_t)bytes) : "memory"); }
 __device__ __forceinline__ void l2_prefetch_bulk(const void *p, uint32_t bytes) { asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory"); }
+// one box of the dense matrix (c0 = first dense column, c1 = first k row) into shared memory, swizzled by the tensor map
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t c0, uint32_t c1, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
+                 : "memory");
+}
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
 {
@@ -127,16 +141,19 @@ template <int N> struct b_geom {
     static constexpr int SBO = 8 * RB;                       // 8 k rows
     static constexpr int K16_STEP = 16 * RB;                 // bytes between the K=16 slices of one tile
     static constexpr int TMEM_COLS = 2 * N < 32 ? 32 : 2 * N;
+    // two CTAs per SM (two launches in flight) while 2 x (stages + TMEM columns) fit; N = 256 fills TMEM on its own
+    static constexpr int CTAS = N <= 128 ? 2 : 1;
+    static constexpr int STAGES = N <= 32 ? 5 : N == 64 ? 4 : N == 128 ? 3 : 4;
     // instruction descriptor (UMMA::InstrDescriptor): D fp32, A/B fp16, A K-major, B MN-major, N >> 3, M >> 4
     static constexpr uint32_t IDESC = (1u << 4) | (1u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 };
 
-template <int N> constexpr int tile_stages() { return N <= 64 ? 8 : N == 128 ? 6 : 4; }
+template <int N> constexpr int tile_stages() { return b_geom<N>::STAGES; }
 
-template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_args a)
+template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>::CTAS) k_b200_tile(tile_args a, const __grid_constant__ CUtensorMap b_map)
 {
     using G = b_geom<N>;
-    constexpr int S = tile_stages<N>();
+    constexpr int S = G::STAGES;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t bars[3 * S + 4];
     __shared__ uint32_t tmem_slot;
@@ -151,16 +168,13 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
     const uint32_t n_local = t1 - t0;
     const uint32_t KT = a.k_tiles;
 
-    if (threadIdx.x == 0) stamp(a, 0);
+    if (DBG && threadIdx.x == 0) stamp(a, 0);
     const uint32_t bar0 = smem_u32(bars);
-    auto full_bar = [&](uint32_t s) { return bar0 + 8u * s; };
-    auto empty_bar = [&](uint32_t s) { return bar0 + 8u * (S + s); };
-    auto zeroed_bar = [&](uint32_t s) { return bar0 + 8u * (2 * S + s); };
-    auto accf_bar = [&](uint32_t b) { return bar0 + 8u * (3 * S + b); };
-    auto acce_bar = [&](uint32_t b) { return bar0 + 8u * (3 * S + 2 + b); };
+    // full[s] = bar0 + 8 s, empty[s] = + 8 (S + s), zeroed[s] = + 8 (2 S + s), acc_full[b] = + 8 (3 S + b), acc_empty[b] = + 8 (3 S + 2 + b)
+    const uint32_t full0 = bar0, empty0 = bar0 + 8u * S, zeroed0 = bar0 + 16u * S, accf0 = bar0 + 24u * S, acce0 = accf0 + 16u;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < S; s++) mbar_init(&bars[s], 8), mbar_init(&bars[S + s], 1), mbar_init(&bars[2 * S + s], 1);
+        for (int s = 0; s < S; s++) mbar_init(&bars[s], PRODUCER_WARPS + 1), mbar_init(&bars[S + s], 1), mbar_init(&bars[2 * S + s], 1);
         mbar_init(&bars[3 * S], 1), mbar_init(&bars[3 * S + 1], 1);
         mbar_init(&bars[3 * S + 2], 4), mbar_init(&bars[3 * S + 3], 4);
     }
@@ -168,69 +182,36 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"((uint32_t)G::TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    const bool ptr_in_smem = n_local + 1 <= a.ptr_cap;
-    if (ptr_in_smem)
-        for (uint32_t i = threadIdx.x; i <= n_local; i += blockDim.x) s_ptr[i] = a.tile_ptr[t0 + i];
+    for (uint32_t i = threadIdx.x; i <= n_local; i += blockDim.x) s_ptr[i] = a.tile_ptr[t0 + i]; // the host made room for n_local + 1 entries
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
     row::pdl_launch_dependents();
-    if (threadIdx.x == 0) stamp(a, 1);
+    if (DBG && threadIdx.x == 0) stamp(a, 1);
 
-    auto run_begin = [&](uint32_t it) { return ptr_in_smem ? s_ptr[it] : a.tile_ptr[t0 + it]; };
+    auto run_begin = [&](uint32_t it) { return s_ptr[it]; };
+    const uint32_t skip = DBG ? a.skip : 0u;
 
-    if (warp < EPI_WARP0) {
+    if (warp < PRODUCER_WARPS) {
         // ------------------------------------------------------------------------------------------ producers
-        const uint32_t g = warp >> 3, gt = threadIdx.x & (GROUP_THREADS - 1);
-        const uint4 *Bg = (const uint4 *)a.B;
-        constexpr int BCH = (G::CHUNKS + GROUP_THREADS - 1) / GROUP_THREADS; // 16-byte pieces of B's slice per thread
-        constexpr bool PRE_B = BCH <= 2;                                     // B pieces travel with the pairs, one tile ahead
+        const uint32_t gt = threadIdx.x;
         long long w_zeroed = 0, w_store = 0;
         struct pre {
-            uint4 o[2], v[2], b[PRE_B ? BCH : 1];
-            uint32_t e0, e1;
-        };
-        // this thread's pieces of the 64 x N slice of B: piece x = k row x / (N/8), column chunk x % (N/8)
-        auto load_b = [&](uint32_t it, int j) {
-            const uint32_t k0 = ((t0 + it) % KT) * TK, x = gt + j * GROUP_THREADS, k = x / (N / 8);
-            uint4 r = make_uint4(0, 0, 0, 0);
-            if (x < (uint32_t)G::CHUNKS && k0 + k < a.K) r = __ldg(Bg + (size_t)(k0 + k) * (N / 8) + x % (N / 8));
-            return r;
+            uint4 o, v;
         };
         auto load_tile = [&](pre &P, uint32_t it) {
             if (it >= n_local) return;
-            P.e0 = run_begin(it), P.e1 = run_begin(it + 1);
-#pragma unroll
-            for (int p = 0; p < 2; p++) {
-                const uint32_t e = P.e0 + p * 2048u + gt * 8u;
-                if (e < P.e1 && !(a.skip & 16u)) P.o[p] = ld_stream_v4(a.off + e), P.v[p] = ld_stream_v4(a.val + e);
-            }
-            if (PRE_B) {
-#pragma unroll
-                for (int j = 0; j < BCH; j++) P.b[j] = load_b(it, j);
-            }
+            const uint32_t e = run_begin(it) + gt * 8u;
+            if (e < run_begin(it + 1) && !(skip & 16u)) P.o = ld_stream_v4(a.off + e), P.v = ld_stream_v4(a.val + e);
         };
+        uint32_t s = 0, ph = 0;
         auto process = [&](const pre &P, uint32_t it) {
-            const uint32_t s = it % S, ph = (it / S) & 1u;
-            const uint32_t abase = smem0 + s * G::STAGE_BYTES, bbase = abase + A_BYTES;
-            uint4 lb[BCH];
-            if (!PRE_B) {
-#pragma unroll
-                for (int j = 0; j < BCH; j++) lb[j] = load_b(it, j);
-            }
-            mbar_wait_t(zeroed_bar(s), ph, w_zeroed); // the stage is free and A's image is all zero
-            const long long tp = clock64();
-            // B's slice into the swizzled MN-major operand layout
-#pragma unroll
-            for (int j = 0; j < BCH; j++) {
-                const uint32_t x = gt + j * GROUP_THREADS;
-                if (x < (uint32_t)G::CHUNKS && !(a.skip & 8u)) {
-                    const uint32_t k = x / (N / 8), c = x % (N / 8), grp = c / (G::ATOM_N / 8), cc = c % (G::ATOM_N / 8);
-                    const uint32_t swz = ((k * G::RB) >> 7) & G::SWZ_MASK;
-                    sts128(bbase + grp * G::GROUP_BYTES + k * G::RB + ((cc ^ swz) << 4), PRE_B ? P.b[j] : lb[j]);
-                }
-            }
+            const uint32_t abase = smem0 + s * G::STAGE_BYTES;
+            const uint32_t e0 = run_begin(it), e1 = run_begin(it + 1);
+            long long tp = 0;
+            if (DBG) mbar_wait_t(zeroed0 + 8u * s, ph, w_zeroed), tp = clock64();
+            else mbar_wait(zeroed0 + 8u * s, ph); // the stage is free and A's image is all zero
             auto scatter = [&](const uint4 &oo, const uint4 &vv) {
                 const uint32_t ow[4] = {oo.x, oo.y, oo.z, oo.w}, vw[4] = {vv.x, vv.y, vv.z, vv.w};
 #pragma unroll
@@ -239,55 +220,58 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
                     sts16(abase + (ow[j] >> 16), (unsigned short)(vw[j] >> 16));
                 }
             };
-#pragma unroll
-            for (int p = 0; p < 2; p++)
-                if (P.e0 + p * 2048u + gt * 8u < P.e1 && !(a.skip & 1u)) scatter(P.o[p], P.v[p]);
-            for (uint32_t e = P.e0 + 4096u + gt * 8u; e < P.e1; e += 2048u) scatter(ld_stream_v4(a.off + e), ld_stream_v4(a.val + e)); // > 4096 pairs: dense tiles
-            if (!(a.skip & 32u)) fence_async_smem();
+            if (e0 + gt * 8u < e1 && !(skip & 1u)) scatter(P.o, P.v);
+            for (uint32_t e = e0 + PASS_PAIRS + gt * 8u; e < e1; e += PASS_PAIRS) scatter(ld_stream_v4(a.off + e), ld_stream_v4(a.val + e)); // tiles denser than 31 %
+            if (!(skip & 32u)) fence_async_smem();
             __syncwarp();
-            if (lane == 0) mbar_arrive(full_bar(s));
-            w_store += clock64() - tp;
-            if (it == 0 && threadIdx.x == 0) stamp(a, 2);
+            if (lane == 0) mbar_arrive(full0 + 8u * s);
+            if (DBG) {
+                w_store += clock64() - tp;
+                if (it == 0 && threadIdx.x == 0) stamp(a, 2);
+            }
+            if (++s == S) s = 0, ph ^= 1u;
         };
-        pre P0, P1;
-        load_tile(P0, g);
-        for (uint32_t it = g; it < n_local; it += 4) {
-            load_tile(P1, it + 2); // the group's next tile is in flight while this one is stored
-            process(P0, it);
-            if (it + 2 >= n_local) break;
-            load_tile(P0, it + 4);
-            process(P1, it + 2);
+        pre P[DEPTH];
+#pragma unroll
+        for (int d = 0; d < DEPTH; d++) load_tile(P[d], d);
+        for (uint32_t it = 0; it < n_local; it += DEPTH) {
+#pragma unroll
+            for (int d = 0; d < DEPTH; d++) {
+                if (it + d < n_local) {
+                    process(P[d], it + d);
+                    load_tile(P[d], it + d + DEPTH); // DEPTH - 1 tiles stay in flight
+                }
+            }
         }
-        if (gt == 0) counter(a, 8 + 2 * g, w_zeroed), counter(a, 9 + 2 * g, w_store);
+        if (DBG && gt == 0) counter(a, 8, w_zeroed), counter(a, 9, w_store);
     } else if (warp == MMA_WARP) {
         // ------------------------------------------------------------------------------------------ MMA issue
         if (lane == 0) {
-            uint32_t it = 0, seg = 0;
+            uint32_t it = 0, seg = 0, s = 0, ph = 0, kt0 = t0 % KT;
             long long w_full = 0, w_acce = 0;
+            const uint64_t adesc0 = smem_desc(smem0, 16, 1024, 2u), bdesc0 = smem_desc(smem0 + A_BYTES, G::GROUP_BYTES, G::SBO, G::LAYOUT);
             while (it < n_local) {
-                const uint32_t kt0 = (t0 + it) % KT, len = min(KT - kt0, n_local - it), ab = seg & 1u;
-                mbar_wait_t(acce_bar(ab), ((seg >> 1) & 1u) ^ 1u, w_acce);
+                const uint32_t len = min(KT - kt0, n_local - it), ab = seg & 1u;
+                if (DBG) mbar_wait_t(acce0 + 8u * ab, ((seg >> 1) & 1u) ^ 1u, w_acce);
+                else mbar_wait(acce0 + 8u * ab, ((seg >> 1) & 1u) ^ 1u);
                 tc_fence_after();
                 const uint32_t d = tmem_base + ab * N;
-                for (uint32_t i = 0; i < len; i++, it++) {
-                    const uint32_t s = it % S, ph = (it / S) & 1u;
-                    mbar_wait_t(full_bar(s), ph, w_full);
+                for (uint32_t i = 0; i < len; i++) {
+                    if (DBG) mbar_wait_t(full0 + 8u * s, ph, w_full);
+                    else mbar_wait(full0 + 8u * s, ph);
                     tc_fence_after();
-                    if (it == 0) stamp(a, 3);
-                    const uint32_t abase = smem0 + s * G::STAGE_BYTES, bbase = abase + A_BYTES;
+                    if (DBG && it + i == 0) stamp(a, 3);
+                    const uint64_t ad = adesc0 + (uint64_t)(s * (G::STAGE_BYTES >> 4)), bd = bdesc0 + (uint64_t)(s * (G::STAGE_BYTES >> 4));
 #pragma unroll
-                    for (int k = 0; k < TK / 16; k++) {
-                        const uint64_t ad = smem_desc(abase + k * 32, 16, 1024, 2u);
-                        const uint64_t bd = smem_desc(bbase + k * G::K16_STEP, G::GROUP_BYTES, G::SBO, G::LAYOUT);
-                        if (!(a.skip & 4u)) tc_mma_f16(d, ad, bd, G::IDESC, (i > 0 || k > 0) ? 1u : 0u);
-                    }
-                    tc_commit(empty_bar(s));
+                    for (int k = 0; k < TK / 16; k++)
+                        if (!(skip & 4u)) tc_mma_f16(d, ad + (uint64_t)(2 * k), bd + (uint64_t)(k * (G::K16_STEP >> 4)), G::IDESC, (i > 0 || k > 0) ? 1u : 0u);
+                    tc_commit(empty0 + 8u * s);
+                    if (++s == S) s = 0, ph ^= 1u;
                 }
-                tc_commit(accf_bar(ab));
-                seg++;
+                tc_commit(accf0 + 8u * ab);
+                it += len, seg++, kt0 = 0;
             }
-            stamp(a, 4);
-            counter(a, 12, w_full), counter(a, 13, w_acce);
+            if (DBG) stamp(a, 4), counter(a, 12, w_full), counter(a, 13, w_acce);
         }
         __syncwarp();
     } else if (warp == AHEAD_WARP) {
@@ -300,16 +284,24 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
             };
             for (uint32_t it = 0; it < PF_TILES; it++) pf(it);
             long long w_empty = 0, w_zero = 0;
+            uint32_t s = 0, ph = 0, kt = t0 % KT;
             for (uint32_t it = 0; it < n_local; it++) {
-                const uint32_t s = it % S, ph = (it / S) & 1u;
                 pf(it + PF_TILES);
-                mbar_wait_t(empty_bar(s), ph ^ 1u, w_empty); // the tensor core has finished reading the stage
-                const long long tz = clock64();
-                if (!(a.skip & 2u)) smem_zero_bulk(smem0 + s * G::STAGE_BYTES, A_BYTES);
-                mbar_arrive(zeroed_bar(s));
-                w_zero += clock64() - tz;
+                if (DBG) mbar_wait_t(empty0 + 8u * s, ph ^ 1u, w_empty);
+                else mbar_wait(empty0 + 8u * s, ph ^ 1u); // the tensor core has finished reading the stage
+                const long long tz = DBG ? clock64() : 0;
+                if (!(skip & 2u)) smem_zero_bulk(smem0 + s * G::STAGE_BYTES, A_BYTES);
+                mbar_arrive(zeroed0 + 8u * s);
+                // B's 64 x N slice: one box per 64-column atom; rows past K come back as zeros
+                mbar_expect_tx(full0 + 8u * s, (uint32_t)G::BYTES);
+#pragma unroll
+                for (int g = 0; g < G::GROUPS; g++)
+                    tma_load_2d(smem0 + s * G::STAGE_BYTES + A_BYTES + g * G::GROUP_BYTES, &b_map, (uint32_t)(g * G::ATOM_N), kt * TK, full0 + 8u * s);
+                if (++kt == KT) kt = 0;
+                if (DBG) w_zero += clock64() - tz;
+                if (++s == S) s = 0, ph ^= 1u;
             }
-            counter(a, 14, w_empty), counter(a, 15, w_zero);
+            if (DBG) counter(a, 14, w_empty), counter(a, 15, w_zero);
         }
         __syncwarp();
     } else {
@@ -320,11 +312,11 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
         uint32_t it = 0, seg = 0;
         while (it < n_local) {
             const uint32_t t = t0 + it, panel = t / KT, kt0 = t % KT, len = min(KT - kt0, n_local - it), ab = seg & 1u;
-            const bool partial_in = kt0 > 0;               // someone else owns the panel: leave a partial
+            const bool partial_in = kt0 > 0;                 // someone else owns the panel: leave a partial
             const bool owner_wait = !partial_in && len < KT; // this CTA owns the panel and others hold its tail
-            mbar_wait(accf_bar(ab), (seg >> 1) & 1u);
+            mbar_wait(accf0 + 8u * ab, (seg >> 1) & 1u);
             tc_fence_after();
-            if (et == 0 && it + len >= n_local) stamp(a, 7);
+            if (DBG && et == 0 && it + len >= n_local) stamp(a, 7);
             if (!waited) row::pdl_wait(), waited = true; // the first global store of this launch
             const uint32_t taddr = tmem_base + ((q * 32u) << 16) + ab * N;
             if (partial_in) {
@@ -345,7 +337,7 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
                     const uint64_t panel_end = (uint64_t)(panel + 1) * KT;
                     while (c_last + 1 < n_cta && (uint64_t)(c_last + 1) * a.n_tiles / n_cta < panel_end) c_last++;
                     for (uint32_t c2 = cta + 1; c2 <= c_last; c2++)
-                        while (ld_acquire(a.flags + c2) != a.seq) __nanosleep(64);
+                        while (ld_acquire(a.flags + c2) != a.seq) __nanosleep(32);
                 }
                 const uint32_t orow = a.out_row[(size_t)panel * TM + rip];
 #pragma unroll 1
@@ -377,14 +369,14 @@ template <int N> __global__ void __launch_bounds__(THREADS, 1) k_b200_tile(tile_
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(acce_bar(ab));
+            if (lane == 0) mbar_arrive(acce0 + 8u * ab);
             it += len, seg++;
         }
-        if (et == 0) stamp(a, 5);
+        if (DBG && et == 0) stamp(a, 5);
     }
     tc_fence_before();
     __syncthreads();
-    if (threadIdx.x == 0) stamp(a, 6);
+    if (DBG && threadIdx.x == 0) stamp(a, 6);
     if (warp == MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)G::TMEM_COLS) : "memory");
 }
 

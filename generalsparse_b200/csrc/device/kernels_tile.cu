@@ -23,16 +23,51 @@ struct b200_tile_plan {
     const void *fn = nullptr;
     int N = 0;
     char name[96] = {0};
+    CUtensorMap b_map;             // the dense matrix as TMA boxes of 64 k rows x one swizzle atom of columns
+    const void *b_mapped = nullptr; // the device pointer b_map was encoded for
+    uint32_t K = 0;
     unsigned long long *dbg = nullptr; // GS_TILE_DEBUG: DBG_RING launches x grid x 8 stamps x 2
 };
 constexpr int DBG_RING = 16;
 
 namespace {
 
-template <int N> void pick(const void *&fn, size_t &stage_bytes)
+template <int N> void pick(bool dbg, const void *&fn, size_t &stage_bytes, int &stages, int &ctas)
 {
-    fn = (const void *)tile::k_b200_tile<N>;
-    stage_bytes = (size_t)tile::tile_stages<N>() * tile::b_geom<N>::STAGE_BYTES;
+    fn = dbg ? (const void *)tile::k_b200_tile<N, true> : (const void *)tile::k_b200_tile<N, false>;
+    stages = tile::b_geom<N>::STAGES, ctas = tile::b_geom<N>::CTAS;
+    stage_bytes = (size_t)stages * tile::b_geom<N>::STAGE_BYTES;
+}
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                    CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through the runtime (libcuda is not linked: the library must load on a CPU-only box)
+encode_tiled_fn encoder()
+{
+    static encode_tiled_fn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        return (encode_tiled_fn)p;
+    }();
+    return fn;
+}
+
+// B is K x N fp16 row-major: dimension 0 = dense column (contiguous), dimension 1 = k
+cudaError_t encode_b_map(b200_tile_plan *pl, const void *B)
+{
+    encode_tiled_fn enc = encoder();
+    if (!enc) return cudaErrorNotSupported;
+    const int atom = pl->N < 64 ? pl->N : 64;
+    cuuint64_t dims[2] = {(cuuint64_t)pl->N, (cuuint64_t)pl->K}, strides[1] = {(cuuint64_t)pl->N * 2};
+    cuuint32_t box[2] = {(cuuint32_t)atom, (cuuint32_t)tile::TK}, estr[2] = {1, 1};
+    CUtensorMapSwizzle sw = atom == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : atom == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+    CUresult r = enc(&pl->b_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(B), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+    pl->b_mapped = B;
+    return cudaSuccess;
 }
 
 int env_int(const char *name, int dflt)
@@ -60,15 +95,18 @@ cudaError_t b200_tile_prepare(const launch_params &p, int sm_count, b200_tile_pl
         return e;
     };
     size_t stage_bytes = 0;
+    int stages = 0, ctas = 1;
+    const bool dbg = env_int("GS_TILE_DEBUG", 0) || env_int("GS_TILE_SKIP", 0);
     switch (p.N) {
-    case 16: pick<16>(pl->fn, stage_bytes); break;
-    case 32: pick<32>(pl->fn, stage_bytes); break;
-    case 64: pick<64>(pl->fn, stage_bytes); break;
-    case 128: pick<128>(pl->fn, stage_bytes); break;
-    case 256: pick<256>(pl->fn, stage_bytes); break;
+    case 16: pick<16>(dbg, pl->fn, stage_bytes, stages, ctas); break;
+    case 32: pick<32>(dbg, pl->fn, stage_bytes, stages, ctas); break;
+    case 64: pick<64>(dbg, pl->fn, stage_bytes, stages, ctas); break;
+    case 128: pick<128>(dbg, pl->fn, stage_bytes, stages, ctas); break;
+    case 256: pick<256>(dbg, pl->fn, stage_bytes, stages, ctas); break;
     default: return fail(cudaErrorInvalidValue); // M=128 tcgen05.mma wants N % 16 == 0; N=8 stays on the stream kernel
     }
-    pl->N = p.N;
+    pl->N = p.N, pl->K = p.a.cols;
+    if (!encoder()) return fail(cudaErrorNotSupported);
 
     // the chain's arrays back to the host, once
     std::vector<uint32_t> rp(n_rows + 1), rid(n_rows), perm, colw(p.a.nnz);
@@ -94,7 +132,7 @@ cudaError_t b200_tile_prepare(const launch_params &p, int sm_count, b200_tile_pl
 
     gs::tile_stream ts;
     try {
-        gs::build_tile_stream(rp.data(), colw.data(), val.data(), n_rows, p.a.cols, !env_int("GS_TILE_NO_BANK_ORDER", 0), ts);
+        gs::build_tile_stream(rp.data(), colw.data(), val.data(), n_rows, p.a.cols, env_int("GS_TILE_NO_BANK_ORDER", 0) ? 0u : (uint32_t)tile::PRODUCER_WARPS, ts);
     } catch (...) {
         return fail(cudaErrorInvalidValue);
     }
@@ -110,10 +148,10 @@ cudaError_t b200_tile_prepare(const launch_params &p, int sm_count, b200_tile_pl
         orow[i] = (p.a.perm ? perm[r] : r) + p.a.begin_row;
     }
 
-    const uint32_t per_cta = (pl->n_tiles + pl->grid - 1) / pl->grid + 1;
-    pl->ptr_cap = std::min<uint32_t>(per_cta + 1, 4096u); // the CTA's slice of tile_ptr sits behind the stages in shared memory
+    // the CTA's slice of tile_ptr sits behind the stages in shared memory
+    pl->ptr_cap = (pl->n_tiles + pl->grid - 1) / pl->grid + 2;
     pl->smem = stage_bytes + 1024 + (size_t)pl->ptr_cap * 4;
-    if (pl->smem > 227 * 1024) pl->ptr_cap = 0, pl->smem = stage_bytes + 1024;
+    if (pl->smem > (size_t)(227 * 1024) / ctas - 2048) return fail(cudaErrorInvalidValue); // > ~2000 tiles per CTA: not a weight-sized matrix
 
     auto up = [&](void **dst, const void *src, size_t bytes) {
         cudaError_t e2 = cudaMalloc(dst, bytes + 16);
@@ -129,7 +167,11 @@ cudaError_t b200_tile_prepare(const launch_params &p, int sm_count, b200_tile_pl
     if ((e = cudaMemsetAsync(pl->flags, 0, (size_t)pl->grid * 4, s)) != cudaSuccess) return fail(e);
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(e);
     if ((e = cudaFuncSetAttribute(pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem)) != cudaSuccess) return fail(e);
-    snprintf(pl->name, sizeof pl->name, "k_b200_tile<N%d,f16,tcgen05 m128n%dk16,%d stages,streamK x%u%s,pdl>", p.N, p.N, p.N <= 64 ? 8 : p.N == 128 ? 6 : 4, pl->grid,
+    if ((e = cudaFuncSetAttribute(pl->fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess) return fail(e);
+    int occ = 0;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pl->fn, tile::THREADS, pl->smem)) != cudaSuccess) return fail(e);
+    if (occ < 1) return fail(cudaErrorInvalidConfiguration);
+    snprintf(pl->name, sizeof pl->name, "k_b200_tile<N%d,f16,tcgen05 m128n%dk16,%d stages,streamK x%u,%d CTA/SM%s,pdl>", p.N, p.N, stages, pl->grid, occ,
              env_int("GS_TILE_NO_BANK_ORDER", 0) ? "" : ",bank-ordered");
     if (env_int("GS_TILE_DEBUG", 0)) {
         if ((e = cudaMalloc((void **)&pl->dbg, (size_t)DBG_RING * pl->grid * 32 * 8)) != cudaSuccess) return fail(e);
@@ -146,7 +188,7 @@ static void dump_debug(b200_tile_plan *pl, cudaStream_t s)
     std::vector<unsigned long long> h((size_t)DBG_RING * pl->grid * 32);
     cudaMemcpy(h.data(), pl->dbg, h.size() * 8, cudaMemcpyDeviceToHost);
     static const char *ev[16] = {"entry", "setup done", "first tile stored", "first full seen", "last mma issued", "epilogue done", "all joined", "last acc ready",
-                                 "g0 wait zeroed", "g0 store", "g1 wait zeroed", "g1 store", "mma wait full", "mma wait acc_empty", "ahead wait empty", "ahead zero+arrive"};
+                                 "producer wait zeroed", "producer store", "-", "-", "mma wait full", "mma wait acc_empty", "ahead wait empty", "ahead zero+arrive"};
     unsigned long long base = ~0ull;
     for (int L = 0; L < DBG_RING; L++)
         for (uint32_t c = 0; c < pl->grid; c++) {
@@ -179,7 +221,11 @@ cudaError_t b200_tile_launch(b200_tile_plan *pl, const launch_params &p, cudaStr
     a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.K = p.a.cols, a.seq = ++pl->seq, a.ptr_cap = pl->ptr_cap;
     a.skip = (uint32_t)env_int("GS_TILE_SKIP", 0);
     a.dbg = pl->dbg ? pl->dbg + (size_t)(pl->seq % DBG_RING) * pl->grid * 32 : nullptr;
-    void *args[] = {&a};
+    if (pl->b_mapped != p.B) {
+        cudaError_t em = encode_b_map(pl, p.B);
+        if (em != cudaSuccess) return em;
+    }
+    void *args[] = {&a, &pl->b_map};
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;

@@ -17,16 +17,17 @@ struct pair16 {
 // Greedy: every store takes one pair from each of the fullest banks; only when fewer banks than lanes are left does a
 // bank give two.  The sum over the stores of the worst bank multiplicity ends within a few percent of
 // max(stores, fullest bank), the lower bound.
-void order_run(std::vector<pair16> &run)
+void order_run(std::vector<pair16> &run, uint32_t pass_warps)
 {
+    const uint32_t pass_pairs = pass_warps * 256u;
     const uint32_t n = (uint32_t)run.size(); // multiple of 8
     std::vector<pair16> bank[32];
     for (const pair16 &p : run) bank[(p.off >> 2) & 31].push_back(p);
     std::vector<pair16> out(n);
     int order[32];
-    for (uint32_t pass = 0; pass * 2048u < n; pass++) {
-        for (uint32_t w = 0; w < 8; w++) {
-            const uint32_t base = pass * 2048u + w * 256u;
+    for (uint32_t pass = 0; pass * pass_pairs < n; pass++) {
+        for (uint32_t w = 0; w < pass_warps; w++) {
+            const uint32_t base = pass * pass_pairs + w * 256u;
             if (base >= n) break;
             for (uint32_t j = 0; j < 8; j++) {
                 uint32_t lanes = std::min<uint32_t>(32u, (n - base) / 8u); // lanes whose 8-pair group exists
@@ -52,7 +53,7 @@ void order_run(std::vector<pair16> &run)
 
 } // namespace
 
-void build_tile_stream(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val, uint32_t n_rows, uint32_t n_cols, bool bank_order, tile_stream &ts)
+void build_tile_stream(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val, uint32_t n_rows, uint32_t n_cols, uint32_t pass_warps, tile_stream &ts)
 {
     ts = tile_stream();
     ts.n_rows = n_rows, ts.n_cols = n_cols;
@@ -94,7 +95,7 @@ void build_tile_stream(const uint32_t *rowptr, const uint32_t *col, const uint16
     for (uint64_t t = 0; t < T; t++) {
         const uint32_t b = ts.tile_ptr[t], e = ts.tile_ptr[t + 1], n = cnt[t];
         if (n == 0) continue;
-        if (!bank_order) {
+        if (!pass_warps) {
             for (uint32_t i = b + n; i < e; i++) ts.off[i] = ts.off[b + n - 1], ts.val[i] = ts.val[b + n - 1];
             continue;
         }
@@ -114,7 +115,7 @@ void build_tile_stream(const uint32_t *rowptr, const uint32_t *col, const uint16
                 }
             hist[best]++;
         }
-        order_run(run);
+        order_run(run, pass_warps);
         for (uint32_t i = 0; i < e - b; i++) ts.off[b + i] = run[i].off, ts.val[b + i] = run[i].val;
     }
 }

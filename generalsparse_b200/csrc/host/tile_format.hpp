@@ -29,9 +29,10 @@ struct tile_stream {
 inline uint32_t tile_offset(uint32_t r, uint32_t c) { return r * 128u + ((((c >> 3) ^ (r & 7u)) & 7u) << 4) + (c & 7u) * 2u; }
 
 // rowptr: n_rows + 1 offsets into col / val_f16 (row i of the row level = row i of the tiled matrix).
-// bank_order: order every run so that the 32 pairs one warp stores together (pair j of lanes 0..31, 8 pairs per lane,
-// 2048 pairs per pass of 256 threads) fall into distinct shared-memory banks where the tile's contents allow it.
-void build_tile_stream(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val_f16, uint32_t n_rows, uint32_t n_cols, bool bank_order, tile_stream &out);
+// pass_warps > 0: order every run so that the 32 pairs one warp stores together (pair j of lanes 0..31, 8 pairs per
+// lane, pass_warps * 256 pairs per sweep of the producer warps) fall into distinct shared-memory banks where the
+// tile's contents allow it; 0: row-major order inside a run.
+void build_tile_stream(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val_f16, uint32_t n_rows, uint32_t n_cols, uint32_t pass_warps, tile_stream &out);
 
 // inverse, for tests: dense row-major n_rows x n_cols fp16 bits (zeros where nothing is stored)
 void expand_tile_stream(const tile_stream &ts, std::vector<uint16_t> &dense);
