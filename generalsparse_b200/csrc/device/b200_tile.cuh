@@ -49,6 +49,7 @@ struct tile_args {
     float *ws;               // grid x 128 x N fp32 partial panels
     uint32_t *flags;         // grid
     uint32_t n_tiles, k_tiles, K, seq, ptr_cap;
+    uint32_t consumer_fence; // 1: the generic->async proxy fence runs on the mma lane after its acquire of full[], not in every producer lane
     uint32_t skip; // GS_TILE_SKIP (timing experiments, wrong results): 1 no scatter, 2 no zero fill, 4 no mma, 8 no B copy, 16 no pair loads, 32 no fence
     unsigned long long *dbg; // GS_TILE_DEBUG: 8 (globaltimer, clock64) stamps per CTA, or null
 };
@@ -80,6 +81,15 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
                  "r"(parity)
                  : "memory");
 }
+// a wait that is expected to last long (the epilogue warps sit out the whole tile loop): every retry of try_wait is an
+// operation in the same memory-instruction queue the producers' stores go through, so poll rarely; the hardware
+// still wakes the thread when the phase completes inside the suspend window
+__device__ __forceinline__ void mbar_wait_idle(uint32_t bar, uint32_t parity)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(bar),
+                 "r"(parity), "r"(100000u)
+                 : "memory");
+}
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -96,6 +106,13 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&r)[16])
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]),
                    "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_ld8(uint32_t taddr, uint32_t (&r)[8])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "r"(taddr));
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
@@ -136,7 +153,7 @@ template <int N> struct b_geom {
     static constexpr int GROUPS = N / ATOM_N;                // atoms along N
     static constexpr int GROUP_BYTES = TK * RB;              // one atom column: 64 k rows
     static constexpr int BYTES = GROUPS * GROUP_BYTES;       // = 64 * N * 2
-    static constexpr int STAGE_BYTES = A_BYTES + (BYTES < 1024 ? 1024 : BYTES);
+    static constexpr int B_SLOT = BYTES < 1024 ? 1024 : BYTES;
     static constexpr int CHUNKS = BYTES / 16;
     static constexpr int SBO = 8 * RB;                       // 8 k rows
     static constexpr int K16_STEP = 16 * RB;                 // bytes between the K=16 slices of one tile
@@ -144,6 +161,10 @@ template <int N> struct b_geom {
     // two CTAs per SM (two launches in flight) while 2 x (stages + TMEM columns) fit; N = 256 fills TMEM on its own
     static constexpr int CTAS = N <= 128 ? 2 : 1;
     static constexpr int STAGES = N <= 32 ? 5 : N == 64 ? 4 : N == 128 ? 3 : 4;
+    // B has its own, deeper ring: its TMA load (an L2 round trip) is issued B_SLOTS - STAGES tiles before A's stage is
+    // even free, so that it is off the loop  stage free -> zero -> scatter -> mma -> stage free  that sets the tile rate
+    static constexpr int B_SLOTS = N == 16 ? 10 : N == 32 ? 7 : N == 64 ? 5 : N == 128 ? 3 : 4;
+    static constexpr int RING_BYTES = STAGES * A_BYTES + B_SLOTS * B_SLOT;
     // instruction descriptor (UMMA::InstrDescriptor): D fp32, A/B fp16, A K-major, B MN-major, N >> 3, M >> 4
     static constexpr uint32_t IDESC = (1u << 4) | (1u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 };
@@ -153,14 +174,15 @@ template <int N> constexpr int tile_stages() { return b_geom<N>::STAGES; }
 template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>::CTAS) k_b200_tile(tile_args a, const __grid_constant__ CUtensorMap b_map)
 {
     using G = b_geom<N>;
-    constexpr int S = G::STAGES;
+    constexpr int S = G::STAGES, SB = G::B_SLOTS;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t bars[3 * S + 4];
+    __shared__ __align__(8) uint64_t bars[3 * S + 4 + SB];
     __shared__ uint32_t tmem_slot;
     // 1024-byte alignment of the stage buffers (128-byte swizzle atoms)
     const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
     unsigned char *smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
-    uint32_t *s_ptr = (uint32_t *)(smem_al + (size_t)S * G::STAGE_BYTES); // the CTA's slice of tile_ptr
+    uint32_t *s_ptr = (uint32_t *)(smem_al + (size_t)G::RING_BYTES); // the CTA's slice of tile_ptr
+    const uint32_t bring0 = smem0 + S * A_BYTES;                  // B's ring behind A's stages
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t n_cta = gridDim.x, cta = blockIdx.x;
@@ -171,10 +193,11 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
     if (DBG && threadIdx.x == 0) stamp(a, 0);
     const uint32_t bar0 = smem_u32(bars);
     // full[s] = bar0 + 8 s, empty[s] = + 8 (S + s), zeroed[s] = + 8 (2 S + s), acc_full[b] = + 8 (3 S + b), acc_empty[b] = + 8 (3 S + 2 + b)
-    const uint32_t full0 = bar0, empty0 = bar0 + 8u * S, zeroed0 = bar0 + 16u * S, accf0 = bar0 + 24u * S, acce0 = accf0 + 16u;
+    const uint32_t full0 = bar0, empty0 = bar0 + 8u * S, zeroed0 = bar0 + 16u * S, accf0 = bar0 + 24u * S, acce0 = accf0 + 16u, bfull0 = accf0 + 32u;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < S; s++) mbar_init(&bars[s], PRODUCER_WARPS + 1), mbar_init(&bars[S + s], 1), mbar_init(&bars[2 * S + s], 1);
+        for (int s = 0; s < S; s++) mbar_init(&bars[s], PRODUCER_WARPS), mbar_init(&bars[S + s], 1), mbar_init(&bars[2 * S + s], 1);
+        for (int b = 0; b < SB; b++) mbar_init(&bars[3 * S + 4 + b], 1);
         mbar_init(&bars[3 * S], 1), mbar_init(&bars[3 * S + 1], 1);
         mbar_init(&bars[3 * S + 2], 4), mbar_init(&bars[3 * S + 3], 4);
     }
@@ -196,7 +219,7 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
     if (warp < PRODUCER_WARPS) {
         // ------------------------------------------------------------------------------------------ producers
         const uint32_t gt = threadIdx.x;
-        long long w_zeroed = 0, w_store = 0;
+        long long w_zeroed = 0, w_store = 0, w_ld = 0, w_sts = 0, w_fence = 0;
         struct pre {
             uint4 o, v;
         };
@@ -207,7 +230,7 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
         };
         uint32_t s = 0, ph = 0;
         auto process = [&](const pre &P, uint32_t it) {
-            const uint32_t abase = smem0 + s * G::STAGE_BYTES;
+            const uint32_t abase = smem0 + s * A_BYTES;
             const uint32_t e0 = run_begin(it), e1 = run_begin(it + 1);
             long long tp = 0;
             if (DBG) mbar_wait_t(zeroed0 + 8u * s, ph, w_zeroed), tp = clock64();
@@ -220,12 +243,23 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
                     sts16(abase + (ow[j] >> 16), (unsigned short)(vw[j] >> 16));
                 }
             };
+            long long t1 = 0, t2 = 0, t3 = 0;
+            if (DBG) {
+                if (e0 + gt * 8u < e1) { // force the wait for the loaded pairs here, so that it is timed on its own
+                    uint32_t dep = P.o.x ^ P.v.x ^ P.o.w ^ P.v.w;
+                    asm volatile("" ::"r"(dep));
+                }
+                t1 = clock64();
+            }
             if (e0 + gt * 8u < e1 && !(skip & 1u)) scatter(P.o, P.v);
             for (uint32_t e = e0 + PASS_PAIRS + gt * 8u; e < e1; e += PASS_PAIRS) scatter(ld_stream_v4(a.off + e), ld_stream_v4(a.val + e)); // tiles denser than 31 %
-            if (!(skip & 32u)) fence_async_smem();
+            if (DBG) t2 = clock64();
+            if (!(skip & 32u) && !a.consumer_fence) fence_async_smem();
+            if (DBG) t3 = clock64();
             __syncwarp();
             if (lane == 0) mbar_arrive(full0 + 8u * s);
             if (DBG) {
+                w_ld += t1 - tp, w_sts += t2 - t1, w_fence += t3 - t2;
                 w_store += clock64() - tp;
                 if (it == 0 && threadIdx.x == 0) stamp(a, 2);
             }
@@ -243,13 +277,13 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
                 }
             }
         }
-        if (DBG && gt == 0) counter(a, 8, w_zeroed), counter(a, 9, w_store);
+        if (DBG && gt == 0) counter(a, 8, w_zeroed), counter(a, 9, w_store), counter(a, 10, w_ld), counter(a, 11, w_sts), counter(a, 5, w_fence);
     } else if (warp == MMA_WARP) {
         // ------------------------------------------------------------------------------------------ MMA issue
         if (lane == 0) {
-            uint32_t it = 0, seg = 0, s = 0, ph = 0, kt0 = t0 % KT;
+            uint32_t it = 0, seg = 0, s = 0, ph = 0, sb = 0, phb = 0, kt0 = t0 % KT;
             long long w_full = 0, w_acce = 0;
-            const uint64_t adesc0 = smem_desc(smem0, 16, 1024, 2u), bdesc0 = smem_desc(smem0 + A_BYTES, G::GROUP_BYTES, G::SBO, G::LAYOUT);
+            const uint64_t adesc0 = smem_desc(smem0, 16, 1024, 2u), bdesc0 = smem_desc(bring0, G::GROUP_BYTES, G::SBO, G::LAYOUT);
             while (it < n_local) {
                 const uint32_t len = min(KT - kt0, n_local - it), ab = seg & 1u;
                 if (DBG) mbar_wait_t(acce0 + 8u * ab, ((seg >> 1) & 1u) ^ 1u, w_acce);
@@ -257,16 +291,20 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
                 tc_fence_after();
                 const uint32_t d = tmem_base + ab * N;
                 for (uint32_t i = 0; i < len; i++) {
+                    if (DBG) mbar_wait_t(bfull0 + 8u * sb, phb, w_acce);
+                    else mbar_wait(bfull0 + 8u * sb, phb); // B's slice has landed (issued several tiles ago)
                     if (DBG) mbar_wait_t(full0 + 8u * s, ph, w_full);
                     else mbar_wait(full0 + 8u * s, ph);
+                    if (a.consumer_fence) fence_async_smem(); // the producers' stores, acquired through full[], made visible to the tensor core's proxy
                     tc_fence_after();
                     if (DBG && it + i == 0) stamp(a, 3);
-                    const uint64_t ad = adesc0 + (uint64_t)(s * (G::STAGE_BYTES >> 4)), bd = bdesc0 + (uint64_t)(s * (G::STAGE_BYTES >> 4));
+                    const uint64_t ad = adesc0 + (uint64_t)(s * (A_BYTES >> 4)), bd = bdesc0 + (uint64_t)(sb * (G::B_SLOT >> 4));
 #pragma unroll
                     for (int k = 0; k < TK / 16; k++)
                         if (!(skip & 4u)) tc_mma_f16(d, ad + (uint64_t)(2 * k), bd + (uint64_t)(k * (G::K16_STEP >> 4)), G::IDESC, (i > 0 || k > 0) ? 1u : 0u);
                     tc_commit(empty0 + 8u * s);
                     if (++s == S) s = 0, ph ^= 1u;
+                    if (++sb == SB) sb = 0, phb ^= 1u;
                 }
                 tc_commit(accf0 + 8u * ab);
                 it += len, seg++, kt0 = 0;
@@ -284,20 +322,27 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
             };
             for (uint32_t it = 0; it < PF_TILES; it++) pf(it);
             long long w_empty = 0, w_zero = 0;
-            uint32_t s = 0, ph = 0, kt = t0 % KT;
+            uint32_t s = 0, ph = 0, kt = t0 % KT, jb = 0, sb = 0;
+            // B's 64 x N slice of tile jb into slot jb % SB: one box per 64-column atom; rows past K come back as zeros
+            auto load_b = [&]() {
+                if (jb < n_local) {
+                    mbar_expect_tx(bfull0 + 8u * sb, (uint32_t)G::BYTES);
+#pragma unroll
+                    for (int g = 0; g < G::GROUPS; g++) tma_load_2d(bring0 + sb * G::B_SLOT + g * G::GROUP_BYTES, &b_map, (uint32_t)(g * G::ATOM_N), kt * TK, bfull0 + 8u * sb);
+                }
+                jb++;
+                if (++kt == KT) kt = 0;
+                if (++sb == SB) sb = 0;
+            };
+            for (int i = 0; i < SB - S; i++) load_b(); // the slots no tile has used yet
             for (uint32_t it = 0; it < n_local; it++) {
                 pf(it + PF_TILES);
                 if (DBG) mbar_wait_t(empty0 + 8u * s, ph ^ 1u, w_empty);
                 else mbar_wait(empty0 + 8u * s, ph ^ 1u); // the tensor core has finished reading the stage
                 const long long tz = DBG ? clock64() : 0;
-                if (!(skip & 2u)) smem_zero_bulk(smem0 + s * G::STAGE_BYTES, A_BYTES);
+                if (!(skip & 2u)) smem_zero_bulk(smem0 + s * A_BYTES, A_BYTES);
                 mbar_arrive(zeroed0 + 8u * s);
-                // B's 64 x N slice: one box per 64-column atom; rows past K come back as zeros
-                mbar_expect_tx(full0 + 8u * s, (uint32_t)G::BYTES);
-#pragma unroll
-                for (int g = 0; g < G::GROUPS; g++)
-                    tma_load_2d(smem0 + s * G::STAGE_BYTES + A_BYTES + g * G::GROUP_BYTES, &b_map, (uint32_t)(g * G::ATOM_N), kt * TK, full0 + 8u * s);
-                if (++kt == KT) kt = 0;
+                load_b(); // tile it + SB - S: its slot was last read by the mma of tile it - S, which has completed
                 if (DBG) w_zero += clock64() - tz;
                 if (++s == S) s = 0, ph ^= 1u;
             }
@@ -314,7 +359,7 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
             const uint32_t t = t0 + it, panel = t / KT, kt0 = t % KT, len = min(KT - kt0, n_local - it), ab = seg & 1u;
             const bool partial_in = kt0 > 0;                 // someone else owns the panel: leave a partial
             const bool owner_wait = !partial_in && len < KT; // this CTA owns the panel and others hold its tail
-            mbar_wait(accf0 + 8u * ab, (seg >> 1) & 1u);
+            mbar_wait_idle(accf0 + 8u * ab, (seg >> 1) & 1u);
             tc_fence_after();
             if (DBG && et == 0 && it + len >= n_local) stamp(a, 7);
             if (!waited) row::pdl_wait(), waited = true; // the first global store of this launch
@@ -322,11 +367,11 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
             if (partial_in) {
                 float *slot = a.ws + ((size_t)cta * TM + rip) * N;
 #pragma unroll 1
-                for (int c = 0; c < N / 16; c++) {
-                    uint32_t r[16];
-                    tc_ld16(taddr + c * 16, r);
-#pragma unroll
-                    for (int j = 0; j < 4; j++) __stcg((uint4 *)(slot + c * 16) + j, make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]));
+                for (int c = 0; c < N / 8; c++) {
+                    uint32_t r[8];
+                    tc_ld8(taddr + c * 8, r);
+                    __stcg((uint4 *)(slot + c * 8), make_uint4(r[0], r[1], r[2], r[3]));
+                    __stcg((uint4 *)(slot + c * 8) + 1, make_uint4(r[4], r[5], r[6], r[7]));
                 }
                 __threadfence();
                 bar_sync(3, 128);
@@ -341,29 +386,25 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
                 }
                 const uint32_t orow = a.out_row[(size_t)panel * TM + rip];
 #pragma unroll 1
-                for (int c = 0; c < N / 16; c++) {
-                    uint32_t r[16];
-                    tc_ld16(taddr + c * 16, r);
-                    float f[16];
-#pragma unroll
-                    for (int j = 0; j < 16; j++) f[j] = __uint_as_float(r[j]);
+                for (int c = 0; c < N / 8; c++) {
+                    uint32_t r[8];
+                    tc_ld8(taddr + c * 8, r);
                     for (uint32_t c2 = cta + 1; c2 <= c_last; c2++) {
-                        const float4 *slot = (const float4 *)(a.ws + ((size_t)c2 * TM + rip) * N + c * 16);
-#pragma unroll
-                        for (int j = 0; j < 4; j++) {
-                            const float4 x = __ldcg(slot + j);
-                            f[4 * j] += x.x, f[4 * j + 1] += x.y, f[4 * j + 2] += x.z, f[4 * j + 3] += x.w;
-                        }
+                        const float4 *slot = (const float4 *)(a.ws + ((size_t)c2 * TM + rip) * N + c * 8);
+                        const float4 x = __ldcg(slot), y = __ldcg(slot + 1);
+                        r[0] = __float_as_uint(__uint_as_float(r[0]) + x.x), r[1] = __float_as_uint(__uint_as_float(r[1]) + x.y);
+                        r[2] = __float_as_uint(__uint_as_float(r[2]) + x.z), r[3] = __float_as_uint(__uint_as_float(r[3]) + x.w);
+                        r[4] = __float_as_uint(__uint_as_float(r[4]) + y.x), r[5] = __float_as_uint(__uint_as_float(r[5]) + y.y);
+                        r[6] = __float_as_uint(__uint_as_float(r[6]) + y.z), r[7] = __float_as_uint(__uint_as_float(r[7]) + y.w);
                     }
                     if (orow != 0xffffffffu) {
-                        uint32_t h[8];
+                        uint32_t h[4];
 #pragma unroll
-                        for (int j = 0; j < 8; j++) {
-                            __half2 p = __floats2half2_rn(f[2 * j], f[2 * j + 1]);
+                        for (int j = 0; j < 4; j++) {
+                            __half2 p = __floats2half2_rn(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
                             h[j] = *(uint32_t *)&p;
                         }
-                        uint4 *dst = (uint4 *)(C + (size_t)orow * N + c * 16);
-                        dst[0] = make_uint4(h[0], h[1], h[2], h[3]), dst[1] = make_uint4(h[4], h[5], h[6], h[7]);
+                        *(uint4 *)(C + (size_t)orow * N + c * 8) = make_uint4(h[0], h[1], h[2], h[3]);
                     }
                 }
             }
@@ -372,7 +413,6 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
             if (lane == 0) mbar_arrive(acce0 + 8u * ab);
             it += len, seg++;
         }
-        if (DBG && et == 0) stamp(a, 5);
     }
     tc_fence_before();
     __syncthreads();

@@ -36,7 +36,7 @@ template <int N> void pick(bool dbg, const void *&fn, size_t &stage_bytes, int &
 {
     fn = dbg ? (const void *)tile::k_b200_tile<N, true> : (const void *)tile::k_b200_tile<N, false>;
     stages = tile::b_geom<N>::STAGES, ctas = tile::b_geom<N>::CTAS;
-    stage_bytes = (size_t)stages * tile::b_geom<N>::STAGE_BYTES;
+    stage_bytes = (size_t)tile::b_geom<N>::RING_BYTES;
 }
 
 typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
@@ -187,8 +187,8 @@ static void dump_debug(b200_tile_plan *pl, cudaStream_t s)
     cudaStreamSynchronize(s);
     std::vector<unsigned long long> h((size_t)DBG_RING * pl->grid * 32);
     cudaMemcpy(h.data(), pl->dbg, h.size() * 8, cudaMemcpyDeviceToHost);
-    static const char *ev[16] = {"entry", "setup done", "first tile stored", "first full seen", "last mma issued", "epilogue done", "all joined", "last acc ready",
-                                 "producer wait zeroed", "producer store", "-", "-", "mma wait full", "mma wait acc_empty", "ahead wait empty", "ahead zero+arrive"};
+    static const char *ev[16] = {"entry", "setup done", "first tile stored", "first full seen", "last mma issued", "producer fence (counter)", "all joined", "last acc ready",
+                                 "producer wait zeroed", "producer store", "producer wait loads", "producer sts", "mma wait full", "mma wait acc_empty+bfull", "ahead wait empty", "ahead zero+arrive"};
     unsigned long long base = ~0ull;
     for (int L = 0; L < DBG_RING; L++)
         for (uint32_t c = 0; c < pl->grid; c++) {
@@ -203,7 +203,7 @@ static void dump_debug(b200_tile_plan *pl, cudaStream_t s)
             for (uint32_t c = 0; c < pl->grid; c++) {
                 const size_t i = (((size_t)slot * pl->grid + c) * 16 + e) * 2, i0 = (((size_t)slot * pl->grid + c) * 16 + 0) * 2;
                 if (!h[i]) continue;
-                t.push_back(e < 8 ? (double)(h[i] - base) * 1e-3 : 0.0), ck.push_back(e < 8 ? (double)(h[i + 1] - h[i0 + 1]) : (double)h[i + 1]);
+                t.push_back(e < 8 && e != 5 ? (double)(h[i] - base) * 1e-3 : 0.0), ck.push_back(e < 8 && e != 5 ? (double)(h[i + 1] - h[i0 + 1]) : (double)h[i + 1]);
             }
             if (t.empty()) continue;
             std::sort(t.begin(), t.end()), std::sort(ck.begin(), ck.end());
@@ -220,6 +220,7 @@ cudaError_t b200_tile_launch(b200_tile_plan *pl, const launch_params &p, cudaStr
     a.ws = pl->ws, a.flags = pl->flags;
     a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.K = p.a.cols, a.seq = ++pl->seq, a.ptr_cap = pl->ptr_cap;
     a.skip = (uint32_t)env_int("GS_TILE_SKIP", 0);
+    a.consumer_fence = (uint32_t)env_int("GS_TILE_CONSUMER_FENCE", 0);
     a.dbg = pl->dbg ? pl->dbg + (size_t)(pl->seq % DBG_RING) * pl->grid * 32 : nullptr;
     if (pl->b_mapped != p.B) {
         cudaError_t em = encode_b_map(pl, p.B);
