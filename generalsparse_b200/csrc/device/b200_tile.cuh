@@ -24,6 +24,11 @@
 // The tiles are dealt in equal contiguous runs to the CTAs (a run crosses row panels: stream-K).  A panel split over
 // several CTAs is summed by the CTA that holds its first tile, in k order, from fp32 partials the others leave in a
 // per-CTA workspace slot (release/acquire flag carrying the launch sequence number): no atomics, bit-reproducible.
+// Launches of one plan overlap on the SMs, so nothing here waits for the previous grid as a whole
+// (griddepcontrol.wait would gate every launch on the slowest CTA of the one before); the two hazards between
+// launches are ordered point to point with the same kind of flag: a panel's rows of C are written by launch L only
+// after launch L-1 has written them (panel_seq), and a workspace slot is refilled by launch L only after launch L-1's
+// owner has consumed it (slot_free).
 #pragma once
 #include "b200_stream.cuh"
 
@@ -47,8 +52,11 @@ struct tile_args {
     void *C;
     const uint32_t *out_row; // n_panels * 128 output rows of C, 0xffffffff = no row
     float *ws;               // grid x 128 x N fp32 partial panels
-    uint32_t *flags;         // grid
+    uint32_t *flags;         // grid: launch number whose partial sits in the CTA's slot
+    uint32_t *slot_free;     // grid: launch number whose partial has been consumed from the CTA's slot
+    uint32_t *panel_seq;     // n_panels: launch number that last wrote the panel's rows of C
     uint32_t n_tiles, k_tiles, K, seq, ptr_cap;
+    uint32_t bulk_zero;      // 1: zero A's image with one st.bulk instead of the warp's STS.128
     uint32_t consumer_fence; // 1: the generic->async proxy fence runs on the mma lane after its acquire of full[], not in every producer lane
     uint32_t skip; // GS_TILE_SKIP (timing experiments, wrong results): 1 no scatter, 2 no zero fill, 4 no mma, 8 no B copy, 16 no pair loads, 32 no fence
     unsigned long long *dbg; // GS_TILE_DEBUG: 8 (globaltimer, clock64) stamps per CTA, or null
@@ -63,6 +71,11 @@ __device__ __forceinline__ void stamp(const tile_args &a, int ev)
     }
 }
 
+// per-tile trace of CTA 0: clock64 of role event `ev` (0 stage zeroed, 1 warp 0 stored, 2 warp 9 stored, 3 mma sees full, 4 mma issued) at tile `it`
+__device__ __forceinline__ void trace(const tile_args &a, int ev, uint32_t it)
+{
+    if (a.dbg && blockIdx.x == 0 && it < 40) a.dbg[(size_t)gridDim.x * 32 + ev * 40 + it] = (unsigned long long)clock64();
+}
 __device__ __forceinline__ void counter(const tile_args &a, int ev, long long v)
 {
     if (a.dbg) a.dbg[((size_t)blockIdx.x * 16 + ev) * 2] = 1, a.dbg[((size_t)blockIdx.x * 16 + ev) * 2 + 1] = (unsigned long long)v;
@@ -258,6 +271,7 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
             if (DBG) t3 = clock64();
             __syncwarp();
             if (lane == 0) mbar_arrive(full0 + 8u * s);
+            if (DBG && lane == 0 && (warp == 0 || warp == PRODUCER_WARPS - 1)) trace(a, warp == 0 ? 1 : 2, it);
             if (DBG) {
                 w_ld += t1 - tp, w_sts += t2 - t1, w_fence += t3 - t2;
                 w_store += clock64() - tp;
@@ -298,11 +312,13 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
                     if (a.consumer_fence) fence_async_smem(); // the producers' stores, acquired through full[], made visible to the tensor core's proxy
                     tc_fence_after();
                     if (DBG && it + i == 0) stamp(a, 3);
+                    if (DBG) trace(a, 3, it + i);
                     const uint64_t ad = adesc0 + (uint64_t)(s * (A_BYTES >> 4)), bd = bdesc0 + (uint64_t)(sb * (G::B_SLOT >> 4));
 #pragma unroll
                     for (int k = 0; k < TK / 16; k++)
                         if (!(skip & 4u)) tc_mma_f16(d, ad + (uint64_t)(2 * k), bd + (uint64_t)(k * (G::K16_STEP >> 4)), G::IDESC, (i > 0 || k > 0) ? 1u : 0u);
                     tc_commit(empty0 + 8u * s);
+                    if (DBG) trace(a, 4, it + i);
                     if (++s == S) s = 0, ph ^= 1u;
                     if (++sb == SB) sb = 0, phb ^= 1u;
                 }
@@ -313,56 +329,77 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
         }
         __syncwarp();
     } else if (warp == AHEAD_WARP) {
-        // ------------------------------------------------------------------------------------------ L2 prefetch + zero fill
-        if (lane == 0) {
-            auto pf = [&](uint32_t it) {
-                if (it >= n_local) return;
-                const uint32_t e0 = run_begin(it), bytes = (run_begin(it + 1) - e0) * 2u;
-                if (bytes) l2_prefetch_bulk(a.off + e0, bytes), l2_prefetch_bulk(a.val + e0, bytes);
-            };
-            for (uint32_t it = 0; it < PF_TILES; it++) pf(it);
-            long long w_empty = 0, w_zero = 0;
-            uint32_t s = 0, ph = 0, kt = t0 % KT, jb = 0, sb = 0;
-            // B's 64 x N slice of tile jb into slot jb % SB: one box per 64-column atom; rows past K come back as zeros
-            auto load_b = [&]() {
-                if (jb < n_local) {
-                    mbar_expect_tx(bfull0 + 8u * sb, (uint32_t)G::BYTES);
+        // ------------------------------------------------------------------------------------------ L2 prefetch, zero fill, B loads
+        // Zero fill with 32 x STS.128 per lane-row of the warp: measured 128 cycles per 16 KB (the full 128 B/clk), against
+        // ~250 for one st.bulk (UMEMSETS), during which the producers' scatter stores queue behind it (scratch/ubench/smem.cu).
+        auto pf = [&](uint32_t it) {
+            if (it >= n_local) return;
+            const uint32_t e0 = run_begin(it), bytes = (run_begin(it + 1) - e0) * 2u;
+            if (bytes) l2_prefetch_bulk(a.off + e0, bytes), l2_prefetch_bulk(a.val + e0, bytes);
+        };
+        long long w_empty = 0, w_zero = 0;
+        uint32_t s = 0, ph = 0, kt = t0 % KT, jb = 0, sb = 0;
+        // B's 64 x N slice of tile jb into slot jb % SB: one box per 64-column atom; rows past K come back as zeros
+        auto load_b = [&]() {
+            if (jb < n_local && lane == 0) {
+                mbar_expect_tx(bfull0 + 8u * sb, (uint32_t)G::BYTES);
 #pragma unroll
-                    for (int g = 0; g < G::GROUPS; g++) tma_load_2d(bring0 + sb * G::B_SLOT + g * G::GROUP_BYTES, &b_map, (uint32_t)(g * G::ATOM_N), kt * TK, bfull0 + 8u * sb);
-                }
-                jb++;
-                if (++kt == KT) kt = 0;
-                if (++sb == SB) sb = 0;
-            };
-            for (int i = 0; i < SB - S; i++) load_b(); // the slots no tile has used yet
-            for (uint32_t it = 0; it < n_local; it++) {
-                pf(it + PF_TILES);
-                if (DBG) mbar_wait_t(empty0 + 8u * s, ph ^ 1u, w_empty);
-                else mbar_wait(empty0 + 8u * s, ph ^ 1u); // the tensor core has finished reading the stage
-                const long long tz = DBG ? clock64() : 0;
-                if (!(skip & 2u)) smem_zero_bulk(smem0 + s * A_BYTES, A_BYTES);
-                mbar_arrive(zeroed0 + 8u * s);
-                load_b(); // tile it + SB - S: its slot was last read by the mma of tile it - S, which has completed
-                if (DBG) w_zero += clock64() - tz;
-                if (++s == S) s = 0, ph ^= 1u;
+                for (int g = 0; g < G::GROUPS; g++) tma_load_2d(bring0 + sb * G::B_SLOT + g * G::GROUP_BYTES, &b_map, (uint32_t)(g * G::ATOM_N), kt * TK, bfull0 + 8u * sb);
             }
-            if (DBG) counter(a, 14, w_empty), counter(a, 15, w_zero);
+            jb++;
+            if (++kt == KT) kt = 0;
+            if (++sb == SB) sb = 0;
+        };
+        if (lane == 0)
+            for (uint32_t it = 0; it < PF_TILES; it++) pf(it);
+        for (int i = 0; i < SB - S; i++) load_b(); // the slots no tile has used yet
+        for (uint32_t it = 0; it < n_local; it++) {
+            if (lane == 0) pf(it + PF_TILES);
+            if (DBG) mbar_wait_t(empty0 + 8u * s, ph ^ 1u, w_empty);
+            else mbar_wait(empty0 + 8u * s, ph ^ 1u); // the tensor core has finished reading the stage
+            const long long tz = DBG ? clock64() : 0;
+            if (!(skip & 2u)) {
+                if (a.bulk_zero) {
+                    if (lane == 0) smem_zero_bulk(smem0 + s * A_BYTES, A_BYTES);
+                } else {
+                    const uint32_t zb = smem0 + s * A_BYTES + lane * 16u;
+#pragma unroll
+                    for (int j = 0; j < A_BYTES / 512; j++) sts128(zb + j * 512, make_uint4(0, 0, 0, 0));
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(zeroed0 + 8u * s);
+            if (DBG && lane == 0) trace(a, 0, it);
+            load_b(); // tile it + SB - S: its slot was last read by the mma of tile it - S, which has completed
+            if (DBG) w_zero += clock64() - tz;
+            if (++s == S) s = 0, ph ^= 1u;
         }
-        __syncwarp();
+        if (DBG && lane == 0) counter(a, 14, w_empty), counter(a, 15, w_zero);
     } else {
         // ------------------------------------------------------------------------------------------ epilogue
         const uint32_t q = warp - EPI_WARP0, rip = q * 32 + lane, et = threadIdx.x - EPI_WARP0 * 32;
         __half *C = (__half *)a.C;
-        bool waited = false;
         uint32_t it = 0, seg = 0;
+        auto wait_for = [&](const uint32_t *flag, uint32_t v) { // one lane polls, the warp follows
+            if (lane == 0)
+                while (ld_acquire(flag) != v) __nanosleep(32);
+            __syncwarp();
+        };
         while (it < n_local) {
             const uint32_t t = t0 + it, panel = t / KT, kt0 = t % KT, len = min(KT - kt0, n_local - it), ab = seg & 1u;
             const bool partial_in = kt0 > 0;                 // someone else owns the panel: leave a partial
             const bool owner_wait = !partial_in && len < KT; // this CTA owns the panel and others hold its tail
+            // what does not depend on the accumulator goes first, while the tile loop is still running: the hand-shakes
+            // with the previous launch and the output row of this thread
+            uint32_t orow = 0xffffffffu;
+            if (partial_in) wait_for(a.slot_free + cta, a.seq - 1); // the previous launch's owner has read this CTA's slot
+            else {
+                wait_for(a.panel_seq + panel, a.seq - 1); // the previous launch has written these rows of C
+                orow = a.out_row[(size_t)panel * TM + rip];
+            }
             mbar_wait_idle(accf0 + 8u * ab, (seg >> 1) & 1u);
             tc_fence_after();
             if (DBG && et == 0 && it + len >= n_local) stamp(a, 7);
-            if (!waited) row::pdl_wait(), waited = true; // the first global store of this launch
             const uint32_t taddr = tmem_base + ((q * 32u) << 16) + ab * N;
             if (partial_in) {
                 float *slot = a.ws + ((size_t)cta * TM + rip) * N;
@@ -381,10 +418,8 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
                 if (owner_wait) {
                     const uint64_t panel_end = (uint64_t)(panel + 1) * KT;
                     while (c_last + 1 < n_cta && (uint64_t)(c_last + 1) * a.n_tiles / n_cta < panel_end) c_last++;
-                    for (uint32_t c2 = cta + 1; c2 <= c_last; c2++)
-                        while (ld_acquire(a.flags + c2) != a.seq) __nanosleep(32);
+                    for (uint32_t c2 = cta + 1; c2 <= c_last; c2++) wait_for(a.flags + c2, a.seq);
                 }
-                const uint32_t orow = a.out_row[(size_t)panel * TM + rip];
 #pragma unroll 1
                 for (int c = 0; c < N / 8; c++) {
                     uint32_t r[8];
@@ -406,6 +441,12 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
                         }
                         *(uint4 *)(C + (size_t)orow * N + c * 8) = make_uint4(h[0], h[1], h[2], h[3]);
                     }
+                }
+                __threadfence();
+                bar_sync(3, 128);
+                if (et == 0) {
+                    st_release(a.panel_seq + panel, a.seq);
+                    for (uint32_t c2 = cta + 1; c2 <= c_last; c2++) st_release(a.slot_free + c2, a.seq);
                 }
             }
             tc_fence_before();

@@ -14,7 +14,7 @@
 namespace gsd {
 
 struct b200_tile_plan {
-    uint32_t *tile_ptr = nullptr, *out_row = nullptr, *flags = nullptr;
+    uint32_t *tile_ptr = nullptr, *out_row = nullptr, *flags = nullptr; // flags: grid ready + grid slot_free + n_panels panel_seq
     uint16_t *off = nullptr, *val = nullptr;
     float *ws = nullptr;
     uint32_t n_tiles = 0, k_tiles = 0, n_panels = 0, grid = 0, ptr_cap = 0, seq = 0;
@@ -163,8 +163,9 @@ cudaError_t b200_tile_prepare(const launch_params &p, int sm_count, b200_tile_pl
     if ((e = up((void **)&pl->val, ts.val.data(), ts.val.size() * 2)) != cudaSuccess) return fail(e);
     if ((e = up((void **)&pl->out_row, orow.data(), orow.size() * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMalloc((void **)&pl->ws, (size_t)pl->grid * tile::TM * p.N * 4)) != cudaSuccess) return fail(e);
-    if ((e = cudaMalloc((void **)&pl->flags, (size_t)pl->grid * 4)) != cudaSuccess) return fail(e);
-    if ((e = cudaMemsetAsync(pl->flags, 0, (size_t)pl->grid * 4, s)) != cudaSuccess) return fail(e);
+    const size_t n_flags = (size_t)pl->grid * 2 + pl->n_panels;
+    if ((e = cudaMalloc((void **)&pl->flags, n_flags * 4)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemsetAsync(pl->flags, 0, n_flags * 4, s)) != cudaSuccess) return fail(e);
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(e);
     if ((e = cudaFuncSetAttribute(pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem)) != cudaSuccess) return fail(e);
     if ((e = cudaFuncSetAttribute(pl->fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess) return fail(e);
@@ -174,8 +175,8 @@ cudaError_t b200_tile_prepare(const launch_params &p, int sm_count, b200_tile_pl
     snprintf(pl->name, sizeof pl->name, "k_b200_tile<N%d,f16,tcgen05 m128n%dk16,%d stages,streamK x%u,%d CTA/SM%s,pdl>", p.N, p.N, stages, pl->grid, occ,
              env_int("GS_TILE_NO_BANK_ORDER", 0) ? "" : ",bank-ordered");
     if (env_int("GS_TILE_DEBUG", 0)) {
-        if ((e = cudaMalloc((void **)&pl->dbg, (size_t)DBG_RING * pl->grid * 32 * 8)) != cudaSuccess) return fail(e);
-        cudaMemset(pl->dbg, 0, (size_t)DBG_RING * pl->grid * 32 * 8);
+        if ((e = cudaMalloc((void **)&pl->dbg, (size_t)DBG_RING * (pl->grid * 32 + 256) * 8)) != cudaSuccess) return fail(e);
+        cudaMemset(pl->dbg, 0, (size_t)DBG_RING * (pl->grid * 32 + 256) * 8);
     }
     *out = pl;
     return cudaSuccess;
@@ -185,14 +186,15 @@ cudaError_t b200_tile_prepare(const launch_params &p, int sm_count, b200_tile_pl
 static void dump_debug(b200_tile_plan *pl, cudaStream_t s)
 {
     cudaStreamSynchronize(s);
-    std::vector<unsigned long long> h((size_t)DBG_RING * pl->grid * 32);
+    const size_t per = (size_t)pl->grid * 32 + 256;
+    std::vector<unsigned long long> h((size_t)DBG_RING * per);
     cudaMemcpy(h.data(), pl->dbg, h.size() * 8, cudaMemcpyDeviceToHost);
     static const char *ev[16] = {"entry", "setup done", "first tile stored", "first full seen", "last mma issued", "producer fence (counter)", "all joined", "last acc ready",
                                  "producer wait zeroed", "producer store", "producer wait loads", "producer sts", "mma wait full", "mma wait acc_empty+bfull", "ahead wait empty", "ahead zero+arrive"};
     unsigned long long base = ~0ull;
     for (int L = 0; L < DBG_RING; L++)
         for (uint32_t c = 0; c < pl->grid; c++) {
-            unsigned long long g = h[(((size_t)L * pl->grid + c) * 16 + 0) * 2];
+            unsigned long long g = h[(size_t)L * per + ((size_t)c * 16 + 0) * 2];
             if (g && g < base) base = g;
         }
     for (int L = DBG_RING - 2; L < DBG_RING; L++) {
@@ -201,12 +203,20 @@ static void dump_debug(b200_tile_plan *pl, cudaStream_t s)
         for (int e = 0; e < 16; e++) {
             std::vector<double> t, ck;
             for (uint32_t c = 0; c < pl->grid; c++) {
-                const size_t i = (((size_t)slot * pl->grid + c) * 16 + e) * 2, i0 = (((size_t)slot * pl->grid + c) * 16 + 0) * 2;
+                const size_t i = (size_t)slot * per + ((size_t)c * 16 + e) * 2, i0 = (size_t)slot * per + ((size_t)c * 16 + 0) * 2;
                 if (!h[i]) continue;
                 t.push_back(e < 8 && e != 5 ? (double)(h[i] - base) * 1e-3 : 0.0), ck.push_back(e < 8 && e != 5 ? (double)(h[i + 1] - h[i0 + 1]) : (double)h[i + 1]);
             }
             if (t.empty()) continue;
             std::sort(t.begin(), t.end()), std::sort(ck.begin(), ck.end());
+            if (e == 0 && L == DBG_RING - 1) {
+                const unsigned long long *tr = &h[(size_t)slot * per + (size_t)pl->grid * 32];
+                const unsigned long long c0 = h[(size_t)slot * per + 1]; // CTA 0 entry clock
+                fprintf(stderr, "  CTA 0 per-tile trace (cycles since entry): tile | zeroed | warp0 stored | warp9 stored | mma sees full | mma issued\n");
+                for (int it = 0; it < 37; it++)
+                    fprintf(stderr, "    %2d %8lld %8lld %8lld %8lld %8lld\n", it, (long long)(tr[it] - c0), (long long)(tr[40 + it] - c0), (long long)(tr[80 + it] - c0), (long long)(tr[120 + it] - c0),
+                            (long long)(tr[160 + it] - c0));
+            }
             fprintf(stderr, "  %-18s globaltimer us min %9.2f med %9.2f max %9.2f | cycles since entry min %8.0f med %8.0f max %8.0f (n=%zu)\n", ev[e], t.front(), t[t.size() / 2],
                     t.back(), ck.front(), ck[ck.size() / 2], ck.back(), t.size());
         }
@@ -217,11 +227,12 @@ cudaError_t b200_tile_launch(b200_tile_plan *pl, const launch_params &p, cudaStr
 {
     tile::tile_args a;
     a.tile_ptr = pl->tile_ptr, a.off = pl->off, a.val = pl->val, a.B = p.B, a.C = p.C, a.out_row = pl->out_row;
-    a.ws = pl->ws, a.flags = pl->flags;
+    a.ws = pl->ws, a.flags = pl->flags, a.slot_free = pl->flags + pl->grid, a.panel_seq = pl->flags + 2 * (size_t)pl->grid;
     a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.K = p.a.cols, a.seq = ++pl->seq, a.ptr_cap = pl->ptr_cap;
     a.skip = (uint32_t)env_int("GS_TILE_SKIP", 0);
-    a.consumer_fence = (uint32_t)env_int("GS_TILE_CONSUMER_FENCE", 0);
-    a.dbg = pl->dbg ? pl->dbg + (size_t)(pl->seq % DBG_RING) * pl->grid * 32 : nullptr;
+    a.consumer_fence = (uint32_t)env_int("GS_TILE_CONSUMER_FENCE", 1);
+    a.bulk_zero = (uint32_t)env_int("GS_TILE_BULK_ZERO", 0);
+    a.dbg = pl->dbg ? pl->dbg + (size_t)(pl->seq % DBG_RING) * ((size_t)pl->grid * 32 + 256) : nullptr;
     if (pl->b_mapped != p.B) {
         cudaError_t em = encode_b_map(pl, p.B);
         if (em != cudaSuccess) return em;

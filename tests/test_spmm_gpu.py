@@ -212,3 +212,31 @@ def test_b200_tile_kernel(engine, N, chain):
         # repeated launches (programmatic dependent launch, workspace and flag reuse) give the same bits
         plan.run(5)
         assert np.array_equal(plan.output(), C)
+
+
+def test_b200_tile_overlapped_launches_keep_order(engine):
+    """back-to-back launches of one plan overlap on the SMs (programmatic dependent launch, two CTAs per SM): C must end
+    up as the LAST launch's product although the dense matrix alternates between launches"""
+    import torch
+    from generalsparse_b200 import api, synth
+    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
+    rows, cols, N = 3000, 4096, 32
+    r, c = _matrix("uniform", rows, cols, seed=61, density=0.2)
+    vals = synth.synth_values(len(r), seed=61).astype(np.float16).astype(np.float32)
+    ms = api.MetaDataSet.from_coo(rows, cols, r, c, vals)
+    s = api.Session(ms).run_family("thread_total", N, 8, 1)
+    engine.upload_session(s, half=True)
+    plan = engine.plan(s, N, half=True, kernel="b200_tcgen05")
+    Bs = [synth.synth_dense(cols, N, seed=70 + i).astype(np.float16) for i in range(2)]
+    dev = [torch.from_numpy(b).cuda() for b in Bs]
+    torch.cuda.synchronize()
+    indptr = csr_from_coo(rows, r)
+    refs = [oracle_spmm_f64acc(rows, N, indptr, c, vals, b.astype(np.float32)) for b in Bs]
+    absrow = [oracle_spmm_absrow(rows, N, indptr, c, vals, b.astype(np.float32)) for b in Bs]
+    for n_launch in (1, 2, 7, 40, 41):
+        for i in range(n_launch):
+            plan.set_dense_device(dev[i % 2].data_ptr())
+            plan.launch()
+        last = (n_launch - 1) % 2
+        C = plan.output()
+        _check(C, refs[last], absrow[last] * 1e-2, 1e-2, abs_floor=2.0 ** -25)
