@@ -4,7 +4,8 @@
 Workload (BASELINE.json configs[1]): synthetic pruned Llama-2-7B FFN weight 11008 x 4096, 70 %
 unstructured sparsity, HALF storage with fp32 accumulation, N dense columns (default 8; --n 16/32).
 A step = one SpMM C = A*B through the reference's thread_total operator chain (sort_operator ->
-row blocking with sparse-coarsen-8 padding -> thread_total_reduce) executed by the B200 row kernel.
+row blocking with sparse-coarsen-8 padding -> thread_total_reduce) executed by the B200 row kernel (N=8) or the
+B200 tile kernel (sparse tile decompress to shared memory + tcgen05, N >= 16).
 Successive steps use successive device copies of A (R copies, R*bytes(A) > L2) so every launch
 streams A from HBM.
 
@@ -41,7 +42,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--n", type=int, default=8, help="dense width N (8, 16 or 32)")
-    ap.add_argument("--kernel", default="b200_row_smem")
+    ap.add_argument("--kernel", default="auto", help="auto: the stream row kernel at N=8, the tcgen05 tile kernel from N=16 up")
     ap.add_argument("--copies", type=int, default=0, help="device copies of A to rotate over (0 = enough to exceed L2 3x)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -155,6 +156,8 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     N, half = args.n, True
+    if args.kernel == "auto":
+        args.kernel = "b200_row_smem" if N < 16 else "b200_tcgen05"
     hbm_peak, peak_src = peaks()
 
     # ---- the global matrix: `world` FFN-sized blocks stacked; this rank's nnz-balanced row block ------------------------
@@ -288,7 +291,7 @@ def main():
         "metric": "SpMM GFLOP/s (2*nnz*N/t)", "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 storage, f32 accumulate",
         "data": "synthetic",
-        "config": {"workload": "pruned Llama-2-7B FFN weight 11008x4096 per GPU, 70%% unstructured, N=%d, HALF, thread_total chain (sort, S=8 pad) on the B200 row kernel" % N,
+        "config": {"workload": "pruned Llama-2-7B FFN weight 11008x4096 per GPU, 70%% unstructured, N=%d, HALF, thread_total chain (sort, S=8 pad) on the B200 %s kernel" % (N, "row" if args.kernel == "b200_row_smem" else "tile (tcgen05)"),
                    "rows_per_gpu": int(desc.rows), "cols": COLS, "nnz_per_gpu": int(desc.origin_nnz), "stored_nnz_per_gpu": int(desc.stored_nnz),
                    "kernel": plans[0].kernel_name, "l2": "steps rotate over %d device copies of A (%.0f MB > 126 MB L2)" % (copies, copies * bytes_a / 1e6),
                    "partition": "nnz-balanced row blocks (balanced_interval rule), B replicated, C rows disjoint, no collective",

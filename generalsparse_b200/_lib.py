@@ -17,6 +17,7 @@ SYMBOLS = [
     "gsh_metadata_check", "gsh_config_load", "gsh_config_set", "gsh_config_get",
     "gsh_session_create", "gsh_session_free", "gsh_session_add_and_run", "gsh_session_record_count", "gsh_session_record",
     "gsh_session_run_family", "gsh_session_compile", "gsh_session_plan_desc", "gsh_partition_rows_balanced",
+    "gsh_tile_stream_roundtrip",
     "gs_create", "gs_destroy", "gs_stream", "gs_upload_array", "gs_upload_session", "gs_upload_session_as", "gs_plan_create", "gs_plan_destroy",
     "gs_plan_set_kernel", "gs_set_dense", "gs_set_dense_device", "gs_launch", "gs_run", "gs_get_output", "gs_output_device",
     "gs_spmm_host", "gs_spmm_host_async", "gs_synchronize", "gs_plan_algorithmic_bytes", "gs_plan_launch_count", "gs_plan_kernel_name", "gs_execute",
@@ -74,6 +75,7 @@ def lib():
         "gsh_session_record": (i32, [vp, u64, cp, sz]), "gsh_session_run_family": (i32, [vp, i32, i32, i32, i32]),
         "gsh_session_compile": (i32, [vp]), "gsh_session_plan_desc": (i32, [vp, P(PlanDesc)]),
         "gsh_partition_rows_balanced": (i32, [vp, u64, i32, vp]),
+        "gsh_tile_stream_roundtrip": (i32, [vp, vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),
         "gs_create": (i32, [P(vp), i32]), "gs_destroy": (None, [vp]), "gs_stream": (vp, [vp]),
         "gs_upload_array": (i32, [vp, cp, vp, u64, i32, i32]), "gs_upload_session": (i32, [vp, vp, i32]), "gs_upload_session_as": (i32, [vp, vp, i32, i32]),
         "gs_plan_create": (i32, [vp, P(PlanDesc), i32, i32, P(vp)]), "gs_plan_destroy": (None, [vp]),

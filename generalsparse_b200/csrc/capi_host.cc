@@ -1,6 +1,9 @@
 // gsh_* entry points of include/gsparse_b200.h: the host side (metadata store, operator graph).
 // Pure C++; nothing here touches CUDA, so these calls work on a box without a GPU.
 #include "capi_internal.hpp"
+#include "host/tile_format.hpp"
+
+#include <algorithm>
 
 #include <cstring>
 
@@ -308,6 +311,44 @@ gs_status gsh_partition_rows_balanced(const uint64_t *row_nnz, uint64_t rows, in
     cut[G] = rows;
     cut[0] = 0;
     for (int g = 0; g <= G; g++) out[g] = cut[g];
+    GS_API_END
+}
+
+gs_status gsh_tile_stream_roundtrip(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val, uint32_t n_rows, uint32_t n_cols, uint32_t pass_warps, uint16_t *dense_out,
+                                    uint64_t *stats)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(rowptr && col && val && dense_out && stats && n_rows > 0 && n_cols > 0, "bad argument");
+    tile_stream ts;
+    try {
+        build_tile_stream(rowptr, col, val, n_rows, n_cols, pass_warps, ts);
+    } catch (const std::exception &e) {
+        throw gs::Error(e.what());
+    }
+    std::vector<uint16_t> dense;
+    expand_tile_stream(ts, dense);
+    std::copy(dense.begin(), dense.end(), dense_out);
+    // the stores of the kernel's producers: pair slot j of the 32 lanes of warp w in sweep p
+    const uint32_t pw = pass_warps ? pass_warps : 10, sweep = pw * 256u;
+    uint64_t n_stores = 0, wavefronts = 0;
+    for (size_t t = 0; t + 1 < ts.tile_ptr.size(); t++) {
+        const uint32_t b = ts.tile_ptr[t], n = ts.tile_ptr[t + 1] - b;
+        for (uint32_t base = 0; base < n; base += 256u) {
+            (void)sweep;
+            const uint32_t lanes = std::min<uint32_t>(32u, (n - base) / 8u);
+            for (uint32_t j = 0; j < 8; j++) {
+                uint32_t hist[32] = {0}, worst = 0;
+                // two lanes that hit the same 32-bit word share a wavefront; distinct words of one bank do not
+                std::vector<uint32_t> words;
+                for (uint32_t l = 0; l < lanes; l++) words.push_back(ts.off[b + base + l * 8u + j] >> 2);
+                std::sort(words.begin(), words.end());
+                words.erase(std::unique(words.begin(), words.end()), words.end());
+                for (uint32_t w : words) worst = std::max(worst, ++hist[w & 31u]);
+                n_stores++, wavefronts += worst;
+            }
+        }
+    }
+    stats[0] = ts.off.size(), stats[1] = ts.nnz, stats[2] = ts.tile_ptr.size() - 1, stats[3] = n_stores, stats[4] = wavefronts;
     GS_API_END
 }
 

@@ -138,6 +138,16 @@ gs_status gsh_session_plan_desc(const gsh_session *s, gs_plan_desc *out);
  * row_nnz: nnz per row (len rows). out_begin_rows: G+1 entries. */
 gs_status gsh_partition_rows_balanced(const uint64_t *row_nnz, uint64_t rows, int G, uint64_t *out_begin_rows);
 
+/* B200 tile stream (csrc/host/tile_format.hpp): the device layout GS_FAMILY_B200_TCGEN05 builds from a row-direction
+ * chain -- 128 x 64 tiles, each a run of (byte offset in the swizzled shared-memory image, fp16 value) pairs.  This entry
+ * point builds the stream from CSR (rowptr: n_rows + 1 offsets, col, fp16 value bits), expands it again and reports
+ * stats[0] = pairs stored (runs padded to 8), [1] = non-zero pairs, [2] = tiles, [3] = warp-wide 2-byte stores the
+ * decompression issues, [4] = shared-memory wavefronts those stores need (bank conflicts included).
+ * pass_warps: producer warps per sweep the runs are bank-ordered for (10 in the kernel; 0 = row-major runs).
+ * dense_out: n_rows * n_cols fp16 bits, row-major.  Host only: the CPU tests use it, the engine does the same at plan time. */
+gs_status gsh_tile_stream_roundtrip(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val_f16, uint32_t n_rows, uint32_t n_cols, uint32_t pass_warps,
+                                    uint16_t *dense_out, uint64_t *stats);
+
 /* ------------------------------------------------------------------ device: engine ---------- */
 typedef struct gs_ctx gs_ctx;   /* replaces executor.cc's compile-and-fork with an in-process device context */
 typedef struct gs_plan gs_plan;
