@@ -28,11 +28,16 @@ void drop_level(meta_data_set &ms, POS_TYPE pos, int id, steps::recs &rec)
     for (const std::string &n : ms.all_item_of_metadata_of_diff_pos(pos, id)) steps::remove_item_of_metadata(ms, id, n, pos, &rec);
 }
 
-void rerun_former(const opv &former, bool check)
+// after a child operator padded the matrix, the parent levels are derived again without their own padding; the steps of
+// the re-run land in the child's record sequence (fixed_interval_col_direction_thread_blocking_operator.cc run())
+void rerun_former(const opv &former, bool check, steps::recs &into)
 {
     for (const auto &o : former) {
+        size_t before = o->get_data_transform_sequence().size();
         o->set_padding_to_false();
         o->run(check);
+        const auto &seq = o->get_data_transform_sequence();
+        into.insert(into.end(), seq.begin() + before, seq.end());
     }
 }
 
@@ -74,6 +79,7 @@ class fixed_interval_row_direction_tblock_blocking_operator : public basic_opera
         : basic_operator("fixed_interval_row_direction_tblock_blocking_operator", std::move(cg), DISTRIBUTING_OP), b_(b), pad_(is_padding)
     {
         GS_REQUIRE(b > 0, "fixed_row_block_size must be > 0");
+        params = ",fixed_row_block_size:" + std::to_string(b);
     }
     bool is_valid_according_to_operator(const operator_context &h) override
     {
@@ -107,6 +113,7 @@ class fixed_interval_row_direction_warp_blocking_operator : public basic_operato
     {
         GS_REQUIRE(b > 0, "fixed_row_block_size must be > 0");
         if (is_padding) GS_REQUIRE(!row_rel && !nz_rel, "row padding excludes relative indices");
+        params = ",fixed_row_block_size:" + std::to_string(b) + ",is_padding:" + std::to_string((int)is_padding);
     }
     bool is_valid_according_to_operator(const operator_context &h) override
     {
@@ -120,6 +127,9 @@ class fixed_interval_row_direction_warp_blocking_operator : public basic_operato
         auto &ms = *meta_data_set_ptr;
         int id = target_matrix_id;
         steps::recs r;
+        // is_valid_according_to_metadata (fixed_interval_row_direction_warp_blocking_operator.cc:154-157): row padding only
+        // while no thread-block level exists -- it would shift rows under the blocks already cut
+        GS_REQUIRE(!(pad_ && ms.count_of_metadata_of_diff_pos(TBLOCK_META, id) != 0), "warp row padding after a tblock level exists");
         if (ms.is_exist(TBLOCK_META, "first_row_indices", id)) {
             steps::get_begin_rows_after_fixed_blocking_in_row_direction_in_parent(ms, WARP_META, TBLOCK_META, id, b_, &r);
             if (row_rel_) steps::get_begin_rows_after_fixed_blocking_in_row_direction_relative_to_parent(ms, WARP_META, TBLOCK_META, id, b_, &r);
@@ -153,6 +163,7 @@ class fixed_interval_row_direction_thread_blocking_operator : public basic_opera
         GS_REQUIRE(b > 0, "fixed_row_block_size must be > 0");
         if (is_row_padding) GS_REQUIRE(!row_rel && !nz_rel, "row padding excludes relative indices");
         former_ = history->read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        params = ",fixed_row_block_size:" + std::to_string(b) + ",is_row_padding:" + std::to_string((int)is_row_padding);
     }
     bool is_valid_according_to_operator(const operator_context &h) override
     {
@@ -176,13 +187,13 @@ class fixed_interval_row_direction_thread_blocking_operator : public basic_opera
                 steps::modify_by_col_pad_parent_blk_to_max_row_size(ms, parent, id, true, pad_bound(), &r);
                 if (has_w) drop_level(ms, WARP_META, id, r);
                 if (has_tb) drop_level(ms, TBLOCK_META, id, r);
-                rerun_former(former_, check);
+                rerun_former(former_, check, r);
             }
             if (col_pad_) {
                 steps::modify_by_col_pad_in_sub_matrix(ms, id, col_size_, pad_bound(), &r);
                 if (has_w) drop_level(ms, WARP_META, id, r);
                 if (has_tb) drop_level(ms, TBLOCK_META, id, r);
-                rerun_former(former_, check);
+                rerun_former(former_, check, r);
             }
             steps::get_begin_rows_after_fixed_blocking_in_row_direction_in_parent(ms, THREAD_META, parent, id, b_, &r);
             if (row_rel_) steps::get_begin_rows_after_fixed_blocking_in_row_direction_relative_to_parent(ms, THREAD_META, parent, id, b_, &r);
@@ -221,6 +232,7 @@ class fixed_interval_col_direction_thread_blocking_operator : public basic_opera
     {
         GS_REQUIRE(col_block > 0, "fixed_col_block_size must be > 0");
         former_ = history->read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        params = ",fixed_col_block_size:" + std::to_string(col_block) + ",is_padding:" + std::to_string((int)(pad_to_col_size || pad_to_row_max));
     }
     bool is_valid_according_to_operator(const operator_context &h) override
     {
@@ -239,15 +251,20 @@ class fixed_interval_col_direction_thread_blocking_operator : public basic_opera
         if (col_pad_ || max_pad_) {
             if (has_tb) drop_level(ms, TBLOCK_META, id, r);
             if (has_w) drop_level(ms, WARP_META, id, r);
-            rerun_former(former_, check);
+            rerun_former(former_, check, r);
         }
         steps::get_begin_rows_after_fixed_blocking_in_col_direction(ms, THREAD_META, id, c_, &r);
         steps::get_begin_nzs_after_fixed_blocking_in_col_direction(ms, THREAD_META, id, c_, &r);
-        GS_REQUIRE(!row_rel_ && !nz_rel_, "col-direction BMT indices relative to a parent: not built yet");
+        // relative to the innermost parent an earlier operator built: BMW if a warp operator ran, else BMTB (ctor, :43-82)
+        const bool w_former = any_name_has(former_, "warp"), tb_former = !w_former && any_name_has(former_, "tblock");
+        if (tb_former && row_rel_) steps::get_begin_rows_after_fixed_blocking_in_col_direction_relative_to_parent(ms, TBLOCK_META, id, c_, &r);
+        if (tb_former && nz_rel_) steps::get_begin_nzs_after_fixed_blocking_in_col_direction_relative_to_parents(ms, TBLOCK_META, id, c_, &r);
         if (has_tb) {
             steps::get_begin_children_of_parent_after_blocking(ms, THREAD_META, TBLOCK_META, id, &r);
             if (col_pad_) steps::get_BMT_size_of_each_parent(ms, TBLOCK_META, id, false, &r);
         }
+        if (w_former && row_rel_) steps::get_begin_rows_after_fixed_blocking_in_col_direction_relative_to_parent(ms, WARP_META, id, c_, &r);
+        if (w_former && nz_rel_) steps::get_begin_nzs_after_fixed_blocking_in_col_direction_relative_to_parents(ms, WARP_META, id, c_, &r);
         if (has_w) {
             steps::get_begin_children_of_parent_after_blocking(ms, THREAD_META, WARP_META, id, &r);
             if (col_pad_) steps::get_BMT_size_of_each_parent(ms, WARP_META, id, false, &r);
@@ -271,6 +288,7 @@ class fixed_interval_nnz_direction_thread_blocking_operator : public basic_opera
           nz_rel_(nz_rel), pad_(nnz_padding)
     {
         GS_REQUIRE(nnz_per_bmt > 0, "nnz_per_BMT must be > 0");
+        params = ",nnz_per_BMT:" + std::to_string(nnz_per_bmt);
     }
     bool is_valid_according_to_operator(const operator_context &h) override
     {
@@ -309,6 +327,7 @@ class balanced_interval_row_direction_blocking_operator : public basic_operator 
                              "_blocking_operator", std::move(cg), DISTRIBUTING_OP), pos_(pos), per_(nnz_per_interval)
     {
         GS_REQUIRE(nnz_per_interval > 0, "nnz_per_interval must be > 0");
+        params = ",nnz_per_interval:" + std::to_string(nnz_per_interval);
     }
     void run(bool) override
     {
@@ -330,9 +349,50 @@ class balanced_interval_row_direction_blocking_operator : public basic_operator 
     uint64_t per_;
 };
 
+// merge_path_{tblock,warp,thread}_operator (operator.hpp:1205,1251,1297; operator/merge_path_*_operator.cc)
+class merge_path_operator : public basic_operator {
+  public:
+    merge_path_operator(std::shared_ptr<code_generator> cg, POS_TYPE pos, int work_size)
+        : basic_operator(std::string("merge_path_") + (pos == TBLOCK_META ? "tblock" : pos == WARP_META ? "warp" : "thread") + "_operator", std::move(cg), DISTRIBUTING_OP),
+          pos_(pos), work_(work_size)
+    {
+        GS_REQUIRE(work_size > 0, "work_size must be > 0");
+        params = ",work_size:" + std::to_string(work_size);
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        // merge_path_thread_operator.cc:30-62: nothing implementing yet, and no thread-level, column-direction or
+        // interlance operator before it (the tblock and warp flavours exclude their own level the same way)
+        if (!h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty()) return false;
+        const auto d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        if (any_name_has(d, "thread") || any_name_has(d, "col") || any_name_has(d, "interlance")) return false;
+        if (pos_ != THREAD_META && any_name_has(d, "warp")) return false;
+        if (pos_ == TBLOCK_META && any_name_has(d, "tblock")) return false;
+        return true;
+    }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        GS_REQUIRE(ms.count_of_metadata_of_diff_pos(THREAD_META, id) == 0, "merge path: thread-level metadata already exists");
+        if (pos_ != THREAD_META) GS_REQUIRE(ms.count_of_metadata_of_diff_pos(WARP_META, id) == 0, "merge path: warp-level metadata already exists");
+        if (pos_ == TBLOCK_META) GS_REQUIRE(ms.count_of_metadata_of_diff_pos(TBLOCK_META, id) == 0, "merge path: tblock-level metadata already exists");
+        steps::recs r;
+        steps::get_begin_rows_of_level_after_merge_path(ms, pos_, id, work_, &r);
+        steps::get_begin_nzs_of_level_after_merge_path(ms, pos_, id, work_, &r);
+        append(transform_seq, r);
+        code_generator_ptr->open_spec_level_of_paral(TBLOCK_META); // all three flavours open the tblock level (merge_path_*_operator.cc)
+        is_run = true;
+    }
+
+  private:
+    POS_TYPE pos_;
+    uint64_t work_;
+};
+
 class empty_row_pad_operator : public basic_operator { // operator.hpp:449
   public:
-    explicit empty_row_pad_operator(std::shared_ptr<code_generator> cg) : basic_operator("empty_row_pad_operator", std::move(cg), DISTRIBUTING_OP) {}
+    explicit empty_row_pad_operator(std::shared_ptr<code_generator> cg) : basic_operator("empty_row_pad_operator", std::move(cg), CONVERTING_OP) {}
     bool is_valid_according_to_operator(const operator_context &h) override
     {
         return h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id).empty() && h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty();
@@ -594,10 +654,16 @@ std::shared_ptr<basic_operator> make_operator(const std::string &op, std::shared
         return need(4), std::make_shared<fixed_interval_nnz_direction_thread_blocking_operator>(cg, (int)a[0], a[1] != 0, a[2] != 0, a[3] != 0);
     if (op == "balanced_interval_row_direction_tblock_blocking_operator")
         return need(1), std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, TBLOCK_META, (int)a[0]);
-    if (op == "balanced_interval_row_direction_warp_blocking_operator")
-        return need(1), std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, WARP_META, (int)a[0]);
-    if (op == "balanced_interval_row_direction_thread_blocking_operator")
-        return need(1), std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, THREAD_META, (int)a[0]);
+    // the warp and thread flavours take (nnz_per_interval, row_index_is_relative, nz_index_is_relative) like the reference;
+    // the one-argument form stays for callers that block at the top level only
+    if (op == "balanced_interval_row_direction_warp_blocking_operator" || op == "balanced_interval_row_direction_thread_blocking_operator") {
+        GS_REQUIRE(a.size() == 1 || a.size() == 3, op + " takes 1 or 3 arguments after code_generator_ptr");
+        GS_REQUIRE(a.size() == 1 || (a[1] == 0 && a[2] == 0), op + ": indices relative to a parent level are not built");
+        return std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, op.find("warp") != std::string::npos ? WARP_META : THREAD_META, (int)a[0]);
+    }
+    if (op == "merge_path_tblock_operator") return need(1), std::make_shared<merge_path_operator>(cg, TBLOCK_META, (int)a[0]);
+    if (op == "merge_path_warp_operator") return need(1), std::make_shared<merge_path_operator>(cg, WARP_META, (int)a[0]);
+    if (op == "merge_path_thread_operator") return need(1), std::make_shared<merge_path_operator>(cg, THREAD_META, (int)a[0]);
     if (op == "empty_row_pad_operator") return need(0), std::make_shared<empty_row_pad_operator>(cg);
     if (op == "thread_total_reduce_operator") return need(3), std::make_shared<thread_total_reduce_operator>(cg, a[0] != 0, (int)a[1], (int)a[2]);
     if (op == "thread_bit_map_operator") return need(4), std::make_shared<thread_bit_map_operator>(cg, (POS_TYPE)a[0], (int)a[1], (int)a[2], (int)a[3]);

@@ -166,7 +166,7 @@ void operator_context::add(std::shared_ptr<basic_operator> op) { all_.push_back(
 
 std::string basic_operator::convert_to_string() const
 {
-    return name + "::{name:\"" + name + "\",stage:" + stage_name(stage) + ",target_matrix_id:" + std::to_string(target_matrix_id) + "}";
+    return name + "::{name:\"" + name + "\",stage:" + stage_name(stage) + ",target_matrix_id:" + std::to_string(target_matrix_id) + params + "}";
 }
 
 void operator_executer::add_and_run(std::shared_ptr<basic_operator> op)

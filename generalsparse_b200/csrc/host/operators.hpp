@@ -117,6 +117,7 @@ class basic_operator { // operator.hpp:64-189
     std::shared_ptr<meta_data_set> meta_data_set_ptr;
     int target_matrix_id;
     std::vector<std::string> transform_seq; // step records, in run order
+    std::string params;                      // ",key:value" pairs the reference's convert_to_string() adds for this operator
     double pad_bound() const { return (double)get_config().as_integer("PADDING_RATE_UP_BOUND"); }
 };
 

@@ -132,7 +132,8 @@ void remove_empty_row_in_end_of_sub_matrix(meta_data_set &ms, int id, recs *rec)
     uint64_t rows = end - begin + 1;
     uint64_t max_row = ms.get(GLOBAL_META, "nz_row_indices", id).u.back();
     GS_REQUIRE(max_row <= rows - 1, "row index past end_row_index");
-    if (max_row < rows - 1) ms.replace_u(GLOBAL_META, "end_row_index", id, {begin + max_row});
+    if (max_row >= rows - 1) return; // a step that touched nothing leaves no record (operator.hpp:163-175 set_transform_seq)
+    ms.replace_u(GLOBAL_META, "end_row_index", id, {begin + max_row});
     record(rec, "remove_empty_row_in_end_of_sub_matrix", id);
 }
 
@@ -172,6 +173,7 @@ void modify_by_col_pad_in_sub_matrix(meta_data_set &ms, int id, uint64_t m, doub
         ms.replace(GLOBAL_META, "nz_vals", id, std::move(va));
         ms.replace_u(GLOBAL_META, "nz_row_indices", id, std::move(nr));
     }
+    if (!padded) return;
     std::string extra = ",multiple_of_each_row_size:" + std::to_string(m);
     record(rec, "modify_col_indices_by_col_pad_in_sub_matrix", id, extra);
     record(rec, "modify_vals_by_col_pad_in_sub_matrix", id, extra);
@@ -185,14 +187,15 @@ void modify_by_nnz_pad(meta_data_set &ms, int id, uint64_t target, double bound,
     universal_array &C = ms.get(GLOBAL_META, "nz_col_indices", id);
     universal_array &V = ms.get(GLOBAL_META, "nz_vals", id);
     uint64_t nnz = C.get_len();
-    if (nnz % target != 0) {
+    if (nnz % target == 0) return;
+    {
         uint64_t n2 = (nnz / target + 1) * target;
         check_pad_rate(n2, nnz, bound, "modify_col_indices_by_nnz_pad");
         C.u.resize(n2, C.u.back());
         V.f.resize(n2, 0.0);
         R.u.resize(n2, R.u.back());
     }
-    std::string extra = ",nnz_target:" + std::to_string(target);
+    std::string extra = "nnz_target:" + std::to_string(target); // (no comma: modify_*_by_nnz_pad.cc convert_to_string)
     record(rec, "modify_col_indices_by_nnz_pad", id, extra);
     record(rec, "modify_vals_by_nnz_pad", id, extra);
     record(rec, "modify_row_indices_by_nnz_pad", id, extra);
@@ -206,7 +209,8 @@ void modify_by_row_pad_in_sub_matrix(meta_data_set &ms, int id, uint64_t multipl
     universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
     universal_array &C = ms.get(GLOBAL_META, "nz_col_indices", id);
     universal_array &V = ms.get(GLOBAL_META, "nz_vals", id);
-    if (rows % multiple != 0) {
+    if (rows % multiple == 0) return;
+    {
         uint64_t added = (rows / multiple + 1) * multiple - rows;
         uint64_t nnz = R.get_len();
         check_pad_rate(nnz + added, nnz, bound, "modify_col_indices_by_row_pad_in_sub_matrix");
@@ -249,6 +253,7 @@ void modify_by_empty_pad_in_submatrix(meta_data_set &ms, int id, recs *rec)
         ms.replace(GLOBAL_META, "nz_vals", id, std::move(va));
         ms.replace_u(GLOBAL_META, "nz_row_indices", id, std::move(nr));
     }
+    if (!padded) return;
     record(rec, "modify_col_indices_by_empty_pad_in_submatrix", id);
     record(rec, "modify_vals_by_empty_pad_in_submatrix", id);
     record(rec, "modify_row_indices_by_empty_pad_in_submatrix", id);
@@ -295,9 +300,11 @@ void modify_by_col_pad_parent_blk_to_max_row_size(meta_data_set &ms, POS_TYPE pa
         ms.replace(GLOBAL_META, "nz_vals", id, std::move(va));
         ms.replace_u(GLOBAL_META, "nz_row_indices", id, std::move(nr));
     }
-    record(rec, "modify_col_indices_by_col_pad_parent_blk_to_max_row_size", id);
-    record(rec, "modify_vals_by_col_pad_parent_blk_to_max_row_size", id);
-    record(rec, "modify_row_indices_by_col_pad_parent_blk_to_max_row_size", id);
+    if (!padded) return;
+    const std::string extra = std::string(",parent_pos:") + pos_name(parent_pos);
+    record(rec, "modify_col_indices_by_col_pad_parent_blk_to_max_row_size", id, extra);
+    record(rec, "modify_vals_by_col_pad_parent_blk_to_max_row_size", id, extra);
+    record(rec, "modify_row_indices_by_col_pad_parent_blk_to_max_row_size", id, extra);
 }
 
 // ---------------------------------------------------------------------------- fixed blocking, row direction
@@ -404,7 +411,8 @@ void get_begin_children_of_parent_after_blocking_in_row_direction(meta_data_set 
     }
     ms.add_u(parent, first_child_name(child), id, std::move(v));
     record(rec, child == WARP_META ? "get_begin_BMWs_of_BMTB_after_blocking_in_row_direction"
-                                   : "get_begin_BMTs_of_specific_parent_after_blocking_in_row_direction", id);
+                                   : "get_begin_BMTs_of_specific_parent_after_blocking_in_row_direction", id,
+           child == WARP_META ? ",fixed_row_block_size:" : std::string(",parent_pos:") + pos_name(parent));
 }
 
 void get_begin_children_of_parent_after_blocking(meta_data_set &ms, POS_TYPE child, POS_TYPE parent, int id, recs *rec)
@@ -420,7 +428,8 @@ void get_begin_children_of_parent_after_blocking(meta_data_set &ms, POS_TYPE chi
         v.push_back(v.back() + n);
     }
     ms.add_u(parent, first_child_name(child), id, std::move(v));
-    record(rec, child == WARP_META ? "get_begin_BMWs_of_BMTB_after_blocking" : "get_begin_BMTs_of_specific_parent_after_blocking", id);
+    record(rec, child == WARP_META ? "get_begin_BMWs_of_BMTB_after_blocking" : "get_begin_BMTs_of_specific_parent_after_blocking", id,
+           child == WARP_META ? "" : std::string(",parent_pos:") + pos_name(parent));
 }
 
 // ---------------------------------------------------------------------------- fixed blocking, col direction
@@ -454,6 +463,43 @@ void get_begin_nzs_after_fixed_blocking_in_col_direction(meta_data_set &ms, POS_
 }
 
 // ---------------------------------------------------------------------------- fixed blocking, nnz direction
+// BMT offsets relative to the parent block that holds them (get_begin_rows_of_BMT_after_fixed_blocking_in_col_direction_
+// relative_to_{BMTB,BMW}.cc, get_begin_nzs_of_BMT_after_fixed_blocking_in_col_direction_relative_to_parents.cc):
+// one entry per BMT, no closing sentinel
+void get_begin_rows_after_fixed_blocking_in_col_direction_relative_to_parent(meta_data_set &ms, POS_TYPE parent, int id, uint64_t c, recs *rec)
+{
+    GS_REQUIRE(parent == TBLOCK_META || parent == WARP_META, "parent_pos");
+    std::vector<uint64_t> len = row_nnz(ms, id);
+    const universal_array &P = ms.get(parent, "first_row_indices", id);
+    std::vector<uint64_t> v;
+    for (uint64_t b = 0; b + 1 < P.get_len(); b++)
+        for (uint64_t r = P.u[b]; r < P.u[b + 1]; r++)
+            for (uint64_t k = 0; k < (len.at(r) + c - 1) / c; k++) v.push_back(r - P.u[b]);
+    const char *sfx = parent == TBLOCK_META ? "_relative_to_BMTB" : "_relative_to_BMW";
+    ms.add_u(THREAD_META, std::string("first_row_indices") + sfx, id, std::move(v));
+    record(rec, std::string("get_begin_rows_of_BMT_after_fixed_blocking_in_col_direction") + sfx, id, ",col_size:" + std::to_string(c));
+}
+
+void get_begin_nzs_after_fixed_blocking_in_col_direction_relative_to_parents(meta_data_set &ms, POS_TYPE parent, int id, uint64_t c, recs *rec)
+{
+    GS_REQUIRE(parent == TBLOCK_META || parent == WARP_META, "parent_pos");
+    std::vector<uint64_t> len = row_nnz(ms, id);
+    const universal_array &P = ms.get(parent, "first_row_indices", id);
+    std::vector<uint64_t> v;
+    for (uint64_t b = 0; b + 1 < P.get_len(); b++) {
+        uint64_t off = 0;
+        for (uint64_t r = P.u[b]; r < P.u[b + 1]; r++)
+            for (uint64_t left = len.at(r); left > 0;) {
+                v.push_back(off);
+                uint64_t take = std::min(left, c);
+                off += take, left -= take;
+            }
+    }
+    ms.add_u(THREAD_META, std::string("first_nz_indices_relative_to_") + (parent == TBLOCK_META ? "BMTB" : "BMW"), id, std::move(v));
+    record(rec, "get_begin_nzs_of_BMT_after_fixed_blocking_in_col_direction_relative_to_parents", id,
+           ",col_size:" + std::to_string(c) + ",parent_pos:" + pos_name(parent));
+}
+
 void get_begin_rows_after_fixed_blocking_in_nnz_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t k, recs *rec)
 {
     GS_REQUIRE(k >= 1, "nnz_per_block must be >= 1");
@@ -480,7 +526,6 @@ void get_begin_nzs_after_fixed_blocking_in_nnz_direction(meta_data_set &ms, POS_
 // --------------------------------------------------------------------------------------------------- sizes
 void get_BMT_size_of_each_parent(meta_data_set &ms, POS_TYPE parent_pos, int id, bool row_direction_blocking, recs *rec)
 {
-    record(rec, "get_BMT_size_of_each_parent", id);
     const universal_array &T = ms.get(THREAD_META, "first_nz_indices", id);
     std::vector<uint64_t> out;
     if (parent_pos == GLOBAL_META) {
@@ -518,6 +563,7 @@ void get_BMT_size_of_each_parent(meta_data_set &ms, POS_TYPE parent_pos, int id,
         }
     }
     ms.add_u(parent_pos, "BMT_size_of_each_blk", id, std::move(out));
+    record(rec, "get_BMT_size_of_each_parent", id, std::string(",parent_pos:") + pos_name(parent_pos)); // nothing emitted, nothing recorded
 }
 
 // -------------------------------------------------------------------------------------- bit maps / segments
@@ -553,7 +599,7 @@ void thread_bit_map(meta_data_set &ms, bool parent_flag, uint64_t parent_size, i
         out.push_back(map);
     }
     ms.add_u(THREAD_META, "thread_bit_map", id, std::move(out));
-    record(rec, "thread_bit_map", id);
+    record(rec, "thread_bit_map", id, ",fixed_row_block_size:");
 }
 
 void parent_bit_map_of_thread(meta_data_set &ms, POS_TYPE pos, int id, uint64_t vector_width, recs *rec)
@@ -581,7 +627,7 @@ void parent_bit_map_of_thread(meta_data_set &ms, POS_TYPE pos, int id, uint64_t 
         throw Error("parent_bit_map_of_thread: pos must be WARP_META or TBLOCK_META");
     }
     ms.add_u(store, "bit_map_of_thread", id, std::move(out));
-    record(rec, "parent_bit_map_of_thread", id);
+    record(rec, "parent_bit_map_of_thread", id, ",fixed_row_block_size:");
 }
 
 void segment_empty_flag(meta_data_set &ms, POS_TYPE, uint64_t size, int id, recs *rec)
@@ -607,7 +653,7 @@ void segment_empty_flag(meta_data_set &ms, POS_TYPE, uint64_t size, int id, recs
         out.push_back(w);
     }
     ms.add_u(THREAD_META, "segment_empty_flag", id, std::move(out));
-    record(rec, "segment_empty_flag", id);
+    record(rec, "segment_empty_flag", id, ",fixed_row_block_size:");
 }
 
 void segment_empty_row_indices(meta_data_set &ms, POS_TYPE, int id, recs *rec)
@@ -622,7 +668,7 @@ void segment_empty_row_indices(meta_data_set &ms, POS_TYPE, int id, recs *rec)
             if (R.u[i] != R.u[i - 1]) out.push_back(R.u[i] - first_row);
     }
     ms.add_u(THREAD_META, "segment_empty_row_indices", id, std::move(out));
-    record(rec, "segment_empty_row_indices", id);
+    record(rec, "segment_empty_row_indices", id, ",fixed_row_block_size:");
 }
 
 void segment_offset(meta_data_set &ms, bool parent_flag, uint64_t size, int id, recs *rec)
@@ -644,7 +690,7 @@ void segment_offset(meta_data_set &ms, bool parent_flag, uint64_t size, int id, 
     }
     // NB: the run that reaches the end of the array is never written back (segment_offset.cc) -- kept
     ms.add_u(THREAD_META, "segment_offset", id, std::move(out));
-    record(rec, "segment_offset", id);
+    record(rec, "segment_offset", id, ",fixed_row_block_size:");
 }
 
 void segment_ptr(meta_data_set &ms, POS_TYPE, int id, recs *rec)
@@ -660,7 +706,7 @@ void segment_ptr(meta_data_set &ms, POS_TYPE, int id, recs *rec)
         out.push_back(count);
     }
     ms.add_u(THREAD_META, "segment_ptr", id, std::move(out));
-    record(rec, "segment_ptr", id);
+    record(rec, "segment_ptr", id, ",fixed_row_block_size:");
 }
 
 // -------------------------------------------------------------------------------------- merge-thread grouping
@@ -761,7 +807,13 @@ void get_begin_rows_after_nnz_blocking_in_row_direction(meta_data_set &ms, POS_T
 {
     GS_REQUIRE(per >= 1, "nnz_per_interval must be >= 1");
     std::vector<uint64_t> len = row_nnz(ms, id);
-    ms.add_u(pos, "first_row_indices", id, balanced_begin_rows(len, per));
+    std::vector<uint64_t> cuts = balanced_begin_rows(len, per);
+    if (cuts.size() >= 3) { // a closing block that the greedy rule did not fill: it must hold something
+        uint64_t tail = 0;
+        for (uint64_t r = cuts[cuts.size() - 2]; r < cuts.back(); r++) tail += len[r];
+        GS_REQUIRE(tail != 0, "the rows after the last interval are all empty (data_transform_common.cc:984 asserts nz_count != 0)");
+    }
+    ms.add_u(pos, "first_row_indices", id, std::move(cuts));
     record(rec, std::string("get_begin_rows_of_") + level_tag(pos) + "_after_nnz_blocking_in_row_direction", id, ",nnz_per_interval:" + std::to_string(per));
 }
 
@@ -773,10 +825,54 @@ void get_begin_nzs_after_nnz_blocking_in_row_direction(meta_data_set &ms, POS_TY
     record(rec, std::string("get_begin_nzs_of_") + level_tag(pos) + "_after_nnz_blocking_in_row_direction", id, ",nnz_per_interval:" + std::to_string(per));
 }
 
+// ---- merge path (get_begin_{rows,nzs}_of_level_after_merge_path.cc) ------------------------------------------------------
+// The path walks the non-empty rows: row j (the j-th non-empty one) ends at path position  sum(nnz of rows 0..j) + j.
+// Part p starts at path position p * work_size: in the first row whose end lies beyond it, at non-zero  position - j.
+// The reference searches that row from the start for every part (get_begin_rows_of_level_after_merge_path.cc:82-93:
+// parts x rows steps -- ~10^13 at 10 M rows and work 128); both sequences are monotone, so one two-pointer walk gives
+// the same arrays in rows + parts steps.
+static void merge_path_walk(const std::vector<uint64_t> &len, uint64_t work, std::vector<uint64_t> *rows_out, std::vector<uint64_t> *nzs_out)
+{
+    std::vector<uint64_t> path_end, path_row;
+    uint64_t count = 0;
+    for (uint64_t i = 0; i < len.size(); i++) {
+        if (len[i] == 0) continue;
+        count += len[i] + (path_end.empty() ? 0 : 1);
+        path_end.push_back(count), path_row.push_back(i);
+    }
+    uint64_t j = 0;
+    for (uint64_t pos = 0; pos < count; pos += work) {
+        while (j < path_end.size() && path_end[j] <= pos) j++;
+        if (j == path_end.size()) break; // (cannot happen: pos < count = path_end.back())
+        if (rows_out) rows_out->push_back(path_row[j]);
+        if (nzs_out) nzs_out->push_back(pos - j);
+    }
+}
+
+void get_begin_rows_of_level_after_merge_path(meta_data_set &ms, POS_TYPE pos, int id, uint64_t work, recs *rec)
+{
+    GS_REQUIRE(work >= 1, "work_size must be >= 1");
+    std::vector<uint64_t> v;
+    merge_path_walk(row_nnz(ms, id), work, &v, nullptr);
+    GS_REQUIRE(!v.empty(), "merge path over a matrix without non-zeros");
+    ms.add_u(pos, "first_row_indices_without_ending", id, std::move(v));
+    record(rec, "get_begin_rows_of_level_after_merge_path", id, ",work_size:" + std::to_string(work));
+}
+
+void get_begin_nzs_of_level_after_merge_path(meta_data_set &ms, POS_TYPE pos, int id, uint64_t work, recs *rec)
+{
+    GS_REQUIRE(work >= 1, "work_size must be >= 1");
+    std::vector<uint64_t> v;
+    merge_path_walk(row_nnz(ms, id), work, nullptr, &v);
+    v.push_back(ms.get(GLOBAL_META, "nz_row_indices", id).get_len());
+    ms.add_u(pos, "first_nz_indices", id, std::move(v));
+    record(rec, "get_begin_nzs_of_level_after_merge_path", id, ",work_size:" + std::to_string(work));
+}
+
 void remove_item_of_metadata(meta_data_set &ms, int id, const std::string &name, POS_TYPE pos, recs *rec)
 {
     ms.remove(pos, name, id);
-    record(rec, "remove_item_of_metadata", id);
+    record(rec, "remove_item_of_metadata", id, std::string(", pos:") + pos_name(pos));
 }
 
 const std::vector<std::string> &covered_reference_step_names()
@@ -812,6 +908,11 @@ const std::vector<std::string> &covered_reference_step_names()
         "get_begin_rows_of_BMT_after_nnz_blocking_in_row_direction", "get_begin_nzs_of_BMT_after_nnz_blocking_in_row_direction",
         "get_begin_rows_of_BMW_after_nnz_blocking_in_row_direction", "get_begin_nzs_of_BMW_after_nnz_blocking_in_row_direction",
         "get_begin_rows_of_BMTB_after_nnz_blocking_in_row_direction", "get_begin_nzs_of_BMTB_after_nnz_blocking_in_row_direction",
+        "get_begin_rows_of_BMT_after_fixed_blocking_in_col_direction_relative_to_BMTB", "get_begin_rows_of_BMT_after_fixed_blocking_in_col_direction_relative_to_BMW",
+        "get_begin_nzs_of_BMT_after_fixed_blocking_in_col_direction_relative_to_parents",
+        "modify_col_indices_by_col_pad_parent_blk_to_max_row_size", "modify_vals_by_col_pad_parent_blk_to_max_row_size",
+        "modify_row_indices_by_col_pad_parent_blk_to_max_row_size",
+        "get_begin_rows_of_level_after_merge_path", "get_begin_nzs_of_level_after_merge_path",
         "remove_item_of_metadata"};
     return names;
 }

@@ -62,6 +62,8 @@ void get_begin_children_of_parent_after_blocking(meta_data_set &ms, POS_TYPE chi
 // get_begin_{rows,nzs}_of_{BMT,BMW,BMTB}_after_fixed_blocking_in_col_direction.cc
 void get_begin_rows_after_fixed_blocking_in_col_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t col_size, recs *rec = nullptr);
 void get_begin_nzs_after_fixed_blocking_in_col_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t col_size, recs *rec = nullptr);
+void get_begin_rows_after_fixed_blocking_in_col_direction_relative_to_parent(meta_data_set &ms, POS_TYPE parent, int id, uint64_t col_size, recs *rec = nullptr);
+void get_begin_nzs_after_fixed_blocking_in_col_direction_relative_to_parents(meta_data_set &ms, POS_TYPE parent, int id, uint64_t col_size, recs *rec = nullptr);
 
 // ---- fixed blocking, nnz direction (every k entries regardless of rows) --------------------------
 // get_begin_{rows,nzs}_of_{BMT,BMW,BMTB}_after_fixed_blocking_in_nnz_direction.cc

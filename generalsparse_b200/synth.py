@@ -8,6 +8,17 @@ order the reference loader demands (struct.cc:125).
 import numpy as np
 
 
+def _sorted_unique(key):
+    """np.unique for int64 keys by sort + neighbour compare (numpy's own is 50x slower on millions of keys)"""
+    key = np.sort(key)
+    if len(key) == 0:
+        return key
+    keep = np.empty(len(key), dtype=bool)
+    keep[0] = True
+    np.not_equal(key[1:], key[:-1], out=keep[1:])
+    return key[keep]
+
+
 def _rows_from_lengths(lengths):
     return np.repeat(np.arange(len(lengths), dtype=np.int64), lengths)
 
@@ -25,7 +36,7 @@ def _cols_for_lengths(rng, lengths, cols, weights=None):
         c = np.searchsorted(cdf, rng.random(total)).astype(np.int64)
         c = np.minimum(c, cols - 1)
     key = r * cols + c
-    key = np.unique(key)  # sorted, duplicates dropped (row lengths shrink slightly)
+    key = _sorted_unique(key)  # sorted, duplicates dropped (row lengths shrink slightly)
     return key // cols, key % cols
 
 
@@ -84,6 +95,40 @@ def synth_matrix(kind, rows, cols, seed=0, **p):
         r = np.repeat(np.arange(rows, dtype=np.int64), c.shape[1])
         return r, c.reshape(-1).astype(np.int64)
     raise ValueError("unknown synthetic kind %r" % kind)
+
+
+def powerlaw_lengths(rows, seed=0, avg_deg=20.0, alpha=2.1, cap=1000000):
+    """Row degrees of the C4 stand-in (10 M-row power-law matrix): Zipf-like tail with exponent alpha, capped, scaled to
+    rows * avg_deg non-zeros in total.  Cheap and global: every rank computes the same array and the same row cuts."""
+    rng = np.random.default_rng(0x6753 + seed)
+    u = rng.random(rows)
+    deg = np.floor((1.0 - u) ** (-1.0 / (alpha - 1.0)))
+    deg = np.minimum(deg, cap)
+    deg *= avg_deg * rows / deg.sum()
+    return np.maximum(0, np.round(deg)).astype(np.int64)
+
+
+def powerlaw_block(rows, cols, lengths, lo, hi, seed=0, chunk=1 << 16):
+    """Rows [lo, hi) of the C4 stand-in as (row - lo, col), row-major sorted.  Column ids follow a power-law popularity
+    (weight rank^-0.6 over a fixed permutation of the columns).  Rows are generated in fixed chunks with one generator
+    per chunk, so the matrix does not depend on how it is cut over the ranks."""
+    # popularity rank^-0.6: the CDF is ~ rank^0.4, so rank = cols * u^2.5 by inversion; a fixed permutation scatters the
+    # popular columns over the id range
+    perm = np.random.default_rng(0x6753 + seed).permutation(cols).astype(np.int64)
+    out_r, out_c = [], []
+    for k in range(lo // chunk, (hi + chunk - 1) // chunk):
+        a, b = k * chunk, min(rows, (k + 1) * chunk)
+        rng = np.random.default_rng([0x6753 + seed, k])
+        ln = np.minimum(lengths[a:b], cols)
+        r = np.repeat(np.arange(a, b, dtype=np.int64), ln)
+        c = perm[np.minimum((rng.random(int(ln.sum()), dtype=np.float32).astype(np.float64) ** 2.5 * cols).astype(np.int64), cols - 1)]
+        key = _sorted_unique(r * cols + c)  # sorted; duplicate draws inside a row are dropped
+        r, c = key // cols, key % cols
+        sel = (r >= lo) & (r < hi)
+        out_r.append(r[sel] - lo), out_c.append(c[sel])
+    if not out_r:
+        return np.zeros(0, np.int64), np.zeros(0, np.int64)
+    return np.concatenate(out_r), np.concatenate(out_c)
 
 
 def synth_values(nnz, seed=0, scale=0.02, dtype=np.float32):

@@ -13,11 +13,21 @@
 // as the hook "the whole chain has run" to dump the metadata set.
 //
 // usage: ref_harness <family> <matrix.mtx> <N> <sparse_coarsen> <coarsen> <dump_dir>
+//        ref_harness "ops=<name>[,<arg>...];<name>..." <matrix.mtx> <N> 0 0 <dump_dir>
+//   the second form runs an arbitrary sequence of the reference's own operators (operator.hpp, the
+//   code_generator constructors; arguments in declaration order, bools as 0/1) the way the driver chains do
+//   (operator_executer::add_and_run), prints each operator's records and dumps the set at the end -- for the
+//   operators none of the seven chains reaches (merge path, balanced intervals, column / nnz direction ...).
 //   CWD must hold global_config.json, arm_code/ and data_source/ (tests/golden/gen_golden.py
 //   prepares such a scratch dir).
 #include "metadata_set.hpp"
 #include "config.hpp"
 #include "executor.hpp"
+#include "operator.hpp"
+#include "operator_executer.hpp"
+#include "code_generator.hpp"
+#include <iostream>
+#include <sstream>
 #include <cstdio>
 #include <cstdlib>
 #include <string>
@@ -87,6 +97,67 @@ bool execute_binary(string execute_path, string filename, float &total_execute_t
 
 bool compile_spmv_code(string) { return true; }
 
+// one operator of the reference by name; a = the constructor's arguments between code_generator_ptr and operator_history
+static shared_ptr<basic_operator> ref_operator(const string &op, shared_ptr<code_generator> cg, shared_ptr<operator_context> h, const vector<long> &a)
+{
+    auto A = [&](size_t i) -> long { if (i >= a.size()) { fprintf(stderr, "%s: missing argument %zu\n", op.c_str(), i); exit(2); } return a[i]; };
+#define OP0(T) if (op == #T) return shared_ptr<basic_operator>(new T(cg, h))
+#define OP1(T) if (op == #T) return shared_ptr<basic_operator>(new T(cg, A(0), h))
+#define OP2(T) if (op == #T) return shared_ptr<basic_operator>(new T(cg, A(0), A(1), h))
+#define OP3(T) if (op == #T) return shared_ptr<basic_operator>(new T(cg, A(0), A(1), A(2), h))
+#define OP4(T) if (op == #T) return shared_ptr<basic_operator>(new T(cg, A(0), A(1), A(2), A(3), h))
+#define OP5(T) if (op == #T) return shared_ptr<basic_operator>(new T(cg, A(0), A(1), A(2), A(3), A(4), h))
+    OP0(sort_operator);
+    OP1(fixed_interval_row_matrix_div_operator);
+    OP3(row_nz_matrix_div_operator);
+    OP2(fixed_interval_row_direction_tblock_blocking_operator);
+    OP4(fixed_interval_row_direction_warp_blocking_operator);
+    OP0(empty_row_pad_operator);
+    OP5(fixed_interval_col_direction_thread_blocking_operator);
+    OP0(interlance_storage_operator);
+    if (op == "fixed_interval_row_direction_thread_blocking_operator")
+        return shared_ptr<basic_operator>(new fixed_interval_row_direction_thread_blocking_operator(cg, A(0), A(1), A(2), A(3), A(4), A(5), A(6), h));
+    OP5(fixed_interval_col_direction_warp_blocking_operator);
+    OP3(fixed_interval_col_direction_tblock_blocking_operator);
+    OP3(balanced_interval_row_direction_thread_blocking_operator);
+    OP3(balanced_interval_row_direction_warp_blocking_operator);
+    OP1(balanced_interval_row_direction_tblock_blocking_operator);
+    OP4(fixed_interval_nnz_direction_thread_blocking_operator);
+    OP4(fixed_interval_nnz_direction_warp_blocking_operator);
+    OP2(fixed_interval_nnz_direction_tblock_blocking_operator);
+    OP1(merge_path_tblock_operator);
+    OP1(merge_path_warp_operator);
+    OP1(merge_path_thread_operator);
+    fprintf(stderr, "ops mode: unknown operator %s\n", op.c_str());
+    exit(2);
+}
+
+static int run_ops(const string &spec)
+{
+    shared_ptr<code_generator> cg(new code_generator(g_set, 0));
+    shared_ptr<operator_executer> ex(new operator_executer());
+    stringstream ss(spec);
+    string item;
+    while (getline(ss, item, ';'))
+    {
+        if (item.empty()) continue;
+        stringstream is(item);
+        string name, tok;
+        getline(is, name, ',');
+        vector<long> a;
+        while (getline(is, tok, ',')) a.push_back(atol(tok.c_str()));
+        shared_ptr<basic_operator> o = ref_operator(name, cg, ex->get_operator_context(), a);
+        // the verdict of the operator's own rule on the history so far (the search uses it to prune chains)
+        cout << "valid::" << name << "::" << (o->is_valid_according_to_operator(ex->get_operator_context()) ? 1 : 0) << endl;
+        ex->add_and_run(o);
+        cout << o->convert_to_string() << endl;
+        vector<shared_ptr<transform_step_record_item>> rec = o->get_data_transform_sequence();
+        for (size_t i = 0; i < rec.size(); i++) cout << rec[i]->convert_to_string() << endl;
+    }
+    dump_all();
+    return 0;
+}
+
 int main(int argc, char **argv)
 {
     if (argc != 7)
@@ -99,6 +170,7 @@ int main(int argc, char **argv)
     g_dump_dir = argv[6];
     set_config("DENSE_MATRIX_SIZE", n); // token_test.cc:1630
     g_set = create_init_metadata_set_from_file(mtx, "");
+    if (family.compare(0, 4, "ops=") == 0) return run_ops(family.substr(4));
     if (family == "load")
     {
         dump_all();

@@ -61,6 +61,47 @@ def cases_for(mname):
     return out
 
 
+# operator sequences none of the seven chains reaches, run through the harness' "ops=" mode
+# (name, [(operator, args...), ...], N) -- arguments are the reference constructors' own, in declaration order
+OPS_CASES = [
+    ("mp_thread4", [("merge_path_thread_operator", 4)], 8),
+    ("mp_thread33", [("merge_path_thread_operator", 33)], 8),
+    ("mp_warp64", [("merge_path_warp_operator", 64)], 8),
+    ("mp_tblock256", [("merge_path_tblock_operator", 256)], 8),
+    ("sort_mp_thread7", [("sort_operator",), ("merge_path_thread_operator", 7)], 8),
+    ("mp_tblock1", [("merge_path_tblock_operator", 1)], 8),
+    # operators the factory already had, pinned here for the first time
+    ("bal_tblock300", [("balanced_interval_row_direction_tblock_blocking_operator", 300)], 8),
+    ("bal_warp64", [("balanced_interval_row_direction_warp_blocking_operator", 64, 0, 0)], 8),
+    ("bal_thread16", [("balanced_interval_row_direction_thread_blocking_operator", 16, 0, 0)], 8),
+    ("sort_bal_thread9", [("sort_operator",), ("balanced_interval_row_direction_thread_blocking_operator", 9, 0, 0)], 8),
+    ("col_thread8_pad", [("fixed_interval_col_direction_thread_blocking_operator", 8, 0, 0, 1, 0)], 8),
+    ("col_thread4_maxpad", [("fixed_interval_col_direction_thread_blocking_operator", 4, 0, 0, 0, 1)], 8),
+    ("nnz_thread32_pad", [("fixed_interval_nnz_direction_thread_blocking_operator", 32, 0, 0, 1)], 8),
+    ("nnz_thread5", [("fixed_interval_nnz_direction_thread_blocking_operator", 5, 0, 0, 0)], 8),
+    ("empty_pad", [("empty_row_pad_operator",)], 8),
+    ("tb16_w4_t1", [("fixed_interval_row_direction_tblock_blocking_operator", 16, 0),
+                    ("fixed_interval_row_direction_warp_blocking_operator", 4, 0, 0, 0),
+                    ("fixed_interval_row_direction_thread_blocking_operator", 1, 0, 0, 0, 0, 0, 0)], 8),
+    ("tb16_w4rel_t1rel", [("fixed_interval_row_direction_tblock_blocking_operator", 16, 0),
+                          ("fixed_interval_row_direction_warp_blocking_operator", 4, 1, 1, 0),
+                          ("fixed_interval_row_direction_thread_blocking_operator", 1, 1, 1, 0, 0, 0, 0)], 8),
+    ("tb32pad_w8pad", [("fixed_interval_row_direction_tblock_blocking_operator", 32, 1),
+                       ("fixed_interval_row_direction_warp_blocking_operator", 8, 0, 0, 1)], 8),
+    ("w2_t1_maxpad", [("fixed_interval_row_direction_warp_blocking_operator", 2, 0, 0, 0),
+                      ("fixed_interval_row_direction_thread_blocking_operator", 1, 0, 0, 0, 1, 0, 0)], 8),
+    ("t4_rowpad", [("fixed_interval_row_direction_thread_blocking_operator", 4, 0, 0, 1, 0, 0, 0)], 8),
+    ("tb8_colthread4", [("fixed_interval_row_direction_tblock_blocking_operator", 8, 0),
+                        ("fixed_interval_col_direction_thread_blocking_operator", 4, 0, 0, 1, 0)], 8),
+    ("tb8_colthread4_rel", [("fixed_interval_row_direction_tblock_blocking_operator", 8, 0),
+                            ("fixed_interval_col_direction_thread_blocking_operator", 4, 1, 1, 1, 0)], 8),
+]
+
+
+def ops_cases_for(mname):
+    return OPS_CASES if mname in ("tiny", "ragged") else OPS_CASES[:2] + OPS_CASES[6:10] if mname == "ig5like" else OPS_CASES[:2]
+
+
 def write_mtx(path, rows, cols, r, c):
     with open(path, "w") as f:
         f.write("%%MatrixMarket matrix coordinate real general\n")
@@ -93,8 +134,8 @@ def read_dump(dump_dir):
     return out, dtypes
 
 
-def run_case(scratch, mtx, fam, n, s, c):
-    dump = os.path.join(scratch, "dump_%s_%d_%d_%d" % (fam, n, s, c))
+def run_case(scratch, mtx, fam, n, s, c, tag=None):
+    dump = os.path.join(scratch, "dump_%s_%d_%d_%d" % (tag or fam, n, s, c))
     shutil.rmtree(dump, ignore_errors=True)
     p = subprocess.run([HARNESS, fam, mtx, str(n), str(s), str(c), dump], cwd=scratch,
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
@@ -117,12 +158,41 @@ def main():
     only = sys.argv[1:]
     scratch = make_scratch()
     summary = {}
+    ops_only = "--ops-only" in only
+    only = [x for x in only if not x.startswith("--")]
+    if ops_only or only:
+        summary = json.load(open(os.path.join(HERE, "SUMMARY.json")))
     for mname, kind, rows, cols, params, seed in MATRICES:
         if only and mname not in only:
             continue
         r, c = synth_matrix(kind, rows, cols, seed=seed, **params)
         mtx = os.path.join(scratch, mname + ".mtx")
         write_mtx(mtx, rows, cols, r, c)
+        for oname, ops, n in ops_cases_for(mname):
+            spec = "ops=" + ";".join(",".join(str(int(x)) if not isinstance(x, str) else x for x in op) for op in ops)
+            res, log = run_case(scratch, mtx, spec, n, 0, 0, tag=oname)
+            name = "%s__ops_%s" % (mname, oname)
+            if res is None:
+                # the reference asserted: keep the input and the assertion text, ours has to refuse the sequence too
+                why = [ln for ln in log.splitlines() if "Assertion" in ln or "padding rate" in ln]
+                print("ABORTED", name, why[-1][-160:] if why else log[-200:])
+                summary[name] = "reference aborted"
+                np.savez_compressed(os.path.join(HERE, name + ".npz"), __coo_row__=r.astype(np.int64), __coo_col__=c.astype(np.int64),
+                                    __shape__=np.array([rows, cols], dtype=np.int64),
+                                    __meta__=np.array(json.dumps(dict(ops=[list(op) for op in ops], N=n, aborted=[w[-300:] for w in why]))))
+                continue
+            payload = {k: v for k, v in res["arrs"].items()}
+            payload["__coo_row__"] = r.astype(np.int64)
+            payload["__coo_col__"] = c.astype(np.int64)
+            payload["__shape__"] = np.array([rows, cols], dtype=np.int64)
+            payload["__meta__"] = np.array(json.dumps(dict(
+                dtypes=res["dtypes"], ops=[list(op) for op in ops], N=n, steps=res["steps"],
+                matrix=dict(kind=kind, rows=rows, cols=cols, params=params, seed=seed))))
+            np.savez_compressed(os.path.join(HERE, name + ".npz"), **payload)
+            summary[name] = "%d arrays" % len(res["arrs"])
+            print(name, summary[name])
+        if ops_only:
+            continue
         for fam, n, s, co in cases_for(mname):
             res, log = run_case(scratch, mtx, fam, n, s, co)
             name = "%s__%s__N%d_S%d_C%d" % (mname, fam, n, s, co)
