@@ -41,7 +41,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=8, help="dense width N (8, 16 or 32)")
+    ap.add_argument("--n", "--dense-n", dest="n", type=int, default=8,
+                    help="dense width N (8 = the bench line; 16..256 run the tile kernel). Under torchrun spell it --dense-n (its parser claims --n)")
+    ap.add_argument("--density", type=float, default=0.30, help="c2: keep probability of the pruned weight (0.30 = C2, 0.10 = C3)")
     ap.add_argument("--kernel", default="auto", help="auto: the stream row kernel at N=8, the tcgen05 tile kernel from N=16 up")
     ap.add_argument("--copies", type=int, default=0, help="device copies of A to rotate over (0 = enough to exceed L2 3x)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -138,7 +140,7 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": "SpMM GFLOP/s (2*nnz*N/t)", "value": gf, "unit": "GFLOP/s", "n_gpus": args.gpus, "steps": steps,
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "pruned Llama-2-7B FFN weight 11008x4096, 70%% unstructured, N=%d (CPU: fp32)" % N, "nnz": int(len(r))},
+            "config": {"workload": "pruned Llama-2-7B FFN weight 11008x4096, %.0f%% unstructured, N=%d (CPU: fp32)" % (100 * (1 - DENSITY), N), "nnz": int(len(r))},
             "cpu_baseline": {"value": gf, "unit": "GFLOP/s", "cores": cores, "kind": kind,
                              "sample": "the whole 11008x4096 matrix, %d passes, all host threads over row chunks" % steps},
             "e2e": {"value": gf, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -232,7 +234,9 @@ def run_c4(args, rank, world, local):
 
 
 def main():
+    global DENSITY
     args = parse()
+    DENSITY = args.density
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -384,7 +388,7 @@ def main():
         "metric": "SpMM GFLOP/s (2*nnz*N/t)", "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 storage, f32 accumulate",
         "data": "synthetic",
-        "config": {"workload": "pruned Llama-2-7B FFN weight 11008x4096 per GPU, 70%% unstructured, N=%d, HALF, thread_total chain (sort, S=8 pad) on the B200 %s kernel" % (N, "row" if args.kernel == "b200_row_smem" else "tile (tcgen05)"),
+        "config": {"workload": "pruned Llama-2-7B FFN weight 11008x4096 per GPU, %.0f%% unstructured, N=%d, HALF, thread_total chain (sort, S=8 pad) on the B200 %s kernel" % (100 * (1 - DENSITY), N, "row" if args.kernel == "b200_row_smem" else "tile (tcgen05)"),
                    "rows_per_gpu": int(desc.rows), "cols": COLS, "nnz_per_gpu": int(desc.origin_nnz), "stored_nnz_per_gpu": int(desc.stored_nnz),
                    "kernel": plans[0].kernel_name, "l2": "steps rotate over %d device copies of A (%.0f MB > 126 MB L2)" % (copies, copies * bytes_a / 1e6),
                    "partition": "nnz-balanced row blocks (balanced_interval rule), B replicated, C rows disjoint, no collective",
