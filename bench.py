@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--n", "--dense-n", dest="n", type=int, default=8,
                     help="dense width N (8 = the bench line; 16..256 run the tile kernel). Under torchrun spell it --dense-n (its parser claims --n)")
     ap.add_argument("--density", type=float, default=0.30, help="c2: keep probability of the pruned weight (0.30 = C2, 0.10 = C3)")
-    ap.add_argument("--kernel", default="auto", help="auto: the stream row kernel at N=8, the tcgen05 tile kernel from N=16 up")
+    ap.add_argument("--kernel", default="auto", help="auto: the stream row kernel at N=8, the tcgen05 tile kernel from N=16 up; c4: auto = b200_nnz, reference = the chain's own family kernel")
     ap.add_argument("--copies", type=int, default=0, help="device copies of A to rotate over (0 = enough to exceed L2 3x)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="c2", choices=["c2", "c4"], help="c2: pruned FFN weight (the bench line); c4: power-law matrix, fp32, N=32, "
@@ -177,7 +177,8 @@ def run_c4(args, rank, world, local):
     host_pipeline_s = time.perf_counter() - t0
     eng = api.Engine(local)
     eng.upload_session(sess)
-    plan = eng.plan(sess, N)
+    c4_kernel = "b200_nnz" if args.kernel == "auto" and args.family in ("thread_bit_map", "warp_segment") else (None if args.kernel in ("auto", "reference") else args.kernel)
+    plan = eng.plan(sess, N, kernel=c4_kernel)
     plan.set_dense(B)
     stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local))
     # parity on the first rows of the block (the f64 oracle over 200 M non-zeros would take minutes; rows are independent)

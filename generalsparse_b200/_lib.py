@@ -26,7 +26,7 @@ SYMBOLS = [
 (GS_U8, GS_U16, GS_U32, GS_U64, GS_F32, GS_F64, GS_F16) = range(7)
 (GLOBAL_META, TBLOCK_META, WARP_META, THREAD_META) = range(4)
 FAMILIES = ["thread_total", "warp_total", "warp_bitmap", "thread_bit_map", "warp_segment", "block_total", "block_bitmap",
-            "b200_row_smem", "b200_tcgen05"]
+            "b200_row_smem", "b200_tcgen05", "b200_nnz"]
 FAMILY_ID = {n: i for i, n in enumerate(FAMILIES)}
 STATUS = {0: "GS_OK", 1: "GS_ERR_INVALID", 2: "GS_ERR_CUDA", 3: "GS_ERR_UNSUPPORTED", 4: "GS_ERR_NOT_FOUND",
           5: "GS_ERR_PADDING_RATE", 6: "GS_ERR_INTERNAL"}

@@ -87,4 +87,9 @@ void b200_tile_free(b200_tile_plan *plan);
 const char *b200_tile_kernel_name(const b200_tile_plan *plan);
 uint64_t b200_tile_bytes(const b200_tile_plan *plan, uint64_t rows, uint64_t cols);
 uint64_t b200_tile_pairs(const b200_tile_plan *plan);
+
+// kernels_nnz.cu: warp-per-run kernel over the nnz-direction bit-map chains (no plan-time state)
+bool b200_nnz_supported(const launch_params &p);
+cudaError_t b200_nnz_launch(const launch_params &p, cudaStream_t s);
+const char *b200_nnz_kernel_name(const launch_params &p);
 } // namespace gsd

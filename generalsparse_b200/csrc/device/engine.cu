@@ -276,6 +276,17 @@ static void select_kernel(gs_plan *p, int family)
         CUDA_TRY(e);
         break;
     }
+    case GS_FAMILY_B200_NNZ: {
+        require(a.t_first_row && a.t_first_nz && !a.t_nz_relative && a.t_bit_map && a.t_seg_ptr && a.t_seg_empty_flag && a.t_seg_empty_rows,
+                "THREAD first_row_indices/first_nz_indices/thread_bit_map/segment_ptr/segment_empty_flag/segment_empty_row_indices");
+        GS_REQUIRE(p->desc.vector_width >= 1 && p->desc.vector_width <= 64, "VECTOR_WIDTH must be 1..64 for the bit map families");
+        gsd::launch_params lp = p->lp;
+        lp.N = p->N;
+        if (!gsd::b200_nnz_supported(lp)) throw gs::Error("b200_nnz: needs N in {32,64,128} and an nnz-direction bit-map chain (thread_bit_map / warp_segment)");
+        add("THREAD_META", "first_row_indices"), add("THREAD_META", "first_nz_indices"), add("THREAD_META", "thread_bit_map");
+        add("THREAD_META", "segment_ptr"), add("THREAD_META", "segment_empty_flag"), add("THREAD_META", "segment_empty_row_indices");
+        break;
+    }
     default: throw gs::Error("kernel family not built: " + std::string(gs_family_name(family)));
     }
     if (p->desc.has_row_permutation && family != GS_FAMILY_B200_TCGEN05) add("GLOBAL_META", "original_nz_row_indices");
@@ -285,7 +296,8 @@ static void select_kernel(gs_plan *p, int family)
 
 static bool uses_atomics(int family)
 {
-    return family == GS_FAMILY_WARP_BITMAP || family == GS_FAMILY_TBLOCK_BITMAP || family == GS_FAMILY_THREAD_BITMAP || family == GS_FAMILY_WARP_SEGMENT;
+    return family == GS_FAMILY_WARP_BITMAP || family == GS_FAMILY_TBLOCK_BITMAP || family == GS_FAMILY_THREAD_BITMAP || family == GS_FAMILY_WARP_SEGMENT ||
+           family == GS_FAMILY_B200_NNZ;
 }
 
 static void enqueue(gs_plan *p)
@@ -304,6 +316,8 @@ static void enqueue(gs_plan *p)
         lp.pdl = p->ctx->row_chain && !no_pdl;
         CUDA_TRY(gsd::b200_tile_launch(p->tile_plan, lp, p->ctx->stream));
         p->ctx->row_chain = true;
+    } else if (p->kernel == GS_FAMILY_B200_NNZ) {
+        CUDA_TRY(gsd::b200_nnz_launch(lp, p->ctx->mem_stream()));
     } else {
         CUDA_TRY(gsd::launch_reference_family(p->kernel, lp, p->ctx->mem_stream()));
     }
@@ -583,6 +597,11 @@ const char *gs_plan_kernel_name(const gs_plan *p)
     if (!p) return "";
     if (p->kernel == GS_FAMILY_B200_ROW_SMEM) return gsd::b200_row_kernel_name(p->row_plan);
     if (p->kernel == GS_FAMILY_B200_TCGEN05) return gsd::b200_tile_kernel_name(p->tile_plan);
+    if (p->kernel == GS_FAMILY_B200_NNZ) {
+        gsd::launch_params lp = p->lp;
+        lp.N = p->N;
+        return gsd::b200_nnz_kernel_name(lp);
+    }
     return gsd::reference_family_kernel_name(p->kernel);
 }
 

@@ -1,0 +1,202 @@
+// B200 nnz kernel (GS_FAMILY_B200_NNZ): the nnz-direction chains (thread_bit_map / warp_segment:
+// fixed 32 non-zeros per BMT, row-start bit maps) for wide dense operands, N a multiple of 32.
+//
+// What it replaces: thread_bit_map_reduce_to_two_register_token.cc:819-1616 gives every thread one
+// BMT and one dense column group, so the col/val loads of a warp are strided by the BMT size and every
+// row end is an atomicAdd.  Here the warp is the unit: it owns a RUN of consecutive BMTs, lane l owns
+// dense columns l, l+32, ... (a row of B is one or more whole 128-byte lines per warp request), and
+//   * a BMT's 32 column ids / values are one coalesced 128-byte load each, handed round by shuffles;
+//   * the row-start bit map is warp-uniform, so the flush branch never diverges;
+//   * a row that starts and ends inside the run is stored with plain coalesced stores; only the first
+//     and the last partial row of a run go through red.global.add (C is zeroed per launch like for the
+//     reference's bit-map families, which also covers empty rows);
+//   * sixteen gathers of B (N=32; eight per column slice above) are in flight per warp before the first
+//     FMA of a group; the next BMT's col/val lines are requested before the current BMT is multiplied.
+// Bound: the gathers of B (stored nnz x N x sizeof(value) bytes through L2, hot columns served by
+// L1/L2), not the A stream; see DESIGN.md section 4.4.
+#include "common.cuh"
+
+#include <cstdio>
+#include <cstdlib>
+
+#include "../../../include/gsparse_b200.h"
+
+namespace gsd {
+
+namespace {
+
+constexpr int RUN = 16;     // BMTs per warp (default; at most 31: one metadata lane per BMT plus the end offset)
+constexpr int WARPS = 8;    // warps per CTA
+
+__device__ __forceinline__ uint32_t out_row(const dev_arrays &a, uint32_t row) { return a.perm ? a.perm[row] + a.begin_row : row + a.begin_row; }
+
+template <typename ValT, int NV>
+__device__ __forceinline__ void flush_row(ValT *C, int N, uint32_t row, int lane, float (&acc)[NV], bool atomic)
+{
+    ValT *dst = C + (size_t)row * N + lane;
+#pragma unroll
+    for (int v = 0; v < NV; v++) {
+        if (atomic) {
+            if (acc[v] != 0.0f) atomic_add_out(dst, (size_t)(32 * v), acc[v]);
+        } else {
+            dst[32 * v] = from_f32<ValT>(acc[v]);
+        }
+        acc[v] = 0.0f;
+    }
+}
+
+template <typename ColT, typename ValT, int NV, int MINB, int GROUP> __global__ void __launch_bounds__(WARPS * 32, MINB) k_b200_nnz(launch_params p, const uint32_t run)
+{
+    const dev_arrays &a = p.a;
+    const int lane = threadIdx.x & 31;
+    const uint32_t w = blockIdx.x * WARPS + (threadIdx.x >> 5);
+    const uint32_t b0 = w * run;
+    if (b0 >= a.n_t) return;
+    const uint32_t nb = min(run, a.n_t - b0);
+    const ColT *col = (const ColT *)a.col;
+    const ValT *val = (const ValT *)a.val;
+    const ValT *B = (const ValT *)p.B;
+    ValT *C = (ValT *)p.C;
+    const int N = p.N;
+
+    // the run's metadata: one BMT per lane, handed round by shuffles afterwards
+    uint32_t m_fn = 0, m_row = 0, m_lo = 0, m_hi = 0, m_gap = 0;
+    if ((uint32_t)lane <= nb) m_fn = a.t_first_nz[b0 + lane];
+    if ((uint32_t)lane < nb) {
+        uint64_t map = a.t_bit_map[b0 + lane];
+        m_lo = (uint32_t)map, m_hi = (uint32_t)(map >> 32);
+        m_row = a.t_first_row[b0 + lane];
+        uint32_t b = b0 + lane;
+        m_gap = (uint32_t)((a.t_seg_empty_flag[b / p.vector_width] >> (b % p.vector_width)) & 1ull);
+    }
+
+    float acc[NV];
+#pragma unroll
+    for (int v = 0; v < NV; v++) acc[v] = 0.0f;
+    uint32_t row = __shfl_sync(0xffffffffu, m_row, 0);
+    bool edge = true; // the open segment may have begun before this run: it goes to C through atomics
+
+    uint32_t lo = __shfl_sync(0xffffffffu, m_fn, 0), hi = __shfl_sync(0xffffffffu, m_fn, 1);
+    uint32_t c_cur = 0;
+    float v_cur = 0.0f;
+    if (lo + lane < hi) c_cur = col[lo + lane], v_cur = to_f32(val[lo + lane]);
+
+    for (uint32_t i = 0; i < nb; i++) {
+        // request the next BMT's first 32 ids / values before multiplying this one
+        uint32_t lo_n = hi, hi_n = __shfl_sync(0xffffffffu, m_fn, (i + 2) & 31);
+        uint32_t c_nxt = 0;
+        float v_nxt = 0.0f;
+        if (i + 1 < nb && lo_n + lane < hi_n) c_nxt = col[lo_n + lane], v_nxt = to_f32(val[lo_n + lane]);
+
+        const uint32_t map_lo = __shfl_sync(0xffffffffu, m_lo, i), map_hi = __shfl_sync(0xffffffffu, m_hi, i);
+        const uint32_t frow = __shfl_sync(0xffffffffu, m_row, i);
+        const bool gaps = __shfl_sync(0xffffffffu, m_gap, i) != 0;
+        if (frow != row) { // the previous BMT ended its row exactly at the boundary
+            flush_row<ValT, NV>(C, N, out_row(a, row), lane, acc, edge);
+            edge = false;
+            row = frow;
+        }
+        uint32_t seg = 0;
+        const uint32_t cnt = hi - lo; // <= 64 (u64 bit map)
+        if (cnt == 32) { // what fixed_interval_nnz_direction_thread_blocking(32) + nnz padding produce: fully unrolled
+#pragma unroll
+            for (int k0 = 0; k0 < 32; k0 += GROUP) {
+                float x[GROUP][NV];
+#pragma unroll
+                for (int j = 0; j < GROUP; j++) {
+                    uint32_t c = __shfl_sync(0xffffffffu, c_cur, k0 + j);
+                    const ValT *src = B + (size_t)c * N + lane;
+#pragma unroll
+                    for (int v = 0; v < NV; v++) x[j][v] = to_f32(__ldg(src + 32 * v));
+                }
+#pragma unroll
+                for (int j = 0; j < GROUP; j++) {
+                    const int k = k0 + j;
+                    float vv = __shfl_sync(0xffffffffu, v_cur, k);
+                    if (k > 0 && ((map_lo >> k) & 1u)) {
+                        flush_row<ValT, NV>(C, N, out_row(a, row), lane, acc, edge);
+                        edge = false;
+                        seg++;
+                        row = gaps ? frow + a.t_seg_empty_rows[a.t_seg_ptr[b0 + i] + seg] : frow + seg;
+                    }
+#pragma unroll
+                    for (int v = 0; v < NV; v++) acc[v] = fmaf(vv, x[j][v], acc[v]);
+                }
+            }
+        } else { // ragged BMTs (the last one of a matrix, or chains with another interval): one non-zero at a time
+            const uint64_t map = ((uint64_t)map_hi << 32) | map_lo;
+            for (uint32_t k = 0; k < cnt; k++) {
+                if (k == 32) { // BMTs wider than 32 non-zeros: the second half is loaded in place
+                    c_cur = 0, v_cur = 0.0f;
+                    if (lo + 32 + lane < hi) c_cur = col[lo + 32 + lane], v_cur = to_f32(val[lo + 32 + lane]);
+                }
+                uint32_t c = __shfl_sync(0xffffffffu, c_cur, k & 31);
+                float vv = __shfl_sync(0xffffffffu, v_cur, k & 31);
+                const ValT *src = B + (size_t)c * N + lane;
+                if (k > 0 && ((map >> k) & 1ull)) {
+                    flush_row<ValT, NV>(C, N, out_row(a, row), lane, acc, edge);
+                    edge = false;
+                    seg++;
+                    row = gaps ? frow + a.t_seg_empty_rows[a.t_seg_ptr[b0 + i] + seg] : frow + seg;
+                }
+#pragma unroll
+                for (int v = 0; v < NV; v++) acc[v] = fmaf(vv, to_f32(__ldg(src + 32 * v)), acc[v]);
+            }
+        }
+        c_cur = c_nxt, v_cur = v_nxt, lo = lo_n, hi = hi_n;
+    }
+    // the last open segment may continue in the next run
+    flush_row<ValT, NV>(C, N, out_row(a, row), lane, acc, true);
+}
+
+unsigned nnz_run()
+{
+    static const int r = getenv("GS_NNZ_RUN") ? atoi(getenv("GS_NNZ_RUN")) : RUN;
+    return (unsigned)(r < 1 ? 1 : r > 31 ? 31 : r);
+}
+
+template <typename ColT, typename ValT> cudaError_t launch_nv(const launch_params &p, cudaStream_t s)
+{
+    static const int occ = getenv("GS_NNZ_OCC") ? atoi(getenv("GS_NNZ_OCC")) : 0;     // timing experiments (N=32 only)
+    static const int grp = getenv("GS_NNZ_GROUP") ? atoi(getenv("GS_NNZ_GROUP")) : 0;
+    const unsigned run = nnz_run();
+    unsigned warps = (p.a.n_t + run - 1) / run;
+    unsigned grid = (warps + WARPS - 1) / WARPS;
+    if (grid == 0) return cudaSuccess;
+    switch (p.N / 32) {
+    case 1:
+        if (grp == 8) k_b200_nnz<ColT, ValT, 1, 5, 8><<<grid, WARPS * 32, 0, s>>>(p, run);
+        else if (occ == 4) k_b200_nnz<ColT, ValT, 1, 4, 16><<<grid, WARPS * 32, 0, s>>>(p, run);
+        else k_b200_nnz<ColT, ValT, 1, 5, 16><<<grid, WARPS * 32, 0, s>>>(p, run);
+        break;
+    case 2: k_b200_nnz<ColT, ValT, 2, 3, 8><<<grid, WARPS * 32, 0, s>>>(p, run); break;
+    case 4: k_b200_nnz<ColT, ValT, 4, 2, 8><<<grid, WARPS * 32, 0, s>>>(p, run); break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+} // namespace
+
+bool b200_nnz_supported(const launch_params &p)
+{
+    int nv = p.N / 32;
+    return p.N % 32 == 0 && (nv == 1 || nv == 2 || nv == 4);
+}
+
+cudaError_t b200_nnz_launch(const launch_params &p, cudaStream_t s)
+{
+    if (!b200_nnz_supported(p)) return cudaErrorInvalidValue;
+    if (p.a.col_is_u16) return p.a.val_is_f16 ? launch_nv<uint16_t, __half>(p, s) : launch_nv<uint16_t, float>(p, s);
+    return p.a.val_is_f16 ? launch_nv<uint32_t, __half>(p, s) : launch_nv<uint32_t, float>(p, s);
+}
+
+const char *b200_nnz_kernel_name(const launch_params &p)
+{
+    static thread_local char name[96];
+    snprintf(name, sizeof name, "k_b200_nnz<N%d,%s,%s,run %d BMTs/warp,%d gathers in flight>", p.N, p.a.col_is_u16 ? "u16" : "u32",
+             p.a.val_is_f16 ? "f16" : "f32", (int)nnz_run(), p.N == 32 ? 16 : 8);
+    return name;
+}
+
+} // namespace gsd

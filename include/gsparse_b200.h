@@ -50,7 +50,8 @@ typedef enum gs_family {
     GS_FAMILY_TBLOCK_BITMAP = 6, /* tblock_bit_map_reduce_token.cc:83-189 */
     GS_FAMILY_B200_ROW_SMEM = 7, /* persistent row kernel, dense B panel staged in shared memory by bulk copy */
     GS_FAMILY_B200_TCGEN05 = 8,  /* sparse-tile decompress to shared memory + tcgen05.mma with TMEM accumulators */
-    GS_FAMILY_COUNT = 9
+    GS_FAMILY_B200_NNZ = 9,      /* warp-per-run kernel for the nnz-direction bit-map chains (thread_bit_map / warp_segment), N % 32 == 0 */
+    GS_FAMILY_COUNT = 10
 } gs_family;
 
 const char *gs_last_error(void);

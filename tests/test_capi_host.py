@@ -43,7 +43,7 @@ def test_header_compiles_as_plain_c(tmp_path):
 def test_version_and_family_names(built_lib):
     L = built_lib
     assert L.gs_version().decode()
-    names = [L.gs_family_name(i).decode() for i in range(9)]
+    names = [L.gs_family_name(i).decode() for i in range(len(_lib.FAMILIES))]
     assert names == _lib.FAMILIES
 
 

@@ -240,3 +240,46 @@ def test_b200_tile_overlapped_launches_keep_order(engine):
         last = (n_launch - 1) % 2
         C = plan.output()
         _check(C, refs[last], absrow[last] * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+
+
+@pytest.mark.parametrize("N", [32, 64, 128])
+@pytest.mark.parametrize("half", [False, True], ids=["fp32", "half"])
+@pytest.mark.parametrize("chain", ["thread_bit_map", "warp_segment"])
+def test_b200_nnz_kernel(engine, N, half, chain):
+    """the B200 nnz kernel (a warp per run of 32-nnz BMTs) on the nnz-direction bit-map chains: exact in reference mode,
+    in tolerance on random values; power-law rows (rows far longer than a run, atomics), ragged rows with empty rows
+    (segment_empty_flag / segment_empty_row_indices), a matrix smaller than one run"""
+    from generalsparse_b200 import synth
+    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    mats = [("powerlaw", 3000, 3000, dict(avg_deg=20.0, alpha=2.1)), ("ragged", 700, 450, dict(mean_len=9.0, empty_frac=0.3)),
+            ("uniform", 40, 30, dict(density=0.1)), ("uniform", 344, 512, dict(density=0.3))]
+    for i, (kind, nrows, cols, kw) in enumerate(mats):
+        rr, cc = _matrix(kind, nrows, cols, seed=81 + i, **kw)
+        indptr = csr_from_coo(nrows, rr)
+        B1 = np.ones((cols, N), dtype=np.float32)
+        C, plan = _run(engine, chain, nrows, cols, rr, cc, None, B1, N, 1, 1, half=half, kernel="b200_nnz")
+        assert "k_b200_nnz" in plan.kernel_name
+        ref = oracle_spmm_f32(nrows, N, indptr, cc, np.ones(len(rr), np.float32), B1)
+        if not half or ref.max() <= 2048:  # fp16 C holds integers exactly up to 2048
+            assert np.array_equal(C.astype(np.float32), ref), plan.kernel_name
+        vals = synth.synth_values(len(rr), seed=5)
+        B = synth.synth_dense(cols, N, seed=5)
+        if half:
+            vals = vals.astype(np.float16).astype(np.float32)
+            B = B.astype(np.float16).astype(np.float32)
+        C, plan = _run(engine, chain, nrows, cols, rr, cc, vals, B, N, 1, 1, half=half, kernel="b200_nnz")
+        ref = oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B)
+        absrow = oracle_spmm_absrow(nrows, N, indptr, cc, vals, B)
+        floor = 2.0 ** -25 if half else 0.0  # half the spacing of fp16 subnormals when C is stored in fp16
+        _check(C, ref, absrow * (1.0 if half else 1e-1), 1e-2 if half else 1e-5, abs_floor=floor)
+        plan.run(3)  # C is zeroed per launch: repeated launches do not accumulate
+        _check(plan.output(), ref, absrow * (1.0 if half else 1e-1), 1e-2 if half else 1e-5, abs_floor=floor)
+
+
+def test_b200_nnz_rejects_narrow_dense(engine):
+    from generalsparse_b200 import api
+    r, c = _matrix("uniform", 64, 48, seed=1, density=0.085)
+    s = api.Session(api.MetaDataSet.from_coo(64, 48, r, c)).run_family("thread_bit_map", 8, 1, 1)
+    engine.upload_session(s)
+    with pytest.raises(api.GsError):
+        engine.plan(s, 8, kernel="b200_nnz")
