@@ -45,6 +45,8 @@ def parse():
                     help="dense width N (8 = the bench line; 16..256 run the tile kernel). Under torchrun spell it --dense-n (its parser claims --n)")
     ap.add_argument("--density", type=float, default=0.30, help="c2: keep probability of the pruned weight (0.30 = C2, 0.10 = C3)")
     ap.add_argument("--kernel", default="auto", help="auto: the stream row kernel at N=8, the tcgen05 tile kernel from N=16 up; c4: auto = b200_nnz, reference = the chain's own family kernel")
+    ap.add_argument("--pattern", default="unstructured", choices=["unstructured", "nm24"],
+                    help="c2: Bernoulli(density) mask, or exactly 2 of every 4 consecutive columns kept (C3's 2:4 half; runs b200_sp24 under --kernel auto)")
     ap.add_argument("--copies", type=int, default=0, help="device copies of A to rotate over (0 = enough to exceed L2 3x)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="c2", choices=["c2", "c4"], help="c2: pruned FFN weight (the bench line); c4: power-law matrix, fp32, N=32, "
@@ -70,9 +72,15 @@ def traffic_bytes(N, half, world, args):
     return json.load(open(p)).get("C2_N8_half_thread_total_S8", {}).get("bytes")
 
 
+PATTERN = "unstructured"
+
+
 def make_weight(seed):
     from generalsparse_b200 import synth
-    r, c = synth.synth_matrix("uniform", ROWS, COLS, seed=seed, density=DENSITY)
+    if PATTERN == "nm24":
+        r, c = synth.synth_matrix("nm24", ROWS, COLS, seed=seed)
+    else:
+        r, c = synth.synth_matrix("uniform", ROWS, COLS, seed=seed, density=DENSITY)
     v = synth.synth_values(len(r), seed=seed).astype(np.float16).astype(np.float32)
     return r, c, v
 
@@ -235,9 +243,9 @@ def run_c4(args, rank, world, local):
 
 
 def main():
-    global DENSITY
+    global DENSITY, PATTERN
     args = parse()
-    DENSITY = args.density
+    DENSITY, PATTERN = args.density, args.pattern
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -255,7 +263,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     N, half = args.n, True
     if args.kernel == "auto":
-        args.kernel = "b200_row_smem" if N < 16 else "b200_tcgen05"
+        args.kernel = "b200_sp24" if args.pattern == "nm24" else "b200_row_smem" if N < 16 else "b200_tcgen05"
     hbm_peak, peak_src = peaks()
 
     # ---- the global matrix: `world` FFN-sized blocks stacked; this rank's nnz-balanced row block ------------------------
@@ -280,7 +288,7 @@ def main():
     host_pipeline_s = time.perf_counter() - t_host0
     eng = api.Engine(local)
     desc = sess.plan_desc()
-    bytes_a = desc.stored_nnz * 4
+    bytes_a = desc.stored_nnz * 4 if args.kernel != "b200_sp24" else int(desc.rows * COLS * 1.125)
     copies = args.copies or max(2, int(3 * 126e6 / bytes_a) + 1)
     plans = []
     B_host = torch.empty((COLS, N), dtype=torch.float16).pin_memory()
@@ -389,7 +397,9 @@ def main():
         "metric": "SpMM GFLOP/s (2*nnz*N/t)", "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 storage, f32 accumulate",
         "data": "synthetic",
-        "config": {"workload": "pruned Llama-2-7B FFN weight 11008x4096 per GPU, %.0f%% unstructured, N=%d, HALF, thread_total chain (sort, S=8 pad) on the B200 %s kernel" % (100 * (1 - DENSITY), N, "row" if args.kernel == "b200_row_smem" else "tile (tcgen05)"),
+        "config": {"workload": "pruned Llama-2-7B FFN weight 11008x4096 per GPU, %s, N=%d, HALF, thread_total chain (sort, S=8 pad) on the B200 %s kernel" % (
+                       "2:4 structured" if args.pattern == "nm24" else "%.0f%% unstructured" % (100 * (1 - DENSITY)), N,
+                       {"b200_row_smem": "row", "b200_tcgen05": "tile (tcgen05)", "b200_sp24": "2:4 (tcgen05.mma.sp)"}.get(args.kernel, args.kernel)),
                    "rows_per_gpu": int(desc.rows), "cols": COLS, "nnz_per_gpu": int(desc.origin_nnz), "stored_nnz_per_gpu": int(desc.stored_nnz),
                    "kernel": plans[0].kernel_name, "l2": "steps rotate over %d device copies of A (%.0f MB > 126 MB L2)" % (copies, copies * bytes_a / 1e6),
                    "partition": "nnz-balanced row blocks (balanced_interval rule), B replicated, C rows disjoint, no collective",

@@ -263,6 +263,12 @@ class Plan:
     def launch_count(self):
         return lib().gs_plan_launch_count(self._h)
 
+    def sp24_probe(self):
+        """the 4 metadata columns of the first tile as tensor memory holds them (plan created under GS_SP24_PROBE=1)"""
+        out = np.empty((128, 4), dtype=np.uint32)
+        check(lib().gs_plan_sp24_probe(self._h, _ptr(out)))
+        return out
+
     @property
     def kernel_name(self):
         return lib().gs_plan_kernel_name(self._h).decode()

@@ -2,6 +2,7 @@
 // Pure C++; nothing here touches CUDA, so these calls work on a box without a GPU.
 #include "capi_internal.hpp"
 #include "host/tile_format.hpp"
+#include "host/sp24_format.hpp"
 
 #include <algorithm>
 
@@ -72,7 +73,7 @@ const char *gs_version(void) { return "gsparse_b200 0.1 (sm_100a)"; }
 const char *gs_family_name(int f)
 {
     static const char *n[] = {"thread_total", "warp_total", "warp_bitmap", "thread_bit_map", "warp_segment",
-                              "block_total", "block_bitmap", "b200_row_smem", "b200_tcgen05", "b200_nnz"};
+                              "block_total", "block_bitmap", "b200_row_smem", "b200_tcgen05", "b200_nnz", "b200_sp24"};
     return (f >= 0 && f < GS_FAMILY_COUNT) ? n[f] : "unknown";
 }
 
@@ -349,6 +350,23 @@ gs_status gsh_tile_stream_roundtrip(const uint32_t *rowptr, const uint32_t *col,
         }
     }
     stats[0] = ts.off.size(), stats[1] = ts.nnz, stats[2] = ts.tile_ptr.size() - 1, stats[3] = n_stores, stats[4] = wavefronts;
+    GS_API_END
+}
+
+gs_status gsh_sp24_roundtrip(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val, uint32_t n_rows, uint32_t n_cols, uint16_t *dense_out, uint64_t *stats)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(rowptr && col && val && dense_out && stats && n_rows > 0 && n_cols > 0, "bad argument");
+    sp24_image im;
+    try {
+        build_sp24_image(rowptr, col, val, n_rows, n_cols, im);
+    } catch (const std::exception &e) {
+        throw gs::Error(e.what());
+    }
+    std::vector<uint16_t> dense;
+    expand_sp24_image(im, dense);
+    std::copy(dense.begin(), dense.end(), dense_out);
+    stats[0] = im.bytes.size(), stats[1] = im.nnz, stats[2] = im.rem_col.size(), stats[3] = (uint64_t)im.n_panels * im.k_tiles;
     GS_API_END
 }
 

@@ -88,6 +88,16 @@ const char *b200_tile_kernel_name(const b200_tile_plan *plan);
 uint64_t b200_tile_bytes(const b200_tile_plan *plan, uint64_t rows, uint64_t cols);
 uint64_t b200_tile_pairs(const b200_tile_plan *plan);
 
+struct b200_sp24_plan; // opaque, kernels_sp24.cu
+cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_remainder, b200_sp24_plan **out, cudaStream_t s);
+cudaError_t b200_sp24_launch(b200_sp24_plan *plan, const launch_params &p, cudaStream_t s);
+void b200_sp24_free(b200_sp24_plan *plan);
+const char *b200_sp24_kernel_name(const b200_sp24_plan *plan);
+uint64_t b200_sp24_bytes(const b200_sp24_plan *plan, uint64_t rows, uint64_t cols);
+uint64_t b200_sp24_remainder(const b200_sp24_plan *plan);
+int b200_sp24_launches(const b200_sp24_plan *plan);
+cudaError_t b200_sp24_probe(const b200_sp24_plan *plan, uint32_t *out512);
+
 // kernels_nnz.cu: warp-per-run kernel over the nnz-direction bit-map chains (no plan-time state)
 bool b200_nnz_supported(const launch_params &p);
 cudaError_t b200_nnz_launch(const launch_params &p, cudaStream_t s);

@@ -56,6 +56,7 @@ struct gs_plan {
     gsd::launch_params lp;
     gsd::b200_row_plan *row_plan = nullptr;
     gsd::b200_tile_plan *tile_plan = nullptr;
+    gsd::b200_sp24_plan *sp24_plan = nullptr;
     void *B_dev = nullptr;  // owned
     const void *B_use = nullptr;
     void *C_dev = nullptr;
@@ -276,6 +277,14 @@ static void select_kernel(gs_plan *p, int family)
         CUDA_TRY(e);
         break;
     }
+    case GS_FAMILY_B200_SP24: {
+        if (p->sp24_plan) gsd::b200_sp24_free(p->sp24_plan), p->sp24_plan = nullptr;
+        GS_REQUIRE(p->half, "b200_sp24: the sparse tensor-core path multiplies fp16 operands (HALF); fp32 values stay on the gather kernels");
+        cudaError_t e = gsd::b200_sp24_prepare(p->lp, ctx->sm_count, true, &p->sp24_plan, ctx->stream);
+        if (e == cudaErrorInvalidValue) throw gs::Error("b200_sp24: needs N in {16,32,64,128,256}, HALF values and a row-direction chain with row block 1");
+        CUDA_TRY(e);
+        break;
+    }
     case GS_FAMILY_B200_NNZ: {
         require(a.t_first_row && a.t_first_nz && !a.t_nz_relative && a.t_bit_map && a.t_seg_ptr && a.t_seg_empty_flag && a.t_seg_empty_rows,
                 "THREAD first_row_indices/first_nz_indices/thread_bit_map/segment_ptr/segment_empty_flag/segment_empty_row_indices");
@@ -289,7 +298,7 @@ static void select_kernel(gs_plan *p, int family)
     }
     default: throw gs::Error("kernel family not built: " + std::string(gs_family_name(family)));
     }
-    if (p->desc.has_row_permutation && family != GS_FAMILY_B200_TCGEN05) add("GLOBAL_META", "original_nz_row_indices");
+    if (p->desc.has_row_permutation && family != GS_FAMILY_B200_TCGEN05 && family != GS_FAMILY_B200_SP24) add("GLOBAL_META", "original_nz_row_indices");
     p->offset_bytes = ob;
     p->kernel = family;
 }
@@ -315,6 +324,11 @@ static void enqueue(gs_plan *p)
         static const bool no_pdl = getenv("GS_NO_PDL") != nullptr;
         lp.pdl = p->ctx->row_chain && !no_pdl;
         CUDA_TRY(gsd::b200_tile_launch(p->tile_plan, lp, p->ctx->stream));
+        p->ctx->row_chain = true;
+    } else if (p->kernel == GS_FAMILY_B200_SP24) {
+        static const bool no_pdl = getenv("GS_NO_PDL") != nullptr;
+        lp.pdl = p->ctx->row_chain && !no_pdl;
+        CUDA_TRY(gsd::b200_sp24_launch(p->sp24_plan, lp, p->ctx->stream));
         p->ctx->row_chain = true;
     } else if (p->kernel == GS_FAMILY_B200_NNZ) {
         CUDA_TRY(gsd::b200_nnz_launch(lp, p->ctx->mem_stream()));
@@ -433,6 +447,7 @@ void gs_plan_destroy(gs_plan *p)
     cudaSetDevice(p->ctx->device);
     if (p->row_plan) gsd::b200_row_free(p->row_plan);
     if (p->tile_plan) gsd::b200_tile_free(p->tile_plan);
+    if (p->sp24_plan) gsd::b200_sp24_free(p->sp24_plan);
     if (p->B_dev) cudaFree(p->B_dev);
     if (p->C_dev) cudaFree(p->C_dev);
     if (p->ev0) cudaEventDestroy(p->ev0);
@@ -586,17 +601,29 @@ uint64_t gs_plan_algorithmic_bytes(const gs_plan *p)
     if (!p) return 0;
     // nnz_stored*(idx+val) + offset arrays + K*N*sizeof(B) + M*N*sizeof(C) (+ permutation)
     if (p->kernel == GS_FAMILY_B200_TCGEN05) return gsd::b200_tile_bytes(p->tile_plan, p->desc.rows, p->desc.cols);
+    if (p->kernel == GS_FAMILY_B200_SP24) return gsd::b200_sp24_bytes(p->sp24_plan, p->desc.rows, p->desc.cols);
     uint64_t idx = p->lp.a.col_is_u16 ? 2 : 4;
     return p->lp.a.nnz * (idx + p->esz()) + p->offset_bytes + (uint64_t)p->desc.cols * p->N * p->esz() + (uint64_t)p->desc.rows * p->N * p->esz();
 }
 
-int gs_plan_launch_count(const gs_plan *p) { return p ? 1 : 0; }
+int gs_plan_launch_count(const gs_plan *p) { return !p ? 0 : p->kernel == GS_FAMILY_B200_SP24 ? gsd::b200_sp24_launches(p->sp24_plan) : 1; }
+
+gs_status gs_plan_sp24_probe(const gs_plan *p, uint32_t *out512)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p && out512 && p->kernel == GS_FAMILY_B200_SP24 && p->sp24_plan, "not a b200_sp24 plan");
+    CUDA_TRY(cudaSetDevice(p->ctx->device));
+    CUDA_TRY(cudaStreamSynchronize(p->ctx->stream));
+    if (gsd::b200_sp24_probe(p->sp24_plan, out512) != cudaSuccess) throw gs::Error("b200_sp24: the plan was not created with GS_SP24_PROBE=1");
+    GS_API_END
+}
 
 const char *gs_plan_kernel_name(const gs_plan *p)
 {
     if (!p) return "";
     if (p->kernel == GS_FAMILY_B200_ROW_SMEM) return gsd::b200_row_kernel_name(p->row_plan);
     if (p->kernel == GS_FAMILY_B200_TCGEN05) return gsd::b200_tile_kernel_name(p->tile_plan);
+    if (p->kernel == GS_FAMILY_B200_SP24) return gsd::b200_sp24_kernel_name(p->sp24_plan);
     if (p->kernel == GS_FAMILY_B200_NNZ) {
         gsd::launch_params lp = p->lp;
         lp.N = p->N;

@@ -1,0 +1,310 @@
+// Host side of the B200 2:4 kernel (GS_FAMILY_B200_SP24): builds the 2:4 image of a row-direction chain once per plan
+// (host/sp24_format.hpp), owns the device copies, the stream-K workspace and the launch.  Device code: b200_sp24.cuh.
+#include "b200_sp24.cuh"
+#include "../host/sp24_format.hpp"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+namespace gsd {
+
+struct b200_sp24_plan {
+    unsigned char *img = nullptr;
+    uint32_t *out_row = nullptr, *flags = nullptr; // flags: grid ready + grid slot_free + n_panels panel_seq + rem_ctas rem_seq
+    float *ws = nullptr, *c_add = nullptr;         // c_add: two buffers (launch parity) of n_panels * 128 x N fp32, when there is a remainder
+    uint32_t *rem_rowptr = nullptr, *rem_col = nullptr;
+    uint16_t *rem_val = nullptr;
+    uint32_t n_tiles = 0, k_tiles = 0, n_panels = 0, grid = 0, seq = 0, n_rows = 0;
+    uint64_t nnz = 0, rem_nnz = 0;
+    size_t smem = 0;
+    const void *fn = nullptr, *rem_fn = nullptr;
+    int N = 0;
+    char name[128] = {0};
+    CUtensorMap b_map;              // the dense matrix as TMA boxes of 128 k rows x one swizzle atom of columns
+    const void *b_mapped = nullptr; // the device pointer b_map was encoded for
+    uint32_t K = 0;
+    uint32_t *dbg = nullptr; // GS_SP24_PROBE: the metadata columns of CTA 0's first tile as tensor memory holds them
+};
+
+namespace sp24 {
+
+constexpr int REM_THREADS = 256, REM_ROWS = 32; // a remainder CTA covers 32 rows = the rows of one epilogue warp of the 2:4 kernel
+
+struct rem_args {
+    const uint32_t *rowptr, *col;
+    const uint16_t *val;
+    const void *B;
+    float *c_add;              // this launch's buffer
+    uint32_t *rem_seq;         // per remainder CTA: launch number whose product sits in c_add
+    const uint32_t *panel_seq; // per panel: launch number that last wrote the panel's rows of C (the buffer's reader two launches back is done)
+    uint32_t n_rows, seq;
+};
+
+// Product of the remainder (what the 2:4 pattern could not hold: 7.7 % of the non-zeros of a 70 %-sparse unstructured
+// matrix, nothing for a 2:4-pruned one) with B, fp32, one warp per row: a group of LPR = N/8 lanes gathers one row of
+// B with 16-byte loads, the 32/LPR groups take the row's non-zeros in turn, a butterfly adds the groups.
+template <int N> __global__ void __launch_bounds__(REM_THREADS) k_b200_sp24_rem(rem_args a)
+{
+    constexpr int LPR = N / 8, GROUPS = 32 / LPR, RPW = REM_ROWS / (REM_THREADS / 32);
+    static_assert(LPR >= 1 && LPR <= 32, "dense width");
+    row::pdl_launch_dependents();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane / LPR, sub = lane % LPR;
+    const uint32_t panel = blockIdx.x / (128 / REM_ROWS);
+    if (threadIdx.x == 0 && a.seq >= 2)
+        while ((int32_t)(tile::ld_acquire(a.panel_seq + panel) - (a.seq - 2)) < 0) __nanosleep(32);
+    __syncthreads();
+    const __half *B = (const __half *)a.B;
+#pragma unroll 1
+    for (int i = 0; i < RPW; i++) {
+        const uint32_t r = blockIdx.x * REM_ROWS + warp * RPW + i;
+        if (r >= a.n_rows) break;
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        const uint32_t e0 = a.rowptr[r], e1 = a.rowptr[r + 1];
+#pragma unroll 4
+        for (uint32_t e = e0 + grp; e < e1; e += GROUPS) {
+            const float v = __half2float(__ushort_as_half(a.val[e]));
+            const uint4 b = __ldg((const uint4 *)(B + (size_t)a.col[e] * N + sub * 8));
+            const uint32_t w[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float2 f = __half22float2(*(const __half2 *)&w[j]);
+                acc[2 * j] = fmaf(v, f.x, acc[2 * j]), acc[2 * j + 1] = fmaf(v, f.y, acc[2 * j + 1]);
+            }
+        }
+#pragma unroll
+        for (int off = LPR; off < 32; off <<= 1)
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], off);
+        if (grp == 0) {
+            float4 *o = (float4 *)(a.c_add + (size_t)r * N + sub * 8);
+            __stcg(o, make_float4(acc[0], acc[1], acc[2], acc[3])), __stcg(o + 1, make_float4(acc[4], acc[5], acc[6], acc[7]));
+        }
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) tile::st_release(a.rem_seq + blockIdx.x, a.seq);
+}
+
+} // namespace sp24
+
+namespace {
+
+template <int N> void pick(const void *&fn, const void *&rem_fn, size_t &ring_bytes, int &stages, int &ctas)
+{
+    fn = (const void *)sp24::k_b200_sp24<N>, rem_fn = (const void *)sp24::k_b200_sp24_rem<N>;
+    stages = sp24::geom<N>::STAGES, ctas = sp24::geom<N>::CTAS, ring_bytes = (size_t)sp24::geom<N>::RING_BYTES;
+}
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                    CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through the runtime (libcuda is not linked: the library must load on a CPU-only box)
+encode_tiled_fn encoder()
+{
+    static encode_tiled_fn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        return (encode_tiled_fn)p;
+    }();
+    return fn;
+}
+
+// B is K x N fp16 row-major: dimension 0 = dense column (contiguous), dimension 1 = k
+cudaError_t encode_b_map(b200_sp24_plan *pl, const void *B)
+{
+    encode_tiled_fn enc = encoder();
+    if (!enc) return cudaErrorNotSupported;
+    const int atom = pl->N < 64 ? pl->N : 64;
+    cuuint64_t dims[2] = {(cuuint64_t)pl->N, (cuuint64_t)pl->K}, strides[1] = {(cuuint64_t)pl->N * 2};
+    cuuint32_t box[2] = {(cuuint32_t)atom, (cuuint32_t)sp24::SK}, estr[2] = {1, 1};
+    CUtensorMapSwizzle sw = atom == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : atom == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+    CUresult r = enc(&pl->b_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(B), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+    pl->b_mapped = B;
+    return cudaSuccess;
+}
+
+int env_int(const char *name, int dflt)
+{
+    const char *v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+
+} // namespace
+
+cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_remainder, b200_sp24_plan **out, cudaStream_t s)
+{
+    *out = nullptr;
+    if (!p.a.val_is_f16) return cudaErrorInvalidValue; // kind::f16 operands
+    const uint32_t *rowptr = nullptr, *rowid = nullptr;
+    uint32_t n_rows = 0;
+    if (p.a.t_first_nz && p.a.t_first_row && !p.a.t_nz_relative) rowptr = p.a.t_first_nz, rowid = p.a.t_first_row, n_rows = p.a.n_t;
+    else if (p.a.w_first_nz && p.a.w_first_row) rowptr = p.a.w_first_nz, rowid = p.a.w_first_row, n_rows = p.a.n_w;
+    else if (p.a.tb_first_nz && p.a.tb_first_row) rowptr = p.a.tb_first_nz, rowid = p.a.tb_first_row, n_rows = p.a.n_tb;
+    else return cudaErrorInvalidValue;
+    b200_sp24_plan *pl = new (std::nothrow) b200_sp24_plan;
+    if (!pl) return cudaErrorMemoryAllocation;
+    auto fail = [&](cudaError_t e) {
+        b200_sp24_free(pl);
+        return e;
+    };
+    size_t ring_bytes = 0;
+    int stages = 0, ctas = 1;
+    switch (p.N) {
+    case 16: pick<16>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 32: pick<32>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 64: pick<64>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 128: pick<128>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 256: pick<256>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    default: return fail(cudaErrorInvalidValue); // M=128 tcgen05.mma wants N % 16 == 0
+    }
+    pl->N = p.N, pl->K = p.a.cols, pl->n_rows = n_rows;
+    if (!encoder()) return fail(cudaErrorNotSupported);
+
+    // the chain's arrays back to the host, once
+    std::vector<uint32_t> rp(n_rows + 1), rid(n_rows), perm, colw(p.a.nnz);
+    std::vector<uint16_t> val(p.a.nnz);
+    cudaError_t e;
+    if ((e = cudaMemcpyAsync(rp.data(), rowptr, rp.size() * 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemcpyAsync(rid.data(), rowid, rid.size() * 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemcpyAsync(val.data(), p.a.val, val.size() * 2, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+    if (p.a.perm) {
+        perm.resize(p.a.rows);
+        if ((e = cudaMemcpyAsync(perm.data(), p.a.perm, perm.size() * 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+    }
+    if (p.a.col_is_u16) {
+        std::vector<uint16_t> c16(p.a.nnz);
+        if ((e = cudaMemcpyAsync(c16.data(), p.a.col, c16.size() * 2, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+        if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(e);
+        for (size_t i = 0; i < c16.size(); i++) colw[i] = c16[i];
+    } else {
+        if ((e = cudaMemcpyAsync(colw.data(), p.a.col, colw.size() * 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
+        if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(e);
+    }
+    if (rp[n_rows] > p.a.nnz) return fail(cudaErrorInvalidValue);
+
+    gs::sp24_image im;
+    try {
+        gs::build_sp24_image(rp.data(), colw.data(), val.data(), n_rows, p.a.cols, im);
+    } catch (...) {
+        return fail(cudaErrorInvalidValue);
+    }
+    pl->rem_nnz = im.rem_col.size();
+    if (pl->rem_nnz && !allow_remainder) return fail(cudaErrorInvalidValue); // not a 2:4 matrix
+    pl->n_panels = im.n_panels, pl->k_tiles = im.k_tiles, pl->n_tiles = im.n_panels * im.k_tiles, pl->nnz = im.nnz;
+    pl->grid = (uint32_t)std::min<uint64_t>((uint64_t)env_int("GS_TILE_CTAS", sm_count), pl->n_tiles);
+    if (pl->grid == 0 || (int)pl->grid > sm_count) return fail(cudaErrorInvalidValue); // the split-panel hand-off needs every CTA resident
+
+    std::vector<uint32_t> orow((size_t)im.n_panels * sp24::SM_ROWS, 0xffffffffu);
+    for (uint32_t i = 0; i < n_rows; i++) {
+        const uint32_t r = rid[i];
+        if (p.a.perm && r >= perm.size()) return fail(cudaErrorInvalidValue);
+        orow[i] = (p.a.perm ? perm[r] : r) + p.a.begin_row;
+    }
+    pl->smem = ring_bytes + 1024;
+
+    auto up = [&](void **dst, const void *src, size_t bytes) {
+        cudaError_t e2 = cudaMalloc(dst, bytes + 16);
+        if (e2 != cudaSuccess) return e2;
+        return bytes ? cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess;
+    };
+    if ((e = up((void **)&pl->img, im.bytes.data(), im.bytes.size())) != cudaSuccess) return fail(e);
+    if ((e = up((void **)&pl->out_row, orow.data(), orow.size() * 4)) != cudaSuccess) return fail(e);
+    if ((e = cudaMalloc((void **)&pl->ws, (size_t)pl->grid * sp24::SM_ROWS * p.N * 4)) != cudaSuccess) return fail(e);
+    const uint32_t rem_ctas = pl->n_panels * (128 / sp24::REM_ROWS);
+    const size_t n_flags = (size_t)pl->grid * 2 + pl->n_panels + rem_ctas;
+    if ((e = cudaMalloc((void **)&pl->flags, n_flags * 4)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemsetAsync(pl->flags, 0, n_flags * 4, s)) != cudaSuccess) return fail(e);
+    if (pl->rem_nnz) {
+        if ((e = up((void **)&pl->rem_rowptr, im.rem_rowptr.data(), im.rem_rowptr.size() * 4)) != cudaSuccess) return fail(e);
+        if ((e = up((void **)&pl->rem_col, im.rem_col.data(), im.rem_col.size() * 4)) != cudaSuccess) return fail(e);
+        if ((e = up((void **)&pl->rem_val, im.rem_val.data(), im.rem_val.size() * 2)) != cudaSuccess) return fail(e);
+        const size_t cb = (size_t)pl->n_panels * sp24::SM_ROWS * p.N * 4;
+        if ((e = cudaMalloc((void **)&pl->c_add, 2 * cb)) != cudaSuccess) return fail(e);
+        if ((e = cudaMemsetAsync(pl->c_add, 0, 2 * cb, s)) != cudaSuccess) return fail(e);
+    }
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(e);
+    if ((e = cudaFuncSetAttribute(pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem)) != cudaSuccess) return fail(e);
+    if ((e = cudaFuncSetAttribute(pl->fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess) return fail(e);
+    int occ = 0;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pl->fn, sp24::SP_THREADS, pl->smem)) != cudaSuccess) return fail(e);
+    if (occ < 1) return fail(cudaErrorInvalidConfiguration);
+    char rem[48] = "";
+    if (pl->rem_nnz) snprintf(rem, sizeof rem, ",+remainder %.1f%% (gather)", 100.0 * (double)pl->rem_nnz / (double)(pl->rem_nnz + pl->nnz));
+    snprintf(pl->name, sizeof pl->name, "k_b200_sp24<N%d,f16,tcgen05.mma.sp m128n%dk32,%d stages,streamK x%u,%d CTA/SM,pdl%s>", p.N, p.N, stages, pl->grid, occ, rem);
+    if (env_int("GS_SP24_PROBE", 0)) {
+        if ((e = cudaMalloc((void **)&pl->dbg, 128 * 4 * 4)) != cudaSuccess) return fail(e);
+        cudaMemset(pl->dbg, 0xff, 128 * 4 * 4);
+    }
+    *out = pl;
+    return cudaSuccess;
+}
+
+cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStream_t s)
+{
+    if (pl->b_mapped != p.B) {
+        cudaError_t em = encode_b_map(pl, p.B);
+        if (em != cudaSuccess) return em;
+    }
+    const uint32_t seq = ++pl->seq;
+    uint32_t *slot_free = pl->flags + pl->grid, *panel_seq = pl->flags + 2 * (size_t)pl->grid, *rem_seq = panel_seq + pl->n_panels;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg;
+    float *c_add = nullptr;
+    if (pl->rem_nnz) {
+        c_add = pl->c_add + (size_t)(seq & 1u) * pl->n_panels * sp24::SM_ROWS * pl->N;
+        sp24::rem_args r;
+        r.rowptr = pl->rem_rowptr, r.col = pl->rem_col, r.val = pl->rem_val, r.B = p.B, r.c_add = c_add, r.rem_seq = rem_seq, r.panel_seq = panel_seq;
+        r.n_rows = pl->n_rows, r.seq = seq;
+        void *rargs[] = {&r};
+        memset(&cfg, 0, sizeof cfg);
+        cfg.gridDim = dim3(pl->n_panels * (128 / sp24::REM_ROWS)), cfg.blockDim = dim3(sp24::REM_THREADS), cfg.stream = s;
+        cfg.attrs = attr, cfg.numAttrs = p.pdl ? 1 : 0;
+        cudaError_t e = cudaLaunchKernelExC(&cfg, pl->rem_fn, rargs);
+        if (e != cudaSuccess) return e;
+    }
+    sp24::sp24_args a;
+    a.img = pl->img, a.C = p.C, a.out_row = pl->out_row, a.c_add = c_add, a.rem_seq = rem_seq;
+    a.ws = pl->ws, a.flags = pl->flags, a.slot_free = slot_free, a.panel_seq = panel_seq;
+    a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.seq = seq;
+    a.dbg = pl->dbg;
+    void *args[] = {&a, &pl->b_map};
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(sp24::SP_THREADS), cfg.dynamicSmemBytes = pl->smem, cfg.stream = s;
+    cfg.attrs = attr, cfg.numAttrs = (p.pdl || pl->rem_nnz) ? 1 : 0; // behind its own remainder launch the 2:4 kernel always overlaps: the flags order them
+    return cudaLaunchKernelExC(&cfg, pl->fn, args);
+}
+
+void b200_sp24_free(b200_sp24_plan *pl)
+{
+    if (!pl) return;
+    cudaFree(pl->img), cudaFree(pl->out_row), cudaFree(pl->flags), cudaFree(pl->ws), cudaFree(pl->c_add), cudaFree(pl->rem_rowptr), cudaFree(pl->rem_col), cudaFree(pl->rem_val),
+        cudaFree(pl->dbg);
+    delete pl;
+}
+
+const char *b200_sp24_kernel_name(const b200_sp24_plan *pl) { return pl ? pl->name : ""; }
+
+// bytes one launch must move: the image, the remainder's streams, the output row table, B and C once each
+uint64_t b200_sp24_bytes(const b200_sp24_plan *pl, uint64_t rows, uint64_t cols)
+{
+    return (uint64_t)pl->n_tiles * sp24::IMG_BYTES + pl->rem_nnz * 6 + (pl->rem_nnz ? ((uint64_t)pl->n_rows + 1) * 4 : 0) + (uint64_t)pl->n_panels * sp24::SM_ROWS * 4 + cols * pl->N * 2 +
+           rows * pl->N * 2;
+}
+uint64_t b200_sp24_remainder(const b200_sp24_plan *pl) { return pl->rem_nnz; }
+int b200_sp24_launches(const b200_sp24_plan *pl) { return pl->rem_nnz ? 2 : 1; }
+cudaError_t b200_sp24_probe(const b200_sp24_plan *pl, uint32_t *out512)
+{
+    if (!pl->dbg) return cudaErrorInvalidValue;
+    return cudaMemcpy(out512, pl->dbg, 128 * 4 * 4, cudaMemcpyDeviceToHost);
+}
+
+} // namespace gsd

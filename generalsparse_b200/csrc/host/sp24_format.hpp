@@ -1,0 +1,56 @@
+// B200 2:4 image: the device layout of the sparse tensor-core path (GS_FAMILY_B200_SP24, tcgen05.mma.sp).  Built once
+// per plan from what a row-direction chain of the reference produces (nz_col_indices, nz_vals and the row level's
+// first_nz_indices -- total_BMT_result_reduce_to_one_register_token.cc:828-892 reads the same three); the
+// reference-order arrays stay untouched.
+//
+// The matrix is cut into tiles of 128 rows x 128 columns, panel-major (tile t = panel * k_tiles + k_tile).  Inside a
+// row every group of four consecutive columns keeps at most two elements (the 2:4 pattern of the sparse tensor core).
+// A tile is SP24_TILE_BYTES = 18 432 bytes, copied to shared memory by ONE bulk copy and consumed as it lies:
+//   [0, 16 384)      the compressed operand: 128 rows x 64 fp16 (slot 2g / 2g+1 = the two kept elements of column
+//                    group g, in column order), in the K-major 128-byte-swizzled layout tcgen05.mma reads
+//                    (row r, slot c -> r*128 + (((c>>3) ^ (r&7)) << 4) + (c&7)*2);
+//   [16 384, 18 432) the metadata, 4 bits per group (index of the first kept element | index of the second << 2,
+//                    first < second), arranged as 128 rows x 16 bytes so that `tcgen05.cp.128x128b` drops it into
+//                    4 columns of tensor memory in the order the instruction expects (the layout CUTLASS names
+//                    TensorEAtom_MMA_F16, cutlass/gemm/collective/builders/sm1xx_sparse_config.inl): the 32-bit word of
+//                    16-byte row L = (r & 7) + 8*((k>>4)&1) + 16*(r>>4) and column j = k>>5 holds, in its low half,
+//                    the four groups k&15 of tile row r with ((r>>3)&1) == 0, and in its high half those of row r + 8.
+// Elements a group cannot hold (a third and fourth non-zero) go to the remainder, a CSR matrix over the same rows that
+// a gather kernel multiplies: an exactly 2:4-pruned matrix has none, a 70 %-sparse unstructured one leaves 7.7 % of
+// its non-zeros there.  Padding zeros the chain added (modify_*_by_col_pad_in_sub_matrix.cc) are dropped.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+namespace gs {
+
+constexpr uint32_t SP24_ROWS = 128, SP24_COLS = 128, SP24_A_BYTES = SP24_ROWS * (SP24_COLS / 2) * 2, SP24_E_BYTES = SP24_ROWS * 16,
+                   SP24_TILE_BYTES = SP24_A_BYTES + SP24_E_BYTES;
+
+struct sp24_image {
+    uint32_t n_rows = 0, n_cols = 0;
+    uint32_t n_panels = 0, k_tiles = 0;
+    uint64_t nnz = 0;           // non-zeros held by the image
+    std::vector<uint8_t> bytes; // n_panels * k_tiles * SP24_TILE_BYTES
+    // what the 2:4 pattern could not hold, CSR over the same n_rows rows, columns ascending inside a row
+    std::vector<uint32_t> rem_rowptr, rem_col;
+    std::vector<uint16_t> rem_val;
+};
+
+inline uint32_t sp24_a_offset(uint32_t r, uint32_t slot) { return r * 128u + ((((slot >> 3) ^ (r & 7u)) & 7u) << 4) + (slot & 7u) * 2u; }
+// byte and shift of the 4-bit metadata of column group (k >> 2) of tile row r
+inline uint32_t sp24_e_byte(uint32_t r, uint32_t k)
+{
+    const uint32_t L = (r & 7u) + 8u * ((k >> 4) & 1u) + 16u * (r >> 4);
+    return SP24_A_BYTES + 16u * L + 4u * (k >> 5) + 2u * ((r >> 3) & 1u) + ((k >> 3) & 1u);
+}
+inline uint32_t sp24_e_shift(uint32_t k) { return ((k >> 2) & 1u) * 4u; }
+
+// rowptr: n_rows + 1 offsets into col / val_f16 (row i of the row level = row i of the image).  Duplicate columns
+// inside a row with a non-zero value are refused (std::invalid_argument).
+void build_sp24_image(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val_f16, uint32_t n_rows, uint32_t n_cols, sp24_image &out);
+
+// inverse, for tests: dense row-major n_rows x n_cols fp16 bits of image + remainder
+void expand_sp24_image(const sp24_image &im, std::vector<uint16_t> &dense);
+
+} // namespace gs

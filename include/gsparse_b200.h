@@ -51,7 +51,8 @@ typedef enum gs_family {
     GS_FAMILY_B200_ROW_SMEM = 7, /* persistent row kernel, dense B panel staged in shared memory by bulk copy */
     GS_FAMILY_B200_TCGEN05 = 8,  /* sparse-tile decompress to shared memory + tcgen05.mma with TMEM accumulators */
     GS_FAMILY_B200_NNZ = 9,      /* warp-per-run kernel for the nnz-direction bit-map chains (thread_bit_map / warp_segment), N % 32 == 0 */
-    GS_FAMILY_COUNT = 10
+    GS_FAMILY_B200_SP24 = 10,    /* 2:4 sparse tensor cores: tcgen05.mma.sp over a pre-laid-out image, what the pattern cannot hold goes to a gather pass */
+    GS_FAMILY_COUNT = 11
 } gs_family;
 
 const char *gs_last_error(void);
@@ -149,6 +150,14 @@ gs_status gsh_partition_rows_balanced(const uint64_t *row_nnz, uint64_t rows, in
 gs_status gsh_tile_stream_roundtrip(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val_f16, uint32_t n_rows, uint32_t n_cols, uint32_t pass_warps,
                                     uint16_t *dense_out, uint64_t *stats);
 
+/* B200 2:4 image (csrc/host/sp24_format.hpp): the device layout GS_FAMILY_B200_SP24 builds from a row-direction chain --
+ * 128 x 128 tiles of 18 432 bytes (compressed operand in the swizzled shared-memory layout + 4-bit metadata per group of
+ * four columns in tensor-memory order) plus a CSR remainder of what the 2:4 pattern cannot hold.  This entry point
+ * builds the image from CSR, expands image + remainder again and reports stats[0] = image bytes, [1] = non-zeros in
+ * the image, [2] = non-zeros in the remainder, [3] = tiles.  Host only: the CPU tests use it, the engine does the
+ * same at plan time. */
+gs_status gsh_sp24_roundtrip(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val_f16, uint32_t n_rows, uint32_t n_cols, uint16_t *dense_out, uint64_t *stats);
+
 /* ------------------------------------------------------------------ device: engine ---------- */
 typedef struct gs_ctx gs_ctx;   /* replaces executor.cc's compile-and-fork with an in-process device context */
 typedef struct gs_plan gs_plan;
@@ -195,6 +204,9 @@ gs_status gs_synchronize(gs_ctx *ctx); /* drains gs_stream() and both copy strea
 uint64_t gs_plan_algorithmic_bytes(const gs_plan *p);
 int gs_plan_launch_count(const gs_plan *p); /* kernels per gs_launch (memset excluded) */
 const char *gs_plan_kernel_name(const gs_plan *p);
+/* GS_FAMILY_B200_SP24 with GS_SP24_PROBE=1 in the environment at plan creation: the 4 metadata columns of the first
+ * tile as tensor memory holds them after tcgen05.cp (128 lanes x 4 words), for the layout test */
+gs_status gs_plan_sp24_probe(const gs_plan *p, uint32_t *out512);
 
 /* execute_binary(path, matrix, &ms_total, &gflops) of executor.hpp:15 for an uploaded plan:
  * 1 warm-up + `repeat` launches, gflops = FLOAT_RATE*origin_nnz*N*repeat/t/1e9 (code_generator.cc:582-624) */

@@ -283,3 +283,95 @@ def test_b200_nnz_rejects_narrow_dense(engine):
     engine.upload_session(s)
     with pytest.raises(api.GsError):
         engine.plan(s, 8, kernel="b200_nnz")
+
+
+@pytest.mark.parametrize("N", [16, 32, 64, 128, 256])
+@pytest.mark.parametrize("chain", ["thread_total", "warp_total"])
+def test_b200_sp24_kernel(engine, N, chain):
+    """2:4 sparse tensor-core path (HALF): exact in reference mode, in tolerance on random values.  Exactly 2:4-pruned
+    matrices have no remainder (one launch); unstructured ones send what the pattern cannot hold through the gather
+    pass (two launches).  1000 x 4096 splits its 8 row panels over all CTAs (stream-K hand-off), 300 x 1000 has a
+    ragged K tail and empty rows, 130 x 72 is smaller than two tiles"""
+    from generalsparse_b200 import synth
+    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    mats = [("nm24", 1000, 4096, {}, 1), ("nm24", 130, 72, {}, 1), ("uniform", 1000, 4096, dict(density=0.3), 2),
+            ("ragged", 300, 1000, dict(mean_len=20.0, empty_frac=0.2), None)]
+    for i, (kind, nrows, cols, kw, launches) in enumerate(mats):
+        rr, cc = _matrix(kind, nrows, cols, seed=81 + i, **kw)
+        indptr = csr_from_coo(nrows, rr)
+        S = 8 if chain == "thread_total" else 1
+        B1 = np.ones((cols, N), dtype=np.float32)
+        C, plan = _run(engine, chain, nrows, cols, rr, cc, None, B1, N, S, 1, half=True, kernel="b200_sp24")
+        assert "k_b200_sp24" in plan.kernel_name
+        if launches is not None:
+            assert plan.launch_count == launches, plan.kernel_name
+        ref = oracle_spmm_f32(nrows, N, indptr, cc, np.ones(len(rr), np.float32), B1)
+        assert np.array_equal(C.astype(np.float32), ref), plan.kernel_name
+        vals = synth.synth_values(len(rr), seed=5).astype(np.float16).astype(np.float32)
+        B = synth.synth_dense(cols, N, seed=5).astype(np.float16).astype(np.float32)
+        C, plan = _run(engine, chain, nrows, cols, rr, cc, vals, B, N, S, 1, half=True, kernel="b200_sp24")
+        ref = oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B)
+        absrow = oracle_spmm_absrow(nrows, N, indptr, cc, vals, B)
+        _check(C, ref, absrow * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        # repeated launches (programmatic dependent launch, workspace, flag and remainder-buffer reuse) give the same bits
+        plan.run(5)
+        assert np.array_equal(plan.output(), C)
+
+
+@pytest.mark.parametrize("kind,kw", [("nm24", {}), ("uniform", dict(density=0.3))])
+def test_b200_sp24_overlapped_launches_keep_order(engine, kind, kw):
+    """back-to-back launches of one plan overlap on the SMs: C must end up as the LAST launch's product although the
+    dense matrix alternates between launches (with a remainder: two product buffers alternate as well)"""
+    import torch
+    from generalsparse_b200 import api, synth
+    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
+    rows, cols, N = 3000, 4096, 32
+    r, c = _matrix(kind, rows, cols, seed=91, **kw)
+    vals = synth.synth_values(len(r), seed=61).astype(np.float16).astype(np.float32)
+    ms = api.MetaDataSet.from_coo(rows, cols, r, c, vals)
+    s = api.Session(ms).run_family("thread_total", N, 8, 1)
+    engine.upload_session(s, half=True)
+    plan = engine.plan(s, N, half=True, kernel="b200_sp24")
+    Bs = [synth.synth_dense(cols, N, seed=70 + i).astype(np.float16) for i in range(2)]
+    dev = [torch.from_numpy(b).cuda() for b in Bs]
+    torch.cuda.synchronize()
+    indptr = csr_from_coo(rows, r)
+    refs = [oracle_spmm_f64acc(rows, N, indptr, c, vals, b.astype(np.float32)) for b in Bs]
+    absrow = [oracle_spmm_absrow(rows, N, indptr, c, vals, b.astype(np.float32)) for b in Bs]
+    for n_launch in (1, 2, 7, 40, 41):
+        for i in range(n_launch):
+            plan.set_dense_device(dev[i % 2].data_ptr())
+            plan.launch()
+        last = (n_launch - 1) % 2
+        C = plan.output()
+        _check(C, refs[last], absrow[last] * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+
+
+def test_b200_sp24_metadata_lands_in_tensor_memory_as_laid_out(engine, monkeypatch):
+    """the 4 metadata columns tcgen05.cp leaves in tensor memory for the first tile are the 16-byte rows of the image"""
+    from generalsparse_b200 import api
+    monkeypatch.setenv("GS_SP24_PROBE", "1")
+    rows, cols, N = 128, 128, 16
+    r, c = _matrix("nm24", rows, cols, seed=95)
+    ms = api.MetaDataSet.from_coo(rows, cols, r, c)
+    s = api.Session(ms).run_family("warp_total", N, 1, 1)
+    engine.upload_session(s, half=True)
+    plan = engine.plan(s, N, half=True, kernel="b200_sp24")
+    plan.set_dense(np.ones((cols, N), dtype=np.float32))
+    plan.run(1)
+    got = plan.sp24_probe()
+    # expected: word (L, j): low half = groups k&15 of row (L&7) + 16*(L>>4), k in [32 j + 16*((L>>3)&1), +16); high half = row + 8
+    keep = np.zeros((rows, cols), dtype=bool)
+    keep[r, c] = True
+    want = np.zeros((128, 4), dtype=np.uint32)
+    for L in range(128):
+        for j in range(4):
+            w = 0
+            for half in range(2):
+                row = (L & 7) + 16 * (L >> 4) + 8 * half
+                k0 = 32 * j + 16 * ((L >> 3) & 1)
+                for q in range(4):
+                    i0, i1 = np.nonzero(keep[row, k0 + 4 * q:k0 + 4 * q + 4])[0]
+                    w |= (int(i0) | (int(i1) << 2)) << (16 * half + 4 * q)
+            want[L, j] = w
+    assert np.array_equal(got, want)
