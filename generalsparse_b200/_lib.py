@@ -85,7 +85,7 @@ def lib():
         "gs_spmm_host_async": (i32, [vp, vp, vp]), "gs_synchronize": (i32, [vp]),
         "gs_plan_algorithmic_bytes": (u64, [vp]), "gs_plan_launch_count": (i32, [vp]), "gs_plan_kernel_name": (cp, [vp]),
         "gs_execute": (i32, [vp, i32, P(C.c_float), P(C.c_float)]),
-        "gsh_sp24_roundtrip": (i32, [vp, vp, vp, C.c_uint32, C.c_uint32, vp, vp]),
+        "gsh_sp24_roundtrip": (i32, [vp, vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),
         "gs_plan_sp24_probe": (i32, [vp, vp]),
     }
     for name, (res, args) in sig.items():

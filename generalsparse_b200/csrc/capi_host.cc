@@ -353,13 +353,13 @@ gs_status gsh_tile_stream_roundtrip(const uint32_t *rowptr, const uint32_t *col,
     GS_API_END
 }
 
-gs_status gsh_sp24_roundtrip(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val, uint32_t n_rows, uint32_t n_cols, uint16_t *dense_out, uint64_t *stats)
+gs_status gsh_sp24_roundtrip(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val, uint32_t n_rows, uint32_t n_cols, uint32_t group, uint16_t *dense_out, uint64_t *stats)
 {
     GS_API_BEGIN
     GS_REQUIRE(rowptr && col && val && dense_out && stats && n_rows > 0 && n_cols > 0, "bad argument");
     sp24_image im;
     try {
-        build_sp24_image(rowptr, col, val, n_rows, n_cols, im);
+        build_sp24_image(rowptr, col, val, n_rows, n_cols, group, im);
     } catch (const std::exception &e) {
         throw gs::Error(e.what());
     }

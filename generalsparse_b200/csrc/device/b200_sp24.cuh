@@ -13,6 +13,10 @@
 //   warp 1      one lane: tcgen05.cp of the stage's metadata into its 4 columns of tensor memory, 4 tcgen05.mma.sp
 //               (M=128, N, K=32) per tile, commit to empty[stage], and to acc_full[] at the end of a row panel;
 //   warps 4-7   epilogue: tcgen05.ld the accumulator (lane = row), convert, store the rows of C.
+// A CTA may take P = 2 row panels at once (the unit of work is then P panels x one 128-column step, one bulk copy of P
+// images): the 128 x N piece of B, which every tile of every panel needs again, is then fetched from L2 and written
+// to shared memory once per 256 rows instead of once per 128 -- at N >= 64 B's re-reads, not A's stream, fill the path
+// from L2 to the SMs (N=128: 32 KB of B per 18 KB of A).
 // Work split, split-panel hand-off and the ordering between overlapped launches (panel_seq / slot_free flags, no
 // griddepcontrol.wait) are those of the tile kernel, b200_tile.cuh.
 #pragma once
@@ -27,16 +31,16 @@ constexpr int SM_ROWS = 128, SK = 128, IMG_A = SM_ROWS * (SK / 2) * 2, IMG_E = S
 constexpr int PRODUCER_WARP = 0, ISSUE_WARP = 1, EPILOGUE_WARP0 = 4, SP_THREADS = 8 * 32, PF_AHEAD = 4;
 
 struct sp24_args {
-    const unsigned char *img; // n_tiles x IMG_BYTES
+    const unsigned char *img; // n_units x P x IMG_BYTES (unit = P consecutive panels x one k step)
     void *C;
     const uint32_t *out_row; // n_panels * 128 output rows of C, 0xffffffff = no row
     const float *c_add;      // n_panels * 128 x N fp32 added to the accumulator before rounding (the remainder's product), or null
     const uint32_t *rem_seq; // per 32 rows: launch number whose remainder product sits in c_add
-    float *ws;               // grid x 128 x N fp32 partial panels
+    float *ws;               // grid x P x 128 x N fp32 partial panels
     uint32_t *flags;         // grid: launch number whose partial sits in the CTA's slot
     uint32_t *slot_free;     // grid: launch number whose partial has been consumed from the CTA's slot
     uint32_t *panel_seq;     // n_panels: launch number that last wrote the panel's rows of C
-    uint32_t n_tiles, k_tiles, seq;
+    uint32_t n_tiles, k_tiles, seq; // n_tiles: units
     uint32_t *dbg; // probe: CTA 0 leaves the 4 metadata columns of stage 0 (128 lanes x 4 words) here, or null
 };
 
@@ -61,32 +65,34 @@ __device__ __forceinline__ void tc_ld4(uint32_t taddr, uint32_t (&r)[4])
 constexpr int pow2_at_least(int x) { return x <= 32 ? 32 : x <= 64 ? 64 : x <= 128 ? 128 : x <= 256 ? 256 : 512; }
 
 // geometry for dense width N: the B operand is the 128 x N piece of the dense matrix, N contiguous = MN-major
-template <int N> struct geom {
+template <int N, int P> struct geom {
     static constexpr int ATOM_N = N < 64 ? N : 64;           // dense columns per swizzle atom
     static constexpr int RB = ATOM_N * 2;                    // bytes of one k row inside an atom: 32 / 64 / 128
     static constexpr uint32_t LAYOUT = RB == 128 ? 2u : RB == 64 ? 4u : 6u; // SWIZZLE_128B / 64B / 32B
     static constexpr int GROUPS = N / ATOM_N;                // atoms along N
     static constexpr int GROUP_BYTES = SK * RB;              // one atom column: 128 k rows
     static constexpr int B_BYTES = GROUPS * GROUP_BYTES;     // = 128 * N * 2
-    static constexpr int STAGE_BYTES = IMG_BYTES + B_BYTES;  // multiples of 1024: the swizzle atoms stay aligned
+    static constexpr int UNIT_BYTES = P * IMG_BYTES;         // the P tile images of a unit lie back to back
+    static constexpr int STAGE_BYTES = UNIT_BYTES + B_BYTES; // multiples of 1024: the swizzle atoms stay aligned
     static constexpr int SBO = 8 * RB;                       // 8 k rows
     static constexpr int K32_STEP = 32 * RB;                 // bytes between the K=32 slices of one tile
     // two CTAs per SM (two launches in flight) while 2 x (stages + TMEM columns) fit
-    static constexpr int CTAS = N <= 64 ? 2 : 1;
-    static constexpr int STAGES = N <= 32 ? 4 : N == 64 ? 3 : N == 128 ? 4 : 2;
-    static constexpr int ACC = N <= 128 ? 2 : 1;             // accumulators in tensor memory (panels in flight)
-    static constexpr int ECOL0 = ACC * N;                    // the metadata columns sit behind the accumulators
-    static constexpr int TMEM_COLS = pow2_at_least(ECOL0 + 4 * STAGES);
+    static constexpr int CTAS = (P == 1 && N <= 64) ? 2 : 1;
+    static constexpr int STAGES = P == 1 ? (N <= 32 ? 4 : N == 64 ? 3 : N == 128 ? 4 : 2) : (N <= 64 ? 4 : 3);
+    static constexpr int ACC = P * N <= 128 ? 2 : 1;         // accumulator sets in tensor memory (segments in flight), P accumulators each
+    static constexpr int ECOL0 = ACC * P * N;                // the metadata columns sit behind the accumulators
+    static constexpr int TMEM_COLS = pow2_at_least(ECOL0 + 4 * P * STAGES);
     static constexpr int RING_BYTES = STAGES * STAGE_BYTES;
     // instruction descriptor (UMMA::InstrDescriptor): sparse, D fp32, A/B fp16, A K-major, B MN-major, N >> 3, M >> 4
     static constexpr uint32_t IDESC = (1u << 2) | (1u << 4) | (1u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(SM_ROWS >> 4) << 24);
-    static_assert(TMEM_COLS * CTAS <= 512, "tensor memory");
+    static_assert(TMEM_COLS * CTAS <= 512 && ECOL0 + 4 * P * STAGES <= 512, "tensor memory");
+    static_assert(RING_BYTES + 2048 <= 227 * 1024 / CTAS, "shared memory");
     static_assert(STAGE_BYTES % 1024 == 0, "stage alignment");
 };
 
-template <int N> __global__ void __launch_bounds__(SP_THREADS, geom<N>::CTAS) k_b200_sp24(sp24_args a, const __grid_constant__ CUtensorMap b_map)
+template <int N, int P> __global__ void __launch_bounds__(SP_THREADS, geom<N, P>::CTAS) k_b200_sp24(sp24_args a, const __grid_constant__ CUtensorMap b_map)
 {
-    using G = geom<N>;
+    using G = geom<N, P>;
     constexpr int S = G::STAGES, ACC = G::ACC;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * S + 4];
@@ -121,17 +127,17 @@ template <int N> __global__ void __launch_bounds__(SP_THREADS, geom<N>::CTAS) k_
     if (warp == PRODUCER_WARP) {
         // ------------------------------------------------------------------------------------------ copies
         if (lane == 0) {
-            const unsigned char *img = a.img + (size_t)t0 * IMG_BYTES;
-            for (uint32_t it = 0; it < (uint32_t)(S + PF_AHEAD) && it < n_local; it++) l2_prefetch_bulk(img + (size_t)it * IMG_BYTES, IMG_BYTES);
+            const unsigned char *img = a.img + (size_t)t0 * G::UNIT_BYTES;
+            for (uint32_t it = 0; it < (uint32_t)(S + PF_AHEAD) && it < n_local; it++) l2_prefetch_bulk(img + (size_t)it * G::UNIT_BYTES, G::UNIT_BYTES);
             uint32_t s = 0, ph = 0, kt = t0 % KT;
             for (uint32_t it = 0; it < n_local; it++) {
-                if (it + S + PF_AHEAD < n_local) l2_prefetch_bulk(img + (size_t)(it + S + PF_AHEAD) * IMG_BYTES, IMG_BYTES);
+                if (it + S + PF_AHEAD < n_local) l2_prefetch_bulk(img + (size_t)(it + S + PF_AHEAD) * G::UNIT_BYTES, G::UNIT_BYTES);
                 mbar_wait(empty0 + 8u * s, ph ^ 1u); // the tensor core has finished reading the stage
                 const uint32_t st = smem0 + s * G::STAGE_BYTES, fb = full0 + 8u * s;
                 mbar_expect_tx(fb, (uint32_t)G::STAGE_BYTES);
-                bulk_load(st, img + (size_t)it * IMG_BYTES, IMG_BYTES, fb);
+                bulk_load(st, img + (size_t)it * G::UNIT_BYTES, G::UNIT_BYTES, fb);
 #pragma unroll
-                for (int g = 0; g < G::GROUPS; g++) tma_load_2d(st + IMG_BYTES + g * G::GROUP_BYTES, &b_map, (uint32_t)(g * G::ATOM_N), kt * SK, fb); // rows past K come back as zeros
+                for (int g = 0; g < G::GROUPS; g++) tma_load_2d(st + G::UNIT_BYTES + g * G::GROUP_BYTES, &b_map, (uint32_t)(g * G::ATOM_N), kt * SK, fb); // rows past K come back as zeros
                 if (++kt == KT) kt = 0;
                 if (++s == S) s = 0, ph ^= 1u;
             }
@@ -142,22 +148,25 @@ template <int N> __global__ void __launch_bounds__(SP_THREADS, geom<N>::CTAS) k_
         if (lane == 0) {
             uint32_t it = 0, seg = 0, s = 0, ph = 0, kt0 = t0 % KT;
             const uint64_t adesc0 = smem_desc(smem0, 16, 1024, 2u), edesc0 = smem_desc(smem0 + IMG_A, 128, 128, 0u),
-                           bdesc0 = smem_desc(smem0 + IMG_BYTES, G::GROUP_BYTES, G::SBO, G::LAYOUT);
+                           bdesc0 = smem_desc(smem0 + G::UNIT_BYTES, G::GROUP_BYTES, G::SBO, G::LAYOUT);
             while (it < n_local) {
                 const uint32_t len = min(KT - kt0, n_local - it), ab = seg % ACC;
                 mbar_wait(acce0 + 8u * ab, ((seg / ACC) & 1u) ^ 1u);
                 tc_fence_after();
-                const uint32_t d = tmem_base + ab * N;
                 for (uint32_t i = 0; i < len; i++) {
                     mbar_wait(full0 + 8u * s, ph);
                     tc_fence_after();
                     const uint64_t so = (uint64_t)(s * (G::STAGE_BYTES >> 4));
-                    const uint32_t ecol = (uint32_t)G::ECOL0 + 4u * s;
-                    tc_cp_128x128b(tmem_base + ecol, edesc0 + so);
 #pragma unroll
-                    for (uint32_t k = 0; k < SK / 32; k++) // the metadata column pair is addressed, the column inside it goes into the descriptor
-                        tc_mma_sp_f16(d, adesc0 + so + (uint64_t)(2 * k), bdesc0 + so + (uint64_t)(k * (G::K32_STEP >> 4)), tmem_base + ((ecol + k) & ~1u), G::IDESC | ((ecol + k) & 1u),
-                                      (i > 0 || k > 0) ? 1u : 0u);
+                    for (uint32_t h = 0; h < (uint32_t)P; h++) {
+                        const uint64_t ho = so + (uint64_t)(h * (IMG_BYTES >> 4));
+                        const uint32_t ecol = (uint32_t)G::ECOL0 + 4u * (s * P + h), d = tmem_base + (ab * P + h) * N;
+                        tc_cp_128x128b(tmem_base + ecol, edesc0 + ho);
+#pragma unroll
+                        for (uint32_t k = 0; k < SK / 32; k++) // the metadata column pair is addressed, the column inside it goes into the descriptor
+                            tc_mma_sp_f16(d, adesc0 + ho + (uint64_t)(2 * k), bdesc0 + so + (uint64_t)(k * (G::K32_STEP >> 4)), tmem_base + ((ecol + k) & ~1u), G::IDESC | ((ecol + k) & 1u),
+                                          (i > 0 || k > 0) ? 1u : 0u);
+                    }
                     tc_commit(empty0 + 8u * s);
                     if (++s == S) s = 0, ph ^= 1u;
                 }
@@ -177,77 +186,93 @@ template <int N> __global__ void __launch_bounds__(SP_THREADS, geom<N>::CTAS) k_
             __syncwarp();
         };
         while (it < n_local) {
-            const uint32_t t = t0 + it, panel = t / KT, kt0 = t % KT, len = min(KT - kt0, n_local - it), ab = seg % ACC;
-            const bool partial_in = kt0 > 0;                 // someone else owns the panel: leave a partial
-            const bool owner_wait = !partial_in && len < KT; // this CTA owns the panel and others hold its tail
-            uint32_t orow = 0xffffffffu;
+            const uint32_t t = t0 + it, unit_panel = t / KT, kt0 = t % KT, len = min(KT - kt0, n_local - it), ab = seg % ACC;
+            const bool partial_in = kt0 > 0;                 // someone else owns the panels: leave partials
+            const bool owner_wait = !partial_in && len < KT; // this CTA owns the panels and others hold their tail
+            // what does not depend on the accumulator goes first, while the tile loop is still running
+            uint32_t orow[P], c_last = cta; // contributors: the CTAs after this one whose first unit lies inside the same panels
             if (partial_in) wait_for(a.slot_free + cta, a.seq - 1); // the previous launch's owner has read this CTA's slot
             else {
-                wait_for(a.panel_seq + panel, a.seq - 1); // the previous launch has written these rows of C
-                orow = a.out_row[(size_t)panel * SM_ROWS + rip];
-                if (a.c_add) wait_for(a.rem_seq + panel * 4u + q, a.seq); // this launch's remainder product of the warp's 32 rows
+#pragma unroll
+                for (int h = 0; h < P; h++) {
+                    const uint32_t panel = unit_panel * P + h;
+                    wait_for(a.panel_seq + panel, a.seq - 1); // the previous launch has written these rows of C
+                    orow[h] = a.out_row[(size_t)panel * SM_ROWS + rip];
+                    if (a.c_add) { // this launch's remainder product of the warp's 32 rows (a later launch's may already have replaced the flag)
+                        if (lane == 0)
+                            while ((int32_t)(ld_acquire(a.rem_seq + panel * 4u + q) - a.seq) < 0) __nanosleep(32);
+                        __syncwarp();
+                    }
+                }
+                if (owner_wait) {
+                    const uint64_t panel_end = (uint64_t)(unit_panel + 1) * KT;
+                    while (c_last + 1 < n_cta && (uint64_t)(c_last + 1) * a.n_tiles / n_cta < panel_end) c_last++;
+                }
             }
             mbar_wait_idle(accf0 + 8u * ab, (seg / ACC) & 1u);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((q * 32u) << 16) + ab * N;
             if (a.dbg && cta == 0 && seg == 0) {
                 uint32_t e[4];
                 tc_ld4(tmem_base + ((q * 32u) << 16) + (uint32_t)G::ECOL0, e);
                 for (int j = 0; j < 4; j++) a.dbg[rip * 4 + j] = e[j];
             }
             if (partial_in) {
-                float *slot = a.ws + ((size_t)cta * SM_ROWS + rip) * N;
+#pragma unroll
+                for (int h = 0; h < P; h++) {
+                    const uint32_t taddr = tmem_base + ((q * 32u) << 16) + (ab * P + h) * N;
+                    float *slot = a.ws + (((size_t)cta * P + h) * SM_ROWS + rip) * N;
 #pragma unroll 1
-                for (int c = 0; c < N / 8; c++) {
-                    uint32_t r[8];
-                    tc_ld8(taddr + c * 8, r);
-                    __stcg((uint4 *)(slot + c * 8), make_uint4(r[0], r[1], r[2], r[3]));
-                    __stcg((uint4 *)(slot + c * 8) + 1, make_uint4(r[4], r[5], r[6], r[7]));
+                    for (int c = 0; c < N / 8; c++) {
+                        uint32_t r[8];
+                        tc_ld8(taddr + c * 8, r);
+                        __stcg((uint4 *)(slot + c * 8), make_uint4(r[0], r[1], r[2], r[3]));
+                        __stcg((uint4 *)(slot + c * 8) + 1, make_uint4(r[4], r[5], r[6], r[7]));
+                    }
                 }
                 __threadfence();
                 bar_sync(3, 128);
                 if (et == 0) st_release(a.flags + cta, a.seq);
             } else {
-                uint32_t c_last = cta; // contributors: the CTAs after this one whose first tile lies inside the panel
-                if (owner_wait) {
-                    const uint64_t panel_end = (uint64_t)(panel + 1) * KT;
-                    while (c_last + 1 < n_cta && (uint64_t)(c_last + 1) * a.n_tiles / n_cta < panel_end) c_last++;
-                    for (uint32_t c2 = cta + 1; c2 <= c_last; c2++) wait_for(a.flags + c2, a.seq);
-                }
-                const float *add = (a.c_add && orow != 0xffffffffu) ? a.c_add + ((size_t)panel * SM_ROWS + rip) * N : nullptr;
-#pragma unroll 1
-                for (int c = 0; c < N / 8; c++) {
-                    uint32_t r[8];
-                    tc_ld8(taddr + c * 8, r);
-                    for (uint32_t c2 = cta + 1; c2 <= c_last; c2++) {
-                        const float4 *slot = (const float4 *)(a.ws + ((size_t)c2 * SM_ROWS + rip) * N + c * 8);
-                        const float4 x = __ldcg(slot), y = __ldcg(slot + 1);
-                        r[0] = __float_as_uint(__uint_as_float(r[0]) + x.x), r[1] = __float_as_uint(__uint_as_float(r[1]) + x.y);
-                        r[2] = __float_as_uint(__uint_as_float(r[2]) + x.z), r[3] = __float_as_uint(__uint_as_float(r[3]) + x.w);
-                        r[4] = __float_as_uint(__uint_as_float(r[4]) + y.x), r[5] = __float_as_uint(__uint_as_float(r[5]) + y.y);
-                        r[6] = __float_as_uint(__uint_as_float(r[6]) + y.z), r[7] = __float_as_uint(__uint_as_float(r[7]) + y.w);
-                    }
-                    if (add) {
-                        const float4 x = __ldcg((const float4 *)(add + c * 8)), y = __ldcg((const float4 *)(add + c * 8) + 1);
-                        r[0] = __float_as_uint(__uint_as_float(r[0]) + x.x), r[1] = __float_as_uint(__uint_as_float(r[1]) + x.y);
-                        r[2] = __float_as_uint(__uint_as_float(r[2]) + x.z), r[3] = __float_as_uint(__uint_as_float(r[3]) + x.w);
-                        r[4] = __float_as_uint(__uint_as_float(r[4]) + y.x), r[5] = __float_as_uint(__uint_as_float(r[5]) + y.y);
-                        r[6] = __float_as_uint(__uint_as_float(r[6]) + y.z), r[7] = __float_as_uint(__uint_as_float(r[7]) + y.w);
-                    }
-                    if (orow != 0xffffffffu) {
-                        uint32_t h[4];
+                for (uint32_t c2 = cta + 1; c2 <= c_last; c2++) wait_for(a.flags + c2, a.seq);
 #pragma unroll
-                        for (int j = 0; j < 4; j++) {
-                            __half2 p = __floats2half2_rn(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
-                            h[j] = *(uint32_t *)&p;
+                for (int h = 0; h < P; h++) {
+                    const uint32_t panel = unit_panel * P + h, taddr = tmem_base + ((q * 32u) << 16) + (ab * P + h) * N;
+                    const float *add = (a.c_add && orow[h] != 0xffffffffu) ? a.c_add + ((size_t)panel * SM_ROWS + rip) * N : nullptr;
+#pragma unroll 1
+                    for (int c = 0; c < N / 8; c++) {
+                        uint32_t r[8];
+                        tc_ld8(taddr + c * 8, r);
+                        for (uint32_t c2 = cta + 1; c2 <= c_last; c2++) {
+                            const float4 *slot = (const float4 *)(a.ws + (((size_t)c2 * P + h) * SM_ROWS + rip) * N + c * 8);
+                            const float4 x = __ldcg(slot), y = __ldcg(slot + 1);
+                            r[0] = __float_as_uint(__uint_as_float(r[0]) + x.x), r[1] = __float_as_uint(__uint_as_float(r[1]) + x.y);
+                            r[2] = __float_as_uint(__uint_as_float(r[2]) + x.z), r[3] = __float_as_uint(__uint_as_float(r[3]) + x.w);
+                            r[4] = __float_as_uint(__uint_as_float(r[4]) + y.x), r[5] = __float_as_uint(__uint_as_float(r[5]) + y.y);
+                            r[6] = __float_as_uint(__uint_as_float(r[6]) + y.z), r[7] = __float_as_uint(__uint_as_float(r[7]) + y.w);
                         }
-                        *(uint4 *)(C + (size_t)orow * N + c * 8) = make_uint4(h[0], h[1], h[2], h[3]);
+                        if (add) {
+                            const float4 x = __ldcg((const float4 *)(add + c * 8)), y = __ldcg((const float4 *)(add + c * 8) + 1);
+                            r[0] = __float_as_uint(__uint_as_float(r[0]) + x.x), r[1] = __float_as_uint(__uint_as_float(r[1]) + x.y);
+                            r[2] = __float_as_uint(__uint_as_float(r[2]) + x.z), r[3] = __float_as_uint(__uint_as_float(r[3]) + x.w);
+                            r[4] = __float_as_uint(__uint_as_float(r[4]) + y.x), r[5] = __float_as_uint(__uint_as_float(r[5]) + y.y);
+                            r[6] = __float_as_uint(__uint_as_float(r[6]) + y.z), r[7] = __float_as_uint(__uint_as_float(r[7]) + y.w);
+                        }
+                        if (orow[h] != 0xffffffffu) {
+                            uint32_t hh[4];
+#pragma unroll
+                            for (int j = 0; j < 4; j++) {
+                                __half2 p = __floats2half2_rn(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+                                hh[j] = *(uint32_t *)&p;
+                            }
+                            *(uint4 *)(C + (size_t)orow[h] * N + c * 8) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+                        }
                     }
                 }
                 __threadfence();
                 bar_sync(3, 128);
                 if (et == 0) {
-                    st_release(a.panel_seq + panel, a.seq);
+#pragma unroll
+                    for (int h = 0; h < P; h++) st_release(a.panel_seq + unit_panel * P + h, a.seq);
                     for (uint32_t c2 = cta + 1; c2 <= c_last; c2++) st_release(a.slot_free + c2, a.seq);
                 }
             }

@@ -18,7 +18,7 @@ struct b200_sp24_plan {
     float *ws = nullptr, *c_add = nullptr;         // c_add: two buffers (launch parity) of n_panels * 128 x N fp32, when there is a remainder
     uint32_t *rem_rowptr = nullptr, *rem_col = nullptr;
     uint16_t *rem_val = nullptr;
-    uint32_t n_tiles = 0, k_tiles = 0, n_panels = 0, grid = 0, seq = 0, n_rows = 0;
+    uint32_t n_tiles = 0, k_tiles = 0, n_panels = 0, grid = 0, seq = 0, n_rows = 0, group = 1; // n_tiles: units of `group` panels x one k step
     uint64_t nnz = 0, rem_nnz = 0;
     size_t smem = 0;
     const void *fn = nullptr, *rem_fn = nullptr;
@@ -32,7 +32,7 @@ struct b200_sp24_plan {
 
 namespace sp24 {
 
-constexpr int REM_THREADS = 256, REM_ROWS = 32; // a remainder CTA covers 32 rows = the rows of one epilogue warp of the 2:4 kernel
+constexpr int REM_THREADS = 512, REM_ROWS = 32; // a remainder CTA covers 32 rows = the rows of one epilogue warp of the 2:4 kernel
 
 struct rem_args {
     const uint32_t *rowptr, *col;
@@ -45,8 +45,10 @@ struct rem_args {
 };
 
 // Product of the remainder (what the 2:4 pattern could not hold: 7.7 % of the non-zeros of a 70 %-sparse unstructured
-// matrix, nothing for a 2:4-pruned one) with B, fp32, one warp per row: a group of LPR = N/8 lanes gathers one row of
-// B with 16-byte loads, the 32/LPR groups take the row's non-zeros in turn, a butterfly adds the groups.
+// matrix, nothing for a 2:4-pruned one) with B, fp32, two rows per warp.  32 (column id, value) entries of a row are one
+// coalesced load per lane and are handed round by shuffles; a group of LPR = N/8 lanes gathers one row of B with
+// 16-byte loads, the 32/LPR groups take the entries in turn, so every gather of a 32-entry block is independent of the
+// others (two dependent memory round trips per block, not per entry); a butterfly adds the groups.
 template <int N> __global__ void __launch_bounds__(REM_THREADS) k_b200_sp24_rem(rem_args a)
 {
     constexpr int LPR = N / 8, GROUPS = 32 / LPR, RPW = REM_ROWS / (REM_THREADS / 32);
@@ -64,15 +66,25 @@ template <int N> __global__ void __launch_bounds__(REM_THREADS) k_b200_sp24_rem(
         if (r >= a.n_rows) break;
         float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         const uint32_t e0 = a.rowptr[r], e1 = a.rowptr[r + 1];
-#pragma unroll 4
-        for (uint32_t e = e0 + grp; e < e1; e += GROUPS) {
-            const float v = __half2float(__ushort_as_half(a.val[e]));
-            const uint4 b = __ldg((const uint4 *)(B + (size_t)a.col[e] * N + sub * 8));
-            const uint32_t w[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll 2
+        for (uint32_t e = e0; e < e1; e += 32) {
+            const bool have = e + lane < e1;
+            const uint32_t mycol = have ? __ldg(a.col + e + lane) : 0u;
+            const float myval = have ? __half2float(__ushort_as_half(__ldg(a.val + e + lane))) : 0.0f;
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const float2 f = __half22float2(*(const __half2 *)&w[j]);
-                acc[2 * j] = fmaf(v, f.x, acc[2 * j]), acc[2 * j + 1] = fmaf(v, f.y, acc[2 * j + 1]);
+            for (int j = 0; j < LPR; j++) {
+                const int src = j * GROUPS + grp;
+                const uint32_t c = __shfl_sync(0xffffffffu, mycol, src);
+                const float v = __shfl_sync(0xffffffffu, myval, src);
+                if (e + src < e1) {
+                    const uint4 b = __ldg((const uint4 *)(B + (size_t)c * N + sub * 8));
+                    const uint32_t w[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        const float2 f = __half22float2(*(const __half2 *)&w[q]);
+                        acc[2 * q] = fmaf(v, f.x, acc[2 * q]), acc[2 * q + 1] = fmaf(v, f.y, acc[2 * q + 1]);
+                    }
+                }
             }
         }
 #pragma unroll
@@ -93,10 +105,10 @@ template <int N> __global__ void __launch_bounds__(REM_THREADS) k_b200_sp24_rem(
 
 namespace {
 
-template <int N> void pick(const void *&fn, const void *&rem_fn, size_t &ring_bytes, int &stages, int &ctas)
+template <int N, int P> void pick(const void *&fn, const void *&rem_fn, size_t &ring_bytes, int &stages, int &ctas)
 {
-    fn = (const void *)sp24::k_b200_sp24<N>, rem_fn = (const void *)sp24::k_b200_sp24_rem<N>;
-    stages = sp24::geom<N>::STAGES, ctas = sp24::geom<N>::CTAS, ring_bytes = (size_t)sp24::geom<N>::RING_BYTES;
+    fn = (const void *)sp24::k_b200_sp24<N, P>, rem_fn = (const void *)sp24::k_b200_sp24_rem<N>;
+    stages = sp24::geom<N, P>::STAGES, ctas = sp24::geom<N, P>::CTAS, ring_bytes = (size_t)sp24::geom<N, P>::RING_BYTES;
 }
 
 typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
@@ -156,12 +168,19 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     };
     size_t ring_bytes = 0;
     int stages = 0, ctas = 1;
-    switch (p.N) {
-    case 16: pick<16>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
-    case 32: pick<32>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
-    case 64: pick<64>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
-    case 128: pick<128>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
-    case 256: pick<256>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    // row panels per unit of work: two halve the re-reads of B (b200_sp24.cuh); at N=256 two accumulators fill tensor memory
+    const int group = p.N == 256 ? 1 : std::max(1, std::min(2, env_int("GS_SP24_PANELS", p.N >= 64 ? 2 : 1)));
+    pl->group = (uint32_t)group;
+    switch (p.N * 4 + group) {
+    case 16 * 4 + 1: pick<16, 1>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 32 * 4 + 1: pick<32, 1>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 64 * 4 + 1: pick<64, 1>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 128 * 4 + 1: pick<128, 1>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 256 * 4 + 1: pick<256, 1>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 16 * 4 + 2: pick<16, 2>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 32 * 4 + 2: pick<32, 2>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 64 * 4 + 2: pick<64, 2>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 128 * 4 + 2: pick<128, 2>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
     default: return fail(cudaErrorInvalidValue); // M=128 tcgen05.mma wants N % 16 == 0
     }
     pl->N = p.N, pl->K = p.a.cols, pl->n_rows = n_rows;
@@ -191,13 +210,13 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
 
     gs::sp24_image im;
     try {
-        gs::build_sp24_image(rp.data(), colw.data(), val.data(), n_rows, p.a.cols, im);
+        gs::build_sp24_image(rp.data(), colw.data(), val.data(), n_rows, p.a.cols, (uint32_t)group, im);
     } catch (...) {
         return fail(cudaErrorInvalidValue);
     }
     pl->rem_nnz = im.rem_col.size();
     if (pl->rem_nnz && !allow_remainder) return fail(cudaErrorInvalidValue); // not a 2:4 matrix
-    pl->n_panels = im.n_panels, pl->k_tiles = im.k_tiles, pl->n_tiles = im.n_panels * im.k_tiles, pl->nnz = im.nnz;
+    pl->n_panels = im.n_panels, pl->k_tiles = im.k_tiles, pl->n_tiles = im.n_panels / group * im.k_tiles, pl->nnz = im.nnz;
     pl->grid = (uint32_t)std::min<uint64_t>((uint64_t)env_int("GS_TILE_CTAS", sm_count), pl->n_tiles);
     if (pl->grid == 0 || (int)pl->grid > sm_count) return fail(cudaErrorInvalidValue); // the split-panel hand-off needs every CTA resident
 
@@ -216,7 +235,7 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     };
     if ((e = up((void **)&pl->img, im.bytes.data(), im.bytes.size())) != cudaSuccess) return fail(e);
     if ((e = up((void **)&pl->out_row, orow.data(), orow.size() * 4)) != cudaSuccess) return fail(e);
-    if ((e = cudaMalloc((void **)&pl->ws, (size_t)pl->grid * sp24::SM_ROWS * p.N * 4)) != cudaSuccess) return fail(e);
+    if ((e = cudaMalloc((void **)&pl->ws, (size_t)pl->grid * group * sp24::SM_ROWS * p.N * 4)) != cudaSuccess) return fail(e);
     const uint32_t rem_ctas = pl->n_panels * (128 / sp24::REM_ROWS);
     const size_t n_flags = (size_t)pl->grid * 2 + pl->n_panels + rem_ctas;
     if ((e = cudaMalloc((void **)&pl->flags, n_flags * 4)) != cudaSuccess) return fail(e);
@@ -237,7 +256,8 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     if (occ < 1) return fail(cudaErrorInvalidConfiguration);
     char rem[48] = "";
     if (pl->rem_nnz) snprintf(rem, sizeof rem, ",+remainder %.1f%% (gather)", 100.0 * (double)pl->rem_nnz / (double)(pl->rem_nnz + pl->nnz));
-    snprintf(pl->name, sizeof pl->name, "k_b200_sp24<N%d,f16,tcgen05.mma.sp m128n%dk32,%d stages,streamK x%u,%d CTA/SM,pdl%s>", p.N, p.N, stages, pl->grid, occ, rem);
+    snprintf(pl->name, sizeof pl->name, "k_b200_sp24<N%d,f16,tcgen05.mma.sp m128n%dk32,%d panel%s/CTA,%d stages,streamK x%u,%d CTA/SM,pdl%s>", p.N, p.N, group, group > 1 ? "s" : "", stages, pl->grid, occ,
+             rem);
     if (env_int("GS_SP24_PROBE", 0)) {
         if ((e = cudaMalloc((void **)&pl->dbg, 128 * 4 * 4)) != cudaSuccess) return fail(e);
         cudaMemset(pl->dbg, 0xff, 128 * 4 * 4);
@@ -259,7 +279,8 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cudaLaunchConfig_t cfg;
     float *c_add = nullptr;
-    if (pl->rem_nnz) {
+    static const bool skip_rem = env_int("GS_SP24_SKIP_REM", 0) != 0; // timing experiments only: wrong results on a matrix with a remainder
+    if (pl->rem_nnz && !skip_rem) {
         c_add = pl->c_add + (size_t)(seq & 1u) * pl->n_panels * sp24::SM_ROWS * pl->N;
         sp24::rem_args r;
         r.rowptr = pl->rem_rowptr, r.col = pl->rem_col, r.val = pl->rem_val, r.B = p.B, r.c_add = c_add, r.rem_seq = rem_seq, r.panel_seq = panel_seq;
@@ -296,7 +317,7 @@ const char *b200_sp24_kernel_name(const b200_sp24_plan *pl) { return pl ? pl->na
 // bytes one launch must move: the image, the remainder's streams, the output row table, B and C once each
 uint64_t b200_sp24_bytes(const b200_sp24_plan *pl, uint64_t rows, uint64_t cols)
 {
-    return (uint64_t)pl->n_tiles * sp24::IMG_BYTES + pl->rem_nnz * 6 + (pl->rem_nnz ? ((uint64_t)pl->n_rows + 1) * 4 : 0) + (uint64_t)pl->n_panels * sp24::SM_ROWS * 4 + cols * pl->N * 2 +
+    return (uint64_t)pl->n_tiles * pl->group * sp24::IMG_BYTES + pl->rem_nnz * 6 + (pl->rem_nnz ? ((uint64_t)pl->n_rows + 1) * 4 : 0) + (uint64_t)pl->n_panels * sp24::SM_ROWS * 4 + cols * pl->N * 2 +
            rows * pl->N * 2;
 }
 uint64_t b200_sp24_remainder(const b200_sp24_plan *pl) { return pl->rem_nnz; }

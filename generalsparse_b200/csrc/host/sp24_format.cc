@@ -7,11 +7,12 @@
 
 namespace gs {
 
-void build_sp24_image(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val, uint32_t n_rows, uint32_t n_cols, sp24_image &im)
+void build_sp24_image(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val, uint32_t n_rows, uint32_t n_cols, uint32_t group, sp24_image &im)
 {
+    if (group < 1 || group > 2) throw std::invalid_argument("2:4 image: group must be 1 or 2");
     im = sp24_image();
-    im.n_rows = n_rows, im.n_cols = n_cols;
-    im.n_panels = (n_rows + SP24_ROWS - 1) / SP24_ROWS;
+    im.n_rows = n_rows, im.n_cols = n_cols, im.group = group;
+    im.n_panels = ((n_rows + SP24_ROWS - 1) / SP24_ROWS + group - 1) / group * group;
     im.k_tiles = (n_cols + SP24_COLS - 1) / SP24_COLS;
     const uint64_t T = (uint64_t)im.n_panels * im.k_tiles;
     if (T + 1 > 0xffffffffull) throw std::invalid_argument("2:4 image: too many tiles");
@@ -39,7 +40,7 @@ void build_sp24_image(const uint32_t *rowptr, const uint32_t *col, const uint16_
                 if (j > i && row[j].first == row[j - 1].first) throw std::invalid_argument("2:4 image: duplicate column inside a row");
                 j++;
             }
-            uint8_t *tile = im.bytes.data() + (p * im.k_tiles + (uint64_t)g * 4u / SP24_COLS) * SP24_TILE_BYTES;
+            uint8_t *tile = im.bytes.data() + sp24_tile_index(p, (uint64_t)g * 4u / SP24_COLS, im.k_tiles, group) * SP24_TILE_BYTES;
             const uint32_t k = (g * 4u) % SP24_COLS, slot = k / 2u; // first slot of the group in the compressed row
             uint32_t i0 = row[i].first & 3u, i1;
             uint16_t v0 = row[i].second, v1 = 0;
@@ -67,7 +68,7 @@ void expand_sp24_image(const sp24_image &im, std::vector<uint16_t> &dense)
         const uint64_t p = r / SP24_ROWS;
         const uint32_t rr = r % SP24_ROWS;
         for (uint32_t g = 0; g * 4u < im.n_cols; g++) {
-            const uint8_t *tile = im.bytes.data() + (p * im.k_tiles + (uint64_t)g * 4u / SP24_COLS) * SP24_TILE_BYTES;
+            const uint8_t *tile = im.bytes.data() + sp24_tile_index(p, (uint64_t)g * 4u / SP24_COLS, im.k_tiles, im.group) * SP24_TILE_BYTES;
             const uint32_t k = (g * 4u) % SP24_COLS, slot = k / 2u;
             const uint32_t e = (tile[sp24_e_byte(rr, k)] >> sp24_e_shift(k)) & 0xfu;
             for (uint32_t s = 0; s < 2; s++) {

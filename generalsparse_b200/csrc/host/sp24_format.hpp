@@ -3,7 +3,10 @@
 // first_nz_indices -- total_BMT_result_reduce_to_one_register_token.cc:828-892 reads the same three); the
 // reference-order arrays stay untouched.
 //
-// The matrix is cut into tiles of 128 rows x 128 columns, panel-major (tile t = panel * k_tiles + k_tile).  Inside a
+// The matrix is cut into tiles of 128 rows x 128 columns.  `group` (1 or 2) consecutive row panels form a unit of work:
+// tile (panel, k_tile) lies at index ((panel / group) * k_tiles + k_tile) * group + panel % group, so the `group` tiles a CTA
+// multiplies with one piece of B are one contiguous run (group = 1: panel-major).  The panel count is padded to a multiple of
+// `group` with empty tiles.  Inside a
 // row every group of four consecutive columns keeps at most two elements (the 2:4 pattern of the sparse tensor core).
 // A tile is SP24_TILE_BYTES = 18 432 bytes, copied to shared memory by ONE bulk copy and consumed as it lies:
 //   [0, 16 384)      the compressed operand: 128 rows x 64 fp16 (slot 2g / 2g+1 = the two kept elements of column
@@ -29,7 +32,7 @@ constexpr uint32_t SP24_ROWS = 128, SP24_COLS = 128, SP24_A_BYTES = SP24_ROWS * 
 
 struct sp24_image {
     uint32_t n_rows = 0, n_cols = 0;
-    uint32_t n_panels = 0, k_tiles = 0;
+    uint32_t n_panels = 0, k_tiles = 0, group = 1; // n_panels: padded to a multiple of group
     uint64_t nnz = 0;           // non-zeros held by the image
     std::vector<uint8_t> bytes; // n_panels * k_tiles * SP24_TILE_BYTES
     // what the 2:4 pattern could not hold, CSR over the same n_rows rows, columns ascending inside a row
@@ -45,10 +48,11 @@ inline uint32_t sp24_e_byte(uint32_t r, uint32_t k)
     return SP24_A_BYTES + 16u * L + 4u * (k >> 5) + 2u * ((r >> 3) & 1u) + ((k >> 3) & 1u);
 }
 inline uint32_t sp24_e_shift(uint32_t k) { return ((k >> 2) & 1u) * 4u; }
+inline uint64_t sp24_tile_index(uint64_t panel, uint64_t k_tile, uint64_t k_tiles, uint64_t group) { return ((panel / group) * k_tiles + k_tile) * group + panel % group; }
 
 // rowptr: n_rows + 1 offsets into col / val_f16 (row i of the row level = row i of the image).  Duplicate columns
 // inside a row with a non-zero value are refused (std::invalid_argument).
-void build_sp24_image(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val_f16, uint32_t n_rows, uint32_t n_cols, sp24_image &out);
+void build_sp24_image(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val_f16, uint32_t n_rows, uint32_t n_cols, uint32_t group, sp24_image &out);
 
 // inverse, for tests: dense row-major n_rows x n_cols fp16 bits of image + remainder
 void expand_sp24_image(const sp24_image &im, std::vector<uint16_t> &dense);

@@ -152,11 +152,13 @@ gs_status gsh_tile_stream_roundtrip(const uint32_t *rowptr, const uint32_t *col,
 
 /* B200 2:4 image (csrc/host/sp24_format.hpp): the device layout GS_FAMILY_B200_SP24 builds from a row-direction chain --
  * 128 x 128 tiles of 18 432 bytes (compressed operand in the swizzled shared-memory layout + 4-bit metadata per group of
- * four columns in tensor-memory order) plus a CSR remainder of what the 2:4 pattern cannot hold.  This entry point
+ * four columns in tensor-memory order) plus a CSR remainder of what the 2:4 pattern cannot hold; `group` (1 or 2) row
+ * panels form one unit of work and lie back to back.  This entry point
  * builds the image from CSR, expands image + remainder again and reports stats[0] = image bytes, [1] = non-zeros in
  * the image, [2] = non-zeros in the remainder, [3] = tiles.  Host only: the CPU tests use it, the engine does the
  * same at plan time. */
-gs_status gsh_sp24_roundtrip(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val_f16, uint32_t n_rows, uint32_t n_cols, uint16_t *dense_out, uint64_t *stats);
+gs_status gsh_sp24_roundtrip(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val_f16, uint32_t n_rows, uint32_t n_cols, uint32_t group, uint16_t *dense_out,
+                             uint64_t *stats);
 
 /* ------------------------------------------------------------------ device: engine ---------- */
 typedef struct gs_ctx gs_ctx;   /* replaces executor.cc's compile-and-fork with an in-process device context */

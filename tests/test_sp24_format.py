@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 
-def _roundtrip(rows, cols, indptr, col, vals16):
+def _roundtrip(rows, cols, indptr, col, vals16, group=1):
     from generalsparse_b200 import _lib
     L = _lib.lib()
     dense = np.zeros((rows, cols), dtype=np.uint16)
@@ -14,7 +14,7 @@ def _roundtrip(rows, cols, indptr, col, vals16):
     rp = np.ascontiguousarray(indptr, dtype=np.uint32)
     cc = np.ascontiguousarray(col, dtype=np.uint32)
     vv = np.ascontiguousarray(vals16.view(np.uint16))
-    _lib.check(L.gsh_sp24_roundtrip(rp.ctypes.data_as(C.c_void_p), cc.ctypes.data_as(C.c_void_p), vv.ctypes.data_as(C.c_void_p), rows, cols,
+    _lib.check(L.gsh_sp24_roundtrip(rp.ctypes.data_as(C.c_void_p), cc.ctypes.data_as(C.c_void_p), vv.ctypes.data_as(C.c_void_p), rows, cols, group,
                                     dense.ctypes.data_as(C.c_void_p), stats.ctypes.data_as(C.c_void_p)))
     return dense, stats
 
@@ -39,13 +39,15 @@ def _mask_24(rows, cols, seed):
     return mask.reshape(rows, cols)
 
 
-@pytest.mark.parametrize("rows,cols", [(128, 128), (130, 260), (1000, 4096), (5, 8)])
-def test_exact_24_has_no_remainder(built_lib, rows, cols):
+@pytest.mark.parametrize("group", [1, 2])
+@pytest.mark.parametrize("rows,cols", [(128, 128), (130, 260), (1000, 4096), (5, 8), (300, 128)])
+def test_exact_24_has_no_remainder(built_lib, rows, cols, group):
     indptr, col, v, dense = _csr_of(_mask_24(rows, cols, rows + cols), seed=1)
-    out, stats = _roundtrip(rows, cols, indptr, col, v)
+    out, stats = _roundtrip(rows, cols, indptr, col, v, group)
     assert np.array_equal(out, dense.view(np.uint16))
     assert int(stats[1]) == len(col) and int(stats[2]) == 0
-    assert int(stats[3]) == -(-rows // 128) * -(-cols // 128) and int(stats[0]) == int(stats[3]) * 18432
+    panels = -(-(-(-rows // 128)) // group) * group  # padded to whole units of `group` panels
+    assert int(stats[3]) == panels * -(-cols // 128) and int(stats[0]) == int(stats[3]) * 18432
 
 
 @pytest.mark.parametrize("rows,cols,density,empty", [(130, 70, 0.3, 0), (300, 1000, 0.02, 60), (1000, 4096, 0.3, 0), (257, 129, 0.9, 3), (5, 3, 1.0, 0)])
@@ -55,7 +57,7 @@ def test_unstructured_goes_to_image_plus_remainder(built_lib, rows, cols, densit
     if empty:
         mask[rng.choice(rows, empty, replace=False)] = False
     indptr, col, v, dense = _csr_of(mask, seed=2)
-    out, stats = _roundtrip(rows, cols, indptr, col, v)
+    out, stats = _roundtrip(rows, cols, indptr, col, v, 1 + rows % 2)
     assert np.array_equal(out, dense.view(np.uint16))
     # every group of four columns keeps its first two non-zeros, the rest is remainder
     pad = (-cols) % 4

@@ -318,6 +318,28 @@ def test_b200_sp24_kernel(engine, N, chain):
         assert np.array_equal(plan.output(), C)
 
 
+@pytest.mark.parametrize("N,panels", [(32, 2), (64, 1), (128, 1), (16, 2)])
+def test_b200_sp24_panels_per_cta(engine, monkeypatch, N, panels):
+    """the other unit size than the default for this N (GS_SP24_PANELS): one or two row panels per CTA and k step;
+    9 panels is an odd count (the image is padded to whole units), with and without a remainder"""
+    from generalsparse_b200 import synth
+    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
+    monkeypatch.setenv("GS_SP24_PANELS", str(panels))
+    for i, (kind, kw) in enumerate([("nm24", {}), ("uniform", dict(density=0.3))]):
+        nrows, cols = 1100, 2048
+        rr, cc = _matrix(kind, nrows, cols, seed=97 + i, **kw)
+        indptr = csr_from_coo(nrows, rr)
+        vals = synth.synth_values(len(rr), seed=6).astype(np.float16).astype(np.float32)
+        B = synth.synth_dense(cols, N, seed=6).astype(np.float16).astype(np.float32)
+        C, plan = _run(engine, "thread_total", nrows, cols, rr, cc, vals, B, N, 8, 1, half=True, kernel="b200_sp24")
+        assert ("%d panel" % panels) in plan.kernel_name, plan.kernel_name
+        ref = oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B)
+        absrow = oracle_spmm_absrow(nrows, N, indptr, cc, vals, B)
+        _check(C, ref, absrow * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        plan.run(7)
+        assert np.array_equal(plan.output(), C)
+
+
 @pytest.mark.parametrize("kind,kw", [("nm24", {}), ("uniform", dict(density=0.3))])
 def test_b200_sp24_overlapped_launches_keep_order(engine, kind, kw):
     """back-to-back launches of one plan overlap on the SMs: C must end up as the LAST launch's product although the
