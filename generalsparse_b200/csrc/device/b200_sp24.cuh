@@ -35,7 +35,8 @@ struct sp24_args {
     void *C;
     const uint32_t *out_row; // n_panels * 128 output rows of C, 0xffffffff = no row
     const float *c_add;      // n_panels * 128 x N fp32 added to the accumulator before rounding (the remainder's product), or null
-    const uint32_t *rem_seq; // per 32 rows: launch number whose remainder product sits in c_add
+    const uint32_t *rem_seq; // per 32 rows: remainder CTAs that have delivered so far (rem_per_flag per launch, monotonic)
+    uint32_t rem_per_flag;
     float *ws;               // grid x P x 128 x N fp32 partial panels
     uint32_t *flags;         // grid: launch number whose partial sits in the CTA's slot
     uint32_t *slot_free;     // grid: launch number whose partial has been consumed from the CTA's slot
@@ -62,6 +63,32 @@ __device__ __forceinline__ void tc_ld4(uint32_t taddr, uint32_t (&r)[4])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// CH accumulator columns of the thread's row, issued only: tc_wait_ld() before the registers are read
+template <int CH> __device__ __forceinline__ void tc_ld_issue(uint32_t taddr, uint32_t (&r)[CH])
+{
+    static_assert(CH == 8 || CH == 32, "chunk");
+    if constexpr (CH == 8) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                     : "r"(taddr));
+    } else {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]),
+                       "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]),
+                       "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                     : "r"(taddr));
+    }
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+template <int CH> __device__ __forceinline__ void add4(uint32_t (&r)[CH], const float4 (&x)[CH / 4])
+{
+#pragma unroll
+    for (int j = 0; j < CH / 4; j++) {
+        r[4 * j] = __float_as_uint(__uint_as_float(r[4 * j]) + x[j].x), r[4 * j + 1] = __float_as_uint(__uint_as_float(r[4 * j + 1]) + x[j].y);
+        r[4 * j + 2] = __float_as_uint(__uint_as_float(r[4 * j + 2]) + x[j].z), r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + x[j].w);
+    }
+}
+
 constexpr int pow2_at_least(int x) { return x <= 32 ? 32 : x <= 64 ? 64 : x <= 128 ? 128 : x <= 256 ? 256 : 512; }
 
 // geometry for dense width N: the B operand is the 128 x N piece of the dense matrix, N contiguous = MN-major
@@ -83,6 +110,11 @@ template <int N, int P> struct geom {
     static constexpr int ECOL0 = ACC * P * N;                // the metadata columns sit behind the accumulators
     static constexpr int TMEM_COLS = pow2_at_least(ECOL0 + 4 * P * STAGES);
     static constexpr int RING_BYTES = STAGES * STAGE_BYTES;
+    // accumulator columns the epilogue moves per step: with one CTA per SM nothing hides the epilogue of a launch's last
+    // panel, so its loads (tensor memory, the other CTAs' partials, the remainder's product) go out 32 columns at a time;
+    // with two CTAs per SM the next launch covers it and the registers stay under the cap that lets two CTAs fit
+    static constexpr int CH = (CTAS == 1 && N >= 32) ? 32 : 8;
+    static constexpr int MIN_CTAS = CTAS == 1 ? 1 : 4;       // __launch_bounds__: 4 x 256 threads = 64 registers, room for the remainder pass beside two CTAs
     // instruction descriptor (UMMA::InstrDescriptor): sparse, D fp32, A/B fp16, A K-major, B MN-major, N >> 3, M >> 4
     static constexpr uint32_t IDESC = (1u << 2) | (1u << 4) | (1u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(SM_ROWS >> 4) << 24);
     static_assert(TMEM_COLS * CTAS <= 512 && ECOL0 + 4 * P * STAGES <= 512, "tensor memory");
@@ -90,10 +122,13 @@ template <int N, int P> struct geom {
     static_assert(STAGE_BYTES % 1024 == 0, "stage alignment");
 };
 
-template <int N, int P> __global__ void __launch_bounds__(SP_THREADS, geom<N, P>::CTAS) k_b200_sp24(sp24_args a, const __grid_constant__ CUtensorMap b_map)
+// N: the width the tensor core multiplies (a multiple of 16); NL <= N: the width of B and C in memory (NL = 8 runs as N = 16,
+// the tensor map returns zeros for the columns B does not have)
+template <int N, int P, int NL> __global__ void __launch_bounds__(SP_THREADS, geom<N, P>::MIN_CTAS) k_b200_sp24(sp24_args a, const __grid_constant__ CUtensorMap b_map)
 {
     using G = geom<N, P>;
-    constexpr int S = G::STAGES, ACC = G::ACC;
+    constexpr int S = G::STAGES, ACC = G::ACC, CH = G::CH;
+    static_assert(NL % CH == 0, "chunk");
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * S + 4];
     __shared__ uint32_t tmem_slot;
@@ -200,7 +235,7 @@ template <int N, int P> __global__ void __launch_bounds__(SP_THREADS, geom<N, P>
                     orow[h] = a.out_row[(size_t)panel * SM_ROWS + rip];
                     if (a.c_add) { // this launch's remainder product of the warp's 32 rows (a later launch's may already have replaced the flag)
                         if (lane == 0)
-                            while ((int32_t)(ld_acquire(a.rem_seq + panel * 4u + q) - a.seq) < 0) __nanosleep(32);
+                            while ((int32_t)(ld_acquire(a.rem_seq + panel * 4u + q) - a.seq * a.rem_per_flag) < 0) __nanosleep(32);
                         __syncwarp();
                     }
                 }
@@ -220,13 +255,14 @@ template <int N, int P> __global__ void __launch_bounds__(SP_THREADS, geom<N, P>
 #pragma unroll
                 for (int h = 0; h < P; h++) {
                     const uint32_t taddr = tmem_base + ((q * 32u) << 16) + (ab * P + h) * N;
-                    float *slot = a.ws + (((size_t)cta * P + h) * SM_ROWS + rip) * N;
+                    float *slot = a.ws + (((size_t)cta * P + h) * SM_ROWS + rip) * NL;
 #pragma unroll 1
-                    for (int c = 0; c < N / 8; c++) {
-                        uint32_t r[8];
-                        tc_ld8(taddr + c * 8, r);
-                        __stcg((uint4 *)(slot + c * 8), make_uint4(r[0], r[1], r[2], r[3]));
-                        __stcg((uint4 *)(slot + c * 8) + 1, make_uint4(r[4], r[5], r[6], r[7]));
+                    for (int c0 = 0; c0 < NL; c0 += CH) {
+                        uint32_t r[CH];
+                        tc_ld_issue<CH>(taddr + c0, r);
+                        tc_wait_ld();
+#pragma unroll
+                        for (int j = 0; j < CH / 4; j++) __stcg((uint4 *)(slot + c0) + j, make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]));
                     }
                 }
                 __threadfence();
@@ -237,34 +273,47 @@ template <int N, int P> __global__ void __launch_bounds__(SP_THREADS, geom<N, P>
 #pragma unroll
                 for (int h = 0; h < P; h++) {
                     const uint32_t panel = unit_panel * P + h, taddr = tmem_base + ((q * 32u) << 16) + (ab * P + h) * N;
-                    const float *add = (a.c_add && orow[h] != 0xffffffffu) ? a.c_add + ((size_t)panel * SM_ROWS + rip) * N : nullptr;
+                    const float *add = (a.c_add && orow[h] != 0xffffffffu) ? a.c_add + ((size_t)panel * SM_ROWS + rip) * NL : nullptr;
+                    const bool h1 = c_last >= cta + 1, h2 = c_last >= cta + 2;
+                    const float *s1 = a.ws + (((size_t)(cta + 1) * P + h) * SM_ROWS + rip) * NL, *s2 = a.ws + (((size_t)(cta + 2) * P + h) * SM_ROWS + rip) * NL;
 #pragma unroll 1
-                    for (int c = 0; c < N / 8; c++) {
-                        uint32_t r[8];
-                        tc_ld8(taddr + c * 8, r);
-                        for (uint32_t c2 = cta + 1; c2 <= c_last; c2++) {
-                            const float4 *slot = (const float4 *)(a.ws + (((size_t)c2 * P + h) * SM_ROWS + rip) * N + c * 8);
-                            const float4 x = __ldcg(slot), y = __ldcg(slot + 1);
-                            r[0] = __float_as_uint(__uint_as_float(r[0]) + x.x), r[1] = __float_as_uint(__uint_as_float(r[1]) + x.y);
-                            r[2] = __float_as_uint(__uint_as_float(r[2]) + x.z), r[3] = __float_as_uint(__uint_as_float(r[3]) + x.w);
-                            r[4] = __float_as_uint(__uint_as_float(r[4]) + y.x), r[5] = __float_as_uint(__uint_as_float(r[5]) + y.y);
-                            r[6] = __float_as_uint(__uint_as_float(r[6]) + y.z), r[7] = __float_as_uint(__uint_as_float(r[7]) + y.w);
+                    for (int c0 = 0; c0 < NL; c0 += CH) { // every load of the step goes out before the first is used; the sums keep the order k, then the remainder
+                        uint32_t r[CH];
+                        float4 x1[CH / 4], x2[CH / 4], xa[CH / 4];
+                        tc_ld_issue<CH>(taddr + c0, r);
+                        if (h1) {
+#pragma unroll
+                            for (int j = 0; j < CH / 4; j++) x1[j] = __ldcg((const float4 *)(s1 + c0) + j);
+                        }
+                        if (h2) {
+#pragma unroll
+                            for (int j = 0; j < CH / 4; j++) x2[j] = __ldcg((const float4 *)(s2 + c0) + j);
                         }
                         if (add) {
-                            const float4 x = __ldcg((const float4 *)(add + c * 8)), y = __ldcg((const float4 *)(add + c * 8) + 1);
-                            r[0] = __float_as_uint(__uint_as_float(r[0]) + x.x), r[1] = __float_as_uint(__uint_as_float(r[1]) + x.y);
-                            r[2] = __float_as_uint(__uint_as_float(r[2]) + x.z), r[3] = __float_as_uint(__uint_as_float(r[3]) + x.w);
-                            r[4] = __float_as_uint(__uint_as_float(r[4]) + y.x), r[5] = __float_as_uint(__uint_as_float(r[5]) + y.y);
-                            r[6] = __float_as_uint(__uint_as_float(r[6]) + y.z), r[7] = __float_as_uint(__uint_as_float(r[7]) + y.w);
-                        }
-                        if (orow[h] != 0xffffffffu) {
-                            uint32_t hh[4];
 #pragma unroll
-                            for (int j = 0; j < 4; j++) {
-                                __half2 p = __floats2half2_rn(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
-                                hh[j] = *(uint32_t *)&p;
+                            for (int j = 0; j < CH / 4; j++) xa[j] = __ldcg((const float4 *)(add + c0) + j);
+                        }
+                        tc_wait_ld();
+                        if (h1) add4<CH>(r, x1);
+                        if (h2) add4<CH>(r, x2);
+                        for (uint32_t c2 = cta + 3; c2 <= c_last; c2++) { // a panel spread over more than three CTAs: small matrices only
+                            const float4 *slot = (const float4 *)(a.ws + (((size_t)c2 * P + h) * SM_ROWS + rip) * NL + c0);
+#pragma unroll
+                            for (int j = 0; j < CH / 4; j++) x1[j] = __ldcg(slot + j);
+                            add4<CH>(r, x1);
+                        }
+                        if (add) add4<CH>(r, xa);
+                        if (orow[h] != 0xffffffffu) {
+#pragma unroll
+                            for (int j8 = 0; j8 < CH / 8; j8++) {
+                                uint32_t hh[4];
+#pragma unroll
+                                for (int j = 0; j < 4; j++) {
+                                    __half2 pr = __floats2half2_rn(__uint_as_float(r[8 * j8 + 2 * j]), __uint_as_float(r[8 * j8 + 2 * j + 1]));
+                                    hh[j] = *(uint32_t *)&pr;
+                                }
+                                *(uint4 *)(C + (size_t)orow[h] * NL + c0 + 8 * j8) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
                             }
-                            *(uint4 *)(C + (size_t)orow[h] * N + c * 8) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
                         }
                     }
                 }

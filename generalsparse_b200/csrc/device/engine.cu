@@ -281,7 +281,7 @@ static void select_kernel(gs_plan *p, int family)
         if (p->sp24_plan) gsd::b200_sp24_free(p->sp24_plan), p->sp24_plan = nullptr;
         GS_REQUIRE(p->half, "b200_sp24: the sparse tensor-core path multiplies fp16 operands (HALF); fp32 values stay on the gather kernels");
         cudaError_t e = gsd::b200_sp24_prepare(p->lp, ctx->sm_count, true, &p->sp24_plan, ctx->stream);
-        if (e == cudaErrorInvalidValue) throw gs::Error("b200_sp24: needs N in {16,32,64,128,256}, HALF values and a row-direction chain with row block 1");
+        if (e == cudaErrorInvalidValue) throw gs::Error("b200_sp24: needs N in {8,16,32,64,128,256}, HALF values and a row-direction chain with row block 1");
         CUDA_TRY(e);
         break;
     }

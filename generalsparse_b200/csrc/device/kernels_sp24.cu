@@ -32,20 +32,22 @@ struct b200_sp24_plan {
 
 namespace sp24 {
 
-constexpr int REM_THREADS = 512, REM_ROWS = 32; // a remainder CTA covers 32 rows = the rows of one epilogue warp of the 2:4 kernel
+// a remainder CTA is four warps and four rows: small enough (5 K registers, no shared memory) that six of them fit an SM beside two
+// CTAs of the 2:4 kernel, so the pass runs under the previous launch's tile loop instead of waiting for its registers
+constexpr int REM_THREADS = 128, REM_ROWS = 4, REM_PER_FLAG = 32 / REM_ROWS;
 
 struct rem_args {
     const uint32_t *rowptr, *col;
     const uint16_t *val;
     const void *B;
     float *c_add;              // this launch's buffer
-    uint32_t *rem_seq;         // per remainder CTA: launch number whose product sits in c_add
+    uint32_t *rem_seq;         // per 32 rows (the rows of one epilogue warp of the 2:4 kernel): remainder CTAs that have delivered, REM_PER_FLAG per launch
     const uint32_t *panel_seq; // per panel: launch number that last wrote the panel's rows of C (the buffer's reader two launches back is done)
     uint32_t n_rows, seq;
 };
 
 // Product of the remainder (what the 2:4 pattern could not hold: 7.7 % of the non-zeros of a 70 %-sparse unstructured
-// matrix, nothing for a 2:4-pruned one) with B, fp32, two rows per warp.  32 (column id, value) entries of a row are one
+// matrix, nothing for a 2:4-pruned one) with B, fp32, one row per warp.  32 (column id, value) entries of a row are one
 // coalesced load per lane and are handed round by shuffles; a group of LPR = N/8 lanes gathers one row of B with
 // 16-byte loads, the 32/LPR groups take the entries in turn, so every gather of a 32-entry block is independent of the
 // others (two dependent memory round trips per block, not per entry); a butterfly adds the groups.
@@ -56,6 +58,7 @@ template <int N> __global__ void __launch_bounds__(REM_THREADS) k_b200_sp24_rem(
     row::pdl_launch_dependents();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane / LPR, sub = lane % LPR;
     const uint32_t panel = blockIdx.x / (128 / REM_ROWS);
+    static_assert(RPW == 1, "one row per warp");
     if (threadIdx.x == 0 && a.seq >= 2)
         while ((int32_t)(tile::ld_acquire(a.panel_seq + panel) - (a.seq - 2)) < 0) __nanosleep(32);
     __syncthreads();
@@ -98,16 +101,16 @@ template <int N> __global__ void __launch_bounds__(REM_THREADS) k_b200_sp24_rem(
     }
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) tile::st_release(a.rem_seq + blockIdx.x, a.seq);
+    if (threadIdx.x == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.rem_seq + blockIdx.x / REM_PER_FLAG) : "memory");
 }
 
 } // namespace sp24
 
 namespace {
 
-template <int N, int P> void pick(const void *&fn, const void *&rem_fn, size_t &ring_bytes, int &stages, int &ctas)
+template <int N, int P, int NL = N> void pick(const void *&fn, const void *&rem_fn, size_t &ring_bytes, int &stages, int &ctas)
 {
-    fn = (const void *)sp24::k_b200_sp24<N, P>, rem_fn = (const void *)sp24::k_b200_sp24_rem<N>;
+    fn = (const void *)sp24::k_b200_sp24<N, P, NL>, rem_fn = (const void *)sp24::k_b200_sp24_rem<NL>;
     stages = sp24::geom<N, P>::STAGES, ctas = sp24::geom<N, P>::CTAS, ring_bytes = (size_t)sp24::geom<N, P>::RING_BYTES;
 }
 
@@ -131,7 +134,7 @@ cudaError_t encode_b_map(b200_sp24_plan *pl, const void *B)
 {
     encode_tiled_fn enc = encoder();
     if (!enc) return cudaErrorNotSupported;
-    const int atom = pl->N < 64 ? pl->N : 64;
+    const int atom = pl->N < 16 ? 16 : pl->N < 64 ? pl->N : 64; // N=8 runs as N=16: the box is wider than the tensor, the rest comes back as zeros
     cuuint64_t dims[2] = {(cuuint64_t)pl->N, (cuuint64_t)pl->K}, strides[1] = {(cuuint64_t)pl->N * 2};
     cuuint32_t box[2] = {(cuuint32_t)atom, (cuuint32_t)sp24::SK}, estr[2] = {1, 1};
     CUtensorMapSwizzle sw = atom == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : atom == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
@@ -168,10 +171,13 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     };
     size_t ring_bytes = 0;
     int stages = 0, ctas = 1;
-    // row panels per unit of work: two halve the re-reads of B (b200_sp24.cuh); at N=256 two accumulators fill tensor memory
-    const int group = p.N == 256 ? 1 : std::max(1, std::min(2, env_int("GS_SP24_PANELS", p.N >= 64 ? 2 : 1)));
+    // row panels per unit of work: two halve the re-reads of B (b200_sp24.cuh) but measured slower at every N (profiles/r1_sp24_summary.md),
+    // so one is the default; at N=256 two accumulators would fill tensor memory
+    const int group = p.N == 256 ? 1 : std::max(1, std::min(2, env_int("GS_SP24_PANELS", 1)));
     pl->group = (uint32_t)group;
     switch (p.N * 4 + group) {
+    case 8 * 4 + 1: pick<16, 1, 8>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
+    case 8 * 4 + 2: pick<16, 2, 8>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
     case 16 * 4 + 1: pick<16, 1>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
     case 32 * 4 + 1: pick<32, 1>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
     case 64 * 4 + 1: pick<64, 1>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
@@ -181,7 +187,7 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     case 32 * 4 + 2: pick<32, 2>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
     case 64 * 4 + 2: pick<64, 2>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
     case 128 * 4 + 2: pick<128, 2>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas); break;
-    default: return fail(cudaErrorInvalidValue); // M=128 tcgen05.mma wants N % 16 == 0
+    default: return fail(cudaErrorInvalidValue); // M=128 tcgen05.mma wants N % 16 == 0 (8 runs as 16)
     }
     pl->N = p.N, pl->K = p.a.cols, pl->n_rows = n_rows;
     if (!encoder()) return fail(cudaErrorNotSupported);
@@ -236,8 +242,7 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     if ((e = up((void **)&pl->img, im.bytes.data(), im.bytes.size())) != cudaSuccess) return fail(e);
     if ((e = up((void **)&pl->out_row, orow.data(), orow.size() * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMalloc((void **)&pl->ws, (size_t)pl->grid * group * sp24::SM_ROWS * p.N * 4)) != cudaSuccess) return fail(e);
-    const uint32_t rem_ctas = pl->n_panels * (128 / sp24::REM_ROWS);
-    const size_t n_flags = (size_t)pl->grid * 2 + pl->n_panels + rem_ctas;
+    const size_t n_flags = (size_t)pl->grid * 2 + pl->n_panels + (size_t)pl->n_panels * 4;
     if ((e = cudaMalloc((void **)&pl->flags, n_flags * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMemsetAsync(pl->flags, 0, n_flags * 4, s)) != cudaSuccess) return fail(e);
     if (pl->rem_nnz) {
@@ -256,7 +261,7 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     if (occ < 1) return fail(cudaErrorInvalidConfiguration);
     char rem[48] = "";
     if (pl->rem_nnz) snprintf(rem, sizeof rem, ",+remainder %.1f%% (gather)", 100.0 * (double)pl->rem_nnz / (double)(pl->rem_nnz + pl->nnz));
-    snprintf(pl->name, sizeof pl->name, "k_b200_sp24<N%d,f16,tcgen05.mma.sp m128n%dk32,%d panel%s/CTA,%d stages,streamK x%u,%d CTA/SM,pdl%s>", p.N, p.N, group, group > 1 ? "s" : "", stages, pl->grid, occ,
+    snprintf(pl->name, sizeof pl->name, "k_b200_sp24<N%d,f16,tcgen05.mma.sp m128n%dk32,%d panel%s/CTA,%d stages,streamK x%u,%d CTA/SM,pdl%s>", p.N, p.N < 16 ? 16 : p.N, group, group > 1 ? "s" : "", stages, pl->grid, occ,
              rem);
     if (env_int("GS_SP24_PROBE", 0)) {
         if ((e = cudaMalloc((void **)&pl->dbg, 128 * 4 * 4)) != cudaSuccess) return fail(e);
@@ -293,7 +298,7 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
         if (e != cudaSuccess) return e;
     }
     sp24::sp24_args a;
-    a.img = pl->img, a.C = p.C, a.out_row = pl->out_row, a.c_add = c_add, a.rem_seq = rem_seq;
+    a.img = pl->img, a.C = p.C, a.out_row = pl->out_row, a.c_add = c_add, a.rem_seq = rem_seq, a.rem_per_flag = sp24::REM_PER_FLAG;
     a.ws = pl->ws, a.flags = pl->flags, a.slot_free = slot_free, a.panel_seq = panel_seq;
     a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.seq = seq;
     a.dbg = pl->dbg;

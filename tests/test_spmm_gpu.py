@@ -285,7 +285,7 @@ def test_b200_nnz_rejects_narrow_dense(engine):
         engine.plan(s, 8, kernel="b200_nnz")
 
 
-@pytest.mark.parametrize("N", [16, 32, 64, 128, 256])
+@pytest.mark.parametrize("N", [8, 16, 32, 64, 128, 256])
 @pytest.mark.parametrize("chain", ["thread_total", "warp_total"])
 def test_b200_sp24_kernel(engine, N, chain):
     """2:4 sparse tensor-core path (HALF): exact in reference mode, in tolerance on random values.  Exactly 2:4-pruned
@@ -318,7 +318,7 @@ def test_b200_sp24_kernel(engine, N, chain):
         assert np.array_equal(plan.output(), C)
 
 
-@pytest.mark.parametrize("N,panels", [(32, 2), (64, 1), (128, 1), (16, 2)])
+@pytest.mark.parametrize("N,panels", [(32, 2), (64, 1), (128, 1), (16, 2), (8, 2)])
 def test_b200_sp24_panels_per_cta(engine, monkeypatch, N, panels):
     """the other unit size than the default for this N (GS_SP24_PANELS): one or two row panels per CTA and k step;
     9 panels is an odd count (the image is padded to whole units), with and without a remainder"""
