@@ -42,6 +42,7 @@ struct sp24_args {
     uint32_t *slot_free;     // grid: launch number whose partial has been consumed from the CTA's slot
     uint32_t *panel_seq;     // n_panels: launch number that last wrote the panel's rows of C
     uint32_t n_tiles, k_tiles, seq; // n_tiles: units
+    uint32_t pf_ahead;              // units the bulk L2 prefetch runs ahead of the copy ring, 0 = no prefetch
     uint32_t *dbg; // probe: CTA 0 leaves the 4 metadata columns of stage 0 (128 lanes x 4 words) here, or null
 };
 
@@ -104,9 +105,9 @@ template <int N, int P> struct geom {
     static constexpr int SBO = 8 * RB;                       // 8 k rows
     static constexpr int K32_STEP = 32 * RB;                 // bytes between the K=32 slices of one tile
     // two CTAs per SM (two launches in flight) while 2 x (stages + TMEM columns) fit
-    static constexpr int CTAS = (P == 1 && N <= 64) ? 2 : 1;
-    static constexpr int STAGES = P == 1 ? (N <= 32 ? 4 : N == 64 ? 3 : N == 128 ? 4 : 2) : (N <= 64 ? 4 : 3);
-    static constexpr int ACC = P * N <= 128 ? 2 : 1;         // accumulator sets in tensor memory (segments in flight), P accumulators each
+    static constexpr int CTAS = (P == 1 && N <= 128) ? 2 : 1;
+    static constexpr int STAGES = P == 1 ? (N <= 32 ? 4 : N == 64 ? 3 : 2) : (N <= 64 ? 4 : 3);
+    static constexpr int ACC = P * N <= 64 ? 2 : 1;         // accumulator sets in tensor memory (segments in flight), P accumulators each
     static constexpr int ECOL0 = ACC * P * N;                // the metadata columns sit behind the accumulators
     static constexpr int TMEM_COLS = pow2_at_least(ECOL0 + 4 * P * STAGES);
     static constexpr int RING_BYTES = STAGES * STAGE_BYTES;
@@ -163,10 +164,11 @@ template <int N, int P, int NL> __global__ void __launch_bounds__(SP_THREADS, ge
         // ------------------------------------------------------------------------------------------ copies
         if (lane == 0) {
             const unsigned char *img = a.img + (size_t)t0 * G::UNIT_BYTES;
-            for (uint32_t it = 0; it < (uint32_t)(S + PF_AHEAD) && it < n_local; it++) l2_prefetch_bulk(img + (size_t)it * G::UNIT_BYTES, G::UNIT_BYTES);
+            const uint32_t pf = a.pf_ahead ? (uint32_t)S + a.pf_ahead : 0u;
+            for (uint32_t it = 0; it < pf && it < n_local; it++) l2_prefetch_bulk(img + (size_t)it * G::UNIT_BYTES, G::UNIT_BYTES);
             uint32_t s = 0, ph = 0, kt = t0 % KT;
             for (uint32_t it = 0; it < n_local; it++) {
-                if (it + S + PF_AHEAD < n_local) l2_prefetch_bulk(img + (size_t)(it + S + PF_AHEAD) * G::UNIT_BYTES, G::UNIT_BYTES);
+                if (pf && it + pf < n_local) l2_prefetch_bulk(img + (size_t)(it + pf) * G::UNIT_BYTES, G::UNIT_BYTES);
                 mbar_wait(empty0 + 8u * s, ph ^ 1u); // the tensor core has finished reading the stage
                 const uint32_t st = smem0 + s * G::STAGE_BYTES, fb = full0 + 8u * s;
                 mbar_expect_tx(fb, (uint32_t)G::STAGE_BYTES);

@@ -301,6 +301,8 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
     a.img = pl->img, a.C = p.C, a.out_row = pl->out_row, a.c_add = c_add, a.rem_seq = rem_seq, a.rem_per_flag = sp24::REM_PER_FLAG;
     a.ws = pl->ws, a.flags = pl->flags, a.slot_free = slot_free, a.panel_seq = panel_seq;
     a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.seq = seq;
+    static const uint32_t pf_ahead = (uint32_t)env_int("GS_SP24_PREFETCH", sp24::PF_AHEAD);
+    a.pf_ahead = pf_ahead;
     a.dbg = pl->dbg;
     void *args[] = {&a, &pl->b_map};
     memset(&cfg, 0, sizeof cfg);
