@@ -67,9 +67,17 @@ def peaks():
 def traffic_bytes(N, half, world, args):
     """DRAM bytes per launch from the committed ncu --set full capture of this workload (profiles/traffic.json), else None"""
     p = os.path.join(ROOT, "profiles", "traffic.json")
-    if not (os.path.exists(p) and N == 8 and half and ROWS == 11008 and args.kernel == "b200_row_smem"):
+    if not (os.path.exists(p) and half and ROWS == 11008):
         return None
-    return json.load(open(p)).get("C2_N8_half_thread_total_S8", {}).get("bytes")
+    t = json.load(open(p))
+    if args.pattern == "nm24":
+        key = "C3_24_N%d_half_sp24" % N if args.kernel == "b200_sp24" else None
+    elif abs(DENSITY - 0.30) > 1e-9:
+        key = None
+    else:
+        key = {"b200_row_smem": "C2_N%d_half_thread_total_S8", "b200_tcgen05": "C2_N%d_half_thread_total_S8_tile"}.get(args.kernel)
+        key = key % N if key else None
+    return t.get(key, {}).get("bytes") if key else None
 
 
 PATTERN = "unstructured"

@@ -256,6 +256,9 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(e);
     if ((e = cudaFuncSetAttribute(pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem)) != cudaSuccess) return fail(e);
     if ((e = cudaFuncSetAttribute(pl->fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess) return fail(e);
+    // the same shared-memory / L1 split for the remainder pass: CTAs of kernels that want different splits cannot share an SM, and the
+    // pass is meant to run beside the resident CTAs of the 2:4 kernel
+    if ((e = cudaFuncSetAttribute(pl->rem_fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess) return fail(e);
     int occ = 0;
     if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pl->fn, sp24::SP_THREADS, pl->smem)) != cudaSuccess) return fail(e);
     if (occ < 1) return fail(cudaErrorInvalidConfiguration);
