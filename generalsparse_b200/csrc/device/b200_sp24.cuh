@@ -17,6 +17,10 @@
 // images): the 128 x N piece of B, which every tile of every panel needs again, is then fetched from L2 and written
 // to shared memory once per 256 rows instead of once per 128 -- at N >= 64 B's re-reads, not A's stream, fill the path
 // from L2 to the SMs (N=128: 32 KB of B per 18 KB of A).
+// With remainder warps (RW = 8, N <= 16): what the 2:4 pattern cannot hold is multiplied inside the same CTA.  The CTA that
+// owns a panel also owns its remainder rows; warps 8-15 (a pair of threads per row: two halves of the row's entries at
+// N=8, the two 16-byte halves of B's row at N=16) gather B from L2 while the tile loop runs, leave the fp32 product in
+// shared memory, and the epilogue adds it before the single rounding.  No second launch, no global hand-off.
 // Work split, split-panel hand-off and the ordering between overlapped launches (panel_seq / slot_free flags, no
 // griddepcontrol.wait) are those of the tile kernel, b200_tile.cuh.
 #pragma once
@@ -43,6 +47,11 @@ struct sp24_args {
     uint32_t *panel_seq;     // n_panels: launch number that last wrote the panel's rows of C
     uint32_t n_tiles, k_tiles, seq; // n_tiles: units
     uint32_t pf_ahead;              // units the bulk L2 prefetch runs ahead of the copy ring, 0 = no prefetch
+    // fused remainder (kernels instantiated with remainder warps): CSR over the image's rows, one packed word per entry
+    // (column id << 16 | fp16 value bits), multiplied by warps 8-15 of the CTA that owns the panel while the tile loop runs
+    const uint32_t *rem_rowptr, *rem_pack;
+    const void *B;
+    uint32_t n_rows;
     uint32_t *dbg; // probe: CTA 0 leaves the 4 metadata columns of stage 0 (128 lanes x 4 words) here, or null
 };
 
@@ -125,13 +134,14 @@ template <int N, int P> struct geom {
 
 // N: the width the tensor core multiplies (a multiple of 16); NL <= N: the width of B and C in memory (NL = 8 runs as N = 16,
 // the tensor map returns zeros for the columns B does not have)
-template <int N, int P, int NL> __global__ void __launch_bounds__(SP_THREADS, geom<N, P>::MIN_CTAS) k_b200_sp24(sp24_args a, const __grid_constant__ CUtensorMap b_map)
+template <int N, int P, int NL, int RW> __global__ void __launch_bounds__(SP_THREADS + 32 * RW, (RW ? 2 : geom<N, P>::MIN_CTAS)) k_b200_sp24(sp24_args a, const __grid_constant__ CUtensorMap b_map)
 {
     using G = geom<N, P>;
     constexpr int S = G::STAGES, ACC = G::ACC, CH = G::CH;
     static_assert(NL % CH == 0, "chunk");
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t bars[2 * S + 4];
+    static_assert(RW == 0 || (RW == 8 && NL <= 16 && P == 1 && G::CTAS == 2), "remainder warps");
+    __shared__ __align__(8) uint64_t bars[2 * S + 8];
     __shared__ uint32_t tmem_slot;
     const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u; // 1024-byte alignment of the stages (128-byte swizzle atoms)
 
@@ -144,11 +154,15 @@ template <int N, int P, int NL> __global__ void __launch_bounds__(SP_THREADS, ge
     const uint32_t bar0 = smem_u32(bars);
     // full[s] = bar0 + 8 s, empty[s] = + 8 (S + s), acc_full[b] = + 8 (2 S + b), acc_empty[b] = + 8 (2 S + 2 + b)
     const uint32_t full0 = bar0, empty0 = bar0 + 8u * S, accf0 = bar0 + 16u * S, acce0 = accf0 + 16u;
+    // rem_full[b] = acce0 + 16 + 8 b, rem_empty[b] = + 16: the two remainder buffers behind the ring (128 rows x NL fp32 each)
+    const uint32_t remf0 = acce0 + 16u, reme0 = remf0 + 16u;
+    float *rem_buf = (float *)(smem_raw + (smem0 - smem_u32(smem_raw)) + G::RING_BYTES);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < S; s++) mbar_init(&bars[s], 1), mbar_init(&bars[S + s], 1);
         mbar_init(&bars[2 * S], 1), mbar_init(&bars[2 * S + 1], 1);
         mbar_init(&bars[2 * S + 2], 4), mbar_init(&bars[2 * S + 3], 4);
+        if (RW) mbar_init(&bars[2 * S + 4], RW), mbar_init(&bars[2 * S + 5], RW), mbar_init(&bars[2 * S + 6], 4), mbar_init(&bars[2 * S + 7], 4);
     }
     if (warp == ISSUE_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"((uint32_t)G::TMEM_COLS) : "memory");
@@ -212,11 +226,11 @@ template <int N, int P, int NL> __global__ void __launch_bounds__(SP_THREADS, ge
             }
         }
         __syncwarp();
-    } else if (warp >= EPILOGUE_WARP0) {
+    } else if (warp >= EPILOGUE_WARP0 && warp < EPILOGUE_WARP0 + 4) {
         // ------------------------------------------------------------------------------------------ epilogue
         const uint32_t q = warp - EPILOGUE_WARP0, rip = q * 32 + lane, et = threadIdx.x - EPILOGUE_WARP0 * 32;
         __half *C = (__half *)a.C;
-        uint32_t it = 0, seg = 0;
+        uint32_t it = 0, seg = 0, own = 0; // own: owner segments so far (the remainder warps count the same way)
         auto wait_for = [&](const uint32_t *flag, uint32_t v) { // one lane polls, the warp follows
             if (lane == 0)
                 while (ld_acquire(flag) != v) __nanosleep(32);
@@ -275,7 +289,11 @@ template <int N, int P, int NL> __global__ void __launch_bounds__(SP_THREADS, ge
 #pragma unroll
                 for (int h = 0; h < P; h++) {
                     const uint32_t panel = unit_panel * P + h, taddr = tmem_base + ((q * 32u) << 16) + (ab * P + h) * N;
-                    const float *add = (a.c_add && orow[h] != 0xffffffffu) ? a.c_add + ((size_t)panel * SM_ROWS + rip) * NL : nullptr;
+                    const float *add;
+                    if constexpr (RW != 0) { // the remainder warps of this CTA left the product of the panel's remainder rows in shared memory
+                        add = a.rem_rowptr ? rem_buf + ((own & 1u) * SM_ROWS + rip) * NL : nullptr;
+                        if (add) mbar_wait(remf0 + 8u * (own & 1u), (own >> 1) & 1u);
+                    } else add = (a.c_add && orow[h] != 0xffffffffu) ? a.c_add + ((size_t)panel * SM_ROWS + rip) * NL : nullptr;
                     const bool h1 = c_last >= cta + 1, h2 = c_last >= cta + 2;
                     const float *s1 = a.ws + (((size_t)(cta + 1) * P + h) * SM_ROWS + rip) * NL, *s2 = a.ws + (((size_t)(cta + 2) * P + h) * SM_ROWS + rip) * NL;
 #pragma unroll 1
@@ -293,7 +311,7 @@ template <int N, int P, int NL> __global__ void __launch_bounds__(SP_THREADS, ge
                         }
                         if (add) {
 #pragma unroll
-                            for (int j = 0; j < CH / 4; j++) xa[j] = __ldcg((const float4 *)(add + c0) + j);
+                            for (int j = 0; j < CH / 4; j++) xa[j] = RW ? ((const float4 *)(add + c0))[j] : __ldcg((const float4 *)(add + c0) + j);
                         }
                         tc_wait_ld();
                         if (h1) add4<CH>(r, x1);
@@ -319,6 +337,11 @@ template <int N, int P, int NL> __global__ void __launch_bounds__(SP_THREADS, ge
                         }
                     }
                 }
+                if (RW != 0 && a.rem_rowptr) { // the remainder buffer is free again
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(reme0 + 8u * (own & 1u));
+                    own++;
+                }
                 __threadfence();
                 bar_sync(3, 128);
                 if (et == 0) {
@@ -331,6 +354,60 @@ template <int N, int P, int NL> __global__ void __launch_bounds__(SP_THREADS, ge
             __syncwarp();
             if (lane == 0) mbar_arrive(acce0 + 8u * ab);
             it += len, seg++;
+        }
+    } else if (RW != 0 && warp >= EPILOGUE_WARP0 + 4) {
+        // ------------------------------------------------------------------------------------------ remainder
+        // a pair of threads per row of the panel this CTA owns: at NL = 8 the two take alternate entries of the row, at
+        // NL = 16 both take every entry and each gathers its 16-byte half of B's row
+        constexpr int LPR = NL / 8;
+        const uint32_t rt = threadIdx.x - (EPILOGUE_WARP0 + 4) * 32, rrow = rt >> 1, sub = rt & 1u;
+        const uint32_t slice = LPR == 2 ? sub : 0u, estart = LPR == 2 ? 0u : sub, estep = LPR == 2 ? 1u : 2u;
+        const __half *B = (const __half *)a.B;
+        uint32_t it = 0, own = 0;
+        while (it < n_local && a.rem_rowptr) {
+            const uint32_t t = t0 + it, panel = t / KT, kt0 = t % KT, len = min(KT - kt0, n_local - it);
+            if (kt0 == 0) {
+                const uint32_t b = own & 1u;
+                mbar_wait(reme0 + 8u * b, ((own >> 1) & 1u) ^ 1u); // the epilogue has read what this buffer held two panels back
+                const uint32_t r = panel * SM_ROWS + rrow;
+                float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                if (r < a.n_rows) {
+                    const uint32_t e1 = a.rem_rowptr[r + 1];
+#pragma unroll 1
+                    for (uint32_t e = a.rem_rowptr[r] + estart; e < e1; e += 4u * estep) {
+                        uint32_t w[4];
+                        uint4 bb[4];
+#pragma unroll
+                        for (int j = 0; j < 4; j++) w[j] = e + j * estep < e1 ? __ldg(a.rem_pack + e + j * estep) : 0xffffffffu;
+#pragma unroll
+                        for (int j = 0; j < 4; j++)
+                            if (e + j * estep < e1) bb[j] = __ldg((const uint4 *)(B + (size_t)(w[j] >> 16) * NL + slice * 8u));
+#pragma unroll
+                        for (int j = 0; j < 4; j++)
+                            if (e + j * estep < e1) {
+                                const float v = __half2float(__ushort_as_half((unsigned short)(w[j] & 0xffffu)));
+                                const uint32_t q[4] = {bb[j].x, bb[j].y, bb[j].z, bb[j].w};
+#pragma unroll
+                                for (int k = 0; k < 4; k++) {
+                                    const float2 f = __half22float2(*(const __half2 *)&q[k]);
+                                    acc[2 * k] = fmaf(v, f.x, acc[2 * k]), acc[2 * k + 1] = fmaf(v, f.y, acc[2 * k + 1]);
+                                }
+                            }
+                    }
+                }
+                if (LPR == 1) {
+#pragma unroll
+                    for (int k = 0; k < 8; k++) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], 1);
+                }
+                if (LPR == 2 || sub == 0u) {
+                    float4 *dst = (float4 *)(rem_buf + (b * SM_ROWS + rrow) * NL + slice * 8u);
+                    dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]), dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(remf0 + 8u * b);
+                own++;
+            }
+            it += len;
         }
     }
     tc_fence_before();

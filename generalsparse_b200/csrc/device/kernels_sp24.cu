@@ -16,7 +16,9 @@ struct b200_sp24_plan {
     unsigned char *img = nullptr;
     uint32_t *out_row = nullptr, *flags = nullptr; // flags: grid ready + grid slot_free + n_panels panel_seq + rem_ctas rem_seq
     float *ws = nullptr, *c_add = nullptr;         // c_add: two buffers (launch parity) of n_panels * 128 x N fp32, when there is a remainder
-    uint32_t *rem_rowptr = nullptr, *rem_col = nullptr;
+    uint32_t *rem_rowptr = nullptr, *rem_col = nullptr, *rem_pack = nullptr; // rem_pack: column id << 16 | value bits, the fused pass's entry stream
+    bool fused = false;                                                       // the remainder is multiplied by warps of the 2:4 kernel itself
+    int threads = 0;
     uint16_t *rem_val = nullptr;
     uint32_t n_tiles = 0, k_tiles = 0, n_panels = 0, grid = 0, seq = 0, n_rows = 0, group = 1; // n_tiles: units of `group` panels x one k step
     uint64_t nnz = 0, rem_nnz = 0;
@@ -108,9 +110,9 @@ template <int N> __global__ void __launch_bounds__(REM_THREADS) k_b200_sp24_rem(
 
 namespace {
 
-template <int N, int P, int NL = N> void pick(const void *&fn, const void *&rem_fn, size_t &ring_bytes, int &stages, int &ctas)
+template <int N, int P, int NL = N, int RW = 0> void pick(const void *&fn, const void *&rem_fn, size_t &ring_bytes, int &stages, int &ctas)
 {
-    fn = (const void *)sp24::k_b200_sp24<N, P, NL>, rem_fn = (const void *)sp24::k_b200_sp24_rem<NL>;
+    fn = (const void *)sp24::k_b200_sp24<N, P, NL, RW>, rem_fn = (const void *)sp24::k_b200_sp24_rem<NL>;
     stages = sp24::geom<N, P>::STAGES, ctas = sp24::geom<N, P>::CTAS, ring_bytes = (size_t)sp24::geom<N, P>::RING_BYTES;
 }
 
@@ -222,6 +224,14 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     }
     pl->rem_nnz = im.rem_col.size();
     if (pl->rem_nnz && !allow_remainder) return fail(cudaErrorInvalidValue); // not a 2:4 matrix
+    // N <= 16: the remainder is multiplied inside the 2:4 kernel (b200_sp24.cuh), no second launch
+    pl->fused = pl->rem_nnz && p.N <= 16 && group == 1 && p.a.cols <= 65536 && env_int("GS_SP24_FUSED_REM", 1);
+    pl->threads = sp24::SP_THREADS + (pl->fused ? 8 * 32 : 0);
+    if (pl->fused) {
+        if (p.N == 8) pick<16, 1, 8, 8>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas);
+        else pick<16, 1, 16, 8>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas);
+        ring_bytes += 2 * sp24::SM_ROWS * p.N * 4; // the two remainder buffers behind the ring
+    }
     pl->n_panels = im.n_panels, pl->k_tiles = im.k_tiles, pl->n_tiles = im.n_panels / group * im.k_tiles, pl->nnz = im.nnz;
     pl->grid = (uint32_t)std::min<uint64_t>((uint64_t)env_int("GS_TILE_CTAS", sm_count), pl->n_tiles);
     if (pl->grid == 0 || (int)pl->grid > sm_count) return fail(cudaErrorInvalidValue); // the split-panel hand-off needs every CTA resident
@@ -245,7 +255,12 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     const size_t n_flags = (size_t)pl->grid * 2 + pl->n_panels + (size_t)pl->n_panels * 4;
     if ((e = cudaMalloc((void **)&pl->flags, n_flags * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMemsetAsync(pl->flags, 0, n_flags * 4, s)) != cudaSuccess) return fail(e);
-    if (pl->rem_nnz) {
+    if (pl->fused) {
+        std::vector<uint32_t> pack(im.rem_col.size());
+        for (size_t i = 0; i < pack.size(); i++) pack[i] = (im.rem_col[i] << 16) | im.rem_val[i];
+        if ((e = up((void **)&pl->rem_rowptr, im.rem_rowptr.data(), im.rem_rowptr.size() * 4)) != cudaSuccess) return fail(e);
+        if ((e = up((void **)&pl->rem_pack, pack.data(), pack.size() * 4)) != cudaSuccess) return fail(e);
+    } else if (pl->rem_nnz) {
         if ((e = up((void **)&pl->rem_rowptr, im.rem_rowptr.data(), im.rem_rowptr.size() * 4)) != cudaSuccess) return fail(e);
         if ((e = up((void **)&pl->rem_col, im.rem_col.data(), im.rem_col.size() * 4)) != cudaSuccess) return fail(e);
         if ((e = up((void **)&pl->rem_val, im.rem_val.data(), im.rem_val.size() * 2)) != cudaSuccess) return fail(e);
@@ -260,10 +275,10 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     // pass is meant to run beside the resident CTAs of the 2:4 kernel
     if ((e = cudaFuncSetAttribute(pl->rem_fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess) return fail(e);
     int occ = 0;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pl->fn, sp24::SP_THREADS, pl->smem)) != cudaSuccess) return fail(e);
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pl->fn, pl->threads, pl->smem)) != cudaSuccess) return fail(e);
     if (occ < 1) return fail(cudaErrorInvalidConfiguration);
     char rem[48] = "";
-    if (pl->rem_nnz) snprintf(rem, sizeof rem, ",+remainder %.1f%% (gather)", 100.0 * (double)pl->rem_nnz / (double)(pl->rem_nnz + pl->nnz));
+    if (pl->rem_nnz) snprintf(rem, sizeof rem, ",+remainder %.1f%% (%s)", 100.0 * (double)pl->rem_nnz / (double)(pl->rem_nnz + pl->nnz), pl->fused ? "8 warps of the owner CTA" : "gather pass");
     snprintf(pl->name, sizeof pl->name, "k_b200_sp24<N%d,f16,tcgen05.mma.sp m128n%dk32,%d panel%s/CTA,%d stages,streamK x%u,%d CTA/SM,pdl%s>", p.N, p.N < 16 ? 16 : p.N, group, group > 1 ? "s" : "", stages, pl->grid, occ,
              rem);
     if (env_int("GS_SP24_PROBE", 0)) {
@@ -288,7 +303,7 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
     cudaLaunchConfig_t cfg;
     float *c_add = nullptr;
     static const bool skip_rem = env_int("GS_SP24_SKIP_REM", 0) != 0; // timing experiments only: wrong results on a matrix with a remainder
-    if (pl->rem_nnz && !skip_rem) {
+    if (pl->rem_nnz && !skip_rem && !pl->fused) {
         c_add = pl->c_add + (size_t)(seq & 1u) * pl->n_panels * sp24::SM_ROWS * pl->N;
         sp24::rem_args r;
         r.rowptr = pl->rem_rowptr, r.col = pl->rem_col, r.val = pl->rem_val, r.B = p.B, r.c_add = c_add, r.rem_seq = rem_seq, r.panel_seq = panel_seq;
@@ -307,17 +322,18 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
     static const uint32_t pf_ahead = (uint32_t)env_int("GS_SP24_PREFETCH", sp24::PF_AHEAD);
     a.pf_ahead = pf_ahead;
     a.dbg = pl->dbg;
+    a.rem_rowptr = (pl->fused && !skip_rem) ? pl->rem_rowptr : nullptr, a.rem_pack = pl->rem_pack, a.B = p.B, a.n_rows = pl->n_rows;
     void *args[] = {&a, &pl->b_map};
     memset(&cfg, 0, sizeof cfg);
-    cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(sp24::SP_THREADS), cfg.dynamicSmemBytes = pl->smem, cfg.stream = s;
-    cfg.attrs = attr, cfg.numAttrs = (p.pdl || pl->rem_nnz) ? 1 : 0; // behind its own remainder launch the 2:4 kernel always overlaps: the flags order them
+    cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(pl->threads), cfg.dynamicSmemBytes = pl->smem, cfg.stream = s;
+    cfg.attrs = attr, cfg.numAttrs = (p.pdl || (pl->rem_nnz && !pl->fused)) ? 1 : 0; // behind its own remainder launch the 2:4 kernel always overlaps: the flags order them
     return cudaLaunchKernelExC(&cfg, pl->fn, args);
 }
 
 void b200_sp24_free(b200_sp24_plan *pl)
 {
     if (!pl) return;
-    cudaFree(pl->img), cudaFree(pl->out_row), cudaFree(pl->flags), cudaFree(pl->ws), cudaFree(pl->c_add), cudaFree(pl->rem_rowptr), cudaFree(pl->rem_col), cudaFree(pl->rem_val),
+    cudaFree(pl->img), cudaFree(pl->out_row), cudaFree(pl->flags), cudaFree(pl->ws), cudaFree(pl->c_add), cudaFree(pl->rem_rowptr), cudaFree(pl->rem_col), cudaFree(pl->rem_val), cudaFree(pl->rem_pack),
         cudaFree(pl->dbg);
     delete pl;
 }
@@ -327,11 +343,11 @@ const char *b200_sp24_kernel_name(const b200_sp24_plan *pl) { return pl ? pl->na
 // bytes one launch must move: the image, the remainder's streams, the output row table, B and C once each
 uint64_t b200_sp24_bytes(const b200_sp24_plan *pl, uint64_t rows, uint64_t cols)
 {
-    return (uint64_t)pl->n_tiles * pl->group * sp24::IMG_BYTES + pl->rem_nnz * 6 + (pl->rem_nnz ? ((uint64_t)pl->n_rows + 1) * 4 : 0) + (uint64_t)pl->n_panels * sp24::SM_ROWS * 4 + cols * pl->N * 2 +
+    return (uint64_t)pl->n_tiles * pl->group * sp24::IMG_BYTES + pl->rem_nnz * (pl->fused ? 4 : 6) + (pl->rem_nnz ? ((uint64_t)pl->n_rows + 1) * 4 : 0) + (uint64_t)pl->n_panels * sp24::SM_ROWS * 4 + cols * pl->N * 2 +
            rows * pl->N * 2;
 }
 uint64_t b200_sp24_remainder(const b200_sp24_plan *pl) { return pl->rem_nnz; }
-int b200_sp24_launches(const b200_sp24_plan *pl) { return pl->rem_nnz ? 2 : 1; }
+int b200_sp24_launches(const b200_sp24_plan *pl) { return pl->rem_nnz && !pl->fused ? 2 : 1; }
 cudaError_t b200_sp24_probe(const b200_sp24_plan *pl, uint32_t *out512)
 {
     if (!pl->dbg) return cudaErrorInvalidValue;

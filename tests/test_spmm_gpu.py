@@ -289,8 +289,8 @@ def test_b200_nnz_rejects_narrow_dense(engine):
 @pytest.mark.parametrize("chain", ["thread_total", "warp_total"])
 def test_b200_sp24_kernel(engine, N, chain):
     """2:4 sparse tensor-core path (HALF): exact in reference mode, in tolerance on random values.  Exactly 2:4-pruned
-    matrices have no remainder (one launch); unstructured ones send what the pattern cannot hold through the gather
-    pass (two launches).  1000 x 4096 splits its 8 row panels over all CTAs (stream-K hand-off), 300 x 1000 has a
+    matrices have no remainder (one launch); unstructured ones send what the pattern cannot hold through remainder
+    warps of the same kernel (N <= 16) or through the gather pass (two launches).  1000 x 4096 splits its 8 row panels over all CTAs (stream-K hand-off), 300 x 1000 has a
     ragged K tail and empty rows, 130 x 72 is smaller than two tiles"""
     from generalsparse_b200 import synth
     from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
@@ -303,8 +303,8 @@ def test_b200_sp24_kernel(engine, N, chain):
         B1 = np.ones((cols, N), dtype=np.float32)
         C, plan = _run(engine, chain, nrows, cols, rr, cc, None, B1, N, S, 1, half=True, kernel="b200_sp24")
         assert "k_b200_sp24" in plan.kernel_name
-        if launches is not None:
-            assert plan.launch_count == launches, plan.kernel_name
+        if launches is not None:  # up to N=16 the remainder is multiplied by warps of the 2:4 kernel itself: one launch
+            assert plan.launch_count == (1 if N <= 16 else launches), plan.kernel_name
         ref = oracle_spmm_f32(nrows, N, indptr, cc, np.ones(len(rr), np.float32), B1)
         assert np.array_equal(C.astype(np.float32), ref), plan.kernel_name
         vals = synth.synth_values(len(rr), seed=5).astype(np.float16).astype(np.float32)
@@ -340,14 +340,32 @@ def test_b200_sp24_panels_per_cta(engine, monkeypatch, N, panels):
         assert np.array_equal(plan.output(), C)
 
 
-@pytest.mark.parametrize("kind,kw", [("nm24", {}), ("uniform", dict(density=0.3))])
-def test_b200_sp24_overlapped_launches_keep_order(engine, kind, kw):
+@pytest.mark.parametrize("N", [8, 16])
+def test_b200_sp24_remainder_as_separate_pass(engine, monkeypatch, N):
+    """GS_SP24_FUSED_REM=0: the gather pass in front of the 2:4 launch also at the widths that fuse it by default"""
+    from generalsparse_b200 import synth
+    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
+    monkeypatch.setenv("GS_SP24_FUSED_REM", "0")
+    nrows, cols = 1000, 4096
+    rr, cc = _matrix("uniform", nrows, cols, seed=99, density=0.3)
+    vals = synth.synth_values(len(rr), seed=7).astype(np.float16).astype(np.float32)
+    B = synth.synth_dense(cols, N, seed=7).astype(np.float16).astype(np.float32)
+    C, plan = _run(engine, "thread_total", nrows, cols, rr, cc, vals, B, N, 8, 1, half=True, kernel="b200_sp24")
+    assert plan.launch_count == 2, plan.kernel_name
+    indptr = csr_from_coo(nrows, rr)
+    _check(C, oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B), oracle_spmm_absrow(nrows, N, indptr, cc, vals, B) * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+    plan.run(6)
+    assert np.array_equal(plan.output(), C)
+
+
+@pytest.mark.parametrize("kind,kw,N", [("nm24", {}, 32), ("uniform", dict(density=0.3), 32), ("uniform", dict(density=0.3), 16)])
+def test_b200_sp24_overlapped_launches_keep_order(engine, kind, kw, N):
     """back-to-back launches of one plan overlap on the SMs: C must end up as the LAST launch's product although the
     dense matrix alternates between launches (with a remainder: two product buffers alternate as well)"""
     import torch
     from generalsparse_b200 import api, synth
     from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
-    rows, cols, N = 3000, 4096, 32
+    rows, cols = 3000, 4096
     r, c = _matrix(kind, rows, cols, seed=91, **kw)
     vals = synth.synth_values(len(r), seed=61).astype(np.float16).astype(np.float32)
     ms = api.MetaDataSet.from_coo(rows, cols, r, c, vals)
