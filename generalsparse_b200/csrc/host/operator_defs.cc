@@ -319,6 +319,98 @@ class fixed_interval_nnz_direction_thread_blocking_operator : public basic_opera
     bool row_rel_, nz_rel_, pad_;
 };
 
+class fixed_interval_nnz_direction_tblock_blocking_operator : public basic_operator { // operator/fixed_interval_nnz_direction_tblock_blocking_operator.cc
+  public:
+    fixed_interval_nnz_direction_tblock_blocking_operator(std::shared_ptr<code_generator> cg, int nnz_per_bmtb, bool nnz_padding)
+        : basic_operator("fixed_interval_nnz_direction_tblock_blocking_operator", std::move(cg), DISTRIBUTING_OP), k_(nnz_per_bmtb), pad_(nnz_padding)
+    {
+        GS_REQUIRE(nnz_per_bmtb > 0, "nnz_per_BMTB must be > 0");
+        params = ",nnz_per_BMTB:" + std::to_string(nnz_per_bmtb);
+    }
+    uint64_t get_nnz_per_BMTB() const { return k_; }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    { // :38-55: the first distributing operator, nothing implemented yet
+        return h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty() && h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id).empty();
+    }
+    bool is_valid_according_to_metadata() override
+    { // :57-94: no level opened yet, no interleaved storage
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        return !ms.is_exist(TBLOCK_META, "first_row_indices", id) && !ms.is_exist(WARP_META, "first_row_indices", id) && !ms.is_exist(THREAD_META, "first_row_indices", id) &&
+               !ms.is_exist(GLOBAL_META, "nz_row_indices_after_interlance_storage", id);
+    }
+    void set_padding_to_false() override { pad_ = false; }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        steps::recs r;
+        if (pad_) steps::modify_by_nnz_pad(ms, id, k_, pad_bound(), &r);
+        steps::get_begin_rows_after_fixed_blocking_in_nnz_direction(ms, TBLOCK_META, id, k_, &r);
+        steps::get_begin_nzs_after_fixed_blocking_in_nnz_direction(ms, TBLOCK_META, id, k_, &r);
+        if (pad_) steps::get_BMTB_size(ms, id, &r);
+        append(transform_seq, r);
+        code_generator_ptr->open_spec_level_of_paral(TBLOCK_META);
+        is_run = true;
+    }
+
+  private:
+    uint64_t k_;
+    bool pad_;
+};
+
+class fixed_interval_nnz_direction_warp_blocking_operator : public basic_operator { // operator/fixed_interval_nnz_direction_warp_blocking_operator.cc
+  public:
+    fixed_interval_nnz_direction_warp_blocking_operator(std::shared_ptr<code_generator> cg, int nnz_per_bmw, bool row_rel, bool nz_rel, bool nnz_padding)
+        : basic_operator("fixed_interval_nnz_direction_warp_blocking_operator", std::move(cg), DISTRIBUTING_OP), k_(nnz_per_bmw), row_rel_(row_rel), nz_rel_(nz_rel),
+          pad_(nnz_padding)
+    {
+        GS_REQUIRE(nnz_per_bmw > 0, "nnz_per_BMW must be > 0");
+        params = ",nnz_per_BMW:" + std::to_string(nnz_per_bmw);
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    { // :44-92: only nnz-direction tblock blocking may precede, and its interval must be a multiple of this one
+        if (!h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty()) return false;
+        for (const auto &op : h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id)) {
+            auto tb = std::dynamic_pointer_cast<fixed_interval_nnz_direction_tblock_blocking_operator>(op);
+            if (!tb || tb->get_nnz_per_BMTB() % k_ != 0) return false;
+        }
+        return true;
+    }
+    bool is_valid_according_to_metadata() override
+    { // :94-143: relative indices need the tblock level, padding forbids it
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        const bool has_tb = ms.is_exist(TBLOCK_META, "first_row_indices", id);
+        if (ms.is_exist(WARP_META, "first_row_indices", id) || ms.is_exist(THREAD_META, "first_row_indices", id)) return false;
+        if ((row_rel_ || nz_rel_) && !has_tb) return false;
+        if (pad_ && has_tb) return false;
+        return !ms.is_exist(GLOBAL_META, "nz_row_indices_after_interlance_storage", id);
+    }
+    void set_padding_to_false() override { pad_ = false; }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        steps::recs r;
+        const bool has_tb = ms.is_exist(TBLOCK_META, "first_row_indices", id);
+        if (pad_) steps::modify_by_nnz_pad(ms, id, k_, pad_bound(), &r);
+        steps::get_begin_rows_after_fixed_blocking_in_nnz_direction(ms, WARP_META, id, k_, &r);
+        steps::get_begin_nzs_after_fixed_blocking_in_nnz_direction(ms, WARP_META, id, k_, &r);
+        if (row_rel_) steps::get_begin_rows_of_BMW_after_fixed_blocking_in_nnz_direction_relative_to_BMTB(ms, id, k_, &r);
+        if (nz_rel_) steps::get_begin_nzs_of_BMW_after_fixed_blocking_in_nnz_direction_relative_to_BMTB(ms, id, k_, &r);
+        if (has_tb) steps::get_begin_children_of_parent_after_blocking(ms, WARP_META, TBLOCK_META, id, &r);
+        steps::get_BMW_size_of_global(ms, id, &r);
+        append(transform_seq, r);
+        code_generator_ptr->open_spec_level_of_paral(WARP_META);
+        is_run = true;
+    }
+
+  private:
+    uint64_t k_;
+    bool row_rel_, nz_rel_, pad_;
+};
+
 // balanced_interval_row_direction_{tblock,warp,thread}_blocking_operator (operator.hpp:871,823,777), top level
 class balanced_interval_row_direction_blocking_operator : public basic_operator {
   public:
@@ -621,6 +713,8 @@ const std::vector<std::string> &operator_names()
                                                "fixed_interval_row_direction_thread_blocking_operator",
                                                "fixed_interval_col_direction_thread_blocking_operator",
                                                "fixed_interval_nnz_direction_thread_blocking_operator",
+                                               "fixed_interval_nnz_direction_warp_blocking_operator",
+                                               "fixed_interval_nnz_direction_tblock_blocking_operator",
                                                "balanced_interval_row_direction_tblock_blocking_operator",
                                                "balanced_interval_row_direction_warp_blocking_operator",
                                                "balanced_interval_row_direction_thread_blocking_operator",
@@ -652,6 +746,10 @@ std::shared_ptr<basic_operator> make_operator(const std::string &op, std::shared
         return need(5), std::make_shared<fixed_interval_col_direction_thread_blocking_operator>(cg, (int)a[0], a[1] != 0, a[2] != 0, a[3] != 0, a[4] != 0, h);
     if (op == "fixed_interval_nnz_direction_thread_blocking_operator")
         return need(4), std::make_shared<fixed_interval_nnz_direction_thread_blocking_operator>(cg, (int)a[0], a[1] != 0, a[2] != 0, a[3] != 0);
+    if (op == "fixed_interval_nnz_direction_warp_blocking_operator")
+        return need(4), std::make_shared<fixed_interval_nnz_direction_warp_blocking_operator>(cg, (int)a[0], a[1] != 0, a[2] != 0, a[3] != 0);
+    if (op == "fixed_interval_nnz_direction_tblock_blocking_operator")
+        return need(2), std::make_shared<fixed_interval_nnz_direction_tblock_blocking_operator>(cg, (int)a[0], a[1] != 0);
     if (op == "balanced_interval_row_direction_tblock_blocking_operator")
         return need(1), std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, TBLOCK_META, (int)a[0]);
     // the warp and thread flavours take (nnz_per_interval, row_index_is_relative, nz_index_is_relative) like the reference;

@@ -523,7 +523,66 @@ void get_begin_nzs_after_fixed_blocking_in_nnz_direction(meta_data_set &ms, POS_
     record(rec, std::string("get_begin_nzs_of_") + level_tag(pos) + "_after_fixed_blocking_in_nnz_direction", id, ",nnz_per_" + std::string(level_tag(pos)) + ":" + std::to_string(k));
 }
 
+void get_begin_rows_of_BMW_after_fixed_blocking_in_nnz_direction_relative_to_BMTB(meta_data_set &ms, int id, uint64_t k, recs *rec)
+{
+    GS_REQUIRE(k >= 1, "nnz_per_block must be >= 1");
+    const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    const universal_array &PR = ms.get(TBLOCK_META, "first_row_indices", id), &PN = ms.get(TBLOCK_META, "first_nz_indices", id);
+    std::vector<uint64_t> v;
+    uint64_t p = 0;
+    for (uint64_t i = 0; i < R.get_len(); i += k) {
+        GS_REQUIRE(p + 1 < PN.get_len(), "BMW beyond the last BMTB");
+        if (i >= PN.u[p + 1]) p++;
+        GS_REQUIRE(p < PR.get_len() && R.u[i] >= PR.u[p], "BMW starts above its BMTB's first row");
+        v.push_back(R.u[i] - PR.u[p]);
+    }
+    ms.add_u(WARP_META, "first_row_indices_relative_to_BMTB", id, std::move(v));
+    record(rec, "get_begin_rows_of_BMW_after_fixed_blocking_in_nnz_direction_relative_to_BMTB", id, ",nnz_per_BMW:" + std::to_string(k));
+}
+
+void get_begin_nzs_of_BMW_after_fixed_blocking_in_nnz_direction_relative_to_BMTB(meta_data_set &ms, int id, uint64_t k, recs *rec)
+{
+    GS_REQUIRE(k >= 1, "nnz_per_block must be >= 1");
+    const uint64_t nnz = ms.get(GLOBAL_META, "nz_row_indices", id).get_len();
+    const universal_array &PN = ms.get(TBLOCK_META, "first_nz_indices", id);
+    std::vector<uint64_t> v;
+    uint64_t p = 0;
+    for (uint64_t i = 0; i < nnz; i += k) {
+        GS_REQUIRE(p + 1 < PN.get_len(), "BMW beyond the last BMTB");
+        if (i >= PN.u[p + 1]) {
+            GS_REQUIRE(i == PN.u[p + 1], "nnz_per_BMTB is not a multiple of nnz_per_BMW"); // the reference asserts the same
+            p++;
+        }
+        v.push_back(i - PN.u[p]);
+    }
+    ms.add_u(WARP_META, "first_nz_indices_relative_to_BMTB", id, std::move(v));
+    record(rec, "get_begin_nzs_of_BMW_after_fixed_blocking_in_nnz_direction_relative_to_BMTB", id, ",nnz_per_BMW:" + std::to_string(k));
+}
+
 // --------------------------------------------------------------------------------------------------- sizes
+void get_BMW_size_of_global(meta_data_set &ms, int id, recs *rec)
+{
+    const universal_array &W = ms.get(WARP_META, "first_nz_indices", id);
+    GS_REQUIRE(W.get_len() >= 2, "no BMW");
+    const uint64_t size = W.u[1] - W.u[0];
+    for (uint64_t w = 0; w + 1 < W.get_len(); w++) {
+        GS_REQUIRE(W.u[w + 1] > W.u[w], "empty BMW");
+        if (W.u[w + 1] - W.u[w] != size) return; // not uniform: nothing emitted, nothing recorded
+    }
+    ms.add_u(GLOBAL_META, "BMW_size_of_each_blk", id, std::vector<uint64_t>{size});
+    record(rec, "get_BMW_size_of_each_parent", id, ",parent_pos:GLOBAL_META");
+}
+
+void get_BMTB_size(meta_data_set &ms, int id, recs *rec)
+{
+    const universal_array &T = ms.get(TBLOCK_META, "first_nz_indices", id);
+    GS_REQUIRE(T.get_len() >= 2, "no BMTB");
+    const uint64_t size = T.u[1] - T.u[0];
+    for (uint64_t t = 0; t + 1 < T.get_len(); t++) GS_REQUIRE(T.u[t + 1] > T.u[t] && T.u[t + 1] - T.u[t] == size, "the BMTB sizes are not the same");
+    ms.add_u(GLOBAL_META, "BMTB_size_of_each_blk", id, std::vector<uint64_t>{size});
+    record(rec, "get_BMTB_size", id, ",parent_pos:GLOBAL_META");
+}
+
 void get_BMT_size_of_each_parent(meta_data_set &ms, POS_TYPE parent_pos, int id, bool row_direction_blocking, recs *rec)
 {
     const universal_array &T = ms.get(THREAD_META, "first_nz_indices", id);
@@ -901,7 +960,9 @@ const std::vector<std::string> &covered_reference_step_names()
         "get_begin_rows_of_BMT_after_fixed_blocking_in_nnz_direction", "get_begin_nzs_of_BMT_after_fixed_blocking_in_nnz_direction",
         "get_begin_rows_of_BMW_after_fixed_blocking_in_nnz_direction", "get_begin_nzs_of_BMW_after_fixed_blocking_in_nnz_direction",
         "get_begin_rows_of_BMTB_after_fixed_blocking_in_nnz_direction", "get_begin_nzs_of_BMTB_after_fixed_blocking_in_nnz_direction",
-        "get_BMT_size_of_each_parent",
+        "get_begin_rows_of_BMW_after_fixed_blocking_in_nnz_direction_relative_to_BMTB",
+        "get_begin_nzs_of_BMW_after_fixed_blocking_in_nnz_direction_relative_to_BMTB",
+        "get_BMT_size_of_each_parent", "get_BMW_size_of_each_parent", "get_BMTB_size",
         "thread_bit_map", "parent_bit_map_of_thread", "segment_empty_flag", "segment_empty_row_indices", "segment_offset", "segment_ptr",
         "get_begin_rows_after_merge_thread", "get_begin_nzs_after_merge_thread", "get_begin_rows_relative_to_parent_after_merge_thread",
         "get_begin_nzs_relative_to_parent_after_merge_thread", "get_begin_BMTs_after_merge_thread",

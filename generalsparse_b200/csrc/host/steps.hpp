@@ -69,11 +69,19 @@ void get_begin_nzs_after_fixed_blocking_in_col_direction_relative_to_parents(met
 // get_begin_{rows,nzs}_of_{BMT,BMW,BMTB}_after_fixed_blocking_in_nnz_direction.cc
 void get_begin_rows_after_fixed_blocking_in_nnz_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t nnz_per_blk, recs *rec = nullptr);
 void get_begin_nzs_after_fixed_blocking_in_nnz_direction(meta_data_set &ms, POS_TYPE pos, int id, uint64_t nnz_per_blk, recs *rec = nullptr);
+// get_begin_{rows,nzs}_of_BMW_after_fixed_blocking_in_nnz_direction_relative_to_BMTB.cc (no sentinel; the parent index moves on by
+// at most one block per BMW, as in the reference)
+void get_begin_rows_of_BMW_after_fixed_blocking_in_nnz_direction_relative_to_BMTB(meta_data_set &ms, int id, uint64_t nnz_per_blk, recs *rec = nullptr);
+void get_begin_nzs_of_BMW_after_fixed_blocking_in_nnz_direction_relative_to_BMTB(meta_data_set &ms, int id, uint64_t nnz_per_blk, recs *rec = nullptr);
 
 // ---- sizes ---------------------------------------------------------------------------------------
 // get_BMT_size_of_each_parent.cc: emits <parent>/BMT_size_of_each_blk only when all BMTs of a parent have
 // the same nnz; returns silently (no output) otherwise.
 void get_BMT_size_of_each_parent(meta_data_set &ms, POS_TYPE parent_pos, int id, bool row_direction_blocking, recs *rec = nullptr);
+// get_BMW_size_of_each_parent.cc with parent GLOBAL_META: GLOBAL/BMW_size_of_each_blk = [size] when all BMWs hold the same nnz,
+// nothing otherwise.  get_BMTB_size.cc: GLOBAL/BMTB_size_of_each_blk = [size]; BMTBs of different sizes are an error there.
+void get_BMW_size_of_global(meta_data_set &ms, int id, recs *rec = nullptr);
+void get_BMTB_size(meta_data_set &ms, int id, recs *rec = nullptr);
 
 // ---- bit maps and segments (thread_bit_map.cc, parent_bit_map_of_thread.cc, segment_*.cc) ----------
 void thread_bit_map(meta_data_set &ms, bool parent_flag, uint64_t parent_size, int id, recs *rec = nullptr);

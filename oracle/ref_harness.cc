@@ -54,7 +54,7 @@ static const char *k_names[] = {
     "first_row_indices", "first_nz_indices", "first_row_indices_without_ending",
     "first_row_indices_relative_to_BMTB", "first_nz_indices_relative_to_BMTB",
     "first_row_indices_relative_to_BMW", "first_nz_indices_relative_to_BMW",
-    "first_BMW_indices", "first_BMT_indices", "BMT_size_of_each_blk", "BMW_size_of_each_blk", "BMTB_size",
+    "first_BMW_indices", "first_BMT_indices", "BMT_size_of_each_blk", "BMW_size_of_each_blk", "BMTB_size", "BMTB_size_of_each_blk",
     "nz_row_indices_after_interlance_storage", "nz_col_indices_after_interlance_storage",
     "nz_vals_after_interlance_storage", "thread_bit_map", "bit_map_of_thread", "segment_ptr", "segment_offset",
     "segment_empty_flag", "segment_empty_row_indices", "first_row_indices_without_ending_relative_to_BMTB",

@@ -95,6 +95,20 @@ OPS_CASES = [
                         ("fixed_interval_col_direction_thread_blocking_operator", 4, 0, 0, 1, 0)], 8),
     ("tb8_colthread4_rel", [("fixed_interval_row_direction_tblock_blocking_operator", 8, 0),
                             ("fixed_interval_col_direction_thread_blocking_operator", 4, 1, 1, 1, 0)], 8),
+    # nnz-direction blocking above the thread level (fixed_interval_nnz_direction_{tblock,warp}_blocking_operator)
+    ("nnz_tblock64", [("fixed_interval_nnz_direction_tblock_blocking_operator", 64, 0)], 8),
+    ("nnz_tblock64_pad", [("fixed_interval_nnz_direction_tblock_blocking_operator", 64, 1)], 8),
+    ("nnz_warp32", [("fixed_interval_nnz_direction_warp_blocking_operator", 32, 0, 0, 0)], 8),
+    ("nnz_warp32_pad", [("fixed_interval_nnz_direction_warp_blocking_operator", 32, 0, 0, 1)], 8),
+    ("nnz_tb128pad_w32", [("fixed_interval_nnz_direction_tblock_blocking_operator", 128, 1),
+                          ("fixed_interval_nnz_direction_warp_blocking_operator", 32, 0, 0, 0)], 8),
+    ("nnz_tb128pad_w32_t8", [("fixed_interval_nnz_direction_tblock_blocking_operator", 128, 1),
+                             ("fixed_interval_nnz_direction_warp_blocking_operator", 32, 0, 0, 0),
+                             ("fixed_interval_nnz_direction_thread_blocking_operator", 8, 0, 0, 0)], 8),
+    ("nnz_tb128pad_w32rel", [("fixed_interval_nnz_direction_tblock_blocking_operator", 128, 1),
+                             ("fixed_interval_nnz_direction_warp_blocking_operator", 32, 1, 1, 0)], 8),
+    ("nnz_w32pad_t8", [("fixed_interval_nnz_direction_warp_blocking_operator", 32, 0, 0, 1),
+                       ("fixed_interval_nnz_direction_thread_blocking_operator", 8, 0, 0, 0)], 8),
 ]
 
 
