@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--n", "--dense-n", dest="n", type=int, default=8,
                     help="dense width N (8 = the bench line; 16..256 run the tile kernel). Under torchrun spell it --dense-n (its parser claims --n)")
     ap.add_argument("--density", type=float, default=0.30, help="c2: keep probability of the pruned weight (0.30 = C2, 0.10 = C3)")
-    ap.add_argument("--kernel", default="auto", help="auto: the stream row kernel at N=8, the 2:4 kernel (image + fused remainder) at N=16 on the 70 % weight and on 2:4 weights, the tcgen05 tile kernel otherwise; c4: auto = b200_nnz, reference = the chain's own family kernel")
+    ap.add_argument("--kernel", default="auto", help="auto: the 2:4 kernel (image + tile-local remainder) at N <= 32 on the 70 % weight and on 2:4 weights, else the stream row kernel at N=8 and the tcgen05 tile kernel from N=16; c4: auto = b200_nnz, reference = the chain's own family kernel")
     ap.add_argument("--pattern", default="unstructured", choices=["unstructured", "nm24"],
                     help="c2: Bernoulli(density) mask, or exactly 2 of every 4 consecutive columns kept (C3's 2:4 half; runs b200_sp24 under --kernel auto)")
     ap.add_argument("--copies", type=int, default=0, help="device copies of A to rotate over (0 = enough to exceed L2 3x)")
@@ -271,9 +271,10 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     N, half = args.n, True
     if args.kernel == "auto":
-        # measured on one B200: gather kernel at N=8 (12.1 us; 2:4 image + fused remainder 11.9 us, a tie),
-        # 2:4 image + fused remainder at N=16 (15.3 us against 16.6 us for the tile kernel), tile kernel from N=32 up
-        args.kernel = "b200_sp24" if args.pattern == "nm24" or (N == 16 and abs(DENSITY - 0.30) < 1e-9) else "b200_row_smem" if N < 16 else "b200_tcgen05"
+        # measured on one B200: on the 70 % weight the 2:4 image with the tile-local remainder at N <= 32
+        # (9.2 / 10.4 / 14.5 us at N = 8 / 16 / 32 against 12.1 us for the gather kernel and 16.6 / 17.9 us for the tile kernel);
+        # the image is 1.125 bytes per matrix element whatever the sparsity, so sparser weights stay on the gather / tile kernels
+        args.kernel = "b200_sp24" if args.pattern == "nm24" or (N <= 32 and abs(DENSITY - 0.30) < 1e-9) else "b200_row_smem" if N < 16 else "b200_tcgen05"
     hbm_peak, peak_src = peaks()
 
     # ---- the global matrix: `world` FFN-sized blocks stacked; this rank's nnz-balanced row block ------------------------

@@ -17,7 +17,7 @@ SYMBOLS = [
     "gsh_metadata_check", "gsh_config_load", "gsh_config_set", "gsh_config_get",
     "gsh_session_create", "gsh_session_free", "gsh_session_add_and_run", "gsh_session_record_count", "gsh_session_record",
     "gsh_session_run_family", "gsh_session_compile", "gsh_session_plan_desc", "gsh_partition_rows_balanced",
-    "gsh_tile_stream_roundtrip", "gsh_sp24_roundtrip",
+    "gsh_tile_stream_roundtrip", "gsh_sp24_roundtrip", "gsh_sp24_tiled_roundtrip",
     "gs_create", "gs_destroy", "gs_stream", "gs_upload_array", "gs_upload_session", "gs_upload_session_as", "gs_plan_create", "gs_plan_destroy",
     "gs_plan_set_kernel", "gs_set_dense", "gs_set_dense_device", "gs_launch", "gs_run", "gs_get_output", "gs_output_device",
     "gs_spmm_host", "gs_spmm_host_async", "gs_synchronize", "gs_plan_algorithmic_bytes", "gs_plan_launch_count", "gs_plan_kernel_name", "gs_plan_sp24_probe", "gs_execute",
@@ -86,6 +86,7 @@ def lib():
         "gs_plan_algorithmic_bytes": (u64, [vp]), "gs_plan_launch_count": (i32, [vp]), "gs_plan_kernel_name": (cp, [vp]),
         "gs_execute": (i32, [vp, i32, P(C.c_float), P(C.c_float)]),
         "gsh_sp24_roundtrip": (i32, [vp, vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),
+        "gsh_sp24_tiled_roundtrip": (i32, [vp, vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),
         "gs_plan_sp24_probe": (i32, [vp, vp]),
     }
     for name, (res, args) in sig.items():

@@ -370,4 +370,23 @@ gs_status gsh_sp24_roundtrip(const uint32_t *rowptr, const uint32_t *col, const 
     GS_API_END
 }
 
+gs_status gsh_sp24_tiled_roundtrip(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val, uint32_t n_rows, uint32_t n_cols, uint32_t row_bytes, uint16_t *dense_out, uint64_t *stats)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(rowptr && col && val && dense_out && stats && n_rows > 0 && n_cols > 0, "bad argument");
+    sp24_image im;
+    sp24_tiled t;
+    std::vector<uint16_t> dense;
+    try {
+        build_sp24_image(rowptr, col, val, n_rows, n_cols, 1, im);
+        localize_sp24_remainder(im, row_bytes, t);
+        expand_sp24_tiled(im, t, dense);
+    } catch (const std::exception &e) {
+        throw gs::Error(e.what());
+    }
+    std::copy(dense.begin(), dense.end(), dense_out);
+    stats[0] = t.bytes.size(), stats[1] = im.nnz, stats[2] = im.rem_col.size(), stats[3] = (uint64_t)im.n_panels * im.k_tiles, stats[4] = t.unit_bytes, stats[5] = t.max_entries;
+    GS_API_END
+}
+
 } // extern "C"

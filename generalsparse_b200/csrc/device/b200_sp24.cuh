@@ -21,6 +21,10 @@
 // owns a panel also owns its remainder rows; warps 8-15 (a pair of threads per row: two halves of the row's entries at
 // N=8, the two 16-byte halves of B's row at N=16) gather B from L2 while the tile loop runs, leave the fp32 product in
 // shared memory, and the epilogue adds it before the single rounding.  No second launch, no global hand-off.
+// Tile-local remainder (TL, N <= 32): the remainder is cut along the tiles and travels with them; warps 8-15 (a pair of threads
+// per tile row, accumulators in registers over the tiles of a segment) multiply a tile's entries with the 128 rows of B
+// that the tile's own multiplication has brought to shared memory -- no gather leaves the SM, the work is split exactly
+// like the tensor core's -- and hand the fp32 product of every segment to the epilogue through shared memory.
 // Work split, split-panel hand-off and the ordering between overlapped launches (panel_seq / slot_free flags, no
 // griddepcontrol.wait) are those of the tile kernel, b200_tile.cuh.
 #pragma once
@@ -52,6 +56,9 @@ struct sp24_args {
     const uint32_t *rem_rowptr, *rem_pack;
     const void *B;
     uint32_t n_rows;
+    // tile-local remainder (kernels instantiated with TL): every tile image is followed by the remainder entries of its 128 x 128 window
+    // (host/sp24_format.hpp, sp24_tiled); one bulk copy of unit_bytes brings both, B's 128 rows sit b_off bytes into the stage
+    uint32_t unit_bytes, b_off, stage_bytes, rem_on;
     uint32_t *dbg; // probe: CTA 0 leaves the 4 metadata columns of stage 0 (128 lanes x 4 words) here, or null
 };
 
@@ -90,6 +97,8 @@ template <int CH> __device__ __forceinline__ void tc_ld_issue(uint32_t taddr, ui
     }
 }
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// acc += a * b, a and b fp16 bits: the product is exact in fp32, one rounding (FHFMA)
+__device__ __forceinline__ void fma_f16(float &acc, unsigned short a, unsigned short b) { asm("fma.rn.f32.f16 %0, %1, %2, %0;" : "+f"(acc) : "h"(a), "h"(b)); }
 template <int CH> __device__ __forceinline__ void add4(uint32_t (&r)[CH], const float4 (&x)[CH / 4])
 {
 #pragma unroll
@@ -134,13 +143,17 @@ template <int N, int P> struct geom {
 
 // N: the width the tensor core multiplies (a multiple of 16); NL <= N: the width of B and C in memory (NL = 8 runs as N = 16,
 // the tensor map returns zeros for the columns B does not have)
-template <int N, int P, int NL, int RW> __global__ void __launch_bounds__(SP_THREADS + 32 * RW, (RW ? 2 : geom<N, P>::MIN_CTAS)) k_b200_sp24(sp24_args a, const __grid_constant__ CUtensorMap b_map)
+// TL: 0 = no tile-local remainder, else the stages of the copy ring (4 where two CTAs with four stages fit an SM, else 3)
+template <int N, int P, int NL, int RW, int TL = 0> __global__ void __launch_bounds__(SP_THREADS + 32 * RW, (RW ? 2 : geom<N, P>::MIN_CTAS)) k_b200_sp24(sp24_args a, const __grid_constant__ CUtensorMap b_map)
 {
     using G = geom<N, P>;
-    constexpr int S = G::STAGES, ACC = G::ACC, CH = G::CH;
+    constexpr int S = TL ? TL : G::STAGES, ACC = G::ACC, CH = G::CH;
     static_assert(NL % CH == 0, "chunk");
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    static_assert(RW == 0 || (RW == 8 && NL <= 16 && P == 1 && G::CTAS == 2), "remainder warps");
+    static_assert(RW == 0 || (RW == 8 && NL <= (TL ? 32 : 16) && P == 1 && G::CTAS == 2), "remainder warps");
+    static_assert(TL == 0 || ((TL == 3 || TL == 4) && RW == 8), "the tile-local remainder is multiplied by the remainder warps");
+    // bytes of a unit in global memory (= one bulk copy), offset of B's rows inside a stage, stage stride
+    const uint32_t UNIT = TL ? a.unit_bytes : (uint32_t)G::UNIT_BYTES, BOFF = TL ? a.b_off : (uint32_t)G::UNIT_BYTES, STG = TL ? a.stage_bytes : (uint32_t)G::STAGE_BYTES;
     __shared__ __align__(8) uint64_t bars[2 * S + 8];
     __shared__ uint32_t tmem_slot;
     const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u; // 1024-byte alignment of the stages (128-byte swizzle atoms)
@@ -156,10 +169,10 @@ template <int N, int P, int NL, int RW> __global__ void __launch_bounds__(SP_THR
     const uint32_t full0 = bar0, empty0 = bar0 + 8u * S, accf0 = bar0 + 16u * S, acce0 = accf0 + 16u;
     // rem_full[b] = acce0 + 16 + 8 b, rem_empty[b] = + 16: the two remainder buffers behind the ring (128 rows x NL fp32 each)
     const uint32_t remf0 = acce0 + 16u, reme0 = remf0 + 16u;
-    float *rem_buf = (float *)(smem_raw + (smem0 - smem_u32(smem_raw)) + G::RING_BYTES);
+    float *rem_buf = (float *)(smem_raw + (smem0 - smem_u32(smem_raw)) + S * STG);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < S; s++) mbar_init(&bars[s], 1), mbar_init(&bars[S + s], 1);
+        for (int s = 0; s < S; s++) mbar_init(&bars[s], 1), mbar_init(&bars[S + s], TL ? 1 + RW : 1); // TL: the remainder warps read the stage too
         mbar_init(&bars[2 * S], 1), mbar_init(&bars[2 * S + 1], 1);
         mbar_init(&bars[2 * S + 2], 4), mbar_init(&bars[2 * S + 3], 4);
         if (RW) mbar_init(&bars[2 * S + 4], RW), mbar_init(&bars[2 * S + 5], RW), mbar_init(&bars[2 * S + 6], 4), mbar_init(&bars[2 * S + 7], 4);
@@ -177,18 +190,18 @@ template <int N, int P, int NL, int RW> __global__ void __launch_bounds__(SP_THR
     if (warp == PRODUCER_WARP) {
         // ------------------------------------------------------------------------------------------ copies
         if (lane == 0) {
-            const unsigned char *img = a.img + (size_t)t0 * G::UNIT_BYTES;
+            const unsigned char *img = a.img + (size_t)t0 * UNIT;
             const uint32_t pf = a.pf_ahead ? (uint32_t)S + a.pf_ahead : 0u;
-            for (uint32_t it = 0; it < pf && it < n_local; it++) l2_prefetch_bulk(img + (size_t)it * G::UNIT_BYTES, G::UNIT_BYTES);
+            for (uint32_t it = 0; it < pf && it < n_local; it++) l2_prefetch_bulk(img + (size_t)it * UNIT, UNIT);
             uint32_t s = 0, ph = 0, kt = t0 % KT;
             for (uint32_t it = 0; it < n_local; it++) {
-                if (pf && it + pf < n_local) l2_prefetch_bulk(img + (size_t)(it + pf) * G::UNIT_BYTES, G::UNIT_BYTES);
+                if (pf && it + pf < n_local) l2_prefetch_bulk(img + (size_t)(it + pf) * UNIT, UNIT);
                 mbar_wait(empty0 + 8u * s, ph ^ 1u); // the tensor core has finished reading the stage
-                const uint32_t st = smem0 + s * G::STAGE_BYTES, fb = full0 + 8u * s;
-                mbar_expect_tx(fb, (uint32_t)G::STAGE_BYTES);
-                bulk_load(st, img + (size_t)it * G::UNIT_BYTES, G::UNIT_BYTES, fb);
+                const uint32_t st = smem0 + s * STG, fb = full0 + 8u * s;
+                mbar_expect_tx(fb, UNIT + (uint32_t)G::B_BYTES);
+                bulk_load(st, img + (size_t)it * UNIT, UNIT, fb);
 #pragma unroll
-                for (int g = 0; g < G::GROUPS; g++) tma_load_2d(st + G::UNIT_BYTES + g * G::GROUP_BYTES, &b_map, (uint32_t)(g * G::ATOM_N), kt * SK, fb); // rows past K come back as zeros
+                for (int g = 0; g < G::GROUPS; g++) tma_load_2d(st + BOFF + g * G::GROUP_BYTES, &b_map, (uint32_t)(g * G::ATOM_N), kt * SK, fb); // rows past K come back as zeros
                 if (++kt == KT) kt = 0;
                 if (++s == S) s = 0, ph ^= 1u;
             }
@@ -199,7 +212,7 @@ template <int N, int P, int NL, int RW> __global__ void __launch_bounds__(SP_THR
         if (lane == 0) {
             uint32_t it = 0, seg = 0, s = 0, ph = 0, kt0 = t0 % KT;
             const uint64_t adesc0 = smem_desc(smem0, 16, 1024, 2u), edesc0 = smem_desc(smem0 + IMG_A, 128, 128, 0u),
-                           bdesc0 = smem_desc(smem0 + G::UNIT_BYTES, G::GROUP_BYTES, G::SBO, G::LAYOUT);
+                           bdesc0 = smem_desc(smem0 + BOFF, G::GROUP_BYTES, G::SBO, G::LAYOUT);
             while (it < n_local) {
                 const uint32_t len = min(KT - kt0, n_local - it), ab = seg % ACC;
                 mbar_wait(acce0 + 8u * ab, ((seg / ACC) & 1u) ^ 1u);
@@ -207,7 +220,7 @@ template <int N, int P, int NL, int RW> __global__ void __launch_bounds__(SP_THR
                 for (uint32_t i = 0; i < len; i++) {
                     mbar_wait(full0 + 8u * s, ph);
                     tc_fence_after();
-                    const uint64_t so = (uint64_t)(s * (G::STAGE_BYTES >> 4));
+                    const uint64_t so = (uint64_t)(s * (STG >> 4));
 #pragma unroll
                     for (uint32_t h = 0; h < (uint32_t)P; h++) {
                         const uint64_t ho = so + (uint64_t)(h * (IMG_BYTES >> 4));
@@ -272,14 +285,25 @@ template <int N, int P, int NL, int RW> __global__ void __launch_bounds__(SP_THR
                 for (int h = 0; h < P; h++) {
                     const uint32_t taddr = tmem_base + ((q * 32u) << 16) + (ab * P + h) * N;
                     float *slot = a.ws + (((size_t)cta * P + h) * SM_ROWS + rip) * NL;
+                    if constexpr (TL) mbar_wait(remf0, seg & 1u); // the segment's share of the remainder goes into the partial
 #pragma unroll 1
                     for (int c0 = 0; c0 < NL; c0 += CH) {
                         uint32_t r[CH];
+                        float4 xa[CH / 4];
                         tc_ld_issue<CH>(taddr + c0, r);
+                        if constexpr (TL) {
+#pragma unroll
+                            for (int j = 0; j < CH / 4; j++) xa[j] = ((const float4 *)(rem_buf + rip * NL + c0))[j];
+                        }
                         tc_wait_ld();
+                        if constexpr (TL) add4<CH>(r, xa);
 #pragma unroll
                         for (int j = 0; j < CH / 4; j++) __stcg((uint4 *)(slot + c0) + j, make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]));
                     }
+                }
+                if constexpr (TL) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(reme0);
                 }
                 __threadfence();
                 bar_sync(3, 128);
@@ -290,7 +314,10 @@ template <int N, int P, int NL, int RW> __global__ void __launch_bounds__(SP_THR
                 for (int h = 0; h < P; h++) {
                     const uint32_t panel = unit_panel * P + h, taddr = tmem_base + ((q * 32u) << 16) + (ab * P + h) * N;
                     const float *add;
-                    if constexpr (RW != 0) { // the remainder warps of this CTA left the product of the panel's remainder rows in shared memory
+                    if constexpr (TL) { // the segment's remainder product, single buffer
+                        add = rem_buf + rip * NL;
+                        mbar_wait(remf0, seg & 1u);
+                    } else if constexpr (RW != 0) { // the remainder warps of this CTA left the product of the panel's remainder rows in shared memory
                         add = a.rem_rowptr ? rem_buf + ((own & 1u) * SM_ROWS + rip) * NL : nullptr;
                         if (add) mbar_wait(remf0 + 8u * (own & 1u), (own >> 1) & 1u);
                     } else add = (a.c_add && orow[h] != 0xffffffffu) ? a.c_add + ((size_t)panel * SM_ROWS + rip) * NL : nullptr;
@@ -337,7 +364,10 @@ template <int N, int P, int NL, int RW> __global__ void __launch_bounds__(SP_THR
                         }
                     }
                 }
-                if (RW != 0 && a.rem_rowptr) { // the remainder buffer is free again
+                if constexpr (TL) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(reme0);
+                } else if (RW != 0 && a.rem_rowptr) { // the remainder buffer is free again
                     __syncwarp();
                     if (lane == 0) mbar_arrive(reme0 + 8u * (own & 1u));
                     own++;
@@ -353,6 +383,74 @@ template <int N, int P, int NL, int RW> __global__ void __launch_bounds__(SP_THR
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acce0 + 8u * ab);
+            it += len, seg++;
+        }
+    } else if (TL && warp >= EPILOGUE_WARP0 + 4) {
+        // ------------------------------------------------------------------------------------------ remainder, tile-local
+        // a pair of threads per tile row; NL = 8: the two take alternate entries, NL = 16: each takes a 16-byte half of B's
+        // row, NL = 32: each takes 32 bytes.  B's rows lie as the tensor map swizzled them; an entry carries the byte offset of
+        // its row's chunk 0 (host/sp24_format.hpp, sp24_b_row_offset), chunk c is at offset ^ (c << 4).  fp16 x fp16 + fp32 in
+        // one instruction (fma.rn.f32.f16: the exact product, one rounding -- what fmaf of the converted operands gives).
+        constexpr int CPT = NL == 32 ? 2 : 1, NA = 8 * CPT;
+        const uint32_t rt = threadIdx.x - (EPILOGUE_WARP0 + 4) * 32, rrow = rt >> 1, sub = rt & 1u;
+        const uint32_t estart = NL == 8 ? sub : 0u, estep = NL == 8 ? 2u : 1u, c16 = NL == 8 ? 0u : sub * CPT;
+        const unsigned char *ring = smem_raw + (smem0 - smem_u32(smem_raw));
+        uint32_t it = 0, seg = 0, s = 0, ph = 0;
+        while (it < n_local) {
+            const uint32_t kt0 = (t0 + it) % KT, len = min(KT - kt0, n_local - it);
+            float acc[NA];
+#pragma unroll
+            for (int j = 0; j < NA; j++) acc[j] = 0.f;
+            for (uint32_t i = 0; i < len; i++) {
+                mbar_wait(full0 + 8u * s, ph);
+                if (a.rem_on) {
+                    const unsigned char *st = ring + s * STG, *bs = st + BOFF;
+                    const unsigned short *start = (const unsigned short *)(st + IMG_BYTES);
+                    const uint32_t *ent = (const uint32_t *)(st + IMG_BYTES + 272);
+                    const uint32_t e1 = start[rrow + 1];
+                    uint32_t e = start[rrow] + estart;
+                    // two entries per round; the next round's entry words are requested before this round's rows of B
+                    uint32_t w0 = e < e1 ? ent[e] : 0u, w1 = e + estep < e1 ? ent[e + estep] : 0u;
+#pragma unroll 1
+                    for (; e < e1; e += 2u * estep) {
+                        const bool two = e + estep < e1; // a missing second entry reads row 0 and is not added
+                        const uint32_t n0 = e + 2u * estep < e1 ? ent[e + 2u * estep] : 0u, n1 = e + 3u * estep < e1 ? ent[e + 3u * estep] : 0u;
+                        uint4 b0[CPT], b1[CPT];
+#pragma unroll
+                        for (int c = 0; c < CPT; c++) {
+                            b0[c] = *(const uint4 *)(bs + ((w0 >> 16) ^ ((c16 + c) << 4)));
+                            b1[c] = *(const uint4 *)(bs + ((w1 >> 16) ^ ((c16 + c) << 4)));
+                        }
+                        const unsigned short v0 = (unsigned short)(w0 & 0xffffu), v1 = (unsigned short)(w1 & 0xffffu);
+#pragma unroll
+                        for (int c = 0; c < CPT; c++) {
+                            const uint32_t q0[4] = {b0[c].x, b0[c].y, b0[c].z, b0[c].w}, q1[4] = {b1[c].x, b1[c].y, b1[c].z, b1[c].w};
+#pragma unroll
+                            for (int k = 0; k < 4; k++) fma_f16(acc[8 * c + 2 * k], v0, (unsigned short)(q0[k] & 0xffffu)), fma_f16(acc[8 * c + 2 * k + 1], v0, (unsigned short)(q0[k] >> 16));
+                            if (two) {
+#pragma unroll
+                                for (int k = 0; k < 4; k++) fma_f16(acc[8 * c + 2 * k], v1, (unsigned short)(q1[k] & 0xffffu)), fma_f16(acc[8 * c + 2 * k + 1], v1, (unsigned short)(q1[k] >> 16));
+                            }
+                        }
+                        w0 = n0, w1 = n1;
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(empty0 + 8u * s); // this warp has read the stage
+                if (++s == S) s = 0, ph ^= 1u;
+            }
+            mbar_wait(reme0, (seg & 1u) ^ 1u); // the epilogue has read the previous segment's product
+            if (NL == 8) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], 1);
+            }
+            if (NL != 8 || sub == 0u) {
+                float4 *dst = (float4 *)(rem_buf + rrow * NL + (NL == 8 ? 0u : sub * NA));
+#pragma unroll
+                for (int j = 0; j < NA / 4; j++) dst[j] = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(remf0);
             it += len, seg++;
         }
     } else if (RW != 0 && warp >= EPILOGUE_WARP0 + 4) {

@@ -18,6 +18,8 @@ struct b200_sp24_plan {
     float *ws = nullptr, *c_add = nullptr;         // c_add: two buffers (launch parity) of n_panels * 128 x N fp32, when there is a remainder
     uint32_t *rem_rowptr = nullptr, *rem_col = nullptr, *rem_pack = nullptr; // rem_pack: column id << 16 | value bits, the fused pass's entry stream
     bool fused = false;                                                       // the remainder is multiplied by warps of the 2:4 kernel itself
+    bool tiled = false;                                                       // ... from tile-local blocks that travel with the tile images (sp24_tiled)
+    uint32_t unit_bytes = 0, b_off = 0, stage_bytes = 0;
     int threads = 0;
     uint16_t *rem_val = nullptr;
     uint32_t n_tiles = 0, k_tiles = 0, n_panels = 0, grid = 0, seq = 0, n_rows = 0, group = 1; // n_tiles: units of `group` panels x one k step
@@ -25,7 +27,7 @@ struct b200_sp24_plan {
     size_t smem = 0;
     const void *fn = nullptr, *rem_fn = nullptr;
     int N = 0;
-    char name[128] = {0};
+    char name[192] = {0};
     CUtensorMap b_map;              // the dense matrix as TMA boxes of 128 k rows x one swizzle atom of columns
     const void *b_mapped = nullptr; // the device pointer b_map was encoded for
     uint32_t K = 0;
@@ -115,6 +117,23 @@ template <int N, int P, int NL = N, int RW = 0> void pick(const void *&fn, const
     fn = (const void *)sp24::k_b200_sp24<N, P, NL, RW>, rem_fn = (const void *)sp24::k_b200_sp24_rem<NL>;
     stages = sp24::geom<N, P>::STAGES, ctas = sp24::geom<N, P>::CTAS, ring_bytes = (size_t)sp24::geom<N, P>::RING_BYTES;
 }
+// tile-local remainder: the stage holds the unit (image + remainder block, rounded up to 1 KB) and B's 128 rows
+int env_int(const char *name, int dflt)
+{
+    const char *v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+
+constexpr size_t TILED_SMEM_MAX = (228 * 1024 - 2 * (1024 + 2048 + 64)) / 2; // two CTAs per SM: alignment slack, static and reserved shared memory
+template <int N, int NL> void pick_tiled(b200_sp24_plan *pl, size_t &ring_bytes, int &stages)
+{
+    pl->b_off = (pl->unit_bytes + 1023u) & ~1023u, pl->stage_bytes = pl->b_off + (uint32_t)sp24::geom<N, 1>::B_BYTES;
+    const size_t rem = (size_t)sp24::SM_ROWS * NL * 4; // the segment's remainder product
+    stages = (N <= 16 && 4 * (size_t)pl->stage_bytes + rem <= TILED_SMEM_MAX && env_int("GS_SP24_TL_STAGES", 4) >= 4) ? 4 : 3;
+    if constexpr (N <= 16) pl->fn = stages == 4 ? (const void *)sp24::k_b200_sp24<N, 1, NL, 8, 4> : (const void *)sp24::k_b200_sp24<N, 1, NL, 8, 3>;
+    else pl->fn = (const void *)sp24::k_b200_sp24<N, 1, NL, 8, 3>;
+    ring_bytes = (size_t)stages * pl->stage_bytes + rem;
+}
 
 typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
                                     CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -147,11 +166,6 @@ cudaError_t encode_b_map(b200_sp24_plan *pl, const void *B)
     return cudaSuccess;
 }
 
-int env_int(const char *name, int dflt)
-{
-    const char *v = getenv(name);
-    return v && *v ? atoi(v) : dflt;
-}
 
 } // namespace
 
@@ -224,10 +238,34 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     }
     pl->rem_nnz = im.rem_col.size();
     if (pl->rem_nnz && !allow_remainder) return fail(cudaErrorInvalidValue); // not a 2:4 matrix
-    // N <= 16: the remainder is multiplied inside the 2:4 kernel (b200_sp24.cuh), no second launch
-    pl->fused = pl->rem_nnz && p.N <= 16 && group == 1 && p.a.cols <= 65536 && env_int("GS_SP24_FUSED_REM", 1);
+    // The remainder is multiplied inside the 2:4 kernel (b200_sp24.cuh), no second launch.  GS_SP24_FUSED_REM: 2 (default) = from
+    // tile-local blocks at N <= 32, as long as two CTAs still fit an SM and the padding to the largest block costs < 10 % of the
+    // stream; 1 = gathers by the CTA that owns the panel (N <= 16); 0 = a separate gather launch.
+    const int fuse = env_int("GS_SP24_FUSED_REM", 2);
+    gs::sp24_tiled tl;
+    if (pl->rem_nnz && fuse >= 2 && p.N <= 32 && group == 1) {
+        try {
+            gs::localize_sp24_remainder(im, p.N == 32 ? 64u : 32u, tl);
+        } catch (...) {
+            tl = gs::sp24_tiled();
+        }
+        if (tl.unit_bytes) {
+            const void *fn0 = pl->fn;
+            const size_t ring0 = ring_bytes;
+            const int stages0 = stages;
+            pl->unit_bytes = tl.unit_bytes;
+            if (p.N == 8) pick_tiled<16, 8>(pl, ring_bytes, stages);
+            else if (p.N == 16) pick_tiled<16, 16>(pl, ring_bytes, stages);
+            else pick_tiled<32, 32>(pl, ring_bytes, stages);
+            const double content = (double)im.bytes.size() + 4.0 * (double)pl->rem_nnz + (double)gs::SP24_REM_HEADER * (double)(im.bytes.size() / gs::SP24_TILE_BYTES);
+            pl->tiled = ring_bytes <= TILED_SMEM_MAX && (double)tl.bytes.size() <= 1.10 * content;
+            if (pl->tiled) ctas = 2;
+            else pl->fn = fn0, ring_bytes = ring0, stages = stages0, pl->unit_bytes = 0;
+        }
+    }
+    pl->fused = pl->tiled || (pl->rem_nnz && fuse >= 1 && p.N <= 16 && group == 1 && p.a.cols <= 65536);
     pl->threads = sp24::SP_THREADS + (pl->fused ? 8 * 32 : 0);
-    if (pl->fused) {
+    if (pl->fused && !pl->tiled) {
         if (p.N == 8) pick<16, 1, 8, 8>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas);
         else pick<16, 1, 16, 8>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas);
         ring_bytes += 2 * sp24::SM_ROWS * p.N * 4; // the two remainder buffers behind the ring
@@ -249,13 +287,15 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
         if (e2 != cudaSuccess) return e2;
         return bytes ? cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess;
     };
-    if ((e = up((void **)&pl->img, im.bytes.data(), im.bytes.size())) != cudaSuccess) return fail(e);
+    if ((e = pl->tiled ? up((void **)&pl->img, tl.bytes.data(), tl.bytes.size()) : up((void **)&pl->img, im.bytes.data(), im.bytes.size())) != cudaSuccess) return fail(e);
     if ((e = up((void **)&pl->out_row, orow.data(), orow.size() * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMalloc((void **)&pl->ws, (size_t)pl->grid * group * sp24::SM_ROWS * p.N * 4)) != cudaSuccess) return fail(e);
     const size_t n_flags = (size_t)pl->grid * 2 + pl->n_panels + (size_t)pl->n_panels * 4;
     if ((e = cudaMalloc((void **)&pl->flags, n_flags * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMemsetAsync(pl->flags, 0, n_flags * 4, s)) != cudaSuccess) return fail(e);
-    if (pl->fused) {
+    if (pl->tiled) {
+        // everything the kernel needs is in the units
+    } else if (pl->fused) {
         std::vector<uint32_t> pack(im.rem_col.size());
         for (size_t i = 0; i < pack.size(); i++) pack[i] = (im.rem_col[i] << 16) | im.rem_val[i];
         if ((e = up((void **)&pl->rem_rowptr, im.rem_rowptr.data(), im.rem_rowptr.size() * 4)) != cudaSuccess) return fail(e);
@@ -277,8 +317,11 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     int occ = 0;
     if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pl->fn, pl->threads, pl->smem)) != cudaSuccess) return fail(e);
     if (occ < 1) return fail(cudaErrorInvalidConfiguration);
+    // 512-thread CTAs at 64 registers fill the register file exactly with two CTAs; the occupancy calculator answers 1 for them, the
+    // hardware runs 2 (ncu: launch__occupancy_limit_registers = launch__occupancy_limit_shared_mem = 2, profiles/r1_sp24_summary.md)
+    if (pl->fused && ctas == 2 && occ == 1 && 2 * (pl->smem + 2048) <= 228 * 1024) occ = 2;
     char rem[48] = "";
-    if (pl->rem_nnz) snprintf(rem, sizeof rem, ",+remainder %.1f%% (%s)", 100.0 * (double)pl->rem_nnz / (double)(pl->rem_nnz + pl->nnz), pl->fused ? "8 warps of the owner CTA" : "gather pass");
+    if (pl->rem_nnz) snprintf(rem, sizeof rem, ",+remainder %.1f%% (%s)", 100.0 * (double)pl->rem_nnz / (double)(pl->rem_nnz + pl->nnz), pl->tiled ? "tile-local, 8 warps" : pl->fused ? "8 warps of the owner CTA" : "gather pass");
     snprintf(pl->name, sizeof pl->name, "k_b200_sp24<N%d,f16,tcgen05.mma.sp m128n%dk32,%d panel%s/CTA,%d stages,streamK x%u,%d CTA/SM,pdl%s>", p.N, p.N < 16 ? 16 : p.N, group, group > 1 ? "s" : "", stages, pl->grid, occ,
              rem);
     if (env_int("GS_SP24_PROBE", 0)) {
@@ -322,7 +365,8 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
     static const uint32_t pf_ahead = (uint32_t)env_int("GS_SP24_PREFETCH", sp24::PF_AHEAD);
     a.pf_ahead = pf_ahead;
     a.dbg = pl->dbg;
-    a.rem_rowptr = (pl->fused && !skip_rem) ? pl->rem_rowptr : nullptr, a.rem_pack = pl->rem_pack, a.B = p.B, a.n_rows = pl->n_rows;
+    a.rem_rowptr = (pl->fused && !pl->tiled && !skip_rem) ? pl->rem_rowptr : nullptr, a.rem_pack = pl->rem_pack, a.B = p.B, a.n_rows = pl->n_rows;
+    a.unit_bytes = pl->unit_bytes, a.b_off = pl->b_off, a.stage_bytes = pl->stage_bytes, a.rem_on = skip_rem ? 0u : 1u;
     void *args[] = {&a, &pl->b_map};
     memset(&cfg, 0, sizeof cfg);
     cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(pl->threads), cfg.dynamicSmemBytes = pl->smem, cfg.stream = s;
@@ -343,6 +387,8 @@ const char *b200_sp24_kernel_name(const b200_sp24_plan *pl) { return pl ? pl->na
 // bytes one launch must move: the image, the remainder's streams, the output row table, B and C once each
 uint64_t b200_sp24_bytes(const b200_sp24_plan *pl, uint64_t rows, uint64_t cols)
 {
+    if (pl->tiled) // the images, 4 bytes per remainder entry, the row starts of every block -- not the padding to the largest block
+        return (uint64_t)pl->n_tiles * (sp24::IMG_BYTES + gs::SP24_REM_HEADER) + pl->rem_nnz * 4 + (uint64_t)pl->n_panels * sp24::SM_ROWS * 4 + cols * pl->N * 2 + rows * pl->N * 2;
     return (uint64_t)pl->n_tiles * pl->group * sp24::IMG_BYTES + pl->rem_nnz * (pl->fused ? 4 : 6) + (pl->rem_nnz ? ((uint64_t)pl->n_rows + 1) * 4 : 0) + (uint64_t)pl->n_panels * sp24::SM_ROWS * 4 + cols * pl->N * 2 +
            rows * pl->N * 2;
 }

@@ -82,4 +82,67 @@ void expand_sp24_image(const sp24_image &im, std::vector<uint16_t> &dense)
     }
 }
 
+void localize_sp24_remainder(const sp24_image &im, uint32_t row_bytes, sp24_tiled &out)
+{
+    if (row_bytes != 32 && row_bytes != 64 && row_bytes != 128) throw std::invalid_argument("2:4 image: B's rows are 32, 64 or 128 bytes");
+    if (im.group != 1) throw std::invalid_argument("2:4 image: the tile-local remainder needs one panel per unit");
+    const uint64_t T = (uint64_t)im.n_panels * im.k_tiles;
+    std::vector<uint32_t> count(T, 0);
+    for (uint32_t r = 0; r < im.n_rows; r++)
+        for (uint32_t i = im.rem_rowptr[r]; i < im.rem_rowptr[r + 1]; i++) count[(uint64_t)(r / SP24_ROWS) * im.k_tiles + im.rem_col[i] / SP24_COLS]++;
+    uint32_t mx = 0;
+    for (uint64_t t = 0; t < T; t++) mx = std::max(mx, count[t]);
+    if (mx > 0xffffu) throw std::invalid_argument("2:4 image: too many remainder entries in one tile");
+    out = sp24_tiled();
+    out.max_entries = mx, out.row_bytes = row_bytes;
+    out.unit_bytes = SP24_TILE_BYTES + SP24_REM_HEADER + ((mx + 3u) & ~3u) * 4u;
+    out.bytes.assign(T * out.unit_bytes, 0);
+    for (uint64_t t = 0; t < T; t++) std::copy_n(im.bytes.begin() + t * SP24_TILE_BYTES, SP24_TILE_BYTES, out.bytes.begin() + t * out.unit_bytes);
+    // rows ascending and, inside a row, columns ascending: a row's entries of one tile are one run of the CSR row
+    std::vector<uint32_t> fill(im.k_tiles);
+    for (uint32_t p = 0; p < im.n_panels; p++) {
+        std::fill(fill.begin(), fill.end(), 0u);
+        for (uint32_t rr = 0; rr < SP24_ROWS; rr++) {
+            const uint32_t r = p * SP24_ROWS + rr;
+            for (uint32_t kt = 0; kt < im.k_tiles; kt++) {
+                uint8_t *h = out.bytes.data() + ((uint64_t)p * im.k_tiles + kt) * out.unit_bytes + SP24_TILE_BYTES + 2u * rr;
+                h[0] = (uint8_t)(fill[kt] & 0xff), h[1] = (uint8_t)(fill[kt] >> 8);
+            }
+            if (r >= im.n_rows) continue;
+            for (uint32_t i = im.rem_rowptr[r]; i < im.rem_rowptr[r + 1]; i++) {
+                const uint32_t kt = im.rem_col[i] / SP24_COLS, w = (sp24_b_row_offset(im.rem_col[i] % SP24_COLS, row_bytes) << 16) | im.rem_val[i];
+                uint8_t *e = out.bytes.data() + ((uint64_t)p * im.k_tiles + kt) * out.unit_bytes + SP24_TILE_BYTES + SP24_REM_HEADER + 4u * fill[kt]++;
+                e[0] = (uint8_t)w, e[1] = (uint8_t)(w >> 8), e[2] = (uint8_t)(w >> 16), e[3] = (uint8_t)(w >> 24);
+            }
+        }
+        for (uint32_t kt = 0; kt < im.k_tiles; kt++) {
+            uint8_t *h = out.bytes.data() + ((uint64_t)p * im.k_tiles + kt) * out.unit_bytes + SP24_TILE_BYTES + 2u * SP24_ROWS;
+            h[0] = (uint8_t)(fill[kt] & 0xff), h[1] = (uint8_t)(fill[kt] >> 8);
+        }
+    }
+}
+
+void expand_sp24_tiled(const sp24_image &geo, const sp24_tiled &t, std::vector<uint16_t> &dense)
+{
+    sp24_image im; // the images back to back, no remainder: expand, then add the tile-local entries
+    im.n_rows = geo.n_rows, im.n_cols = geo.n_cols, im.n_panels = geo.n_panels, im.k_tiles = geo.k_tiles, im.group = 1;
+    const uint64_t T = (uint64_t)im.n_panels * im.k_tiles;
+    im.bytes.resize(T * SP24_TILE_BYTES);
+    for (uint64_t i = 0; i < T; i++) std::copy_n(t.bytes.begin() + i * t.unit_bytes, SP24_TILE_BYTES, im.bytes.begin() + i * SP24_TILE_BYTES);
+    im.rem_rowptr.assign((size_t)im.n_rows + 1, 0);
+    expand_sp24_image(im, dense);
+    for (uint64_t i = 0; i < T; i++) {
+        const uint8_t *blk = t.bytes.data() + i * t.unit_bytes + SP24_TILE_BYTES, *ent = blk + SP24_REM_HEADER;
+        const uint64_t p = i / im.k_tiles, kt = i % im.k_tiles;
+        auto start = [&](uint32_t rr) { return (uint32_t)(blk[2 * rr] | (blk[2 * rr + 1] << 8)); };
+        for (uint32_t rr = 0; rr < SP24_ROWS; rr++)
+            for (uint32_t e = start(rr); e < start(rr + 1); e++) {
+                const uint32_t w = (uint32_t)ent[4 * e] | ((uint32_t)ent[4 * e + 1] << 8) | ((uint32_t)ent[4 * e + 2] << 16) | ((uint32_t)ent[4 * e + 3] << 24);
+                const uint64_t r = p * SP24_ROWS + rr, c = kt * SP24_COLS + (w >> 16) / t.row_bytes;
+                if (r >= im.n_rows || c >= im.n_cols || e >= t.max_entries || sp24_b_row_offset((w >> 16) / t.row_bytes, t.row_bytes) != (w >> 16)) throw std::invalid_argument("2:4 image: tile-local entry out of range");
+                dense[r * im.n_cols + c] = (uint16_t)(w & 0xffffu);
+            }
+    }
+}
+
 } // namespace gs

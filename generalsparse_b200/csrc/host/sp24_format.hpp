@@ -57,4 +57,23 @@ void build_sp24_image(const uint32_t *rowptr, const uint32_t *col, const uint16_
 // inverse, for tests: dense row-major n_rows x n_cols fp16 bits of image + remainder
 void expand_sp24_image(const sp24_image &im, std::vector<uint16_t> &dense);
 
+// The remainder cut along the tiles (group = 1 only): every tile image is followed by the remainder entries that fall into its
+// 128 x 128 window, so the CTA that multiplies the tile finds them -- and the 128 rows of B they need, which the tile's own
+// multiplication has brought to shared memory -- in the same stage of its copy ring.  A unit is `unit_bytes` =
+// SP24_TILE_BYTES + SP24_REM_HEADER + 4 * (the largest entry count of any tile, rounded up to 4) bytes:
+//   [0, 18 432)            the tile image as above;
+//   [18 432, + 272)        u16 start[129] (+ padding): entries of tile row r are start[r] .. start[r+1];
+//   [18 704, unit_bytes)   u32 entries, rows ascending, columns ascending inside a row: (where B's row lies << 16) | fp16 bits.
+// "Where B's row lies": the byte offset of the row's first 16-byte chunk inside the 128 x N piece of B as the tensor map
+// swizzles it into shared memory, k * row_bytes + (((k * row_bytes) >> 7) & (row_bytes / 16 - 1)) * 16 for column k of the
+// tile and row_bytes = 2 N (32, 64 or 128): the thread that wants chunk c of the row reads at (offset ^ (c << 4)).
+struct sp24_tiled {
+    uint32_t unit_bytes = 0, max_entries = 0, row_bytes = 0;
+    std::vector<uint8_t> bytes; // n_panels * k_tiles * unit_bytes
+};
+constexpr uint32_t SP24_REM_HEADER = 272;
+inline uint32_t sp24_b_row_offset(uint32_t k, uint32_t row_bytes) { return k * row_bytes + ((((k * row_bytes) >> 7) & (row_bytes / 16u - 1u)) << 4); }
+void localize_sp24_remainder(const sp24_image &im, uint32_t row_bytes, sp24_tiled &out);
+void expand_sp24_tiled(const sp24_image &im, const sp24_tiled &t, std::vector<uint16_t> &dense); // im: geometry only, its remainder arrays are not read
+
 } // namespace gs

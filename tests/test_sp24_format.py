@@ -99,3 +99,39 @@ def test_lone_elements_and_metadata_patterns(built_lib):
     indptr, col, v, dense = _csr_of(mask, seed=4)
     out, stats = _roundtrip(rows, cols, indptr, col, v)
     assert np.array_equal(out, dense.view(np.uint16)) and int(stats[2]) == 0
+
+
+def _tiled_roundtrip(rows, cols, indptr, col, vals16, row_bytes=32):
+    from generalsparse_b200 import _lib
+    L = _lib.lib()
+    dense = np.zeros((rows, cols), dtype=np.uint16)
+    stats = np.zeros(6, dtype=np.uint64)
+    rp = np.ascontiguousarray(indptr, dtype=np.uint32)
+    cc = np.ascontiguousarray(col, dtype=np.uint32)
+    vv = np.ascontiguousarray(vals16.view(np.uint16))
+    _lib.check(L.gsh_sp24_tiled_roundtrip(rp.ctypes.data_as(C.c_void_p), cc.ctypes.data_as(C.c_void_p), vv.ctypes.data_as(C.c_void_p), rows, cols, row_bytes,
+                                          dense.ctypes.data_as(C.c_void_p), stats.ctypes.data_as(C.c_void_p)))
+    return dense, stats
+
+
+@pytest.mark.parametrize("rows,cols,density,empty", [(130, 70, 0.3, 0), (300, 1000, 0.02, 60), (1000, 4096, 0.3, 0), (257, 129, 0.9, 3), (5, 3, 1.0, 0), (128, 128, 1.0, 0)])
+def test_remainder_cut_along_the_tiles(built_lib, rows, cols, density, empty):
+    """Every tile image followed by the remainder entries of its window: image + tile-local blocks expand to the matrix, the
+    unit is the image + 272 bytes of row starts + the largest block, and the blocks hold what the CSR remainder held."""
+    rng = np.random.default_rng(rows * cols + 1)
+    mask = rng.random((rows, cols)) < density
+    if empty:
+        mask[rng.choice(rows, empty, replace=False)] = False
+    indptr, col, v, dense = _csr_of(mask, seed=3)
+    out, stats = _tiled_roundtrip(rows, cols, indptr, col, v, 32 << (rows % 3))
+    assert np.array_equal(out, dense.view(np.uint16))
+    _, s0 = _roundtrip(rows, cols, indptr, col, v, 1)
+    assert int(stats[1]) == int(s0[1]) and int(stats[2]) == int(s0[2]) and int(stats[3]) == int(s0[3])
+    # the largest block, counted independently: third and fourth non-zeros of a 4-column group, per 128 x 128 window
+    pr, pc = -(-rows // 128) * 128, -(-cols // 128) * 128
+    m = np.zeros((pr, pc), dtype=bool)
+    m[:rows, :cols] = mask
+    extra = np.maximum(m.reshape(pr, pc // 4, 4).sum(axis=2) - 2, 0)
+    per_tile = extra.reshape(pr // 128, 128, pc // 128, 32).sum(axis=(1, 3))
+    assert int(stats[5]) == int(per_tile.max())
+    assert int(stats[4]) == 18432 + 272 + 4 * (-(-int(per_tile.max()) // 4) * 4) and int(stats[0]) == int(stats[3]) * int(stats[4])

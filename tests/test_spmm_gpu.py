@@ -290,7 +290,7 @@ def test_b200_nnz_rejects_narrow_dense(engine):
 def test_b200_sp24_kernel(engine, N, chain):
     """2:4 sparse tensor-core path (HALF): exact in reference mode, in tolerance on random values.  Exactly 2:4-pruned
     matrices have no remainder (one launch); unstructured ones send what the pattern cannot hold through remainder
-    warps of the same kernel (N <= 16) or through the gather pass (two launches).  1000 x 4096 splits its 8 row panels over all CTAs (stream-K hand-off), 300 x 1000 has a
+    warps of the same kernel (N <= 32: tile-local blocks that travel with the tile images) or through the gather pass (two launches).  1000 x 4096 splits its 8 row panels over all CTAs (stream-K hand-off), 300 x 1000 has a
     ragged K tail and empty rows, 130 x 72 is smaller than two tiles"""
     from generalsparse_b200 import synth
     from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
@@ -303,8 +303,9 @@ def test_b200_sp24_kernel(engine, N, chain):
         B1 = np.ones((cols, N), dtype=np.float32)
         C, plan = _run(engine, chain, nrows, cols, rr, cc, None, B1, N, S, 1, half=True, kernel="b200_sp24")
         assert "k_b200_sp24" in plan.kernel_name
-        if launches is not None:  # up to N=16 the remainder is multiplied by warps of the 2:4 kernel itself: one launch
-            assert plan.launch_count == (1 if N <= 16 else launches), plan.kernel_name
+        if launches is not None:  # up to N=32 the remainder is multiplied by warps of the 2:4 kernel itself: one launch
+            assert plan.launch_count == (1 if N <= 32 else launches), plan.kernel_name
+            assert ("tile-local" in plan.kernel_name) == (launches == 2 and N <= 32), plan.kernel_name
         ref = oracle_spmm_f32(nrows, N, indptr, cc, np.ones(len(rr), np.float32), B1)
         assert np.array_equal(C.astype(np.float32), ref), plan.kernel_name
         vals = synth.synth_values(len(rr), seed=5).astype(np.float16).astype(np.float32)
@@ -340,22 +341,56 @@ def test_b200_sp24_panels_per_cta(engine, monkeypatch, N, panels):
         assert np.array_equal(plan.output(), C)
 
 
-@pytest.mark.parametrize("N", [8, 16])
-def test_b200_sp24_remainder_as_separate_pass(engine, monkeypatch, N):
-    """GS_SP24_FUSED_REM=0: the gather pass in front of the 2:4 launch also at the widths that fuse it by default"""
+@pytest.mark.parametrize("N,mode", [(8, 0), (16, 0), (32, 0), (8, 1), (16, 1), (32, 1)])
+def test_b200_sp24_remainder_as_separate_pass(engine, monkeypatch, N, mode):
+    """GS_SP24_FUSED_REM=0: the gather pass in front of the 2:4 launch also at the widths that fuse it by default;
+    =1: gathers by eight warps of the CTA that owns the panel (N <= 16), not the tile-local blocks"""
     from generalsparse_b200 import synth
     from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
-    monkeypatch.setenv("GS_SP24_FUSED_REM", "0")
+    monkeypatch.setenv("GS_SP24_FUSED_REM", str(mode))
     nrows, cols = 1000, 4096
     rr, cc = _matrix("uniform", nrows, cols, seed=99, density=0.3)
     vals = synth.synth_values(len(rr), seed=7).astype(np.float16).astype(np.float32)
     B = synth.synth_dense(cols, N, seed=7).astype(np.float16).astype(np.float32)
     C, plan = _run(engine, "thread_total", nrows, cols, rr, cc, vals, B, N, 8, 1, half=True, kernel="b200_sp24")
-    assert plan.launch_count == 2, plan.kernel_name
+    assert plan.launch_count == (1 if mode == 1 and N <= 16 else 2) and "tile-local" not in plan.kernel_name, plan.kernel_name
+    assert ("owner CTA" in plan.kernel_name) == (mode == 1 and N <= 16), plan.kernel_name
     indptr = csr_from_coo(nrows, rr)
     _check(C, oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B), oracle_spmm_absrow(nrows, N, indptr, cc, vals, B) * 1e-2, 1e-2, abs_floor=2.0 ** -25)
     plan.run(6)
     assert np.array_equal(plan.output(), C)
+
+
+@pytest.mark.parametrize("N", [8, 16, 32])
+def test_b200_sp24_tile_local_remainder(engine, N):
+    """the remainder cut along the tiles: dense (a stage of the ring must hold the largest block: 42 % keeps two CTAs per
+    SM with three stages, 90 % does not fit and falls back), ragged K tail and row tail, a split panel per CTA (3000 x 4096: 24 panels over
+    148 CTAs, every CTA leaves or collects partials that carry a share of the remainder), and a matrix whose one dense
+    corner would make every unit as large as the largest (falls back as well); reference-mode ones exact"""
+    from generalsparse_b200 import synth
+    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    rng = np.random.default_rng(5)
+    corner = rng.random((2000, 2048)) < 0.05
+    corner[:128, :128] = True
+    cr, ccol = np.nonzero(corner)
+    mats = [("uniform", 3000, 4096, dict(density=0.3), True), ("uniform", 700, 1000, dict(density=0.42), True), ("uniform", 300, 520, dict(density=0.9), False),
+            ("uniform", 130, 72, dict(density=0.4), True), (None, 2000, 2048, None, False)]
+    for i, (kind, nrows, cols, kw, tiled) in enumerate(mats):
+        rr, cc = _matrix(kind, nrows, cols, seed=31 + i, **kw) if kind else (cr.astype(np.int64), ccol.astype(np.int64))
+        indptr = csr_from_coo(nrows, rr)
+        B1 = np.ones((cols, N), dtype=np.float32)
+        C, plan = _run(engine, "thread_total", nrows, cols, rr, cc, None, B1, N, 8, 1, half=True, kernel="b200_sp24")
+        assert ("tile-local" in plan.kernel_name) == tiled, plan.kernel_name
+        if tiled:
+            assert plan.launch_count == 1 and "2 CTA/SM" in plan.kernel_name, plan.kernel_name
+            assert ("3 stages" in plan.kernel_name) == (N == 32 or i == 1), plan.kernel_name
+        assert np.array_equal(C.astype(np.float32), oracle_spmm_f32(nrows, N, indptr, cc, np.ones(len(rr), np.float32), B1)), plan.kernel_name
+        vals = synth.synth_values(len(rr), seed=8).astype(np.float16).astype(np.float32)
+        B = synth.synth_dense(cols, N, seed=8).astype(np.float16).astype(np.float32)
+        C, plan = _run(engine, "thread_total", nrows, cols, rr, cc, vals, B, N, 8, 1, half=True, kernel="b200_sp24")
+        _check(C, oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B), oracle_spmm_absrow(nrows, N, indptr, cc, vals, B) * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        plan.run(9)
+        assert np.array_equal(plan.output(), C)
 
 
 @pytest.mark.parametrize("kind,kw,N", [("nm24", {}, 32), ("uniform", dict(density=0.3), 32), ("uniform", dict(density=0.3), 16)])
