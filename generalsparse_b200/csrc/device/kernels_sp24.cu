@@ -272,7 +272,7 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     }
     pl->n_panels = im.n_panels, pl->k_tiles = im.k_tiles, pl->n_tiles = im.n_panels / group * im.k_tiles, pl->nnz = im.nnz;
     pl->grid = (uint32_t)std::min<uint64_t>((uint64_t)env_int("GS_TILE_CTAS", sm_count), pl->n_tiles);
-    if (pl->grid == 0 || (int)pl->grid > sm_count) return fail(cudaErrorInvalidValue); // the split-panel hand-off needs every CTA resident
+    if (pl->grid == 0 || (int)pl->grid > sm_count * ctas) return fail(cudaErrorInvalidValue); // the split-panel hand-off needs every CTA resident
 
     std::vector<uint32_t> orow((size_t)im.n_panels * sp24::SM_ROWS, 0xffffffffu);
     for (uint32_t i = 0; i < n_rows; i++) {
