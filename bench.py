@@ -385,6 +385,7 @@ def main():
     tw0 = time.perf_counter()
     for i in range(e2e_steps):
         plans[i % copies].spmm_host_async_ptr(bp, cps[i % copies])
+    e2e_enqueue_s = time.perf_counter() - tw0  # the host's share: all calls issued, the device may still be working
     eng.synchronize()
     e2e_s = torch.tensor([time.perf_counter() - tw0, e2e_sync_s], device="cuda")
     if world > 1:
@@ -421,7 +422,7 @@ def main():
         "e2e": {"value": 2.0 * nnz_all * N * e2e_steps / e2e_s / 1e9, "unit": "GFLOP/s", "h2d_bytes_per_step": int(COLS * N * 2),
                 "d2h_bytes_per_step": int(desc.rows * N * 2), "ms_per_step": e2e_s / e2e_steps * 1e3, "steps": e2e_steps,
                 "api": "gs_spmm_host_async per step (pinned B in, pinned C out) + one gs_synchronize; results equal the blocking call: %s" % e2e_ok,
-                "blocking_ms_per_step": e2e_sync_s / e2e_steps * 1e3},
+                "blocking_ms_per_step": e2e_sync_s / e2e_steps * 1e3, "host_enqueue_ms_per_step": e2e_enqueue_s / e2e_steps * 1e3},
         "gpu_launches": args.steps * plans[0].launch_count, "clocks": clocks, "parity": parity,
     }
     if not args.no_cpu_baseline and world == 1:

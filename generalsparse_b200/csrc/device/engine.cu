@@ -36,12 +36,29 @@ struct gs_ctx {
     int sm_count = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t copy_in = nullptr, copy_out = nullptr; // gs_spmm_host_async: H2D and D2H beside the launch stream (lazy)
+    // gs_spmm_host_async rotates its launches over `stream` and `launch_extra[1 ...]`: consecutive steps use different plans, and a B200
+    // launch alone fills one CTA slot per SM of two, so the kernels of two steps run side by side instead of one after the other
+    static constexpr int MAX_LAUNCH = 4;
+    cudaStream_t launch_extra[MAX_LAUNCH] = {nullptr, nullptr, nullptr, nullptr}; // [0] unused: index 0 is `stream`
+    cudaEvent_t ev_join[MAX_LAUNCH] = {nullptr, nullptr, nullptr, nullptr};
+    unsigned async_turn = 0;
+    bool chain_extra[MAX_LAUNCH] = {false, false, false, false}, dirty_extra[MAX_LAUNCH] = {false, false, false, false};
+    // everything this library puts on `stream` comes after what gs_spmm_host_async has put on the other launch streams
+    void join_async()
+    {
+        for (int i = 1; i < MAX_LAUNCH; i++) {
+            if (!dirty_extra[i]) continue;
+            dirty_extra[i] = false;
+            if (cudaEventRecord(ev_join[i], launch_extra[i]) == cudaSuccess) cudaStreamWaitEvent(stream, ev_join[i], 0);
+        }
+    }
     // true while the last operation this library put on `stream` was a B200 row kernel launch: only then may the
     // next row launch use programmatic dependent launch (it reads A and the panel before griddepcontrol.wait)
     bool row_chain = false;
     cudaStream_t mem_stream()
     {
         row_chain = false;
+        join_async();
         return stream;
     }
     std::map<std::string, dev_array> arrays;
@@ -309,32 +326,28 @@ static bool uses_atomics(int family)
            family == GS_FAMILY_B200_NNZ;
 }
 
-static void enqueue(gs_plan *p)
+// which: 0 = ctx->stream, else one of gs_spmm_host_async's other launch streams
+static void enqueue(gs_plan *p, int which = 0)
 {
     GS_REQUIRE(p->B_use != nullptr, "gs_set_dense has not been called");
+    gs_ctx *ctx = p->ctx;
     gsd::launch_params lp = p->lp;
     lp.B = p->B_use, lp.C = p->C_dev, lp.N = p->N;
-    if (uses_atomics(p->kernel)) CUDA_TRY(cudaMemsetAsync(p->C_dev, 0, (size_t)p->desc.rows * p->N * p->esz(), p->ctx->mem_stream()));
-    if (p->kernel == GS_FAMILY_B200_ROW_SMEM) {
-        static const bool no_pdl = getenv("GS_NO_PDL") != nullptr;
-        lp.pdl = p->ctx->row_chain && !no_pdl;
-        CUDA_TRY(gsd::b200_row_launch(p->row_plan, lp, p->ctx->stream));
-        p->ctx->row_chain = true;
-    } else if (p->kernel == GS_FAMILY_B200_TCGEN05) {
-        static const bool no_pdl = getenv("GS_NO_PDL") != nullptr;
-        lp.pdl = p->ctx->row_chain && !no_pdl;
-        CUDA_TRY(gsd::b200_tile_launch(p->tile_plan, lp, p->ctx->stream));
-        p->ctx->row_chain = true;
-    } else if (p->kernel == GS_FAMILY_B200_SP24) {
-        static const bool no_pdl = getenv("GS_NO_PDL") != nullptr;
-        lp.pdl = p->ctx->row_chain && !no_pdl;
-        CUDA_TRY(gsd::b200_sp24_launch(p->sp24_plan, lp, p->ctx->stream));
-        p->ctx->row_chain = true;
-    } else if (p->kernel == GS_FAMILY_B200_NNZ) {
-        CUDA_TRY(gsd::b200_nnz_launch(lp, p->ctx->mem_stream()));
-    } else {
-        CUDA_TRY(gsd::launch_reference_family(p->kernel, lp, p->ctx->mem_stream()));
-    }
+    if (which == 0) ctx->join_async();
+    else ctx->dirty_extra[which] = true;
+    cudaStream_t st = which ? ctx->launch_extra[which] : ctx->stream;
+    bool &chain = which ? ctx->chain_extra[which] : ctx->row_chain;
+    static const bool no_pdl = getenv("GS_NO_PDL") != nullptr;
+    const bool b200_chain = p->kernel == GS_FAMILY_B200_ROW_SMEM || p->kernel == GS_FAMILY_B200_TCGEN05 || p->kernel == GS_FAMILY_B200_SP24;
+    if (!b200_chain) chain = false;
+    if (uses_atomics(p->kernel)) CUDA_TRY(cudaMemsetAsync(p->C_dev, 0, (size_t)p->desc.rows * p->N * p->esz(), st));
+    lp.pdl = chain && !no_pdl;
+    if (p->kernel == GS_FAMILY_B200_ROW_SMEM) CUDA_TRY(gsd::b200_row_launch(p->row_plan, lp, st));
+    else if (p->kernel == GS_FAMILY_B200_TCGEN05) CUDA_TRY(gsd::b200_tile_launch(p->tile_plan, lp, st));
+    else if (p->kernel == GS_FAMILY_B200_SP24) CUDA_TRY(gsd::b200_sp24_launch(p->sp24_plan, lp, st));
+    else if (p->kernel == GS_FAMILY_B200_NNZ) CUDA_TRY(gsd::b200_nnz_launch(lp, st));
+    else CUDA_TRY(gsd::launch_reference_family(p->kernel, lp, st));
+    if (b200_chain) chain = true;
 }
 
 extern "C" {
@@ -370,6 +383,10 @@ void gs_destroy(gs_ctx *ctx)
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
     if (ctx->copy_out) cudaStreamDestroy(ctx->copy_out);
+    for (int i = 1; i < gs_ctx::MAX_LAUNCH; i++) {
+        if (ctx->launch_extra[i]) cudaStreamDestroy(ctx->launch_extra[i]);
+        if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]);
+    }
     delete ctx;
 }
 
@@ -559,6 +576,22 @@ gs_status gs_spmm_host_async(gs_plan *p, const void *B_host, void *C_host)
     CUDA_TRY(cudaSetDevice(ctx->device));
     if (!ctx->copy_in) CUDA_TRY(cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking));
     if (!ctx->copy_out) CUDA_TRY(cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
+    // launch streams the steps rotate over (GS_ASYNC_STREAMS, 1 ... 4).  Measured on C2 N=8 (profiles/r1_sp24_summary.md): 22.6 / 16.5 /
+    // 11.9 / 11.1 us per step with 1 / 2 / 3 / 4 streams.  Every B200 launch needs all its CTAs resident (split-panel hand-off); two
+    // fit an SM side by side, and the CTAs of a younger grid are dispatched only after those of the older grids, so a queued third
+    // or fourth launch never holds slots an older one is waiting for.
+    static const int n_launch = [] {
+        const char *v = getenv("GS_ASYNC_STREAMS");
+        const int n = v && *v ? atoi(v) : 4;
+        return n < 1 ? 1 : n > gs_ctx::MAX_LAUNCH ? gs_ctx::MAX_LAUNCH : n;
+    }();
+    const int which = (int)(ctx->async_turn++ % (unsigned)n_launch);
+    if (which && !ctx->launch_extra[which]) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&ctx->launch_extra[which], cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&ctx->ev_join[which], cudaEventDisableTiming));
+    }
+    cudaStream_t ls = which ? ctx->launch_extra[which] : ctx->stream;
+    if (which == 0) ctx->join_async(); // only matters when a caller mixes this call with launches of its own on the main stream
     if (!p->ev_b) {
         CUDA_TRY(cudaEventCreateWithFlags(&p->ev_b, cudaEventDisableTiming));
         CUDA_TRY(cudaEventCreateWithFlags(&p->ev_k, cudaEventDisableTiming));
@@ -574,11 +607,13 @@ gs_status gs_spmm_host_async(gs_plan *p, const void *B_host, void *C_host)
     CUDA_TRY(cudaMemcpyAsync(p->B_dev, B_host, nb, cudaMemcpyHostToDevice, ctx->copy_in));
     CUDA_TRY(cudaEventRecord(p->ev_b, ctx->copy_in));
     p->B_use = p->B_dev;
-    // kernel: after B has landed and the plan's previous C has been read back
-    CUDA_TRY(cudaStreamWaitEvent(ctx->stream, p->ev_b, 0));
-    CUDA_TRY(cudaStreamWaitEvent(ctx->stream, p->ev_c, 0));
-    enqueue(p);
-    CUDA_TRY(cudaEventRecord(p->ev_k, ctx->stream));
+    // kernel: after B has landed, the plan's previous C has been read back and the plan's previous launch (it may sit on the other
+    // launch stream; the split-panel flags count launches of one plan in order) has finished
+    CUDA_TRY(cudaStreamWaitEvent(ls, p->ev_b, 0));
+    CUDA_TRY(cudaStreamWaitEvent(ls, p->ev_c, 0));
+    CUDA_TRY(cudaStreamWaitEvent(ls, p->ev_k, 0));
+    enqueue(p, which);
+    CUDA_TRY(cudaEventRecord(p->ev_k, ls));
     CUDA_TRY(cudaStreamWaitEvent(ctx->copy_out, p->ev_k, 0));
     CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, nc, cudaMemcpyDeviceToHost, ctx->copy_out));
     CUDA_TRY(cudaEventRecord(p->ev_c, ctx->copy_out));
@@ -591,6 +626,10 @@ gs_status gs_synchronize(gs_ctx *ctx)
     GS_REQUIRE(ctx, "null argument");
     CUDA_TRY(cudaSetDevice(ctx->device));
     CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    for (int i = 1; i < gs_ctx::MAX_LAUNCH; i++) {
+        if (ctx->launch_extra[i]) CUDA_TRY(cudaStreamSynchronize(ctx->launch_extra[i]));
+        ctx->dirty_extra[i] = false;
+    }
     if (ctx->copy_in) CUDA_TRY(cudaStreamSynchronize(ctx->copy_in));
     if (ctx->copy_out) CUDA_TRY(cudaStreamSynchronize(ctx->copy_out));
     GS_API_END

@@ -204,11 +204,13 @@ void *gs_output_device(gs_plan *p);
 /* host-buffer round trip the reference's execute_binary does through files (executor.cc:6-58):
  * H2D of B, launch, D2H of C, all on gs_stream(); returns after the stream drained */
 gs_status gs_spmm_host(gs_plan *p, const void *B_host, void *C_host);
-/* the same round trip without the host wait: H2D on a copy-in stream, launch on gs_stream(), D2H on a copy-out
- * stream, chained by events, so that consecutive calls on different plans overlap copy and compute.  B_host and
- * C_host must be pinned and stay valid until gs_synchronize() returns; C_host is complete only then. */
+/* the same round trip without the host wait: H2D on a copy-in stream, launch on one of up to four launch streams
+ * (gs_stream() and three more, taken in turn; GS_ASYNC_STREAMS=1..4), D2H on a copy-out stream, chained by events,
+ * so that consecutive calls on different plans overlap copies and kernels; calls on one plan stay in order.  Whatever
+ * is put on gs_stream() afterwards (gs_launch, gs_get_output ...) is ordered behind them.  B_host and C_host must be
+ * pinned and stay valid until gs_synchronize() returns; C_host is complete only then. */
 gs_status gs_spmm_host_async(gs_plan *p, const void *B_host, void *C_host);
-gs_status gs_synchronize(gs_ctx *ctx); /* drains gs_stream() and both copy streams */
+gs_status gs_synchronize(gs_ctx *ctx); /* drains gs_stream(), the other launch streams and both copy streams */
 /* bytes one launch must move (SURVEY.md section 8d formula, with the device's actual dtypes) */
 uint64_t gs_plan_algorithmic_bytes(const gs_plan *p);
 int gs_plan_launch_count(const gs_plan *p); /* kernels per gs_launch (memset excluded) */

@@ -174,6 +174,38 @@ def test_async_roundtrip_equals_blocking(engine):
         assert np.array_equal(outs[i].numpy(), want[i]), i
 
 
+@pytest.mark.parametrize("kernel,density", [("b200_sp24", 0.3), ("b200_tcgen05", 0.1)])
+def test_async_roundtrip_rotates_over_launch_streams(engine, kernel, density):
+    """gs_spmm_host_async puts consecutive steps on different launch streams: kernels that hand split panels over between
+    their CTAs (every CTA of a launch resident) run side by side, a plan's own launches stay in order (5 plans over 4
+    streams: every plan meets every stream), and a launch on gs_stream() right after the calls -- no gs_synchronize in
+    between -- is ordered behind them"""
+    import torch
+    from generalsparse_b200 import api, synth
+    rows, cols, N = 3000, 4096, 16
+    r, c = _matrix("uniform", rows, cols, seed=33, density=density)
+    vals = synth.synth_values(len(r), seed=33).astype(np.float16).astype(np.float32)
+    ms = api.MetaDataSet.from_coo(rows, cols, r, c, vals)
+    s = api.Session(ms).run_family("thread_total", N, 8, 1)
+    plans = []
+    for k in range(5):
+        engine.upload_session(s, half=True, as_id=30 + k)
+        plans.append(engine.plan(s, N, half=True, kernel=kernel, sub_matrix_id=30 + k))
+    Bs = [torch.from_numpy(synth.synth_dense(cols, N, seed=50 + i).astype(np.float16)).pin_memory() for i in range(10)]
+    want = [plans[i % 5].spmm_host(Bs[i].numpy()) for i in range(10)]
+    outs = [torch.empty((rows, N), dtype=torch.float16).pin_memory() for _ in range(10)]
+    for rep in range(20):
+        for i in range(10):
+            plans[i % 5].spmm_host_async_ptr(Bs[i].data_ptr(), outs[i].data_ptr())
+    # the last async step of plan 4 used Bs[9]; a plain launch of the same plan must see that B and come after it
+    plans[4].launch()
+    last = plans[4].output()
+    engine.synchronize()
+    for i in range(10):
+        assert np.array_equal(outs[i].numpy(), want[i]), i
+    assert np.array_equal(last, want[9])
+
+
 def test_errors_are_statuses_not_aborts(engine):
     from generalsparse_b200 import api
     rows, cols = 64, 48
