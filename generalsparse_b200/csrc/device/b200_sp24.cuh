@@ -17,7 +17,8 @@
 // images): the 128 x N piece of B, which every tile of every panel needs again, is then fetched from L2 and written
 // to shared memory once per 256 rows instead of once per 128 -- at N >= 64 B's re-reads, not A's stream, fill the path
 // from L2 to the SMs (N=128: 32 KB of B per 18 KB of A).
-// With remainder warps (RW = 8, N <= 16): what the 2:4 pattern cannot hold is multiplied inside the same CTA.  The CTA that
+// With remainder warps and gathers from L2 (RW = 8, TL = 0, N <= 16; the fallback of the tile-local form below): what the 2:4
+// pattern cannot hold is multiplied inside the same CTA.  The CTA that
 // owns a panel also owns its remainder rows; warps 8-15 (a pair of threads per row: two halves of the row's entries at
 // N=8, the two 16-byte halves of B's row at N=16) gather B from L2 while the tile loop runs, leave the fp32 product in
 // shared memory, and the epilogue adds it before the single rounding.  No second launch, no global hand-off.
