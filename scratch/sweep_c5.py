@@ -18,6 +18,7 @@ KERNELS = [("thread_total f32", "thread_total", 4, None, False), ("warp_total f3
            ("thread_bit_map f32", "thread_bit_map", 1, None, False), ("warp_segment f32", "warp_segment", 1, None, False),
            ("b200_nnz f32", "thread_bit_map", 1, "b200_nnz", False),
            ("b200_row_smem f16", "thread_total", 8, "b200_row_smem", True), ("b200_tcgen05 f16", "thread_total", 8, "b200_tcgen05", True),
+           ("b200_sp24 f16", "thread_total", 8, "b200_sp24", True),
            ("thread_total f16", "thread_total", 8, None, True)]
 eng = api.Engine(0)
 out = []
