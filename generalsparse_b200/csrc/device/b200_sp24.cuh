@@ -60,8 +60,35 @@ struct sp24_args {
     // tile-local remainder (kernels instantiated with TL): every tile image is followed by the remainder entries of its 128 x 128 window
     // (host/sp24_format.hpp, sp24_tiled); one bulk copy of unit_bytes brings both, B's 128 rows sit b_off bytes into the stage
     uint32_t unit_bytes, b_off, stage_bytes, rem_on;
+    // image without its empty tiles (group = 1): the units of panel p are panel_ptr[p] .. panel_ptr[p+1] (every panel keeps at least
+    // one), unit u multiplies columns 128 unit_kt[u] ...; null = every tile present, unit t is tile (t / k_tiles, t % k_tiles)
+    const uint32_t *panel_ptr, *unit_kt;
+    uint32_t n_panels;
     uint32_t *dbg; // probe: CTA 0 leaves the 4 metadata columns of stage 0 (128 lanes x 4 words) here, or null
 };
+
+// where unit t lies: its panel and the panel's first and one-past-last unit
+template <bool CP> __device__ __forceinline__ void seg_locate(const sp24_args &a, uint32_t t, uint32_t &panel, uint32_t &pbeg, uint32_t &pend)
+{
+    if constexpr (CP) {
+        uint32_t lo = 0, hi = a.n_panels; // the largest p with panel_ptr[p] <= t (no panel is empty)
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (a.panel_ptr[mid] <= t) lo = mid;
+            else hi = mid;
+        }
+        panel = lo, pbeg = a.panel_ptr[lo], pend = a.panel_ptr[lo + 1];
+    } else panel = t / a.k_tiles, pbeg = panel * a.k_tiles, pend = pbeg + a.k_tiles;
+}
+// the segment that starts at unit t: kernels over the full image compute it from t (nothing kept between segments), kernels over
+// the image without its empty tiles (CP) walk the panel table
+template <bool CP> __device__ __forceinline__ void seg_begin(const sp24_args &a, uint32_t t, bool first, uint32_t &panel, uint32_t &pbeg, uint32_t &pend)
+{
+    if constexpr (CP) {
+        if (first) seg_locate<true>(a, t, panel, pbeg, pend);
+        else panel++, pbeg = pend, pend = a.panel_ptr[panel + 1];
+    } else seg_locate<false>(a, t, panel, pbeg, pend);
+}
 
 __device__ __forceinline__ void bulk_load(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
 {
@@ -145,13 +172,14 @@ template <int N, int P> struct geom {
 // N: the width the tensor core multiplies (a multiple of 16); NL <= N: the width of B and C in memory (NL = 8 runs as N = 16,
 // the tensor map returns zeros for the columns B does not have)
 // TL: 0 = no tile-local remainder, else the stages of the copy ring (4 where two CTAs with four stages fit an SM, else 3)
-template <int N, int P, int NL, int RW, int TL = 0> __global__ void __launch_bounds__(SP_THREADS + 32 * RW, (RW ? 2 : geom<N, P>::MIN_CTAS)) k_b200_sp24(sp24_args a, const __grid_constant__ CUtensorMap b_map)
+template <int N, int P, int NL, int RW, int TL = 0, bool CP = false> __global__ void __launch_bounds__(SP_THREADS + 32 * RW, (RW ? 2 : geom<N, P>::MIN_CTAS)) k_b200_sp24(sp24_args a, const __grid_constant__ CUtensorMap b_map)
 {
     using G = geom<N, P>;
     constexpr int S = TL ? TL : G::STAGES, ACC = G::ACC, CH = G::CH;
     static_assert(NL % CH == 0, "chunk");
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     static_assert(RW == 0 || (RW == 8 && NL <= (TL ? 32 : 16) && P == 1 && G::CTAS == 2), "remainder warps");
+    static_assert(!CP || P == 1, "the image without its empty tiles has one panel per unit");
     static_assert(TL == 0 || ((TL == 3 || TL == 4) && RW == 8), "the tile-local remainder is multiplied by the remainder warps");
     // bytes of a unit in global memory (= one bulk copy), offset of B's rows inside a stage, stage stride
     const uint32_t UNIT = TL ? a.unit_bytes : (uint32_t)G::UNIT_BYTES, BOFF = TL ? a.b_off : (uint32_t)G::UNIT_BYTES, STG = TL ? a.stage_bytes : (uint32_t)G::STAGE_BYTES;
@@ -194,8 +222,10 @@ template <int N, int P, int NL, int RW, int TL = 0> __global__ void __launch_bou
             const unsigned char *img = a.img + (size_t)t0 * UNIT;
             const uint32_t pf = a.pf_ahead ? (uint32_t)S + a.pf_ahead : 0u;
             for (uint32_t it = 0; it < pf && it < n_local; it++) l2_prefetch_bulk(img + (size_t)it * UNIT, UNIT);
-            uint32_t s = 0, ph = 0, kt = t0 % KT;
+            uint32_t s = 0, ph = 0, kt = CP ? a.unit_kt[t0] : t0 % KT;
             for (uint32_t it = 0; it < n_local; it++) {
+                uint32_t kt_next = 0; // requested before the wait below, so the table's latency hides behind it
+                if (CP && it + 1 < n_local) kt_next = a.unit_kt[t0 + it + 1];
                 if (pf && it + pf < n_local) l2_prefetch_bulk(img + (size_t)(it + pf) * UNIT, UNIT);
                 mbar_wait(empty0 + 8u * s, ph ^ 1u); // the tensor core has finished reading the stage
                 const uint32_t st = smem0 + s * STG, fb = full0 + 8u * s;
@@ -203,7 +233,8 @@ template <int N, int P, int NL, int RW, int TL = 0> __global__ void __launch_bou
                 bulk_load(st, img + (size_t)it * UNIT, UNIT, fb);
 #pragma unroll
                 for (int g = 0; g < G::GROUPS; g++) tma_load_2d(st + BOFF + g * G::GROUP_BYTES, &b_map, (uint32_t)(g * G::ATOM_N), kt * SK, fb); // rows past K come back as zeros
-                if (++kt == KT) kt = 0;
+                if (CP) kt = kt_next;
+                else if (++kt == KT) kt = 0;
                 if (++s == S) s = 0, ph ^= 1u;
             }
         }
@@ -211,11 +242,12 @@ template <int N, int P, int NL, int RW, int TL = 0> __global__ void __launch_bou
     } else if (warp == ISSUE_WARP) {
         // ------------------------------------------------------------------------------------------ MMA issue
         if (lane == 0) {
-            uint32_t it = 0, seg = 0, s = 0, ph = 0, kt0 = t0 % KT;
+            uint32_t it = 0, seg = 0, s = 0, ph = 0, panel = 0, pbeg = 0, pend = 0;
             const uint64_t adesc0 = smem_desc(smem0, 16, 1024, 2u), edesc0 = smem_desc(smem0 + IMG_A, 128, 128, 0u),
                            bdesc0 = smem_desc(smem0 + BOFF, G::GROUP_BYTES, G::SBO, G::LAYOUT);
             while (it < n_local) {
-                const uint32_t len = min(KT - kt0, n_local - it), ab = seg % ACC;
+                seg_begin<CP>(a, t0 + it, it == 0, panel, pbeg, pend);
+                const uint32_t len = min(pend - (t0 + it), n_local - it), ab = seg % ACC;
                 mbar_wait(acce0 + 8u * ab, ((seg / ACC) & 1u) ^ 1u);
                 tc_fence_after();
                 for (uint32_t i = 0; i < len; i++) {
@@ -236,7 +268,7 @@ template <int N, int P, int NL, int RW, int TL = 0> __global__ void __launch_bou
                     if (++s == S) s = 0, ph ^= 1u;
                 }
                 tc_commit(accf0 + 8u * ab);
-                it += len, seg++, kt0 = 0;
+                it += len, seg++;
             }
         }
         __syncwarp();
@@ -245,15 +277,17 @@ template <int N, int P, int NL, int RW, int TL = 0> __global__ void __launch_bou
         const uint32_t q = warp - EPILOGUE_WARP0, rip = q * 32 + lane, et = threadIdx.x - EPILOGUE_WARP0 * 32;
         __half *C = (__half *)a.C;
         uint32_t it = 0, seg = 0, own = 0; // own: owner segments so far (the remainder warps count the same way)
+        uint32_t unit_panel = 0, pbeg = 0, pend = 0;
         auto wait_for = [&](const uint32_t *flag, uint32_t v) { // one lane polls, the warp follows
             if (lane == 0)
                 while (ld_acquire(flag) != v) __nanosleep(32);
             __syncwarp();
         };
         while (it < n_local) {
-            const uint32_t t = t0 + it, unit_panel = t / KT, kt0 = t % KT, len = min(KT - kt0, n_local - it), ab = seg % ACC;
-            const bool partial_in = kt0 > 0;                 // someone else owns the panels: leave partials
-            const bool owner_wait = !partial_in && len < KT; // this CTA owns the panels and others hold their tail
+            seg_begin<CP>(a, t0 + it, it == 0, unit_panel, pbeg, pend);
+            const uint32_t t = t0 + it, len = min(pend - t, n_local - it), ab = seg % ACC;
+            const bool partial_in = t > pbeg;                         // someone else owns the panels: leave partials
+            const bool owner_wait = !partial_in && len < pend - pbeg; // this CTA owns the panels and others hold their tail
             // what does not depend on the accumulator goes first, while the tile loop is still running
             uint32_t orow[P], c_last = cta; // contributors: the CTAs after this one whose first unit lies inside the same panels
             if (partial_in) wait_for(a.slot_free + cta, a.seq - 1); // the previous launch's owner has read this CTA's slot
@@ -270,7 +304,7 @@ template <int N, int P, int NL, int RW, int TL = 0> __global__ void __launch_bou
                     }
                 }
                 if (owner_wait) {
-                    const uint64_t panel_end = (uint64_t)(unit_panel + 1) * KT;
+                    const uint64_t panel_end = pend;
                     while (c_last + 1 < n_cta && (uint64_t)(c_last + 1) * a.n_tiles / n_cta < panel_end) c_last++;
                 }
             }
@@ -396,9 +430,10 @@ template <int N, int P, int NL, int RW, int TL = 0> __global__ void __launch_bou
         const uint32_t rt = threadIdx.x - (EPILOGUE_WARP0 + 4) * 32, rrow = rt >> 1, sub = rt & 1u;
         const uint32_t estart = NL == 8 ? sub : 0u, estep = NL == 8 ? 2u : 1u, c16 = NL == 8 ? 0u : sub * CPT;
         const unsigned char *ring = smem_raw + (smem0 - smem_u32(smem_raw));
-        uint32_t it = 0, seg = 0, s = 0, ph = 0;
+        uint32_t it = 0, seg = 0, s = 0, ph = 0, panel = 0, pbeg = 0, pend = 0;
         while (it < n_local) {
-            const uint32_t kt0 = (t0 + it) % KT, len = min(KT - kt0, n_local - it);
+            seg_begin<CP>(a, t0 + it, it == 0, panel, pbeg, pend);
+            const uint32_t len = min(pend - (t0 + it), n_local - it);
             float acc[NA];
 #pragma unroll
             for (int j = 0; j < NA; j++) acc[j] = 0.f;
@@ -462,10 +497,11 @@ template <int N, int P, int NL, int RW, int TL = 0> __global__ void __launch_bou
         const uint32_t rt = threadIdx.x - (EPILOGUE_WARP0 + 4) * 32, rrow = rt >> 1, sub = rt & 1u;
         const uint32_t slice = LPR == 2 ? sub : 0u, estart = LPR == 2 ? 0u : sub, estep = LPR == 2 ? 1u : 2u;
         const __half *B = (const __half *)a.B;
-        uint32_t it = 0, own = 0;
+        uint32_t it = 0, own = 0, panel = 0, pbeg = 0, pend = 0;
         while (it < n_local && a.rem_rowptr) {
-            const uint32_t t = t0 + it, panel = t / KT, kt0 = t % KT, len = min(KT - kt0, n_local - it);
-            if (kt0 == 0) {
+            seg_begin<CP>(a, t0 + it, it == 0, panel, pbeg, pend);
+            const uint32_t t = t0 + it, len = min(pend - t, n_local - it);
+            if (t == pbeg) {
                 const uint32_t b = own & 1u;
                 mbar_wait(reme0 + 8u * b, ((own >> 1) & 1u) ^ 1u); // the epilogue has read what this buffer held two panels back
                 const uint32_t r = panel * SM_ROWS + rrow;

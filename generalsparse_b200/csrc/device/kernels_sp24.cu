@@ -20,6 +20,8 @@ struct b200_sp24_plan {
     bool fused = false;                                                       // the remainder is multiplied by warps of the 2:4 kernel itself
     bool tiled = false;                                                       // ... from tile-local blocks that travel with the tile images (sp24_tiled)
     uint32_t unit_bytes = 0, b_off = 0, stage_bytes = 0;
+    uint32_t *panel_ptr = nullptr, *unit_kt = nullptr; // the image without its empty tiles (b200_sp24.cuh), null = every tile present
+    uint32_t n_units_full = 0;
     int threads = 0;
     uint16_t *rem_val = nullptr;
     uint32_t n_tiles = 0, k_tiles = 0, n_panels = 0, grid = 0, seq = 0, n_rows = 0, group = 1; // n_tiles: units of `group` panels x one k step
@@ -271,6 +273,50 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
         ring_bytes += 2 * sp24::SM_ROWS * p.N * 4; // the two remainder buffers behind the ring
     }
     pl->n_panels = im.n_panels, pl->k_tiles = im.k_tiles, pl->n_tiles = im.n_panels / group * im.k_tiles, pl->nnz = im.nnz;
+    pl->n_units_full = pl->n_tiles;
+    // Tiles that hold nothing (banded, block-sparse matrices) are dropped from the stream when that saves at least a tenth of it; every
+    // panel keeps one tile so that its rows of C are written.  GS_SP24_SKIP_EMPTY=0 keeps them all.
+    std::vector<uint32_t> panel_ptr, unit_kt;
+    std::vector<uint8_t> compact;
+    if (group == 1 && env_int("GS_SP24_SKIP_EMPTY", 1)) {
+        const size_t U = pl->tiled ? tl.unit_bytes : (size_t)sp24::IMG_BYTES;
+        const uint8_t *src = pl->tiled ? tl.bytes.data() : im.bytes.data();
+        panel_ptr.assign(1, 0u);
+        for (uint32_t pn = 0; pn < im.n_panels; pn++) {
+            const size_t before = unit_kt.size();
+            for (uint32_t kt = 0; kt < im.k_tiles; kt++) {
+                const uint8_t *t = src + ((size_t)pn * im.k_tiles + kt) * U;
+                bool any = false;
+                const uint64_t *w = (const uint64_t *)t; // the compressed operand: 16 KB, 8-byte aligned inside the vector's units
+                for (size_t i = 0; i < gs::SP24_A_BYTES / 8 && !any; i++) any = w[i] != 0;
+                if (!any && pl->tiled) any = (t[gs::SP24_TILE_BYTES + 2 * gs::SP24_ROWS] | t[gs::SP24_TILE_BYTES + 2 * gs::SP24_ROWS + 1]) != 0; // start[128]: entries in the block
+                if (any) unit_kt.push_back(kt);
+            }
+            if (unit_kt.size() == before) unit_kt.push_back(0u);
+            panel_ptr.push_back((uint32_t)unit_kt.size());
+        }
+        const void *cfn = nullptr; // the kernel over a panel table: same shape as the one picked above
+        if (pl->tiled) {
+            if (p.N == 8) cfn = stages == 4 ? (const void *)sp24::k_b200_sp24<16, 1, 8, 8, 4, true> : (const void *)sp24::k_b200_sp24<16, 1, 8, 8, 3, true>;
+            else if (p.N == 16) cfn = stages == 4 ? (const void *)sp24::k_b200_sp24<16, 1, 16, 8, 4, true> : (const void *)sp24::k_b200_sp24<16, 1, 16, 8, 3, true>;
+            else cfn = (const void *)sp24::k_b200_sp24<32, 1, 32, 8, 3, true>;
+        } else if (pl->fused) cfn = p.N == 8 ? (const void *)sp24::k_b200_sp24<16, 1, 8, 8, 0, true> : (const void *)sp24::k_b200_sp24<16, 1, 16, 8, 0, true>;
+        else switch (p.N) {
+            case 8: cfn = (const void *)sp24::k_b200_sp24<16, 1, 8, 0, 0, true>; break;
+            case 16: cfn = (const void *)sp24::k_b200_sp24<16, 1, 16, 0, 0, true>; break;
+            case 32: cfn = (const void *)sp24::k_b200_sp24<32, 1, 32, 0, 0, true>; break;
+            case 64: cfn = (const void *)sp24::k_b200_sp24<64, 1, 64, 0, 0, true>; break;
+            case 128: cfn = (const void *)sp24::k_b200_sp24<128, 1, 128, 0, 0, true>; break;
+            case 256: cfn = (const void *)sp24::k_b200_sp24<256, 1, 256, 0, 0, true>; break;
+            }
+        if (cfn && (double)unit_kt.size() <= 0.9 * (double)pl->n_tiles) {
+            pl->fn = cfn;
+            compact.resize(unit_kt.size() * U);
+            for (uint32_t pn = 0; pn < im.n_panels; pn++)
+                for (uint32_t u = panel_ptr[pn]; u < panel_ptr[pn + 1]; u++) memcpy(compact.data() + (size_t)u * U, src + ((size_t)pn * im.k_tiles + unit_kt[u]) * U, U);
+            pl->n_tiles = (uint32_t)unit_kt.size();
+        } else panel_ptr.clear(), unit_kt.clear();
+    }
     pl->grid = (uint32_t)std::min<uint64_t>((uint64_t)env_int("GS_TILE_CTAS", sm_count), pl->n_tiles);
     if (pl->grid == 0 || (int)pl->grid > sm_count * ctas) return fail(cudaErrorInvalidValue); // the split-panel hand-off needs every CTA resident
 
@@ -287,7 +333,11 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
         if (e2 != cudaSuccess) return e2;
         return bytes ? cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess;
     };
-    if ((e = pl->tiled ? up((void **)&pl->img, tl.bytes.data(), tl.bytes.size()) : up((void **)&pl->img, im.bytes.data(), im.bytes.size())) != cudaSuccess) return fail(e);
+    if (!compact.empty()) {
+        if ((e = up((void **)&pl->img, compact.data(), compact.size())) != cudaSuccess) return fail(e);
+        if ((e = up((void **)&pl->panel_ptr, panel_ptr.data(), panel_ptr.size() * 4)) != cudaSuccess) return fail(e);
+        if ((e = up((void **)&pl->unit_kt, unit_kt.data(), unit_kt.size() * 4)) != cudaSuccess) return fail(e);
+    } else if ((e = pl->tiled ? up((void **)&pl->img, tl.bytes.data(), tl.bytes.size()) : up((void **)&pl->img, im.bytes.data(), im.bytes.size())) != cudaSuccess) return fail(e);
     if ((e = up((void **)&pl->out_row, orow.data(), orow.size() * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMalloc((void **)&pl->ws, (size_t)pl->grid * group * sp24::SM_ROWS * p.N * 4)) != cudaSuccess) return fail(e);
     const size_t n_flags = (size_t)pl->grid * 2 + pl->n_panels + (size_t)pl->n_panels * 4;
@@ -320,10 +370,11 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     // 512-thread CTAs at 64 registers fill the register file exactly with two CTAs; the occupancy calculator answers 1 for them, the
     // hardware runs 2 (ncu: launch__occupancy_limit_registers = launch__occupancy_limit_shared_mem = 2, profiles/r1_sp24_summary.md)
     if (pl->fused && ctas == 2 && occ == 1 && 2 * (pl->smem + 2048) <= 228 * 1024) occ = 2;
-    char rem[48] = "";
+    char rem[48] = "", skip[40] = "";
+    if (pl->panel_ptr) snprintf(skip, sizeof skip, ",%u of %u tiles", pl->n_tiles, pl->n_units_full);
     if (pl->rem_nnz) snprintf(rem, sizeof rem, ",+remainder %.1f%% (%s)", 100.0 * (double)pl->rem_nnz / (double)(pl->rem_nnz + pl->nnz), pl->tiled ? "tile-local, 8 warps" : pl->fused ? "8 warps of the owner CTA" : "gather pass");
-    snprintf(pl->name, sizeof pl->name, "k_b200_sp24<N%d,f16,tcgen05.mma.sp m128n%dk32,%d panel%s/CTA,%d stages,streamK x%u,%d CTA/SM,pdl%s>", p.N, p.N < 16 ? 16 : p.N, group, group > 1 ? "s" : "", stages, pl->grid, occ,
-             rem);
+    snprintf(pl->name, sizeof pl->name, "k_b200_sp24<N%d,f16,tcgen05.mma.sp m128n%dk32,%d panel%s/CTA,%d stages,streamK x%u,%d CTA/SM,pdl%s%s>", p.N, p.N < 16 ? 16 : p.N, group, group > 1 ? "s" : "", stages, pl->grid, occ,
+             rem, skip);
     if (env_int("GS_SP24_PROBE", 0)) {
         if ((e = cudaMalloc((void **)&pl->dbg, 128 * 4 * 4)) != cudaSuccess) return fail(e);
         cudaMemset(pl->dbg, 0xff, 128 * 4 * 4);
@@ -367,6 +418,7 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
     a.dbg = pl->dbg;
     a.rem_rowptr = (pl->fused && !pl->tiled && !skip_rem) ? pl->rem_rowptr : nullptr, a.rem_pack = pl->rem_pack, a.B = p.B, a.n_rows = pl->n_rows;
     a.unit_bytes = pl->unit_bytes, a.b_off = pl->b_off, a.stage_bytes = pl->stage_bytes, a.rem_on = skip_rem ? 0u : 1u;
+    a.panel_ptr = pl->panel_ptr, a.unit_kt = pl->unit_kt, a.n_panels = pl->n_panels;
     void *args[] = {&a, &pl->b_map};
     memset(&cfg, 0, sizeof cfg);
     cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(pl->threads), cfg.dynamicSmemBytes = pl->smem, cfg.stream = s;
@@ -378,7 +430,7 @@ void b200_sp24_free(b200_sp24_plan *pl)
 {
     if (!pl) return;
     cudaFree(pl->img), cudaFree(pl->out_row), cudaFree(pl->flags), cudaFree(pl->ws), cudaFree(pl->c_add), cudaFree(pl->rem_rowptr), cudaFree(pl->rem_col), cudaFree(pl->rem_val), cudaFree(pl->rem_pack),
-        cudaFree(pl->dbg);
+        cudaFree(pl->dbg), cudaFree(pl->panel_ptr), cudaFree(pl->unit_kt);
     delete pl;
 }
 

@@ -425,6 +425,44 @@ def test_b200_sp24_tile_local_remainder(engine, N):
         assert np.array_equal(plan.output(), C)
 
 
+@pytest.mark.parametrize("N", [8, 16, 32, 64])
+def test_b200_sp24_skips_empty_tiles(engine, monkeypatch, N):
+    """tiles that hold nothing leave the stream (unit -> (panel, k tile) table): a block-sparse matrix (30 % dense blocks, the
+    rest empty, some row panels entirely empty), a full band, and the same matrices with GS_SP24_SKIP_EMPTY=0;
+    reference-mode ones exact"""
+    from generalsparse_b200 import synth
+    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    rng = np.random.default_rng(17)
+    nrows, cols = 3000, 4096
+    mask = rng.random((nrows, cols)) < 0.3
+    blocks = rng.random((-(-nrows // 128), cols // 128)) < 0.25
+    blocks[5] = False  # an empty row panel keeps one (empty) tile
+    blocks[7, :] = False
+    blocks[7, 31] = True  # a panel whose only tile is the last k tile
+    mask &= np.kron(blocks, np.ones((128, 128), dtype=bool))[:nrows]
+    br, bc = np.nonzero(mask)
+    mats = [(br.astype(np.int64), bc.astype(np.int64), nrows, cols)]
+    r2, c2 = _matrix("banded", 2000, 2048, seed=3, half_bandwidth=64)
+    mats.append((r2, c2, 2000, 2048))
+    for rr, cc, nr, nc in mats:
+        indptr = csr_from_coo(nr, rr)
+        vals = synth.synth_values(len(rr), seed=9).astype(np.float16).astype(np.float32)
+        B = synth.synth_dense(nc, N, seed=9).astype(np.float16).astype(np.float32)
+        B1 = np.ones((nc, N), dtype=np.float32)
+        C1, plan = _run(engine, "thread_total", nr, nc, rr, cc, None, B1, N, 8, 1, half=True, kernel="b200_sp24")
+        assert " tiles" in plan.kernel_name, plan.kernel_name
+        assert np.array_equal(C1.astype(np.float32), oracle_spmm_f32(nr, N, indptr, cc, np.ones(len(rr), np.float32), B1)), plan.kernel_name
+        C, plan = _run(engine, "thread_total", nr, nc, rr, cc, vals, B, N, 8, 1, half=True, kernel="b200_sp24")
+        _check(C, oracle_spmm_f64acc(nr, N, indptr, cc, vals, B), oracle_spmm_absrow(nr, N, indptr, cc, vals, B) * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        plan.run(9)
+        assert np.array_equal(plan.output(), C)
+        monkeypatch.setenv("GS_SP24_SKIP_EMPTY", "0")
+        Cfull, plan = _run(engine, "thread_total", nr, nc, rr, cc, vals, B, N, 8, 1, half=True, kernel="b200_sp24")
+        monkeypatch.delenv("GS_SP24_SKIP_EMPTY")
+        assert " tiles" not in plan.kernel_name, plan.kernel_name  # another split of the panels over the CTAs: other fp32 summation order
+        _check(Cfull, oracle_spmm_f64acc(nr, N, indptr, cc, vals, B), oracle_spmm_absrow(nr, N, indptr, cc, vals, B) * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+
+
 @pytest.mark.parametrize("kind,kw,N", [("nm24", {}, 32), ("uniform", dict(density=0.3), 32), ("uniform", dict(density=0.3), 16)])
 def test_b200_sp24_overlapped_launches_keep_order(engine, kind, kw, N):
     """back-to-back launches of one plan overlap on the SMs: C must end up as the LAST launch's product although the
