@@ -377,15 +377,25 @@ gs_status gsh_sp24_tiled_roundtrip(const uint32_t *rowptr, const uint32_t *col, 
     sp24_image im;
     sp24_tiled t;
     std::vector<uint16_t> dense;
+    uint64_t kept = 0;
     try {
         build_sp24_image(rowptr, col, val, n_rows, n_cols, 1, im);
         localize_sp24_remainder(im, row_bytes, t);
-        expand_sp24_tiled(im, t, dense);
+        // through the stream without its empty tiles and back: what the kept units hold is the whole matrix
+        sp24_compact cp;
+        GS_REQUIRE(compact_sp24_units(t.bytes.data(), t.unit_bytes, true, im.n_panels, im.k_tiles, 1.0, cp), "compaction refused");
+        sp24_tiled back = t;
+        std::fill(back.bytes.begin(), back.bytes.end(), (uint8_t)0);
+        for (uint32_t p = 0; p < im.n_panels; p++)
+            for (uint32_t u = cp.panel_ptr[p]; u < cp.panel_ptr[p + 1]; u++)
+                std::copy_n(cp.bytes.begin() + (size_t)u * t.unit_bytes, t.unit_bytes, back.bytes.begin() + ((size_t)p * im.k_tiles + cp.unit_kt[u]) * t.unit_bytes);
+        kept = cp.unit_kt.size();
+        expand_sp24_tiled(im, back, dense);
     } catch (const std::exception &e) {
         throw gs::Error(e.what());
     }
     std::copy(dense.begin(), dense.end(), dense_out);
-    stats[0] = t.bytes.size(), stats[1] = im.nnz, stats[2] = im.rem_col.size(), stats[3] = (uint64_t)im.n_panels * im.k_tiles, stats[4] = t.unit_bytes, stats[5] = t.max_entries;
+    stats[0] = t.bytes.size(), stats[1] = im.nnz, stats[2] = im.rem_col.size(), stats[3] = (uint64_t)im.n_panels * im.k_tiles, stats[4] = t.unit_bytes, stats[5] = t.max_entries, stats[6] = kept;
     GS_API_END
 }
 

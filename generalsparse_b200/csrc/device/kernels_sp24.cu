@@ -276,25 +276,8 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     pl->n_units_full = pl->n_tiles;
     // Tiles that hold nothing (banded, block-sparse matrices) are dropped from the stream when that saves at least a tenth of it; every
     // panel keeps one tile so that its rows of C are written.  GS_SP24_SKIP_EMPTY=0 keeps them all.
-    std::vector<uint32_t> panel_ptr, unit_kt;
-    std::vector<uint8_t> compact;
+    gs::sp24_compact cp;
     if (group == 1 && env_int("GS_SP24_SKIP_EMPTY", 1)) {
-        const size_t U = pl->tiled ? tl.unit_bytes : (size_t)sp24::IMG_BYTES;
-        const uint8_t *src = pl->tiled ? tl.bytes.data() : im.bytes.data();
-        panel_ptr.assign(1, 0u);
-        for (uint32_t pn = 0; pn < im.n_panels; pn++) {
-            const size_t before = unit_kt.size();
-            for (uint32_t kt = 0; kt < im.k_tiles; kt++) {
-                const uint8_t *t = src + ((size_t)pn * im.k_tiles + kt) * U;
-                bool any = false;
-                const uint64_t *w = (const uint64_t *)t; // the compressed operand: 16 KB, 8-byte aligned inside the vector's units
-                for (size_t i = 0; i < gs::SP24_A_BYTES / 8 && !any; i++) any = w[i] != 0;
-                if (!any && pl->tiled) any = (t[gs::SP24_TILE_BYTES + 2 * gs::SP24_ROWS] | t[gs::SP24_TILE_BYTES + 2 * gs::SP24_ROWS + 1]) != 0; // start[128]: entries in the block
-                if (any) unit_kt.push_back(kt);
-            }
-            if (unit_kt.size() == before) unit_kt.push_back(0u);
-            panel_ptr.push_back((uint32_t)unit_kt.size());
-        }
         const void *cfn = nullptr; // the kernel over a panel table: same shape as the one picked above
         if (pl->tiled) {
             if (p.N == 8) cfn = stages == 4 ? (const void *)sp24::k_b200_sp24<16, 1, 8, 8, 4, true> : (const void *)sp24::k_b200_sp24<16, 1, 8, 8, 3, true>;
@@ -309,13 +292,10 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
             case 128: cfn = (const void *)sp24::k_b200_sp24<128, 1, 128, 0, 0, true>; break;
             case 256: cfn = (const void *)sp24::k_b200_sp24<256, 1, 256, 0, 0, true>; break;
             }
-        if (cfn && (double)unit_kt.size() <= 0.9 * (double)pl->n_tiles) {
+        if (cfn && gs::compact_sp24_units(pl->tiled ? tl.bytes.data() : im.bytes.data(), pl->tiled ? tl.unit_bytes : (size_t)sp24::IMG_BYTES, pl->tiled, im.n_panels, im.k_tiles, 0.9, cp)) {
             pl->fn = cfn;
-            compact.resize(unit_kt.size() * U);
-            for (uint32_t pn = 0; pn < im.n_panels; pn++)
-                for (uint32_t u = panel_ptr[pn]; u < panel_ptr[pn + 1]; u++) memcpy(compact.data() + (size_t)u * U, src + ((size_t)pn * im.k_tiles + unit_kt[u]) * U, U);
-            pl->n_tiles = (uint32_t)unit_kt.size();
-        } else panel_ptr.clear(), unit_kt.clear();
+            pl->n_tiles = (uint32_t)cp.unit_kt.size();
+        }
     }
     pl->grid = (uint32_t)std::min<uint64_t>((uint64_t)env_int("GS_TILE_CTAS", sm_count), pl->n_tiles);
     if (pl->grid == 0 || (int)pl->grid > sm_count * ctas) return fail(cudaErrorInvalidValue); // the split-panel hand-off needs every CTA resident
@@ -333,10 +313,10 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
         if (e2 != cudaSuccess) return e2;
         return bytes ? cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess;
     };
-    if (!compact.empty()) {
-        if ((e = up((void **)&pl->img, compact.data(), compact.size())) != cudaSuccess) return fail(e);
-        if ((e = up((void **)&pl->panel_ptr, panel_ptr.data(), panel_ptr.size() * 4)) != cudaSuccess) return fail(e);
-        if ((e = up((void **)&pl->unit_kt, unit_kt.data(), unit_kt.size() * 4)) != cudaSuccess) return fail(e);
+    if (!cp.bytes.empty()) {
+        if ((e = up((void **)&pl->img, cp.bytes.data(), cp.bytes.size())) != cudaSuccess) return fail(e);
+        if ((e = up((void **)&pl->panel_ptr, cp.panel_ptr.data(), cp.panel_ptr.size() * 4)) != cudaSuccess) return fail(e);
+        if ((e = up((void **)&pl->unit_kt, cp.unit_kt.data(), cp.unit_kt.size() * 4)) != cudaSuccess) return fail(e);
     } else if ((e = pl->tiled ? up((void **)&pl->img, tl.bytes.data(), tl.bytes.size()) : up((void **)&pl->img, im.bytes.data(), im.bytes.size())) != cudaSuccess) return fail(e);
     if ((e = up((void **)&pl->out_row, orow.data(), orow.size() * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMalloc((void **)&pl->ws, (size_t)pl->grid * group * sp24::SM_ROWS * p.N * 4)) != cudaSuccess) return fail(e);

@@ -2,6 +2,7 @@
 #include "sp24_format.hpp"
 
 #include <algorithm>
+#include <cstring>
 #include <stdexcept>
 #include <utility>
 
@@ -143,6 +144,33 @@ void expand_sp24_tiled(const sp24_image &geo, const sp24_tiled &t, std::vector<u
                 dense[r * im.n_cols + c] = (uint16_t)(w & 0xffffu);
             }
     }
+}
+
+bool compact_sp24_units(const uint8_t *units, size_t U, bool tiled, uint32_t n_panels, uint32_t k_tiles, double keep_frac, sp24_compact &out)
+{
+    out = sp24_compact();
+    out.panel_ptr.assign(1, 0u);
+    for (uint32_t p = 0; p < n_panels; p++) {
+        const size_t before = out.unit_kt.size();
+        for (uint32_t kt = 0; kt < k_tiles; kt++) {
+            const uint8_t *t = units + ((size_t)p * k_tiles + kt) * U;
+            bool any = false;
+            for (size_t i = 0; i < SP24_A_BYTES && !any; i += 8) {
+                uint64_t w;
+                std::memcpy(&w, t + i, 8);
+                any = w != 0;
+            }
+            if (!any && tiled) any = (t[SP24_TILE_BYTES + 2 * SP24_ROWS] | t[SP24_TILE_BYTES + 2 * SP24_ROWS + 1]) != 0; // start[128]: entries in the block
+            if (any) out.unit_kt.push_back(kt);
+        }
+        if (out.unit_kt.size() == before) out.unit_kt.push_back(0u);
+        out.panel_ptr.push_back((uint32_t)out.unit_kt.size());
+    }
+    if ((double)out.unit_kt.size() > keep_frac * (double)n_panels * (double)k_tiles) return false;
+    out.bytes.resize(out.unit_kt.size() * U);
+    for (uint32_t p = 0; p < n_panels; p++)
+        for (uint32_t u = out.panel_ptr[p]; u < out.panel_ptr[p + 1]; u++) std::memcpy(out.bytes.data() + (size_t)u * U, units + ((size_t)p * k_tiles + out.unit_kt[u]) * U, U);
+    return true;
 }
 
 } // namespace gs

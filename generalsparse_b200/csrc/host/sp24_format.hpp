@@ -76,4 +76,15 @@ inline uint32_t sp24_b_row_offset(uint32_t k, uint32_t row_bytes) { return k * r
 void localize_sp24_remainder(const sp24_image &im, uint32_t row_bytes, sp24_tiled &out);
 void expand_sp24_tiled(const sp24_image &im, const sp24_tiled &t, std::vector<uint16_t> &dense); // im: geometry only, its remainder arrays are not read
 
+// The stream without the tiles that hold nothing (group = 1): units of `unit_bytes` (SP24_TILE_BYTES, or a sp24_tiled unit when
+// `tiled`), panel-major; the units of panel p are panel_ptr[p] .. panel_ptr[p+1] and unit u multiplies columns
+// 128 * unit_kt[u] ...  A tile is kept when its compressed operand holds a non-zero bit or its tile-local block an entry;
+// a panel with none keeps its first tile, so that its rows of the product are written.
+struct sp24_compact {
+    std::vector<uint32_t> panel_ptr, unit_kt;
+    std::vector<uint8_t> bytes; // unit_kt.size() * unit_bytes
+};
+// fills panel_ptr / unit_kt always; copies the kept units (and returns true) only if they are at most keep_frac of all units
+bool compact_sp24_units(const uint8_t *units, size_t unit_bytes, bool tiled, uint32_t n_panels, uint32_t k_tiles, double keep_frac, sp24_compact &out);
+
 } // namespace gs

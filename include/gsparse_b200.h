@@ -162,7 +162,8 @@ gs_status gsh_sp24_roundtrip(const uint32_t *rowptr, const uint32_t *col, const 
 /* The same with the remainder cut along the tiles (every tile image followed by the remainder entries of its 128 x 128
  * window, the form the kernel multiplies at N <= 32 without a second launch): stats[0] = bytes, [1] = non-zeros in the
  * images, [2] = non-zeros in the tile-local remainder blocks, [3] = tiles, [4] = bytes per tile, [5] = the largest entry
- * count of a tile.  row_bytes (32, 64, 128): the bytes of one row of the 128 x N piece of B in shared memory (2 N; N = 8 runs
+ * count of a tile, [6] = units left when the tiles that hold nothing leave the stream (every row panel keeps one; the
+ * expansion goes through that form).  row_bytes (32, 64, 128): the bytes of one row of the 128 x N piece of B in shared memory (2 N; N = 8 runs
  * as 16), which the entries address directly. */
 gs_status gsh_sp24_tiled_roundtrip(const uint32_t *rowptr, const uint32_t *col, const uint16_t *val_f16, uint32_t n_rows, uint32_t n_cols, uint32_t row_bytes, uint16_t *dense_out,
                                    uint64_t *stats);

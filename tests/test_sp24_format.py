@@ -105,7 +105,7 @@ def _tiled_roundtrip(rows, cols, indptr, col, vals16, row_bytes=32):
     from generalsparse_b200 import _lib
     L = _lib.lib()
     dense = np.zeros((rows, cols), dtype=np.uint16)
-    stats = np.zeros(6, dtype=np.uint64)
+    stats = np.zeros(7, dtype=np.uint64)
     rp = np.ascontiguousarray(indptr, dtype=np.uint32)
     cc = np.ascontiguousarray(col, dtype=np.uint32)
     vv = np.ascontiguousarray(vals16.view(np.uint16))
@@ -135,3 +135,22 @@ def test_remainder_cut_along_the_tiles(built_lib, rows, cols, density, empty):
     per_tile = extra.reshape(pr // 128, 128, pc // 128, 32).sum(axis=(1, 3))
     assert int(stats[5]) == int(per_tile.max())
     assert int(stats[4]) == 18432 + 272 + 4 * (-(-int(per_tile.max()) // 4) * 4) and int(stats[0]) == int(stats[3]) * int(stats[4])
+
+
+def test_empty_tiles_leave_the_stream(built_lib):
+    """a block-sparse matrix: the units kept are the blocks that hold something plus one for every row panel that holds
+    nothing, and image + tile-local blocks of the kept units still expand to the matrix"""
+    rng = np.random.default_rng(23)
+    rows, cols = 1100, 1300  # 9 row panels (the last ragged), 11 k tiles (the last ragged)
+    blocks = rng.random((9, 11)) < 0.3
+    blocks[2] = False
+    blocks[8] = False
+    blocks[8, 10] = True
+    mask = (rng.random((rows, cols)) < 0.5) & np.kron(blocks, np.ones((128, 128), dtype=bool))[:rows, :cols]
+    indptr, col, v, dense = _csr_of(mask, seed=4)
+    out, stats = _tiled_roundtrip(rows, cols, indptr, col, v, 64)
+    assert np.array_equal(out, dense.view(np.uint16))
+    pm = np.zeros((9 * 128, 11 * 128), dtype=bool)
+    pm[:rows, :cols] = mask
+    held = pm.reshape(9, 128, 11, 128).any(axis=(1, 3))
+    assert int(stats[6]) == int(held.sum()) + int((~held.any(axis=1)).sum()) and int(stats[3]) == 99
