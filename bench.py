@@ -274,7 +274,10 @@ def main():
         # measured on one B200: on the 70 % weight the 2:4 image with the tile-local remainder at N <= 32
         # (9.2 / 10.4 / 14.5 us at N = 8 / 16 / 32 against 12.1 us for the gather kernel and 16.6 / 17.9 us for the tile kernel);
         # the image is 1.125 bytes per matrix element whatever the sparsity, so sparser weights stay on the gather / tile kernels
-        args.kernel = "b200_sp24" if args.pattern == "nm24" or (N <= 32 and abs(DENSITY - 0.30) < 1e-9) else "b200_row_smem" if N < 16 else "b200_tcgen05"
+        # C3's unstructured half (90 % sparse) at N=64: 14.6 us on the 2:4 kernel (tile-local remainder, 0.9 % of the non-zeros)
+        # against 17.1 us on the tile kernel; from N=128 up the remainder needs the gather pass and the tile kernel wins
+        sp24 = args.pattern == "nm24" or (N <= 32 and abs(DENSITY - 0.30) < 1e-9) or (N == 64 and abs(DENSITY - 0.10) < 1e-9)
+        args.kernel = "b200_sp24" if sp24 else "b200_row_smem" if N < 16 else "b200_tcgen05"
     hbm_peak, peak_src = peaks()
 
     # ---- the global matrix: `world` FFN-sized blocks stacked; this rank's nnz-balanced row block ------------------------

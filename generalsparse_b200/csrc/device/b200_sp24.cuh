@@ -178,9 +178,9 @@ template <int N, int P, int NL, int RW, int TL = 0, bool CP = false> __global__ 
     constexpr int S = TL ? TL : G::STAGES, ACC = G::ACC, CH = G::CH;
     static_assert(NL % CH == 0, "chunk");
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    static_assert(RW == 0 || (RW == 8 && NL <= (TL ? 32 : 16) && P == 1 && G::CTAS == 2), "remainder warps");
+    static_assert(RW == 0 || (RW == 8 && NL <= (TL ? 64 : 16) && P == 1 && G::CTAS == 2), "remainder warps");
     static_assert(!CP || P == 1, "the image without its empty tiles has one panel per unit");
-    static_assert(TL == 0 || ((TL == 3 || TL == 4) && RW == 8), "the tile-local remainder is multiplied by the remainder warps");
+    static_assert(TL == 0 || (TL >= 2 && TL <= 4 && RW == 8), "the tile-local remainder is multiplied by the remainder warps");
     // bytes of a unit in global memory (= one bulk copy), offset of B's rows inside a stage, stage stride
     const uint32_t UNIT = TL ? a.unit_bytes : (uint32_t)G::UNIT_BYTES, BOFF = TL ? a.b_off : (uint32_t)G::UNIT_BYTES, STG = TL ? a.stage_bytes : (uint32_t)G::STAGE_BYTES;
     __shared__ __align__(8) uint64_t bars[2 * S + 8];
@@ -426,7 +426,8 @@ template <int N, int P, int NL, int RW, int TL = 0, bool CP = false> __global__ 
         // row, NL = 32: each takes 32 bytes.  B's rows lie as the tensor map swizzled them; an entry carries the byte offset of
         // its row's chunk 0 (host/sp24_format.hpp, sp24_b_row_offset), chunk c is at offset ^ (c << 4).  fp16 x fp16 + fp32 in
         // one instruction (fma.rn.f32.f16: the exact product, one rounding -- what fmaf of the converted operands gives).
-        constexpr int CPT = NL == 32 ? 2 : 1, NA = 8 * CPT;
+        constexpr int CPT = NL >= 32 ? NL / 16 : 1, NA = 8 * CPT; // NL = 64: 64 bytes of B's row per thread, one entry per round (registers)
+        constexpr bool TWO = NL <= 32;
         const uint32_t rt = threadIdx.x - (EPILOGUE_WARP0 + 4) * 32, rrow = rt >> 1, sub = rt & 1u;
         const uint32_t estart = NL == 8 ? sub : 0u, estep = NL == 8 ? 2u : 1u, c16 = NL == 8 ? 0u : sub * CPT;
         const unsigned char *ring = smem_raw + (smem0 - smem_u32(smem_raw));
@@ -446,26 +447,30 @@ template <int N, int P, int NL, int RW, int TL = 0, bool CP = false> __global__ 
                     const uint32_t e1 = start[rrow + 1];
                     uint32_t e = start[rrow] + estart;
                     // two entries per round; the next round's entry words are requested before this round's rows of B
-                    uint32_t w0 = e < e1 ? ent[e] : 0u, w1 = e + estep < e1 ? ent[e + estep] : 0u;
+                    constexpr uint32_t PER = TWO ? 2u : 1u; // entries per round
+                    uint32_t w0 = e < e1 ? ent[e] : 0u, w1 = TWO && e + estep < e1 ? ent[e + estep] : 0u;
 #pragma unroll 1
-                    for (; e < e1; e += 2u * estep) {
-                        const bool two = e + estep < e1; // a missing second entry reads row 0 and is not added
-                        const uint32_t n0 = e + 2u * estep < e1 ? ent[e + 2u * estep] : 0u, n1 = e + 3u * estep < e1 ? ent[e + 3u * estep] : 0u;
-                        uint4 b0[CPT], b1[CPT];
+                    for (; e < e1; e += PER * estep) {
+                        const bool two = TWO && e + estep < e1; // a missing second entry reads row 0 and is not added
+                        const uint32_t n0 = e + PER * estep < e1 ? ent[e + PER * estep] : 0u, n1 = TWO && e + 3u * estep < e1 ? ent[e + 3u * estep] : 0u;
+                        uint4 b0[CPT], b1[TWO ? CPT : 1];
 #pragma unroll
                         for (int c = 0; c < CPT; c++) {
                             b0[c] = *(const uint4 *)(bs + ((w0 >> 16) ^ ((c16 + c) << 4)));
-                            b1[c] = *(const uint4 *)(bs + ((w1 >> 16) ^ ((c16 + c) << 4)));
+                            if constexpr (TWO) b1[c] = *(const uint4 *)(bs + ((w1 >> 16) ^ ((c16 + c) << 4)));
                         }
                         const unsigned short v0 = (unsigned short)(w0 & 0xffffu), v1 = (unsigned short)(w1 & 0xffffu);
 #pragma unroll
                         for (int c = 0; c < CPT; c++) {
-                            const uint32_t q0[4] = {b0[c].x, b0[c].y, b0[c].z, b0[c].w}, q1[4] = {b1[c].x, b1[c].y, b1[c].z, b1[c].w};
+                            const uint32_t q0[4] = {b0[c].x, b0[c].y, b0[c].z, b0[c].w};
 #pragma unroll
                             for (int k = 0; k < 4; k++) fma_f16(acc[8 * c + 2 * k], v0, (unsigned short)(q0[k] & 0xffffu)), fma_f16(acc[8 * c + 2 * k + 1], v0, (unsigned short)(q0[k] >> 16));
-                            if (two) {
+                            if constexpr (TWO) {
+                                const uint32_t q1[4] = {b1[c].x, b1[c].y, b1[c].z, b1[c].w};
+                                if (two) {
 #pragma unroll
-                                for (int k = 0; k < 4; k++) fma_f16(acc[8 * c + 2 * k], v1, (unsigned short)(q1[k] & 0xffffu)), fma_f16(acc[8 * c + 2 * k + 1], v1, (unsigned short)(q1[k] >> 16));
+                                    for (int k = 0; k < 4; k++) fma_f16(acc[8 * c + 2 * k], v1, (unsigned short)(q1[k] & 0xffffu)), fma_f16(acc[8 * c + 2 * k + 1], v1, (unsigned short)(q1[k] >> 16));
+                                }
                             }
                         }
                         w0 = n0, w1 = n1;

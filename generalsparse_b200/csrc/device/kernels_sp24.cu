@@ -131,8 +131,9 @@ template <int N, int NL> void pick_tiled(b200_sp24_plan *pl, size_t &ring_bytes,
 {
     pl->b_off = (pl->unit_bytes + 1023u) & ~1023u, pl->stage_bytes = pl->b_off + (uint32_t)sp24::geom<N, 1>::B_BYTES;
     const size_t rem = (size_t)sp24::SM_ROWS * NL * 4; // the segment's remainder product
-    stages = (N <= 16 && 4 * (size_t)pl->stage_bytes + rem <= TILED_SMEM_MAX && env_int("GS_SP24_TL_STAGES", 4) >= 4) ? 4 : 3;
+    stages = N == 64 ? 2 : (N <= 16 && 4 * (size_t)pl->stage_bytes + rem <= TILED_SMEM_MAX && env_int("GS_SP24_TL_STAGES", 4) >= 4) ? 4 : 3;
     if constexpr (N <= 16) pl->fn = stages == 4 ? (const void *)sp24::k_b200_sp24<N, 1, NL, 8, 4> : (const void *)sp24::k_b200_sp24<N, 1, NL, 8, 3>;
+    else if constexpr (N == 64) pl->fn = (const void *)sp24::k_b200_sp24<N, 1, NL, 8, 2>; // two stages of 38 KB + 32 KB of product: two CTAs per SM
     else pl->fn = (const void *)sp24::k_b200_sp24<N, 1, NL, 8, 3>;
     ring_bytes = (size_t)stages * pl->stage_bytes + rem;
 }
@@ -241,13 +242,13 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     pl->rem_nnz = im.rem_col.size();
     if (pl->rem_nnz && !allow_remainder) return fail(cudaErrorInvalidValue); // not a 2:4 matrix
     // The remainder is multiplied inside the 2:4 kernel (b200_sp24.cuh), no second launch.  GS_SP24_FUSED_REM: 2 (default) = from
-    // tile-local blocks at N <= 32, as long as two CTAs still fit an SM and the padding to the largest block costs < 10 % of the
+    // tile-local blocks at N <= 64, as long as two CTAs still fit an SM and the padding to the largest block costs < 10 % of the
     // stream; 1 = gathers by the CTA that owns the panel (N <= 16); 0 = a separate gather launch.
     const int fuse = env_int("GS_SP24_FUSED_REM", 2);
     gs::sp24_tiled tl;
-    if (pl->rem_nnz && fuse >= 2 && p.N <= 32 && group == 1) {
+    if (pl->rem_nnz && fuse >= 2 && p.N <= 64 && group == 1) {
         try {
-            gs::localize_sp24_remainder(im, p.N == 32 ? 64u : 32u, tl);
+            gs::localize_sp24_remainder(im, p.N == 64 ? 128u : p.N == 32 ? 64u : 32u, tl);
         } catch (...) {
             tl = gs::sp24_tiled();
         }
@@ -258,7 +259,8 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
             pl->unit_bytes = tl.unit_bytes;
             if (p.N == 8) pick_tiled<16, 8>(pl, ring_bytes, stages);
             else if (p.N == 16) pick_tiled<16, 16>(pl, ring_bytes, stages);
-            else pick_tiled<32, 32>(pl, ring_bytes, stages);
+            else if (p.N == 32) pick_tiled<32, 32>(pl, ring_bytes, stages);
+            else pick_tiled<64, 64>(pl, ring_bytes, stages);
             const double content = (double)im.bytes.size() + 4.0 * (double)pl->rem_nnz + (double)gs::SP24_REM_HEADER * (double)(im.bytes.size() / gs::SP24_TILE_BYTES);
             pl->tiled = ring_bytes <= TILED_SMEM_MAX && (double)tl.bytes.size() <= 1.10 * content;
             if (pl->tiled) ctas = 2;
@@ -282,7 +284,8 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
         if (pl->tiled) {
             if (p.N == 8) cfn = stages == 4 ? (const void *)sp24::k_b200_sp24<16, 1, 8, 8, 4, true> : (const void *)sp24::k_b200_sp24<16, 1, 8, 8, 3, true>;
             else if (p.N == 16) cfn = stages == 4 ? (const void *)sp24::k_b200_sp24<16, 1, 16, 8, 4, true> : (const void *)sp24::k_b200_sp24<16, 1, 16, 8, 3, true>;
-            else cfn = (const void *)sp24::k_b200_sp24<32, 1, 32, 8, 3, true>;
+            else if (p.N == 32) cfn = (const void *)sp24::k_b200_sp24<32, 1, 32, 8, 3, true>;
+            else cfn = (const void *)sp24::k_b200_sp24<64, 1, 64, 8, 2, true>;
         } else if (pl->fused) cfn = p.N == 8 ? (const void *)sp24::k_b200_sp24<16, 1, 8, 8, 0, true> : (const void *)sp24::k_b200_sp24<16, 1, 16, 8, 0, true>;
         else switch (p.N) {
             case 8: cfn = (const void *)sp24::k_b200_sp24<16, 1, 8, 0, 0, true>; break;

@@ -322,7 +322,7 @@ def test_b200_nnz_rejects_narrow_dense(engine):
 def test_b200_sp24_kernel(engine, N, chain):
     """2:4 sparse tensor-core path (HALF): exact in reference mode, in tolerance on random values.  Exactly 2:4-pruned
     matrices have no remainder (one launch); unstructured ones send what the pattern cannot hold through remainder
-    warps of the same kernel (N <= 32: tile-local blocks that travel with the tile images) or through the gather pass (two launches).  1000 x 4096 splits its 8 row panels over all CTAs (stream-K hand-off), 300 x 1000 has a
+    warps of the same kernel (N <= 64: tile-local blocks that travel with the tile images) or through the gather pass (two launches).  1000 x 4096 splits its 8 row panels over all CTAs (stream-K hand-off), 300 x 1000 has a
     ragged K tail and empty rows, 130 x 72 is smaller than two tiles"""
     from generalsparse_b200 import synth
     from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
@@ -335,9 +335,9 @@ def test_b200_sp24_kernel(engine, N, chain):
         B1 = np.ones((cols, N), dtype=np.float32)
         C, plan = _run(engine, chain, nrows, cols, rr, cc, None, B1, N, S, 1, half=True, kernel="b200_sp24")
         assert "k_b200_sp24" in plan.kernel_name
-        if launches is not None:  # up to N=32 the remainder is multiplied by warps of the 2:4 kernel itself: one launch
-            assert plan.launch_count == (1 if N <= 32 else launches), plan.kernel_name
-            assert ("tile-local" in plan.kernel_name) == (launches == 2 and N <= 32), plan.kernel_name
+        if launches is not None:  # up to N=64 the remainder is multiplied by warps of the 2:4 kernel itself: one launch
+            assert plan.launch_count == (1 if N <= 64 else launches), plan.kernel_name
+            assert ("tile-local" in plan.kernel_name) == (launches == 2 and N <= 64), plan.kernel_name
         ref = oracle_spmm_f32(nrows, N, indptr, cc, np.ones(len(rr), np.float32), B1)
         assert np.array_equal(C.astype(np.float32), ref), plan.kernel_name
         vals = synth.synth_values(len(rr), seed=5).astype(np.float16).astype(np.float32)
@@ -393,7 +393,7 @@ def test_b200_sp24_remainder_as_separate_pass(engine, monkeypatch, N, mode):
     assert np.array_equal(plan.output(), C)
 
 
-@pytest.mark.parametrize("N", [8, 16, 32])
+@pytest.mark.parametrize("N", [8, 16, 32, 64])
 def test_b200_sp24_tile_local_remainder(engine, N):
     """the remainder cut along the tiles: dense (a stage of the ring must hold the largest block: 42 % keeps two CTAs per
     SM with three stages, 90 % does not fit and falls back), ragged K tail and row tail, a split panel per CTA (3000 x 4096: 24 panels over
@@ -415,7 +415,7 @@ def test_b200_sp24_tile_local_remainder(engine, N):
         assert ("tile-local" in plan.kernel_name) == tiled, plan.kernel_name
         if tiled:
             assert plan.launch_count == 1 and "2 CTA/SM" in plan.kernel_name, plan.kernel_name
-            assert ("3 stages" in plan.kernel_name) == (N == 32 or i == 1), plan.kernel_name
+            assert ("%d stages" % (2 if N == 64 else 3 if N == 32 or i == 1 else 4)) in plan.kernel_name, plan.kernel_name
         assert np.array_equal(C.astype(np.float32), oracle_spmm_f32(nrows, N, indptr, cc, np.ones(len(rr), np.float32), B1)), plan.kernel_name
         vals = synth.synth_values(len(rr), seed=8).astype(np.float16).astype(np.float32)
         B = synth.synth_dense(cols, N, seed=8).astype(np.float16).astype(np.float32)
