@@ -21,6 +21,7 @@ SYMBOLS = [
     "gs_create", "gs_destroy", "gs_stream", "gs_upload_array", "gs_upload_session", "gs_upload_session_as", "gs_plan_create", "gs_plan_destroy",
     "gs_plan_set_kernel", "gs_set_dense", "gs_set_dense_device", "gs_launch", "gs_run", "gs_get_output", "gs_output_device",
     "gs_spmm_host", "gs_spmm_host_async", "gs_synchronize", "gs_plan_algorithmic_bytes", "gs_plan_launch_count", "gs_plan_kernel_name", "gs_plan_sp24_probe", "gs_execute",
+    "gs_launch_no_alloc",
 ]
 
 (GS_U8, GS_U16, GS_U32, GS_U64, GS_F32, GS_F64, GS_F16) = range(7)
@@ -88,6 +89,7 @@ def lib():
         "gsh_sp24_roundtrip": (i32, [vp, vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),
         "gsh_sp24_tiled_roundtrip": (i32, [vp, vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),
         "gs_plan_sp24_probe": (i32, [vp, vp]),
+        "gs_launch_no_alloc": (i32, [vp, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

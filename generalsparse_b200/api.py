@@ -232,6 +232,10 @@ class Plan:
         check(lib().gs_get_output(self._h, _ptr(out)))
         return out
 
+    def launch_no_alloc(self, b_ptr, c_ptr, stream_ptr=None):
+        """gs_launch_no_alloc: caller's device B, C and stream; scratch in the library's static device array"""
+        check(lib().gs_launch_no_alloc(self._h, C.c_void_p(b_ptr), C.c_void_p(c_ptr), C.c_void_p(stream_ptr)))
+
     def output_device(self):
         return lib().gs_output_device(self._h)
 

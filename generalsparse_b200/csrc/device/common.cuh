@@ -87,6 +87,9 @@ void b200_tile_free(b200_tile_plan *plan);
 const char *b200_tile_kernel_name(const b200_tile_plan *plan);
 uint64_t b200_tile_bytes(const b200_tile_plan *plan, uint64_t rows, uint64_t cols);
 uint64_t b200_tile_pairs(const b200_tile_plan *plan);
+// the launch of gs_launch_no_alloc: workspace and flags in a file-scope device array instead of the plan's allocations
+cudaError_t b200_tile_launch_no_alloc(const b200_tile_plan *plan, int device, const void *B, void *C, cudaStream_t s, const char **why);
+size_t b200_tile_no_alloc_scratch_bytes();
 
 struct b200_sp24_plan; // opaque, kernels_sp24.cu
 cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_remainder, b200_sp24_plan **out, cudaStream_t s);

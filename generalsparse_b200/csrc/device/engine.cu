@@ -553,6 +553,20 @@ gs_status gs_get_output(gs_plan *p, void *C_host)
 
 void *gs_output_device(gs_plan *p) { return p ? p->C_dev : nullptr; }
 
+gs_status gs_launch_no_alloc(gs_plan *p, const void *B_dev, void *C_dev, void *stream)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p && B_dev && C_dev, "null argument");
+    GS_REQUIRE(p->kernel == GS_FAMILY_B200_TCGEN05 && p->tile_plan, "gs_launch_no_alloc: the plan must run the b200_tcgen05 kernel (gs_plan_set_kernel)");
+    GS_REQUIRE(((uintptr_t)B_dev & 15) == 0 && ((uintptr_t)C_dev & 15) == 0, "device B and C must be 16-byte aligned");
+    CUDA_TRY(cudaSetDevice(p->ctx->device));
+    const char *why = nullptr;
+    cudaError_t e = gsd::b200_tile_launch_no_alloc(p->tile_plan, p->ctx->device, B_dev, C_dev, (cudaStream_t)stream, &why);
+    if (e == cudaErrorInvalidValue && why) throw gs::Error(std::string("gs_launch_no_alloc: ") + why + " (the scratch array is fixed at " + std::to_string(gsd::b200_tile_no_alloc_scratch_bytes()) + " bytes)");
+    CUDA_TRY(e);
+    GS_API_END
+}
+
 gs_status gs_spmm_host(gs_plan *p, const void *B_host, void *C_host)
 {
     GS_API_BEGIN

@@ -267,3 +267,94 @@ uint64_t b200_tile_bytes(const b200_tile_plan *pl, uint64_t rows, uint64_t cols)
 uint64_t b200_tile_pairs(const b200_tile_plan *pl) { return pl->pairs; }
 
 } // namespace gsd
+
+// ---------------------------------------------------------------------------------------------------------------------
+// gs_launch_no_alloc: the same kernel for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  The stream-K workspace and the hand-off flags, which b200_tile_prepare allocates per
+// plan, live here in one file-scope device array of a fixed, modest size that every launch through this entry point shares
+// (every GPU that loads the library holds it until exit).  The caller passes B, C and the stream; nothing on this path
+// allocates.  No counterpart in the reference.
+namespace gsd {
+namespace {
+constexpr uint32_t NA_MAX_CTAS = 160;      // CTAs of one launch (one per SM; a B200 has 148)
+constexpr uint32_t NA_MAX_N = 64;          // dense width
+constexpr uint32_t NA_MAX_PANELS = 16384;  // row panels of 128 rows: 2 097 152 rows
+constexpr size_t NA_WS_BYTES = (size_t)NA_MAX_CTAS * tile::TM * NA_MAX_N * sizeof(float); // 5 242 880
+constexpr size_t NA_FLAG_WORDS = 2 * (size_t)NA_MAX_CTAS + NA_MAX_PANELS;                 // ready + slot_free + panel_seq
+constexpr size_t NA_BYTES = NA_WS_BYTES + NA_FLAG_WORDS * sizeof(uint32_t);               // 5 309 696 bytes
+constexpr int NA_MAX_DEVICES = 64;
+} // namespace
+
+// In host code this name is a host-side stand-in for the symbol, NOT a device address: it must never be handed to a kernel
+// or to cudaMemsetAsync.  The device address comes from cudaGetSymbolAddress, once per device (no_alloc_scratch below).
+static __device__ __align__(256) unsigned char g_no_alloc_scratch[NA_BYTES];
+
+// device address of g_no_alloc_scratch on `device` (which must be current); looked up once per device
+static cudaError_t no_alloc_scratch(int device, unsigned char **out)
+{
+    static unsigned char *addr[NA_MAX_DEVICES] = {nullptr};
+    if (device < 0 || device >= NA_MAX_DEVICES) return cudaErrorInvalidDevice;
+    unsigned char *p = __atomic_load_n(&addr[device], __ATOMIC_ACQUIRE);
+    if (!p) {
+        int cur = -1;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess) return e;
+        if (cur != device) return cudaErrorInvalidDevice;
+        void *sym = nullptr;
+        e = cudaGetSymbolAddress(&sym, g_no_alloc_scratch);
+        if (e != cudaSuccess) return e;
+        if (!sym || ((uintptr_t)sym & 255u)) return cudaErrorInvalidSymbol;
+        p = (unsigned char *)sym;
+        __atomic_store_n(&addr[device], p, __ATOMIC_RELEASE); // two threads racing here store the same address
+    }
+    *out = p;
+    return cudaSuccess;
+}
+
+size_t b200_tile_no_alloc_scratch_bytes() { return NA_BYTES; }
+
+// One launch of plan `pl` with the shared scratch.  `device` is the plan's device and is current.  *why names the limit
+// that was exceeded when the return value is cudaErrorInvalidValue.  Calls that overlap on the GPU (two streams, or two
+// host threads) race on the scratch; calls on one stream are ordered by the stream.
+cudaError_t b200_tile_launch_no_alloc(const b200_tile_plan *pl, int device, const void *B, void *C, cudaStream_t s, const char **why)
+{
+    *why = nullptr;
+    if (pl->N > (int)NA_MAX_N) {
+        *why = "dense width above the no-alloc maximum of 64";
+        return cudaErrorInvalidValue;
+    }
+    if (pl->grid > NA_MAX_CTAS) {
+        *why = "more CTAs per launch than the no-alloc maximum of 160";
+        return cudaErrorInvalidValue;
+    }
+    if (pl->n_panels > NA_MAX_PANELS) {
+        *why = "more row panels than the no-alloc maximum of 16384 (2 097 152 rows)";
+        return cudaErrorInvalidValue;
+    }
+    unsigned char *scratch = nullptr;
+    cudaError_t e = no_alloc_scratch(device, &scratch);
+    if (e != cudaSuccess) return e;
+    float *ws = (float *)scratch;
+    uint32_t *flags = (uint32_t *)(scratch + NA_WS_BYTES);
+    // the array keeps the last call's contents: the flags compare against the launch number, so they start at zero
+    // and this launch is number 1; the workspace is written before it is read and needs no clearing
+    const size_t n_flags = 2 * (size_t)pl->grid + pl->n_panels;
+    if ((e = cudaMemsetAsync(flags, 0, n_flags * sizeof(uint32_t), s)) != cudaSuccess) return e;
+    tile::tile_args a;
+    a.tile_ptr = pl->tile_ptr, a.off = pl->off, a.val = pl->val, a.B = B, a.C = C, a.out_row = pl->out_row;
+    a.ws = ws, a.flags = flags, a.slot_free = flags + pl->grid, a.panel_seq = flags + 2 * (size_t)pl->grid;
+    a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.K = pl->K, a.seq = 1, a.ptr_cap = pl->ptr_cap;
+    a.skip = 0, a.consumer_fence = 1, a.bulk_zero = 0, a.dbg = nullptr;
+    // the tensor map of B is a kernel parameter, encoded on the host into a local (the plan's own map stays as it is)
+    b200_tile_plan tmp;
+    tmp.N = pl->N, tmp.K = pl->K;
+    if ((e = encode_b_map(&tmp, B)) != cudaSuccess) return e;
+    void *args[] = {&a, &tmp.b_map};
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(tile::THREADS), cfg.dynamicSmemBytes = pl->smem, cfg.stream = s;
+    cfg.attrs = nullptr, cfg.numAttrs = 0; // no programmatic dependent launch: the memset above must have completed
+    return cudaLaunchKernelExC(&cfg, pl->fn, args);
+}
+
+} // namespace gsd

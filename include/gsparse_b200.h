@@ -202,6 +202,17 @@ gs_status gs_run(gs_plan *p, int repeat, float *ms_per_iter);
 /* C (rows x N row-major, y_arr[row*N+n]) in the plan's value type (f32, or f16 when half) */
 gs_status gs_get_output(gs_plan *p, void *C_host);
 void *gs_output_device(gs_plan *p);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  One SpMM of a plan that runs the
+ * GS_FAMILY_B200_TCGEN05 kernel, with the caller's B (K x N fp16, device, 16-byte aligned), the caller's C (rows x N fp16,
+ * device, 16-byte aligned) and the caller's stream (cudaStream_t; NULL = the legacy default stream).  The kernel's scratch
+ * -- the stream-K workspace and the hand-off flags gs_plan_create allocates per plan -- is a file-scope device array of
+ * 5 309 696 bytes that every GPU which loads the library holds until exit; this call allocates and frees nothing (no
+ * cudaMalloc, cudaFree or allocating library routine).  Limits, beyond which GS_ERR_INVALID is returned with the limit
+ * in gs_last_error(): N <= 64, at most 160 CTAs per launch (one per SM), at most 16 384 row panels (2 097 152 rows).
+ * Every call shares the array: calls that overlap on the GPU (different streams, or several host threads) race; calls
+ * on one stream are ordered.  Rows of C the matrix does not have (trimmed trailing empty rows) are not written. */
+gs_status gs_launch_no_alloc(gs_plan *p, const void *B_dev, void *C_dev, void *stream);
 /* host-buffer round trip the reference's execute_binary does through files (executor.cc:6-58):
  * H2D of B, launch, D2H of C, all on gs_stream(); returns after the stream drained */
 gs_status gs_spmm_host(gs_plan *p, const void *B_host, void *C_host);
