@@ -133,7 +133,7 @@ def run_reference(args, rank, world):
     compiled from /root/reference into oracle/_ref when it was built; else the oracle port) on all host threads."""
     if rank != 0:
         return
-    from generalsparse_b200 import oracle_check as oc
+    from oracle import oracle_check as oc
     r, c, v = make_weight(1)
     N = args.n
     B = np.random.default_rng(7).uniform(-1, 1, (COLS, N)).astype(np.float32)
@@ -170,7 +170,7 @@ def run_c4(args, rank, world, local):
     import torch
     import torch.distributed as dist
     from generalsparse_b200 import api, shard, synth
-    from generalsparse_b200 import oracle_check as oc
+    from oracle import oracle_check as oc
 
     torch.cuda.set_device(local)
     if world > 1:
@@ -318,7 +318,7 @@ def main():
     # ---- parity gate on the timed configuration (oracle = checker only) ------------------------------------------------
     parity = None
     if rank == 0:
-        from generalsparse_b200 import oracle_check as oc
+        from oracle import oracle_check as oc
         plans[0].run(1)
         C = plans[0].output().astype(np.float64)
         indptr = oc.csr_from_coo(my_rows, r)
@@ -429,7 +429,7 @@ def main():
         "gpu_launches": args.steps * plans[0].launch_count, "clocks": clocks, "parity": parity,
     }
     if not args.no_cpu_baseline and world == 1:
-        from generalsparse_b200 import oracle_check as oc
+        from oracle import oracle_check as oc
         indptr = oc.csr_from_coo(my_rows, r)
         Bf = B_host.numpy().astype(np.float32)
         cores = os.cpu_count() or 1

@@ -29,6 +29,7 @@ struct dev_array {
     int dtype = GS_U32;   // device dtype
     uint64_t max_value = 0;
     uint64_t align = 0;   // gcd of all entries (offset arrays): the row alignment vector loads may rely on
+    bool iota = false;    // entry i == i for every i: a first_row_indices array of a row level with one row per block
 };
 
 struct gs_ctx {
@@ -117,13 +118,15 @@ static void upload(gs_ctx *ctx, const std::string &key, const void *host, uint64
         GS_REQUIRE(dtype == GS_U8 || dtype == GS_U16 || dtype == GS_U32 || dtype == GS_U64, "index arrays must be unsigned integers");
         std::vector<uint64_t> w(len);
         uint64_t mx = 0, g = 0;
+        bool iota = true;
         for (uint64_t i = 0; i < len; i++) {
             uint64_t v = dtype == GS_U8 ? ((const uint8_t *)host)[i] : dtype == GS_U16 ? ((const uint16_t *)host)[i] : dtype == GS_U32 ? ((const uint32_t *)host)[i] : ((const uint64_t *)host)[i];
             w[i] = v;
             mx = v > mx ? v : mx;
             g = gcd64(g, v);
+            iota = iota && v == i;
         }
-        d.max_value = mx, d.align = g;
+        d.max_value = mx, d.align = g, d.iota = iota;
         const bool is_col = key_has(key, "nz_col_indices");
         const bool is_bits = key_has(key, "thread_bit_map") || key_has(key, "segment_empty_flag") || (key_has(key, "bit_map_of_thread") && key_has(key, "WARP_META"));
         if (is_bits) d.dtype = GS_U64;
@@ -232,6 +235,23 @@ static uint64_t arr_bytes(const gs_ctx *ctx, const char *pos, const char *name, 
     return d ? d->len * dsize(d->dtype) : 0;
 }
 
+// the row level the B200 row / tile / 2:4 kernels read (the same choice their prepare functions make), or null
+static const char *row_level(const gsd::dev_arrays &a)
+{
+    return (a.t_first_nz && a.t_first_row && !a.t_nz_relative) ? "THREAD_META" : (a.w_first_nz && a.w_first_row) ? "WARP_META" : (a.tb_first_nz && a.tb_first_row) ? "TBLOCK_META" : nullptr;
+}
+
+// Those kernels treat block i of the row level as row first_row_indices[i] and STORE its sum: that is only SpMM when every block is one
+// whole row, i.e. first_row_indices = 0, 1, 2, ... (row-direction blocking with block size 1).  An nnz-direction chain (several blocks per
+// row, which the reference refuses to pair with a total reduction) or a row block > 1 would silently overwrite rows.
+static void require_one_row_per_block(const gs_plan *p, const char *who)
+{
+    const char *lvl = row_level(p->lp.a);
+    if (!lvl) throw gs::Error(std::string(who) + ": needs a row-direction chain (first_row_indices / first_nz_indices at one level)");
+    const dev_array *fr = find_arr(p->ctx, lvl, "first_row_indices", p->desc.sub_matrix_id);
+    if (!fr || !fr->iota) throw gs::Error(std::string(who) + ": " + lvl + " first_row_indices is not 0, 1, 2, ...: the kernel needs one whole row per block (row-direction blocking, block size 1)");
+}
+
 static void select_kernel(gs_plan *p, int family)
 {
     const gsd::dev_arrays &a = p->lp.a;
@@ -274,6 +294,7 @@ static void select_kernel(gs_plan *p, int family)
         break;
     case GS_FAMILY_B200_ROW_SMEM: {
         if (p->row_plan) gsd::b200_row_free(p->row_plan), p->row_plan = nullptr;
+        require_one_row_per_block(p, "b200_row_smem");
         gsd::launch_params lp = p->lp;
         // row alignment: vector loads need every row offset to be a multiple of 8 (sparse coarsen 8 padding)
         const char *lvl = (a.t_first_nz && a.t_first_row && !a.t_nz_relative) ? "THREAD_META" : (a.w_first_nz && a.w_first_row) ? "WARP_META" : "TBLOCK_META";
@@ -289,6 +310,7 @@ static void select_kernel(gs_plan *p, int family)
     case GS_FAMILY_B200_TCGEN05: {
         if (p->tile_plan) gsd::b200_tile_free(p->tile_plan), p->tile_plan = nullptr;
         GS_REQUIRE(p->half, "b200_tcgen05: the tensor-core path multiplies fp16 operands (HALF); fp32 values stay on the gather kernels");
+        require_one_row_per_block(p, "b200_tcgen05");
         cudaError_t e = gsd::b200_tile_prepare(p->lp, ctx->sm_count, &p->tile_plan, ctx->stream);
         if (e == cudaErrorInvalidValue) throw gs::Error("b200_tcgen05: needs N in {16,32,64,128,256}, HALF values and a row-direction chain with row block 1");
         CUDA_TRY(e);
@@ -297,6 +319,7 @@ static void select_kernel(gs_plan *p, int family)
     case GS_FAMILY_B200_SP24: {
         if (p->sp24_plan) gsd::b200_sp24_free(p->sp24_plan), p->sp24_plan = nullptr;
         GS_REQUIRE(p->half, "b200_sp24: the sparse tensor-core path multiplies fp16 operands (HALF); fp32 values stay on the gather kernels");
+        require_one_row_per_block(p, "b200_sp24");
         cudaError_t e = gsd::b200_sp24_prepare(p->lp, ctx->sm_count, true, &p->sp24_plan, ctx->stream);
         if (e == cudaErrorInvalidValue) throw gs::Error("b200_sp24: needs N in {8,16,32,64,128,256}, HALF values and a row-direction chain with row block 1");
         CUDA_TRY(e);
@@ -480,6 +503,7 @@ gs_status gs_plan_set_kernel(gs_plan *p, int family)
     GS_API_BEGIN
     GS_REQUIRE(p, "null plan");
     CUDA_TRY(cudaSetDevice(p->ctx->device));
+    p->ctx->row_chain = false; // prepare() puts copies and layout kernels on the stream
     select_kernel(p, family);
     GS_API_END
 }
@@ -514,6 +538,10 @@ gs_status gs_set_dense_device(gs_plan *p, const void *B_dev)
     GS_REQUIRE(p && B_dev, "null argument");
     GS_REQUIRE(((uintptr_t)B_dev & 15) == 0, "device B must be 16-byte aligned");
     p->B_use = B_dev;
+    // whoever produced this B on gs_stream() is not a launch of ours: the next launch must not start under programmatic dependent launch
+    // (the B200 kernels read A and B before griddepcontrol.wait) -- break the chain when the pointer changes hands
+    p->ctx->row_chain = false;
+    for (int i = 1; i < gs_ctx::MAX_LAUNCH; i++) p->ctx->chain_extra[i] = false;
     GS_API_END
 }
 

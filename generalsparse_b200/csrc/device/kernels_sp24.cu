@@ -13,6 +13,7 @@
 namespace gsd {
 
 struct b200_sp24_plan {
+    bool poisoned = false; // a launch failed half way (remainder pass out, 2:4 kernel not): the flags are out of step
     unsigned char *img = nullptr;
     uint32_t *out_row = nullptr, *flags = nullptr; // flags: grid ready + grid slot_free + n_panels panel_seq + rem_ctas rem_seq
     float *ws = nullptr, *c_add = nullptr;         // c_add: two buffers (launch parity) of n_panels * 128 x N fp32, when there is a remainder
@@ -372,13 +373,18 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
         cudaError_t em = encode_b_map(pl, p.B);
         if (em != cudaSuccess) return em;
     }
-    const uint32_t seq = ++pl->seq;
+    // the launch number is committed only after every launch of this call succeeded: the kernels of later launches wait for flags == seq - 1, and a
+    // number no kernel ever publishes would make them spin for ever.  A call that launched its remainder pass but not the 2:4 kernel leaves
+    // rem_seq ahead of panel_seq: the plan refuses further launches instead of deadlocking.
+    if (pl->poisoned) return cudaErrorLaunchFailure;
+    const uint32_t seq = pl->seq + 1;
     uint32_t *slot_free = pl->flags + pl->grid, *panel_seq = pl->flags + 2 * (size_t)pl->grid, *rem_seq = panel_seq + pl->n_panels;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cudaLaunchConfig_t cfg;
     float *c_add = nullptr;
+    bool rem_launched = false;
     static const bool skip_rem = env_int("GS_SP24_SKIP_REM", 0) != 0; // timing experiments only: wrong results on a matrix with a remainder
     if (pl->rem_nnz && !skip_rem && !pl->fused) {
         c_add = pl->c_add + (size_t)(seq & 1u) * pl->n_panels * sp24::SM_ROWS * pl->N;
@@ -390,7 +396,8 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
         cfg.gridDim = dim3(pl->n_panels * (128 / sp24::REM_ROWS)), cfg.blockDim = dim3(sp24::REM_THREADS), cfg.stream = s;
         cfg.attrs = attr, cfg.numAttrs = p.pdl ? 1 : 0;
         cudaError_t e = cudaLaunchKernelExC(&cfg, pl->rem_fn, rargs);
-        if (e != cudaSuccess) return e;
+        if (e != cudaSuccess) return e; // nothing launched: seq stays
+        rem_launched = true;
     }
     sp24::sp24_args a;
     a.img = pl->img, a.C = p.C, a.out_row = pl->out_row, a.c_add = c_add, a.rem_seq = rem_seq, a.rem_per_flag = sp24::REM_PER_FLAG;
@@ -406,7 +413,10 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
     memset(&cfg, 0, sizeof cfg);
     cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(pl->threads), cfg.dynamicSmemBytes = pl->smem, cfg.stream = s;
     cfg.attrs = attr, cfg.numAttrs = (p.pdl || (pl->rem_nnz && !pl->fused)) ? 1 : 0; // behind its own remainder launch the 2:4 kernel always overlaps: the flags order them
-    return cudaLaunchKernelExC(&cfg, pl->fn, args);
+    const cudaError_t e = cudaLaunchKernelExC(&cfg, pl->fn, args);
+    if (e == cudaSuccess) pl->seq = seq;
+    else if (rem_launched) pl->poisoned = true;
+    return e;
 }
 
 void b200_sp24_free(b200_sp24_plan *pl)

@@ -228,11 +228,11 @@ cudaError_t b200_tile_launch(b200_tile_plan *pl, const launch_params &p, cudaStr
     tile::tile_args a;
     a.tile_ptr = pl->tile_ptr, a.off = pl->off, a.val = pl->val, a.B = p.B, a.C = p.C, a.out_row = pl->out_row;
     a.ws = pl->ws, a.flags = pl->flags, a.slot_free = pl->flags + pl->grid, a.panel_seq = pl->flags + 2 * (size_t)pl->grid;
-    a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.K = p.a.cols, a.seq = ++pl->seq, a.ptr_cap = pl->ptr_cap;
+    a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.K = p.a.cols, a.seq = pl->seq + 1, a.ptr_cap = pl->ptr_cap;
     a.skip = (uint32_t)env_int("GS_TILE_SKIP", 0);
     a.consumer_fence = (uint32_t)env_int("GS_TILE_CONSUMER_FENCE", 1);
     a.bulk_zero = (uint32_t)env_int("GS_TILE_BULK_ZERO", 0);
-    a.dbg = pl->dbg ? pl->dbg + (size_t)(pl->seq % DBG_RING) * ((size_t)pl->grid * 32 + 256) : nullptr;
+    a.dbg = pl->dbg ? pl->dbg + (size_t)(a.seq % DBG_RING) * ((size_t)pl->grid * 32 + 256) : nullptr;
     if (pl->b_mapped != p.B) {
         cudaError_t em = encode_b_map(pl, p.B);
         if (em != cudaSuccess) return em;
@@ -246,6 +246,7 @@ cudaError_t b200_tile_launch(b200_tile_plan *pl, const launch_params &p, cudaStr
     cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(tile::THREADS), cfg.dynamicSmemBytes = pl->smem, cfg.stream = s;
     cfg.attrs = attr, cfg.numAttrs = p.pdl ? 1 : 0;
     cudaError_t e = cudaLaunchKernelExC(&cfg, pl->fn, args);
+    if (e == cudaSuccess) pl->seq = a.seq; // committed only now: a number no kernel publishes would make every later launch spin for ever
     if (pl->dbg && pl->seq == 100) dump_debug(pl, s);
     return e;
 }

@@ -508,12 +508,15 @@ class thread_total_reduce_operator : public basic_operator { // operator.hpp:107
     }
     bool is_valid_according_to_operator(const operator_context &h) override
     {
-        // needs a thread-level distribution and no earlier implementing operator (thread_total_reduce_operator.cc:23-31)
-        return any_name_has(h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id), "thread") &&
-               h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty();
+        // thread_total_reduce_operator.cc:14-40: a thread-level distribution, no nnz-direction operator before it (an nnz chunk is not a
+        // row: the token stores its sum), nothing implemented yet
+        const opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        return h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty() && !any_name_has(d, "nnz") && any_name_has(d, "thread");
     }
+    bool is_valid_according_to_metadata() override { return meta_data_set_ptr->is_exist(THREAD_META, "first_nz_indices", target_matrix_id); } // :41-55
     void run(bool) override
     {
+        GS_REQUIRE(is_valid_according_to_metadata(), "thread_total_reduce_operator: no THREAD first_nz_indices");
         reduction_token t;
         t.kind = RED_TOTAL_BMT, t.need_warp_reduction = nwr_, t.sparse_coarsen_factor = S_, t.coarsen_factor = C_;
         code_generator_ptr->set_reduction_token(THREAD_META, t);
@@ -535,11 +538,14 @@ class thread_bit_map_operator : public basic_operator { // operator.hpp:1093, op
     }
     bool is_valid_according_to_operator(const operator_context &h) override
     {
-        return any_name_has(h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id), "thread") &&
-               h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty();
+        // thread_bit_map_operator.cc: nothing implemented yet, a thread-level AND an nnz-direction distribution
+        const opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        return h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty() && any_name_has(d, "thread") && any_name_has(d, "nnz");
     }
+    bool is_valid_according_to_metadata() override { return meta_data_set_ptr->is_exist(THREAD_META, "first_nz_indices", target_matrix_id); }
     void run(bool) override
     {
+        GS_REQUIRE(is_valid_according_to_metadata(), "thread_bit_map_operator: no THREAD first_nz_indices");
         auto &ms = *meta_data_set_ptr;
         int id = target_matrix_id;
         steps::recs r;
@@ -567,10 +573,14 @@ class warp_total_reduce_operator : public basic_operator { // operator.hpp:1117
     warp_total_reduce_operator(std::shared_ptr<code_generator> cg, int C) : basic_operator("warp_total_reduce_operator", std::move(cg), IMPLEMENTING_OP), C_(C) {}
     bool is_valid_according_to_operator(const operator_context &h) override
     {
-        return any_name_has(h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id), "warp");
+        // warp_total_reduce_operator.cc: nothing implemented yet, a warp-level distribution, no nnz-direction operator
+        const opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        return h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty() && !any_name_has(d, "nnz") && any_name_has(d, "warp");
     }
+    bool is_valid_according_to_metadata() override { return meta_data_set_ptr->is_exist(WARP_META, "first_nz_indices", target_matrix_id); }
     void run(bool) override
     {
+        GS_REQUIRE(is_valid_according_to_metadata(), "warp_total_reduce_operator: no WARP first_nz_indices");
         reduction_token t;
         t.kind = RED_TOTAL_WARP, t.coarsen_factor = C_;
         code_generator_ptr->set_reduction_token(WARP_META, t);
@@ -592,12 +602,21 @@ class warp_group_operator : public basic_operator {
     }
     bool is_valid_according_to_operator(const operator_context &h) override
     {
-        // must follow the thread-level reduction that feeds it
-        opv im = h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id);
-        return any_name_has(im, bitmap_ ? "thread_total_reduce" : "thread_bit_map");
+        // warp_bit_map_operator.cc: a thread-level distribution, no warp-level one, no nnz-direction operator;
+        // warp_segment_reduce_operator.cc: thread-level AND nnz-direction distribution, no warp-level one, thread_bit_map implemented.
+        // Both consume what the thread-level reduction before them leaves, so that one must have run (the reference fails later, in the token)
+        const opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id), im = h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id);
+        if (!any_name_has(d, "thread") || any_name_has(d, "warp")) return false;
+        if (bitmap_) return !any_name_has(d, "nnz") && any_name_has(im, "thread_total_reduce");
+        return any_name_has(d, "nnz") && any_name_has(im, "thread_bit_map");
+    }
+    bool is_valid_according_to_metadata() override
+    {
+        return meta_data_set_ptr->is_exist(THREAD_META, "first_nz_indices", target_matrix_id) && !meta_data_set_ptr->is_exist(WARP_META, "first_nz_indices", target_matrix_id);
     }
     void run(bool) override
     {
+        GS_REQUIRE(is_valid_according_to_metadata(), name + ": needs THREAD first_nz_indices and no WARP first_nz_indices");
         auto &ms = *meta_data_set_ptr;
         int id = target_matrix_id;
         uint64_t vw = (uint64_t)get_config().as_float("VECTOR_WIDTH");
@@ -627,10 +646,14 @@ class tblock_total_reduce_operator : public basic_operator { // operator.hpp:118
     tblock_total_reduce_operator(std::shared_ptr<code_generator> cg, int C) : basic_operator("tblock_total_reduce_operator", std::move(cg), IMPLEMENTING_OP), C_(C) {}
     bool is_valid_according_to_operator(const operator_context &h) override
     {
-        return any_name_has(h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id), "tblock");
+        // tblock_total_reduce_operator.cc: nothing implemented yet, a tblock-level distribution, no nnz-direction operator
+        const opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        return h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty() && !any_name_has(d, "nnz") && any_name_has(d, "tblock");
     }
+    bool is_valid_according_to_metadata() override { return meta_data_set_ptr->is_exist(TBLOCK_META, "first_nz_indices", target_matrix_id); }
     void run(bool) override
     {
+        GS_REQUIRE(is_valid_according_to_metadata(), "tblock_total_reduce_operator: no TBLOCK first_nz_indices");
         reduction_token t;
         t.kind = RED_TOTAL_TBLOCK, t.coarsen_factor = C_;
         code_generator_ptr->set_reduction_token(TBLOCK_META, t);
@@ -651,7 +674,11 @@ class tblock_thread_bit_map_operator : public basic_operator { // operator.hpp:1
     }
     bool is_valid_according_to_operator(const operator_context &h) override
     {
-        return any_name_has(h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id), "thread_total_reduce");
+        // tblock_thread_bit_map_operator.cc: a thread-level distribution, no tblock-level one, no nnz-direction operator; it consumes
+        // the BMT sums of thread_total_reduce
+        const opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        return any_name_has(d, "thread") && !any_name_has(d, "tblock") && !any_name_has(d, "nnz") &&
+               any_name_has(h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id), "thread_total_reduce");
     }
     void run(bool) override
     {

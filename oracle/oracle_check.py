@@ -9,7 +9,7 @@ import os
 
 import numpy as np
 
-_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))  # repo root: this file lives in oracle/
 _ORACLE = os.path.join(_ROOT, "oracle", "liboracle_spmm.so")
 _REF = os.path.join(_ROOT, "oracle", "_ref", "libref_spmm.so")
 _o = None

@@ -2,7 +2,7 @@ import sys, os, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from generalsparse_b200 import api, synth
-from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_f64acc, oracle_spmm_absrow
+from oracle.oracle_check import csr_from_coo, oracle_spmm_f64acc, oracle_spmm_absrow
 rows = int(os.environ.get("ROWS", 1000000)); N = 32
 t=time.time()
 r, c = synth.synth_matrix("powerlaw", rows, rows, seed=4, avg_deg=20.0, alpha=2.1, cap=100000)

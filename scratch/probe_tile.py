@@ -3,7 +3,7 @@ import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from generalsparse_b200 import api, synth
-from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_f64acc
+from oracle.oracle_check import csr_from_coo, oracle_spmm_f64acc
 
 eng = api.Engine(0)
 for N in (32, 16, 64, 128):

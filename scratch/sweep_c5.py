@@ -9,7 +9,7 @@ import time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from generalsparse_b200 import api, synth
-from generalsparse_b200 import oracle_check as oc
+from oracle import oracle_check as oc
 
 M = int(os.environ.get("C5_ROWS", 16384))
 NS = [1, 2, 4, 8, 16, 32, 64, 128, 256, 512]

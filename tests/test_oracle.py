@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 from generalsparse_b200 import synth
-from generalsparse_b200.oracle_check import (csr_from_coo, oracle_lib, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc,
+from oracle.oracle_check import (csr_from_coo, oracle_lib, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc,
                                              ref_lib, ref_spmm_f32)
 
 

@@ -28,7 +28,7 @@ def _worker(rank, world, port, out_dir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from generalsparse_b200 import api, shard, synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_f32
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_f32
 
     rows, cols, N = 3000, 3000, 8
     r, c = synth.synth_matrix("powerlaw", rows, cols, seed=7, avg_deg=8.0)  # skewed rows: the case balancing is for

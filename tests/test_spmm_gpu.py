@@ -62,7 +62,7 @@ CASES = [("tiny", "uniform", 64, 48, dict(density=0.085)), ("ragged", "ragged", 
 def test_reference_mode_exact(engine, family, case, N, coarsen):
     """all-ones A and B: C[i][*] == nnz(row i), exact, for every family on every matrix shape"""
     from generalsparse_b200 import api
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_f32
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_f32
     name, kind, rows, cols, kw = case
     r, c = _matrix(kind, rows, cols, seed=CASES.index(case) + 1, **kw)
     B = np.ones((cols, N), dtype=np.float32)
@@ -82,7 +82,7 @@ def test_reference_mode_exact(engine, family, case, N, coarsen):
 @pytest.mark.parametrize("half", [False, True], ids=["fp32", "half"])
 def test_random_values_tolerance(engine, family, half):
     from generalsparse_b200 import synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
     rows, cols, N = 344, 512, 16
     r, c = _matrix("uniform", rows, cols, seed=4, density=0.3)
     vals = synth.synth_values(len(r), seed=4)
@@ -109,7 +109,7 @@ def test_random_values_tolerance(engine, family, half):
 def test_b200_row_kernel(engine, N, half, chain):
     """the B200 row kernel on each row-direction chain: exact in reference mode, in tolerance on random values"""
     from generalsparse_b200 import synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
     rows, cols = 1000, 4096 if N <= 16 else 1024
     r, c = _matrix("uniform", rows, cols, seed=21, density=0.1)
     r2, c2 = _matrix("ragged", 300, cols, seed=22, mean_len=20.0, empty_frac=0.2)
@@ -224,7 +224,7 @@ def test_b200_tile_kernel(engine, N, chain):
     1000 x 4096 splits its 8 row panels over all CTAs (stream-K hand-off), 300 x 1000 has a ragged K tail and
     empty rows, 130 x 70 is smaller than two tiles"""
     from generalsparse_b200 import synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
     mats = [("uniform", 1000, 4096, dict(density=0.1)), ("ragged", 300, 1000, dict(mean_len=20.0, empty_frac=0.2)), ("uniform", 130, 70, dict(density=0.3))]
     for i, (kind, nrows, cols, kw) in enumerate(mats):
         rr, cc = _matrix(kind, nrows, cols, seed=51 + i, **kw)
@@ -251,7 +251,7 @@ def test_b200_tile_overlapped_launches_keep_order(engine):
     up as the LAST launch's product although the dense matrix alternates between launches"""
     import torch
     from generalsparse_b200 import api, synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
     rows, cols, N = 3000, 4096, 32
     r, c = _matrix("uniform", rows, cols, seed=61, density=0.2)
     vals = synth.synth_values(len(r), seed=61).astype(np.float16).astype(np.float32)
@@ -282,7 +282,7 @@ def test_b200_nnz_kernel(engine, N, half, chain):
     in tolerance on random values; power-law rows (rows far longer than a run, atomics), ragged rows with empty rows
     (segment_empty_flag / segment_empty_row_indices), a matrix smaller than one run"""
     from generalsparse_b200 import synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
     mats = [("powerlaw", 3000, 3000, dict(avg_deg=20.0, alpha=2.1)), ("ragged", 700, 450, dict(mean_len=9.0, empty_frac=0.3)),
             ("uniform", 40, 30, dict(density=0.1)), ("uniform", 344, 512, dict(density=0.3))]
     for i, (kind, nrows, cols, kw) in enumerate(mats):
@@ -325,7 +325,7 @@ def test_b200_sp24_kernel(engine, N, chain):
     warps of the same kernel (N <= 64: tile-local blocks that travel with the tile images) or through the gather pass (two launches).  1000 x 4096 splits its 8 row panels over all CTAs (stream-K hand-off), 300 x 1000 has a
     ragged K tail and empty rows, 130 x 72 is smaller than two tiles"""
     from generalsparse_b200 import synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
     mats = [("nm24", 1000, 4096, {}, 1), ("nm24", 130, 72, {}, 1), ("uniform", 1000, 4096, dict(density=0.3), 2),
             ("ragged", 300, 1000, dict(mean_len=20.0, empty_frac=0.2), None)]
     for i, (kind, nrows, cols, kw, launches) in enumerate(mats):
@@ -356,7 +356,7 @@ def test_b200_sp24_panels_per_cta(engine, monkeypatch, N, panels):
     """the other unit size than the default for this N (GS_SP24_PANELS): one or two row panels per CTA and k step;
     9 panels is an odd count (the image is padded to whole units), with and without a remainder"""
     from generalsparse_b200 import synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
     monkeypatch.setenv("GS_SP24_PANELS", str(panels))
     for i, (kind, kw) in enumerate([("nm24", {}), ("uniform", dict(density=0.3))]):
         nrows, cols = 1100, 2048
@@ -378,7 +378,7 @@ def test_b200_sp24_remainder_as_separate_pass(engine, monkeypatch, N, mode):
     """GS_SP24_FUSED_REM=0: the gather pass in front of the 2:4 launch also at the widths that fuse it by default;
     =1: gathers by eight warps of the CTA that owns the panel (N <= 16), not the tile-local blocks"""
     from generalsparse_b200 import synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
     monkeypatch.setenv("GS_SP24_FUSED_REM", str(mode))
     nrows, cols = 1000, 4096
     rr, cc = _matrix("uniform", nrows, cols, seed=99, density=0.3)
@@ -400,7 +400,7 @@ def test_b200_sp24_tile_local_remainder(engine, N):
     148 CTAs, every CTA leaves or collects partials that carry a share of the remainder), and a matrix whose one dense
     corner would make every unit as large as the largest (falls back as well); reference-mode ones exact"""
     from generalsparse_b200 import synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
     rng = np.random.default_rng(5)
     corner = rng.random((2000, 2048)) < 0.05
     corner[:128, :128] = True
@@ -431,7 +431,7 @@ def test_b200_sp24_skips_empty_tiles(engine, monkeypatch, N):
     rest empty, some row panels entirely empty), a full band, and the same matrices with GS_SP24_SKIP_EMPTY=0;
     reference-mode ones exact"""
     from generalsparse_b200 import synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
     rng = np.random.default_rng(17)
     nrows, cols = 3000, 4096
     mask = rng.random((nrows, cols)) < 0.3
@@ -469,7 +469,7 @@ def test_b200_sp24_overlapped_launches_keep_order(engine, kind, kw, N):
     dense matrix alternates between launches (with a remainder: two product buffers alternate as well)"""
     import torch
     from generalsparse_b200 import api, synth
-    from generalsparse_b200.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
     rows, cols = 3000, 4096
     r, c = _matrix(kind, rows, cols, seed=91, **kw)
     vals = synth.synth_values(len(r), seed=61).astype(np.float16).astype(np.float32)
