@@ -21,7 +21,7 @@ SYMBOLS = [
     "gs_create", "gs_destroy", "gs_stream", "gs_upload_array", "gs_upload_session", "gs_upload_session_as", "gs_plan_create", "gs_plan_destroy",
     "gs_plan_set_kernel", "gs_set_dense", "gs_set_dense_device", "gs_launch", "gs_run", "gs_get_output", "gs_output_device",
     "gs_spmm_host", "gs_spmm_host_async", "gs_synchronize", "gs_plan_algorithmic_bytes", "gs_plan_launch_count", "gs_plan_kernel_name", "gs_plan_sp24_probe", "gs_execute",
-    "gs_launch_no_alloc",
+    "gs_launch_no_alloc", "gs_plan_format_bytes",
 ]
 
 (GS_U8, GS_U16, GS_U32, GS_U64, GS_F32, GS_F64, GS_F16) = range(7)
@@ -29,6 +29,7 @@ SYMBOLS = [
 FAMILIES = ["thread_total", "warp_total", "warp_bitmap", "thread_bit_map", "warp_segment", "block_total", "block_bitmap",
             "b200_row_smem", "b200_tcgen05", "b200_nnz", "b200_sp24"]
 FAMILY_ID = {n: i for i, n in enumerate(FAMILIES)}
+FAMILY_ID["auto"] = -1  # GS_KERNEL_AUTO
 STATUS = {0: "GS_OK", 1: "GS_ERR_INVALID", 2: "GS_ERR_CUDA", 3: "GS_ERR_UNSUPPORTED", 4: "GS_ERR_NOT_FOUND",
           5: "GS_ERR_PADDING_RATE", 6: "GS_ERR_INTERNAL"}
 
@@ -84,7 +85,7 @@ def lib():
         "gs_launch": (i32, [vp]), "gs_run": (i32, [vp, i32, P(C.c_float)]), "gs_get_output": (i32, [vp, vp]),
         "gs_output_device": (vp, [vp]), "gs_spmm_host": (i32, [vp, vp, vp]),
         "gs_spmm_host_async": (i32, [vp, vp, vp]), "gs_synchronize": (i32, [vp]),
-        "gs_plan_algorithmic_bytes": (u64, [vp]), "gs_plan_launch_count": (i32, [vp]), "gs_plan_kernel_name": (cp, [vp]),
+        "gs_plan_algorithmic_bytes": (u64, [vp]), "gs_plan_format_bytes": (u64, [vp]), "gs_plan_launch_count": (i32, [vp]), "gs_plan_kernel_name": (cp, [vp]),
         "gs_execute": (i32, [vp, i32, P(C.c_float), P(C.c_float)]),
         "gsh_sp24_roundtrip": (i32, [vp, vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),
         "gsh_sp24_tiled_roundtrip": (i32, [vp, vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),

@@ -264,6 +264,10 @@ class Plan:
         return lib().gs_plan_algorithmic_bytes(self._h)
 
     @property
+    def format_bytes(self):
+        return lib().gs_plan_format_bytes(self._h)
+
+    @property
     def launch_count(self):
         return lib().gs_plan_launch_count(self._h)
 

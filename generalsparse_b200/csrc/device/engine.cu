@@ -4,6 +4,8 @@
 #include "../capi_internal.hpp"
 #include "common.cuh"
 
+#include <algorithm>
+#include <cmath>
 #include <cstring>
 #include <map>
 #include <string>
@@ -80,6 +82,7 @@ struct gs_plan {
     void *C_dev = nullptr;
     void *B_pinned = nullptr, *C_pinned = nullptr; // staging for pageable host buffers is NOT used; these stay null
     uint64_t offset_bytes = 0; // bytes of the offset / bitmap arrays the launched kernel reads
+    uint64_t chain_offset_bytes = 0; // the same for the chain's own family (desc.family): SURVEY.md 8(d)'s offset term, independent of the kernel chosen
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t ev_b = nullptr, ev_k = nullptr, ev_c = nullptr; // async round trip: B landed, kernel done, C read back
     size_t esz() const { return half ? 2 : 4; }
@@ -343,6 +346,120 @@ static void select_kernel(gs_plan *p, int family)
     p->kernel = family;
 }
 
+// ---- GS_KERNEL_AUTO: which kernel for this chain, matrix, N and value type (smallest useful slice) ----------------
+// A cost model in microseconds per launch from the measured rates of this round's and round 1's profiles:
+// every candidate that accepts the chain is priced, the cheapest is prepared, and a candidate whose prepare refuses the matrix
+// (panel too large for shared memory, remainder blocks too large for a stage ...) falls to the next one.  The chain's own
+// reference-shaped family is always the last candidate, so the call cannot fail on a valid chain.
+struct auto_choice {
+    int family;
+    double us;
+};
+
+// 128 x 128 tiles of the row-level matrix that hold at least one entry (every row panel counts one at least): one pass over the
+// pattern on the host, at plan time
+static uint64_t count_nonempty_tiles(const gs_plan *p, const char *lvl)
+{
+    const gs_ctx *ctx = p->ctx;
+    const int id = p->desc.sub_matrix_id;
+    const dev_array *rp = find_arr(ctx, lvl, "first_nz_indices", id), *col = find_arr(ctx, "GLOBAL_META", "nz_col_indices", id);
+    if (!rp || !col || rp->len < 2) return 0;
+    std::vector<uint32_t> h_rp(rp->len);
+    CUDA_TRY(cudaMemcpy(h_rp.data(), rp->ptr, rp->len * 4, cudaMemcpyDeviceToHost));
+    std::vector<unsigned char> h_col(col->len * dsize(col->dtype));
+    CUDA_TRY(cudaMemcpy(h_col.data(), col->ptr, h_col.size(), cudaMemcpyDeviceToHost));
+    const uint64_t kt = (p->desc.cols + 127) / 128, n_rows = rp->len - 1, panels = (n_rows + 127) / 128;
+    std::vector<bool> seen(panels * kt, false);
+    const bool u16 = col->dtype == GS_U16;
+    for (uint64_t r = 0; r < n_rows; r++) {
+        const uint64_t base = (r >> 7) * kt;
+        for (uint64_t i = h_rp[r]; i < h_rp[r + 1] && i < col->len; i++) seen[base + ((u16 ? ((const uint16_t *)h_col.data())[i] : ((const uint32_t *)h_col.data())[i]) >> 7)] = true;
+    }
+    uint64_t n = 0;
+    for (uint64_t pnl = 0; pnl < panels; pnl++) {
+        uint64_t here = 0;
+        for (uint64_t k = 0; k < kt; k++) here += seen[pnl * kt + k];
+        n += here ? here : 1;
+    }
+    return n;
+}
+
+static std::vector<auto_choice> auto_candidates(const gs_plan *p)
+{
+    const gsd::dev_arrays &a = p->lp.a;
+    const gs_ctx *ctx = p->ctx;
+    const int N = p->N, id = p->desc.sub_matrix_id;
+    const double nnz = (double)a.nnz, rows = (double)p->desc.rows, cols = (double)p->desc.cols;
+    const double bw = 6470.2e3; // bytes per microsecond: MEASURED_PEAKS.json hbm_gbs of this pool's B200s
+    const double idxb = a.col_is_u16 ? 2 : 4, vb = p->esz();
+    const double bc = (cols + rows) * N * vb;
+    std::vector<auto_choice> c;
+    const char *lvl = row_level(a);
+    const dev_array *fr = lvl ? find_arr(ctx, lvl, "first_row_indices", id) : nullptr;
+    const bool row_chain = fr && fr->iota;
+    const bool bitmap_chain = a.t_first_row && a.t_first_nz && !a.t_nz_relative && a.t_bit_map && a.t_seg_ptr && a.t_seg_empty_flag && a.t_seg_empty_rows;
+    if (row_chain) {
+        const double mean_len = nnz / (rows > 0 ? rows : 1);
+        if (N == 8 || N == 16 || N == 32) {
+            // gather kernel: streams 4-8 B per non-zero at ~70 % of the HBM peak while the K x N panel fits shared memory, else its gathers
+            // go to L2 (~2.2x); from N = 16 the shared-memory gathers and the FMAs bound it (13.5 M nnz x N = 32: 23 us); short rows
+            // (one warp per row) waste lanes below ~64 entries
+            const bool panel = cols * N * vb <= 200.0 * 1024;
+            double t = (nnz * (idxb + vb) + bc) / (0.70 * bw) * (panel ? 1.0 : 2.2);
+            t = std::max(t, nnz * N / 18.8e6);
+            if (mean_len < 64) t *= 1.0 + (64 - mean_len) / 64.0;
+            c.push_back({GS_FAMILY_B200_ROW_SMEM, t + 2.5});
+        }
+        // the tensor-core layouts are built for weight-sized matrices: their host builders lay the whole rows x cols grid out before
+        // empty tiles are dropped, so a 65 536^2 pattern (4.8 GB of image for 172 MB of non-zeros) never gets there
+        const bool weight_sized = rows * cols * 1.125 <= 2147483648.0;
+        double nonempty128 = std::ceil(rows / 128) * std::ceil(cols / 128);
+        if (weight_sized && p->half) nonempty128 = (double)count_nonempty_tiles(p, lvl);
+        if (weight_sized && p->half && (N == 16 || N == 32 || N == 64 || N == 128 || N == 256)) {
+            // tile kernel: one 2-byte store per non-zero, but every 128 x 64 tile costs its zero fill + tensor-core read whatever it holds:
+            // ~3.0 ns per tile over the whole GPU up to N = 64, 3.9 at 128, 7.8 at 256 (profiles/r1_tile_summary.md)
+            const double tiles = std::ceil(rows / 128) * std::ceil(cols / 64);
+            const double per_tile = N <= 64 ? 3.0e-3 : N == 128 ? 3.9e-3 : 7.8e-3;
+            c.push_back({GS_FAMILY_B200_TCGEN05, std::max(tiles * per_tile, (nnz * 4 + bc) / (0.55 * bw)) + 4.0});
+        }
+        if (weight_sized && p->half && (N == 8 || N == 16 || N == 32 || N == 64 || N == 128 || N == 256)) {
+            // 2:4 kernel: 18 432 B per non-empty 128 x 128 tile whatever it holds (counted on the host from the pattern; every row panel keeps one), ~90 % of the HBM peak up to N = 32, then the L2 -> SM intake of B's
+            // slices bounds it (profiles/r1_sp24_summary.md); what 2:4 cannot hold (expected share from the density, exact for a
+            // 2:4-pruned matrix only after prepare) is multiplied by remainder warps at ~5 M entry-columns per us
+            const double d = nnz / (rows * cols);
+            const double tiles = std::ceil(rows / 128) * std::ceil(cols / 128);
+            const double p_empty = 1.0 - nonempty128 / tiles;
+            const double g = N <= 16 ? 1.0 : N == 32 ? 1.1 : N == 64 ? 1.35 : N == 128 ? 2.0 : 4.3;
+            // expected entries beyond two per group of four columns under independent keep-probability d
+            const double q = std::min(d, 1.0), over = 4 * q * q * q * (1 - q) * 1 + q * q * q * q * 2;
+            const double rem = d > 0.45 && d < 0.55 ? 0.0 : rows * cols / 4 * over; // a 2:4-pruned weight sits at exactly 0.5: no remainder
+            double t = tiles * (1 - p_empty) * 18432.0 / (0.90 * bw) * g + bc / bw + rem * N / 5.1e6;
+            if (N >= 128 && rem > 0) t += (rem * 6) / (0.5 * bw) + 6.0; // separate gather launch
+            c.push_back({GS_FAMILY_B200_SP24, t + 1.0});
+        }
+    }
+    if (bitmap_chain && (N == 32 || N == 64 || N == 128))
+        c.push_back({GS_FAMILY_B200_NNZ, (nnz * (idxb + vb) + bc) / (0.25 * bw) + 3.0}); // bound by the gathers of B rows through L2
+    std::sort(c.begin(), c.end(), [](const auto_choice &x, const auto_choice &y) { return x.us < y.us; });
+    c.push_back({p->desc.family, 1e30});
+    return c;
+}
+
+static void select_auto(gs_plan *p)
+{
+    std::string why;
+    for (const auto_choice &c : auto_candidates(p)) {
+        try {
+            select_kernel(p, c.family);
+            return;
+        } catch (const gs::Error &e) {
+            why += std::string(why.empty() ? "" : "; ") + gs_family_name(c.family) + ": " + e.what();
+            cudaGetLastError();
+        }
+    }
+    throw gs::Error("auto: no kernel accepts this chain (" + why + ")");
+}
+
 static bool uses_atomics(int family)
 {
     return family == GS_FAMILY_WARP_BITMAP || family == GS_FAMILY_TBLOCK_BITMAP || family == GS_FAMILY_THREAD_BITMAP || family == GS_FAMILY_WARP_SEGMENT ||
@@ -466,6 +583,14 @@ gs_status gs_plan_create(gs_ctx *ctx, const gs_plan_desc *desc, int N, int half,
         p->lp.coarsen = desc->coarsen, p->lp.vector_width = desc->vector_width, p->lp.block_size = (int)desc->block[1];
         p->lp.N = N;
         bind_arrays(p);
+        for (int i = 0; i < desc->n_deps && i < 16; i++) {
+            const std::string key(desc->deps[i], strnlen(desc->deps[i], sizeof desc->deps[i]));
+            if (key_has(key, "nz_col_indices") || key_has(key, "nz_vals")) continue;
+            // the key carries the session's sub-matrix id; the arrays may live under another one (gs_upload_session_as)
+            const size_t us = key.rfind('_');
+            auto it = ctx->arrays.find(us == std::string::npos ? key : key.substr(0, us + 1) + std::to_string(desc->sub_matrix_id));
+            if (it != ctx->arrays.end()) p->chain_offset_bytes += it->second.len * dsize(it->second.dtype);
+        }
         select_kernel(p, desc->family);
         size_t cbytes = (size_t)desc->rows * N * p->esz();
         CUDA_TRY(cudaMalloc(&p->C_dev, cbytes + 16));
@@ -504,7 +629,8 @@ gs_status gs_plan_set_kernel(gs_plan *p, int family)
     GS_REQUIRE(p, "null plan");
     CUDA_TRY(cudaSetDevice(p->ctx->device));
     p->ctx->row_chain = false; // prepare() puts copies and layout kernels on the stream
-    select_kernel(p, family);
+    if (family == GS_KERNEL_AUTO) select_auto(p);
+    else select_kernel(p, family);
     GS_API_END
 }
 
@@ -680,7 +806,16 @@ gs_status gs_synchronize(gs_ctx *ctx)
 uint64_t gs_plan_algorithmic_bytes(const gs_plan *p)
 {
     if (!p) return 0;
-    // nnz_stored*(idx+val) + offset arrays + K*N*sizeof(B) + M*N*sizeof(C) (+ permutation)
+    // SURVEY.md 8(d), the one number builder and judge both compute: nnz_stored*(idx+val) + the chain's offset arrays + K*N*sizeof(B) +
+    // M*N*sizeof(C) (+ the row permutation when sort_operator ran) -- the CHAIN's arrays, whatever layout the launched kernel streams
+    // (gs_plan_format_bytes reports that)
+    uint64_t idx = p->lp.a.col_is_u16 ? 2 : 4;
+    return p->lp.a.nnz * (idx + p->esz()) + p->chain_offset_bytes + (uint64_t)p->desc.cols * p->N * p->esz() + (uint64_t)p->desc.rows * p->N * p->esz();
+}
+
+uint64_t gs_plan_format_bytes(const gs_plan *p)
+{
+    if (!p) return 0;
     if (p->kernel == GS_FAMILY_B200_TCGEN05) return gsd::b200_tile_bytes(p->tile_plan, p->desc.rows, p->desc.cols);
     if (p->kernel == GS_FAMILY_B200_SP24) return gsd::b200_sp24_bytes(p->sp24_plan, p->desc.rows, p->desc.cols);
     uint64_t idx = p->lp.a.col_is_u16 ? 2 : 4;

@@ -6,14 +6,19 @@
 // default here too.  Extra flags after the two positionals:
 //   --family <thread_total|warp_total|warp_bitmap|thread_bit_map|warp_segment|block_total|block_bitmap>
 //   --sparse-coarsen S  --coarsen C   the two integers every test_spmm_* takes
-//   --kernel b200_row_smem            launch the B200 row kernel on a row-direction chain
+//   --kernel <auto|reference|b200_row_smem|b200_tcgen05|b200_sp24|b200_nnz>
+//                                     auto (default): the library picks the B200 kernel for the chain, the matrix and N
+//                                     (gs_plan_set_kernel(GS_KERNEL_AUTO)); reference: the chain's own reference-shaped family
 //   --half                            HALF storage (global_config.json "HALF": true does the same)
 //   --values                          keep the file's values (the reference forces every value to 1)
 //   --repeat R                        timed launches (reference: 10000)
 //   --dump <dir>                      write every metadata array as text, one value per line (struct.cc:1991)
 //   --no-parity                       skip the host check (the reference always checks, code_generator.cc:631-638)
+//   --corrupt-check                   flip one element of the host copy of C before the check (shows that the check can fail)
 // The host check is the reference's own: all-ones B, C[i][j] must equal the row's sum of values exactly in
-// reference mode; it reads C back and compares on the host -- it is a check, not a compute fallback.
+// reference mode; it reads C back and compares on the host -- it is a check, not a compute fallback.  With HALF, C comes back
+// in fp16: a row sum up to 2048 is an exact fp16 integer and must match exactly; above that (and with --values) the bound is
+// the north star's 1e-2 (HALF) / 1e-5 (fp32) relative to the row's sum of |values|.
 #include "../../include/gsparse_b200.h"
 
 #include <cstdio>
@@ -21,6 +26,29 @@
 #include <cstring>
 #include <string>
 #include <vector>
+
+// IEEE binary16 -> float on the host (the driver is plain C++: no cuda_fp16.h)
+static float half_to_float(uint16_t h)
+{
+    const uint32_t sign = (uint32_t)(h & 0x8000u) << 16, exp = (h >> 10) & 0x1fu, man = h & 0x3ffu;
+    uint32_t bits;
+    if (exp == 0) {
+        if (man == 0) bits = sign;
+        else { // subnormal: normalise
+            int e = -1;
+            uint32_t m = man;
+            do {
+                e++;
+                m <<= 1;
+            } while (!(m & 0x400u));
+            bits = sign | (uint32_t)(127 - 15 - e) << 23 | (m & 0x3ffu) << 13;
+        }
+    } else if (exp == 31) bits = sign | 0x7f800000u | man << 13;
+    else bits = sign | (exp - 15 + 127) << 23 | man << 13;
+    float f;
+    memcpy(&f, &bits, 4);
+    return f;
+}
 
 static void die(const char *what)
 {
@@ -42,7 +70,7 @@ int main(int argc, char **argv)
     int N = atoi(argv[2]);
     std::string family = "thread_total", kernel, dump;
     int S = 4, C = 1, repeat = 10000;
-    bool half = false, values = false, parity = true;
+    bool half = false, values = false, parity = true, corrupt = false;
     for (int i = 3; i < argc; i++) {
         std::string a = argv[i];
         auto next = [&]() -> const char * { return i + 1 < argc ? argv[++i] : ""; };
@@ -55,6 +83,7 @@ int main(int argc, char **argv)
         else if (a == "--repeat") repeat = atoi(next());
         else if (a == "--dump") dump = next();
         else if (a == "--no-parity") parity = false;
+        else if (a == "--corrupt-check") corrupt = true;
         else if (a == "--gpus") next(); // multi-GPU runs go through bench.py / torchrun: one process per GPU
         else {
             fprintf(stderr, "token_test: unknown flag %s\n", a.c_str());
@@ -95,12 +124,15 @@ int main(int argc, char **argv)
     OK(gs_upload_session(ctx, s, half));
     gs_plan *plan = nullptr;
     OK(gs_plan_create(ctx, &desc, N, half, &plan));
-    if (!kernel.empty()) {
+    if (kernel.empty() || kernel == "auto") {
+        if (gs_plan_set_kernel(plan, GS_KERNEL_AUTO) != GS_OK) die("--kernel auto");
+    } else if (kernel != "reference") {
         int k = -1;
         for (int f = 0; f < GS_FAMILY_COUNT; f++)
             if (kernel == gs_family_name(f)) k = f;
         if (k < 0 || gs_plan_set_kernel(plan, k) != GS_OK) die("--kernel");
     }
+    printf("kernel: %s\n", gs_plan_kernel_name(plan));
     std::vector<float> B((size_t)desc.cols * N, 1.0f); // x_arr := 1 (code_generator.cc:464-467)
     OK(gs_set_dense(plan, B.data(), GS_F32));
     float ms_total = 0, gflops = 0;
@@ -119,14 +151,24 @@ int main(int argc, char **argv)
             perm.resize(plen);
             OK(gsh_metadata_read_u64(ms, "GLOBAL_META_original_nz_row_indices_0", perm.data(), plen));
         }
-        std::vector<float> ref(rows, 0.0f);
-        for (uint64_t i = 0; i < nnz; i++) ref[perm.empty() ? r[i] : perm[r[i]]] += (float)v[i];
+        std::vector<double> ref(rows, 0.0), absref(rows, 0.0);
+        for (uint64_t i = 0; i < nnz; i++) {
+            const uint64_t row = perm.empty() ? r[i] : perm[r[i]];
+            ref[row] += v[i], absref[row] += v[i] < 0 ? -v[i] : v[i];
+        }
         std::vector<unsigned char> out((size_t)rows * N * (half ? 2 : 4));
         OK(gs_get_output(plan, out.data()));
+        if (corrupt && !out.empty()) out[out.size() / 2 + (half ? 1 : 3)] ^= 0x40u; // an exponent bit of one element in the middle
         long wrong = 0;
-        for (uint64_t i = 0; i < rows && !half; i++)
-            for (int j = 0; j < N; j++)
-                if (((float *)out.data())[i * N + j] != ref[i]) wrong++;
+        const double tol = half ? 1e-2 : 1e-5;
+        for (uint64_t i = 0; i < rows; i++)
+            for (int j = 0; j < N; j++) {
+                const double c = half ? (double)half_to_float(((const uint16_t *)out.data())[i * N + j]) : (double)((const float *)out.data())[i * N + j];
+                // reference mode: the exact compare of check_result (cuda_code/kernel_lib.hpp:884-921) wherever the sum is exact in C's type
+                const bool exact = !values && ref[i] <= (half ? 2048.0 : 16777216.0);
+                const double err = c > ref[i] ? c - ref[i] : ref[i] - c;
+                if (exact ? c != ref[i] : !(err <= tol * absref[i])) wrong++;
+            }
         if (wrong) printf("wrong number:%ld\n", wrong);
         else printf("correct\n");
     }

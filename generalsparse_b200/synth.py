@@ -140,3 +140,62 @@ def synth_values(nnz, seed=0, scale=0.02, dtype=np.float32):
 def synth_dense(k, n, seed=0, dtype=np.float32):
     rng = np.random.default_rng(0xB0B + seed)
     return rng.uniform(-1.0, 1.0, size=(k, n)).astype(dtype)
+
+
+def exact_lengths_matrix(rng, lengths, cols):
+    """Distinct uniform column ids, EXACTLY lengths[i] of them in row i (row-major sorted): candidates are over-drawn,
+    de-duplicated keeping the first draw, and every row keeps its first lengths[i] distinct ones."""
+    lengths = np.minimum(lengths, cols).astype(np.int64)
+    draw = lengths + lengths // 8 + 4
+    r = _rows_from_lengths(draw)
+    c = rng.integers(0, cols, size=int(draw.sum()), dtype=np.int64)
+    key = r * cols + c
+    _, first = np.unique(key, return_index=True)
+    first.sort()  # distinct (row, col) pairs in draw order; rows stay grouped because r is non-decreasing
+    r, c = r[first], c[first]
+    start = np.zeros(len(lengths) + 1, dtype=np.int64)
+    np.cumsum(np.bincount(r, minlength=len(lengths)), out=start[1:])
+    rank = np.arange(len(r), dtype=np.int64) - start[r]
+    keep = rank < lengths[r]
+    r, c = r[keep], c[keep]
+    assert np.array_equal(np.bincount(r, minlength=len(lengths)), lengths), "over-draw too small for a row"
+    order = np.argsort(r * cols + c, kind="stable")
+    return r[order], c[order]
+
+
+C1_SHAPE = (47894, 41550, 1790490)  # SuiteSparse Meszaros/IG5-18: rows, cols, nnz (SURVEY.md section 0 fact 5)
+
+
+def c1_standin(seed=1):
+    """Stand-in for BASELINE.json configs[0] (matrix_example/suite_collection/IG5-18.mtx is a missing blob): the shape and
+    EXACT non-zero count of IG5-18, LP-constraint-like row lengths (lognormal, mean 37.4, sigma 0.9), uniform columns
+    (SURVEY.md section 8d).  Returns (rows, cols, row, col)."""
+    rows, cols, nnz = C1_SHAPE
+    rng = np.random.default_rng(0x6753 + seed)
+    sigma = 0.9
+    mu = np.log(nnz / rows) - sigma * sigma / 2
+    lengths = np.maximum(1, rng.lognormal(mu, sigma, size=rows)).astype(np.int64)
+    # land on the exact count: +-1 on randomly chosen rows (never below 1)
+    diff = nnz - int(lengths.sum())
+    while diff != 0:
+        pick = rng.choice(rows, size=min(abs(diff), rows), replace=False)
+        if diff < 0:
+            pick = pick[lengths[pick] > 1]
+        lengths[pick] += 1 if diff > 0 else -1
+        diff = nnz - int(lengths.sum())
+    r, c = exact_lengths_matrix(rng, lengths, cols)
+    return rows, cols, r, c
+
+
+def write_mtx(path, rows, cols, r, c, vals=None, comments=("%%MatrixMarket matrix coordinate real general",)):
+    """1-based, row-major-sorted coordinate text, `%` comment lines first, then `rows cols nnz` -- the only input the
+    reference loader accepts (struct.cc:97-125)."""
+    with open(path, "w") as f:
+        for line in comments:
+            f.write(line + "\n")
+        f.write("%d %d %d\n" % (rows, cols, len(r)))
+        if vals is None:
+            np.savetxt(f, np.stack([r + 1, c + 1, np.ones(len(r), dtype=np.int64)], axis=1), fmt="%d %d %d")
+        else:
+            rc = np.char.add(np.char.add((r + 1).astype(str), " "), (c + 1).astype(str))
+            f.write("\n".join(np.char.add(np.char.add(rc, " "), np.char.mod("%.9g", vals)).tolist()) + "\n")

@@ -54,6 +54,10 @@ typedef enum gs_family {
     GS_FAMILY_B200_SP24 = 10,    /* 2:4 sparse tensor cores: tcgen05.mma.sp over a pre-laid-out image, what the pattern cannot hold goes to a gather pass */
     GS_FAMILY_COUNT = 11
 } gs_family;
+/* gs_plan_set_kernel(plan, GS_KERNEL_AUTO): the library picks the kernel for (chain, matrix, N, value type) from a cost model of the
+ * measured rates -- the slice of the reference's unbuilt calculation_method_choose_operator (README.md:36, "under development") this
+ * path needs; the chain's own family is the last resort */
+#define GS_KERNEL_AUTO (-1)
 
 const char *gs_last_error(void);
 const char *gs_version(void);
@@ -223,8 +227,12 @@ gs_status gs_spmm_host(gs_plan *p, const void *B_host, void *C_host);
  * pinned and stay valid until gs_synchronize() returns; C_host is complete only then. */
 gs_status gs_spmm_host_async(gs_plan *p, const void *B_host, void *C_host);
 gs_status gs_synchronize(gs_ctx *ctx); /* drains gs_stream(), the other launch streams and both copy streams */
-/* bytes one launch must move (SURVEY.md section 8d formula, with the device's actual dtypes) */
+/* bytes one launch must move by SURVEY.md section 8d: stored nnz * (index + value) + the chain's registered offset / bitmap arrays
+ * (+ row permutation) + K*N + M*N values, with the device's dtypes -- the same number whatever kernel the plan launches */
 uint64_t gs_plan_algorithmic_bytes(const gs_plan *p);
+/* bytes the launched kernel's own layout streams per launch (2:4 image, tile stream, or the chain's arrays): format waste is
+ * gs_plan_format_bytes / gs_plan_algorithmic_bytes */
+uint64_t gs_plan_format_bytes(const gs_plan *p);
 int gs_plan_launch_count(const gs_plan *p); /* kernels per gs_launch (memset excluded) */
 const char *gs_plan_kernel_name(const gs_plan *p);
 /* GS_FAMILY_B200_SP24 with GS_SP24_PROBE=1 in the environment at plan creation: the 4 metadata columns of the first

@@ -95,9 +95,14 @@ def test_random_values_tolerance(engine, family, half):
     indptr = csr_from_coo(rows, r)
     ref = oracle_spmm_f64acc(rows, N, indptr, c, vals, B)
     absrow = oracle_spmm_absrow(rows, N, indptr, c, vals, B)
-    if half:
-        # C is stored in fp16: one final rounding (2^-11 relative) on top of the fp32 accumulation;
-        # the atomic families add fp16 partials, hence the row-L1 floor scales with the tolerance too
+    if half and family in ("thread_total", "warp_total", "block_total"):
+        # fp32 accumulation, one final rounding to fp16 (2^-11 relative): SURVEY.md 8(d)'s gate, floor 1e-6 * |row|_1 + half the
+        # spacing of fp16 subnormals
+        _check(C, ref, absrow * 1e-4, 1e-2, abs_floor=2.0 ** -25)
+    elif half:
+        # the bit-map / segment families add their partial sums into an fp16 C with atomicAdd(half), as the reference's HALF tokens
+        # do (total_BMT...token.cc:510-513): every partial is rounded to fp16 on the way, so the error scales with the row's
+        # L1 norm, not with |C| -- the loose floor stays for these four families only
         _check(C, ref, absrow, 1e-2)
     else:
         _check(C, ref, absrow * 1e-1, 1e-5)
@@ -129,7 +134,7 @@ def test_b200_row_kernel(engine, N, half, chain):
         C, plan = _run(engine, chain, nrows, cols, rr, cc, vals, B, N, S, 1, half=half, kernel="b200_row_smem")
         ref = oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B)
         absrow = oracle_spmm_absrow(nrows, N, indptr, cc, vals, B)
-        _check(C, ref, absrow * (1e-2 if half else 1e-1), 1e-2 if half else 1e-5)
+        _check(C, ref, absrow * (1e-4 if half else 1e-1), 1e-2 if half else 1e-5, abs_floor=2.0 ** -25 if half else 0.0)
 
 
 def test_host_roundtrip_and_execute(engine):
@@ -240,7 +245,7 @@ def test_b200_tile_kernel(engine, N, chain):
         C, plan = _run(engine, chain, nrows, cols, rr, cc, vals, B, N, S, 1, half=True, kernel="b200_tcgen05")
         ref = oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B)
         absrow = oracle_spmm_absrow(nrows, N, indptr, cc, vals, B)
-        _check(C, ref, absrow * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        _check(C, ref, absrow * 1e-4, 1e-2, abs_floor=2.0 ** -25)
         # repeated launches (programmatic dependent launch, workspace and flag reuse) give the same bits
         plan.run(5)
         assert np.array_equal(plan.output(), C)
@@ -271,7 +276,7 @@ def test_b200_tile_overlapped_launches_keep_order(engine):
             plan.launch()
         last = (n_launch - 1) % 2
         C = plan.output()
-        _check(C, refs[last], absrow[last] * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        _check(C, refs[last], absrow[last] * 1e-4, 1e-2, abs_floor=2.0 ** -25)
 
 
 @pytest.mark.parametrize("N", [32, 64, 128])
@@ -303,6 +308,8 @@ def test_b200_nnz_kernel(engine, N, half, chain):
         ref = oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B)
         absrow = oracle_spmm_absrow(nrows, N, indptr, cc, vals, B)
         floor = 2.0 ** -25 if half else 0.0  # half the spacing of fp16 subnormals when C is stored in fp16
+        # HALF: rows that cross a run edge are completed with red.global.add on the fp16 C (each partial rounded to fp16), hence the
+        # row-L1 floor at the tolerance itself; fp32 keeps SURVEY.md 8(d)'s 1e-6 * |row|_1
         _check(C, ref, absrow * (1.0 if half else 1e-1), 1e-2 if half else 1e-5, abs_floor=floor)
         plan.run(3)  # C is zeroed per launch: repeated launches do not accumulate
         _check(plan.output(), ref, absrow * (1.0 if half else 1e-1), 1e-2 if half else 1e-5, abs_floor=floor)
@@ -345,7 +352,7 @@ def test_b200_sp24_kernel(engine, N, chain):
         C, plan = _run(engine, chain, nrows, cols, rr, cc, vals, B, N, S, 1, half=True, kernel="b200_sp24")
         ref = oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B)
         absrow = oracle_spmm_absrow(nrows, N, indptr, cc, vals, B)
-        _check(C, ref, absrow * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        _check(C, ref, absrow * 1e-4, 1e-2, abs_floor=2.0 ** -25)
         # repeated launches (programmatic dependent launch, workspace, flag and remainder-buffer reuse) give the same bits
         plan.run(5)
         assert np.array_equal(plan.output(), C)
@@ -368,7 +375,7 @@ def test_b200_sp24_panels_per_cta(engine, monkeypatch, N, panels):
         assert ("%d panel" % panels) in plan.kernel_name, plan.kernel_name
         ref = oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B)
         absrow = oracle_spmm_absrow(nrows, N, indptr, cc, vals, B)
-        _check(C, ref, absrow * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        _check(C, ref, absrow * 1e-4, 1e-2, abs_floor=2.0 ** -25)
         plan.run(7)
         assert np.array_equal(plan.output(), C)
 
@@ -388,7 +395,7 @@ def test_b200_sp24_remainder_as_separate_pass(engine, monkeypatch, N, mode):
     assert plan.launch_count == (1 if mode == 1 and N <= 16 else 2) and "tile-local" not in plan.kernel_name, plan.kernel_name
     assert ("owner CTA" in plan.kernel_name) == (mode == 1 and N <= 16), plan.kernel_name
     indptr = csr_from_coo(nrows, rr)
-    _check(C, oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B), oracle_spmm_absrow(nrows, N, indptr, cc, vals, B) * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+    _check(C, oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B), oracle_spmm_absrow(nrows, N, indptr, cc, vals, B) * 1e-4, 1e-2, abs_floor=2.0 ** -25)
     plan.run(6)
     assert np.array_equal(plan.output(), C)
 
@@ -420,7 +427,7 @@ def test_b200_sp24_tile_local_remainder(engine, N):
         vals = synth.synth_values(len(rr), seed=8).astype(np.float16).astype(np.float32)
         B = synth.synth_dense(cols, N, seed=8).astype(np.float16).astype(np.float32)
         C, plan = _run(engine, "thread_total", nrows, cols, rr, cc, vals, B, N, 8, 1, half=True, kernel="b200_sp24")
-        _check(C, oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B), oracle_spmm_absrow(nrows, N, indptr, cc, vals, B) * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        _check(C, oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B), oracle_spmm_absrow(nrows, N, indptr, cc, vals, B) * 1e-4, 1e-2, abs_floor=2.0 ** -25)
         plan.run(9)
         assert np.array_equal(plan.output(), C)
 
@@ -453,14 +460,14 @@ def test_b200_sp24_skips_empty_tiles(engine, monkeypatch, N):
         assert " tiles" in plan.kernel_name, plan.kernel_name
         assert np.array_equal(C1.astype(np.float32), oracle_spmm_f32(nr, N, indptr, cc, np.ones(len(rr), np.float32), B1)), plan.kernel_name
         C, plan = _run(engine, "thread_total", nr, nc, rr, cc, vals, B, N, 8, 1, half=True, kernel="b200_sp24")
-        _check(C, oracle_spmm_f64acc(nr, N, indptr, cc, vals, B), oracle_spmm_absrow(nr, N, indptr, cc, vals, B) * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        _check(C, oracle_spmm_f64acc(nr, N, indptr, cc, vals, B), oracle_spmm_absrow(nr, N, indptr, cc, vals, B) * 1e-4, 1e-2, abs_floor=2.0 ** -25)
         plan.run(9)
         assert np.array_equal(plan.output(), C)
         monkeypatch.setenv("GS_SP24_SKIP_EMPTY", "0")
         Cfull, plan = _run(engine, "thread_total", nr, nc, rr, cc, vals, B, N, 8, 1, half=True, kernel="b200_sp24")
         monkeypatch.delenv("GS_SP24_SKIP_EMPTY")
         assert " tiles" not in plan.kernel_name, plan.kernel_name  # another split of the panels over the CTAs: other fp32 summation order
-        _check(Cfull, oracle_spmm_f64acc(nr, N, indptr, cc, vals, B), oracle_spmm_absrow(nr, N, indptr, cc, vals, B) * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        _check(Cfull, oracle_spmm_f64acc(nr, N, indptr, cc, vals, B), oracle_spmm_absrow(nr, N, indptr, cc, vals, B) * 1e-4, 1e-2, abs_floor=2.0 ** -25)
 
 
 @pytest.mark.parametrize("kind,kw,N", [("nm24", {}, 32), ("uniform", dict(density=0.3), 32), ("uniform", dict(density=0.3), 16)])
@@ -489,7 +496,7 @@ def test_b200_sp24_overlapped_launches_keep_order(engine, kind, kw, N):
             plan.launch()
         last = (n_launch - 1) % 2
         C = plan.output()
-        _check(C, refs[last], absrow[last] * 1e-2, 1e-2, abs_floor=2.0 ** -25)
+        _check(C, refs[last], absrow[last] * 1e-4, 1e-2, abs_floor=2.0 ** -25)
 
 
 def test_b200_sp24_metadata_lands_in_tensor_memory_as_laid_out(engine, monkeypatch):
