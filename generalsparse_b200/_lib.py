@@ -21,7 +21,10 @@ SYMBOLS = [
     "gs_create", "gs_destroy", "gs_stream", "gs_upload_array", "gs_upload_session", "gs_upload_session_as", "gs_plan_create", "gs_plan_destroy",
     "gs_plan_set_kernel", "gs_set_dense", "gs_set_dense_device", "gs_launch", "gs_run", "gs_get_output", "gs_output_device",
     "gs_spmm_host", "gs_spmm_host_async", "gs_synchronize", "gs_plan_algorithmic_bytes", "gs_plan_launch_count", "gs_plan_kernel_name", "gs_plan_sp24_probe", "gs_execute",
-    "gs_launch_no_alloc", "gs_plan_format_bytes",
+    "gs_launch_no_alloc", "gs_plan_format_bytes", "gsh_metadata_row_block", "gsh_metadata_row_nnz", "gs_plan_set_output_device",
+    "gs_comm_unique_id", "gs_comm_init", "gs_comm_allgather_rows", "gs_comm_destroy",
+    "gs_exec_create", "gs_exec_destroy", "gs_exec_devices", "gs_exec_build", "gs_exec_row_cuts", "gs_exec_kernel_name", "gs_exec_set_dense", "gs_exec_run",
+    "gs_exec_get_output", "gs_exec_enable_allgather", "gs_exec_allgather_output", "gs_exec_get_replica",
 ]
 
 (GS_U8, GS_U16, GS_U32, GS_U64, GS_F32, GS_F64, GS_F16) = range(7)
@@ -30,6 +33,7 @@ FAMILIES = ["thread_total", "warp_total", "warp_bitmap", "thread_bit_map", "warp
             "b200_row_smem", "b200_tcgen05", "b200_nnz", "b200_sp24"]
 FAMILY_ID = {n: i for i, n in enumerate(FAMILIES)}
 FAMILY_ID["auto"] = -1  # GS_KERNEL_AUTO
+FAMILY_ID["chain"] = -2  # GS_KERNEL_CHAIN
 STATUS = {0: "GS_OK", 1: "GS_ERR_INVALID", 2: "GS_ERR_CUDA", 3: "GS_ERR_UNSUPPORTED", 4: "GS_ERR_NOT_FOUND",
           5: "GS_ERR_PADDING_RATE", 6: "GS_ERR_INTERNAL"}
 
@@ -91,6 +95,14 @@ def lib():
         "gsh_sp24_tiled_roundtrip": (i32, [vp, vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),
         "gs_plan_sp24_probe": (i32, [vp, vp]),
         "gs_launch_no_alloc": (i32, [vp, vp, vp, vp]),
+        "gsh_metadata_row_block": (i32, [vp, u64, u64, P(vp)]), "gsh_metadata_row_nnz": (i32, [vp, vp, u64]),
+        "gs_plan_set_output_device": (i32, [vp, vp]),
+        "gs_comm_unique_id": (i32, [vp]), "gs_comm_init": (i32, [vp, i32, i32, vp]), "gs_comm_allgather_rows": (i32, [vp, vp, vp, u64]),
+        "gs_comm_destroy": (None, [vp]),
+        "gs_exec_create": (i32, [P(vp), vp, i32]), "gs_exec_destroy": (None, [vp]), "gs_exec_devices": (i32, [vp]),
+        "gs_exec_build": (i32, [vp, vp, i32, i32, i32, i32, i32, i32]), "gs_exec_row_cuts": (i32, [vp, vp, vp]), "gs_exec_kernel_name": (cp, [vp, i32]),
+        "gs_exec_set_dense": (i32, [vp, vp, i32]), "gs_exec_run": (i32, [vp, i32, P(C.c_float), vp]), "gs_exec_get_output": (i32, [vp, vp]),
+        "gs_exec_enable_allgather": (i32, [vp]), "gs_exec_allgather_output": (i32, [vp, P(C.c_float)]), "gs_exec_get_replica": (i32, [vp, i32, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

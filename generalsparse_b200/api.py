@@ -96,6 +96,18 @@ class MetaDataSet:
         v = np.ascontiguousarray(vals, dtype=np.float32)
         check(lib().gsh_metadata_set_vals(self._h, sub_matrix_id, _ptr(v), len(v)))
 
+    def row_block(self, lo, hi):
+        """rows [lo, hi) of the matrix as loaded, rebased to 0: one GPU's block of the row partition"""
+        h = C.c_void_p()
+        check(lib().gsh_metadata_row_block(self._h, lo, hi, C.byref(h)))
+        return MetaDataSet(h)
+
+    def row_nnz(self):
+        rows = int(self["GLOBAL_META_origin_row_num_-1"][0])
+        out = np.empty(rows, dtype=np.uint64)
+        check(lib().gsh_metadata_row_nnz(self._h, _ptr(out), rows))
+        return out
+
     def dump(self, directory):
         check(lib().gsh_metadata_dump(self._h, directory.encode()))
 
@@ -178,6 +190,20 @@ class Engine:
     def synchronize(self):
         check(lib().gs_synchronize(self._h))
 
+    # ---- optional all-gather of C over NCCL, one process per GPU ----
+    @staticmethod
+    def comm_unique_id():
+        buf = C.create_string_buffer(128)
+        check(lib().gs_comm_unique_id(buf))
+        return buf.raw
+
+    def comm_init(self, nranks, rank, unique_id):
+        check(lib().gs_comm_init(self._h, nranks, rank, C.c_char_p(unique_id)))
+
+    def comm_allgather_rows(self, c_full_ptr, row_cuts, row_bytes):
+        cuts = np.ascontiguousarray(row_cuts, dtype=np.uint64)
+        check(lib().gs_comm_allgather_rows(self._h, C.c_void_p(c_full_ptr), _ptr(cuts), row_bytes))
+
     def upload_array(self, key, arr, half=False):
         a = np.ascontiguousarray(arr)
         check(lib().gs_upload_array(self._h, key.encode(), _ptr(a), a.size, _NP2GS[a.dtype], int(half)))
@@ -232,6 +258,9 @@ class Plan:
         check(lib().gs_get_output(self._h, _ptr(out)))
         return out
 
+    def set_output_device(self, ptr):
+        check(lib().gs_plan_set_output_device(self._h, C.c_void_p(ptr)))
+
     def launch_no_alloc(self, b_ptr, c_ptr, stream_ptr=None):
         """gs_launch_no_alloc: caller's device B, C and stream; scratch in the library's static device array"""
         check(lib().gs_launch_no_alloc(self._h, C.c_void_p(b_ptr), C.c_void_p(c_ptr), C.c_void_p(stream_ptr)))
@@ -282,5 +311,65 @@ class Plan:
         return lib().gs_plan_kernel_name(self._h).decode()
 
 
-__all__ = ["MetaDataSet", "Session", "Engine", "Plan", "GsError", "FAMILIES", "FAMILY_ID", "config_set", "config_get",
+class Executor:
+    """gs_exec: one SpMM over several GPUs from one process (north star (3)): nnz-balanced row blocks, B replicated, C rows disjoint"""
+
+    def __init__(self, device_ids):
+        ids = np.ascontiguousarray(device_ids, dtype=np.int32)
+        h = C.c_void_p()
+        check(lib().gs_exec_create(C.byref(h), _ptr(ids), len(ids)))
+        self._h, self.n = h, len(ids)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().gs_exec_destroy(self._h)
+            self._h = None
+
+    def build(self, ms, family, N, sparse_coarsen=1, coarsen=1, half=False, kernel="auto"):
+        fid = FAMILY_ID[family] if isinstance(family, str) else family
+        kid = FAMILY_ID[kernel] if isinstance(kernel, str) else kernel
+        check(lib().gs_exec_build(self._h, ms._h, fid, N, sparse_coarsen, coarsen, int(half), kid))
+        self.N, self.half = N, half
+        self.rows = int(ms["GLOBAL_META_origin_row_num_-1"][0])
+        self.cols = int(ms["GLOBAL_META_origin_col_num_-1"][0])
+        return self
+
+    def row_cuts(self):
+        cuts, nnz = np.empty(self.n + 1, dtype=np.uint64), np.empty(self.n, dtype=np.uint64)
+        check(lib().gs_exec_row_cuts(self._h, _ptr(cuts), _ptr(nnz)))
+        return cuts, nnz
+
+    def kernel_name(self, g=0):
+        return lib().gs_exec_kernel_name(self._h, g).decode()
+
+    def set_dense(self, B):
+        B = np.ascontiguousarray(B)
+        assert B.shape == (self.cols, self.N)
+        check(lib().gs_exec_set_dense(self._h, _ptr(B), _NP2GS[B.dtype]))
+
+    def run(self, repeat=1):
+        mx, per = C.c_float(), np.zeros(self.n, dtype=np.float32)
+        check(lib().gs_exec_run(self._h, repeat, C.byref(mx), _ptr(per)))
+        return mx.value, per
+
+    def output(self):
+        out = np.empty((self.rows, self.N), dtype=np.float16 if self.half else np.float32)
+        check(lib().gs_exec_get_output(self._h, _ptr(out)))
+        return out
+
+    def enable_allgather(self):
+        check(lib().gs_exec_enable_allgather(self._h))
+
+    def allgather_output(self):
+        ms = C.c_float()
+        check(lib().gs_exec_allgather_output(self._h, C.byref(ms)))
+        return ms.value
+
+    def replica(self, g):
+        out = np.empty((self.rows, self.N), dtype=np.float16 if self.half else np.float32)
+        check(lib().gs_exec_get_replica(self._h, g, _ptr(out)))
+        return out
+
+
+__all__ = ["Executor", "MetaDataSet", "Session", "Engine", "Plan", "GsError", "FAMILIES", "FAMILY_ID", "config_set", "config_get",
            "partition_rows_balanced"]

@@ -108,6 +108,49 @@ gs_status gsh_metadata_from_coo(uint64_t rows, uint64_t cols, uint64_t nnz, cons
     GS_API_END
 }
 
+gs_status gsh_metadata_row_block(const gsh_metadata *ms, uint64_t lo, uint64_t hi, gsh_metadata **out)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ms && out && lo < hi, "bad argument");
+    const meta_data_set &src = *ms->ms;
+    GS_REQUIRE(src.is_exist(GLOBAL_META, "nz_row_indices", 0) && !src.is_exist(GLOBAL_META, "original_nz_row_indices", 0) &&
+                   src.count_of_metadata_of_diff_pos(TBLOCK_META, 0) + src.count_of_metadata_of_diff_pos(WARP_META, 0) + src.count_of_metadata_of_diff_pos(THREAD_META, 0) == 0,
+               "row blocks are cut from the matrix as loaded, before any operator ran");
+    const std::vector<uint64_t> &r = src.get(GLOBAL_META, "nz_row_indices", 0).u, &c = src.get(GLOBAL_META, "nz_col_indices", 0).u;
+    const universal_array &v = src.get(GLOBAL_META, "nz_vals", 0);
+    const uint64_t rows = src.scalar(GLOBAL_META, "origin_row_num", -1), cols = src.scalar(GLOBAL_META, "origin_col_num", -1);
+    GS_REQUIRE(hi <= rows, "row block past the end of the matrix");
+    // rows are sorted (struct.cc:125): the block is one contiguous run of the COO streams
+    const uint64_t b = (uint64_t)(std::lower_bound(r.begin(), r.end(), lo) - r.begin()), e = (uint64_t)(std::lower_bound(r.begin(), r.end(), hi) - r.begin());
+    std::vector<int64_t> br(e - b), bc(e - b);
+    std::vector<float> bv(e - b);
+    for (uint64_t i = b; i < e; i++) br[i - b] = (int64_t)(r[i] - lo), bc[i - b] = (int64_t)c[i], bv[i - b] = (float)v.f[i];
+    auto h = new gsh_metadata;
+    try {
+        h->ms = create_init_metadata_set_from_coo(hi - lo, cols, e - b, br.data(), bc.data(), bv.data(), get_config().as_string("PRECISE_OF_FLOAT"));
+    } catch (...) {
+        delete h;
+        throw;
+    }
+    *out = h;
+    GS_API_END
+}
+
+gs_status gsh_metadata_row_nnz(const gsh_metadata *ms, uint64_t *out, uint64_t rows)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ms && out, "null argument");
+    const meta_data_set &src = *ms->ms;
+    GS_REQUIRE(rows == src.scalar(GLOBAL_META, "origin_row_num", -1), "rows must be origin_row_num");
+    GS_REQUIRE(!src.is_exist(GLOBAL_META, "original_nz_row_indices", 0), "row lengths are taken from the matrix as loaded");
+    std::fill(out, out + rows, (uint64_t)0);
+    for (uint64_t x : src.get(GLOBAL_META, "nz_row_indices", 0).u) {
+        GS_REQUIRE(x < rows, "row index out of range");
+        out[x]++;
+    }
+    GS_API_END
+}
+
 void gsh_metadata_free(gsh_metadata *ms) { delete ms; }
 
 uint64_t gsh_metadata_count(const gsh_metadata *ms) { return ms ? ms->ms->keys().size() : 0; }

@@ -3,6 +3,7 @@
 // fork nvcc, fork a.out, read perf_result) with in-process launches on one CUDA stream.
 #include "../capi_internal.hpp"
 #include "common.cuh"
+#include "nccl_dl.hpp"
 
 #include <algorithm>
 #include <cmath>
@@ -65,6 +66,8 @@ struct gs_ctx {
         return stream;
     }
     std::map<std::string, dev_array> arrays;
+    gsd::nccl::comm_t comm = nullptr; // gs_comm_init: this rank's communicator for the optional all-gather of C
+    int comm_rank = -1, comm_size = 0;
 };
 
 struct gs_plan {
@@ -80,6 +83,8 @@ struct gs_plan {
     void *B_dev = nullptr;  // owned
     const void *B_use = nullptr;
     void *C_dev = nullptr;
+    void *C_ext = nullptr;  // gs_plan_set_output_device: the caller's buffer (not owned); launches write here instead of C_dev
+    void *C_out() const { return C_ext ? C_ext : C_dev; }
     void *B_pinned = nullptr, *C_pinned = nullptr; // staging for pageable host buffers is NOT used; these stay null
     uint64_t offset_bytes = 0; // bytes of the offset / bitmap arrays the launched kernel reads
     uint64_t chain_offset_bytes = 0; // the same for the chain's own family (desc.family): SURVEY.md 8(d)'s offset term, independent of the kernel chosen
@@ -472,7 +477,7 @@ static void enqueue(gs_plan *p, int which = 0)
     GS_REQUIRE(p->B_use != nullptr, "gs_set_dense has not been called");
     gs_ctx *ctx = p->ctx;
     gsd::launch_params lp = p->lp;
-    lp.B = p->B_use, lp.C = p->C_dev, lp.N = p->N;
+    lp.B = p->B_use, lp.C = p->C_out(), lp.N = p->N;
     if (which == 0) ctx->join_async();
     else ctx->dirty_extra[which] = true;
     cudaStream_t st = which ? ctx->launch_extra[which] : ctx->stream;
@@ -480,7 +485,7 @@ static void enqueue(gs_plan *p, int which = 0)
     static const bool no_pdl = getenv("GS_NO_PDL") != nullptr;
     const bool b200_chain = p->kernel == GS_FAMILY_B200_ROW_SMEM || p->kernel == GS_FAMILY_B200_TCGEN05 || p->kernel == GS_FAMILY_B200_SP24;
     if (!b200_chain) chain = false;
-    if (uses_atomics(p->kernel)) CUDA_TRY(cudaMemsetAsync(p->C_dev, 0, (size_t)p->desc.rows * p->N * p->esz(), st));
+    if (uses_atomics(p->kernel)) CUDA_TRY(cudaMemsetAsync(p->C_out(), 0, (size_t)p->desc.rows * p->N * p->esz(), st));
     lp.pdl = chain && !no_pdl;
     if (p->kernel == GS_FAMILY_B200_ROW_SMEM) CUDA_TRY(gsd::b200_row_launch(p->row_plan, lp, st));
     else if (p->kernel == GS_FAMILY_B200_TCGEN05) CUDA_TRY(gsd::b200_tile_launch(p->tile_plan, lp, st));
@@ -518,6 +523,7 @@ gs_status gs_create(gs_ctx **out, int device_id)
 void gs_destroy(gs_ctx *ctx)
 {
     if (!ctx) return;
+    gs_comm_destroy(ctx);
     cudaSetDevice(ctx->device);
     for (auto &kv : ctx->arrays) cudaFree(kv.second.ptr);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -700,12 +706,81 @@ gs_status gs_get_output(gs_plan *p, void *C_host)
     GS_API_BEGIN
     GS_REQUIRE(p && C_host, "null argument");
     CUDA_TRY(cudaSetDevice(p->ctx->device));
-    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, (size_t)p->desc.rows * p->N * p->esz(), cudaMemcpyDeviceToHost, p->ctx->mem_stream()));
+    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_out(), (size_t)p->desc.rows * p->N * p->esz(), cudaMemcpyDeviceToHost, p->ctx->mem_stream()));
     CUDA_TRY(cudaStreamSynchronize(p->ctx->stream));
     GS_API_END
 }
 
-void *gs_output_device(gs_plan *p) { return p ? p->C_dev : nullptr; }
+void *gs_output_device(gs_plan *p) { return p ? p->C_out() : nullptr; }
+
+gs_status gs_plan_set_output_device(gs_plan *p, void *C_dev)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(p, "null plan");
+    GS_REQUIRE(((uintptr_t)C_dev & 15) == 0, "device C must be 16-byte aligned");
+    p->C_ext = C_dev; // NULL: back to the plan's own buffer
+    p->ctx->row_chain = false;
+    GS_API_END
+}
+
+// ------------------------------------------------------------------------------------------- optional all-gather of C over NCCL
+#define NCCL_TRY(expr)                                                                                                              \
+    do {                                                                                                                            \
+        int r__ = (expr);                                                                                                           \
+        if (r__ != gsd::nccl::SUCCESS) throw gs::Error(std::string("NCCL: ") + (na.GetErrorString ? na.GetErrorString(r__) : "error") + " at " #expr); \
+    } while (0)
+
+gs_status gs_comm_unique_id(void *id128)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(id128, "null argument");
+    const gsd::nccl::api &na = gsd::nccl::load();
+    if (!na.ok) return fail(GS_ERR_UNSUPPORTED, na.why);
+    gsd::nccl::unique_id id;
+    NCCL_TRY(na.GetUniqueId(&id));
+    memcpy(id128, &id, sizeof id);
+    GS_API_END
+}
+
+gs_status gs_comm_init(gs_ctx *ctx, int nranks, int rank, const void *id128)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ctx && id128 && nranks >= 1 && rank >= 0 && rank < nranks, "bad argument");
+    GS_REQUIRE(!ctx->comm, "the context already has a communicator");
+    const gsd::nccl::api &na = gsd::nccl::load();
+    if (!na.ok) return fail(GS_ERR_UNSUPPORTED, na.why);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    gsd::nccl::unique_id id;
+    memcpy(&id, id128, sizeof id);
+    NCCL_TRY(na.CommInitRank(&ctx->comm, nranks, id, rank));
+    ctx->comm_rank = rank, ctx->comm_size = nranks;
+    GS_API_END
+}
+
+gs_status gs_comm_allgather_rows(gs_ctx *ctx, void *C_full_dev, const uint64_t *row_cuts, uint64_t row_bytes)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ctx && C_full_dev && row_cuts && row_bytes > 0, "bad argument");
+    GS_REQUIRE(ctx->comm, "gs_comm_init has not been called on this context");
+    const gsd::nccl::api &na = gsd::nccl::load();
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->mem_stream(); // ordered behind the launches on gs_stream(); breaks the PDL chain
+    NCCL_TRY(na.GroupStart());
+    const int r = gsd::nccl::allgather_rows(na, ctx->comm, st, C_full_dev, row_cuts, ctx->comm_size, row_bytes);
+    const int r2 = na.GroupEnd();
+    NCCL_TRY(r);
+    NCCL_TRY(r2);
+    GS_API_END
+}
+
+void gs_comm_destroy(gs_ctx *ctx)
+{
+    if (!ctx || !ctx->comm) return;
+    const gsd::nccl::api &na = gsd::nccl::load();
+    cudaSetDevice(ctx->device);
+    if (na.ok) na.CommDestroy(ctx->comm);
+    ctx->comm = nullptr, ctx->comm_size = 0, ctx->comm_rank = -1;
+}
 
 gs_status gs_launch_no_alloc(gs_plan *p, const void *B_dev, void *C_dev, void *stream)
 {
@@ -731,7 +806,7 @@ gs_status gs_spmm_host(gs_plan *p, const void *B_host, void *C_host)
     CUDA_TRY(cudaMemcpyAsync(p->B_dev, B_host, nb, cudaMemcpyHostToDevice, p->ctx->mem_stream()));
     p->B_use = p->B_dev;
     enqueue(p);
-    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, nc, cudaMemcpyDeviceToHost, p->ctx->mem_stream()));
+    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_out(), nc, cudaMemcpyDeviceToHost, p->ctx->mem_stream()));
     CUDA_TRY(cudaStreamSynchronize(p->ctx->stream));
     GS_API_END
 }
@@ -783,7 +858,7 @@ gs_status gs_spmm_host_async(gs_plan *p, const void *B_host, void *C_host)
     enqueue(p, which);
     CUDA_TRY(cudaEventRecord(p->ev_k, ls));
     CUDA_TRY(cudaStreamWaitEvent(ctx->copy_out, p->ev_k, 0));
-    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_dev, nc, cudaMemcpyDeviceToHost, ctx->copy_out));
+    CUDA_TRY(cudaMemcpyAsync(C_host, p->C_out(), nc, cudaMemcpyDeviceToHost, ctx->copy_out));
     CUDA_TRY(cudaEventRecord(p->ev_c, ctx->copy_out));
     GS_API_END
 }

@@ -13,6 +13,8 @@
 //   --values                          keep the file's values (the reference forces every value to 1)
 //   --repeat R                        timed launches (reference: 10000)
 //   --dump <dir>                      write every metadata array as text, one value per line (struct.cc:1991)
+//   --gpus G                          the matrix is cut into G nnz-balanced row blocks, one per GPU 0..G-1 (gs_exec_*: B replicated,
+//                                     C rows disjoint, no collective); --allgather: then replicate C on every GPU over NCCL and time it
 //   --no-parity                       skip the host check (the reference always checks, code_generator.cc:631-638)
 //   --corrupt-check                   flip one element of the host copy of C before the check (shows that the check can fail)
 // The host check is the reference's own: all-ones B, C[i][j] must equal the row's sum of values exactly in
@@ -70,7 +72,8 @@ int main(int argc, char **argv)
     int N = atoi(argv[2]);
     std::string family = "thread_total", kernel, dump;
     int S = 4, C = 1, repeat = 10000;
-    bool half = false, values = false, parity = true, corrupt = false;
+    bool half = false, values = false, parity = true, corrupt = false, allgather = false;
+    int gpus = 1;
     for (int i = 3; i < argc; i++) {
         std::string a = argv[i];
         auto next = [&]() -> const char * { return i + 1 < argc ? argv[++i] : ""; };
@@ -84,7 +87,8 @@ int main(int argc, char **argv)
         else if (a == "--dump") dump = next();
         else if (a == "--no-parity") parity = false;
         else if (a == "--corrupt-check") corrupt = true;
-        else if (a == "--gpus") next(); // multi-GPU runs go through bench.py / torchrun: one process per GPU
+        else if (a == "--gpus") gpus = atoi(next());
+        else if (a == "--allgather") allgather = true;
         else {
             fprintf(stderr, "token_test: unknown flag %s\n", a.c_str());
             return 2;
@@ -108,6 +112,77 @@ int main(int argc, char **argv)
     gsh_metadata *ms = nullptr;
     OK(gsh_metadata_from_mtx(mtx.c_str(), "float", values ? 0 : 1, &ms));
     printf("finish read file\n");
+
+    if (gpus > 1) {
+        // ---- several GPUs, one process: the executor cuts the matrix as loaded, every block runs the chain on its own device ----
+        std::vector<int> ids(gpus);
+        for (int g = 0; g < gpus; g++) ids[g] = g;
+        gs_exec *ex = nullptr;
+        OK(gs_exec_create(&ex, ids.data(), gpus));
+        const int k = kernel.empty() || kernel == "auto" ? GS_KERNEL_AUTO : kernel == "reference" ? GS_KERNEL_CHAIN : [&] {
+            for (int f = 0; f < GS_FAMILY_COUNT; f++)
+                if (kernel == gs_family_name(f)) return f;
+            fprintf(stderr, "token_test: unknown kernel %s\n", kernel.c_str());
+            exit(2);
+            return 0;
+        }();
+        OK(gs_exec_build(ex, ms, fam, N, S, C, half, k));
+        uint64_t rows = 0, cols = 0, nnz = 0, one = 0;
+        OK(gsh_metadata_read_u64(ms, "GLOBAL_META_origin_row_num_-1", &rows, 1));
+        OK(gsh_metadata_read_u64(ms, "GLOBAL_META_origin_col_num_-1", &cols, 1));
+        OK(gsh_metadata_info(ms, "GLOBAL_META_nz_row_indices_0", &nnz, nullptr, nullptr));
+        (void)one;
+        std::vector<uint64_t> cuts(gpus + 1), bnnz(gpus);
+        OK(gs_exec_row_cuts(ex, cuts.data(), bnnz.data()));
+        for (int g = 0; g < gpus; g++) printf("gpu %d: rows [%llu, %llu) nnz %llu kernel: %s\n", g, (unsigned long long)cuts[g], (unsigned long long)cuts[g + 1], (unsigned long long)bnnz[g], gs_exec_kernel_name(ex, g));
+        std::vector<float> B((size_t)cols * N, 1.0f);
+        OK(gs_exec_set_dense(ex, B.data(), GS_F32));
+        if (allgather) OK(gs_exec_enable_allgather(ex));
+        float ms_iter = 0;
+        OK(gs_exec_run(ex, 1, &ms_iter, nullptr)); // warm-up
+        OK(gs_exec_run(ex, repeat, &ms_iter, nullptr));
+        char fr[64] = "2";
+        gsh_config_get("FLOAT_RATE", fr, sizeof fr);
+        const double gflops = atof(fr) * (double)nnz * N / (ms_iter * 1e-3) / 1e9;
+        std::vector<unsigned char> out((size_t)rows * N * (half ? 2 : 4));
+        OK(gs_exec_get_output(ex, out.data()));
+        if (allgather) {
+            float ag = 0;
+            OK(gs_exec_allgather_output(ex, &ag));
+            std::vector<unsigned char> rep(out.size());
+            long diff = 0;
+            for (int g = 0; g < gpus; g++) {
+                OK(gs_exec_get_replica(ex, g, rep.data()));
+                if (memcmp(rep.data(), out.data(), out.size()) != 0) diff++;
+            }
+            printf("allgather: %g ms, %ld of %d replicas differ from C\n", ag, diff, gpus);
+        }
+        if (parity) {
+            std::vector<uint64_t> r(nnz);
+            std::vector<double> v(nnz);
+            OK(gsh_metadata_read_u64(ms, "GLOBAL_META_nz_row_indices_0", r.data(), nnz));
+            OK(gsh_metadata_read_f64(ms, "GLOBAL_META_nz_vals_0", v.data(), nnz));
+            std::vector<double> ref(rows, 0.0), absref(rows, 0.0);
+            for (uint64_t i = 0; i < nnz; i++) ref[r[i]] += v[i], absref[r[i]] += v[i] < 0 ? -v[i] : v[i];
+            if (corrupt && !out.empty()) out[out.size() / 2 + (half ? 1 : 3)] ^= 0x40u;
+            long wrong = 0;
+            const double tol = half ? 1e-2 : 1e-5;
+            for (uint64_t i = 0; i < rows; i++)
+                for (int j = 0; j < N; j++) {
+                    const double c = half ? (double)half_to_float(((const uint16_t *)out.data())[i * N + j]) : (double)((const float *)out.data())[i * N + j];
+                    const bool exact = !values && ref[i] <= (half ? 2048.0 : 16777216.0);
+                    const double err = c > ref[i] ? c - ref[i] : ref[i] - c;
+                    if (exact ? c != ref[i] : !(err <= tol * absref[i])) wrong++;
+                }
+            if (wrong) printf("wrong number:%ld\n", wrong);
+            else printf("correct\n");
+        }
+        printf("%s %g\n", mtx.c_str(), gflops);
+        printf("%s : min time: %g\n", mtx.c_str(), ms_iter * 1e-3);
+        gs_exec_destroy(ex);
+        gsh_metadata_free(ms);
+        return 0;
+    }
     gsh_session *s = nullptr;
     OK(gsh_session_create(ms, 0, &s));
     OK(gsh_session_run_family(s, fam, N, S, C));

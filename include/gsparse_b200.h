@@ -58,6 +58,7 @@ typedef enum gs_family {
  * measured rates -- the slice of the reference's unbuilt calculation_method_choose_operator (README.md:36, "under development") this
  * path needs; the chain's own family is the last resort */
 #define GS_KERNEL_AUTO (-1)
+#define GS_KERNEL_CHAIN (-2) /* gs_exec_build: keep the chain's own reference-shaped family */
 
 const char *gs_last_error(void);
 const char *gs_version(void);
@@ -72,6 +73,11 @@ gs_status gsh_metadata_from_mtx(const char *path, const char *float_precise, int
 /* the same store from in-memory COO (row-major sorted, 0-based); vals may be NULL (all ones) */
 gs_status gsh_metadata_from_coo(uint64_t rows, uint64_t cols, uint64_t nnz, const int64_t *row, const int64_t *col,
                                 const float *vals, gsh_metadata **out);
+/* rows [lo, hi) of the matrix as loaded (sub-matrix 0, before any operator ran) as a store of its own, rows rebased to 0: the
+ * block one GPU owns in the row partition (the reference's matrix-div operators cut sub-matrices the same way,
+ * fixed_div_row_indices.cc).  gsh_metadata_row_nnz: non-zeros per row of the matrix as loaded (len rows = origin_row_num). */
+gs_status gsh_metadata_row_block(const gsh_metadata *ms, uint64_t lo, uint64_t hi, gsh_metadata **out);
+gs_status gsh_metadata_row_nnz(const gsh_metadata *ms, uint64_t *out, uint64_t rows);
 void gsh_metadata_free(gsh_metadata *ms);
 /* number of items; key of item i in insertion order ("<POS>_<name>_<id>", metadata_set.cc:147-151) */
 uint64_t gsh_metadata_count(const gsh_metadata *ms);
@@ -217,6 +223,10 @@ void *gs_output_device(gs_plan *p);
  * Every call shares the array: calls that overlap on the GPU (different streams, or several host threads) race; calls
  * on one stream are ordered.  Rows of C the matrix does not have (trimmed trailing empty rows) are not written. */
 gs_status gs_launch_no_alloc(gs_plan *p, const void *B_dev, void *C_dev, void *stream);
+/* launches write C into the caller's device buffer (rows x N, plan's value type, 16-byte aligned) instead of the plan's own; NULL
+ * switches back.  Rows the matrix does not have are not written: zero the buffer first.  (How a row block lands in place in a
+ * full-size C for the all-gather.) */
+gs_status gs_plan_set_output_device(gs_plan *p, void *C_dev);
 /* host-buffer round trip the reference's execute_binary does through files (executor.cc:6-58):
  * H2D of B, launch, D2H of C, all on gs_stream(); returns after the stream drained */
 gs_status gs_spmm_host(gs_plan *p, const void *B_host, void *C_host);
@@ -242,6 +252,41 @@ gs_status gs_plan_sp24_probe(const gs_plan *p, uint32_t *out512);
 /* execute_binary(path, matrix, &ms_total, &gflops) of executor.hpp:15 for an uploaded plan:
  * 1 warm-up + `repeat` launches, gflops = FLOAT_RATE*origin_nnz*N*repeat/t/1e9 (code_generator.cc:582-624) */
 gs_status gs_execute(gs_plan *p, int repeat, float *ms_total, float *gflops);
+
+/* ------------------------------------------------------------------ device: several GPUs ----- */
+/* The reference has no multi-GPU path (executor.hpp:15 hands one program to one device).  North star (3):
+ * A is cut into nnz-balanced contiguous row blocks (balanced_interval rule, data_transform_common.cc:934-988), one block per GPU, B is
+ * replicated, C rows are disjoint, NCCL only for an optional all-gather of C.
+ *
+ * One process per GPU (torchrun): every rank owns a gs_ctx; gs_comm_* gives the contexts a communicator.  rank 0 calls
+ * gs_comm_unique_id (128 bytes, ncclGetUniqueId), ships the bytes to the other ranks by any means, every rank calls gs_comm_init.
+ * gs_comm_allgather_rows: rank g's rows [row_cuts[g], row_cuts[g+1]) already sit at their place in C_full_dev (gs_plan_set_output_device);
+ * after the call, enqueued on gs_stream(), every rank holds all rows (ragged blocks: one group of ncclBroadcast).  NCCL is reached
+ * through dlopen; GS_ERR_UNSUPPORTED when libnccl.so.2 is absent. */
+gs_status gs_comm_unique_id(void *id128);
+gs_status gs_comm_init(gs_ctx *ctx, int nranks, int rank, const void *id128);
+gs_status gs_comm_allgather_rows(gs_ctx *ctx, void *C_full_dev, const uint64_t *row_cuts, uint64_t row_bytes);
+void gs_comm_destroy(gs_ctx *ctx);
+
+/* One process, several GPUs: SURVEY.md section 8b's gs_create(ctx, device_ids, n_dev).  gs_exec_build cuts the matrix of `ms` (as
+ * loaded) into gs_exec_devices() row blocks, runs the driver chain `family` (test_spmm_<family>, token_test.cc:1003-1582) on every
+ * block and plans it on its device with `kernel` (a gs_family, GS_KERNEL_AUTO or GS_KERNEL_CHAIN).  gs_exec_run: every device runs
+ * `repeat` launches on its own stream, enqueued by its own host thread, CUDA-event timed; *ms_per_iter_max = the slowest device.
+ * gs_exec_get_output: C (rows x N) in the matrix's row order.  gs_exec_enable_allgather + gs_exec_allgather_output: C replicated on
+ * every device (NCCL, in place), *ms = the slowest device's time for the collective; gs_exec_get_replica reads device g's copy. */
+typedef struct gs_exec gs_exec;
+gs_status gs_exec_create(gs_exec **out, const int *device_ids, int n_dev);
+void gs_exec_destroy(gs_exec *ex);
+int gs_exec_devices(const gs_exec *ex);
+gs_status gs_exec_build(gs_exec *ex, const gsh_metadata *ms, int family, int N, int sparse_coarsen, int coarsen, int half, int kernel);
+gs_status gs_exec_row_cuts(const gs_exec *ex, uint64_t *cuts /* n_dev + 1 */, uint64_t *block_nnz /* n_dev, may be NULL */);
+const char *gs_exec_kernel_name(const gs_exec *ex, int g);
+gs_status gs_exec_set_dense(gs_exec *ex, const void *B_host, int dtype);
+gs_status gs_exec_run(gs_exec *ex, int repeat, float *ms_per_iter_max, float *ms_per_iter_dev /* n_dev, may be NULL */);
+gs_status gs_exec_get_output(gs_exec *ex, void *C_host);
+gs_status gs_exec_enable_allgather(gs_exec *ex);
+gs_status gs_exec_allgather_output(gs_exec *ex, float *ms);
+gs_status gs_exec_get_replica(gs_exec *ex, int g, void *C_host);
 
 #ifdef __cplusplus
 }
