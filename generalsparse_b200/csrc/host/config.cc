@@ -18,6 +18,7 @@ config_store::config_store()
            {"FLOAT_RATE", "2"},
            {"GFLOPS_UP_BOUND", "1000000"}, // the reference's 10000 is below what a B200 reaches
            {"HALF", "false"},
+           {"MAX_DIV_TIMES_OF_DIV", "12"},
            {"OPERATOR_RUNTIME_CHECK", "true"},
            {"PADDING_RATE_UP_BOUND", "4"},
            {"PRECISE_OF_FLOAT", "\"float\""},

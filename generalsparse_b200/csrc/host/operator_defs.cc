@@ -175,6 +175,7 @@ class fixed_interval_row_direction_thread_blocking_operator : public basic_opera
         return !any_name_has(d, "thread") && !any_name_has(d, "col") && !any_name_has(d, "interlance") && !balanced;
     }
     void set_padding_to_false() override { row_pad_ = max_pad_ = col_pad_ = false; }
+    bool get_is_col_padding_with_row_max_size_with_empty_row() const override { return max_pad_; }
     void run(bool check) override
     {
         auto &ms = *meta_data_set_ptr;
@@ -240,6 +241,7 @@ class fixed_interval_col_direction_thread_blocking_operator : public basic_opera
         return h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty() && !any_name_has(d, "thread") && !any_name_has(d, "interlance");
     }
     void set_padding_to_false() override { col_pad_ = max_pad_ = false; }
+    bool get_is_padding_with_col_size_in_bmt() const override { return col_pad_; }
     void run(bool check) override
     {
         auto &ms = *meta_data_set_ptr;
@@ -304,8 +306,11 @@ class fixed_interval_nnz_direction_thread_blocking_operator : public basic_opera
         bool has_tb = ms.is_exist(TBLOCK_META, "first_row_indices", id), has_w = ms.is_exist(WARP_META, "first_row_indices", id);
         if (pad_) steps::modify_by_nnz_pad(ms, id, k_, pad_bound(), &r);
         steps::get_begin_rows_after_fixed_blocking_in_nnz_direction(ms, THREAD_META, id, k_, &r);
-        GS_REQUIRE(!row_rel_ && !nz_rel_, "nnz-direction BMT indices relative to a parent: not built yet");
+        // relative to the innermost parent level: BMW, else BMTB (fixed_interval_nnz_direction_thread_blocking_operator.cc run())
+        GS_REQUIRE(!(row_rel_ || nz_rel_) || has_w || has_tb, "relative indices need a parent level");
+        if (row_rel_) steps::get_begin_rows_of_BMT_after_fixed_blocking_in_nnz_direction_relative_to_parent(ms, has_w ? WARP_META : TBLOCK_META, id, k_, &r);
         steps::get_begin_nzs_after_fixed_blocking_in_nnz_direction(ms, THREAD_META, id, k_, &r);
+        if (nz_rel_) steps::get_begin_nzs_of_BMT_after_fixed_blocking_in_nnz_direction_relative_to_parent(ms, has_w ? WARP_META : TBLOCK_META, id, k_, &r);
         if (has_w) steps::get_begin_children_of_parent_after_blocking(ms, THREAD_META, WARP_META, id, &r);
         else if (has_tb) steps::get_begin_children_of_parent_after_blocking(ms, THREAD_META, TBLOCK_META, id, &r);
         steps::get_BMT_size_of_each_parent(ms, GLOBAL_META, id, false, &r);
@@ -411,25 +416,45 @@ class fixed_interval_nnz_direction_warp_blocking_operator : public basic_operato
     bool row_rel_, nz_rel_, pad_;
 };
 
-// balanced_interval_row_direction_{tblock,warp,thread}_blocking_operator (operator.hpp:871,823,777), top level
+// balanced_interval_row_direction_{tblock,warp,thread}_blocking_operator (operator.hpp:871,823,777; operator/balanced_interval_*.cc)
 class balanced_interval_row_direction_blocking_operator : public basic_operator {
   public:
-    balanced_interval_row_direction_blocking_operator(std::shared_ptr<code_generator> cg, POS_TYPE pos, int nnz_per_interval)
+    balanced_interval_row_direction_blocking_operator(std::shared_ptr<code_generator> cg, POS_TYPE pos, int nnz_per_interval, bool row_rel, bool nz_rel)
         : basic_operator(std::string("balanced_interval_row_direction_") + (pos == TBLOCK_META ? "tblock" : pos == WARP_META ? "warp" : "thread") +
-                             "_blocking_operator", std::move(cg), DISTRIBUTING_OP), pos_(pos), per_(nnz_per_interval)
+                             "_blocking_operator", std::move(cg), DISTRIBUTING_OP), pos_(pos), per_(nnz_per_interval), row_rel_(row_rel), nz_rel_(nz_rel)
     {
         GS_REQUIRE(nnz_per_interval > 0, "nnz_per_interval must be > 0");
         params = ",nnz_per_interval:" + std::to_string(nnz_per_interval);
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        // nothing implemented yet; tblock: the first distributing operator; warp: no warp / thread / col / interlance / nnz_direction operator
+        // before it; thread: no thread / col / interlance / nnz_direction operator before it
+        if (!h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty()) return false;
+        const opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        if (pos_ == TBLOCK_META) return d.empty();
+        if (any_name_has(d, "thread") || any_name_has(d, "col") || any_name_has(d, "interlance") || any_name_has(d, "nnz_direction")) return false;
+        return pos_ == THREAD_META || !any_name_has(d, "warp");
     }
     void run(bool) override
     {
         auto &ms = *meta_data_set_ptr;
         int id = target_matrix_id;
-        GS_REQUIRE(ms.count_of_metadata_of_diff_pos(TBLOCK_META, id) + ms.count_of_metadata_of_diff_pos(WARP_META, id) == 0 || pos_ == TBLOCK_META,
-                   "balanced blocking inside a parent level: not built yet");
         steps::recs r;
-        steps::get_begin_rows_after_nnz_blocking_in_row_direction(ms, pos_, id, per_, &r);
-        steps::get_begin_nzs_after_nnz_blocking_in_row_direction(ms, pos_, id, per_, &r);
+        const bool has_tb = ms.is_exist(TBLOCK_META, "first_row_indices", id), has_w = ms.is_exist(WARP_META, "first_row_indices", id);
+        const POS_TYPE parent = pos_ == THREAD_META && has_w ? WARP_META : (pos_ != TBLOCK_META && has_tb) ? TBLOCK_META : NONE_META;
+        GS_REQUIRE(ms.count_of_metadata_of_diff_pos(pos_, id) == 0, "balanced blocking: the level already has metadata");
+        if (parent != NONE_META) {
+            steps::get_begin_rows_after_nnz_blocking_in_row_direction_in_parent(ms, pos_, parent, id, per_, false, &r);
+            if (row_rel_) steps::get_begin_rows_after_nnz_blocking_in_row_direction_in_parent(ms, pos_, parent, id, per_, true, &r);
+            steps::get_begin_nzs_after_nnz_blocking_in_row_direction_in_parent(ms, pos_, parent, id, per_, false, &r);
+            if (nz_rel_) steps::get_begin_nzs_after_nnz_blocking_in_row_direction_in_parent(ms, pos_, parent, id, per_, true, &r);
+            steps::get_begin_children_of_parent_after_blocking_in_row_direction(ms, pos_, parent, id, &r);
+        } else {
+            GS_REQUIRE(!row_rel_ && !nz_rel_, "relative indices need a parent level");
+            steps::get_begin_rows_after_nnz_blocking_in_row_direction(ms, pos_, id, per_, &r);
+            steps::get_begin_nzs_after_nnz_blocking_in_row_direction(ms, pos_, id, per_, &r);
+        }
         append(transform_seq, r);
         code_generator_ptr->open_spec_level_of_paral(pos_);
         if (pos_ == THREAD_META) code_generator_ptr->set_thread_for_row(true);
@@ -439,6 +464,213 @@ class balanced_interval_row_direction_blocking_operator : public basic_operator 
   private:
     POS_TYPE pos_;
     uint64_t per_;
+    bool row_rel_, nz_rel_;
+};
+
+// fixed_interval_col_direction_tblock_blocking_operator (operator.hpp:727): the first distributing operator of a chain
+class fixed_interval_col_direction_tblock_blocking_operator : public basic_operator {
+  public:
+    fixed_interval_col_direction_tblock_blocking_operator(std::shared_ptr<code_generator> cg, int col_block, bool pad_to_col_size, bool pad_to_row_max)
+        : basic_operator("fixed_interval_col_direction_tblock_blocking_operator", std::move(cg), DISTRIBUTING_OP), c_(col_block), col_pad_(pad_to_col_size), max_pad_(pad_to_row_max)
+    {
+        GS_REQUIRE(col_block > 0, "fixed_col_block_size must be > 0");
+        params = ",fixed_col_block_size:" + std::to_string(col_block) + ",is_padding:" + std::to_string((int)(pad_to_col_size || pad_to_row_max));
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        return h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty() && h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id).empty();
+    }
+    void set_padding_to_false() override { col_pad_ = max_pad_ = false; }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        GS_REQUIRE(ms.count_of_metadata_of_diff_pos(TBLOCK_META, id) + ms.count_of_metadata_of_diff_pos(WARP_META, id) + ms.count_of_metadata_of_diff_pos(THREAD_META, id) == 0 &&
+                       !ms.is_exist(GLOBAL_META, "nz_row_indices_after_interlance_storage", id),
+                   "col-direction tblock blocking: a level or interleaved storage already exists");
+        steps::recs r;
+        if (max_pad_) steps::modify_by_col_pad_parent_blk_to_max_row_size(ms, GLOBAL_META, id, false, pad_bound(), &r);
+        if (col_pad_) steps::modify_by_col_pad_in_sub_matrix(ms, id, c_, pad_bound(), &r);
+        steps::get_begin_rows_after_fixed_blocking_in_col_direction(ms, TBLOCK_META, id, c_, &r);
+        steps::get_begin_nzs_after_fixed_blocking_in_col_direction(ms, TBLOCK_META, id, c_, &r);
+        if (col_pad_) steps::get_BMTB_size(ms, id, &r);
+        append(transform_seq, r);
+        code_generator_ptr->open_spec_level_of_paral(TBLOCK_META);
+        is_run = true;
+    }
+
+  private:
+    uint64_t c_;
+    bool col_pad_, max_pad_;
+};
+
+// fixed_interval_col_direction_warp_blocking_operator (operator.hpp:652)
+class fixed_interval_col_direction_warp_blocking_operator : public basic_operator {
+  public:
+    fixed_interval_col_direction_warp_blocking_operator(std::shared_ptr<code_generator> cg, int col_block, bool row_rel_bmtb, bool nz_rel_bmtb, bool pad_to_col_size, bool pad_to_row_max,
+                                                        std::shared_ptr<operator_context> history)
+        : basic_operator("fixed_interval_col_direction_warp_blocking_operator", std::move(cg), DISTRIBUTING_OP), c_(col_block), row_rel_(row_rel_bmtb), nz_rel_(nz_rel_bmtb),
+          col_pad_(pad_to_col_size), max_pad_(pad_to_row_max)
+    {
+        GS_REQUIRE(col_block > 0, "fixed_col_block_size must be > 0");
+        former_ = history->read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        pad_pos_ = any_name_has(former_, "tblock") ? TBLOCK_META : GLOBAL_META; // ctor, :38-54
+        params = ",fixed_col_block_size:" + std::to_string(col_block) + ",is_padding:" + std::to_string((int)(pad_to_col_size || pad_to_row_max));
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        if (!h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty()) return false;
+        const opv d = h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        const bool balanced = any_name_has(d, "balanced_interval") && max_pad_;
+        return !any_name_has(d, "thread") && !any_name_has(d, "warp") && !any_name_has(d, "col") && !any_name_has(d, "interlance") && !balanced;
+    }
+    void set_padding_to_false() override { col_pad_ = max_pad_ = false; }
+    void run(bool check) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        const bool has_tb = ms.is_exist(TBLOCK_META, "first_row_indices", id);
+        GS_REQUIRE(ms.count_of_metadata_of_diff_pos(WARP_META, id) + ms.count_of_metadata_of_diff_pos(THREAD_META, id) == 0, "col-direction warp blocking: a warp or thread level already exists");
+        GS_REQUIRE(!(row_rel_ || nz_rel_) || has_tb, "indices relative to BMTB need a tblock level");
+        GS_REQUIRE(!(max_pad_ && pad_pos_ == TBLOCK_META) || has_tb, "padding to the BMTB's row maximum needs a tblock level");
+        GS_REQUIRE(has_tb == !former_.empty(), "col-direction warp blocking: the tblock level and the operator history disagree");
+        GS_REQUIRE(!ms.is_exist(GLOBAL_META, "nz_row_indices_after_interlance_storage", id), "interleaved storage already exists");
+        steps::recs r;
+        if (max_pad_) steps::modify_by_col_pad_parent_blk_to_max_row_size(ms, pad_pos_, id, false, pad_bound(), &r);
+        if (col_pad_) steps::modify_by_col_pad_in_sub_matrix(ms, id, c_, pad_bound(), &r);
+        if (col_pad_ || max_pad_) {
+            if (has_tb) drop_level(ms, TBLOCK_META, id, r);
+            rerun_former(former_, check, r);
+        }
+        steps::get_begin_rows_after_fixed_blocking_in_col_direction(ms, WARP_META, id, c_, &r);
+        steps::get_begin_nzs_after_fixed_blocking_in_col_direction(ms, WARP_META, id, c_, &r);
+        if (row_rel_) steps::get_begin_rows_of_BMW_after_fixed_blocking_in_col_direction_relative_to_BMTB(ms, id, c_, &r);
+        if (nz_rel_) steps::get_begin_nzs_of_BMW_after_fixed_blocking_in_col_direction_relative_to_BMTB(ms, id, c_, &r);
+        if (has_tb) steps::get_begin_children_of_parent_after_blocking(ms, WARP_META, TBLOCK_META, id, &r);
+        if (col_pad_ && has_tb) steps::get_BMW_size_of_each_parent(ms, TBLOCK_META, id, &r);
+        if (col_pad_) steps::get_BMW_size_of_each_parent(ms, GLOBAL_META, id, &r);
+        append(transform_seq, r);
+        code_generator_ptr->open_spec_level_of_paral(WARP_META);
+        is_run = true;
+    }
+
+  private:
+    uint64_t c_;
+    bool row_rel_, nz_rel_, col_pad_, max_pad_;
+    POS_TYPE pad_pos_ = GLOBAL_META;
+    opv former_;
+};
+
+// interlance_storage_operator (operator.hpp:567, operator/interlance_storage_operator.cc)
+class interlance_storage_operator : public basic_operator {
+  public:
+    interlance_storage_operator(std::shared_ptr<code_generator> cg, std::shared_ptr<operator_context> history)
+        : basic_operator("interlance_storage_operator", std::move(cg), DISTRIBUTING_OP)
+    {
+        // the innermost parent level an earlier operator built (ctor, :9-38)
+        const opv d = history->read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id);
+        bool warp = false, tblock = false;
+        for (const auto &o : d) {
+            if (o->get_name().find("warp") != std::string::npos) warp = true;
+            else if (o->get_name().find("tblock") != std::string::npos) tblock = true;
+        }
+        pos_ = warp ? WARP_META : tblock ? TBLOCK_META : GLOBAL_META;
+        code_generator_ptr->set_interleave_storage();
+    }
+    std::string convert_to_string() const override { return "interlance_storage_operator::{name:\"" + name + ",target_matrix_id:" + std::to_string(target_matrix_id) + "}"; } // (sic: no closing quote)
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        // after a thread-level operator that made the BMTs of a parent equally long (column blocking padded to the block size, or row
+        // blocking padded to the parent's longest row), once, before anything is implemented
+        if (!h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty()) return false;
+        bool ok = false;
+        for (const auto &o : h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id)) {
+            if (o->get_name().find("interlance") != std::string::npos) return false;
+            if (o->get_name().find("fixed_interval_col_direction_thread_blocking_operator") != std::string::npos && o->get_is_padding_with_col_size_in_bmt()) ok = true;
+            if (o->get_name().find("fixed_interval_row_direction_thread_blocking_operator") != std::string::npos && o->get_is_col_padding_with_row_max_size_with_empty_row()) ok = true;
+        }
+        return ok;
+    }
+    bool is_valid_according_to_metadata() override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        if (ms.is_exist(GLOBAL_META, "nz_row_indices_after_interlance_storage", id) || ms.is_exist(GLOBAL_META, "nz_col_indices_after_interlance_storage", id) ||
+            ms.is_exist(GLOBAL_META, "nz_vals_after_interlance_storage", id))
+            return false;
+        if (pos_ != GLOBAL_META && !ms.is_exist(pos_, "first_BMT_indices", id)) return false;
+        return ms.is_exist(pos_, "BMT_size_of_each_blk", id);
+    }
+    void run(bool) override
+    {
+        GS_REQUIRE(is_valid_according_to_metadata(), "interlance_storage_operator: needs BMT_size_of_each_blk (equally long BMTs) at the parent level and no interleaved arrays yet");
+        steps::recs r;
+        steps::modify_by_interlance_storage(*meta_data_set_ptr, pos_, target_matrix_id, &r);
+        append(transform_seq, r);
+        is_run = true;
+    }
+
+  private:
+    POS_TYPE pos_ = GLOBAL_META;
+};
+
+// fixed_interval_row_matrix_div_operator (operator.hpp:289) and row_nz_matrix_div_operator (:319): CONVERTING operators that cut the
+// sub-matrix into new sub-matrices (ids max + 1 ...); the parent's streams are removed, its boundaries stay
+class matrix_div_operator : public basic_operator {
+  public:
+    matrix_div_operator(std::shared_ptr<code_generator> cg, int fixed_row_interval_size)
+        : basic_operator("fixed_interval_row_matrix_div_operator", std::move(cg), CONVERTING_OP), fixed_(true), a_(fixed_row_interval_size)
+    {
+        GS_REQUIRE(fixed_row_interval_size > 0, "fixed_row_interval_size must be > 0");
+        params = ",fixed_row_interval_size:" + std::to_string(fixed_row_interval_size);
+    }
+    matrix_div_operator(std::shared_ptr<code_generator> cg, int init_upper, int max_upper, int expansion)
+        : basic_operator("row_nz_matrix_div_operator", std::move(cg), CONVERTING_OP), fixed_(false), a_(init_upper), b_(max_upper), c_(expansion)
+    {
+        GS_REQUIRE(init_upper > 0 && expansion > 0, "init_row_size_upper_boundary and expansion_rate must be > 0");
+    }
+    bool is_valid_according_to_operator(const operator_context &h) override
+    {
+        // (sic) only a division of the same sub-matrix, met while nothing is distributed or implemented, makes the operator invalid
+        if (!h.read_operator_context_arr(IMPLEMENTING_OP, target_matrix_id).empty() || !h.read_operator_context_arr(DISTRIBUTING_OP, target_matrix_id).empty()) return true;
+        for (const auto &o : h.read_operator_context_arr(CONVERTING_OP, target_matrix_id))
+            if (o->get_name().find("div_operator") != std::string::npos) return false;
+        return true;
+    }
+    void run(bool) override
+    {
+        auto &ms = *meta_data_set_ptr;
+        int id = target_matrix_id;
+        GS_REQUIRE(ms.is_exist(GLOBAL_META, "nz_row_indices", id) && ms.is_exist(GLOBAL_META, "nz_col_indices", id) && ms.is_exist(GLOBAL_META, "nz_vals", id) &&
+                       ms.is_exist(GLOBAL_META, "begin_row_index", id) && ms.is_exist(GLOBAL_META, "end_row_index", id) && ms.is_exist(GLOBAL_META, "begin_col_index", id) &&
+                       ms.is_exist(GLOBAL_META, "end_col_index", id) && !ms.is_exist(GLOBAL_META, "nz_row_indices_after_interlance_storage", id),
+                   name + ": the sub-matrix has no streams or boundaries to divide");
+        const uint64_t row_num = ms.scalar(GLOBAL_META, "end_row_index", id) - ms.scalar(GLOBAL_META, "begin_row_index", id) + 1;
+        const uint64_t max_div = (uint64_t)get_config().as_integer("MAX_DIV_TIMES_OF_DIV");
+        steps::recs r;
+        if (fixed_) {
+            const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+            std::vector<bool> used((row_num + a_ - 1) / a_, false);
+            uint64_t n = 0;
+            for (uint64_t x : R.u) {
+                GS_REQUIRE(x / a_ < used.size(), name + ": row index beyond end_row_index");
+                if (!used[x / a_]) used[x / a_] = true, n++;
+            }
+            GS_REQUIRE(row_num > a_ && n <= max_div, name + ": needs more rows than one interval and at most MAX_DIV_TIMES_OF_DIV non-empty parts");
+            steps::fixed_div_in_row_direction(ms, id, a_, &r);
+        } else {
+            const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+            std::vector<uint64_t> len = get_nnz_of_each_row_in_spec_range(R, 0, row_num - 1, 0, R.get_len() - 1);
+            GS_REQUIRE(steps::div_positions_by_row_nnz(len, a_, b_, c_).size() <= max_div, name + ": more parts than MAX_DIV_TIMES_OF_DIV");
+            steps::div_according_to_row_nz(ms, id, a_, b_, c_, &r);
+        }
+        append(transform_seq, r);
+        is_run = true;
+    }
+
+  private:
+    bool fixed_;
+    uint64_t a_, b_ = 0, c_ = 0;
 };
 
 // merge_path_{tblock,warp,thread}_operator (operator.hpp:1205,1251,1297; operator/merge_path_*_operator.cc)
@@ -746,6 +978,14 @@ const std::vector<std::string> &operator_names()
                                                "balanced_interval_row_direction_warp_blocking_operator",
                                                "balanced_interval_row_direction_thread_blocking_operator",
                                                "empty_row_pad_operator",
+                                               "fixed_interval_col_direction_tblock_blocking_operator",
+                                               "fixed_interval_col_direction_warp_blocking_operator",
+                                               "interlance_storage_operator",
+                                               "fixed_interval_row_matrix_div_operator",
+                                               "row_nz_matrix_div_operator",
+                                               "merge_path_tblock_operator",
+                                               "merge_path_warp_operator",
+                                               "merge_path_thread_operator",
                                                "thread_total_reduce_operator",
                                                "thread_bit_map_operator",
                                                "warp_total_reduce_operator",
@@ -778,13 +1018,20 @@ std::shared_ptr<basic_operator> make_operator(const std::string &op, std::shared
     if (op == "fixed_interval_nnz_direction_tblock_blocking_operator")
         return need(2), std::make_shared<fixed_interval_nnz_direction_tblock_blocking_operator>(cg, (int)a[0], a[1] != 0);
     if (op == "balanced_interval_row_direction_tblock_blocking_operator")
-        return need(1), std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, TBLOCK_META, (int)a[0]);
+        return need(1), std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, TBLOCK_META, (int)a[0], false, false);
+    if (op == "fixed_interval_col_direction_tblock_blocking_operator")
+        return need(3), std::make_shared<fixed_interval_col_direction_tblock_blocking_operator>(cg, (int)a[0], a[1] != 0, a[2] != 0);
+    if (op == "fixed_interval_col_direction_warp_blocking_operator")
+        return need(5), std::make_shared<fixed_interval_col_direction_warp_blocking_operator>(cg, (int)a[0], a[1] != 0, a[2] != 0, a[3] != 0, a[4] != 0, h);
+    if (op == "interlance_storage_operator") return need(0), std::make_shared<interlance_storage_operator>(cg, h);
+    if (op == "fixed_interval_row_matrix_div_operator") return need(1), std::make_shared<matrix_div_operator>(cg, (int)a[0]);
+    if (op == "row_nz_matrix_div_operator") return need(3), std::make_shared<matrix_div_operator>(cg, (int)a[0], (int)a[1], (int)a[2]);
     // the warp and thread flavours take (nnz_per_interval, row_index_is_relative, nz_index_is_relative) like the reference;
     // the one-argument form stays for callers that block at the top level only
     if (op == "balanced_interval_row_direction_warp_blocking_operator" || op == "balanced_interval_row_direction_thread_blocking_operator") {
         GS_REQUIRE(a.size() == 1 || a.size() == 3, op + " takes 1 or 3 arguments after code_generator_ptr");
-        GS_REQUIRE(a.size() == 1 || (a[1] == 0 && a[2] == 0), op + ": indices relative to a parent level are not built");
-        return std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, op.find("warp") != std::string::npos ? WARP_META : THREAD_META, (int)a[0]);
+        return std::make_shared<balanced_interval_row_direction_blocking_operator>(cg, op.find("warp") != std::string::npos ? WARP_META : THREAD_META, (int)a[0], a.size() == 3 && a[1] != 0,
+                                                                                   a.size() == 3 && a[2] != 0);
     }
     if (op == "merge_path_tblock_operator") return need(1), std::make_shared<merge_path_operator>(cg, TBLOCK_META, (int)a[0]);
     if (op == "merge_path_warp_operator") return need(1), std::make_shared<merge_path_operator>(cg, WARP_META, (int)a[0]);

@@ -103,6 +103,9 @@ class basic_operator { // operator.hpp:64-189
     virtual bool is_valid_according_to_metadata() { return true; }
     virtual bool is_valid_according_to_operator(const operator_context &) { return true; }
     virtual void set_padding_to_false() {}
+    // what interlance_storage_operator asks the thread-level operators before it (operator.hpp:567)
+    virtual bool get_is_padding_with_col_size_in_bmt() const { return false; }
+    virtual bool get_is_col_padding_with_row_max_size_with_empty_row() const { return false; }
     virtual std::string convert_to_string() const;
     const std::string &get_name() const { return name; }
     operator_stage_type get_stage() const { return stage; }

@@ -928,6 +928,329 @@ void get_begin_nzs_of_level_after_merge_path(meta_data_set &ms, POS_TYPE pos, in
     record(rec, "get_begin_nzs_of_level_after_merge_path", id, ",work_size:" + std::to_string(work));
 }
 
+// ------------------------------------------------------------------- col / nnz direction: a child level relative to its parent
+// get_begin_rows_of_BMW_after_fixed_blocking_in_col_direction_relative_to_BMTB.cc: the BMT rule above one level up
+void get_begin_rows_of_BMW_after_fixed_blocking_in_col_direction_relative_to_BMTB(meta_data_set &ms, int id, uint64_t c, recs *rec)
+{
+    std::vector<uint64_t> len = row_nnz(ms, id);
+    const universal_array &P = ms.get(TBLOCK_META, "first_row_indices", id);
+    std::vector<uint64_t> v;
+    for (uint64_t b = 0; b + 1 < P.get_len(); b++)
+        for (uint64_t r = P.u[b]; r < P.u[b + 1]; r++)
+            for (uint64_t k = 0; k < (len.at(r) + c - 1) / c; k++) v.push_back(r - P.u[b]);
+    GS_REQUIRE(!v.empty(), "no BMW");
+    ms.add_u(WARP_META, "first_row_indices_relative_to_BMTB", id, std::move(v));
+    record(rec, "get_begin_rows_of_BMW_after_fixed_blocking_in_col_direction_relative_to_BMTB", id, ",col_size:" + std::to_string(c));
+}
+
+// get_begin_nzs_of_BMW_after_fixed_blocking_in_col_direction_relative_to_BMTB.cc: the offset of every BMW inside its BMTB, no sentinel
+void get_begin_nzs_of_BMW_after_fixed_blocking_in_col_direction_relative_to_BMTB(meta_data_set &ms, int id, uint64_t c, recs *rec)
+{
+    std::vector<uint64_t> len = row_nnz(ms, id);
+    const universal_array &P = ms.get(TBLOCK_META, "first_row_indices", id);
+    std::vector<uint64_t> v;
+    for (uint64_t b = 0; b + 1 < P.get_len(); b++) {
+        v.push_back(0);
+        for (uint64_t r = P.u[b]; r < P.u[b + 1]; r++)
+            for (uint64_t left = len.at(r); left > 0;) {
+                uint64_t take = std::min(left, c);
+                v.push_back(v.back() + take);
+                left -= take;
+            }
+        v.pop_back(); // the parent's closing offset is dropped again: one entry per BMW
+    }
+    ms.add_u(WARP_META, "first_nz_indices_relative_to_BMTB", id, std::move(v));
+    record(rec, "get_begin_nzs_of_BMW_after_fixed_blocking_in_col_direction_relative_to_BMTB", id, ",col_size:" + std::to_string(c));
+}
+
+// get_begin_{rows,nzs}_of_BMT_after_fixed_blocking_in_nnz_direction_relative_to_{BMW,BMTB}.cc: as the BMW-to-BMTB pair above
+void get_begin_rows_of_BMT_after_fixed_blocking_in_nnz_direction_relative_to_parent(meta_data_set &ms, POS_TYPE parent, int id, uint64_t k, recs *rec)
+{
+    GS_REQUIRE(k >= 1 && (parent == WARP_META || parent == TBLOCK_META), "bad argument");
+    const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    const universal_array &PR = ms.get(parent, "first_row_indices", id), &PN = ms.get(parent, "first_nz_indices", id);
+    std::vector<uint64_t> v;
+    uint64_t p = 0;
+    for (uint64_t i = 0; i < R.get_len(); i += k) {
+        GS_REQUIRE(p + 1 < PN.get_len(), "BMT beyond the last parent block");
+        if (i >= PN.u[p + 1]) p++;
+        GS_REQUIRE(p < PR.get_len() && R.u[i] >= PR.u[p], "BMT starts above its parent's first row");
+        v.push_back(R.u[i] - PR.u[p]);
+    }
+    const char *tag = level_tag(parent);
+    ms.add_u(THREAD_META, std::string("first_row_indices_relative_to_") + tag, id, std::move(v));
+    record(rec, std::string("get_begin_rows_of_BMT_after_fixed_blocking_in_nnz_direction_relative_to_") + tag, id, ",nnz_per_BMT:" + std::to_string(k));
+}
+
+void get_begin_nzs_of_BMT_after_fixed_blocking_in_nnz_direction_relative_to_parent(meta_data_set &ms, POS_TYPE parent, int id, uint64_t k, recs *rec)
+{
+    GS_REQUIRE(k >= 1 && (parent == WARP_META || parent == TBLOCK_META), "bad argument");
+    const uint64_t nnz = ms.get(GLOBAL_META, "nz_row_indices", id).get_len();
+    const universal_array &PN = ms.get(parent, "first_nz_indices", id);
+    std::vector<uint64_t> v;
+    uint64_t p = 0;
+    for (uint64_t i = 0; i < nnz; i += k) {
+        GS_REQUIRE(p + 1 < PN.get_len(), "BMT beyond the last parent block");
+        if (i >= PN.u[p + 1]) p++;
+        GS_REQUIRE(i >= PN.u[p], "BMT starts above its parent's first non-zero");
+        v.push_back(i - PN.u[p]);
+    }
+    const char *tag = level_tag(parent);
+    ms.add_u(THREAD_META, std::string("first_nz_indices_relative_to_") + tag, id, std::move(v));
+    record(rec, std::string("get_begin_nzs_of_BMT_after_fixed_blocking_in_nnz_direction_relative_to_") + tag, id, ",nnz_per_BMT:" + std::to_string(k));
+}
+
+// get_BMW_size_of_each_parent.cc: one size per parent block (GLOBAL: one in all) when the BMWs of that parent hold the same nnz;
+// the first parent whose BMWs differ ends the step with no output and no record
+void get_BMW_size_of_each_parent(meta_data_set &ms, POS_TYPE parent, int id, recs *rec)
+{
+    if (parent == GLOBAL_META) return get_BMW_size_of_global(ms, id, rec);
+    GS_REQUIRE(parent == TBLOCK_META, "parent_pos must be GLOBAL_META or TBLOCK_META");
+    const universal_array &W = ms.get(WARP_META, "first_nz_indices", id), &P = ms.get(TBLOCK_META, "first_nz_indices", id);
+    GS_REQUIRE(W.get_len() >= 2 && W.u[0] == P.u[0] && W.u.back() == P.u.back(), "BMW and BMTB offsets do not span the same non-zeros");
+    std::vector<uint64_t> out;
+    uint64_t w = 0;
+    for (uint64_t b = 0; b + 1 < P.get_len(); b++) {
+        GS_REQUIRE(w < W.get_len() && W.u[w] == P.u[b], "BMW does not start at its BMTB's first non-zero");
+        uint64_t size = 0;
+        bool seen = false;
+        while (w + 1 < W.get_len() && W.u[w] < P.u[b + 1]) {
+            GS_REQUIRE(W.u[w + 1] > W.u[w], "empty BMW");
+            const uint64_t sz = W.u[w + 1] - W.u[w];
+            if (!seen) size = sz, seen = true;
+            else if (sz != size) return;
+            w++;
+        }
+        out.push_back(size);
+    }
+    GS_REQUIRE(w == W.get_len() - 1, "BMW offsets run past the last BMTB");
+    ms.add_u(TBLOCK_META, "BMW_size_of_each_blk", id, std::move(out));
+    record(rec, "get_BMW_size_of_each_parent", id, ",parent_pos:TBLOCK_META");
+}
+
+// ---------------------------------------------------------------------- balanced (nnz) blocking inside a parent level
+// data_transform_common.cc:794-931: the greedy >= rule restarts in every parent block and never cuts behind a parent's last row
+static void balanced_in_parent(const universal_array &PR, const universal_array *PN, const std::vector<uint64_t> &len, uint64_t per, bool relative, bool nzs, uint64_t row_num,
+                               std::vector<uint64_t> &out)
+{
+    for (uint64_t j = 0; j + 1 < PR.get_len(); j++) {
+        const uint64_t r0 = PR.u[j], r1 = PR.u[j + 1], nz0 = PN ? PN->u[j] : 0;
+        out.push_back(nzs ? (relative ? 0 : nz0) : (relative ? 0 : r0));
+        uint32_t count = 0; // `unsigned int nz_count` in the reference
+        uint64_t in_block = 0;
+        for (uint64_t i = r0; i < r1; i++) {
+            count += (uint32_t)len.at(i), in_block += len[i];
+            if (count >= per && i != r1 - 1) {
+                out.push_back(nzs ? (relative ? in_block : nz0 + in_block) : (relative ? i + 1 - r0 : i + 1));
+                count = 0;
+            }
+        }
+    }
+    if (!relative) out.push_back(nzs ? PN->u.back() : row_num);
+}
+
+void get_begin_rows_after_nnz_blocking_in_row_direction_in_parent(meta_data_set &ms, POS_TYPE pos, POS_TYPE parent, int id, uint64_t per, bool relative, recs *rec)
+{
+    GS_REQUIRE(per >= 1, "nnz_per_interval must be >= 1");
+    uint64_t row_num;
+    std::vector<uint64_t> len = row_nnz(ms, id, &row_num), v;
+    balanced_in_parent(ms.get(parent, "first_row_indices", id), nullptr, len, per, relative, false, row_num, v);
+    ms.add_u(pos, relative ? std::string("first_row_indices_relative_to_") + level_tag(parent) : std::string("first_row_indices"), id, std::move(v));
+    record(rec, std::string("get_begin_rows_of_") + level_tag(pos) + "_after_nnz_blocking_in_row_direction_" + (relative ? "relative_to_" : "in_") + level_tag(parent), id,
+           ",nnz_per_interval:" + std::to_string(per));
+}
+
+void get_begin_nzs_after_nnz_blocking_in_row_direction_in_parent(meta_data_set &ms, POS_TYPE pos, POS_TYPE parent, int id, uint64_t per, bool relative, recs *rec)
+{
+    GS_REQUIRE(per >= 1, "nnz_per_interval must be >= 1");
+    uint64_t row_num;
+    std::vector<uint64_t> len = row_nnz(ms, id, &row_num), v;
+    const universal_array &PR = ms.get(parent, "first_row_indices", id), &PN = ms.get(parent, "first_nz_indices", id);
+    GS_REQUIRE(PR.get_len() == PN.get_len(), "parent row and nz offsets differ in length");
+    balanced_in_parent(PR, &PN, len, per, relative, true, row_num, v);
+    ms.add_u(pos, relative ? std::string("first_nz_indices_relative_to_") + level_tag(parent) : std::string("first_nz_indices"), id, std::move(v));
+    record(rec, std::string("get_begin_nzs_of_") + level_tag(pos) + "_after_nnz_blocking_in_row_direction_" + (relative ? "relative_to_" : "in_") + level_tag(parent), id,
+           ",nnz_per_interval:" + std::to_string(per));
+}
+
+// ----------------------------------------------------------------------------------------------- interleaved storage
+// modify_{col_indices,vals,row_indices}_by_interlance_storage.cc: inside every parent block (GLOBAL: the whole stream) the BMTs, all of
+// one size, are stored element-interleaved: new[bmt + j * n_bmt + base] = old[j + bmt * size + base]; the originals stay
+void modify_by_interlance_storage(meta_data_set &ms, POS_TYPE parent_pos, int id, recs *rec)
+{
+    GS_REQUIRE(parent_pos == GLOBAL_META || parent_pos == TBLOCK_META || parent_pos == WARP_META, "parent_pos");
+    const universal_array &C = ms.get(GLOBAL_META, "nz_col_indices", id), &V = ms.get(GLOBAL_META, "nz_vals", id), &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    const universal_array &S = ms.get(parent_pos, "BMT_size_of_each_blk", id);
+    const uint64_t n = C.get_len();
+    std::vector<uint64_t> perm(n); // perm[new] = old
+    for (uint64_t i = 0; i < n; i++) perm[i] = i; // positions no block covers keep their element (the reference leaves zeros there: none exist for valid input)
+    auto block = [&](uint64_t base, uint64_t n_bmt, uint64_t size) {
+        GS_REQUIRE(base + n_bmt * size <= n, "interleave: BMTs run past the stream");
+        for (uint64_t b = 0; b < n_bmt; b++)
+            for (uint64_t j = 0; j < size; j++) perm[b + j * n_bmt + base] = j + b * size + base;
+    };
+    if (parent_pos == GLOBAL_META) {
+        const uint64_t size = S.u.at(0);
+        GS_REQUIRE(size > 0 && n % size == 0, "interleave: the stream is not a whole number of BMTs");
+        block(0, n / size, size);
+    } else {
+        const universal_array &FB = ms.get(parent_pos, "first_BMT_indices", id);
+        GS_REQUIRE(S.get_len() + 1 == FB.get_len(), "interleave: one BMT size per parent block expected");
+        uint64_t base = 0;
+        for (uint64_t p = 0; p + 1 < FB.get_len(); p++) {
+            const uint64_t n_bmt = FB.u[p + 1] - FB.u[p], size = S.u[p];
+            block(base, n_bmt, size);
+            base += n_bmt * size;
+        }
+        GS_REQUIRE(base == n, "interleave: the parent blocks do not cover the stream");
+    }
+    std::vector<uint64_t> nc(n), nr(n);
+    std::vector<double> nv(n);
+    for (uint64_t i = 0; i < n; i++) nc[i] = C.u[perm[i]], nr[i] = R.u[perm[i]], nv[i] = V.f[perm[i]];
+    const std::string pp = std::string(",parent_pos:") + pos_name(parent_pos);
+    ms.add_u(GLOBAL_META, "nz_col_indices_after_interlance_storage", id, std::move(nc));
+    record(rec, "modify_col_indices_by_interlance_storage", id, pp);
+    ms.add(GLOBAL_META, "nz_vals_after_interlance_storage", id, vals_like(V, std::move(nv)));
+    record(rec, "modify_vals_by_interlance_storage", id, pp);
+    ms.add_u(GLOBAL_META, "nz_row_indices_after_interlance_storage", id, std::move(nr));
+    record(rec, "modify_row_indices_by_interlance_storage", id, pp);
+}
+
+// ------------------------------------------------------------------------------------------------ sub-matrix division
+// meta_data_set::get_max_sub_matrix_id_of_data_item (metadata_set.cc:363-424)
+static int max_sub_matrix_id(const meta_data_set &ms, POS_TYPE pos, const std::string &name)
+{
+    const std::string prefix = std::string(pos_name(pos)) + "_" + name + "_";
+    int mx = -2;
+    for (const std::string &k : ms.keys()) {
+        if (k.compare(0, prefix.size(), prefix) != 0) continue;
+        const std::string rest = k.substr(prefix.size());
+        if (rest.empty() || rest.find_first_not_of("-0123456789") != std::string::npos) continue;
+        mx = std::max(mx, atoi(rest.c_str()));
+    }
+    GS_REQUIRE(mx != -2, "no item " + prefix + "*");
+    return mx;
+}
+
+// the 7 steps both division operators run, in the reference's order: row start, row end, col start, col end boundaries of every new
+// sub-matrix, then the column, value and row streams (each removes the parent's array).  `first_row[b]` = first row of part b (parts
+// ascending), `rebase`: store row indices relative to the part (fixed division) or as they are (division by row nnz, as the reference does)
+static void divide_rows(meta_data_set &ms, int id, const std::vector<uint64_t> &first_row, const std::vector<uint64_t> &last_row, const std::vector<bool> &has_boundary, bool rebase,
+                        const char *const names[7], const std::string &param, recs *rec)
+{
+    const uint64_t begin_row = ms.scalar(GLOBAL_META, "begin_row_index", id), begin_col = ms.scalar(GLOBAL_META, "begin_col_index", id), end_col = ms.scalar(GLOBAL_META, "end_col_index", id);
+    const std::vector<uint64_t> R = ms.get(GLOBAL_META, "nz_row_indices", id).u, C = ms.get(GLOBAL_META, "nz_col_indices", id).u;
+    const universal_array V = ms.get(GLOBAL_META, "nz_vals", id);
+    const size_t parts = first_row.size();
+    // part of every non-zero (rows ascending)
+    std::vector<std::vector<uint64_t>> pr(parts), pc(parts);
+    std::vector<std::vector<double>> pv(parts);
+    size_t b = 0;
+    for (uint64_t i = 0; i < R.size(); i++) {
+        while (b + 1 < parts && R[i] >= first_row[b + 1]) b++;
+        GS_REQUIRE(R[i] >= first_row[b], "division: non-zero above its part");
+        pr[b].push_back(rebase ? R[i] - first_row[b] : R[i]), pc[b].push_back(C[i]), pv[b].push_back(V.f[i]);
+    }
+    auto add_scalars = [&](const char *key, const char *step, auto value) {
+        for (size_t q = 0; q < parts; q++)
+            if (has_boundary[q]) ms.add_scalar(GLOBAL_META, key, max_sub_matrix_id(ms, GLOBAL_META, key) + 1, value(q));
+        record(rec, step, id, param);
+    };
+    add_scalars("begin_row_index", names[0], [&](size_t q) { return begin_row + first_row[q]; });
+    add_scalars("end_row_index", names[1], [&](size_t q) { return begin_row + last_row[q]; });
+    add_scalars("begin_col_index", names[2], [&](size_t) { return begin_col; });
+    add_scalars("end_col_index", names[3], [&](size_t) { return end_col; });
+    for (size_t q = 0; q < parts; q++)
+        if (!pc[q].empty()) ms.add_u(GLOBAL_META, "nz_col_indices", max_sub_matrix_id(ms, GLOBAL_META, "nz_col_indices") + 1, std::move(pc[q]));
+    ms.remove(GLOBAL_META, "nz_col_indices", id);
+    if (std::string(names[4]) == "fixed_div_col_indices_by_corr_row_indices") { // (sic) convert_to_string() of that step drops the "fixed_" before the "::"
+        if (rec) rec->push_back(std::string("div_col_indices_by_corr_row_indices::{name:\"") + names[4] + "\",target_matrix_id:" + std::to_string(id) + param + "}");
+    } else record(rec, names[4], id, param);
+    for (size_t q = 0; q < parts; q++)
+        if (!pv[q].empty()) ms.add(GLOBAL_META, "nz_vals", max_sub_matrix_id(ms, GLOBAL_META, "nz_vals") + 1, vals_like(V, std::move(pv[q])));
+    ms.remove(GLOBAL_META, "nz_vals", id);
+    record(rec, names[5], id, param);
+    for (size_t q = 0; q < parts; q++)
+        if (!pr[q].empty()) ms.add_u(GLOBAL_META, "nz_row_indices", max_sub_matrix_id(ms, GLOBAL_META, "nz_row_indices") + 1, std::move(pr[q]));
+    ms.remove(GLOBAL_META, "nz_row_indices", id);
+    record(rec, names[6], id, param);
+    // the reference asserts that every kind of item ends at the same sub-matrix id (operator run(), check == true)
+    const int m = max_sub_matrix_id(ms, GLOBAL_META, "end_row_index");
+    GS_REQUIRE(m == max_sub_matrix_id(ms, GLOBAL_META, "begin_row_index") && m == max_sub_matrix_id(ms, GLOBAL_META, "nz_row_indices") && m == max_sub_matrix_id(ms, GLOBAL_META, "nz_col_indices") &&
+                   m == max_sub_matrix_id(ms, GLOBAL_META, "nz_vals"),
+               "division: a part without non-zeros got boundaries but no arrays");
+}
+
+// fixed_interval_row_matrix_div_operator's steps (modify_*_boundary_after_fixed_div_in_row_direction.cc, fixed_div_*.cc): part s = rows
+// [s * gap, (s + 1) * gap); only parts that hold a non-zero become sub-matrices; row indices are stored modulo gap
+void fixed_div_in_row_direction(meta_data_set &ms, int id, uint64_t gap, recs *rec)
+{
+    GS_REQUIRE(gap >= 1, "fixed_row_gap_size must be >= 1");
+    const uint64_t begin_row = ms.scalar(GLOBAL_META, "begin_row_index", id), end_row = ms.scalar(GLOBAL_META, "end_row_index", id);
+    const uint64_t row_num = end_row - begin_row + 1, n_sub = (row_num + gap - 1) / gap;
+    std::vector<bool> used(n_sub, false);
+    for (uint64_t r : ms.get(GLOBAL_META, "nz_row_indices", id).u) {
+        GS_REQUIRE(r / gap < n_sub, "division: row index beyond end_row_index");
+        used[r / gap] = true;
+    }
+    std::vector<uint64_t> first, last;
+    for (uint64_t q = 0; q < n_sub; q++)
+        if (used[q]) first.push_back(q * gap), last.push_back(std::min((q + 1) * gap - 1, end_row - begin_row));
+    static const char *const names[7] = {"modify_row_start_boundary_after_fixed_div_in_row_direction", "modify_row_end_boundary_after_fixed_div_in_row_direction",
+                                         "modify_col_start_boundary_after_fixed_div_in_row_direction", "modify_col_end_boundary_after_fixed_div_in_row_direction",
+                                         "fixed_div_col_indices_by_corr_row_indices", "fixed_div_vals_by_corr_row_indices", "fixed_div_row_indices"};
+    divide_rows(ms, id, first, last, std::vector<bool>(first.size(), true), true, names, ",fixed_row_gap_size:" + std::to_string(gap), rec);
+}
+
+// row_nz_matrix_div_operator's steps (modify_*_boundary_after_div_according_to_row_nz.cc, div_*_by_row_nnz.cc): a new part starts at
+// every row whose nnz leaves the geometric window [low, low * expansion) the part opened with; windows start at [0, nz_gap) and stop
+// growing past max_gap.  Row indices keep their value (the reference does not rebase them here).
+std::vector<uint64_t> div_positions_by_row_nnz(const std::vector<uint64_t> &len, uint64_t nz_gap, uint64_t max_gap, uint64_t expansion)
+{
+    std::vector<uint64_t> pos;
+    if (len.empty()) return pos;
+    uint64_t lo = 0, hi = nz_gap;
+    auto window = [&](uint64_t nz) {
+        lo = 0, hi = nz_gap;
+        if (nz < max_gap) {
+            while (nz >= hi && hi <= max_gap) lo = hi, hi = hi * expansion;
+        } else lo = max_gap, hi = lo * expansion;
+    };
+    pos.push_back(0);
+    window(len[0]);
+    for (uint64_t r = 1; r < len.size(); r++) {
+        const uint64_t nz = len[r];
+        if ((nz >= lo && nz < hi) || (nz >= hi && hi > max_gap)) continue;
+        pos.push_back(r);
+        window(nz);
+    }
+    return pos;
+}
+
+void div_according_to_row_nz(meta_data_set &ms, int id, uint64_t nz_gap, uint64_t max_gap, uint64_t expansion, recs *rec)
+{
+    GS_REQUIRE(nz_gap >= 1 && expansion >= 1, "bad division parameters");
+    const uint64_t begin_row = ms.scalar(GLOBAL_META, "begin_row_index", id), end_row = ms.scalar(GLOBAL_META, "end_row_index", id);
+    const universal_array &R = ms.get(GLOBAL_META, "nz_row_indices", id);
+    const uint64_t row_num = end_row - begin_row + 1;
+    std::vector<uint64_t> len = get_nnz_of_each_row_in_spec_range(R, 0, row_num - 1, 0, R.get_len() - 1);
+    std::vector<uint64_t> first = div_positions_by_row_nnz(len, nz_gap, max_gap, expansion), last;
+    for (size_t q = 0; q < first.size(); q++) last.push_back((q + 1 < first.size() ? first[q + 1] : len.size()) - 1);
+    static const char *const names[7] = {"modify_row_start_boundary_after_div_according_to_row_nz", "modify_row_end_boundary_after_div_according_to_row_nz",
+                                         "modify_col_start_boundary_after_div_according_to_row_nz", "modify_col_end_boundary_after_div_according_to_row_nz",
+                                         "div_col_indices_by_row_nnz", "div_val_indices_by_row_nnz", "div_row_indices_by_row_nnz"};
+    // begin_row_index of a part is div_position itself, not begin_row + div_position (modify_row_start_boundary_after_div_according_to_row_nz.cc)
+    const uint64_t saved = begin_row;
+    if (saved != 0) ms.replace_u(GLOBAL_META, "begin_row_index", id, std::vector<uint64_t>{0});
+    try {
+        divide_rows(ms, id, first, last, std::vector<bool>(first.size(), true), false, names, ",nz_gap_size:" + std::to_string(nz_gap), rec);
+    } catch (...) {
+        if (saved != 0) ms.replace_u(GLOBAL_META, "begin_row_index", id, std::vector<uint64_t>{saved});
+        throw;
+    }
+    if (saved != 0) ms.replace_u(GLOBAL_META, "begin_row_index", id, std::vector<uint64_t>{saved});
+}
+
 void remove_item_of_metadata(meta_data_set &ms, int id, const std::string &name, POS_TYPE pos, recs *rec)
 {
     ms.remove(pos, name, id);

@@ -108,6 +108,21 @@ void get_begin_nzs_after_nnz_blocking_in_row_direction(meta_data_set &ms, POS_TY
 void get_begin_rows_of_level_after_merge_path(meta_data_set &ms, POS_TYPE pos, int id, uint64_t work_size, recs *rec = nullptr);
 void get_begin_nzs_of_level_after_merge_path(meta_data_set &ms, POS_TYPE pos, int id, uint64_t work_size, recs *rec = nullptr);
 
+// ---- child levels relative to their parent, one level up / other directions -------------------------
+void get_begin_rows_of_BMW_after_fixed_blocking_in_col_direction_relative_to_BMTB(meta_data_set &ms, int id, uint64_t col_size, recs *rec = nullptr);
+void get_begin_nzs_of_BMW_after_fixed_blocking_in_col_direction_relative_to_BMTB(meta_data_set &ms, int id, uint64_t col_size, recs *rec = nullptr);
+void get_begin_rows_of_BMT_after_fixed_blocking_in_nnz_direction_relative_to_parent(meta_data_set &ms, POS_TYPE parent, int id, uint64_t nnz_per_blk, recs *rec = nullptr);
+void get_begin_nzs_of_BMT_after_fixed_blocking_in_nnz_direction_relative_to_parent(meta_data_set &ms, POS_TYPE parent, int id, uint64_t nnz_per_blk, recs *rec = nullptr);
+void get_BMW_size_of_each_parent(meta_data_set &ms, POS_TYPE parent, int id, recs *rec = nullptr);
+// balanced (nnz) blocking inside a parent level: get_begin_{rows,nzs}_of_{BMT,BMW}_after_nnz_blocking_in_row_direction_{in,relative_to}_{BMW,BMTB}.cc
+void get_begin_rows_after_nnz_blocking_in_row_direction_in_parent(meta_data_set &ms, POS_TYPE pos, POS_TYPE parent, int id, uint64_t nnz_per_interval, bool relative, recs *rec = nullptr);
+void get_begin_nzs_after_nnz_blocking_in_row_direction_in_parent(meta_data_set &ms, POS_TYPE pos, POS_TYPE parent, int id, uint64_t nnz_per_interval, bool relative, recs *rec = nullptr);
+
+// ---- sub-matrix division (the 7 steps of fixed_interval_row_matrix_div_operator / row_nz_matrix_div_operator) --------
+void fixed_div_in_row_direction(meta_data_set &ms, int id, uint64_t fixed_row_gap_size, recs *rec = nullptr);
+std::vector<uint64_t> div_positions_by_row_nnz(const std::vector<uint64_t> &nnz_of_each_row, uint64_t nz_gap, uint64_t max_gap, uint64_t expansion);
+void div_according_to_row_nz(meta_data_set &ms, int id, uint64_t nz_gap_size, uint64_t max_gap, uint64_t expansion_rate, recs *rec = nullptr);
+
 // ---- interleave (modify_*_by_interlance_storage.cc) -------------------------------------------------
 void modify_by_interlance_storage(meta_data_set &ms, POS_TYPE parent_pos, int id, recs *rec = nullptr);
 

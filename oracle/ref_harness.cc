@@ -67,7 +67,7 @@ static void dump_all()
     FILE *idx = fopen((g_dump_dir + "/INDEX").c_str(), "w");
     for (POS_TYPE pos : k_pos)
         for (const char *name : k_names)
-            for (int id = -1; id <= 0; id++)
+            for (int id = -1; id <= 48; id++) // sub-matrix ids the division operators create
             {
                 if (!g_set->is_exist(pos, name, id))
                     continue;

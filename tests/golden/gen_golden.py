@@ -111,8 +111,58 @@ OPS_CASES = [
                        ("fixed_interval_nnz_direction_thread_blocking_operator", 8, 0, 0, 0)], 8),
 ]
 
+# round 2: the operators that were missing (column-direction blocking above the thread level, interleaved storage, the two sub-matrix
+# divisions, balanced blocking inside a parent level, nnz-direction BMT indices relative to their parent)
+OPS_CASES_R2 = [
+    ("col_tblock16", [("fixed_interval_col_direction_tblock_blocking_operator", 16, 0, 0)], 8),
+    ("col_tblock16_pad", [("fixed_interval_col_direction_tblock_blocking_operator", 16, 1, 0)], 8),
+    ("col_tblock4_maxpad", [("fixed_interval_col_direction_tblock_blocking_operator", 4, 0, 1)], 8),
+    ("col_warp8", [("fixed_interval_col_direction_warp_blocking_operator", 8, 0, 0, 0, 0)], 8),
+    ("col_warp8_pad", [("fixed_interval_col_direction_warp_blocking_operator", 8, 0, 0, 1, 0)], 8),
+    ("tb8_colwarp4_rel", [("fixed_interval_row_direction_tblock_blocking_operator", 8, 0),
+                          ("fixed_interval_col_direction_warp_blocking_operator", 4, 1, 1, 0, 0)], 8),
+    ("tb8_colwarp4_pad", [("fixed_interval_row_direction_tblock_blocking_operator", 8, 0),
+                          ("fixed_interval_col_direction_warp_blocking_operator", 4, 1, 1, 1, 0)], 8),
+    ("tb8_colwarp4_maxpad", [("fixed_interval_row_direction_tblock_blocking_operator", 8, 0),
+                             ("fixed_interval_col_direction_warp_blocking_operator", 4, 0, 0, 0, 1)], 8),
+    ("colwarp8_colthread", [("fixed_interval_col_direction_warp_blocking_operator", 8, 0, 0, 1, 0),
+                            ("fixed_interval_col_direction_thread_blocking_operator", 4, 0, 0, 1, 0)], 8),
+    ("col_thread8_pad_interlance", [("fixed_interval_col_direction_thread_blocking_operator", 8, 0, 0, 1, 0), ("interlance_storage_operator",)], 8),
+    ("tb8_colthread4_pad_interlance", [("fixed_interval_row_direction_tblock_blocking_operator", 8, 0),
+                                       ("fixed_interval_col_direction_thread_blocking_operator", 4, 0, 0, 1, 0), ("interlance_storage_operator",)], 8),
+    ("w2_t1_maxpad_interlance", [("fixed_interval_row_direction_warp_blocking_operator", 2, 0, 0, 0),
+                                 ("fixed_interval_row_direction_thread_blocking_operator", 1, 0, 0, 0, 1, 0, 0), ("interlance_storage_operator",)], 8),
+    ("t1_maxpad_interlance", [("fixed_interval_row_direction_thread_blocking_operator", 1, 0, 0, 0, 1, 0, 0), ("interlance_storage_operator",)], 8),
+    ("interlance_without_padding", [("fixed_interval_col_direction_thread_blocking_operator", 8, 0, 0, 0, 0), ("interlance_storage_operator",)], 8),
+    ("fixed_div16", [("fixed_interval_row_matrix_div_operator", 16)], 8),
+    ("fixed_div40", [("fixed_interval_row_matrix_div_operator", 40)], 8),
+    ("fixed_div_too_many", [("fixed_interval_row_matrix_div_operator", 3)], 8),
+    ("sort_rownz_div", [("sort_operator",), ("row_nz_matrix_div_operator", 2, 16, 2)], 8),
+    ("sort_rownz_div_4_64_4", [("sort_operator",), ("row_nz_matrix_div_operator", 4, 64, 4)], 8),
+    ("rownz_div_unsorted", [("row_nz_matrix_div_operator", 8, 64, 4)], 8),
+    ("tb16_balwarp40", [("fixed_interval_row_direction_tblock_blocking_operator", 16, 0),
+                        ("balanced_interval_row_direction_warp_blocking_operator", 40, 0, 0)], 8),
+    ("tb16_balwarp40_rel", [("fixed_interval_row_direction_tblock_blocking_operator", 16, 0),
+                            ("balanced_interval_row_direction_warp_blocking_operator", 40, 1, 1)], 8),
+    ("tb16_balwarp40_balthread9_rel", [("fixed_interval_row_direction_tblock_blocking_operator", 16, 0),
+                                       ("balanced_interval_row_direction_warp_blocking_operator", 40, 0, 0),
+                                       ("balanced_interval_row_direction_thread_blocking_operator", 9, 1, 1)], 8),
+    ("tb16_balthread12_rel", [("fixed_interval_row_direction_tblock_blocking_operator", 16, 0),
+                              ("balanced_interval_row_direction_thread_blocking_operator", 12, 1, 1)], 8),
+    ("baltb300_balthread30", [("balanced_interval_row_direction_tblock_blocking_operator", 300),
+                              ("balanced_interval_row_direction_thread_blocking_operator", 30, 0, 1)], 8),
+    ("nnz_tb128pad_w32_t8_rel", [("fixed_interval_nnz_direction_tblock_blocking_operator", 128, 1),
+                                 ("fixed_interval_nnz_direction_warp_blocking_operator", 32, 0, 0, 0),
+                                 ("fixed_interval_nnz_direction_thread_blocking_operator", 8, 1, 1, 0)], 8),
+    ("nnz_tb64pad_t8_rel", [("fixed_interval_nnz_direction_tblock_blocking_operator", 64, 1),
+                            ("fixed_interval_nnz_direction_thread_blocking_operator", 8, 1, 1, 0)], 8),
+]
+OPS_CASES = OPS_CASES + OPS_CASES_R2
+
 
 def ops_cases_for(mname):
+    if "--r2-only" in sys.argv:
+        return OPS_CASES_R2 if mname in ("tiny", "ragged") else []
     return OPS_CASES if mname in ("tiny", "ragged") else OPS_CASES[:2] + OPS_CASES[6:10] if mname == "ig5like" else OPS_CASES[:2]
 
 
