@@ -152,6 +152,12 @@ class Session:
             out.append(buf.value.decode())
         return out
 
+    def generate_final_program(self, repeat=10000):
+        """code_generator::generate_final_program: -> (id, directory) of the hand-off (one text file per array the kernel reads)"""
+        i, buf = C.c_uint64(), C.create_string_buffer(1024)
+        check(lib().gsh_session_generate_final_program(self._h, repeat, C.byref(i), buf, 1024))
+        return i.value, buf.value.decode()
+
     def plan_desc(self):
         d = PlanDesc()
         check(lib().gsh_session_plan_desc(self._h, C.byref(d)))
@@ -160,6 +166,13 @@ class Session:
     def deps(self):
         d = self.plan_desc()
         return [bytes(d.deps[i]).split(b"\0")[0].decode() for i in range(d.n_deps)]
+
+
+def execute_binary(execute_path, matrix_file, repeat=10000, kernel="auto"):
+    """execute_binary(path, matrix, &ms_total, &gflops) of executor.hpp:15 on a hand-off directory -> (ms_total, gflops)"""
+    ms, gf = C.c_float(), C.c_float()
+    check(lib().gs_execute_binary(execute_path.encode(), matrix_file.encode(), repeat, FAMILY_ID[kernel] if isinstance(kernel, str) else kernel, C.byref(ms), C.byref(gf)))
+    return ms.value, gf.value
 
 
 def partition_rows_balanced(row_nnz, G):

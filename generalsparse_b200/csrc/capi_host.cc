@@ -316,6 +316,16 @@ gs_status gsh_session_compile(gsh_session *s)
     GS_API_END
 }
 
+gs_status gsh_session_generate_final_program(gsh_session *s, unsigned int repeat, uint64_t *id_out, char *path_buf, size_t path_len)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(s && id_out, "null argument");
+    const unsigned long id = s->cg->generate_final_program(repeat);
+    *id_out = id;
+    if (path_buf) return copy_out(get_config().as_string("ROOT_PATH_STR") + "/data_source/" + std::to_string(id), path_buf, path_len);
+    GS_API_END
+}
+
 gs_status gsh_session_plan_desc(const gsh_session *s, gs_plan_desc *out)
 {
     GS_API_BEGIN

@@ -3,6 +3,11 @@
 #include "../../../include/gsparse_b200.h"
 
 #include <algorithm>
+#include <cerrno>
+#include <cstdlib>
+#include <ctime>
+#include <fstream>
+#include <sys/stat.h>
 
 namespace gs {
 
@@ -151,6 +156,28 @@ void code_generator::compile()
     p.stored_nnz = ms_->get(GLOBAL_META, "nz_col_indices", id_).get_len();
     plan_ = p;
     compiled_ = true;
+}
+
+unsigned long code_generator::generate_final_program(unsigned int repeat_num)
+{
+    GS_REQUIRE(repeat_num >= 1, "repeat_num must be >= 1");
+    if (!compiled_) compile();
+    // the directory id: rand() + time % 1000 in the reference (metadata_set.cc:529-530); any id not taken yet will do
+    const std::string root = get_config().as_string("ROOT_PATH_STR") + "/data_source";
+    mkdir(root.c_str(), 0755);
+    unsigned long id = (unsigned long)time(nullptr) % 1000 + (unsigned long)rand();
+    std::string dir;
+    for (;; id++) {
+        dir = root + "/" + std::to_string(id);
+        if (mkdir(dir.c_str(), 0755) == 0) break;
+        GS_REQUIRE(errno == EEXIST, "cannot create " + dir);
+    }
+    for (const metadata_dependency &d : plan_.deps) {
+        const std::string key = meta_data_set::item_name(d.pos, d.name, d.sub_matrix_id);
+        ms_->output_item_to_file(key, dir + "/" + key);
+    }
+    std::ofstream(dir + "/gs_repeat") << repeat_num << "\n"; // the reference bakes the count into the program text
+    return id;
 }
 
 // ---------------------------------------------------------------------------------- context / executer

@@ -65,6 +65,10 @@ class code_generator {
     void set_interleave_storage() { interleave_ = true; }                        // :209
     void add_new_metadata_dependency(POS_TYPE pos, const std::string &name, int id); // :66
     void compile();                                                              // :265
+    // :271-280: writes the arrays the kernel reads to ROOT_PATH_STR/data_source/<id>/ (one text file per array, the reference's hand-off,
+    // metadata_set.cc:517-571) and returns <id>; what the reference also writes there -- the generated program text -- has no counterpart:
+    // execute_binary() runs pre-built kernels on those files
+    unsigned long generate_final_program(unsigned int repeat_num);
     bool compiled() const { return compiled_; }
     const kernel_plan &plan() const;
     bool level_open(POS_TYPE pos) const { return open_[pos]; }
@@ -139,6 +143,10 @@ class operator_executer {
 std::shared_ptr<basic_operator> make_operator(const std::string &op_name, std::shared_ptr<code_generator> cg,
                                               std::shared_ptr<operator_context> history, const std::vector<int64_t> &args);
 const std::vector<std::string> &operator_names();
+
+// execute_binary (executor.hpp:15): the arrays of data_source/<id>/ and the matrix file -> B200 kernels (csrc/handoff.cc), timing and
+// GFLOP/s as code_generator.cc:582-624, the host check of :631-638; false on failure (the reference asserts)
+bool execute_binary(const std::string &execute_path, const std::string &filename, float &total_execute_time, float &gflops);
 
 // the driver's seven chains (token_test.cc:1003-1582)
 void run_family_chain(int family, std::shared_ptr<code_generator> cg, operator_executer &ex, int N, int sparse_coarsen, int coarsen);

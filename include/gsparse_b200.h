@@ -124,6 +124,11 @@ gs_status gsh_session_run_family(gsh_session *s, int family, int N, int sparse_c
  * code_generator.hpp:66). */
 gs_status gsh_session_compile(gsh_session *s);
 
+/* code_generator::generate_final_program(repeat) (code_generator.hpp:271-280): compiles if needed, writes the arrays the kernel reads to
+ * ROOT_PATH_STR/data_source/<id>/ as the reference does (one text file per array, metadata_set.cc:517-571) and returns <id>; path_buf
+ * (may be NULL) receives the directory.  gs_execute_binary() below runs it. */
+gs_status gsh_session_generate_final_program(gsh_session *s, unsigned int repeat, uint64_t *id_out, char *path_buf, size_t path_len);
+
 typedef struct gs_plan_desc {
     int32_t family;          /* gs_family */
     int32_t sub_matrix_id;
@@ -252,6 +257,14 @@ gs_status gs_plan_sp24_probe(const gs_plan *p, uint32_t *out512);
 /* execute_binary(path, matrix, &ms_total, &gflops) of executor.hpp:15 for an uploaded plan:
  * 1 warm-up + `repeat` launches, gflops = FLOAT_RATE*origin_nnz*N*repeat/t/1e9 (code_generator.cc:582-624) */
 gs_status gs_execute(gs_plan *p, int repeat, float *ms_total, float *gflops);
+
+/* execute_binary(execute_path, matrix_file, &ms_total, &gflops) of executor.hpp:15 / executor.cc:6-58, on the reference's own hand-off: the
+ * directory generate_final_program wrote (the reference's or gsh_session_generate_final_program's) holds one text file per array the
+ * kernel reads; the matrix file is read again for the shape and for the host check (code_generator.cc:631-638), N / HALF / VECTOR_WIDTH
+ * come from ./global_config.json as in the reference.  No compiler, no fork: the arrays go through gs_upload_array, `kernel` is a
+ * gs_family, GS_KERNEL_AUTO or GS_KERNEL_CHAIN.  Prints `correct` or `wrong number:<n>` like the generated program, writes perf_result
+ * into the directory, and returns GS_ERR_INTERNAL when the check fails.  `repeat` is used when the directory does not name one. */
+gs_status gs_execute_binary(const char *execute_path, const char *matrix_file, int repeat, int kernel, float *ms_total, float *gflops);
 
 /* ------------------------------------------------------------------ device: several GPUs ----- */
 /* The reference has no multi-GPU path (executor.hpp:15 hands one program to one device).  North star (3):
