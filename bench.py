@@ -57,6 +57,7 @@ def parse():
     ap.add_argument("--rows", type=int, default=10_000_000, help="c4: rows = cols of the power-law matrix")
     ap.add_argument("--avg-deg", type=float, default=20.0, help="c4: mean non-zeros per row")
     ap.add_argument("--family", default="thread_bit_map", help="c4: operator chain / kernel family")
+    ap.add_argument("--no-yardstick", action="store_true", help="skip the cuSPARSE yardstick (N=1 GPU only)")
     ap.add_argument("--no-c4", action="store_true", help="c2: leave the c4 block (strong scaling of the power-law matrix) out of the line")
     ap.add_argument("--c4-steps", type=int, default=20)
     ap.add_argument("--c4-kernel", default="auto", help="c4: auto = b200_nnz on the bit-map chains, reference = the chain's own family kernel, or a kernel name")
@@ -134,6 +135,30 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in inside)]
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(inside[0][1]), "reasons": reasons, "samples": len(inside)}
+
+
+def cusparse_yardstick(rows, cols, r, c, v, B_t, steps=200):
+    """the one external sanity bar the reference ships -- baseline/base_cusparse/spmm.cu:82-162, cusparseSpMM on CSR with
+    10 warm-ups, gflops = 2 * nnz * N / t -- here through torch's CSR matmul (cuSPARSE SpMM underneath; a library call, comparison only, never
+    on the product path).  B_t: K x N torch tensor on the device; values take its dtype."""
+    import torch
+    try:
+        crow = torch.from_numpy(np.concatenate([[0], np.cumsum(np.bincount(r, minlength=rows))]).astype(np.int32)).cuda()
+        A = torch.sparse_csr_tensor(crow, torch.from_numpy(c.astype(np.int32)).cuda(), torch.from_numpy(v).to(B_t.dtype).cuda(), size=(rows, cols))
+        for _ in range(10):
+            C = A @ B_t
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            C = A @ B_t
+        e1.record()
+        e1.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        return {"what": "cusparseSpMM, CSR, %s, through torch.sparse CSR @ dense (10 warm-ups, %d timed; baseline/base_cusparse/spmm.cu protocol)" % (str(B_t.dtype).replace("torch.", ""), steps),
+                "ms_per_step": ms, "value": 2.0 * len(r) * B_t.shape[1] / (ms * 1e-3) / 1e9, "unit": "GFLOP/s", "note": "one matrix, A stays in L2 between launches where it fits"}
+    except Exception as e:  # a yardstick must never break the line
+        return {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:200])}
 
 
 def run_reference(args, rank, world):
@@ -290,6 +315,11 @@ def c4_block(args, rank, world, local, dist):
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
     kname, launches = plan.kernel_name, steps * plan.launch_count
     del plan, C_full
+    yard = None
+    if world == 1 and not args.no_yardstick:
+        del eng
+        torch.cuda.empty_cache()
+        yard = cusparse_yardstick(my_rows, rows, r, c, v, torch.from_numpy(B).cuda(), steps=10)
     if rank != 0:
         return None
     ms_step = float(tmax[0].item()) / steps
@@ -306,7 +336,7 @@ def c4_block(args, rank, world, local, dist):
                          "note": "B and C counted once for the whole job; traffic = ncu dram bytes of one launch on 1 GPU (profiles/traffic.json, a committed capture)"},
             "parity": {"rows_checked_per_rank": checked, "includes_longest_row_of_every_block": True, "tolerance": "1e-5*|ref| + 1e-6*sum|a*b|", "worst_rel_err": float(-ok[2].item()),
                        "ok_on_every_rank": bool(ok[0].item() > 0.5)},
-            "clocks": clocks, "allgather": ag, "generate_s": round(gen_s, 1), "host_pipeline_s": round(host_pipeline_s, 1)}
+            "clocks": clocks, "allgather": ag, "yardstick_cusparse": yard, "generate_s": round(gen_s, 1), "host_pipeline_s": round(host_pipeline_s, 1)}
 
 
 def run_c4(args, rank, world, local):
@@ -493,6 +523,10 @@ def main():
         dist.all_reduce(nnz_all)
     nnz_all = float(nnz_all.item())
     alg_bytes, fmt_bytes, kernel_name, launch_count = plans[0].algorithmic_bytes, plans[0].format_bytes, plans[0].kernel_name, plans[0].launch_count
+    yard = None
+    if world == 1 and not args.no_yardstick:
+        yard = {"f16": cusparse_yardstick(my_rows, COLS, r, c, v, torch.from_numpy(B_host.numpy().copy()).cuda()),
+                "f32": cusparse_yardstick(my_rows, COLS, r, c, v, torch.from_numpy(B_host.numpy().astype(np.float32)).cuda())}
     c4 = None
     if not args.no_c4:
         del plans, C_hosts, eng, launch, e2e_fn, dep
@@ -533,7 +567,7 @@ def main():
                 "d2h_bytes_per_step": int(desc.rows * N * 2), "ms_per_step": e2e_s / e2e_steps * 1e3, "steps": e2e_steps,
                 "api": "gs_spmm_host_async per step (pinned B in, pinned C out) + one gs_synchronize; results equal the blocking call: %s" % e2e_ok,
                 "blocking_ms_per_step": e2e_sync_s / e2e_steps * 1e3, "host_enqueue_ms_per_step": e2e_enqueue_s / e2e_steps * 1e3},
-        "gpu_launches": args.steps * launch_count, "clocks": clocks, "parity": parity, "c4": c4,
+        "gpu_launches": args.steps * launch_count, "clocks": clocks, "parity": parity, "c4": c4, "yardstick_cusparse": yard,
     }
     if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1

@@ -31,7 +31,7 @@ SYMBOLS = [
 (GS_U8, GS_U16, GS_U32, GS_U64, GS_F32, GS_F64, GS_F16) = range(7)
 (GLOBAL_META, TBLOCK_META, WARP_META, THREAD_META) = range(4)
 FAMILIES = ["thread_total", "warp_total", "warp_bitmap", "thread_bit_map", "warp_segment", "block_total", "block_bitmap",
-            "b200_row_smem", "b200_tcgen05", "b200_nnz", "b200_sp24"]
+            "b200_row_smem", "b200_tcgen05", "b200_nnz", "b200_sp24", "b200_merge"]
 FAMILY_ID = {n: i for i, n in enumerate(FAMILIES)}
 FAMILY_ID["auto"] = -1  # GS_KERNEL_AUTO
 FAMILY_ID["chain"] = -2  # GS_KERNEL_CHAIN

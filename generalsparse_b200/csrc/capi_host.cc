@@ -73,7 +73,7 @@ const char *gs_version(void) { return "gsparse_b200 0.1 (sm_100a)"; }
 const char *gs_family_name(int f)
 {
     static const char *n[] = {"thread_total", "warp_total", "warp_bitmap", "thread_bit_map", "warp_segment",
-                              "block_total", "block_bitmap", "b200_row_smem", "b200_tcgen05", "b200_nnz", "b200_sp24"};
+                              "block_total", "block_bitmap", "b200_row_smem", "b200_tcgen05", "b200_nnz", "b200_sp24", "b200_merge"};
     return (f >= 0 && f < GS_FAMILY_COUNT) ? n[f] : "unknown";
 }
 

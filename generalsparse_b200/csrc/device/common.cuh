@@ -103,6 +103,19 @@ cudaError_t b200_sp24_probe(const b200_sp24_plan *plan, uint32_t *out512);
 
 // kernels_nnz.cu: warp-per-run kernel over the nnz-direction bit-map chains (no plan-time state)
 bool b200_nnz_supported(const launch_params &p);
-cudaError_t b200_nnz_launch(const launch_params &p, cudaStream_t s);
-const char *b200_nnz_kernel_name(const launch_params &p);
+struct b200_nnz_plan; // hot-column copy of the ids for matrices whose B does not fit L2 (may stay null)
+cudaError_t b200_nnz_prepare(const launch_params &p, b200_nnz_plan **out, cudaStream_t s);
+void b200_nnz_free(b200_nnz_plan *plan);
+cudaError_t b200_nnz_launch(const launch_params &p, const b200_nnz_plan *plan, cudaStream_t s);
+const char *b200_nnz_kernel_name(const launch_params &p, const b200_nnz_plan *plan);
+
+// kernels_merge.cu: range kernel over merge-path / balanced / column-direction chains
+struct b200_merge_plan;
+bool b200_merge_supported(int N);
+cudaError_t b200_merge_prepare(const launch_params &p, const uint32_t *parts_dev, uint32_t n_parts, const uint32_t *nz_rows_dev, const uint32_t *part_rows_dev, bool parts_are_rows,
+                               b200_merge_plan **out, cudaStream_t s);
+cudaError_t b200_merge_launch(const b200_merge_plan *plan, const launch_params &p, cudaStream_t s);
+void b200_merge_free(b200_merge_plan *plan);
+const char *b200_merge_kernel_name(const b200_merge_plan *plan);
+uint64_t b200_merge_bytes(const b200_merge_plan *plan, uint64_t nnz, uint64_t idx_bytes, uint64_t val_bytes, uint64_t rows, uint64_t cols);
 } // namespace gsd

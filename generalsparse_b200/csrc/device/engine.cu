@@ -80,6 +80,8 @@ struct gs_plan {
     gsd::b200_row_plan *row_plan = nullptr;
     gsd::b200_tile_plan *tile_plan = nullptr;
     gsd::b200_sp24_plan *sp24_plan = nullptr;
+    gsd::b200_merge_plan *merge_plan = nullptr;
+    gsd::b200_nnz_plan *nnz_plan = nullptr;
     void *B_dev = nullptr;  // owned
     const void *B_use = nullptr;
     void *C_dev = nullptr;
@@ -260,6 +262,14 @@ static void require_one_row_per_block(const gs_plan *p, const char *who)
     if (!fr || !fr->iota) throw gs::Error(std::string(who) + ": " + lvl + " first_row_indices is not 0, 1, 2, ...: the kernel needs one whole row per block (row-direction blocking, block size 1)");
 }
 
+// the reference-shaped total families reduce a block to one register per dense column and store it as ONE row (kernels_ref.cu): a block of
+// several rows (balanced blocking, row block > 1) needs the range kernel instead
+static void require_iota(const gs_plan *p, const char *lvl, const char *who)
+{
+    const dev_array *fr = find_arr(p->ctx, lvl, "first_row_indices", p->desc.sub_matrix_id);
+    if (fr && !fr->iota) throw gs::Error(std::string(who) + ": " + lvl + " first_row_indices is not 0, 1, 2, ...: a block of several rows cannot be stored as one row; use b200_merge (or auto)");
+}
+
 static void select_kernel(gs_plan *p, int family)
 {
     const gsd::dev_arrays &a = p->lp.a;
@@ -270,14 +280,17 @@ static void select_kernel(gs_plan *p, int family)
     switch (family) {
     case GS_FAMILY_THREAD_TOTAL:
         require(a.t_first_row && a.t_first_nz && !a.t_nz_relative, "THREAD first_row_indices/first_nz_indices");
+        require_iota(p, "THREAD_META", "thread_total");
         add("THREAD_META", "first_row_indices"), add("THREAD_META", "first_nz_indices");
         break;
     case GS_FAMILY_WARP_TOTAL:
         require(a.w_first_row && a.w_first_nz, "WARP first_row_indices/first_nz_indices");
+        require_iota(p, "WARP_META", "warp_total");
         add("WARP_META", "first_row_indices"), add("WARP_META", "first_nz_indices");
         break;
     case GS_FAMILY_TBLOCK_TOTAL:
         require(a.tb_first_row && a.tb_first_nz, "TBLOCK first_row_indices/first_nz_indices");
+        require_iota(p, "TBLOCK_META", "block_total");
         add("TBLOCK_META", "first_row_indices"), add("TBLOCK_META", "first_nz_indices");
         break;
     case GS_FAMILY_WARP_BITMAP:
@@ -333,6 +346,31 @@ static void select_kernel(gs_plan *p, int family)
         CUDA_TRY(e);
         break;
     }
+    case GS_FAMILY_B200_MERGE: {
+        if (p->merge_plan) gsd::b200_merge_free(p->merge_plan), p->merge_plan = nullptr;
+        // the finest level the chain built gives the ranges; the row pointer comes from nz_row_indices when the chain uploaded it (merge-path
+        // and balanced chains register it), from the row of every chunk on the column-direction chains (every chunk lies in one row), or
+        // from the ranges themselves when every block is one row
+        const char *lvl = find_arr(ctx, "THREAD_META", "first_nz_indices", id) ? "THREAD_META" : find_arr(ctx, "WARP_META", "first_nz_indices", id) ? "WARP_META" : "TBLOCK_META";
+        const dev_array *parts = find_arr(ctx, lvl, "first_nz_indices", id), *rows = find_arr(ctx, "GLOBAL_META", "nz_row_indices", id);
+        const dev_array *fr = find_arr(ctx, lvl, "first_row_indices", id), *frwe = find_arr(ctx, lvl, "first_row_indices_without_ending", id);
+        require(parts != nullptr && parts->len >= 2, "a first_nz_indices array at the thread, warp or tblock level");
+        GS_REQUIRE(parts->dtype == GS_U32 && (!rows || rows->dtype == GS_U32) && (!frwe || frwe->dtype == GS_U32), "b200_merge: unexpected device type of an offset array");
+        const bool col_dir = p->desc.family == GS_FAMILY_WARP_BITMAP || p->desc.family == GS_FAMILY_TBLOCK_BITMAP;
+        const uint32_t *part_rows = !rows && col_dir && frwe && frwe->len + 1 == parts->len ? (const uint32_t *)frwe->ptr : nullptr;
+        const bool parts_are_rows = !rows && !part_rows && fr && fr->iota;
+        if (!rows && !part_rows && !parts_are_rows)
+            throw gs::Error("b200_merge: needs GLOBAL nz_row_indices uploaded (merge-path and balanced chains register it), or a column-direction chain, or one row per block");
+        gsd::launch_params lp = p->lp;
+        lp.N = p->N;
+        cudaError_t e = gsd::b200_merge_prepare(lp, (const uint32_t *)parts->ptr, (uint32_t)(parts->len - 1), rows ? (const uint32_t *)rows->ptr : nullptr, part_rows, parts_are_rows, &p->merge_plan,
+                                                ctx->stream);
+        if (e == cudaErrorInvalidValue) throw gs::Error("b200_merge: needs N in {1,2,4,8,16} or a multiple of 32 up to 512, and offsets that cover the stream in order");
+        CUDA_TRY(e);
+        add(lvl, "first_nz_indices");
+        if (rows) add("GLOBAL_META", "nz_row_indices");
+        break;
+    }
     case GS_FAMILY_B200_NNZ: {
         require(a.t_first_row && a.t_first_nz && !a.t_nz_relative && a.t_bit_map && a.t_seg_ptr && a.t_seg_empty_flag && a.t_seg_empty_rows,
                 "THREAD first_row_indices/first_nz_indices/thread_bit_map/segment_ptr/segment_empty_flag/segment_empty_row_indices");
@@ -340,6 +378,8 @@ static void select_kernel(gs_plan *p, int family)
         gsd::launch_params lp = p->lp;
         lp.N = p->N;
         if (!gsd::b200_nnz_supported(lp)) throw gs::Error("b200_nnz: needs N in {32,64,128} and an nnz-direction bit-map chain (thread_bit_map / warp_segment)");
+        if (p->nnz_plan) gsd::b200_nnz_free(p->nnz_plan), p->nnz_plan = nullptr;
+        CUDA_TRY(gsd::b200_nnz_prepare(lp, &p->nnz_plan, ctx->stream));
         add("THREAD_META", "first_row_indices"), add("THREAD_META", "first_nz_indices"), add("THREAD_META", "thread_bit_map");
         add("THREAD_META", "segment_ptr"), add("THREAD_META", "segment_empty_flag"), add("THREAD_META", "segment_empty_row_indices");
         break;
@@ -413,6 +453,9 @@ static std::vector<auto_choice> auto_candidates(const gs_plan *p)
             double t = (nnz * (idxb + vb) + bc) / (0.70 * bw) * (panel ? 1.0 : 2.2);
             t = std::max(t, nnz * N / 18.8e6);
             if (mean_len < 64) t *= 1.0 + (64 - mean_len) / 64.0;
+            // short rows (one warp per row) with the panel in global memory: measured on the C1 stand-in (37 non-zeros per row, fp32):
+            // 26.7 us at N = 8, 148 us at N = 32 (profiles/r2_c1_kernels.log)
+            if (mean_len < 64 && !panel) t = std::max(t, nnz * N / (N <= 8 ? 0.54e6 : 0.39e6));
             c.push_back({GS_FAMILY_B200_ROW_SMEM, t + 2.5});
         }
         // the tensor-core layouts are built for weight-sized matrices: their host builders lay the whole rows x cols grid out before
@@ -443,8 +486,35 @@ static std::vector<auto_choice> auto_candidates(const gs_plan *p)
             c.push_back({GS_FAMILY_B200_SP24, t + 1.0});
         }
     }
+    if (gsd::b200_merge_supported(N) && (find_arr(ctx, "GLOBAL_META", "nz_row_indices", id) || row_chain || p->desc.family == GS_FAMILY_WARP_BITMAP || p->desc.family == GS_FAMILY_TBLOCK_BITMAP)) {
+        // range kernel: A streamed once at ~60 % of the HBM peak, B's rows gathered through L1/L2 (N * value bytes per non-zero); the only
+        // B200 kernel for merge-path / balanced / column-direction chains and for wide N on matrices too large for the tensor-core layouts
+        const double gather = nnz * N * vb, l2_bw = 2.5 * bw;
+        const bool b_in_l2 = cols * N * vb <= 96e6;
+        // a segment is walked serially by its lanes; non-zeros per microsecond measured on C5's 65 536^2 uniform matrix, fp32
+        // (profiles/r2_c5_sweep.md): 15 K at N = 1 (one lane per segment), 89 K at N = 8, 40 K at N = 32, 29 K at N = 128, 5.5 K at N = 512;
+        // fp16 values load 2 bytes per lane and run at about half of that from N = 16 up
+        static const double mn[] = {1, 2, 4, 8, 16, 32, 64, 128, 256, 512}, mr[] = {15e3, 29e3, 50e3, 89e3, 65e3, 40e3, 35.5e3, 28.6e3, 13.9e3, 5.5e3};
+        double rate = mr[9];
+        for (int i = 0; i < 10; i++)
+            if (N <= mn[i]) {
+                rate = mr[i];
+                break;
+            }
+        if (p->half && N >= 16) rate *= 0.5;
+        const double walk = nnz / rate;
+        c.push_back({GS_FAMILY_B200_MERGE, std::max({(nnz * (idxb + vb) + bc) / (0.60 * bw), gather / (b_in_l2 ? l2_bw : 0.9 * bw), walk}) + 3.0});
+    }
     if (bitmap_chain && (N == 32 || N == 64 || N == 128))
         c.push_back({GS_FAMILY_B200_NNZ, (nnz * (idxb + vb) + bc) / (0.25 * bw) + 3.0}); // bound by the gathers of B rows through L2
+    // the chain's own reference-shaped family competes where it was measured to win: narrow N on the row-parallel total chains (same
+    // sweep: thread_total 124 K non-zeros per us at N <= 2, 80 K at 4, 67 K at 8, halving per doubling of N; warp_total 170 K at N = 1,
+    // 155 K at 2, 76 K at 4)
+    if (row_chain && (p->desc.family == GS_FAMILY_THREAD_TOTAL || p->desc.family == GS_FAMILY_WARP_TOTAL)) {
+        const bool tt = p->desc.family == GS_FAMILY_THREAD_TOTAL;
+        const double r = tt ? (N <= 2 ? 124e3 : N <= 4 ? 80e3 : 67e3 * 8.0 / N) : (N <= 1 ? 170e3 : N <= 2 ? 155e3 : 76e3 * 4.0 / N);
+        c.push_back({p->desc.family, nnz / r + 3.0});
+    }
     std::sort(c.begin(), c.end(), [](const auto_choice &x, const auto_choice &y) { return x.us < y.us; });
     c.push_back({p->desc.family, 1e30});
     return c;
@@ -468,7 +538,7 @@ static void select_auto(gs_plan *p)
 static bool uses_atomics(int family)
 {
     return family == GS_FAMILY_WARP_BITMAP || family == GS_FAMILY_TBLOCK_BITMAP || family == GS_FAMILY_THREAD_BITMAP || family == GS_FAMILY_WARP_SEGMENT ||
-           family == GS_FAMILY_B200_NNZ;
+           family == GS_FAMILY_B200_NNZ || family == GS_FAMILY_B200_MERGE;
 }
 
 // which: 0 = ctx->stream, else one of gs_spmm_host_async's other launch streams
@@ -490,7 +560,8 @@ static void enqueue(gs_plan *p, int which = 0)
     if (p->kernel == GS_FAMILY_B200_ROW_SMEM) CUDA_TRY(gsd::b200_row_launch(p->row_plan, lp, st));
     else if (p->kernel == GS_FAMILY_B200_TCGEN05) CUDA_TRY(gsd::b200_tile_launch(p->tile_plan, lp, st));
     else if (p->kernel == GS_FAMILY_B200_SP24) CUDA_TRY(gsd::b200_sp24_launch(p->sp24_plan, lp, st));
-    else if (p->kernel == GS_FAMILY_B200_NNZ) CUDA_TRY(gsd::b200_nnz_launch(lp, st));
+    else if (p->kernel == GS_FAMILY_B200_NNZ) CUDA_TRY(gsd::b200_nnz_launch(lp, p->nnz_plan, st));
+    else if (p->kernel == GS_FAMILY_B200_MERGE) CUDA_TRY(gsd::b200_merge_launch(p->merge_plan, lp, st));
     else CUDA_TRY(gsd::launch_reference_family(p->kernel, lp, st));
     if (b200_chain) chain = true;
 }
@@ -572,6 +643,17 @@ gs_status gs_upload_session_as(gs_ctx *ctx, const gsh_session *s, int half, int 
         if (a.is_float()) upload(ctx, key, a.f.data(), a.f.size(), GS_F64, half);
         else upload(ctx, key, a.u.data(), a.u.size(), GS_U64, half);
     }
+    // the row of every stored non-zero travels too, whatever the chain registered: it is what lets the range kernel (b200_merge) run on
+    // any chain.  It is not one of the chain's kernel inputs, so SURVEY 8(d)'s algorithmic bytes do not count it.
+    {
+        const int sid = s->cg->get_sub_matrix_id();
+        bool listed = false;
+        for (const auto &d : kp.deps) listed = listed || d.name == "nz_row_indices";
+        if (!listed && s->ms->is_exist(GLOBAL_META, "nz_row_indices", sid)) {
+            const universal_array &a = s->ms->get(GLOBAL_META, "nz_row_indices", sid);
+            upload(ctx, meta_data_set::item_name(GLOBAL_META, "nz_row_indices", as_id >= 0 ? as_id : sid), a.u.data(), a.u.size(), GS_U64, half);
+        }
+    }
     GS_API_END
 }
 
@@ -619,6 +701,8 @@ void gs_plan_destroy(gs_plan *p)
     if (p->row_plan) gsd::b200_row_free(p->row_plan);
     if (p->tile_plan) gsd::b200_tile_free(p->tile_plan);
     if (p->sp24_plan) gsd::b200_sp24_free(p->sp24_plan);
+    if (p->merge_plan) gsd::b200_merge_free(p->merge_plan);
+    if (p->nnz_plan) gsd::b200_nnz_free(p->nnz_plan);
     if (p->B_dev) cudaFree(p->B_dev);
     if (p->C_dev) cudaFree(p->C_dev);
     if (p->ev0) cudaEventDestroy(p->ev0);
@@ -894,6 +978,7 @@ uint64_t gs_plan_format_bytes(const gs_plan *p)
     if (p->kernel == GS_FAMILY_B200_TCGEN05) return gsd::b200_tile_bytes(p->tile_plan, p->desc.rows, p->desc.cols);
     if (p->kernel == GS_FAMILY_B200_SP24) return gsd::b200_sp24_bytes(p->sp24_plan, p->desc.rows, p->desc.cols);
     uint64_t idx = p->lp.a.col_is_u16 ? 2 : 4;
+    if (p->kernel == GS_FAMILY_B200_MERGE) return gsd::b200_merge_bytes(p->merge_plan, p->lp.a.nnz, idx, p->esz(), p->desc.rows, p->desc.cols);
     return p->lp.a.nnz * (idx + p->esz()) + p->offset_bytes + (uint64_t)p->desc.cols * p->N * p->esz() + (uint64_t)p->desc.rows * p->N * p->esz();
 }
 
@@ -915,10 +1000,11 @@ const char *gs_plan_kernel_name(const gs_plan *p)
     if (p->kernel == GS_FAMILY_B200_ROW_SMEM) return gsd::b200_row_kernel_name(p->row_plan);
     if (p->kernel == GS_FAMILY_B200_TCGEN05) return gsd::b200_tile_kernel_name(p->tile_plan);
     if (p->kernel == GS_FAMILY_B200_SP24) return gsd::b200_sp24_kernel_name(p->sp24_plan);
+    if (p->kernel == GS_FAMILY_B200_MERGE) return gsd::b200_merge_kernel_name(p->merge_plan);
     if (p->kernel == GS_FAMILY_B200_NNZ) {
         gsd::launch_params lp = p->lp;
         lp.N = p->N;
-        return gsd::b200_nnz_kernel_name(lp);
+        return gsd::b200_nnz_kernel_name(lp, p->nnz_plan);
     }
     return gsd::reference_family_kernel_name(p->kernel);
 }

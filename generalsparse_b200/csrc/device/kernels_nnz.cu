@@ -16,8 +16,11 @@
 // L1/L2), not the A stream; see DESIGN.md section 4.4.
 #include "common.cuh"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <new>
+#include <vector>
 
 #include "../../../include/gsparse_b200.h"
 
@@ -30,14 +33,19 @@ constexpr int WARPS = 8;    // warps per CTA
 
 __device__ __forceinline__ uint32_t out_row(const dev_arrays &a, uint32_t row) { return a.perm ? a.perm[row] + a.begin_row : row + a.begin_row; }
 
+__device__ __forceinline__ void stg_policy(float *a, float v, uint64_t pol);
+__device__ __forceinline__ void stg_policy(__half *, float, uint64_t) {}
+
 template <typename ValT, int NV>
-__device__ __forceinline__ void flush_row(ValT *C, int N, uint32_t row, int lane, float (&acc)[NV], bool atomic)
+__device__ __forceinline__ void flush_row(ValT *C, int N, uint32_t row, int lane, float (&acc)[NV], bool atomic, uint64_t store_pol = 0)
 {
     ValT *dst = C + (size_t)row * N + lane;
 #pragma unroll
     for (int v = 0; v < NV; v++) {
         if (atomic) {
             if (acc[v] != 0.0f) atomic_add_out(dst, (size_t)(32 * v), acc[v]);
+        } else if (store_pol != 0 && sizeof(ValT) == 4) {
+            stg_policy(dst + 32 * v, acc[v], store_pol); // C is written once and never read: it must not displace B's popular rows
         } else {
             dst[32 * v] = from_f32<ValT>(acc[v]);
         }
@@ -45,8 +53,48 @@ __device__ __forceinline__ void flush_row(ValT *C, int N, uint32_t row, int lane
     }
 }
 
-template <typename ColT, typename ValT, int NV, int MINB, int GROUP> __global__ void __launch_bounds__(WARPS * 32, MINB) k_b200_nnz(launch_params p, const uint32_t run)
+// L2 residency control for matrices whose dense operand does not fit L2 (C4: B = 1.28 GB against 126 MB).  ncu on the plain kernel
+// (profiles/r2_c4_nnz_summary.md): 23.8 GB of DRAM traffic per launch for 4.28 GB of compulsory bytes, L2 read hit rate 12 % -- the
+// 24.6 GB of row gathers miss because the A stream, the C stores and the cold rows of B wash the popular rows out.  With HOT the plan
+// marks the columns that carry most non-zeros (bit 31 of the stored id, as many as fit GS_NNZ_HOT_MB of B) : their rows are loaded
+// with an evict_last policy, every other row and the streams with evict_first, so the popular rows stay.
+__device__ __forceinline__ uint64_t policy_evict_last()
 {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_first()
+{
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ float ldg_policy(const float *a, uint64_t pol)
+{
+    float x;
+    asm volatile("ld.global.nc.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(x) : "l"(a), "l"(pol));
+    return x;
+}
+__device__ __forceinline__ float ldg_policy_na(const float *a, uint64_t pol)
+{
+    float x;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(x) : "l"(a), "l"(pol));
+    return x;
+}
+__device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t *a, uint64_t pol)
+{
+    uint32_t x;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(x) : "l"(a), "l"(pol));
+    return x;
+}
+__device__ __forceinline__ void stg_policy(float *a, float v, uint64_t pol) { asm volatile("st.global.L2::cache_hint.f32 [%0], %1, %2;" ::"l"(a), "f"(v), "l"(pol) : "memory"); }
+
+template <typename ColT, typename ValT, int NV, int MINB, int GROUP, bool HOT = false> __global__ void __launch_bounds__(WARPS * 32, MINB) k_b200_nnz(launch_params p, const uint32_t run)
+{
+    static_assert(!HOT || (sizeof(ColT) == 4 && sizeof(ValT) == 4), "the hot-column variant is built for u32 ids and fp32 values");
+    uint64_t pol_last = 0, pol_first = 0;
+    if (HOT) pol_last = policy_evict_last(), pol_first = policy_evict_first();
     const dev_arrays &a = p.a;
     const int lane = threadIdx.x & 31;
     const uint32_t w = blockIdx.x * WARPS + (threadIdx.x >> 5);
@@ -79,20 +127,26 @@ template <typename ColT, typename ValT, int NV, int MINB, int GROUP> __global__ 
     uint32_t lo = __shfl_sync(0xffffffffu, m_fn, 0), hi = __shfl_sync(0xffffffffu, m_fn, 1);
     uint32_t c_cur = 0;
     float v_cur = 0.0f;
-    if (lo + lane < hi) c_cur = col[lo + lane], v_cur = to_f32(val[lo + lane]);
+    if (lo + lane < hi) {
+        if (HOT) c_cur = ldg_stream_u32((const uint32_t *)col + lo + lane, pol_first), v_cur = __uint_as_float(ldg_stream_u32((const uint32_t *)val + lo + lane, pol_first));
+        else c_cur = col[lo + lane], v_cur = to_f32(val[lo + lane]);
+    }
 
     for (uint32_t i = 0; i < nb; i++) {
         // request the next BMT's first 32 ids / values before multiplying this one
         uint32_t lo_n = hi, hi_n = __shfl_sync(0xffffffffu, m_fn, (i + 2) & 31);
         uint32_t c_nxt = 0;
         float v_nxt = 0.0f;
-        if (i + 1 < nb && lo_n + lane < hi_n) c_nxt = col[lo_n + lane], v_nxt = to_f32(val[lo_n + lane]);
+        if (i + 1 < nb && lo_n + lane < hi_n) {
+            if (HOT) c_nxt = ldg_stream_u32((const uint32_t *)col + lo_n + lane, pol_first), v_nxt = __uint_as_float(ldg_stream_u32((const uint32_t *)val + lo_n + lane, pol_first));
+            else c_nxt = col[lo_n + lane], v_nxt = to_f32(val[lo_n + lane]);
+        }
 
         const uint32_t map_lo = __shfl_sync(0xffffffffu, m_lo, i), map_hi = __shfl_sync(0xffffffffu, m_hi, i);
         const uint32_t frow = __shfl_sync(0xffffffffu, m_row, i);
         const bool gaps = __shfl_sync(0xffffffffu, m_gap, i) != 0;
         if (frow != row) { // the previous BMT ended its row exactly at the boundary
-            flush_row<ValT, NV>(C, N, out_row(a, row), lane, acc, edge);
+            flush_row<ValT, NV>(C, N, out_row(a, row), lane, acc, edge, pol_first);
             edge = false;
             row = frow;
         }
@@ -105,6 +159,13 @@ template <typename ColT, typename ValT, int NV, int MINB, int GROUP> __global__ 
 #pragma unroll
                 for (int j = 0; j < GROUP; j++) {
                     uint32_t c = __shfl_sync(0xffffffffu, c_cur, k0 + j);
+                    if (HOT) {
+                        const bool hot = (c >> 31) != 0; // warp-uniform: every lane holds the same id
+                        const float *src = (const float *)B + (size_t)(c & 0x7fffffffu) * N + lane;
+#pragma unroll
+                        for (int v = 0; v < NV; v++) x[j][v] = hot ? ldg_policy(src + 32 * v, pol_last) : ldg_policy_na(src + 32 * v, pol_first);
+                        continue;
+                    }
                     const ValT *src = B + (size_t)c * N + lane;
 #pragma unroll
                     for (int v = 0; v < NV; v++) x[j][v] = to_f32(__ldg(src + 32 * v));
@@ -114,7 +175,7 @@ template <typename ColT, typename ValT, int NV, int MINB, int GROUP> __global__ 
                     const int k = k0 + j;
                     float vv = __shfl_sync(0xffffffffu, v_cur, k);
                     if (k > 0 && ((map_lo >> k) & 1u)) {
-                        flush_row<ValT, NV>(C, N, out_row(a, row), lane, acc, edge);
+                        flush_row<ValT, NV>(C, N, out_row(a, row), lane, acc, edge, pol_first);
                         edge = false;
                         seg++;
                         row = gaps ? frow + a.t_seg_empty_rows[a.t_seg_ptr[b0 + i] + seg] : frow + seg;
@@ -128,13 +189,14 @@ template <typename ColT, typename ValT, int NV, int MINB, int GROUP> __global__ 
             for (uint32_t k = 0; k < cnt; k++) {
                 if (k == 32) { // BMTs wider than 32 non-zeros: the second half is loaded in place
                     c_cur = 0, v_cur = 0.0f;
-                    if (lo + 32 + lane < hi) c_cur = col[lo + 32 + lane], v_cur = to_f32(val[lo + 32 + lane]);
+                    if (lo + 32 + lane < hi) c_cur = (uint32_t)col[lo + 32 + lane], v_cur = to_f32(val[lo + 32 + lane]);
                 }
                 uint32_t c = __shfl_sync(0xffffffffu, c_cur, k & 31);
+                if (HOT) c &= 0x7fffffffu;
                 float vv = __shfl_sync(0xffffffffu, v_cur, k & 31);
                 const ValT *src = B + (size_t)c * N + lane;
                 if (k > 0 && ((map >> k) & 1ull)) {
-                    flush_row<ValT, NV>(C, N, out_row(a, row), lane, acc, edge);
+                    flush_row<ValT, NV>(C, N, out_row(a, row), lane, acc, edge, pol_first);
                     edge = false;
                     seg++;
                     row = gaps ? frow + a.t_seg_empty_rows[a.t_seg_ptr[b0 + i] + seg] : frow + seg;
@@ -155,7 +217,7 @@ unsigned nnz_run()
     return (unsigned)(r < 1 ? 1 : r > 31 ? 31 : r);
 }
 
-template <typename ColT, typename ValT> cudaError_t launch_nv(const launch_params &p, cudaStream_t s)
+template <typename ColT, typename ValT> cudaError_t launch_nv(const launch_params &p, cudaStream_t s, bool hot = false)
 {
     static const int occ = getenv("GS_NNZ_OCC") ? atoi(getenv("GS_NNZ_OCC")) : 0;     // timing experiments (N=32 only)
     static const int grp = getenv("GS_NNZ_GROUP") ? atoi(getenv("GS_NNZ_GROUP")) : 0;
@@ -163,6 +225,16 @@ template <typename ColT, typename ValT> cudaError_t launch_nv(const launch_param
     unsigned warps = (p.a.n_t + run - 1) / run;
     unsigned grid = (warps + WARPS - 1) / WARPS;
     if (grid == 0) return cudaSuccess;
+    if (hot) { // u32 ids with the hot bit, fp32 values (b200_nnz_prepare)
+        if (sizeof(ColT) != 4 || sizeof(ValT) != 4) return cudaErrorInvalidValue;
+        switch (p.N / 32) {
+        case 1: k_b200_nnz<uint32_t, float, 1, 5, 16, true><<<grid, WARPS * 32, 0, s>>>(p, run); break;
+        case 2: k_b200_nnz<uint32_t, float, 2, 3, 8, true><<<grid, WARPS * 32, 0, s>>>(p, run); break;
+        case 4: k_b200_nnz<uint32_t, float, 4, 2, 8, true><<<grid, WARPS * 32, 0, s>>>(p, run); break;
+        default: return cudaErrorInvalidValue;
+        }
+        return cudaGetLastError();
+    }
     switch (p.N / 32) {
     case 1:
         if (grp == 8) k_b200_nnz<ColT, ValT, 1, 5, 8><<<grid, WARPS * 32, 0, s>>>(p, run);
@@ -184,18 +256,79 @@ bool b200_nnz_supported(const launch_params &p)
     return p.N % 32 == 0 && (nv == 1 || nv == 2 || nv == 4);
 }
 
-cudaError_t b200_nnz_launch(const launch_params &p, cudaStream_t s)
+// Plan-time state of the hot-column variant: a copy of the column ids with bit 31 set on the columns that carry the most non-zeros, as many
+// as fit `GS_NNZ_HOT_MB` (default 72) megabytes of B.  Only built when B is larger than L2 can hold (else every row stays anyway), for
+// u32 ids and fp32 values; GS_NNZ_HOT=0 switches it off.  Returns cudaSuccess with *out == nullptr when the variant does not apply.
+struct b200_nnz_plan {
+    uint32_t *col_hot = nullptr;
+    uint64_t hot_cols = 0, hot_nnz = 0;
+};
+
+cudaError_t b200_nnz_prepare(const launch_params &p, b200_nnz_plan **out, cudaStream_t s)
 {
+    *out = nullptr;
+    static const int on = getenv("GS_NNZ_HOT") ? atoi(getenv("GS_NNZ_HOT")) : 1;
+    static const int mb = getenv("GS_NNZ_HOT_MB") ? atoi(getenv("GS_NNZ_HOT_MB")) : 72;
+    const uint64_t b_bytes = (uint64_t)p.a.cols * p.N * 4;
+    if (!on || p.a.col_is_u16 || p.a.val_is_f16 || b_bytes <= 96ull * 1000 * 1000 || p.a.cols >= 0x80000000u || p.a.nnz == 0) return cudaSuccess;
+    std::vector<uint32_t> col(p.a.nnz), cnt(p.a.cols, 0);
+    cudaError_t e = cudaMemcpyAsync(col.data(), p.a.col, p.a.nnz * 4, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return e;
+    for (uint32_t c : col) {
+        if (c >= p.a.cols) return cudaErrorInvalidValue;
+        cnt[c]++;
+    }
+    const uint64_t max_hot = (uint64_t)mb * 1000 * 1000 / ((uint64_t)p.N * 4);
+    if (max_hot == 0 || max_hot >= p.a.cols) return cudaSuccess;
+    std::vector<uint32_t> sorted(cnt);
+    std::nth_element(sorted.begin(), sorted.begin() + (sorted.size() - max_hot), sorted.end());
+    const uint32_t thr = std::max<uint32_t>(2u, sorted[sorted.size() - max_hot]); // a column used once gains nothing from staying
+    b200_nnz_plan *pl = new (std::nothrow) b200_nnz_plan;
+    if (!pl) return cudaErrorMemoryAllocation;
+    uint64_t budget = max_hot;
+    std::vector<uint8_t> hot(p.a.cols, 0);
+    for (uint32_t c = 0; c < p.a.cols && budget; c++)
+        if (cnt[c] > thr) hot[c] = 1, budget--, pl->hot_cols++;
+    for (uint32_t c = 0; c < p.a.cols && budget; c++)
+        if (cnt[c] == thr) hot[c] = 1, budget--, pl->hot_cols++;
+    for (uint32_t &c : col)
+        if (hot[c]) c |= 0x80000000u, pl->hot_nnz++;
+    if ((e = cudaMalloc((void **)&pl->col_hot, p.a.nnz * 4 + 16)) != cudaSuccess || (e = cudaMemcpyAsync(pl->col_hot, col.data(), p.a.nnz * 4, cudaMemcpyHostToDevice, s)) != cudaSuccess ||
+        (e = cudaStreamSynchronize(s)) != cudaSuccess) {
+        b200_nnz_free(pl);
+        return e;
+    }
+    *out = pl;
+    return cudaSuccess;
+}
+
+void b200_nnz_free(b200_nnz_plan *pl)
+{
+    if (!pl) return;
+    cudaFree(pl->col_hot);
+    delete pl;
+}
+
+cudaError_t b200_nnz_launch(const launch_params &p0, const b200_nnz_plan *pl, cudaStream_t s)
+{
+    launch_params p = p0;
     if (!b200_nnz_supported(p)) return cudaErrorInvalidValue;
+    if (pl && pl->col_hot) {
+        p.a.col = pl->col_hot;
+        return launch_nv<uint32_t, float>(p, s, true);
+    }
     if (p.a.col_is_u16) return p.a.val_is_f16 ? launch_nv<uint16_t, __half>(p, s) : launch_nv<uint16_t, float>(p, s);
     return p.a.val_is_f16 ? launch_nv<uint32_t, __half>(p, s) : launch_nv<uint32_t, float>(p, s);
 }
 
-const char *b200_nnz_kernel_name(const launch_params &p)
+const char *b200_nnz_kernel_name(const launch_params &p, const b200_nnz_plan *pl)
 {
-    static thread_local char name[96];
-    snprintf(name, sizeof name, "k_b200_nnz<N%d,%s,%s,run %d BMTs/warp,%d gathers in flight>", p.N, p.a.col_is_u16 ? "u16" : "u32",
-             p.a.val_is_f16 ? "f16" : "f32", (int)nnz_run(), p.N == 32 ? 16 : 8);
+    static thread_local char name[160];
+    char hot[80] = "";
+    if (pl && pl->col_hot) snprintf(hot, sizeof hot, ",L2 evict_last on %llu hot columns (%.0f%% of the gathers)", (unsigned long long)pl->hot_cols, 100.0 * (double)pl->hot_nnz / (double)p.a.nnz);
+    snprintf(name, sizeof name, "k_b200_nnz<N%d,%s,%s,run %d BMTs/warp,%d gathers in flight%s>", p.N, p.a.col_is_u16 ? "u16" : "u32",
+             p.a.val_is_f16 ? "f16" : "f32", (int)nnz_run(), p.N == 32 ? 16 : 8, hot);
     return name;
 }
 

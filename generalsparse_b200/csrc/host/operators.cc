@@ -79,7 +79,27 @@ void code_generator::compile()
     p.has_row_permutation = ms_->is_exist(GLOBAL_META, "original_nz_row_indices", id_);
     if (p.has_row_permutation) dep(GLOBAL_META, "original_nz_row_indices");
 
-    if (b.kind == RED_TOTAL_TBLOCK && w.kind == RED_NONE && t.kind == RED_NONE) {
+    // a total reduction over blocks that are not one row each -- merge-path parts (first_row_indices_without_ending only), nnz-balanced row
+    // groups, row blocks of several rows -- has no reference-shaped kernel (those store a block's sum as one row): the range kernel
+    // takes the level's first_nz_indices as ranges and needs the row of every non-zero
+    auto one_row_per_block = [&](POS_TYPE pos) {
+        if (!ms_->is_exist(pos, "first_row_indices", id_)) return false;
+        const std::vector<uint64_t> &fr = ms_->get(pos, "first_row_indices", id_).u;
+        for (uint64_t i = 0; i < fr.size(); i++)
+            if (fr[i] != i) return false;
+        return true;
+    };
+    const POS_TYPE total_level = (t.kind == RED_TOTAL_BMT && w.kind == RED_NONE && b.kind == RED_NONE) ? THREAD_META
+                                 : (w.kind == RED_TOTAL_WARP && t.kind == RED_NONE)                     ? WARP_META
+                                 : (b.kind == RED_TOTAL_TBLOCK && w.kind == RED_NONE && t.kind == RED_NONE) ? TBLOCK_META
+                                                                                                         : NONE_META;
+    if (total_level != NONE_META && ms_->is_exist(total_level, "first_nz_indices", id_) && !one_row_per_block(total_level)) {
+        p.family = GS_FAMILY_B200_MERGE;
+        p.coarsen = total_level == THREAD_META ? t.coarsen_factor : total_level == WARP_META ? w.coarsen_factor : b.coarsen_factor;
+        dep(GLOBAL_META, "nz_row_indices");
+        dep(total_level, "first_nz_indices");
+        dep(total_level, ms_->is_exist(total_level, "first_row_indices", id_) ? "first_row_indices" : "first_row_indices_without_ending");
+    } else if (b.kind == RED_TOTAL_TBLOCK && w.kind == RED_NONE && t.kind == RED_NONE) {
         p.family = GS_FAMILY_TBLOCK_TOTAL;
         p.coarsen = b.coarsen_factor;
         dep(TBLOCK_META, "first_row_indices");

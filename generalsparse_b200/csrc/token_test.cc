@@ -6,6 +6,9 @@
 // default here too.  Extra flags after the two positionals:
 //   --family <thread_total|warp_total|warp_bitmap|thread_bit_map|warp_segment|block_total|block_bitmap>
 //   --sparse-coarsen S  --coarsen C   the two integers every test_spmm_* takes
+//   --ops "<operator>[,<arg>...];..." instead of a driver chain: any sequence of the reference's operators by class name (operator.hpp; arguments
+//                                     = the constructor's, after code_generator_ptr, booleans as 0/1), run through operator_executer::add_and_run,
+//                                     e.g. "sort_operator;merge_path_thread_operator,64;thread_total_reduce_operator,0,1,1;grid_block_operator,64,8,16,1"
 //   --kernel <auto|reference|b200_row_smem|b200_tcgen05|b200_sp24|b200_nnz>
 //                                     auto (default): the library picks the B200 kernel for the chain, the matrix and N
 //                                     (gs_plan_set_kernel(GS_KERNEL_AUTO)); reference: the chain's own reference-shaped family
@@ -70,7 +73,7 @@ int main(int argc, char **argv)
     }
     std::string mtx = argv[1];
     int N = atoi(argv[2]);
-    std::string family = "thread_total", kernel, dump;
+    std::string family = "thread_total", kernel, dump, ops;
     int S = 4, C = 1, repeat = 10000;
     bool half = false, values = false, parity = true, corrupt = false, allgather = false;
     int gpus = 1;
@@ -81,6 +84,7 @@ int main(int argc, char **argv)
         else if (a == "--sparse-coarsen") S = atoi(next());
         else if (a == "--coarsen") C = atoi(next());
         else if (a == "--kernel") kernel = next();
+        else if (a == "--ops") ops = next();
         else if (a == "--half") half = true;
         else if (a == "--values") values = true;
         else if (a == "--repeat") repeat = atoi(next());
@@ -185,7 +189,32 @@ int main(int argc, char **argv)
     }
     gsh_session *s = nullptr;
     OK(gsh_session_create(ms, 0, &s));
-    OK(gsh_session_run_family(s, fam, N, S, C));
+    if (ops.empty()) OK(gsh_session_run_family(s, fam, N, S, C));
+    else {
+        char num[32];
+        snprintf(num, sizeof num, "%d", N);
+        OK(gsh_config_set("DENSE_MATRIX_SIZE", num)); // token_test.cc:1630
+        snprintf(num, sizeof num, "%d", N < 32 ? N : 32);
+        OK(gsh_config_set("VECTOR_WIDTH", num));
+        size_t pos = 0;
+        while (pos < ops.size()) {
+            size_t end = ops.find(';', pos);
+            if (end == std::string::npos) end = ops.size();
+            std::string item = ops.substr(pos, end - pos);
+            pos = end + 1;
+            if (item.empty()) continue;
+            std::vector<int64_t> args;
+            size_t c0 = item.find(',');
+            std::string name = item.substr(0, c0);
+            while (c0 != std::string::npos) {
+                size_t c1 = item.find(',', c0 + 1);
+                args.push_back(atoll(item.substr(c0 + 1, c1 == std::string::npos ? std::string::npos : c1 - c0 - 1).c_str()));
+                c0 = c1;
+            }
+            OK(gsh_session_add_and_run(s, name.c_str(), args.empty() ? nullptr : args.data(), (int)args.size()));
+        }
+        OK(gsh_session_compile(s));
+    }
     for (uint64_t i = 0; i < gsh_session_record_count(s); i++) {
         char buf[1024];
         if (gsh_session_record(s, i, buf, sizeof buf) == GS_OK) printf("%s\n", buf);

@@ -52,7 +52,8 @@ typedef enum gs_family {
     GS_FAMILY_B200_TCGEN05 = 8,  /* sparse-tile decompress to shared memory + tcgen05.mma with TMEM accumulators */
     GS_FAMILY_B200_NNZ = 9,      /* warp-per-run kernel for the nnz-direction bit-map chains (thread_bit_map / warp_segment), N % 32 == 0 */
     GS_FAMILY_B200_SP24 = 10,    /* 2:4 sparse tensor cores: tcgen05.mma.sp over a pre-laid-out image, what the pattern cannot hold goes to a gather pass */
-    GS_FAMILY_COUNT = 11
+    GS_FAMILY_B200_MERGE = 11,   /* range kernel: merge-path parts, nnz-balanced row groups, column-direction chunks, row blocks > 1 row; N in {1,2,4,8,16} or 32k <= 512 */
+    GS_FAMILY_COUNT = 12
 } gs_family;
 /* gs_plan_set_kernel(plan, GS_KERNEL_AUTO): the library picks the kernel for (chain, matrix, N, value type) from a cost model of the
  * measured rates -- the slice of the reference's unbuilt calculation_method_choose_operator (README.md:36, "under development") this
