@@ -58,6 +58,9 @@ __device__ __forceinline__ void flush_row(ValT *C, int N, uint32_t row, int lane
 // 24.6 GB of row gathers miss because the A stream, the C stores and the cold rows of B wash the popular rows out.  With HOT the plan
 // marks the columns that carry most non-zeros (bit 31 of the stored id, as many as fit GS_NNZ_HOT_MB of B) : their rows are loaded
 // with an evict_last policy, every other row and the streams with evict_first, so the popular rows stay.
+// MEASURED on C4, one B200 (profiles/r2_c4_nnz_summary.md): plain kernel 5.36 ms; GS_NNZ_HOT=1 (evict_first on the A, metadata and C streams
+// only) 6.26 ms; GS_NNZ_HOT=2 (that + evict_last / evict_first per gathered row, 31 % of the gathers marked hot) 7.58-7.86 ms whatever the
+// size of the hot set.  The hardware's own replacement does better than either hint, so both stay opt-in experiments.
 __device__ __forceinline__ uint64_t policy_evict_last()
 {
     uint64_t p;
@@ -90,7 +93,7 @@ __device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t *a, uint64_t p
 }
 __device__ __forceinline__ void stg_policy(float *a, float v, uint64_t pol) { asm volatile("st.global.L2::cache_hint.f32 [%0], %1, %2;" ::"l"(a), "f"(v), "l"(pol) : "memory"); }
 
-template <typename ColT, typename ValT, int NV, int MINB, int GROUP, bool HOT = false> __global__ void __launch_bounds__(WARPS * 32, MINB) k_b200_nnz(launch_params p, const uint32_t run)
+template <typename ColT, typename ValT, int NV, int MINB, int GROUP, int HOT = 0> __global__ void __launch_bounds__(WARPS * 32, MINB) k_b200_nnz(launch_params p, const uint32_t run)
 {
     static_assert(!HOT || (sizeof(ColT) == 4 && sizeof(ValT) == 4), "the hot-column variant is built for u32 ids and fp32 values");
     uint64_t pol_last = 0, pol_first = 0;
@@ -159,11 +162,11 @@ template <typename ColT, typename ValT, int NV, int MINB, int GROUP, bool HOT = 
 #pragma unroll
                 for (int j = 0; j < GROUP; j++) {
                     uint32_t c = __shfl_sync(0xffffffffu, c_cur, k0 + j);
-                    if (HOT) {
-                        const bool hot = (c >> 31) != 0; // warp-uniform: every lane holds the same id
+                    if (HOT == 2) { // one load instruction, the policy picked per id (no branch: the gathers of a group stay in flight together)
+                        const uint64_t pol = (c >> 31) ? pol_last : pol_first;
                         const float *src = (const float *)B + (size_t)(c & 0x7fffffffu) * N + lane;
 #pragma unroll
-                        for (int v = 0; v < NV; v++) x[j][v] = hot ? ldg_policy(src + 32 * v, pol_last) : ldg_policy_na(src + 32 * v, pol_first);
+                        for (int v = 0; v < NV; v++) x[j][v] = ldg_policy(src + 32 * v, pol);
                         continue;
                     }
                     const ValT *src = B + (size_t)c * N + lane;
@@ -192,7 +195,7 @@ template <typename ColT, typename ValT, int NV, int MINB, int GROUP, bool HOT = 
                     if (lo + 32 + lane < hi) c_cur = (uint32_t)col[lo + 32 + lane], v_cur = to_f32(val[lo + 32 + lane]);
                 }
                 uint32_t c = __shfl_sync(0xffffffffu, c_cur, k & 31);
-                if (HOT) c &= 0x7fffffffu;
+                if (HOT == 2) c &= 0x7fffffffu;
                 float vv = __shfl_sync(0xffffffffu, v_cur, k & 31);
                 const ValT *src = B + (size_t)c * N + lane;
                 if (k > 0 && ((map >> k) & 1ull)) {
@@ -217,7 +220,7 @@ unsigned nnz_run()
     return (unsigned)(r < 1 ? 1 : r > 31 ? 31 : r);
 }
 
-template <typename ColT, typename ValT> cudaError_t launch_nv(const launch_params &p, cudaStream_t s, bool hot = false)
+template <typename ColT, typename ValT> cudaError_t launch_nv(const launch_params &p, cudaStream_t s, int hot = 0)
 {
     static const int occ = getenv("GS_NNZ_OCC") ? atoi(getenv("GS_NNZ_OCC")) : 0;     // timing experiments (N=32 only)
     static const int grp = getenv("GS_NNZ_GROUP") ? atoi(getenv("GS_NNZ_GROUP")) : 0;
@@ -228,9 +231,18 @@ template <typename ColT, typename ValT> cudaError_t launch_nv(const launch_param
     if (hot) { // u32 ids with the hot bit, fp32 values (b200_nnz_prepare)
         if (sizeof(ColT) != 4 || sizeof(ValT) != 4) return cudaErrorInvalidValue;
         switch (p.N / 32) {
-        case 1: k_b200_nnz<uint32_t, float, 1, 5, 16, true><<<grid, WARPS * 32, 0, s>>>(p, run); break;
-        case 2: k_b200_nnz<uint32_t, float, 2, 3, 8, true><<<grid, WARPS * 32, 0, s>>>(p, run); break;
-        case 4: k_b200_nnz<uint32_t, float, 4, 2, 8, true><<<grid, WARPS * 32, 0, s>>>(p, run); break;
+        case 1:
+            if (hot == 2) k_b200_nnz<uint32_t, float, 1, 5, 16, 2><<<grid, WARPS * 32, 0, s>>>(p, run);
+            else k_b200_nnz<uint32_t, float, 1, 5, 16, 1><<<grid, WARPS * 32, 0, s>>>(p, run);
+            break;
+        case 2:
+            if (hot == 2) k_b200_nnz<uint32_t, float, 2, 3, 8, 2><<<grid, WARPS * 32, 0, s>>>(p, run);
+            else k_b200_nnz<uint32_t, float, 2, 3, 8, 1><<<grid, WARPS * 32, 0, s>>>(p, run);
+            break;
+        case 4:
+            if (hot == 2) k_b200_nnz<uint32_t, float, 4, 2, 8, 2><<<grid, WARPS * 32, 0, s>>>(p, run);
+            else k_b200_nnz<uint32_t, float, 4, 2, 8, 1><<<grid, WARPS * 32, 0, s>>>(p, run);
+            break;
         default: return cudaErrorInvalidValue;
         }
         return cudaGetLastError();
@@ -260,6 +272,7 @@ bool b200_nnz_supported(const launch_params &p)
 // as fit `GS_NNZ_HOT_MB` (default 72) megabytes of B.  Only built when B is larger than L2 can hold (else every row stays anyway), for
 // u32 ids and fp32 values; GS_NNZ_HOT=0 switches it off.  Returns cudaSuccess with *out == nullptr when the variant does not apply.
 struct b200_nnz_plan {
+    int mode = 0; // 1: the streams (A, metadata, C) carry an evict_first policy; 2: and B's rows evict_last on the hot columns, evict_first elsewhere
     uint32_t *col_hot = nullptr;
     uint64_t hot_cols = 0, hot_nnz = 0;
 };
@@ -267,10 +280,17 @@ struct b200_nnz_plan {
 cudaError_t b200_nnz_prepare(const launch_params &p, b200_nnz_plan **out, cudaStream_t s)
 {
     *out = nullptr;
-    static const int on = getenv("GS_NNZ_HOT") ? atoi(getenv("GS_NNZ_HOT")) : 1;
+    static const int on = getenv("GS_NNZ_HOT") ? atoi(getenv("GS_NNZ_HOT")) : 0; // off by default: both modes measured SLOWER on C4 (see below)
     static const int mb = getenv("GS_NNZ_HOT_MB") ? atoi(getenv("GS_NNZ_HOT_MB")) : 72;
     const uint64_t b_bytes = (uint64_t)p.a.cols * p.N * 4;
     if (!on || p.a.col_is_u16 || p.a.val_is_f16 || b_bytes <= 96ull * 1000 * 1000 || p.a.cols >= 0x80000000u || p.a.nnz == 0) return cudaSuccess;
+    if (on == 1) { // streams only: no copy of the ids
+        b200_nnz_plan *pl1 = new (std::nothrow) b200_nnz_plan;
+        if (!pl1) return cudaErrorMemoryAllocation;
+        pl1->mode = 1;
+        *out = pl1;
+        return cudaSuccess;
+    }
     std::vector<uint32_t> col(p.a.nnz), cnt(p.a.cols, 0);
     cudaError_t e = cudaMemcpyAsync(col.data(), p.a.col, p.a.nnz * 4, cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
@@ -286,6 +306,7 @@ cudaError_t b200_nnz_prepare(const launch_params &p, b200_nnz_plan **out, cudaSt
     const uint32_t thr = std::max<uint32_t>(2u, sorted[sorted.size() - max_hot]); // a column used once gains nothing from staying
     b200_nnz_plan *pl = new (std::nothrow) b200_nnz_plan;
     if (!pl) return cudaErrorMemoryAllocation;
+    pl->mode = 2;
     uint64_t budget = max_hot;
     std::vector<uint8_t> hot(p.a.cols, 0);
     for (uint32_t c = 0; c < p.a.cols && budget; c++)
@@ -314,10 +335,11 @@ cudaError_t b200_nnz_launch(const launch_params &p0, const b200_nnz_plan *pl, cu
 {
     launch_params p = p0;
     if (!b200_nnz_supported(p)) return cudaErrorInvalidValue;
-    if (pl && pl->col_hot) {
+    if (pl && pl->mode == 2 && pl->col_hot) {
         p.a.col = pl->col_hot;
-        return launch_nv<uint32_t, float>(p, s, true);
+        return launch_nv<uint32_t, float>(p, s, 2);
     }
+    if (pl && pl->mode == 1 && !p.a.col_is_u16 && !p.a.val_is_f16) return launch_nv<uint32_t, float>(p, s, 1);
     if (p.a.col_is_u16) return p.a.val_is_f16 ? launch_nv<uint16_t, __half>(p, s) : launch_nv<uint16_t, float>(p, s);
     return p.a.val_is_f16 ? launch_nv<uint32_t, __half>(p, s) : launch_nv<uint32_t, float>(p, s);
 }
@@ -326,7 +348,8 @@ const char *b200_nnz_kernel_name(const launch_params &p, const b200_nnz_plan *pl
 {
     static thread_local char name[160];
     char hot[80] = "";
-    if (pl && pl->col_hot) snprintf(hot, sizeof hot, ",L2 evict_last on %llu hot columns (%.0f%% of the gathers)", (unsigned long long)pl->hot_cols, 100.0 * (double)pl->hot_nnz / (double)p.a.nnz);
+    if (pl && pl->mode == 1) snprintf(hot, sizeof hot, ",L2 evict_first on the A, metadata and C streams");
+    if (pl && pl->mode == 2 && pl->col_hot) snprintf(hot, sizeof hot, ",L2 evict_last on %llu hot columns (%.0f%% of the gathers)", (unsigned long long)pl->hot_cols, 100.0 * (double)pl->hot_nnz / (double)p.a.nnz);
     snprintf(name, sizeof name, "k_b200_nnz<N%d,%s,%s,run %d BMTs/warp,%d gathers in flight%s>", p.N, p.a.col_is_u16 ? "u16" : "u32",
              p.a.val_is_f16 ? "f16" : "f32", (int)nnz_run(), p.N == 32 ? 16 : 8, hot);
     return name;
