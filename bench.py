@@ -517,6 +517,17 @@ def main():
     for i in range(1, 4):
         dep(i)
     ms_dep = timed(dep, dep_steps) / dep_steps
+    # one launch alone: event pair around a single launch, the device idle before it (what ncu's gpu__time_duration sees, warm caches aside)
+    iso = []
+    for i in range(64):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        plans[i % copies].launch()
+        e1.record(stream)
+        e1.synchronize()
+        iso.append(e0.elapsed_time(e1))
+    ms_iso = float(np.median(iso))
 
     nnz_all = torch.tensor([desc.origin_nnz], device="cuda", dtype=torch.float64)
     if world > 1:
@@ -562,7 +573,9 @@ def main():
                      "traffic_source": "profiles/traffic.json: one ncu --set full capture of this kernel, committed; not measured in this run",
                      "sustained_ms_per_step": ms_sustain / min(sustain_steps, 200000),
                      "dependent_chain_ms_per_step": ms_dep, "dependent_chain_frac": alg_bytes / (ms_dep * 1e-3) / 1e9 / hbm_peak,
-                     "dependent_chain": "step i+1's B is the first K rows of step i's C: one stream, no overlap between launches"},
+                     "dependent_chain": "step i+1's B is the first K rows of step i's C: one stream; the launch starts under programmatic dependent launch and waits on the device (griddepcontrol.wait) before it requests B",
+                     "isolated_launch_ms": ms_iso, "isolated_launch_frac": alg_bytes / (ms_iso * 1e-3) / 1e9 / hbm_peak,
+                     "isolated_launch": "median of 64 single launches, device idle before each, CUDA events around the one launch"},
         "e2e": {"value": 2.0 * nnz_all * N * e2e_steps / e2e_s / 1e9, "unit": "GFLOP/s", "h2d_bytes_per_step": int(COLS * N * 2),
                 "d2h_bytes_per_step": int(desc.rows * N * 2), "ms_per_step": e2e_s / e2e_steps * 1e3, "steps": e2e_steps,
                 "api": "gs_spmm_host_async per step (pinned B in, pinned C out) + one gs_synchronize; results equal the blocking call: %s" % e2e_ok,

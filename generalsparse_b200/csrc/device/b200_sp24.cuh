@@ -60,6 +60,7 @@ struct sp24_args {
     // tile-local remainder (kernels instantiated with TL): every tile image is followed by the remainder entries of its 128 x 128 window
     // (host/sp24_format.hpp, sp24_tiled); one bulk copy of unit_bytes brings both, B's 128 rows sit b_off bytes into the stage
     uint32_t unit_bytes, b_off, stage_bytes, rem_on;
+    uint32_t dep_wait; // 1: B may come from the kernel before this one on the stream: griddepcontrol.wait before B's first slice is requested
     // image without its empty tiles (group = 1): the units of panel p are panel_ptr[p] .. panel_ptr[p+1] (every panel keeps at least
     // one), unit u multiplies columns 128 unit_kt[u] ...; null = every tile present, unit t is tile (t / k_tiles, t % k_tiles)
     const uint32_t *panel_ptr, *unit_kt;
@@ -222,8 +223,30 @@ template <int N, int P, int NL, int RW, int TL = 0, bool CP = false> __global__ 
             const unsigned char *img = a.img + (size_t)t0 * UNIT;
             const uint32_t pf = a.pf_ahead ? (uint32_t)S + a.pf_ahead : 0u;
             for (uint32_t it = 0; it < pf && it < n_local; it++) l2_prefetch_bulk(img + (size_t)it * UNIT, UNIT);
-            uint32_t s = 0, ph = 0, kt = CP ? a.unit_kt[t0] : t0 % KT;
-            for (uint32_t it = 0; it < n_local; it++) {
+            uint32_t s = 0, ph = 0, kt = CP ? a.unit_kt[t0] : t0 % KT, it0 = 0;
+            if (a.dep_wait) {
+                // B may be what the previous kernel on the stream is still writing (a dependent chain: step i+1 multiplies step i's C).  The
+                // launch was allowed to start early all the same: the images of A for the whole ring go out now, griddepcontrol.wait then
+                // holds this lane until the predecessor has completed and flushed, and only then are B's slices requested.  Prologue,
+                // tensor-memory allocation, L2 prefetch and the first S images overlap the predecessor's tail instead of following it.
+                const uint32_t n0 = min((uint32_t)S, n_local);
+                for (uint32_t it = 0; it < n0; it++) {
+                    mbar_expect_tx(full0 + 8u * it, UNIT + (uint32_t)G::B_BYTES);
+                    bulk_load(smem0 + it * STG, img + (size_t)it * UNIT, UNIT, full0 + 8u * it);
+                }
+                row::pdl_wait();
+                for (uint32_t it = 0; it < n0; it++) {
+                    uint32_t kt_next = 0;
+                    if (CP && it + 1 < n_local) kt_next = a.unit_kt[t0 + it + 1];
+#pragma unroll
+                    for (int g = 0; g < G::GROUPS; g++) tma_load_2d(smem0 + it * STG + BOFF + g * G::GROUP_BYTES, &b_map, (uint32_t)(g * G::ATOM_N), kt * SK, full0 + 8u * it);
+                    if (CP) kt = kt_next;
+                    else if (++kt == KT) kt = 0;
+                    if (++s == S) s = 0, ph ^= 1u;
+                }
+                it0 = n0;
+            }
+            for (uint32_t it = it0; it < n_local; it++) {
                 uint32_t kt_next = 0; // requested before the wait below, so the table's latency hides behind it
                 if (CP && it + 1 < n_local) kt_next = a.unit_kt[t0 + it + 1];
                 if (pf && it + pf < n_local) l2_prefetch_bulk(img + (size_t)(it + pf) * UNIT, UNIT);

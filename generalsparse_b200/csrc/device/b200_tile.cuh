@@ -59,6 +59,7 @@ struct tile_args {
     uint32_t bulk_zero;      // 1: zero A's image with one st.bulk instead of the warp's STS.128
     uint32_t consumer_fence; // 1: the generic->async proxy fence runs on the mma lane after its acquire of full[], not in every producer lane
     uint32_t skip; // GS_TILE_SKIP (timing experiments, wrong results): 1 no scatter, 2 no zero fill, 4 no mma, 8 no B copy, 16 no pair loads, 32 no fence
+    uint32_t dep_wait;       // 1: griddepcontrol.wait before B's first slice is requested (B may belong to the previous kernel on the stream)
     unsigned long long *dbg; // GS_TILE_DEBUG: 8 (globaltimer, clock64) stamps per CTA, or null
 };
 
@@ -352,6 +353,7 @@ template <int N, bool DBG> __global__ void __launch_bounds__(THREADS, b_geom<N>:
         };
         if (lane == 0)
             for (uint32_t it = 0; it < PF_TILES; it++) pf(it);
+        if (a.dep_wait) row::pdl_wait(); // the L2 prefetch of A's runs is out; B belongs to the predecessor until it has completed
         for (int i = 0; i < SB - S; i++) load_b(); // the slots no tile has used yet
         for (uint32_t it = 0; it < n_local; it++) {
             if (lane == 0) pf(it + PF_TILES);

@@ -44,7 +44,9 @@ struct launch_params {
     int coarsen = 1;
     int vector_width = 32;   // VECTOR_WIDTH of the chain (BMTs per BMW / flag packing size)
     int block_size = 32;     // BMTs per BMTB in tblock-bitmap mode
-    bool pdl = false;        // the previous operation on the stream was a B200 row kernel launch (engine.cu)
+    bool pdl = false;        // programmatic dependent launch allowed (engine.cu)
+    bool dep_wait = false;   // B (or whatever else the launch reads) may belong to the operation before it on the stream: a kernel that cannot wait
+                             // for it on the device (griddepcontrol.wait before its first read of B) must be launched without the attribute
 };
 
 template <typename T> __device__ __forceinline__ float to_f32(T v);

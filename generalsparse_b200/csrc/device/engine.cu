@@ -556,7 +556,9 @@ static void enqueue(gs_plan *p, int which = 0)
     const bool b200_chain = p->kernel == GS_FAMILY_B200_ROW_SMEM || p->kernel == GS_FAMILY_B200_TCGEN05 || p->kernel == GS_FAMILY_B200_SP24;
     if (!b200_chain) chain = false;
     if (uses_atomics(p->kernel)) CUDA_TRY(cudaMemsetAsync(p->C_out(), 0, (size_t)p->desc.rows * p->N * p->esz(), st));
-    lp.pdl = chain && !no_pdl;
+    // the attribute is always set for the B200 kernels; what differs is whether the launch may read B at once (the chain is intact: the
+    // operation before it on this stream was one of ours and B did not change hands) or must wait for the predecessor on the device
+    lp.pdl = !no_pdl, lp.dep_wait = !chain;
     if (p->kernel == GS_FAMILY_B200_ROW_SMEM) CUDA_TRY(gsd::b200_row_launch(p->row_plan, lp, st));
     else if (p->kernel == GS_FAMILY_B200_TCGEN05) CUDA_TRY(gsd::b200_tile_launch(p->tile_plan, lp, st));
     else if (p->kernel == GS_FAMILY_B200_SP24) CUDA_TRY(gsd::b200_sp24_launch(p->sp24_plan, lp, st));

@@ -348,7 +348,7 @@ cudaError_t b200_row_launch(const b200_row_plan *pl, const launch_params &p, cud
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof cfg);
         cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(pl->threads), cfg.dynamicSmemBytes = pl->smem_bytes + pl->table_bytes, cfg.stream = s;
-        cfg.attrs = attr, cfg.numAttrs = p.pdl ? 1 : 0;
+        cfg.attrs = attr, cfg.numAttrs = (p.pdl && !p.dep_wait) ? 1 : 0; // the panel of B is staged before griddepcontrol.wait
         return cudaLaunchKernelExC(&cfg, pl->fn, args);
     }
     row::row_args a;

@@ -394,7 +394,7 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
         void *rargs[] = {&r};
         memset(&cfg, 0, sizeof cfg);
         cfg.gridDim = dim3(pl->n_panels * (128 / sp24::REM_ROWS)), cfg.blockDim = dim3(sp24::REM_THREADS), cfg.stream = s;
-        cfg.attrs = attr, cfg.numAttrs = p.pdl ? 1 : 0;
+        cfg.attrs = attr, cfg.numAttrs = (p.pdl && !p.dep_wait) ? 1 : 0; // the gather pass reads B at once
         cudaError_t e = cudaLaunchKernelExC(&cfg, pl->rem_fn, rargs);
         if (e != cudaSuccess) return e; // nothing launched: seq stays
         rem_launched = true;
@@ -409,10 +409,15 @@ cudaError_t b200_sp24_launch(b200_sp24_plan *pl, const launch_params &p, cudaStr
     a.rem_rowptr = (pl->fused && !pl->tiled && !skip_rem) ? pl->rem_rowptr : nullptr, a.rem_pack = pl->rem_pack, a.B = p.B, a.n_rows = pl->n_rows;
     a.unit_bytes = pl->unit_bytes, a.b_off = pl->b_off, a.stage_bytes = pl->stage_bytes, a.rem_on = skip_rem ? 0u : 1u;
     a.panel_ptr = pl->panel_ptr, a.unit_kt = pl->unit_kt, a.n_panels = pl->n_panels;
+    // B read only through the copy lane's TMA (no remainder, or the tile-local one, whose entries read B's rows from the stage): the launch
+    // may start under programmatic dependent launch even when B belongs to the previous kernel -- the lane waits before B's first slice
+    const bool can_wait = pl->tiled || !pl->rem_nnz || skip_rem;
+    a.dep_wait = (p.dep_wait && can_wait) ? 1u : 0u;
+    const bool pdl = p.pdl && (!p.dep_wait || can_wait);
     void *args[] = {&a, &pl->b_map};
     memset(&cfg, 0, sizeof cfg);
     cfg.gridDim = dim3(pl->grid), cfg.blockDim = dim3(pl->threads), cfg.dynamicSmemBytes = pl->smem, cfg.stream = s;
-    cfg.attrs = attr, cfg.numAttrs = (p.pdl || (pl->rem_nnz && !pl->fused)) ? 1 : 0; // behind its own remainder launch the 2:4 kernel always overlaps: the flags order them
+    cfg.attrs = attr, cfg.numAttrs = (pdl || (pl->rem_nnz && !pl->fused)) ? 1 : 0; // behind its own remainder launch the 2:4 kernel always overlaps: the flags order them
     const cudaError_t e = cudaLaunchKernelExC(&cfg, pl->fn, args);
     if (e == cudaSuccess) pl->seq = seq;
     else if (rem_launched) pl->poisoned = true;

@@ -232,6 +232,7 @@ cudaError_t b200_tile_launch(b200_tile_plan *pl, const launch_params &p, cudaStr
     a.skip = (uint32_t)env_int("GS_TILE_SKIP", 0);
     a.consumer_fence = (uint32_t)env_int("GS_TILE_CONSUMER_FENCE", 1);
     a.bulk_zero = (uint32_t)env_int("GS_TILE_BULK_ZERO", 0);
+    a.dep_wait = p.dep_wait ? 1u : 0u;
     a.dbg = pl->dbg ? pl->dbg + (size_t)(a.seq % DBG_RING) * ((size_t)pl->grid * 32 + 256) : nullptr;
     if (pl->b_mapped != p.B) {
         cudaError_t em = encode_b_map(pl, p.B);
@@ -345,7 +346,7 @@ cudaError_t b200_tile_launch_no_alloc(const b200_tile_plan *pl, int device, cons
     a.tile_ptr = pl->tile_ptr, a.off = pl->off, a.val = pl->val, a.B = B, a.C = C, a.out_row = pl->out_row;
     a.ws = ws, a.flags = flags, a.slot_free = flags + pl->grid, a.panel_seq = flags + 2 * (size_t)pl->grid;
     a.n_tiles = pl->n_tiles, a.k_tiles = pl->k_tiles, a.K = pl->K, a.seq = 1, a.ptr_cap = pl->ptr_cap;
-    a.skip = 0, a.consumer_fence = 1, a.bulk_zero = 0, a.dbg = nullptr;
+    a.skip = 0, a.consumer_fence = 1, a.bulk_zero = 0, a.dep_wait = 0, a.dbg = nullptr;
     // the tensor map of B is a kernel parameter, encoded on the host into a local (the plan's own map stays as it is)
     b200_tile_plan tmp;
     tmp.N = pl->N, tmp.K = pl->K;
