@@ -24,7 +24,7 @@ SYMBOLS = [
     "gs_launch_no_alloc", "gs_plan_format_bytes", "gsh_metadata_row_block", "gsh_metadata_row_nnz", "gs_plan_set_output_device",
     "gs_comm_unique_id", "gs_comm_init", "gs_comm_allgather_rows", "gs_comm_destroy",
     "gs_exec_create", "gs_exec_destroy", "gs_exec_devices", "gs_exec_build", "gs_exec_row_cuts", "gs_exec_kernel_name", "gs_exec_set_dense", "gs_exec_run",
-    "gsh_session_generate_final_program", "gs_execute_binary",
+    "gsh_session_generate_final_program", "gs_execute_binary", "gsh_metadata_fit_model", "gs_plan_model_bytes",
     "gs_exec_get_output", "gs_exec_enable_allgather", "gs_exec_allgather_output", "gs_exec_get_replica",
 ]
 
@@ -99,6 +99,7 @@ def lib():
         "gsh_metadata_row_block": (i32, [vp, u64, u64, P(vp)]), "gsh_metadata_row_nnz": (i32, [vp, vp, u64]),
         "gs_plan_set_output_device": (i32, [vp, vp]),
         "gsh_session_generate_final_program": (i32, [vp, C.c_uint, P(u64), cp, sz]),
+        "gsh_metadata_fit_model": (i32, [vp, cp, P(i32), vp]), "gs_plan_model_bytes": (u64, [vp]),
         "gs_execute_binary": (i32, [cp, cp, i32, i32, P(C.c_float), P(C.c_float)]),
         "gs_comm_unique_id": (i32, [vp]), "gs_comm_init": (i32, [vp, i32, i32, vp]), "gs_comm_allgather_rows": (i32, [vp, vp, vp, u64]),
         "gs_comm_destroy": (None, [vp]),

@@ -92,6 +92,12 @@ class MetaDataSet:
             check(lib().gsh_metadata_read_u64(self._h, key.encode(), _ptr(a), n))
         return a
 
+    def fit_model(self, key):
+        """model-driven index compression: (type name, coefficient, intercept, cycle or branch count) of the closed form the item follows"""
+        t, prm = C.c_int(), np.zeros(4, dtype=np.uint64)
+        check(lib().gsh_metadata_fit_model(self._h, key.encode(), C.byref(t), _ptr(prm)))
+        return ["none", "linear", "constant", "branch", "cycle_linear", "cycle_increase"][t.value], int(prm[0]), int(prm[1]), int(prm[2])
+
     def set_vals(self, vals, sub_matrix_id=0):
         v = np.ascontiguousarray(vals, dtype=np.float32)
         check(lib().gsh_metadata_set_vals(self._h, sub_matrix_id, _ptr(v), len(v)))
@@ -304,6 +310,10 @@ class Plan:
     @property
     def algorithmic_bytes(self):
         return lib().gs_plan_algorithmic_bytes(self._h)
+
+    @property
+    def model_bytes(self):
+        return lib().gs_plan_model_bytes(self._h)
 
     @property
     def format_bytes(self):

@@ -1,6 +1,7 @@
 // gsh_* entry points of include/gsparse_b200.h: the host side (metadata store, operator graph).
 // Pure C++; nothing here touches CUDA, so these calls work on a box without a GPU.
 #include "capi_internal.hpp"
+#include "host/arr_optimization.hpp"
 #include "host/tile_format.hpp"
 #include "host/sp24_format.hpp"
 
@@ -224,6 +225,19 @@ gs_status gsh_metadata_check(const gsh_metadata *ms)
     GS_API_BEGIN
     GS_REQUIRE(ms, "null metadata");
     GS_REQUIRE(ms->ms->check(), "meta_data_set::check failed");
+    GS_API_END
+}
+
+gs_status gsh_metadata_fit_model(const gsh_metadata *ms, const char *key, int *type, uint64_t *params)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ms && key && type && params, "null argument");
+    const universal_array *a = ms->ms->find_key(key);
+    if (!a) return fail(GS_ERR_NOT_FOUND, std::string("no metadata item ") + key);
+    GS_REQUIRE(!a->is_float(), "models are fitted to integer items");
+    const arr_model m = fit_arr_model(a->u, (uint64_t)get_config().as_integer("BRANCH_COMPRESS_MAX_SIZE"));
+    *type = (int)m.type;
+    params[0] = m.coefficient, params[1] = m.intercept, params[2] = m.type == BRANCH_COMPRESS ? m.low.size() : m.cycle, params[3] = 0;
     GS_API_END
 }
 

@@ -44,6 +44,7 @@ struct launch_params {
     int coarsen = 1;
     int vector_width = 32;   // VECTOR_WIDTH of the chain (BMTs per BMW / flag packing size)
     int block_size = 32;     // BMTs per BMTB in tblock-bitmap mode
+    uint32_t first_nz_step = 0; // != 0: THREAD first_nz_indices[i] == first_nz_step * i (model-driven index compression): computed, not loaded
     bool pdl = false;        // programmatic dependent launch allowed (engine.cu)
     bool dep_wait = false;   // B (or whatever else the launch reads) may belong to the operation before it on the stream: a kernel that cannot wait
                              // for it on the device (griddepcontrol.wait before its first read of B) must be launched without the attribute

@@ -4,6 +4,7 @@
 #include "../capi_internal.hpp"
 #include "common.cuh"
 #include "nccl_dl.hpp"
+#include "../host/arr_optimization.hpp"
 
 #include <algorithm>
 #include <cmath>
@@ -32,6 +33,8 @@ struct dev_array {
     int dtype = GS_U32;   // device dtype
     uint64_t max_value = 0;
     uint64_t align = 0;   // gcd of all entries (offset arrays): the row alignment vector loads may rely on
+    int model = 0;        // gs::arr_compress_type of the closed form the array follows (0 = none), fitted at upload
+    uint64_t model_coefficient = 0, model_intercept = 0;
     bool iota = false;    // entry i == i for every i: a first_row_indices array of a row level with one row per block
 };
 
@@ -89,6 +92,7 @@ struct gs_plan {
     void *C_out() const { return C_ext ? C_ext : C_dev; }
     void *B_pinned = nullptr, *C_pinned = nullptr; // staging for pageable host buffers is NOT used; these stay null
     uint64_t offset_bytes = 0; // bytes of the offset / bitmap arrays the launched kernel reads
+    uint64_t model_bytes = 0; // of chain_offset_bytes: arrays a closed-form model reproduces
     uint64_t chain_offset_bytes = 0; // the same for the chain's own family (desc.family): SURVEY.md 8(d)'s offset term, independent of the kernel chosen
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t ev_b = nullptr, ev_k = nullptr, ev_c = nullptr; // async round trip: B landed, kernel done, C read back
@@ -137,6 +141,10 @@ static void upload(gs_ctx *ctx, const std::string &key, const void *host, uint64
             iota = iota && v == i;
         }
         d.max_value = mx, d.align = g, d.iota = iota;
+        if (!key_has(key, "nz_col_indices") && !key_has(key, "nz_row_indices")) { // offset arrays only: the streams never follow a formula
+            const gs::arr_model m = gs::fit_arr_model(w, (uint64_t)gs::get_config().as_integer("BRANCH_COMPRESS_MAX_SIZE"));
+            d.model = (int)m.type, d.model_coefficient = m.coefficient, d.model_intercept = m.intercept;
+        }
         const bool is_col = key_has(key, "nz_col_indices");
         const bool is_bits = key_has(key, "thread_bit_map") || key_has(key, "segment_empty_flag") || (key_has(key, "bit_map_of_thread") && key_has(key, "WARP_META"));
         if (is_bits) d.dtype = GS_U64;
@@ -380,6 +388,10 @@ static void select_kernel(gs_plan *p, int family)
         if (!gsd::b200_nnz_supported(lp)) throw gs::Error("b200_nnz: needs N in {32,64,128} and an nnz-direction bit-map chain (thread_bit_map / warp_segment)");
         if (p->nnz_plan) gsd::b200_nnz_free(p->nnz_plan), p->nnz_plan = nullptr;
         CUDA_TRY(gsd::b200_nnz_prepare(lp, &p->nnz_plan, ctx->stream));
+        { // model-driven index compression: first_nz_indices of a padded nnz-direction level is coefficient * i: the kernel computes it
+            const dev_array *fn = find_arr(ctx, "THREAD_META", "first_nz_indices", id);
+            p->lp.first_nz_step = (fn && fn->model == (int)gs::LINEAR_COMPRESS && fn->model_intercept == 0 && !getenv("GS_NO_INDEX_MODEL")) ? (uint32_t)fn->model_coefficient : 0u;
+        }
         add("THREAD_META", "first_row_indices"), add("THREAD_META", "first_nz_indices"), add("THREAD_META", "thread_bit_map");
         add("THREAD_META", "segment_ptr"), add("THREAD_META", "segment_empty_flag"), add("THREAD_META", "segment_empty_row_indices");
         break;
@@ -679,7 +691,10 @@ gs_status gs_plan_create(gs_ctx *ctx, const gs_plan_desc *desc, int N, int half,
             // the key carries the session's sub-matrix id; the arrays may live under another one (gs_upload_session_as)
             const size_t us = key.rfind('_');
             auto it = ctx->arrays.find(us == std::string::npos ? key : key.substr(0, us + 1) + std::to_string(desc->sub_matrix_id));
-            if (it != ctx->arrays.end()) p->chain_offset_bytes += it->second.len * dsize(it->second.dtype);
+            if (it != ctx->arrays.end()) {
+                p->chain_offset_bytes += it->second.len * dsize(it->second.dtype);
+                if (it->second.model != 0) p->model_bytes += it->second.len * dsize(it->second.dtype);
+            }
         }
         select_kernel(p, desc->family);
         size_t cbytes = (size_t)desc->rows * N * p->esz();
@@ -973,6 +988,8 @@ uint64_t gs_plan_algorithmic_bytes(const gs_plan *p)
     uint64_t idx = p->lp.a.col_is_u16 ? 2 : 4;
     return p->lp.a.nnz * (idx + p->esz()) + p->chain_offset_bytes + (uint64_t)p->desc.cols * p->N * p->esz() + (uint64_t)p->desc.rows * p->N * p->esz();
 }
+
+uint64_t gs_plan_model_bytes(const gs_plan *p) { return p ? p->model_bytes : 0; }
 
 uint64_t gs_plan_format_bytes(const gs_plan *p)
 {

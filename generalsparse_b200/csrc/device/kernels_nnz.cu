@@ -112,7 +112,7 @@ template <typename ColT, typename ValT, int NV, int MINB, int GROUP, int HOT = 0
 
     // the run's metadata: one BMT per lane, handed round by shuffles afterwards
     uint32_t m_fn = 0, m_row = 0, m_lo = 0, m_hi = 0, m_gap = 0;
-    if ((uint32_t)lane <= nb) m_fn = a.t_first_nz[b0 + lane];
+    if ((uint32_t)lane <= nb) m_fn = p.first_nz_step ? (b0 + lane) * p.first_nz_step : a.t_first_nz[b0 + lane];
     if ((uint32_t)lane < nb) {
         uint64_t map = a.t_bit_map[b0 + lane];
         m_lo = (uint32_t)map, m_hi = (uint32_t)(map >> 32);

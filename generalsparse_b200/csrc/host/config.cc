@@ -11,7 +11,8 @@ namespace gs {
 config_store::config_store()
 {
     // the keys the path reads, defaults from global_config.json.bak with HALF off
-    kv_ = {{"DATA_SET", "\"\""},
+    kv_ = {{"BRANCH_COMPRESS_MAX_SIZE", "5"},
+           {"DATA_SET", "\"\""},
            {"DATA_TYPE_COMPRESS", "true"},
            {"DEFAULT_DEVICE_ID", "0"},
            {"DENSE_MATRIX_SIZE", "8"},

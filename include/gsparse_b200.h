@@ -94,6 +94,12 @@ gs_status gsh_metadata_set_vals(gsh_metadata *ms, int sub_matrix_id, const float
 gs_status gsh_metadata_dump(const gsh_metadata *ms, const char *dir);
 gs_status gsh_metadata_check(const gsh_metadata *ms); /* meta_data_set::check + logical_check */
 
+/* Model-driven index compression (arr_optimization.hpp:13-85; the reference's MODEL_DRIVEN_INDEX_COMPRESS): the closed form an integer item
+ * follows, fitted with the reference's acceptance rules (checked mode).  *type: 0 none, 1 linear (params: coefficient, intercept),
+ * 2 constant (-, value), 3 branch (params[2] = number of runs), 4 cycle_linear (coefficient, intercept, cycle), 5 cycle_increase
+ * (-, intercept, cycle).  params: 4 entries. */
+gs_status gsh_metadata_fit_model(const gsh_metadata *ms, const char *key, int *type, uint64_t *params);
+
 /* get_config()/set_config() (config.cc:2-40): numbers, booleans ("true"/"false") and strings */
 gs_status gsh_config_load(const char *path);
 gs_status gsh_config_set(const char *key, const char *json_scalar);
@@ -249,6 +255,9 @@ uint64_t gs_plan_algorithmic_bytes(const gs_plan *p);
 /* bytes the launched kernel's own layout streams per launch (2:4 image, tile stream, or the chain's arrays): format waste is
  * gs_plan_format_bytes / gs_plan_algorithmic_bytes */
 uint64_t gs_plan_format_bytes(const gs_plan *p);
+/* bytes of the chain's registered offset arrays that a closed-form model reproduces exactly (what model-driven index compression takes out
+ * of the byte stream: first_row_indices of a one-row-per-block level, first_nz_indices of a padded nnz-direction level ...) */
+uint64_t gs_plan_model_bytes(const gs_plan *p);
 int gs_plan_launch_count(const gs_plan *p); /* kernels per gs_launch (memset excluded) */
 const char *gs_plan_kernel_name(const gs_plan *p);
 /* GS_FAMILY_B200_SP24 with GS_SP24_PROBE=1 in the environment at plan creation: the 4 metadata columns of the first
