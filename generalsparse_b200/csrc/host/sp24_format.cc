@@ -2,6 +2,7 @@
 #include "sp24_format.hpp"
 
 #include <algorithm>
+#include <array>
 #include <cstring>
 #include <stdexcept>
 #include <utility>
@@ -99,26 +100,58 @@ void localize_sp24_remainder(const sp24_image &im, uint32_t row_bytes, sp24_tile
     out.unit_bytes = SP24_TILE_BYTES + SP24_REM_HEADER + ((mx + 3u) & ~3u) * 4u;
     out.bytes.assign(T * out.unit_bytes, 0);
     for (uint64_t t = 0; t < T; t++) std::copy_n(im.bytes.begin() + t * SP24_TILE_BYTES, SP24_TILE_BYTES, out.bytes.begin() + t * out.unit_bytes);
-    // rows ascending and, inside a row, columns ascending: a row's entries of one tile are one run of the CSR row
-    std::vector<uint32_t> fill(im.k_tiles);
+    // Rows ascending; INSIDE a row the order of the entries is free (a sum), and it decides how the remainder warps' shared-memory
+    // gathers collide: a warp holds 16 consecutive tile rows (a pair of threads per row), in round j every row reads the row of B its
+    // j-th entry names, one 16-byte chunk per thread, i.e. 32 requests into the 8 sixteen-byte bank groups of a 128-byte line.  Entries
+    // in column order land at random: ~7 of the 4 wavefronts a request needs at best (58 % of the kernel's shared-load wavefronts were
+    // bank conflicts at N = 32, profiles/traffic.json).  So every row picks, position by position, the entry whose bank groups are
+    // least used at that position by the rows of its warp so far (greedy; the groups come from the very offsets the threads will use).
+    const uint32_t cpt = row_bytes >= 64 ? row_bytes / 32u : 1u; // 16-byte chunks a thread reads per entry (b200_sp24.cuh: CPT)
+    auto groups_of = [&](uint32_t off, uint32_t g[2]) {
+        if (row_bytes == 16) g[0] = g[1] = (off >> 4) & 7u; // NL = 8: the pair's threads take alternate entries, one chunk each
+        else g[0] = (off >> 4) & 7u, g[1] = ((off ^ (cpt << 4)) >> 4) & 7u;
+    };
+    std::vector<std::vector<uint32_t>> rows_of_tile((size_t)im.k_tiles * SP24_ROWS);
     for (uint32_t p = 0; p < im.n_panels; p++) {
-        std::fill(fill.begin(), fill.end(), 0u);
+        for (auto &v : rows_of_tile) v.clear();
         for (uint32_t rr = 0; rr < SP24_ROWS; rr++) {
             const uint32_t r = p * SP24_ROWS + rr;
-            for (uint32_t kt = 0; kt < im.k_tiles; kt++) {
-                uint8_t *h = out.bytes.data() + ((uint64_t)p * im.k_tiles + kt) * out.unit_bytes + SP24_TILE_BYTES + 2u * rr;
-                h[0] = (uint8_t)(fill[kt] & 0xff), h[1] = (uint8_t)(fill[kt] >> 8);
-            }
-            if (r >= im.n_rows) continue;
+            if (r >= im.n_rows) break;
             for (uint32_t i = im.rem_rowptr[r]; i < im.rem_rowptr[r + 1]; i++) {
-                const uint32_t kt = im.rem_col[i] / SP24_COLS, w = (sp24_b_row_offset(im.rem_col[i] % SP24_COLS, row_bytes) << 16) | im.rem_val[i];
-                uint8_t *e = out.bytes.data() + ((uint64_t)p * im.k_tiles + kt) * out.unit_bytes + SP24_TILE_BYTES + SP24_REM_HEADER + 4u * fill[kt]++;
-                e[0] = (uint8_t)w, e[1] = (uint8_t)(w >> 8), e[2] = (uint8_t)(w >> 16), e[3] = (uint8_t)(w >> 24);
+                const uint32_t kt = im.rem_col[i] / SP24_COLS;
+                rows_of_tile[(size_t)kt * SP24_ROWS + rr].push_back((sp24_b_row_offset(im.rem_col[i] % SP24_COLS, row_bytes) << 16) | im.rem_val[i]);
             }
         }
         for (uint32_t kt = 0; kt < im.k_tiles; kt++) {
-            uint8_t *h = out.bytes.data() + ((uint64_t)p * im.k_tiles + kt) * out.unit_bytes + SP24_TILE_BYTES + 2u * SP24_ROWS;
-            h[0] = (uint8_t)(fill[kt] & 0xff), h[1] = (uint8_t)(fill[kt] >> 8);
+            uint8_t *unit = out.bytes.data() + ((uint64_t)p * im.k_tiles + kt) * out.unit_bytes;
+            uint32_t n = 0;
+            for (uint32_t w0 = 0; w0 < SP24_ROWS; w0 += 16) { // the 16 rows of one remainder warp
+                std::vector<std::array<uint16_t, 8>> used; // used[position][bank group]
+                for (uint32_t rr = w0; rr < w0 + 16; rr++) {
+                    unit[SP24_TILE_BYTES + 2u * rr] = (uint8_t)(n & 0xff), unit[SP24_TILE_BYTES + 2u * rr + 1] = (uint8_t)(n >> 8);
+                    std::vector<uint32_t> &e = rows_of_tile[(size_t)kt * SP24_ROWS + rr];
+                    if (used.size() < e.size()) used.resize(e.size(), std::array<uint16_t, 8>{});
+                    for (size_t pos = 0; pos < e.size(); pos++) {
+                        size_t best = pos;
+                        uint32_t best_cost = ~0u;
+                        for (size_t q = pos; q < e.size(); q++) {
+                            uint32_t g[2];
+                            groups_of(e[q] >> 16, g);
+                            const uint32_t cost = std::max<uint32_t>(used[pos][g[0]], used[pos][g[1]]) * 16u + used[pos][g[0]] + used[pos][g[1]];
+                            if (cost < best_cost) best_cost = cost, best = q;
+                        }
+                        std::swap(e[pos], e[best]);
+                        uint32_t g[2];
+                        groups_of(e[pos] >> 16, g);
+                        used[pos][g[0]]++;
+                        if (g[1] != g[0]) used[pos][g[1]]++;
+                        uint8_t *dst = unit + SP24_TILE_BYTES + SP24_REM_HEADER + 4u * n++;
+                        const uint32_t w = e[pos];
+                        dst[0] = (uint8_t)w, dst[1] = (uint8_t)(w >> 8), dst[2] = (uint8_t)(w >> 16), dst[3] = (uint8_t)(w >> 24);
+                    }
+                }
+            }
+            unit[SP24_TILE_BYTES + 2u * SP24_ROWS] = (uint8_t)(n & 0xff), unit[SP24_TILE_BYTES + 2u * SP24_ROWS + 1] = (uint8_t)(n >> 8);
         }
     }
 }
