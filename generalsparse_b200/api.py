@@ -16,6 +16,7 @@ from ._lib import FAMILIES, FAMILY_ID, GsError, PlanDesc, check, lib
 _NP2GS = {np.dtype(np.uint8): _lib.GS_U8, np.dtype(np.uint16): _lib.GS_U16, np.dtype(np.uint32): _lib.GS_U32,
           np.dtype(np.uint64): _lib.GS_U64, np.dtype(np.float32): _lib.GS_F32, np.dtype(np.float64): _lib.GS_F64,
           np.dtype(np.float16): _lib.GS_F16}
+_GS2NP = {v: k for k, v in _NP2GS.items()}
 _GS2NAME = {0: "UNSIGNED_CHAR", 1: "UNSIGNED_SHORT", 2: "UNSIGNED_INT", 3: "UNSIGNED_LONG", 4: "FLOAT", 5: "DOUBLE"}
 
 
@@ -229,6 +230,33 @@ class Engine:
 
     def upload_session(self, session, half=False, as_id=-1):
         check(lib().gs_upload_session_as(self._h, session._h, int(half), as_id))
+
+    def transform_coo(self, family, rows, cols, r, c, vals, N, sparse_coarsen=1, coarsen=1, half=False, as_id=0):
+        """ the driver chain of `family` ("thread_total", "warp_total", "thread_bit_map") built by device passes from a row-major
+        COO; returns (PlanDesc, device milliseconds of the passes).  The arrays land where upload_session(as_id=...) would have put them."""
+        r32, c32 = np.ascontiguousarray(r, dtype=np.uint32), np.ascontiguousarray(c, dtype=np.uint32)
+        v32 = np.ones(len(r32), np.float32) if vals is None else np.ascontiguousarray(vals, dtype=np.float32)
+        desc, ms = PlanDesc(), C.c_float(0)
+        fid = FAMILY_ID[family] if isinstance(family, str) else family
+        check(lib().gs_transform_host_coo(self._h, fid, rows, cols, len(r32), _ptr(r32), _ptr(c32), _ptr(v32), N, sparse_coarsen, coarsen, int(half), as_id, C.byref(desc),
+                                          C.byref(ms)))
+        return desc, ms.value
+
+    def transform_coo_device(self, family, rows, cols, nnz, row_ptr, col_ptr, val_ptr, N, sparse_coarsen=1, coarsen=1, half=False, as_id=0):
+        """the same from device pointers (u32 row ids ascending, u32 column ids, fp32 values)"""
+        desc = PlanDesc()
+        fid = FAMILY_ID[family] if isinstance(family, str) else family
+        check(lib().gs_transform_device(self._h, fid, rows, cols, nnz, C.c_void_p(row_ptr), C.c_void_p(col_ptr), C.c_void_p(val_ptr), N, sparse_coarsen, coarsen, int(half), as_id,
+                                        C.byref(desc)))
+        return desc
+
+    def download_array(self, key):
+        """a device array of the context as numpy, in its device dtype"""
+        n, dt = C.c_uint64(0), C.c_int32(0)
+        check(lib().gs_download_array(self._h, key.encode(), None, 0, C.byref(n), C.byref(dt)))
+        out = np.empty(n.value, dtype=_GS2NP[dt.value])
+        check(lib().gs_download_array(self._h, key.encode(), _ptr(out), out.nbytes, C.byref(n), C.byref(dt)))
+        return out
 
     def plan(self, session_or_desc, N, half=False, kernel=None, sub_matrix_id=None):
         desc = session_or_desc.plan_desc() if isinstance(session_or_desc, Session) else session_or_desc

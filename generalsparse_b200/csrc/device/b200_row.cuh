@@ -441,5 +441,73 @@ __global__ void k_rainbow_rows(const ColT *col, const ValT *val, ColT *col2, Val
     }
 }
 
+
+// ---- short rows: a GROUP of G lanes per row instead of a warp -------------------------------------------------------------------------
+// One warp per row (k_b200_row) leaves most lanes idle on matrices like BASELINE's C1 (IG5-18: 37 non-zeros per row) and walks its rows
+// one after the other: 12 rows per warp, each a chain of dependent loads (row pointer -> ids / values -> rows of B -> shuffles -> store),
+// 26.7 us for a 14 MB problem.  Here 32 / G rows are in flight per warp: lane j of a group takes the row's non-zeros j, j + G, ... with all
+// NT dense columns in registers (a row of B is one or two 128-bit loads), a halving butterfly leaves lane j with columns
+// j * NT / G ... of the row sum (NT - NT / G shuffles instead of NT * log2 G), and the group stores the row of C as one coalesced piece.
+// Groups take rows gid, gid + groups, ...: after sort_operator (rows by length, descending) the rows of a warp are equally long.
+// The dense matrix is read through L1 / L2 (this variant is for panels that do not fit shared memory).
+template <int NT, typename ColT, typename ValT, int G> __global__ void __launch_bounds__(256) k_b200_row_short(row_args a)
+{
+    static_assert(NT % G == 0 || G % NT == 0, "columns per lane");
+    constexpr int PER = NT >= G ? NT / G : 1; // columns a lane owns after the reduction (G > NT: only the first NT lanes own one)
+    const ColT *col = (const ColT *)a.col;
+    const ValT *val = (const ValT *)a.val, *B = (const ValT *)a.B;
+    ValT *C = (ValT *)a.C;
+    const int lane = threadIdx.x & 31, j = lane % G;
+    const unsigned mask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (lane & ~(G - 1)));
+    const uint32_t groups = gridDim.x * (256 / G), gid = (blockIdx.x * 256 + threadIdx.x) / G;
+    constexpr int VPL = 16 / sizeof(ValT); // values per 128-bit load
+    for (uint32_t r = gid; r < a.n_rows; r += groups) {
+        const uint32_t lo = a.rowptr[r], hi = a.rowptr[r + 1];
+        float acc[NT];
+#pragma unroll
+        for (int i = 0; i < NT; i++) acc[i] = 0.0f;
+        for (uint32_t k = lo + j; k < hi; k += 2 * G) { // two non-zeros per lane and round: their loads go out together
+            const bool two = k + G < hi;
+            const uint32_t c0 = (uint32_t)col[k], c1 = two ? (uint32_t)col[k + G] : c0;
+            const float v0 = to_f32(val[k]), v1 = two ? to_f32(val[k + G]) : 0.0f;
+            uint4 b0[NT / VPL], b1[NT / VPL];
+#pragma unroll
+            for (int q = 0; q < NT / VPL; q++) b0[q] = __ldg((const uint4 *)(B + (size_t)c0 * NT) + q), b1[q] = __ldg((const uint4 *)(B + (size_t)c1 * NT) + q);
+#pragma unroll
+            for (int q = 0; q < NT / VPL; q++) {
+                const ValT *x0 = (const ValT *)&b0[q], *x1 = (const ValT *)&b1[q];
+#pragma unroll
+                for (int t = 0; t < VPL; t++) acc[q * VPL + t] = fmaf(v1, to_f32(x1[t]), fmaf(v0, to_f32(x0[t]), acc[q * VPL + t]));
+            }
+        }
+        // halving butterfly: at distance d the lane keeps the half of its columns its bit d selects and adds the partner's
+        int n = NT;
+#pragma unroll
+        for (int d = G / 2; d >= 1; d >>= 1) {
+            if (n > 1) {
+                n >>= 1;
+                const bool upper = (j & d) != 0;
+#pragma unroll
+                for (int i = 0; i < NT / 2; i++) {
+                    if (i < n) {
+                        const float keep = upper ? acc[i + n] : acc[i], give = upper ? acc[i] : acc[i + n];
+                        acc[i] = keep + __shfl_xor_sync(mask, give, d, G);
+                    }
+                }
+            } else { // more lanes than columns left: plain sum, the lanes of one column end up with the same total
+                acc[0] += __shfl_xor_sync(mask, acc[0], d, G);
+            }
+        }
+        const uint32_t row = a.rowid[r];
+        ValT *dst = C + (size_t)((a.perm ? a.perm[row] : row) + a.begin_row) * NT;
+        if (NT >= G) {
+#pragma unroll
+            for (int i = 0; i < PER; i++) dst[j * PER + i] = from_f32<ValT>(acc[i]);
+        } else { // G > NT: after log2(NT) halving steps lane j holds column (j / (G / NT)); one lane per column stores
+            if (j % (G / NT) == 0) dst[j / (G / NT)] = from_f32<ValT>(acc[0]);
+        }
+    }
+}
+
 } // namespace row
 } // namespace gsd

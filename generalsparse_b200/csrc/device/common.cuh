@@ -120,5 +120,6 @@ cudaError_t b200_merge_prepare(const launch_params &p, const uint32_t *parts_dev
 cudaError_t b200_merge_launch(const b200_merge_plan *plan, const launch_params &p, cudaStream_t s);
 void b200_merge_free(b200_merge_plan *plan);
 const char *b200_merge_kernel_name(const b200_merge_plan *plan);
+bool b200_merge_needs_zero(const b200_merge_plan *plan); // false: the kernel writes every row itself (ticket mode), no memset of C
 uint64_t b200_merge_bytes(const b200_merge_plan *plan, uint64_t nnz, uint64_t idx_bytes, uint64_t val_bytes, uint64_t rows, uint64_t cols);
 } // namespace gsd

@@ -4,6 +4,7 @@
 #include "../capi_internal.hpp"
 #include "common.cuh"
 #include "nccl_dl.hpp"
+#include "transform.hpp"
 #include "../host/arr_optimization.hpp"
 
 #include <algorithm>
@@ -567,7 +568,7 @@ static void enqueue(gs_plan *p, int which = 0)
     static const bool no_pdl = getenv("GS_NO_PDL") != nullptr;
     const bool b200_chain = p->kernel == GS_FAMILY_B200_ROW_SMEM || p->kernel == GS_FAMILY_B200_TCGEN05 || p->kernel == GS_FAMILY_B200_SP24;
     if (!b200_chain) chain = false;
-    if (uses_atomics(p->kernel)) CUDA_TRY(cudaMemsetAsync(p->C_out(), 0, (size_t)p->desc.rows * p->N * p->esz(), st));
+    if (uses_atomics(p->kernel) && !(p->kernel == GS_FAMILY_B200_MERGE && !gsd::b200_merge_needs_zero(p->merge_plan))) CUDA_TRY(cudaMemsetAsync(p->C_out(), 0, (size_t)p->desc.rows * p->N * p->esz(), st));
     // the attribute is always set for the B200 kernels; what differs is whether the launch may read B at once (the chain is intact: the
     // operation before it on this stream was one of ours and B did not change hands) or must wait for the predecessor on the device
     lp.pdl = !no_pdl, lp.dep_wait = !chain;
@@ -667,6 +668,151 @@ gs_status gs_upload_session_as(gs_ctx *ctx, const gsh_session *s, int half, int 
             const universal_array &a = s->ms->get(GLOBAL_META, "nz_row_indices", sid);
             upload(ctx, meta_data_set::item_name(GLOBAL_META, "nz_row_indices", as_id >= 0 ? as_id : sid), a.u.data(), a.u.size(), GS_U64, half);
         }
+    }
+    GS_API_END
+}
+
+// ---- (f2) the chain built on the device ----------------------------------------------------------------------------------------------------------
+static void drop_arrays_of_id(gs_ctx *ctx, int id)
+{
+    const std::string suffix = "_" + std::to_string(id);
+    for (auto it = ctx->arrays.begin(); it != ctx->arrays.end();) {
+        const std::string &k = it->first;
+        if (k.size() > suffix.size() && k.compare(k.size() - suffix.size(), suffix.size(), suffix) == 0) {
+            cudaFree(it->second.ptr);
+            it = ctx->arrays.erase(it);
+        } else ++it;
+    }
+}
+
+gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t cols, uint64_t nnz, const uint32_t *row_dev, const uint32_t *col_dev, const float *val_dev, int N,
+                              int sparse_coarsen, int coarsen, int half, int as_id, gs_plan_desc *desc_out)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ctx && desc_out && row_dev && col_dev && val_dev, "null argument");
+    GS_REQUIRE(N >= 1 && sparse_coarsen >= 1 && coarsen >= 1, "N, sparse_coarsen and coarsen must be >= 1");
+    GS_REQUIRE(as_id >= 0, "as_id must be >= 0");
+    if (family != GS_FAMILY_THREAD_TOTAL && family != GS_FAMILY_WARP_TOTAL && family != GS_FAMILY_THREAD_BITMAP)
+        return fail(GS_ERR_UNSUPPORTED, "gs_transform_device builds the thread_total, warp_total and thread_bit_map driver chains; the others are built on the host (gsh_session_run_family)");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    ctx->join_async();
+    const double bound = (double)gs::get_config().as_integer("PADDING_RATE_UP_BOUND");
+    gsd::coo_dev m;
+    m.row = row_dev, m.col = col_dev, m.val = val_dev, m.rows = rows, m.cols = cols, m.nnz = nnz;
+    gsd::transform_out out;
+    // the launch shape the driver would have passed to grid_block_operator (token_test.cc:1042-1077, :1215-1232, :1342-1375)
+    gs_plan_desc d;
+    memset(&d, 0, sizeof d);
+    d.family = family, d.sub_matrix_id = as_id, d.sparse_coarsen = sparse_coarsen, d.coarsen = coarsen;
+    d.rows = rows, d.cols = cols, d.origin_nnz = nnz;
+    unsigned x = 0, y = 0, grid_x = 0;
+    cudaError_t e = cudaSuccess;
+    if (family == GS_FAMILY_THREAD_TOTAL) {
+        x = (unsigned)std::min(N / coarsen, 32);
+        GS_REQUIRE(x >= 1, "N / coarsen must be >= 1");
+        y = 128 / x, grid_x = (unsigned)(rows / y + 1);
+        d.thread_for_row = 1;
+        e = gsd::transform_row_chain(m, true, (uint32_t)sparse_coarsen, half != 0, "THREAD_META", bound, ctx->stream, out);
+    } else if (family == GS_FAMILY_WARP_TOTAL) {
+        y = (unsigned)std::min(N / coarsen, 32);
+        GS_REQUIRE(y >= 1, "N / coarsen must be >= 1");
+        x = std::max(256 / y, 32u), grid_x = (unsigned)rows;
+        e = gsd::transform_row_chain(m, false, 0, half != 0, "WARP_META", bound, ctx->stream, out);
+    } else {
+        x = (unsigned)std::min(N / coarsen, 32);
+        GS_REQUIRE(x >= 1, "N / coarsen must be >= 1");
+        y = 128 / x, grid_x = (unsigned)(nnz / y + 1);
+        e = gsd::transform_nnz_chain(m, x, half != 0, bound, ctx->stream, out);
+    }
+    if (e != cudaSuccess) {
+        out.release();
+        cudaGetLastError();
+        if (!out.error.empty()) return fail(out.refused ? GS_ERR_PADDING_RATE : GS_ERR_INVALID, out.error);
+        return fail(GS_ERR_CUDA, std::string("device transform: ") + cudaGetErrorString(e));
+    }
+    d.vector_width = (int)x;
+    d.block[0] = x, d.block[1] = y % 2 ? y + 1 : y; // grid_block_operator.cc:13-33
+    const unsigned per = (family == GS_FAMILY_WARP_TOTAL ? d.block[1] : d.block[0]) * (unsigned)coarsen;
+    d.grid[0] = grid_x, d.grid[1] = (unsigned)((N + per - 1) / per);
+    d.has_row_permutation = out.has_perm, d.stored_nnz = out.stored_nnz;
+    drop_arrays_of_id(ctx, as_id);
+    // what compile() registers for the family, in its order (operators.cc: code_generator::compile)
+    std::vector<std::pair<const char *, const char *>> deps = {{"GLOBAL_META", "nz_col_indices"}, {"GLOBAL_META", "nz_vals"}};
+    if (out.has_perm) deps.push_back({"GLOBAL_META", "original_nz_row_indices"});
+    const char *lvl = family == GS_FAMILY_WARP_TOTAL ? "WARP_META" : "THREAD_META";
+    deps.push_back({lvl, "first_row_indices"}), deps.push_back({lvl, "first_nz_indices"});
+    if (family == GS_FAMILY_THREAD_BITMAP)
+        for (const char *n : {"thread_bit_map", "segment_ptr", "segment_empty_flag", "segment_empty_row_indices"}) deps.push_back({"THREAD_META", n});
+    for (const auto &k : deps) {
+        const std::string key = std::string(k.first) + "_" + k.second + "_" + std::to_string(as_id);
+        GS_REQUIRE(key.size() < 64, "key too long");
+        strcpy(d.deps[d.n_deps++], key.c_str());
+    }
+    for (gsd::built_array &a : out.arrays) {
+        dev_array da;
+        da.ptr = a.ptr, da.len = a.len, da.dtype = a.dtype, da.max_value = a.max_value, da.align = a.align, da.iota = a.iota;
+        if (a.linear) da.model = (int)gs::LINEAR_COMPRESS, da.model_coefficient = a.linear_step, da.model_intercept = 0;
+        ctx->arrays[a.pos + "_" + a.name + "_" + std::to_string(as_id)] = da;
+        a.ptr = nullptr; // the context owns it now
+    }
+    out.arrays.clear();
+    *desc_out = d;
+    GS_API_END
+}
+
+gs_status gs_transform_host_coo(gs_ctx *ctx, int family, uint64_t rows, uint64_t cols, uint64_t nnz, const uint32_t *row, const uint32_t *col, const float *val, int N,
+                                int sparse_coarsen, int coarsen, int half, int as_id, gs_plan_desc *desc_out, float *ms_device)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ctx && row && col && val && nnz > 0, "null argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    uint32_t *r = nullptr, *c = nullptr;
+    float *v = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    gs_status st = GS_OK;
+    auto cleanup = [&] {
+        cudaFree(r), cudaFree(c), cudaFree(v);
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
+    };
+    try {
+        CUDA_TRY(cudaMalloc((void **)&r, nnz * 4));
+        CUDA_TRY(cudaMalloc((void **)&c, nnz * 4));
+        CUDA_TRY(cudaMalloc((void **)&v, nnz * 4));
+        CUDA_TRY(cudaMemcpyAsync(r, row, nnz * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CUDA_TRY(cudaMemcpyAsync(c, col, nnz * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CUDA_TRY(cudaMemcpyAsync(v, val, nnz * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CUDA_TRY(cudaEventCreate(&e0));
+        CUDA_TRY(cudaEventCreate(&e1));
+        CUDA_TRY(cudaEventRecord(e0, ctx->stream));
+        st = gs_transform_device(ctx, family, rows, cols, nnz, r, c, v, N, sparse_coarsen, coarsen, half, as_id, desc_out);
+        CUDA_TRY(cudaEventRecord(e1, ctx->stream));
+        CUDA_TRY(cudaEventSynchronize(e1));
+        if (ms_device) CUDA_TRY(cudaEventElapsedTime(ms_device, e0, e1));
+    } catch (...) {
+        cleanup();
+        throw;
+    }
+    cleanup();
+    if (st != GS_OK) return st;
+    GS_API_END
+}
+
+gs_status gs_download_array(gs_ctx *ctx, const char *key, void *host, uint64_t capacity_bytes, uint64_t *len, int *dtype)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ctx && key, "null argument");
+    auto it = ctx->arrays.find(key);
+    if (it == ctx->arrays.end()) return fail(GS_ERR_NOT_FOUND, std::string("no device array ") + key);
+    const dev_array &a = it->second;
+    if (len) *len = a.len;
+    if (dtype) *dtype = a.dtype;
+    if (host) {
+        GS_REQUIRE(capacity_bytes >= a.len * dsize(a.dtype), "buffer too small");
+        CUDA_TRY(cudaSetDevice(ctx->device));
+        ctx->join_async();
+        CUDA_TRY(cudaMemcpyAsync(host, a.ptr, a.len * dsize(a.dtype), cudaMemcpyDeviceToHost, ctx->stream));
+        CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     }
     GS_API_END
 }

@@ -89,6 +89,25 @@ template <typename ColT, typename ValT> const void *pick_nt(int N, int vec, bool
     }
 }
 
+template <int NT, typename ColT, typename ValT> const void *pick_short_g(int G)
+{
+    switch (G) {
+    case 4: return (const void *)row::k_b200_row_short<NT, ColT, ValT, 4>;
+    case 8: return (const void *)row::k_b200_row_short<NT, ColT, ValT, 8>;
+    case 16: return (const void *)row::k_b200_row_short<NT, ColT, ValT, 16>;
+    default: return nullptr;
+    }
+}
+template <typename ColT, typename ValT> const void *pick_short(int N, int G)
+{
+    switch (N) {
+    case 8: return pick_short_g<8, ColT, ValT>(G);
+    case 16: return pick_short_g<16, ColT, ValT>(G);
+    case 32: return pick_short_g<32, ColT, ValT>(G);
+    default: return nullptr;
+    }
+}
+
 template <typename ColT, typename ValT> cudaError_t rainbow(const launch_params &p, b200_row_plan *pl, cudaStream_t s)
 {
     size_t cb = p.a.nnz * sizeof(ColT) + 16, vb = p.a.nnz * sizeof(ValT) + 16;
@@ -288,6 +307,31 @@ cudaError_t b200_row_prepare(const launch_params &p, int sm_count, b200_row_plan
         cudaGetLastError();
         cudaFree(pl->col2), cudaFree(pl->val2), cudaFree(pl->w_nz), cudaFree(pl->w_row);
         pl->col2 = pl->val2 = nullptr, pl->w_nz = pl->w_row = nullptr;
+    }
+    // short rows and a panel that does not fit shared memory (C1: 37 non-zeros per row, 1.3 MB of B): a group of lanes per row, several
+    // rows in flight per warp (b200_row.cuh, k_b200_row_short).  GS_ROW_GROUP = lanes per row (4 / 8 / 16), 0 = off.
+    {
+        const double mean_len = pl->n_rows ? (double)p.a.nnz / pl->n_rows : 0.0;
+        (void)mean_len;
+        // opt-in (GS_ROW_GROUP = 4 / 8 / 16): on the C1 stand-in every setting measured slower than one warp per row (80 / 49 / 33 us against 26.7): the
+        // longest row (935 non-zeros) is walked by G lanes only, and the gathers of B are bound by L1 wavefronts either way (profiles/r2_c1_summary.md);
+        // the range kernel's chunk variant (kernels_merge.cu) is the answer for short rows
+        const int G = env_int("GS_ROW_GROUP", 0);
+        if (!pl->smem_b && G > 0 && (!sched || strcmp(sched, "short") == 0)) {
+            const void *sf = p.a.col_is_u16 ? (p.a.val_is_f16 ? pick_short<uint16_t, __half>(p.N, G) : pick_short<uint16_t, float>(p.N, G))
+                                            : (p.a.val_is_f16 ? pick_short<uint32_t, __half>(p.N, G) : pick_short<uint32_t, float>(p.N, G));
+            int occ = 0;
+            if (sf && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sf, 256, 0) == cudaSuccess && occ >= 1) {
+                pl->fn = sf, pl->threads = 256, pl->smem_bytes = 0;
+                const uint64_t want = ((uint64_t)pl->n_rows * G + 255) / 256; // one row per group is enough CTAs; more than fit at once only queue
+                pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)sm_count * occ, want));
+                snprintf(pl->name, sizeof pl->name, "k_b200_row_short<N%d,%s,%s,%d lanes per row,%d rows in flight per warp,%dx%d CTAs>", p.N, p.a.col_is_u16 ? "u16" : "u32",
+                         p.a.val_is_f16 ? "f16" : "f32", G, 32 / G, sm_count, occ);
+                *out = pl;
+                return cudaSuccess;
+            }
+            cudaGetLastError();
+        }
     }
     // pipelined variant: rows padded to 8, panel in shared memory, D chunks of A per warp in flight
     // (opt-in: measured slower than the plain kernel at every depth on C2, profiles/r1_row_v2_summary.md)

@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <new>
 #include <vector>
 
@@ -29,7 +30,13 @@ struct b200_merge_plan {
     uint32_t n_seg = 0, n_rows = 0;
     uint64_t part_bytes = 0; // the chain's own range array, as the kernel's format bytes count it
     int N = 0;
-    char name[128] = {0};
+    uint32_t *head_s0 = nullptr, *tail_s1 = nullptr, *ticket = nullptr, *zero_rows = nullptr; // ticket mode (see the chunk kernel)
+    float *partial = nullptr;
+    uint32_t n_zero = 0, max_sharers = 1;
+    uint32_t cap = 0;        // no segment is longer
+    bool stage = false;      // chunk kernel: the CTA's piece of the stream goes through shared memory
+    bool per_thread = false; // N <= 32: one lane per 16-byte chunk of B's row (k_b200_merge_chunk), else a group of 32 lanes
+    char name[160] = {0};
 };
 
 namespace {
@@ -42,6 +49,13 @@ struct merge_args {
     const uint32_t *seg_nz, *seg_row, *rowptr, *perm;
     uint32_t n_seg, begin_row;
     int N;
+    uint32_t nnz, stage_col_words; // staged chunk kernel: length of the stream, words of shared memory the ids take
+    // ticket mode (chunk kernel): rows shared by several segments are summed by the LAST segment to arrive, from partial sums in `partial`
+    const uint32_t *head_s0, *tail_s1; // first segment that shares segment s's first row / last segment that shares its last row
+    uint32_t *ticket;                  // one counter per segment (indexed by the first sharer of a row), zero between launches
+    float *partial;                    // [segment][first row, last row][N]
+    const uint32_t *zero_rows;         // rows with no stored non-zero: written as zeros by the kernel itself
+    uint32_t n_zero;
 };
 
 template <typename ValT, int NV, int LG> __device__ __forceinline__ void flush(ValT *C, int N, uint32_t out_row, int j, float (&acc)[NV], bool edge)
@@ -56,11 +70,71 @@ template <typename ValT, int NV, int LG> __device__ __forceinline__ void flush(V
     }
 }
 
-template <typename ColT, typename ValT, int LG, int NV> __global__ void __launch_bounds__(MERGE_WARPS * 32) k_b200_merge(merge_args p)
+
+// ---- ticket mode ------------------------------------------------------------------------------------------------------------------------------
+// No memset of C and no atomics on it.  A segment stores the rows that lie wholly inside it; for a row it shares with its neighbours it writes
+// its partial sum (fp32) to `partial`, fences, and takes a ticket from the row's counter; the segment that draws the last ticket reads every
+// sharer's partial in stream order and stores the row.  The order of the sum is fixed, so C is bit-reproducible from launch to launch (red.add
+// is not), a HALF row is rounded ONCE (red.add rounds every slice's partial to fp16: 2^-11 of the partial, which breaks SURVEY 8(d)'s gate
+// where slices cancel), and the launch is one kernel (a memset in front costs ~4 us of launch latency: scratch/launch_floor.sh).  The counters
+// are reset by the last arriver.  Rows without non-zeros come from a list.  The plan falls back to memset + red.add when a row is shared by
+// more than GS_MERGE_TICKET_MAX segments (a hub row cut into thousands: the last arriver would sum them alone).
+// Lane j of a group of LG holds NC columns: j + LG * t (STRIDED, the group kernel) or j * NC + t (the chunk kernel).
+template <int LG, int NC, bool STRIDED, typename ValT>
+__device__ __forceinline__ void ticket_flush(const merge_args &p, uint32_t g, uint32_t r, uint32_t s0, uint32_t s1, uint32_t slot, int j, unsigned gmask, const float (&acc)[NC], ValT *dst_row)
+{
+    constexpr int N = LG * NC;
+    auto colof = [&](int t) { return STRIDED ? j + LG * t : j * NC + t; };
+    float *mine = p.partial + ((size_t)g * 2 + slot) * N;
+#pragma unroll
+    for (int t = 0; t < NC; t++) __stcg(mine + colof(t), acc[t]);
+    __threadfence();
+    unsigned tk = 0;
+    if (LG > 1) __syncwarp(gmask);
+    if (j == 0) tk = atomicAdd(p.ticket + s0, 1u);
+    if (LG > 1) tk = __shfl_sync(gmask, tk, (threadIdx.x & 31) & ~(LG - 1));
+    if (tk != s1 - s0) return;
+    // every other sharer has published its partial
+    __threadfence();
+    if (j == 0) p.ticket[s0] = 0;
+    float sum[NC];
+#pragma unroll
+    for (int t = 0; t < NC; t++) sum[t] = 0.0f;
+    const uint32_t slot0 = p.seg_row[s0] == r ? 0u : 1u; // the first sharer holds the row as its last row unless the row begins with it
+#pragma unroll 4
+    for (uint32_t q = s0; q <= s1; q++) {
+        const float *src = p.partial + ((size_t)q * 2 + (q == s0 ? slot0 : 0u)) * N;
+#pragma unroll
+        for (int t = 0; t < NC; t++) sum[t] += __ldcg(src + colof(t));
+    }
+    if (!STRIDED && NC * (int)sizeof(ValT) == 16) {
+        uint4 o;
+        ValT *ov = (ValT *)&o;
+#pragma unroll
+        for (int t = 0; t < NC; t++) ov[t] = from_f32<ValT>(sum[t]);
+        *(uint4 *)(dst_row + j * NC) = o;
+    } else {
+#pragma unroll
+        for (int t = 0; t < NC; t++) dst_row[colof(t)] = from_f32<ValT>(sum[t]);
+    }
+}
+
+// rows without stored non-zeros (ticket mode has no memset): every thread of the grid takes its share
+template <typename ValT> __device__ __forceinline__ void zero_listed_rows(const merge_args &p, int N)
+{
+    const uint64_t total = (uint64_t)p.n_zero * N;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t zr = p.zero_rows[i / N];
+        ((ValT *)p.C)[(size_t)((p.perm ? p.perm[zr] : zr) + p.begin_row) * N + i % N] = from_f32<ValT>(0.0f);
+    }
+}
+
+template <typename ColT, typename ValT, int LG, int NV, bool TICKET> __global__ void __launch_bounds__(MERGE_WARPS * 32) k_b200_merge(merge_args p)
 {
     const uint32_t tid = blockIdx.x * (MERGE_WARPS * 32) + threadIdx.x;
     const uint32_t g = tid / LG;
     const int j = tid % LG, lane = threadIdx.x & 31;
+    if (TICKET) zero_listed_rows<ValT>(p, p.N);
     if (g >= p.n_seg) return; // whole groups leave together
     const unsigned mask = LG == 32 ? 0xffffffffu : (((1u << LG) - 1u) << (lane & ~(LG - 1)));
     const ColT *col = (const ColT *)p.col;
@@ -71,10 +145,20 @@ template <typename ColT, typename ValT, int LG, int NV> __global__ void __launch
     uint32_t r = p.seg_row[g];
     uint32_t row_begin = p.rowptr[r], e = p.rowptr[r + 1];
     bool edge = a != row_begin; // the first row began before this segment: others add to it too
+    bool first = true;          // still in the segment's first row
+    const uint32_t head_s0 = TICKET ? p.head_s0[g] : g, tail_s1 = TICKET ? p.tail_s1[g] : g;
     float acc[NV];
 #pragma unroll
     for (int v = 0; v < NV; v++) acc[v] = 0.0f;
     auto out = [&](uint32_t row) { return (p.perm ? p.perm[row] : row) + p.begin_row; };
+    // closing: the segment ends here (the row may go on in the next one)
+    auto flush_row = [&](bool as_edge, bool closing) {
+        if (TICKET && as_edge) {
+            ticket_flush<LG, NV, true, ValT>(p, g, r, first ? head_s0 : g, closing && b != e ? tail_s1 : g, first ? 0u : 1u, j, mask, acc, C + (size_t)out(r) * N);
+#pragma unroll
+            for (int v = 0; v < NV; v++) acc[v] = 0.0f;
+        } else flush<ValT, NV, LG>(C, N, out(r), j, acc, as_edge);
+    };
 
     for (uint32_t k = a; k < b; k += LG) {
         uint32_t c_mine = 0;
@@ -99,8 +183,8 @@ template <typename ColT, typename ValT, int LG, int NV> __global__ void __launch
                 const float vv = __shfl_sync(mask, v_mine, (int)((j0 + q) & (LG - 1)), LG);
                 if (j0 + q < cnt) {
                     while (kk == e) { // the row ended (possibly followed by empty rows: C keeps its zeros)
-                        if (e != row_begin) flush<ValT, NV, LG>(C, N, out(r), j, acc, edge);
-                        edge = false;
+                        if (e != row_begin) flush_row(edge, false);
+                        edge = false, first = false;
                         r++, row_begin = e, e = p.rowptr[r + 1];
                     }
 #pragma unroll
@@ -109,25 +193,232 @@ template <typename ColT, typename ValT, int LG, int NV> __global__ void __launch
             }
         }
     }
-    if (b > a) flush<ValT, NV, LG>(C, N, out(r), j, acc, edge || b != e); // the last row may go on in the next segment
+    if (b > a) flush_row(edge || b != e, true); // the last row may go on in the next segment
 }
 
-template <typename ColT, typename ValT> const void *pick(int N)
+// ---- narrow N: one 16-byte chunk of B's row per lane ---------------------------------------------------------------------------------------
+// ncu on the group kernel above at C1 (N = 8, merge_path_thread(32); profiles/r2_c1_summary.md): 14.1 M warp instructions for 1.79 M non-zeros,
+// the issue slots 52 % busy, short-scoreboard (shuffle) stalls on top -- with 8 lanes per segment and 4 bytes per lane a warp instruction
+// serves 4 non-zeros, and handing ids and values round by shuffle costs more than the arithmetic.  And the one-warp-per-row gather kernel
+// sits at the same 26 us for another reason: every 128-bit load whose 32 lanes touch 32 different lines costs ~2 cycles of the L1 wavefront
+// queue per line (B300_MICROARCH.md, "L1tex wavefront queue"), and it issues two per non-zero for a 32-byte row of B.
+// Here a segment belongs to LG = (row bytes) / 16 lanes and every lane owns ONE 16-byte chunk of the row (4 fp32 or 8 fp16 columns):
+// one load instruction per non-zero and group, one L1 wavefront per gathered row, ids and values read by every lane of the group itself
+// (the same address: one wavefront, no shuffle), four non-zeros in flight.  A warp instruction serves 32 / LG non-zeros (16 at N = 8 fp32).
+// Rows narrower than 16 bytes (N <= 2 fp32 ...) run with one lane per segment and scalar loads.  Edges as above (red.add), whole rows stored.
+template <size_t B> struct raw_of;
+template <> struct raw_of<2> { typedef uint16_t type; };
+template <> struct raw_of<4> { typedef uint32_t type; };
+__device__ __forceinline__ void red_add_chunk(float *dst, const float (&acc)[4])
+{
+#pragma unroll
+    for (int t = 0; t < 4; t++)
+        if (acc[t] != 0.0f) atomicAdd(dst + t, acc[t]);
+}
+__device__ __forceinline__ void red_add_chunk(__half *dst, const float (&acc)[8])
+{
+#pragma unroll
+    for (int t = 0; t < 4; t++) // packed: one red.global.add.noftz.f16x2 per pair of columns
+        if (acc[2 * t] != 0.0f || acc[2 * t + 1] != 0.0f) atomicAdd((__half2 *)dst + t, __floats2half2_rn(acc[2 * t], acc[2 * t + 1]));
+}
+template <int CH> __device__ __forceinline__ void red_add_chunk(float *dst, const float (&acc)[CH])
+{
+#pragma unroll
+    for (int t = 0; t < CH; t++)
+        if (acc[t] != 0.0f) atomicAdd(dst + t, acc[t]);
+}
+template <int CH> __device__ __forceinline__ void red_add_chunk(__half *dst, const float (&acc)[CH])
+{
+#pragma unroll
+    for (int t = 0; t < CH; t++)
+        if (acc[t] != 0.0f) atomicAdd(dst + t, __float2half_rn(acc[t]));
+}
+
+// Staging (STAGE): the segments of a CTA are consecutive, so the CTA's piece of the stream is ONE contiguous range of at most
+// (128 / LG) * cap non-zeros.  ncu on the unstaged kernel (C1, N = 8: 17.3 us, long-scoreboard 21 per issue, 45 % of the warp slots, L1 data pipe
+// 53 %) shows a latency chain: every lane walks its own segment, so each round is a DRAM round trip for ids / values (16 different lines per
+// load instruction) followed by an L2 round trip for B, cap / U times in a row.  Staged, the CTA copies its range to shared memory with
+// coalesced 128-bit loads, all in flight at once (one DRAM round trip), and the walk reads ids and values from shared memory: what is left
+// per round is the gather of B alone, eight rows in flight.  Shared memory is padded by one word per 32 so that lanes whose segments start
+// a regular distance apart (every slice 32 long) fall into different banks.
+template <typename T> __device__ __forceinline__ T staged_at(const uint32_t *sw, uint32_t idx)
+{
+    constexpr uint32_t EPW = 4 / sizeof(T); // elements per word
+    const uint32_t w = idx / EPW;
+    return ((const T *)(sw + w + (w >> 5)))[idx % EPW];
+}
+// eight elements (one 16-byte-aligned piece of the stream; `first` is a multiple of 8) from global to padded shared memory
+template <typename T> __device__ __forceinline__ void stage8(uint32_t *sw, const T *g, uint32_t chunk, uint32_t first, uint32_t total)
+{
+    constexpr int W = 2 * (int)sizeof(T); // words per eight elements: 4 or 8, never across a 32-word boundary
+    uint32_t w[W];
+    if (first + 8 <= total) {
+#pragma unroll
+        for (int q = 0; q < W / 4; q++) {
+            const uint4 x = __ldg((const uint4 *)(g + first) + q);
+            w[4 * q] = x.x, w[4 * q + 1] = x.y, w[4 * q + 2] = x.z, w[4 * q + 3] = x.w;
+        }
+    } else { // the end of the stream: nothing is read past it
+        typedef typename raw_of<sizeof(T)>::type R;
+        R *e = (R *)w;
+#pragma unroll
+        for (int t = 0; t < 8; t++) e[t] = first + t < total ? ((const R *)g)[first + t] : (R)0;
+    }
+    const uint32_t w0 = chunk * W, at = w0 + (w0 >> 5);
+#pragma unroll
+    for (int q = 0; q < W; q++) sw[at + q] = w[q];
+}
+__host__ __device__ constexpr uint32_t stage_words(uint32_t elems, uint32_t elem_bytes)
+{
+    return (elems * elem_bytes / 4) + (elems * elem_bytes / 4 >> 5) + 8; // padded, plus slack for the last (partly filled) piece
+}
+
+// programmatic dependent launch (ticket mode only: a memset node in front is not a kernel)
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename ColT, typename ValT, int NT, int LG, bool STAGE, bool TICKET> __global__ void __launch_bounds__(128) k_b200_merge_chunk(merge_args p)
+{
+    grid_dep_launch(); // the next launch on the stream may begin its prologue (plan tables and the stream of A only)
+    constexpr int CH = NT / LG;                               // columns per lane
+    constexpr bool VEC = CH * (int)sizeof(ValT) == 16;        // the lane's piece of a row is one 128-bit load
+    static_assert(NT % LG == 0 && (VEC || LG == 1), "chunking");
+    extern __shared__ __align__(16) uint32_t stage_mem[];
+    const uint32_t tid = blockIdx.x * 128 + threadIdx.x, g = tid / LG;
+    const int j = tid % LG;
+    const ColT *col = (const ColT *)p.col;
+    const ValT *val = (const ValT *)p.val, *B = (const ValT *)p.B + j * CH;
+    ValT *C = (ValT *)p.C + j * CH;
+    const bool mine = g < p.n_seg;
+    constexpr bool ticketed = TICKET;
+    const uint32_t a = mine ? p.seg_nz[g] : 0u, b = mine ? p.seg_nz[g + 1] : 0u;
+    uint32_t r = mine ? p.seg_row[g] : 0u;
+    const uint32_t head_s0 = mine && ticketed ? p.head_s0[g] : g, tail_s1 = mine && ticketed ? p.tail_s1[g] : g;
+    uint32_t base = 0;
+    const uint32_t *s_col = stage_mem, *s_val = stage_mem + p.stage_col_words;
+    if (STAGE) {
+        constexpr uint32_t SEGS = 128 / LG;
+        const uint32_t g0 = blockIdx.x * SEGS, g1 = min(g0 + SEGS, p.n_seg);
+        const uint32_t A1 = p.seg_nz[g1];
+        base = p.seg_nz[g0] & ~7u;
+#pragma unroll 2
+        for (uint32_t i = threadIdx.x; base + 8 * i < A1; i += 128) {
+            stage8<ColT>(stage_mem, col, i, base + 8 * i, p.nnz);
+            stage8<ValT>(stage_mem + p.stage_col_words, val, i, base + 8 * i, p.nnz);
+        }
+    }
+    // the row pointer is read one row ahead: the load for the next row end is in flight while this row is summed
+    uint32_t row_begin = p.rowptr[r], e = p.rowptr[r + 1], e_next = p.rowptr[r + 2];
+    if (STAGE) __syncthreads();
+    grid_dep_wait(); // B, C, the tickets and the partial sums belong to the launch before this one until it has completed
+    if (ticketed) zero_listed_rows<ValT>(p, NT);
+    if (!mine) return;
+    const unsigned gmask = LG == 1 ? 0u : (((1u << LG) - 1u) << ((threadIdx.x & 31) & ~(LG - 1)));
+    bool first = true; // still in the segment's first row
+    bool edge = a != row_begin;
+    float acc[CH];
+#pragma unroll
+    for (int t = 0; t < CH; t++) acc[t] = 0.0f;
+    // closing: the segment ends here (the row may go on in the next one)
+    auto flush_row = [&](bool as_edge, bool closing) {
+        ValT *dst = C + (size_t)((p.perm ? p.perm[r] : r) + p.begin_row) * NT;
+        if (as_edge && ticketed) {
+            ticket_flush<LG, CH, false, ValT>(p, g, r, first ? head_s0 : g, closing && b != e ? tail_s1 : g, first ? 0u : 1u, j, gmask, acc, (ValT *)p.C + (size_t)((p.perm ? p.perm[r] : r) + p.begin_row) * NT);
+        } else if (as_edge) red_add_chunk(dst, acc);
+        else if (VEC) {
+            uint4 o;
+            ValT *ov = (ValT *)&o;
+#pragma unroll
+            for (int t = 0; t < CH; t++) ov[t] = from_f32<ValT>(acc[t]);
+            *(uint4 *)dst = o;
+        } else {
+#pragma unroll
+            for (int t = 0; t < CH; t++) dst[t] = from_f32<ValT>(acc[t]);
+        }
+#pragma unroll
+        for (int t = 0; t < CH; t++) acc[t] = 0.0f;
+    };
+    constexpr int U = STAGE ? 8 : 4; // non-zeros whose loads are in flight together
+    for (uint32_t k = a; k < b; k += U) {
+        uint32_t c[U];
+        float v[U];
+        uint4 x[U];
+        float xs[U][VEC ? 1 : CH];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const bool in = k + u < b;
+            if (STAGE) c[u] = in ? (uint32_t)staged_at<ColT>(s_col, k + u - base) : 0u, v[u] = in ? to_f32(staged_at<ValT>(s_val, k + u - base)) : 0.0f;
+            else c[u] = in ? (uint32_t)col[k + u] : 0u, v[u] = in ? to_f32(val[k + u]) : 0.0f;
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const ValT *src = B + (size_t)c[u] * NT;
+            if (VEC) x[u] = __ldg((const uint4 *)src);
+            else {
+#pragma unroll
+                for (int t = 0; t < CH; t++) xs[u][VEC ? 0 : t] = to_f32(__ldg(src + t));
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (k + u < b) {
+                while (k + u == e) { // the row ended (possibly followed by empty rows)
+                    if (e != row_begin) flush_row(edge, false);
+                    edge = false, first = false;
+                    r++, row_begin = e, e = e_next, e_next = p.rowptr[r + 2];
+                }
+                if (VEC) {
+                    const ValT *xv = (const ValT *)&x[u];
+#pragma unroll
+                    for (int t = 0; t < CH; t++) acc[t] = fmaf(v[u], to_f32(xv[t]), acc[t]);
+                } else {
+#pragma unroll
+                    for (int t = 0; t < CH; t++) acc[t] = fmaf(v[u], xs[u][VEC ? 0 : t], acc[t]);
+                }
+            }
+        }
+    }
+    if (b > a) flush_row(edge || b != e, true);
+}
+
+// lanes per segment of the chunk kernel: bytes of a row of B / 16, at least 1
+template <typename ValT> constexpr int chunk_lanes(int N) { return N * (int)sizeof(ValT) >= 16 ? N * (int)sizeof(ValT) / 16 : 1; }
+
+template <typename ColT, typename ValT, bool STAGE, bool TICKET> const void *pick_thread_s(int N)
 {
     switch (N) {
-    case 1: return (const void *)k_b200_merge<ColT, ValT, 1, 1>;
-    case 2: return (const void *)k_b200_merge<ColT, ValT, 2, 1>;
-    case 4: return (const void *)k_b200_merge<ColT, ValT, 4, 1>;
-    case 8: return (const void *)k_b200_merge<ColT, ValT, 8, 1>;
-    case 16: return (const void *)k_b200_merge<ColT, ValT, 16, 1>;
-    case 32: return (const void *)k_b200_merge<ColT, ValT, 32, 1>;
-    case 64: return (const void *)k_b200_merge<ColT, ValT, 32, 2>;
-    case 128: return (const void *)k_b200_merge<ColT, ValT, 32, 4>;
-    case 256: return (const void *)k_b200_merge<ColT, ValT, 32, 8>;
-    case 512: return (const void *)k_b200_merge<ColT, ValT, 32, 16>;
+    case 1: return (const void *)k_b200_merge_chunk<ColT, ValT, 1, 1, STAGE, TICKET>;
+    case 2: return (const void *)k_b200_merge_chunk<ColT, ValT, 2, 1, STAGE, TICKET>;
+    case 4: return (const void *)k_b200_merge_chunk<ColT, ValT, 4, 1, STAGE, TICKET>;
+    case 8: return (const void *)k_b200_merge_chunk<ColT, ValT, 8, chunk_lanes<ValT>(8), STAGE, TICKET>;
+    case 16: return (const void *)k_b200_merge_chunk<ColT, ValT, 16, chunk_lanes<ValT>(16), STAGE, TICKET>;
+    case 32: return (const void *)k_b200_merge_chunk<ColT, ValT, 32, chunk_lanes<ValT>(32), STAGE, TICKET>;
     default: return nullptr;
     }
 }
+template <typename ColT, typename ValT> const void *pick_thread(int N, bool stage, bool ticket)
+{
+    return stage ? (ticket ? pick_thread_s<ColT, ValT, true, true>(N) : pick_thread_s<ColT, ValT, true, false>(N))
+                 : (ticket ? pick_thread_s<ColT, ValT, false, true>(N) : pick_thread_s<ColT, ValT, false, false>(N));
+}
+
+template <typename ColT, typename ValT, bool TICKET> const void *pick_t(int N)
+{
+    switch (N) {
+    case 1: return (const void *)k_b200_merge<ColT, ValT, 1, 1, TICKET>;
+    case 2: return (const void *)k_b200_merge<ColT, ValT, 2, 1, TICKET>;
+    case 4: return (const void *)k_b200_merge<ColT, ValT, 4, 1, TICKET>;
+    case 8: return (const void *)k_b200_merge<ColT, ValT, 8, 1, TICKET>;
+    case 16: return (const void *)k_b200_merge<ColT, ValT, 16, 1, TICKET>;
+    case 32: return (const void *)k_b200_merge<ColT, ValT, 32, 1, TICKET>;
+    case 64: return (const void *)k_b200_merge<ColT, ValT, 32, 2, TICKET>;
+    case 128: return (const void *)k_b200_merge<ColT, ValT, 32, 4, TICKET>;
+    case 256: return (const void *)k_b200_merge<ColT, ValT, 32, 8, TICKET>;
+    case 512: return (const void *)k_b200_merge<ColT, ValT, 32, 16, TICKET>;
+    default: return nullptr;
+    }
+}
+template <typename ColT, typename ValT> const void *pick(int N, bool ticket = false) { return ticket ? pick_t<ColT, ValT, true>(N) : pick_t<ColT, ValT, false>(N); }
 
 int env_int(const char *name, int dflt)
 {
@@ -187,8 +478,15 @@ cudaError_t b200_merge_prepare(const launch_params &p, const uint32_t *parts_dev
     if (parts[0] != 0 || parts[n_parts] > nnz || rowptr[n_rows] < parts[n_parts]) return fail(cudaErrorInvalidValue);
 
     // segments: the chain's parts, long ones cut into equal slices (GS_MERGE_CAP non-zeros at most)
-    const int LG = p.N < 32 ? p.N : 32;
-    const uint32_t cap = (uint32_t)std::max(LG, env_int("GS_MERGE_CAP", LG == 32 ? 512 : 32 * LG));
+    const bool per_thread = p.N <= 32 && env_int("GS_MERGE_THREAD", 1) != 0;
+    const int LG = per_thread ? (p.a.val_is_f16 ? chunk_lanes<__half>(p.N) : chunk_lanes<float>(p.N)) : p.N < 32 ? p.N : 32;
+    const uint32_t cap = (uint32_t)std::max(LG, env_int("GS_MERGE_CAP", per_thread ? (LG >= 4 ? 64 : 32) : LG == 32 ? 512 : 32 * LG)); // chunk kernel: every lane of a group walks the whole segment
+    pl->per_thread = per_thread, pl->cap = cap;
+    if (per_thread) { // staging needs 16-byte aligned streams and at most 48 KB for a CTA's piece
+        const uint32_t elems = (128 / LG) * cap + 8;
+        const uint64_t bytes = 4ull * (stage_words(elems, p.a.col_is_u16 ? 2 : 4) + stage_words(elems, p.a.val_is_f16 ? 2 : 4));
+        pl->stage = env_int("GS_MERGE_STAGE", LG <= 4) != 0 && bytes <= 48 * 1024 && (((uintptr_t)p.a.col | (uintptr_t)p.a.val) & 15) == 0;
+    }
     std::vector<uint32_t> seg_nz, seg_row;
     for (uint32_t i = 0; i < n_parts; i++) {
         const uint32_t a = parts[i], b = parts[i + 1];
@@ -209,9 +507,38 @@ cudaError_t b200_merge_prepare(const launch_params &p, const uint32_t *parts_dev
         return e2 != cudaSuccess ? e2 : cudaMemcpyAsync(*dst, v.data(), v.size() * 4, cudaMemcpyHostToDevice, s);
     };
     if ((e = up(&pl->seg_nz, seg_nz)) != cudaSuccess || (e = up(&pl->seg_row, seg_row)) != cudaSuccess || (e = up(&pl->rowptr, rowptr)) != cudaSuccess) return fail(e);
+    // ticket mode: who shares which row
+    if (p.a.begin_row == 0 && env_int("GS_MERGE_TICKET", 1) != 0) { // (a plan on a sub-matrix keeps the memset of the whole of C)
+        const uint32_t n_seg = pl->n_seg;
+        std::vector<uint32_t> head(n_seg), tail(n_seg), zero;
+        auto seg_of = [&](uint32_t nz) { // the segment that holds stream position nz
+            const uint32_t q = (uint32_t)(std::upper_bound(seg_nz.begin(), seg_nz.end(), nz) - seg_nz.begin());
+            return std::min(q ? q - 1 : 0u, n_seg - 1);
+        };
+        uint32_t most = 1;
+        for (uint32_t q = 0; q < n_seg; q++) {
+            const uint32_t a = seg_nz[q], b = seg_nz[q + 1], f = seg_row[q];
+            const uint32_t l = (uint32_t)(std::upper_bound(rowptr.begin(), rowptr.end(), b - 1) - rowptr.begin()) - 1;
+            head[q] = rowptr[f] < a ? seg_of(rowptr[f]) : q;
+            tail[q] = rowptr[l + 1] > b ? seg_of(rowptr[l + 1] - 1) : q;
+            most = std::max(most, std::max(q - head[q], tail[q] - q) + 1);
+        }
+        for (uint32_t r = 0; r < n_rows; r++)
+            if (rowptr[r + 1] == rowptr[r] || rowptr[r] >= parts[n_parts]) zero.push_back(r);
+        for (uint32_t r = n_rows; r < p.a.rows; r++) zero.push_back(r);
+        pl->max_sharers = most;
+        // (the partial sums take 8 N bytes per segment: beyond GS_MERGE_TICKET_MB the plan stays with red.add)
+        if (most <= (uint32_t)env_int("GS_MERGE_TICKET_MAX", 64) && (uint64_t)n_seg * 2 * p.N * sizeof(float) <= (uint64_t)env_int("GS_MERGE_TICKET_MB", 512) << 20) {
+            if ((e = up(&pl->head_s0, head)) != cudaSuccess || (e = up(&pl->tail_s1, tail)) != cudaSuccess) return fail(e);
+            if (!zero.empty() && (e = up(&pl->zero_rows, zero)) != cudaSuccess) return fail(e);
+            pl->n_zero = (uint32_t)zero.size();
+            if ((e = cudaMalloc((void **)&pl->ticket, (size_t)n_seg * 4)) != cudaSuccess || (e = cudaMemsetAsync(pl->ticket, 0, (size_t)n_seg * 4, s)) != cudaSuccess) return fail(e);
+            if ((e = cudaMalloc((void **)&pl->partial, (size_t)n_seg * 2 * p.N * sizeof(float))) != cudaSuccess) return fail(e);
+        }
+    }
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(e);
-    snprintf(pl->name, sizeof pl->name, "k_b200_merge<N%d,%s,%s,%d lanes/segment,%u segments of <=%u nnz from %u parts>", p.N, p.a.col_is_u16 ? "u16" : "u32", p.a.val_is_f16 ? "f16" : "f32",
-             LG, pl->n_seg, cap, n_parts);
+    snprintf(pl->name, sizeof pl->name, "k_b200_merge%s<N%d,%s,%s,%d lane%s/segment,%s%s%u segments of <=%u nnz from %u parts>", per_thread ? "_chunk" : "", p.N, p.a.col_is_u16 ? "u16" : "u32",
+             p.a.val_is_f16 ? "f16" : "f32", LG, LG > 1 ? "s" : "", pl->stage ? "staged," : "", pl->ticket ? "tickets," : "", pl->n_seg, cap, n_parts);
     *out = pl;
     return cudaSuccess;
 }
@@ -221,7 +548,36 @@ cudaError_t b200_merge_launch(const b200_merge_plan *pl, const launch_params &p,
     merge_args a;
     a.col = p.a.col, a.val = p.a.val, a.B = p.B, a.C = p.C, a.seg_nz = pl->seg_nz, a.seg_row = pl->seg_row, a.rowptr = pl->rowptr, a.perm = p.a.perm;
     a.n_seg = pl->n_seg, a.begin_row = p.a.begin_row, a.N = pl->N;
-    const void *fn = p.a.col_is_u16 ? (p.a.val_is_f16 ? pick<uint16_t, __half>(pl->N) : pick<uint16_t, float>(pl->N)) : (p.a.val_is_f16 ? pick<uint32_t, __half>(pl->N) : pick<uint32_t, float>(pl->N));
+    a.nnz = (uint32_t)p.a.nnz, a.stage_col_words = 0;
+    a.head_s0 = pl->head_s0, a.tail_s1 = pl->tail_s1, a.ticket = pl->ticket, a.partial = pl->partial, a.zero_rows = pl->zero_rows, a.n_zero = pl->n_zero;
+    if (pl->per_thread) {
+        const int lanes = p.a.val_is_f16 ? chunk_lanes<__half>(pl->N) : chunk_lanes<float>(pl->N);
+        // the plan's decision holds for the arrays it was made on; a stream that moved to an unaligned address runs unstaged
+        const bool stage = pl->stage && (((uintptr_t)p.a.col | (uintptr_t)p.a.val) & 15) == 0;
+        const bool tk = pl->ticket != nullptr;
+        const void *tf = p.a.col_is_u16 ? (p.a.val_is_f16 ? pick_thread<uint16_t, __half>(pl->N, stage, tk) : pick_thread<uint16_t, float>(pl->N, stage, tk))
+                                        : (p.a.val_is_f16 ? pick_thread<uint32_t, __half>(pl->N, stage, tk) : pick_thread<uint32_t, float>(pl->N, stage, tk));
+        if (!tf) return cudaErrorInvalidValue;
+        void *targs[] = {&a};
+        const uint32_t elems = (128 / lanes) * pl->cap + 8;
+        a.stage_col_words = stage_words(elems, p.a.col_is_u16 ? 2 : 4);
+        const size_t smem = stage ? 4ull * (a.stage_col_words + stage_words(elems, p.a.val_is_f16 ? 2 : 4)) : 0;
+        const uint64_t threads = (uint64_t)pl->n_seg * lanes;
+        // programmatic dependent launch whenever the engine allows it: the kernel touches nothing but the plan's tables and the stream of A
+        // before griddepcontrol.wait, so it does not matter who ran before it.  Not behind the memset of the red.add mode (a memset node
+        // is not a kernel: the attribute would be ignored, and the order must hold).
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof cfg);
+        cfg.gridDim = dim3((unsigned)((threads + 127) / 128)), cfg.blockDim = dim3(128), cfg.dynamicSmemBytes = smem, cfg.stream = s;
+        cfg.attrs = attr, cfg.numAttrs = (p.pdl && pl->ticket) ? 1 : 0;
+        return cudaLaunchKernelExC(&cfg, tf, targs);
+    }
+    const bool tk = pl->ticket != nullptr;
+    const void *fn = p.a.col_is_u16 ? (p.a.val_is_f16 ? pick<uint16_t, __half>(pl->N, tk) : pick<uint16_t, float>(pl->N, tk))
+                                    : (p.a.val_is_f16 ? pick<uint32_t, __half>(pl->N, tk) : pick<uint32_t, float>(pl->N, tk));
     if (!fn) return cudaErrorInvalidValue;
     const int LG = pl->N < 32 ? pl->N : 32;
     const uint64_t threads = (uint64_t)pl->n_seg * LG;
@@ -234,10 +590,14 @@ void b200_merge_free(b200_merge_plan *pl)
 {
     if (!pl) return;
     cudaFree(pl->seg_nz), cudaFree(pl->seg_row), cudaFree(pl->rowptr);
+    cudaFree(pl->head_s0), cudaFree(pl->tail_s1), cudaFree(pl->ticket), cudaFree(pl->zero_rows), cudaFree(pl->partial);
     delete pl;
 }
 
 const char *b200_merge_kernel_name(const b200_merge_plan *pl) { return pl ? pl->name : ""; }
+
+// red.add mode: C must be zero when the kernel starts; ticket mode writes every row itself
+bool b200_merge_needs_zero(const b200_merge_plan *pl) { return !pl || !pl->ticket; }
 
 // what one launch streams: A once, the segment table and the row pointer, B and C once each
 uint64_t b200_merge_bytes(const b200_merge_plan *pl, uint64_t nnz, uint64_t idx_bytes, uint64_t val_bytes, uint64_t rows, uint64_t cols)

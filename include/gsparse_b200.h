@@ -209,6 +209,24 @@ gs_status gs_upload_session(gs_ctx *ctx, const gsh_session *s, int half);
  * a plan reaches them by setting gs_plan_desc.sub_matrix_id = as_id */
 gs_status gs_upload_session_as(gs_ctx *ctx, const gsh_session *s, int half, int as_id);
 
+/*  the chain's transform steps run on the DEVICE instead of the host pipeline: from a row-major COO already
+ * on the device (u32 ids, fp32 values; row ids ascending) to the arrays a plan of `family` binds, stored under sub-matrix id `as_id`
+ * exactly as gs_upload_session_as would have stored the host pipeline's -- byte for byte the same device arrays (tests/
+ * test_device_transform_gpu.py).  Families: GS_FAMILY_THREAD_TOTAL = sort_operator (sort_operator.cc:70-108: get_row_order_by_length,
+ * reorder_{val,col,row}_by_index, remove_empty_row_in_end_of_sub_matrix) + fixed_interval_row_direction_thread_blocking_operator(1,
+ * col pad to sparse_coarsen; ...thread_blocking_operator.cc:482-565); GS_FAMILY_WARP_TOTAL = fixed_interval_row_direction_warp_
+ * blocking_operator(1), no sort, no pad; GS_FAMILY_THREAD_BITMAP = fixed_interval_nnz_direction_thread_blocking_operator(32, pad) +
+ * thread_bit_map_operator (thread_bit_map.cc, segment_{ptr,empty_flag,empty_row_indices}.cc).  desc_out is what
+ * gsh_session_plan_desc would return after the driver's chain (token_test.cc:1003-1092, :1188-1249, :1319-1391), launch shape
+ * included.  GS_ERR_PADDING_RATE where the reference's padding assert fires; GS_ERR_UNSUPPORTED for the other families. */
+gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t cols, uint64_t nnz, const uint32_t *row_dev, const uint32_t *col_dev, const float *val_dev, int N,
+                              int sparse_coarsen, int coarsen, int half, int as_id, gs_plan_desc *desc_out);
+/* the same from host arrays (H2D, then the device passes); ms_device = the device time of the passes alone (CUDA events), may be NULL */
+gs_status gs_transform_host_coo(gs_ctx *ctx, int family, uint64_t rows, uint64_t cols, uint64_t nnz, const uint32_t *row, const uint32_t *col, const float *val, int N,
+                                int sparse_coarsen, int coarsen, int half, int as_id, gs_plan_desc *desc_out, float *ms_device);
+/* a device array of the context back on the host (tests, dumps): len in elements, dtype = its device gs_dtype; host may be NULL to ask for the size */
+gs_status gs_download_array(gs_ctx *ctx, const char *key, void *host, uint64_t capacity_bytes, uint64_t *len, int *dtype);
+
 gs_status gs_plan_create(gs_ctx *ctx, const gs_plan_desc *desc, int N, int half, gs_plan **out);
 void gs_plan_destroy(gs_plan *p);
 /* override the family the plan launches with (e.g. GS_FAMILY_B200_ROW_SMEM on a thread_total chain) */

@@ -121,3 +121,85 @@ def test_total_families_refuse_multi_row_blocks(engine):
         plan.set_kernel("b200_row_smem")
     plan.set_kernel("auto")
     assert "k_b200_merge" in plan.kernel_name
+
+
+@pytest.mark.parametrize("stage,ticket", [(0, 0), (1, 0), (0, 1), (1, 1)])
+@pytest.mark.parametrize("N,half", [(8, False), (2, False), (32, False), (16, True), (8, True)])
+def test_chunk_kernel_modes(engine, monkeypatch, stage, ticket, N, half):
+    """the narrow-N variant (one 16-byte chunk of B's row per lane) in its four modes: the CTA's piece of the stream staged through shared memory or
+    not; rows shared between segments completed by red.add into a zeroed C, or by tickets (partials summed in stream order by the last segment to
+    arrive: no memset, and the result is the same bits on every launch).  Matrices with empty rows in the middle and at the end, sorted chains
+    (the row permutation applies to the zero rows too), slices of 5 non-zeros so that every row of the long-row matrix is shared."""
+    from generalsparse_b200 import api, synth
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    monkeypatch.setenv("GS_MERGE_STAGE", str(stage))
+    monkeypatch.setenv("GS_MERGE_TICKET", str(ticket))
+    rr, rc = synth.synth_matrix("ragged", 700, 450, seed=2, mean_len=9.0, empty_frac=0.3)
+    keep = rr < 640  # sixty trailing rows without a non-zero
+    lr, lc = synth.synth_matrix("lognormal", 900, 1200, seed=3, mean_len=60.0)
+    for name, rows, cols, r, c, cap, ops in (
+            ("ragged+tail", 700, 450, rr[keep], rc[keep], 5, CHAINS["merge_path_thread"](N)),
+            ("ragged sorted", 700, 450, rr[keep], rc[keep], 32, CHAINS["sort_merge_path_thread"](N)),
+            ("long rows", 900, 1200, lr, lc, 16, None),
+            ("long rows balanced", 900, 1200, lr, lc, 32, CHAINS["balanced_thread"](N))):
+        monkeypatch.setenv("GS_MERGE_CAP", str(cap))
+        ip = csr_from_coo(rows, r)
+        for ones in (True, False):
+            vals = None if ones else synth.synth_values(len(r), seed=9)
+            B = np.ones((cols, N), np.float32) if ones else synth.synth_dense(cols, N, seed=9)
+            if half and not ones:
+                vals, B = vals.astype(np.float16).astype(np.float32), B.astype(np.float16).astype(np.float32)
+            api.config_set("DENSE_MATRIX_SIZE", N)
+            api.config_set("VECTOR_WIDTH", min(N, 32))
+            s = api.Session(api.MetaDataSet.from_coo(rows, cols, r, c, vals))
+            if ops is None:
+                s.run_family("warp_total", N, 1, 1)  # one row per block: the ranges are the rows, cut into slices of <= cap
+            else:
+                for op in ops:
+                    s.add_and_run(op[0], *op[1:])
+                s.compile()
+            engine.upload_session(s, half=half, as_id=73)
+            plan = engine.plan(s, N, half=half, kernel="b200_merge", sub_matrix_id=73)
+            kn = plan.kernel_name
+            assert "k_b200_merge_chunk" in kn and ("staged," in kn) == bool(stage), kn
+            if ticket:
+                assert "tickets," in kn, kn  # no row of these matrices is shared by more than 64 slices
+            plan.set_dense(B)
+            plan.run(1)
+            C = plan.output()
+            if ones:
+                ref = oracle_spmm_f32(rows, N, ip, c, np.ones(len(r), np.float32), B)
+                if not half or ref.max() <= 2048:
+                    assert np.array_equal(C.astype(np.float32), ref), (name, kn)
+            else:
+                _check(C, oracle_spmm_f64acc(rows, N, ip, c, vals, B), oracle_spmm_absrow(rows, N, ip, c, vals, B), half)
+            plan.run(5)  # back to back (programmatic dependent launch in ticket mode): the counters are back at zero after every launch
+            C2 = plan.output()
+            if ticket:
+                assert np.array_equal(C2.view(np.uint8), C.view(np.uint8)), (name, kn)  # fixed order of the sum: the same bits
+            elif ones and (not half or ref.max() <= 2048):
+                assert np.array_equal(C2.astype(np.float32), ref)
+
+
+def test_chunk_kernel_hub_row_keeps_red_add(engine, monkeypatch):
+    """a row cut into more than GS_MERGE_TICKET_MAX slices: the plan stays with memset + red.add (the last arriver would sum thousands of partials alone)"""
+    from generalsparse_b200 import api, synth
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f64acc
+    monkeypatch.setenv("GS_MERGE_TICKET", "1")
+    rows, cols, N = 300, 5000, 8
+    r, c = synth.synth_matrix("uniform", rows, cols, seed=7, density=0.004)
+    hub = np.arange(0, cols, 1, dtype=r.dtype)
+    keep = r != 17
+    r, c = np.concatenate([r[keep], np.full(len(hub), 17, r.dtype)]), np.concatenate([c[keep], hub])
+    order = np.lexsort((c, r))
+    r, c = r[order], c[order]
+    vals, B = synth.synth_values(len(r), seed=1), synth.synth_dense(cols, N, seed=1)
+    s = api.Session(api.MetaDataSet.from_coo(rows, cols, r, c, vals))
+    s.run_family("warp_total", N, 1, 1)
+    engine.upload_session(s, as_id=74)
+    plan = engine.plan(s, N, kernel="b200_merge", sub_matrix_id=74)
+    assert "k_b200_merge_chunk" in plan.kernel_name and "tickets," not in plan.kernel_name, plan.kernel_name
+    plan.set_dense(B)
+    plan.run(2)
+    ip = csr_from_coo(rows, r)
+    _check(plan.output(), oracle_spmm_f64acc(rows, N, ip, c, vals, B), oracle_spmm_absrow(rows, N, ip, c, vals, B), False)

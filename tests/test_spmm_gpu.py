@@ -527,3 +527,32 @@ def test_b200_sp24_metadata_lands_in_tensor_memory_as_laid_out(engine, monkeypat
                     w |= (int(i0) | (int(i1) << 2)) << (16 * half + 4 * q)
             want[L, j] = w
     assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("N", [8, 16, 32])
+@pytest.mark.parametrize("half", [False, True], ids=["fp32", "half"])
+def test_b200_row_short_rows(engine, monkeypatch, N, half):
+    """(opt-in variant, GS_ROW_GROUP) short rows with a dense panel too large for shared memory (BASELINE's C1 shape in small): a group of 4 / 8 / 16 lanes per row, several rows
+    in flight per warp; sorted (thread_total chain) and unsorted (warp_total chain) rows, empty rows, one long row; exact on ones, 8(d) gate on values"""
+    from generalsparse_b200 import synth
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_absrow, oracle_spmm_f32, oracle_spmm_f64acc
+    monkeypatch.setenv("GS_ROW_GROUP", "8")
+    cols = 60000
+    mats = [("lognormal", 3000, dict(mean_len=37.4)), ("ragged", 2500, dict(mean_len=9.0, empty_frac=0.3)), ("lognormal", 900, dict(mean_len=150.0))]
+    for i, (kind, nrows, kw) in enumerate(mats):
+        rr, cc = _matrix(kind, nrows, cols, seed=41 + i, **kw)
+        indptr = csr_from_coo(nrows, rr)
+        for chain, S in (("thread_total", 4), ("warp_total", 1)):
+            B1 = np.ones((cols, N), dtype=np.float32)
+            C, plan = _run(engine, chain, nrows, cols, rr, cc, None, B1, N, S, 1, half=half, kernel="b200_row_smem")
+            assert "k_b200_row_short" in plan.kernel_name, plan.kernel_name
+            ref = oracle_spmm_f32(nrows, N, indptr, cc, np.ones(len(rr), np.float32), B1)
+            assert np.array_equal(C.astype(np.float32), ref), plan.kernel_name
+            vals = synth.synth_values(len(rr), seed=5)
+            B = synth.synth_dense(cols, N, seed=5)
+            if half:
+                vals, B = vals.astype(np.float16).astype(np.float32), B.astype(np.float16).astype(np.float32)
+            C, plan = _run(engine, chain, nrows, cols, rr, cc, vals, B, N, S, 1, half=half, kernel="b200_row_smem")
+            ref = oracle_spmm_f64acc(nrows, N, indptr, cc, vals, B)
+            absrow = oracle_spmm_absrow(nrows, N, indptr, cc, vals, B)
+            _check(C, ref, absrow * (1e-4 if half else 1e-1), 1e-2 if half else 1e-5, abs_floor=2.0 ** -25 if half else 0.0)
