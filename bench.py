@@ -137,6 +137,24 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(inside[0][1]), "reasons": reasons, "samples": len(inside)}
 
 
+def device_transform_block(eng, sess, family, rows, cols, r, c, v, N, S, half, host_id, host_pipeline_s):
+    """the chain's transform steps as device passes (gs_transform_host_coo) beside the host pipeline that built the timed plan:
+    every array the chain registers must come out byte-equal; device_ms = CUDA events around the passes alone, wall_ms adds the H2D of the COO."""
+    eng.transform_coo(family, rows, cols, r, c, v, N, S, 1, half=half, as_id=900)  # warm-up (allocations, module load)
+    t0 = time.perf_counter()
+    dd, dev_ms = eng.transform_coo(family, rows, cols, r, c, v, N, S, 1, half=half, as_id=900)
+    wall = time.perf_counter() - t0
+    keys = [k[: k.rfind("_")] for k in sess.deps()]
+    same = True
+    for k in keys:
+        a, b = eng.download_array("%s_%d" % (k, host_id)), eng.download_array(k + "_900")
+        same = same and a.dtype == b.dtype and a.shape == b.shape and bool(np.array_equal(a.view(np.uint8), b.view(np.uint8)))
+    hd = sess.plan_desc()
+    same = same and (hd.stored_nnz, tuple(hd.grid), tuple(hd.block), hd.vector_width) == (dd.stored_nnz, tuple(dd.grid), tuple(dd.block), dd.vector_width)
+    return {"device_ms": dev_ms, "wall_ms_with_h2d_of_coo": wall * 1e3, "host_pipeline_s": host_pipeline_s, "arrays": len(keys), "identical_to_host_pipeline": bool(same),
+            "speedup_vs_host_pipeline": host_pipeline_s * 1e3 / max(dev_ms, 1e-6)}
+
+
 def cusparse_yardstick(rows, cols, r, c, v, B_t, steps=200):
     """the one external sanity bar the reference ships -- baseline/base_cusparse/spmm.cu:82-162, cusparseSpMM on CSR with
     10 warm-ups, gflops = 2 * nnz * N / t -- here through torch's CSR matmul (cuSPARSE SpMM underneath; a library call, comparison only, never
@@ -228,6 +246,9 @@ def c4_block(args, rank, world, local, dist):
         c4_kernel = None if args.c4_kernel == "reference" else args.c4_kernel
     plan = eng.plan(sess, N, kernel=c4_kernel)
     plan.set_dense(B)
+    dtf = None
+    if args.family in ("thread_bit_map", "warp_total", "thread_total"):
+        dtf = device_transform_block(eng, sess, args.family, my_rows, rows, r, c, v, N, 1, False, plan.desc.sub_matrix_id, host_pipeline_s)
     dev = torch.device("cuda", local)
     stream = torch.cuda.ExternalStream(eng.stream, device=dev)
     # C of this rank lands in place in a full-size C (rows x N): what the optional all-gather replicates
@@ -336,7 +357,7 @@ def c4_block(args, rank, world, local, dist):
                          "note": "B and C counted once for the whole job; traffic = ncu dram bytes of one launch on 1 GPU (profiles/traffic.json, a committed capture)"},
             "parity": {"rows_checked_per_rank": checked, "includes_longest_row_of_every_block": True, "tolerance": "1e-5*|ref| + 1e-6*sum|a*b|", "worst_rel_err": float(-ok[2].item()),
                        "ok_on_every_rank": bool(ok[0].item() > 0.5)},
-            "clocks": clocks, "allgather": ag, "yardstick_cusparse": yard, "generate_s": round(gen_s, 1), "host_pipeline_s": round(host_pipeline_s, 1)}
+            "clocks": clocks, "allgather": ag, "yardstick_cusparse": yard, "generate_s": round(gen_s, 1), "host_pipeline_s": round(host_pipeline_s, 1), "device_transform": dtf}
 
 
 def run_c4(args, rank, world, local):
@@ -440,6 +461,7 @@ def main():
     parity = {"max_rel_err_vs_f64": -float(par[1].item()), "tolerance": "1e-2*|ref| + 1e-6*sum|a*b| + 2^-25", "ok": bool(par[0].item() > 0.5),
               "ranks_checked": world}
     del C, ref, absrow, err
+    dtf = device_transform_block(eng, sess, "thread_total", my_rows, COLS, r, c, v, N, 8, half, 0, host_pipeline_s)
 
     def barrier():
         if world > 1:
@@ -581,6 +603,7 @@ def main():
                 "api": "gs_spmm_host_async per step (pinned B in, pinned C out) + one gs_synchronize; results equal the blocking call: %s" % e2e_ok,
                 "blocking_ms_per_step": e2e_sync_s / e2e_steps * 1e3, "host_enqueue_ms_per_step": e2e_enqueue_s / e2e_steps * 1e3},
         "gpu_launches": args.steps * launch_count, "clocks": clocks, "parity": parity, "c4": c4, "yardstick_cusparse": yard,
+        "device_transform": dtf,
     }
     if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1

@@ -466,9 +466,13 @@ static std::vector<auto_choice> auto_candidates(const gs_plan *p)
             double t = (nnz * (idxb + vb) + bc) / (0.70 * bw) * (panel ? 1.0 : 2.2);
             t = std::max(t, nnz * N / 18.8e6);
             if (mean_len < 64) t *= 1.0 + (64 - mean_len) / 64.0;
-            // short rows (one warp per row) with the panel in global memory: measured on the C1 stand-in (37 non-zeros per row, fp32):
-            // 26.7 us at N = 8, 148 us at N = 32 (profiles/r2_c1_kernels.log)
-            if (mean_len < 64 && !panel) t = std::max(t, nnz * N / (N <= 8 ? 0.54e6 : 0.39e6));
+            // the panel of B in global memory: the gathers decide.  Non-zeros per us by the bytes of one row of B, measured on C5's uniform 65 536^2
+            // matrix (655 per row; profiles/r2_c5_sweep_narrow.md): 286 K at 16 B, 165 K at 32, 75 K at 64, 30 K at 128; shorter rows run at 0.6
+            // (banded, 129 per row) and 0.3 - 0.4 (C1 stand-in, 37 per row) of that
+            if (!panel) {
+                const double rb = N * vb, rate = rb <= 16 ? 286e3 : rb <= 32 ? 165e3 : rb <= 64 ? 75e3 : 30e3;
+                t = nnz / (rate * std::min(1.0, 0.25 + mean_len / 400.0));
+            }
             c.push_back({GS_FAMILY_B200_ROW_SMEM, t + 2.5});
         }
         // the tensor-core layouts are built for weight-sized matrices: their host builders lay the whole rows x cols grid out before
@@ -504,17 +508,19 @@ static std::vector<auto_choice> auto_candidates(const gs_plan *p)
         // B200 kernel for merge-path / balanced / column-direction chains and for wide N on matrices too large for the tensor-core layouts
         const double gather = nnz * N * vb, l2_bw = 2.5 * bw;
         const bool b_in_l2 = cols * N * vb <= 96e6;
-        // a segment is walked serially by its lanes; non-zeros per microsecond measured on C5's 65 536^2 uniform matrix, fp32
-        // (profiles/r2_c5_sweep.md): 15 K at N = 1 (one lane per segment), 89 K at N = 8, 40 K at N = 32, 29 K at N = 128, 5.5 K at N = 512;
-        // fp16 values load 2 bytes per lane and run at about half of that from N = 16 up
-        static const double mn[] = {1, 2, 4, 8, 16, 32, 64, 128, 256, 512}, mr[] = {15e3, 29e3, 50e3, 89e3, 65e3, 40e3, 35.5e3, 28.6e3, 13.9e3, 5.5e3};
+        // a segment is walked serially by its lanes; non-zeros per microsecond measured on C5's 65 536^2 uniform matrix (profiles/r2_c5_sweep.md,
+        // r2_c5_sweep_narrow.md): the chunk kernel 110 K at N = 1, 83 K at 2, 137 K at 4 (the first width with a 16-byte row), 100 K at 8, 75 K at
+        // 16, 68 K at 32, fp32 and fp16 alike (C1 stand-in: 100 / 89 / 77 K at N = 8 / 16 / 32); the group kernel 35.5 K at N = 64, 29 K at 128,
+        // 5.5 K at 512, where fp16 values load 2 bytes per lane and run at about half of that
+        static const double mn[] = {1, 2, 4, 8, 16, 32, 64, 128, 256, 512}, mr[] = {110e3, 83e3, 137e3, 100e3, 75e3, 68e3, 35.5e3, 28.6e3, 13.9e3, 5.5e3};
         double rate = mr[9];
         for (int i = 0; i < 10; i++)
             if (N <= mn[i]) {
                 rate = mr[i];
                 break;
             }
-        if (p->half && N >= 16) rate *= 0.5;
+        if (p->half && N >= 64) rate *= 0.5;
+        if (p->half && N <= 8) rate *= 0.75; // one lane per segment (C1 stand-in: 24.8 us against 17.8 in fp32)
         const double walk = nnz / rate;
         c.push_back({GS_FAMILY_B200_MERGE, std::max({(nnz * (idxb + vb) + bc) / (0.60 * bw), gather / (b_in_l2 ? l2_bw : 0.9 * bw), walk}) + 3.0});
     }

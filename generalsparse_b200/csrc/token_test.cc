@@ -18,6 +18,8 @@
 //   --dump <dir>                      write every metadata array as text, one value per line (struct.cc:1991)
 //   --gpus G                          the matrix is cut into G nnz-balanced row blocks, one per GPU 0..G-1 (gs_exec_*: B replicated,
 //                                     C rows disjoint, no collective); --allgather: then replicate C on every GPU over NCCL and time it
+//   --device-transform                the driver's chain (default / warp_total / thread_bit_map family) is built by device passes from the loader's COO
+//                                     (gs_transform_host_coo) instead of the host transform steps; prints the device time
 //   --no-parity                       skip the host check (the reference always checks, code_generator.cc:631-638)
 //   --corrupt-check                   flip one element of the host copy of C before the check (shows that the check can fail)
 // The host check is the reference's own: all-ones B, C[i][j] must equal the row's sum of values exactly in
@@ -77,6 +79,7 @@ int main(int argc, char **argv)
     int S = 4, C = 1, repeat = 10000;
     bool half = false, values = false, parity = true, corrupt = false, allgather = false;
     int gpus = 1;
+    bool device_transform = false;
     for (int i = 3; i < argc; i++) {
         std::string a = argv[i];
         auto next = [&]() -> const char * { return i + 1 < argc ? argv[++i] : ""; };
@@ -92,6 +95,7 @@ int main(int argc, char **argv)
         else if (a == "--no-parity") parity = false;
         else if (a == "--corrupt-check") corrupt = true;
         else if (a == "--gpus") gpus = atoi(next());
+        else if (a == "--device-transform") device_transform = true;
         else if (a == "--allgather") allgather = true;
         else {
             fprintf(stderr, "token_test: unknown flag %s\n", a.c_str());
@@ -188,6 +192,28 @@ int main(int argc, char **argv)
         return 0;
     }
     gsh_session *s = nullptr;
+    gs_ctx *ctx = nullptr;
+    gs_plan_desc desc;
+    if (device_transform) {
+        // the driver's chain built by device passes from the loader's COO (gs_transform_host_coo) -- no host transform steps
+        if (!ops.empty()) die("--device-transform builds the thread_total / warp_total / thread_bit_map driver chains, not --ops");
+        uint64_t nnz = 0, rows = 0, cols = 0;
+        OK(gsh_metadata_info(ms, "GLOBAL_META_nz_row_indices_0", &nnz, nullptr, nullptr));
+        OK(gsh_metadata_read_u64(ms, "GLOBAL_META_origin_row_num_-1", &rows, 1));
+        OK(gsh_metadata_read_u64(ms, "GLOBAL_META_origin_col_num_-1", &cols, 1));
+        std::vector<uint64_t> r64(nnz), c64(nnz);
+        std::vector<double> v64(nnz);
+        OK(gsh_metadata_read_u64(ms, "GLOBAL_META_nz_row_indices_0", r64.data(), nnz));
+        OK(gsh_metadata_read_u64(ms, "GLOBAL_META_nz_col_indices_0", c64.data(), nnz));
+        OK(gsh_metadata_read_f64(ms, "GLOBAL_META_nz_vals_0", v64.data(), nnz));
+        std::vector<uint32_t> r32(nnz), c32(nnz);
+        std::vector<float> v32(nnz);
+        for (uint64_t i = 0; i < nnz; i++) r32[i] = (uint32_t)r64[i], c32[i] = (uint32_t)c64[i], v32[i] = (float)v64[i];
+        OK(gs_create(&ctx, 0));
+        float tms = 0;
+        OK(gs_transform_host_coo(ctx, fam, rows, cols, nnz, r32.data(), c32.data(), v32.data(), N, S, C, half, 0, &desc, &tms));
+        printf("device transform: %g ms\n", tms);
+    } else {
     OK(gsh_session_create(ms, 0, &s));
     if (ops.empty()) OK(gsh_session_run_family(s, fam, N, S, C));
     else {
@@ -221,11 +247,10 @@ int main(int argc, char **argv)
     }
     if (!dump.empty()) OK(gsh_metadata_dump(ms, dump.c_str()));
 
-    gs_plan_desc desc;
     OK(gsh_session_plan_desc(s, &desc));
-    gs_ctx *ctx = nullptr;
     OK(gs_create(&ctx, 0));
     OK(gs_upload_session(ctx, s, half));
+    }
     gs_plan *plan = nullptr;
     OK(gs_plan_create(ctx, &desc, N, half, &plan));
     if (kernel.empty() || kernel == "auto") {
@@ -280,7 +305,7 @@ int main(int argc, char **argv)
     printf("%s : min time: %g\n", mtx.c_str(), ms_total * 1e-3 / repeat);
     gs_plan_destroy(plan);
     gs_destroy(ctx);
-    gsh_session_free(s);
+    if (s) gsh_session_free(s);
     gsh_metadata_free(ms);
     return 0;
 }

@@ -58,6 +58,9 @@ for mat, kind, kw in (("uniform 1 %", "uniform", dict(density=0.01)), ("banded, 
                 continue
             uploaded = {}
             for lab, kernel, half in kernels:
+                if os.environ.get("C5_ONLY") and os.environ["C5_ONLY"] not in lab:
+                    table[(lab, N)] = None
+                    continue
                 if kernel in ("b200_tcgen05", "b200_sp24") and not WEIGHT_SIZED:
                     table[(lab, N)] = None  # the tensor-core layouts are built for weight-sized matrices (4.8 GB of image here)
                     continue

@@ -132,6 +132,24 @@ def test_token_test_binary_b200_kernels_on_c1(built_lib, c1_mtx, tmp_path, args)
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("args", [[], ["--half"], ["--family", "warp_total"], ["--family", "thread_bit_map", "--kernel", "reference"],
+                                  ["--family", "thread_bit_map", "--kernel", "b200_nnz", "--n32"]],
+                         ids=["default", "default_half", "warp_total", "thread_bit_map", "nnz_N32"])
+def test_token_test_binary_device_transform_on_c1(built_lib, c1_mtx, tmp_path, args):
+    """--device-transform: the loader's COO goes to the device and the chain is built there; same kernel line, same check"""
+    path = c1_mtx[0]
+    N = "8"
+    if "--n32" in args:
+        args = [a for a in args if a != "--n32"]
+        N = "32"
+    host = _run([path, N, "--repeat", "20", "--sparse-coarsen", "4"] + args, str(tmp_path))
+    dev = _run([path, N, "--repeat", "20", "--sparse-coarsen", "4", "--device-transform"] + args, str(tmp_path))
+    assert "\ncorrect\n" in dev and "wrong number" not in dev and "device transform: " in dev, dev[-1500:]
+    kernel = [l for l in host.splitlines() if l.startswith("kernel: ")]
+    assert kernel and kernel == [l for l in dev.splitlines() if l.startswith("kernel: ")], (kernel, dev[-800:])
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("half", [False, True], ids=["fp32", "half"])
 def test_token_test_check_can_fail(built_lib, c1_mtx, tmp_path, half):
     """--corrupt-check flips one element of the host copy of C: the check must say `wrong number:1`, with HALF too

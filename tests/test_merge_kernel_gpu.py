@@ -1,7 +1,8 @@
 """The B200 range kernel (GS_FAMILY_B200_MERGE): the device consumer of merge-path, nnz-balanced, column-direction and multi-row-block
 chains (round 1 produced their host arrays bit-exactly but nothing on the device read them).  Parity with the oracle through the C ABI:
-all-ones exact, random values within SURVEY.md 8(d)'s gate; fp16 C is completed with red.add at segment edges (each partial rounded to
-fp16), hence the row-L1 floor at the tolerance for HALF, as for the other atomic kernels."""
+all-ones exact, random values within SURVEY.md 8(d)'s gate.  Rows shared between segments are completed by tickets (fp32 partials, summed in
+stream order by the last segment to arrive) unless a row has more than 64 sharers, where the plan keeps red.add into a zeroed C (each partial
+rounded to fp16 when C is HALF, hence the row-L1 floor at the tolerance for HALF in _check)."""
 import numpy as np
 import pytest
 
