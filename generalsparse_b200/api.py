@@ -62,7 +62,7 @@ class MetaDataSet:
         return cls(h)
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:  # (module globals are gone at interpreter shutdown: the process takes the handle with it)
             lib().gsh_metadata_free(self._h)
             self._h = None
 
@@ -132,7 +132,7 @@ class Session:
         self._h = h
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:  # (module globals are gone at interpreter shutdown: the process takes the handle with it)
             lib().gsh_session_free(self._h)
             self._h = None
 
@@ -199,7 +199,7 @@ class Engine:
         self.device_id = device_id
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:  # (module globals are gone at interpreter shutdown: the process takes the handle with it)
             lib().gs_destroy(self._h)
             self._h = None
 
@@ -276,7 +276,7 @@ class Plan:
         self.vdtype = np.float16 if half else np.float32
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:  # (module globals are gone at interpreter shutdown: the process takes the handle with it)
             lib().gs_plan_destroy(self._h)
             self._h = None
 
@@ -372,7 +372,7 @@ class Executor:
         self._h, self.n = h, len(ids)
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:  # (module globals are gone at interpreter shutdown: the process takes the handle with it)
             lib().gs_exec_destroy(self._h)
             self._h = None
 
