@@ -394,7 +394,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from generalsparse_b200 import api
+    from generalsparse_b200 import api, synth
 
     torch.cuda.set_device(local)
     if world > 1:
@@ -550,6 +550,26 @@ def main():
         e1.synchronize()
         iso.append(e0.elapsed_time(e1))
     ms_iso = float(np.median(iso))
+    # the floor of that measurement: the same event pair around one launch of the same kernel family on a 256 x 256 matrix (what an idle device
+    # charges for any launch: profiles/r2_sp24_timeline.md)
+    tr, tc = synth.synth_matrix("uniform", 256, 256, seed=1, density=0.05)
+    tsess = api.Session(api.MetaDataSet.from_coo(256, 256, tr, tc, None)).run_family("thread_total", N, 8, 1)
+    eng.upload_session(tsess, half=half, as_id=901)
+    tplan = eng.plan(tsess, N, half=half, kernel=kfam if kfam.startswith("b200") else args.kernel, sub_matrix_id=901)
+    tplan.set_dense(np.ones((256, N), np.float16 if half else np.float32))
+    for _ in range(5):
+        tplan.launch()
+    iso_floor = []
+    for i in range(64):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        tplan.launch()
+        e1.record(stream)
+        e1.synchronize()
+        iso_floor.append(e0.elapsed_time(e1))
+    ms_iso_floor = float(np.median(iso_floor))
+    del tplan, tsess
 
     nnz_all = torch.tensor([desc.origin_nnz], device="cuda", dtype=torch.float64)
     if world > 1:
@@ -597,7 +617,9 @@ def main():
                      "dependent_chain_ms_per_step": ms_dep, "dependent_chain_frac": alg_bytes / (ms_dep * 1e-3) / 1e9 / hbm_peak,
                      "dependent_chain": "step i+1's B is the first K rows of step i's C: one stream; the launch starts under programmatic dependent launch and waits on the device (griddepcontrol.wait) before it requests B",
                      "isolated_launch_ms": ms_iso, "isolated_launch_frac": alg_bytes / (ms_iso * 1e-3) / 1e9 / hbm_peak,
-                     "isolated_launch": "median of 64 single launches, device idle before each, CUDA events around the one launch"},
+                     "isolated_launch": "median of 64 single launches, device idle before each, CUDA events around the one launch",
+                     "isolated_launch_floor_ms": ms_iso_floor,
+                     "isolated_launch_floor": "the same event pair around one launch of the same kernel on a 256 x 256 matrix: what an idle device charges for any launch"},
         "e2e": {"value": 2.0 * nnz_all * N * e2e_steps / e2e_s / 1e9, "unit": "GFLOP/s", "h2d_bytes_per_step": int(COLS * N * 2),
                 "d2h_bytes_per_step": int(desc.rows * N * 2), "ms_per_step": e2e_s / e2e_steps * 1e3, "steps": e2e_steps,
                 "api": "gs_spmm_host_async per step (pinned B in, pinned C out) + one gs_synchronize; results equal the blocking call: %s" % e2e_ok,

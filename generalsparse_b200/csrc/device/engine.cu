@@ -698,8 +698,8 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
     GS_REQUIRE(ctx && desc_out && row_dev && col_dev && val_dev, "null argument");
     GS_REQUIRE(N >= 1 && sparse_coarsen >= 1 && coarsen >= 1, "N, sparse_coarsen and coarsen must be >= 1");
     GS_REQUIRE(as_id >= 0, "as_id must be >= 0");
-    if (family != GS_FAMILY_THREAD_TOTAL && family != GS_FAMILY_WARP_TOTAL && family != GS_FAMILY_THREAD_BITMAP)
-        return fail(GS_ERR_UNSUPPORTED, "gs_transform_device builds the thread_total, warp_total and thread_bit_map driver chains; the others are built on the host (gsh_session_run_family)");
+    if (family != GS_FAMILY_THREAD_TOTAL && family != GS_FAMILY_WARP_TOTAL && family != GS_FAMILY_THREAD_BITMAP && family != GS_FAMILY_WARP_SEGMENT)
+        return fail(GS_ERR_UNSUPPORTED, "gs_transform_device builds the thread_total, warp_total, thread_bit_map and warp_segment driver chains; the others are built on the host (gsh_session_run_family)");
     CUDA_TRY(cudaSetDevice(ctx->device));
     ctx->join_async();
     const double bound = (double)gs::get_config().as_integer("PADDING_RATE_UP_BOUND");
@@ -724,11 +724,16 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
         GS_REQUIRE(y >= 1, "N / coarsen must be >= 1");
         x = std::max(256 / y, 32u), grid_x = (unsigned)rows;
         e = gsd::transform_row_chain(m, false, 0, half != 0, "WARP_META", bound, ctx->stream, out);
+    } else if (family == GS_FAMILY_WARP_SEGMENT) { // token_test.cc:1393-1455
+        x = (unsigned)std::min(N, 32);
+        y = 256 / x, grid_x = (unsigned)(nnz / 128 + 1);
+        d.need_warp_reduction = 1;
+        e = gsd::transform_nnz_chain(m, x, true, half != 0, bound, ctx->stream, out);
     } else {
         x = (unsigned)std::min(N / coarsen, 32);
         GS_REQUIRE(x >= 1, "N / coarsen must be >= 1");
         y = 128 / x, grid_x = (unsigned)(nnz / y + 1);
-        e = gsd::transform_nnz_chain(m, x, half != 0, bound, ctx->stream, out);
+        e = gsd::transform_nnz_chain(m, x, false, half != 0, bound, ctx->stream, out);
     }
     if (e != cudaSuccess) {
         out.release();
@@ -738,7 +743,7 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
     }
     d.vector_width = (int)x;
     d.block[0] = x, d.block[1] = y % 2 ? y + 1 : y; // grid_block_operator.cc:13-33
-    const unsigned per = (family == GS_FAMILY_WARP_TOTAL ? d.block[1] : d.block[0]) * (unsigned)coarsen;
+    const unsigned per = ((family == GS_FAMILY_WARP_TOTAL || family == GS_FAMILY_WARP_SEGMENT) ? d.block[1] : d.block[0]) * (unsigned)coarsen; // a WARP first_nz_indices exists
     d.grid[0] = grid_x, d.grid[1] = (unsigned)((N + per - 1) / per);
     d.has_row_permutation = out.has_perm, d.stored_nnz = out.stored_nnz;
     drop_arrays_of_id(ctx, as_id);
@@ -746,9 +751,12 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
     std::vector<std::pair<const char *, const char *>> deps = {{"GLOBAL_META", "nz_col_indices"}, {"GLOBAL_META", "nz_vals"}};
     if (out.has_perm) deps.push_back({"GLOBAL_META", "original_nz_row_indices"});
     const char *lvl = family == GS_FAMILY_WARP_TOTAL ? "WARP_META" : "THREAD_META";
+    if (family == GS_FAMILY_WARP_SEGMENT) deps.push_back({"WARP_META", "first_BMT_indices"});
     deps.push_back({lvl, "first_row_indices"}), deps.push_back({lvl, "first_nz_indices"});
     if (family == GS_FAMILY_THREAD_BITMAP)
         for (const char *n : {"thread_bit_map", "segment_ptr", "segment_empty_flag", "segment_empty_row_indices"}) deps.push_back({"THREAD_META", n});
+    if (family == GS_FAMILY_WARP_SEGMENT)
+        for (const char *n : {"thread_bit_map", "segment_ptr", "segment_offset", "segment_empty_flag", "segment_empty_row_indices"}) deps.push_back({"THREAD_META", n});
     for (const auto &k : deps) {
         const std::string key = std::string(k.first) + "_" + k.second + "_" + std::to_string(as_id);
         GS_REQUIRE(key.size() < 64, "key too long");

@@ -323,8 +323,9 @@ __global__ void k_pad_stream(const uint32_t *row, const uint32_t *col, const flo
 // the BMT's segment count (segment_ptr.cc: one plus the row changes inside the BMT) and its gap flag (segment_empty_flag.cc: two neighbours inside
 // the BMT more than one row apart).  Pass 2, after the scan of the counts: segment_empty_row_indices (segment_empty_row_indices.cc: 0, then the row
 // offset of every row change from the BMT's first row).
+// parent: thread_bit_map.cc's parent_flag loop (thread_bit_map_operator at WARP level): the first non-zero of every `parent`-th BMT starts a segment too (0 = off)
 __global__ void __launch_bounds__(256) k_bmt_pass(const uint32_t *row_pad, uint32_t n_bmt, uint32_t *first_row, uint64_t *bit_map, uint32_t *seg_count, uint8_t *gap_flag,
-                                                  const uint32_t *seg_ptr, uint32_t *seg_rows)
+                                                  const uint32_t *seg_ptr, uint32_t *seg_rows, uint32_t parent)
 {
     const int lane = threadIdx.x & 31;
     for (uint64_t b = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < n_bmt; b += ((uint64_t)gridDim.x * blockDim.x) >> 5) {
@@ -336,13 +337,34 @@ __global__ void __launch_bounds__(256) k_bmt_pass(const uint32_t *row_pad, uint3
         const unsigned gaps = __ballot_sync(0xffffffffu, lane > 0 && r - prev > 1);
         const uint32_t r0 = __shfl_sync(0xffffffffu, r, 0);
         if (!seg_ptr) {
-            if (lane == 0) first_row[b] = r0, bit_map[b] = (uint64_t)starts, seg_count[b] = 1u + __popc(inner), gap_flag[b] = gaps ? 1 : 0;
+            if (lane == 0) first_row[b] = r0, bit_map[b] = (uint64_t)(starts | ((parent && b % parent == 0) ? 1u : 0u)), seg_count[b] = 1u + __popc(inner), gap_flag[b] = gaps ? 1 : 0;
         } else {
             const uint32_t at = seg_ptr[b];
             if (lane == 0) seg_rows[at] = 0;
             else if (start) seg_rows[at + 1 + __popc(inner & ((1u << lane) - 1u))] = r - r0;
         }
     }
+}
+
+// segment_offset.cc: a BMT whose bit map is not zero gets the number of all-zero BMTs between it and the next non-zero one; the run that reaches
+// the end of the array is never written back (kept: the reference's loop ends without flushing it)
+__global__ void k_segment_offset(const uint64_t *bit_map, uint32_t n_bmt, uint32_t *out)
+{
+    for (uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; b < n_bmt; b += (uint64_t)gridDim.x * blockDim.x) {
+        uint32_t v = 0;
+        if (b == 0 || bit_map[b] != 0) {
+            uint64_t j = b + 1;
+            while (j < n_bmt && bit_map[j] == 0) j++;
+            if (j < n_bmt) v = (uint32_t)(j - b - 1);
+        }
+        out[b] = v;
+    }
+}
+
+// get_begin_BMTs_after_merge_thread.cc: [0, m, 2 m, ..., n]
+__global__ void k_group_starts(uint32_t *out, uint32_t n_out, uint32_t m, uint32_t n)
+{
+    for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_out; j += (uint64_t)gridDim.x * blockDim.x) out[j] = (uint32_t)min((uint64_t)j * m, (uint64_t)n);
 }
 
 // segment_empty_flag.cc: `size` consecutive BMT flags per word, the first in the LSB
@@ -500,7 +522,7 @@ cudaError_t transform_row_chain(const coo_dev &m, bool sort, uint32_t S, bool ha
     return cudaStreamSynchronize(s);
 }
 
-cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool half, double pad_bound, cudaStream_t s, transform_out &out)
+cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool warp_level, bool half, double pad_bound, cudaStream_t s, transform_out &out)
 {
     scratch sc;
     uint32_t max_col = 0;
@@ -552,7 +574,7 @@ cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool half, doub
     const unsigned g2 = std::min(blocks_for((uint64_t)n_bmt * 32, 256), 148u * 64u);
     k_first_rows<<<blocks_for((uint64_t)n_bmt + 1, 256 * 4), 256, 0, s>>>(row_out, n_bmt, rows, first_row);
     k_iota<<<blocks_for((uint64_t)n_bmt + 1, 256 * 4), 256, 0, s>>>(first_nz, (uint64_t)n_bmt + 1, 32);
-    k_bmt_pass<<<g2, 256, 0, s>>>(row_out, n_bmt, first_row, bit_map, seg_count, gap, nullptr, nullptr);
+    k_bmt_pass<<<g2, 256, 0, s>>>(row_out, n_bmt, first_row, bit_map, seg_count, gap, nullptr, nullptr, warp_level ? size : 0u);
     TRY(cudaGetLastError());
     TRY(scan_exclusive(seg_count, seg_ptr, n_bmt, sc, s));
     uint32_t n_seg_rows = 0, first_row_gcd = 0, not_iota = 0;
@@ -571,9 +593,22 @@ cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool half, doub
     const uint32_t n_words = (n_bmt + size - 1) / size;
     TRY(alloc_out(&gap_words, n_words));
     take(out, "THREAD_META", "segment_empty_flag", gap_words, n_words, GS_U64, 0, 0);
-    k_bmt_pass<<<g2, 256, 0, s>>>(row_out, n_bmt, nullptr, nullptr, nullptr, nullptr, seg_ptr, seg_rows);
+    k_bmt_pass<<<g2, 256, 0, s>>>(row_out, n_bmt, nullptr, nullptr, nullptr, nullptr, seg_ptr, seg_rows, 0u);
     k_pack_flags<<<blocks_for(n_words, 256), 256, 0, s>>>(gap, n_bmt, size, gap_words, n_words);
     TRY(cudaGetLastError());
+    if (warp_level) { // thread_bit_map_operator(WARP_META) + warp_segment_reduce_operator: segment_offset and the BMWs of `size` BMTs
+        uint32_t *seg_off = nullptr, *first_bmt = nullptr;
+        TRY(alloc_out(&seg_off, n_bmt));
+        take(out, "THREAD_META", "segment_offset", seg_off, n_bmt, GS_U32, 0, 0);
+        const uint32_t n_w = (n_bmt + size - 1) / size + 1;
+        TRY(alloc_out(&first_bmt, n_w));
+        const uint32_t g = n_bmt % size ? 1u : size;
+        take(out, "WARP_META", "first_BMT_indices", first_bmt, n_w, GS_U32, n_bmt, n_bmt % size ? std::__gcd(size, n_bmt) : size, size == 1, n_bmt % size == 0, size);
+        (void)g;
+        k_segment_offset<<<blocks_for(n_bmt, 256), 256, 0, s>>>(bit_map, n_bmt, seg_off);
+        k_group_starts<<<blocks_for(n_w, 256), 256, 0, s>>>(first_bmt, n_w, size, n_bmt);
+        TRY(cudaGetLastError());
+    }
     return cudaStreamSynchronize(s);
 }
 

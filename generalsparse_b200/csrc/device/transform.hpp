@@ -47,6 +47,8 @@ cudaError_t transform_row_chain(const coo_dev &m, bool sort, uint32_t S, bool ha
 // fixed_interval_nnz_direction_thread_blocking_operator(32, pad) + thread_bit_map_operator(THREAD_META, size):
 // nz_* padded to a multiple of 32; THREAD first_row_indices, first_nz_indices, thread_bit_map, segment_ptr, segment_empty_flag (packed
 // `size` BMTs per word), segment_empty_row_indices
-cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool half, double pad_bound, cudaStream_t s, transform_out &out);
+// warp_level: the warp_segment driver chain -- thread_bit_map_operator(WARP_META, size) forces a segment start at every `size`-th BMT, and
+// warp_segment_reduce_operator adds THREAD segment_offset and WARP first_BMT_indices (BMWs of `size` BMTs)
+cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool warp_level, bool half, double pad_bound, cudaStream_t s, transform_out &out);
 
 } // namespace gsd

@@ -216,8 +216,10 @@ gs_status gs_upload_session_as(gs_ctx *ctx, const gsh_session *s, int half, int 
  * reorder_{val,col,row}_by_index, remove_empty_row_in_end_of_sub_matrix) + fixed_interval_row_direction_thread_blocking_operator(1,
  * col pad to sparse_coarsen; ...thread_blocking_operator.cc:482-565); GS_FAMILY_WARP_TOTAL = fixed_interval_row_direction_warp_
  * blocking_operator(1), no sort, no pad; GS_FAMILY_THREAD_BITMAP = fixed_interval_nnz_direction_thread_blocking_operator(32, pad) +
- * thread_bit_map_operator (thread_bit_map.cc, segment_{ptr,empty_flag,empty_row_indices}.cc).  desc_out is what
- * gsh_session_plan_desc would return after the driver's chain (token_test.cc:1003-1092, :1188-1249, :1319-1391), launch shape
+ * thread_bit_map_operator (thread_bit_map.cc, segment_{ptr,empty_flag,empty_row_indices}.cc); GS_FAMILY_WARP_SEGMENT = the same blocking +
+ * thread_bit_map_operator at WARP level (a segment start forced at every VECTOR_WIDTH-th BMT) + warp_segment_reduce_operator (segment_offset.cc,
+ * get_begin_BMTs_after_merge_thread.cc).  desc_out is what
+ * gsh_session_plan_desc would return after the driver's chain (token_test.cc:1003-1092, :1188-1249, :1319-1391, :1393-1455), launch shape
  * included.  GS_ERR_PADDING_RATE where the reference's padding assert fires; GS_ERR_UNSUPPORTED for the other families. */
 gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t cols, uint64_t nnz, const uint32_t *row_dev, const uint32_t *col_dev, const float *val_dev, int N,
                               int sparse_coarsen, int coarsen, int half, int as_id, gs_plan_desc *desc_out);

@@ -133,8 +133,8 @@ def test_token_test_binary_b200_kernels_on_c1(built_lib, c1_mtx, tmp_path, args)
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("args", [[], ["--half"], ["--family", "warp_total"], ["--family", "thread_bit_map", "--kernel", "reference"],
-                                  ["--family", "thread_bit_map", "--kernel", "b200_nnz", "--n32"]],
-                         ids=["default", "default_half", "warp_total", "thread_bit_map", "nnz_N32"])
+                                  ["--family", "thread_bit_map", "--kernel", "b200_nnz", "--n32"], ["--family", "warp_segment", "--kernel", "reference"]],
+                         ids=["default", "default_half", "warp_total", "thread_bit_map", "nnz_N32", "warp_segment"])
 def test_token_test_binary_device_transform_on_c1(built_lib, c1_mtx, tmp_path, args):
     """--device-transform: the loader's COO goes to the device and the chain is built there; same kernel line, same check"""
     path = c1_mtx[0]
