@@ -24,17 +24,40 @@ namespace {
         if (e_ != cudaSuccess) return e_;                                                                                                            \
     } while (0)
 
+// Every buffer of a transform comes from the device's stream-ordered pool (cudaMallocAsync on the transform's stream) with the pool told to keep
+// what is freed: a chain takes ~16 allocations, and plain cudaMalloc / cudaFree cost tens of milliseconds each once peer access is on (a 2-GPU
+// bench line measured 465 ms for the passes that take 12 ms on one GPU).  Arrays handed to the context are freed by it with cudaFree, which takes
+// pool memory too.
+cudaError_t pool_alloc(void **p, uint64_t bytes, cudaStream_t s)
+{
+    static bool keep[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev >= 0 && dev < 64 && !keep[dev]) {
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            uint64_t all = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &all);
+        }
+        keep[dev] = true;
+    }
+    return cudaMallocAsync(p, bytes, s);
+}
+
 // scratch that lives for one transform
 struct scratch {
     std::vector<void *> bufs;
+    cudaStream_t stream = nullptr;
+    explicit scratch(cudaStream_t s) : stream(s) {}
     ~scratch()
     {
-        for (void *p : bufs) cudaFree(p);
+        for (void *p : bufs) cudaFreeAsync(p, stream);
     }
     template <typename T> cudaError_t get(T **p, uint64_t n)
     {
         void *q = nullptr;
-        cudaError_t e = cudaMalloc(&q, std::max<uint64_t>(n, 1) * sizeof(T) + 16);
+        cudaError_t e = pool_alloc(&q, std::max<uint64_t>(n, 1) * sizeof(T) + 16, stream);
         if (e == cudaSuccess) bufs.push_back(q), *p = (T *)q;
         return e;
     }
@@ -386,7 +409,7 @@ cudaError_t take(transform_out &out, const char *pos, const char *name, void *pt
     return cudaSuccess;
 }
 
-template <typename T> cudaError_t alloc_out(T **p, uint64_t n) { return cudaMalloc((void **)p, std::max<uint64_t>(n, 1) * sizeof(T) + 16); }
+template <typename T> cudaError_t alloc_out(T **p, uint64_t n, cudaStream_t s) { return pool_alloc((void **)p, std::max<uint64_t>(n, 1) * sizeof(T) + 16, s); }
 
 cudaError_t check_input(const coo_dev &m, scratch &sc, cudaStream_t s, transform_out &out, uint32_t *max_col)
 {
@@ -445,7 +468,7 @@ int bit_width(uint32_t v)
 
 cudaError_t transform_row_chain(const coo_dev &m, bool sort, uint32_t S, bool half, const char *level, double pad_bound, cudaStream_t s, transform_out &out)
 {
-    scratch sc;
+    scratch sc(s);
     uint32_t max_col = 0;
     TRY(check_input(m, sc, s, out, &max_col));
     if (S == 1) { // modify_col_indices_by_col_pad_in_sub_matrix.cc asserts multiple_of_each_row_size >= 2
@@ -467,7 +490,7 @@ cudaError_t transform_row_chain(const coo_dev &m, bool sort, uint32_t S, bool ha
         TRY(reduce_u32<op_max>(len, rows, &max_len, sc, s));
         uint32_t *key = nullptr;
         TRY(sc.get(&key, rows));
-        TRY(alloc_out(&order, rows));
+        TRY(alloc_out(&order, rows, s));
         take(out, "GLOBAL_META", "original_nz_row_indices", order, rows, GS_U32, rows - 1, 1);
         k_sort_keys<<<blocks_for(rows, 256 * 4), 256, 0, s>>>(len, rows, max_len, key, order);
         TRY(cudaGetLastError());
@@ -482,9 +505,9 @@ cudaError_t transform_row_chain(const coo_dev &m, bool sort, uint32_t S, bool ha
     out.rows_kept = rows_kept;
 
     uint32_t *first_nz = nullptr, *first_row = nullptr;
-    TRY(alloc_out(&first_nz, (uint64_t)rows_kept + 1));
+    TRY(alloc_out(&first_nz, (uint64_t)rows_kept + 1, s));
     take(out, level, "first_nz_indices", first_nz, (uint64_t)rows_kept + 1, GS_U32, 0, 0);
-    TRY(alloc_out(&first_row, (uint64_t)rows_kept + 1));
+    TRY(alloc_out(&first_row, (uint64_t)rows_kept + 1, s));
     take(out, level, "first_row_indices", first_row, (uint64_t)rows_kept + 1, GS_U32, rows_kept, 1, true, true, 1);
     k_padded_len<<<blocks_for(rows_kept, 256 * 4), 256, 0, s>>>(len, order, rows_kept, S, plen);
     k_iota<<<blocks_for((uint64_t)rows_kept + 1, 256 * 4), 256, 0, s>>>(first_row, (uint64_t)rows_kept + 1, 1);
@@ -507,11 +530,11 @@ cudaError_t transform_row_chain(const coo_dev &m, bool sort, uint32_t S, bool ha
     const bool c16 = max_col <= 65535u;
     void *col_out = nullptr, *val_out = nullptr;
     uint32_t *row_out = nullptr;
-    TRY(cudaMalloc(&col_out, (uint64_t)nnz_pad * (c16 ? 2 : 4) + 16));
+    TRY(pool_alloc(&col_out, (uint64_t)nnz_pad * (c16 ? 2 : 4) + 16, s));
     take(out, "GLOBAL_META", "nz_col_indices", col_out, nnz_pad, c16 ? GS_U16 : GS_U32, max_col, 0);
-    TRY(cudaMalloc(&val_out, (uint64_t)nnz_pad * (half ? 2 : 4) + 16));
+    TRY(pool_alloc(&val_out, (uint64_t)nnz_pad * (half ? 2 : 4) + 16, s));
     take(out, "GLOBAL_META", "nz_vals", val_out, nnz_pad, half ? GS_F16 : GS_F32, 0, 0);
-    TRY(alloc_out(&row_out, nnz_pad));
+    TRY(alloc_out(&row_out, nnz_pad, s));
     take(out, "GLOBAL_META", "nz_row_indices", row_out, nnz_pad, GS_U32, rows_kept ? rows_kept - 1 : 0, 0);
     const unsigned grid = std::min(blocks_for((uint64_t)rows_kept * 32, 256), 148u * 64u);
     if (c16 && half) k_scatter_rows<uint16_t, __half><<<grid, 256, 0, s>>>(m.col, m.val, rowptr, order, first_nz, rows_kept, (uint16_t *)col_out, (__half *)val_out, row_out);
@@ -524,7 +547,7 @@ cudaError_t transform_row_chain(const coo_dev &m, bool sort, uint32_t S, bool ha
 
 cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool warp_level, bool half, double pad_bound, cudaStream_t s, transform_out &out)
 {
-    scratch sc;
+    scratch sc(s);
     uint32_t max_col = 0;
     TRY(check_input(m, sc, s, out, &max_col));
     if (size < 1 || size > 64) {
@@ -544,11 +567,11 @@ cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool warp_level
     const bool c16 = max_col <= 65535u;
     void *col_out = nullptr, *val_out = nullptr;
     uint32_t *row_out = nullptr;
-    TRY(cudaMalloc(&col_out, (uint64_t)nnz_pad * (c16 ? 2 : 4) + 16));
+    TRY(pool_alloc(&col_out, (uint64_t)nnz_pad * (c16 ? 2 : 4) + 16, s));
     take(out, "GLOBAL_META", "nz_col_indices", col_out, nnz_pad, c16 ? GS_U16 : GS_U32, max_col, 0);
-    TRY(cudaMalloc(&val_out, (uint64_t)nnz_pad * (half ? 2 : 4) + 16));
+    TRY(pool_alloc(&val_out, (uint64_t)nnz_pad * (half ? 2 : 4) + 16, s));
     take(out, "GLOBAL_META", "nz_vals", val_out, nnz_pad, half ? GS_F16 : GS_F32, 0, 0);
-    TRY(alloc_out(&row_out, nnz_pad));
+    TRY(alloc_out(&row_out, nnz_pad, s));
     take(out, "GLOBAL_META", "nz_row_indices", row_out, nnz_pad, GS_U32, rows - 1, 0);
     const unsigned g1 = std::min(blocks_for(nnz_pad, 256 * 4), 148u * 64u);
     if (c16 && half) k_pad_stream<uint16_t, __half><<<g1, 256, 0, s>>>(m.row, m.col, m.val, nnz, nnz_pad, (uint16_t *)col_out, (__half *)val_out, row_out);
@@ -560,13 +583,13 @@ cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool warp_level
     uint32_t *first_row = nullptr, *first_nz = nullptr, *seg_ptr = nullptr, *seg_count = nullptr, *seg_rows = nullptr, *flag = nullptr;
     uint64_t *bit_map = nullptr, *gap_words = nullptr;
     uint8_t *gap = nullptr;
-    TRY(alloc_out(&first_row, (uint64_t)n_bmt + 1));
+    TRY(alloc_out(&first_row, (uint64_t)n_bmt + 1, s));
     take(out, "THREAD_META", "first_row_indices", first_row, (uint64_t)n_bmt + 1, GS_U32, rows, 0);
-    TRY(alloc_out(&first_nz, (uint64_t)n_bmt + 1));
+    TRY(alloc_out(&first_nz, (uint64_t)n_bmt + 1, s));
     take(out, "THREAD_META", "first_nz_indices", first_nz, (uint64_t)n_bmt + 1, GS_U32, nnz_pad, 32, false, true, 32);
-    TRY(alloc_out(&bit_map, n_bmt));
+    TRY(alloc_out(&bit_map, n_bmt, s));
     take(out, "THREAD_META", "thread_bit_map", bit_map, n_bmt, GS_U64, 0, 0);
-    TRY(alloc_out(&seg_ptr, (uint64_t)n_bmt + 1));
+    TRY(alloc_out(&seg_ptr, (uint64_t)n_bmt + 1, s));
     take(out, "THREAD_META", "segment_ptr", seg_ptr, n_bmt, GS_U32, 0, 0);
     TRY(sc.get(&seg_count, n_bmt));
     TRY(sc.get(&gap, n_bmt));
@@ -588,20 +611,20 @@ cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool warp_level
         fr.align = first_row_gcd, fr.iota = !not_iota, fr.linear = fr.iota, fr.linear_step = 1;
         out.arrays.back().max_value = n_seg_rows;
     }
-    TRY(alloc_out(&seg_rows, n_seg_rows));
+    TRY(alloc_out(&seg_rows, n_seg_rows, s));
     take(out, "THREAD_META", "segment_empty_row_indices", seg_rows, n_seg_rows, GS_U32, 0, 0);
     const uint32_t n_words = (n_bmt + size - 1) / size;
-    TRY(alloc_out(&gap_words, n_words));
+    TRY(alloc_out(&gap_words, n_words, s));
     take(out, "THREAD_META", "segment_empty_flag", gap_words, n_words, GS_U64, 0, 0);
     k_bmt_pass<<<g2, 256, 0, s>>>(row_out, n_bmt, nullptr, nullptr, nullptr, nullptr, seg_ptr, seg_rows, 0u);
     k_pack_flags<<<blocks_for(n_words, 256), 256, 0, s>>>(gap, n_bmt, size, gap_words, n_words);
     TRY(cudaGetLastError());
     if (warp_level) { // thread_bit_map_operator(WARP_META) + warp_segment_reduce_operator: segment_offset and the BMWs of `size` BMTs
         uint32_t *seg_off = nullptr, *first_bmt = nullptr;
-        TRY(alloc_out(&seg_off, n_bmt));
+        TRY(alloc_out(&seg_off, n_bmt, s));
         take(out, "THREAD_META", "segment_offset", seg_off, n_bmt, GS_U32, 0, 0);
         const uint32_t n_w = (n_bmt + size - 1) / size + 1;
-        TRY(alloc_out(&first_bmt, n_w));
+        TRY(alloc_out(&first_bmt, n_w, s));
         const uint32_t g = n_bmt % size ? 1u : size;
         take(out, "WARP_META", "first_BMT_indices", first_bmt, n_w, GS_U32, n_bmt, n_bmt % size ? std::__gcd(size, n_bmt) : size, size == 1, n_bmt % size == 0, size);
         (void)g;
