@@ -25,7 +25,7 @@ SYMBOLS = [
     "gs_comm_unique_id", "gs_comm_init", "gs_comm_allgather_rows", "gs_comm_destroy",
     "gs_exec_create", "gs_exec_destroy", "gs_exec_devices", "gs_exec_build", "gs_exec_row_cuts", "gs_exec_kernel_name", "gs_exec_set_dense", "gs_exec_run",
     "gsh_session_generate_final_program", "gs_execute_binary", "gsh_metadata_fit_model", "gs_plan_model_bytes",
-    "gs_transform_device", "gs_transform_host_coo", "gs_download_array",
+    "gs_transform_device", "gs_transform_host_coo", "gs_download_array", "gs_exec_build_on_device",
     "gs_exec_get_output", "gs_exec_enable_allgather", "gs_exec_allgather_output", "gs_exec_get_replica",
 ]
 
@@ -108,7 +108,7 @@ def lib():
         "gs_comm_unique_id": (i32, [vp]), "gs_comm_init": (i32, [vp, i32, i32, vp]), "gs_comm_allgather_rows": (i32, [vp, vp, vp, u64]),
         "gs_comm_destroy": (None, [vp]),
         "gs_exec_create": (i32, [P(vp), vp, i32]), "gs_exec_destroy": (None, [vp]), "gs_exec_devices": (i32, [vp]),
-        "gs_exec_build": (i32, [vp, vp, i32, i32, i32, i32, i32, i32]), "gs_exec_row_cuts": (i32, [vp, vp, vp]), "gs_exec_kernel_name": (cp, [vp, i32]),
+        "gs_exec_build": (i32, [vp, vp, i32, i32, i32, i32, i32, i32]), "gs_exec_build_on_device": (i32, [vp, vp, i32, i32, i32, i32, i32, i32]), "gs_exec_row_cuts": (i32, [vp, vp, vp]), "gs_exec_kernel_name": (cp, [vp, i32]),
         "gs_exec_set_dense": (i32, [vp, vp, i32]), "gs_exec_run": (i32, [vp, i32, P(C.c_float), vp]), "gs_exec_get_output": (i32, [vp, vp]),
         "gs_exec_enable_allgather": (i32, [vp]), "gs_exec_allgather_output": (i32, [vp, P(C.c_float)]), "gs_exec_get_replica": (i32, [vp, i32, vp]),
     }

@@ -376,10 +376,11 @@ class Executor:
             lib().gs_exec_destroy(self._h)
             self._h = None
 
-    def build(self, ms, family, N, sparse_coarsen=1, coarsen=1, half=False, kernel="auto"):
+    def build(self, ms, family, N, sparse_coarsen=1, coarsen=1, half=False, kernel="auto", on_device=False):
+        """on_device: every block's chain is built by its GPU (gs_exec_build_on_device) instead of the host pipeline"""
         fid = FAMILY_ID[family] if isinstance(family, str) else family
         kid = FAMILY_ID[kernel] if isinstance(kernel, str) else kernel
-        check(lib().gs_exec_build(self._h, ms._h, fid, N, sparse_coarsen, coarsen, int(half), kid))
+        check((lib().gs_exec_build_on_device if on_device else lib().gs_exec_build)(self._h, ms._h, fid, N, sparse_coarsen, coarsen, int(half), kid))
         self.N, self.half = N, half
         self.rows = int(ms["GLOBAL_META_origin_row_num_-1"][0])
         self.cols = int(ms["GLOBAL_META_origin_col_num_-1"][0])

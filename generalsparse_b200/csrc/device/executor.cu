@@ -132,6 +132,50 @@ gs_status gs_exec_build(gs_exec *ex, const gsh_metadata *ms, int family, int N, 
     GS_API_END
 }
 
+// The same partition, every block's chain built by its device (gs_transform_host_coo) instead of the host pipeline: the block's slice of
+// the COO goes to the device as u32 / fp32 and comes out as the arrays gs_upload_session would have stored.  One host thread per device, so
+// the G conversions and transfers overlap.  Families: those gs_transform_device builds.
+gs_status gs_exec_build_on_device(gs_exec *ex, const gsh_metadata *ms, int family, int N, int sparse_coarsen, int coarsen, int half, int kernel)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ex && ms && N >= 1, "bad argument");
+    ex->clear_build();
+    const meta_data_set &src = *ms->ms;
+    GS_REQUIRE(src.is_exist(GLOBAL_META, "nz_row_indices", 0) && !src.is_exist(GLOBAL_META, "original_nz_row_indices", 0), "row blocks are cut from the matrix as loaded, before any operator ran");
+    ex->rows = src.scalar(GLOBAL_META, "origin_row_num", -1), ex->cols = src.scalar(GLOBAL_META, "origin_col_num", -1);
+    ex->nnz = src.scalar(GLOBAL_META, "origin_nnz_num", -1);
+    ex->N = N, ex->half = half;
+    std::vector<uint64_t> row_nnz(ex->rows);
+    ABI_TRY(gsh_metadata_row_nnz(ms, row_nnz.data(), ex->rows));
+    ex->cuts.assign(ex->n + 1, 0);
+    ABI_TRY(gsh_partition_rows_balanced(row_nnz.data(), ex->rows, ex->n, ex->cuts.data()));
+    ex->blk.assign(ex->n, nullptr), ex->sess.assign(ex->n, nullptr), ex->plan.assign(ex->n, nullptr), ex->blk_nnz.assign(ex->n, 0);
+    const std::vector<uint64_t> &r = src.get(GLOBAL_META, "nz_row_indices", 0).u, &c = src.get(GLOBAL_META, "nz_col_indices", 0).u;
+    const std::vector<double> &v = src.get(GLOBAL_META, "nz_vals", 0).f;
+    std::vector<std::string> err(ex->n);
+    std::vector<std::thread> th;
+    for (int g = 0; g < ex->n; g++) {
+        const uint64_t lo = ex->cuts[g], hi = ex->cuts[g + 1];
+        for (uint64_t q = lo; q < hi; q++) ex->blk_nnz[g] += row_nnz[q];
+        if (ex->blk_nnz[g] == 0) continue;
+        th.emplace_back([&, g, lo, hi] {
+            // rows are sorted (struct.cc:125): the block is one contiguous run of the COO streams
+            const uint64_t b = (uint64_t)(std::lower_bound(r.begin(), r.end(), lo) - r.begin()), e = (uint64_t)(std::lower_bound(r.begin(), r.end(), hi) - r.begin());
+            std::vector<uint32_t> br(e - b), bc(e - b);
+            std::vector<float> bv(e - b);
+            for (uint64_t i = b; i < e; i++) br[i - b] = (uint32_t)(r[i] - lo), bc[i - b] = (uint32_t)c[i], bv[i - b] = (float)v[i];
+            gs_plan_desc d;
+            if (gs_transform_host_coo(ex->ctx[g], family, hi - lo, ex->cols, e - b, br.data(), bc.data(), bv.data(), N, sparse_coarsen, coarsen, half, 0, &d, nullptr) != GS_OK ||
+                gs_plan_create(ex->ctx[g], &d, N, half, &ex->plan[g]) != GS_OK || (kernel != GS_KERNEL_CHAIN && gs_plan_set_kernel(ex->plan[g], kernel) != GS_OK))
+                err[g] = gs_last_error();
+        });
+    }
+    for (std::thread &t : th) t.join();
+    for (int g = 0; g < ex->n; g++)
+        if (!err[g].empty()) throw gs::Error("device " + std::to_string(ex->dev[g]) + ": " + err[g]);
+    GS_API_END
+}
+
 gs_status gs_exec_row_cuts(const gs_exec *ex, uint64_t *cuts, uint64_t *block_nnz)
 {
     GS_API_BEGIN

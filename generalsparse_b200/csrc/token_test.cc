@@ -134,7 +134,8 @@ int main(int argc, char **argv)
             exit(2);
             return 0;
         }();
-        OK(gs_exec_build(ex, ms, fam, N, S, C, half, k));
+        if (device_transform) OK(gs_exec_build_on_device(ex, ms, fam, N, S, C, half, k)); // every block's chain built by its GPU
+        else OK(gs_exec_build(ex, ms, fam, N, S, C, half, k));
         uint64_t rows = 0, cols = 0, nnz = 0, one = 0;
         OK(gsh_metadata_read_u64(ms, "GLOBAL_META_origin_row_num_-1", &rows, 1));
         OK(gsh_metadata_read_u64(ms, "GLOBAL_META_origin_col_num_-1", &cols, 1));

@@ -322,6 +322,9 @@ gs_status gs_exec_create(gs_exec **out, const int *device_ids, int n_dev);
 void gs_exec_destroy(gs_exec *ex);
 int gs_exec_devices(const gs_exec *ex);
 gs_status gs_exec_build(gs_exec *ex, const gsh_metadata *ms, int family, int N, int sparse_coarsen, int coarsen, int half, int kernel);
+/* the same partition with every block's chain built by its device (gs_transform_host_coo above, one host thread per device) instead of the host
+ * pipeline; families: those gs_transform_device builds */
+gs_status gs_exec_build_on_device(gs_exec *ex, const gsh_metadata *ms, int family, int N, int sparse_coarsen, int coarsen, int half, int kernel);
 gs_status gs_exec_row_cuts(const gs_exec *ex, uint64_t *cuts /* n_dev + 1 */, uint64_t *block_nnz /* n_dev, may be NULL */);
 const char *gs_exec_kernel_name(const gs_exec *ex, int g);
 gs_status gs_exec_set_dense(gs_exec *ex, const void *B_host, int dtype);

@@ -101,6 +101,36 @@ def test_executor_parity_and_allgather(built_lib, G, family, kernel, N, half):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("G", [1, 2, 8])
+@pytest.mark.parametrize("family,kernel,N,half", [("thread_total", "auto", 8, True), ("warp_segment", "chain", 32, False), ("thread_bit_map", "auto", 32, False), ("warp_total", "chain", 4, False)])
+def test_executor_blocks_built_on_device(built_lib, G, family, kernel, N, half):
+    """gs_exec_build_on_device: every block's chain comes from its GPU's transform passes; same cuts, same kernels, same C as the
+    blocks built by the host pipeline (bit-equal where the kernel is deterministic)"""
+    from generalsparse_b200 import api, synth
+    if _devices() < G:
+        pytest.skip("needs %d GPUs" % G)
+    r, c = _matrix()
+    rows = cols = 3000
+    vals = synth.synth_values(len(r), seed=3)
+    B = synth.synth_dense(cols, N, seed=3)
+    if half:
+        vals, B = vals.astype(np.float16).astype(np.float32), B.astype(np.float16).astype(np.float32)
+    ms = api.MetaDataSet.from_coo(rows, cols, r, c, vals)
+    S = 8 if family == "thread_total" else 1
+    eh = api.Executor(list(range(G))).build(ms, family, N, S, 1, half=half, kernel=kernel)
+    ed = api.Executor(list(range(G))).build(ms, family, N, S, 1, half=half, kernel=kernel, on_device=True)
+    assert np.array_equal(eh.row_cuts()[0], ed.row_cuts()[0]) and np.array_equal(eh.row_cuts()[1], ed.row_cuts()[1])
+    assert [eh.kernel_name(g) for g in range(G)] == [ed.kernel_name(g) for g in range(G)]
+    eh.set_dense(B), ed.set_dense(B)
+    eh.run(2), ed.run(2)
+    Ch, Cd = eh.output().astype(np.float32), ed.output().astype(np.float32)
+    if family in ("thread_bit_map", "warp_segment") or "merge" in ed.kernel_name(0) or "nnz" in ed.kernel_name(0):
+        assert np.allclose(Ch, Cd, rtol=1e-5, atol=1e-5)
+    else:
+        assert np.array_equal(Ch, Cd)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("G", [2, 8])
 def test_token_test_gpus(built_lib, tmp_path, G):
     """`token_test c1.mtx 8 --gpus G --allgather`: the driver's multi-GPU switch is functional (round 1 swallowed it)"""
