@@ -449,6 +449,67 @@ template <int N, int P, int NL, int RW, int TL = 0, bool CP = false> __global__ 
         // row, NL = 32: each takes 32 bytes.  B's rows lie as the tensor map swizzled them; an entry carries the byte offset of
         // its row's chunk 0 (host/sp24_format.hpp, sp24_b_row_offset), chunk c is at offset ^ (c << 4).  fp16 x fp16 + fp32 in
         // one instruction (fma.rn.f32.f16: the exact product, one rounding -- what fmaf of the converted operands gives).
+        if constexpr (NL == 32) {
+            // NL = 32 (round 2): FOUR threads per tile row, one 16-byte chunk of B's row each, the tile's rows in two passes of 64.  The pair-of-
+            // threads form below (32 bytes per thread) issues 128-bit loads whose eight lanes per wavefront point at eight different rows of B:
+            // ~960 shared-memory wavefronts per tile, 58 % of them bank conflicts -- more than the MMA operands and the copies together, and what
+            // holds C2 N = 32 at 58 % of its roofline (profiles/traffic.json C2_N32_half_sp24; the remainder skipped: 9.95 us against 14.6).  With
+            // four lanes on one row a wavefront's eight lanes read two whole 64-byte rows, which collide only when both fall into the same half
+            // of the banks.  Same entries per row, same order of the sums; a warp now spans 8 rows instead of 16 (less waiting for its longest).
+            const uint32_t rt = threadIdx.x - (EPILOGUE_WARP0 + 4) * 32, rq = rt >> 2, coff = (rt & 3u) << 4;
+            const unsigned char *ring = smem_raw + (smem0 - smem_u32(smem_raw));
+            uint32_t it = 0, seg = 0, s = 0, ph = 0, panel = 0, pbeg = 0, pend = 0;
+            while (it < n_local) {
+                seg_begin<CP>(a, t0 + it, it == 0, panel, pbeg, pend);
+                const uint32_t len = min(pend - (t0 + it), n_local - it);
+                float acc[2][8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) acc[0][j] = acc[1][j] = 0.f;
+                for (uint32_t i = 0; i < len; i++) {
+                    mbar_wait(full0 + 8u * s, ph);
+                    if (a.rem_on) {
+                        const unsigned char *st = ring + s * STG, *bs = st + BOFF;
+                        const unsigned short *start = (const unsigned short *)(st + IMG_BYTES);
+                        const uint32_t *ent = (const uint32_t *)(st + IMG_BYTES + 272);
+#pragma unroll
+                        for (int pass = 0; pass < 2; pass++) {
+                            const uint32_t rrow = rq + 64u * pass, e1 = start[rrow + 1];
+                            uint32_t e = start[rrow];
+                            // two entries per round; the next round's entry words are requested before this round's rows of B
+                            uint32_t w0 = e < e1 ? ent[e] : 0u, w1 = e + 1 < e1 ? ent[e + 1] : 0u;
+#pragma unroll 1
+                            for (; e < e1; e += 2) {
+                                const bool two = e + 1 < e1; // a missing second entry reads row 0 and is not added
+                                const uint32_t n0 = e + 2 < e1 ? ent[e + 2] : 0u, n1 = e + 3 < e1 ? ent[e + 3] : 0u;
+                                const uint4 b0 = *(const uint4 *)(bs + ((w0 >> 16) ^ coff)), b1 = *(const uint4 *)(bs + ((w1 >> 16) ^ coff));
+                                const unsigned short v0 = (unsigned short)(w0 & 0xffffu), v1 = (unsigned short)(w1 & 0xffffu);
+                                const uint32_t q0[4] = {b0.x, b0.y, b0.z, b0.w}, q1[4] = {b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                                for (int k = 0; k < 4; k++) fma_f16(acc[pass][2 * k], v0, (unsigned short)(q0[k] & 0xffffu)), fma_f16(acc[pass][2 * k + 1], v0, (unsigned short)(q0[k] >> 16));
+                                if (two) {
+#pragma unroll
+                                    for (int k = 0; k < 4; k++) fma_f16(acc[pass][2 * k], v1, (unsigned short)(q1[k] & 0xffffu)), fma_f16(acc[pass][2 * k + 1], v1, (unsigned short)(q1[k] >> 16));
+                                }
+                                w0 = n0, w1 = n1;
+                            }
+                        }
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(empty0 + 8u * s); // this warp has read the stage
+                    if (++s == S) s = 0, ph ^= 1u;
+                }
+                mbar_wait(reme0, (seg & 1u) ^ 1u); // the epilogue has read the previous segment's product
+#pragma unroll
+                for (int pass = 0; pass < 2; pass++) {
+                    float4 *dst = (float4 *)(rem_buf + (rq + 64u * pass) * NL + (rt & 3u) * 8u);
+                    dst[0] = make_float4(acc[pass][0], acc[pass][1], acc[pass][2], acc[pass][3]);
+                    dst[1] = make_float4(acc[pass][4], acc[pass][5], acc[pass][6], acc[pass][7]);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(remf0);
+                it += len, seg++;
+            }
+        } else {
         constexpr int CPT = NL >= 32 ? NL / 16 : 1, NA = 8 * CPT; // NL = 64: 64 bytes of B's row per thread, one entry per round (registers)
         constexpr bool TWO = NL <= 32;
         const uint32_t rt = threadIdx.x - (EPILOGUE_WARP0 + 4) * 32, rrow = rt >> 1, sub = rt & 1u;
@@ -517,6 +578,7 @@ template <int N, int P, int NL, int RW, int TL = 0, bool CP = false> __global__ 
             if (lane == 0) mbar_arrive(remf0);
             it += len, seg++;
         }
+        } // NL != 32
     } else if (RW != 0 && warp >= EPILOGUE_WARP0 + 4) {
         // ------------------------------------------------------------------------------------------ remainder
         // a pair of threads per row of the panel this CTA owns: at NL = 8 the two take alternate entries of the row, at

@@ -125,6 +125,32 @@ void localize_sp24_remainder(const sp24_image &im, uint32_t row_bytes, sp24_tile
         for (uint32_t kt = 0; kt < im.k_tiles; kt++) {
             uint8_t *unit = out.bytes.data() + ((uint64_t)p * im.k_tiles + kt) * out.unit_bytes;
             uint32_t n = 0;
+            if (row_bytes == 64) {
+                // N = 32: four threads read one 64-byte row of B (b200_sp24.cuh, NL = 32), a wavefront's eight lanes cover tile rows 2 j and 2 j + 1, and the
+                // two reads collide exactly when both rows of B lie in the same 64-byte half of the banks, i.e. when the two column indices have the
+                // same parity.  So an even tile row lists its even-column entries first, and its odd neighbour picks, position by position, an entry
+                // of the other parity while it has one.
+                auto half_of = [](uint32_t w) { return ((w >> 16) >> 6) & 1u; };
+                for (uint32_t rr = 0; rr < SP24_ROWS; rr += 2) {
+                    std::vector<uint32_t> &e0 = rows_of_tile[(size_t)kt * SP24_ROWS + rr], &e1 = rows_of_tile[(size_t)kt * SP24_ROWS + rr + 1];
+                    std::stable_partition(e0.begin(), e0.end(), [&](uint32_t w) { return half_of(w) == 0; });
+                    for (size_t pos = 0; pos < e1.size(); pos++) {
+                        const uint32_t want = pos < e0.size() ? 1u - half_of(e0[pos]) : 1u;
+                        for (size_t q = pos; q < e1.size(); q++)
+                            if (half_of(e1[q]) == want) {
+                                std::swap(e1[pos], e1[q]);
+                                break;
+                            }
+                    }
+                    for (uint32_t r2 = rr; r2 < rr + 2; r2++) {
+                        unit[SP24_TILE_BYTES + 2u * r2] = (uint8_t)(n & 0xff), unit[SP24_TILE_BYTES + 2u * r2 + 1] = (uint8_t)(n >> 8);
+                        for (uint32_t w : rows_of_tile[(size_t)kt * SP24_ROWS + r2]) {
+                            uint8_t *dst = unit + SP24_TILE_BYTES + SP24_REM_HEADER + 4u * n++;
+                            dst[0] = (uint8_t)w, dst[1] = (uint8_t)(w >> 8), dst[2] = (uint8_t)(w >> 16), dst[3] = (uint8_t)(w >> 24);
+                        }
+                    }
+                }
+            } else
             for (uint32_t w0 = 0; w0 < SP24_ROWS; w0 += 16) { // the 16 rows of one remainder warp
                 std::vector<std::array<uint16_t, 8>> used; // used[position][bank group]
                 for (uint32_t rr = w0; rr < w0 + 16; rr++) {
