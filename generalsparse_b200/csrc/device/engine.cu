@@ -698,8 +698,8 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
     GS_REQUIRE(ctx && desc_out && row_dev && col_dev && val_dev, "null argument");
     GS_REQUIRE(N >= 1 && sparse_coarsen >= 1 && coarsen >= 1, "N, sparse_coarsen and coarsen must be >= 1");
     GS_REQUIRE(as_id >= 0, "as_id must be >= 0");
-    if (family != GS_FAMILY_THREAD_TOTAL && family != GS_FAMILY_WARP_TOTAL && family != GS_FAMILY_THREAD_BITMAP && family != GS_FAMILY_WARP_SEGMENT)
-        return fail(GS_ERR_UNSUPPORTED, "gs_transform_device builds the thread_total, warp_total, thread_bit_map and warp_segment driver chains; the others are built on the host (gsh_session_run_family)");
+    if (family != GS_FAMILY_THREAD_TOTAL && family != GS_FAMILY_WARP_TOTAL && family != GS_FAMILY_TBLOCK_TOTAL && family != GS_FAMILY_THREAD_BITMAP && family != GS_FAMILY_WARP_SEGMENT)
+        return fail(GS_ERR_UNSUPPORTED, "gs_transform_device builds the thread_total, warp_total, block_total, thread_bit_map and warp_segment driver chains; the others are built on the host (gsh_session_run_family)");
     CUDA_TRY(cudaSetDevice(ctx->device));
     ctx->join_async();
     const double bound = (double)gs::get_config().as_integer("PADDING_RATE_UP_BOUND");
@@ -723,7 +723,13 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
         y = (unsigned)std::min(N / coarsen, 32);
         GS_REQUIRE(y >= 1, "N / coarsen must be >= 1");
         x = std::max(256 / y, 32u), grid_x = (unsigned)rows;
+        d.sparse_coarsen = 1; // (the warp / tblock total tokens carry no sparse coarsening: compile() leaves the default)
         e = gsd::transform_row_chain(m, false, 0, half != 0, "WARP_META", bound, ctx->stream, out);
+    } else if (family == GS_FAMILY_TBLOCK_TOTAL) { // token_test.cc:1458-1514
+        x = (unsigned)std::min(N, 32);
+        y = 256 / x, grid_x = (unsigned)rows;
+        d.sparse_coarsen = 1;
+        e = gsd::transform_row_chain(m, false, 0, half != 0, "TBLOCK_META", bound, ctx->stream, out);
     } else if (family == GS_FAMILY_WARP_SEGMENT) { // token_test.cc:1393-1455
         x = (unsigned)std::min(N, 32);
         y = 256 / x, grid_x = (unsigned)(nnz / 128 + 1);
@@ -750,7 +756,7 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
     // what compile() registers for the family, in its order (operators.cc: code_generator::compile)
     std::vector<std::pair<const char *, const char *>> deps = {{"GLOBAL_META", "nz_col_indices"}, {"GLOBAL_META", "nz_vals"}};
     if (out.has_perm) deps.push_back({"GLOBAL_META", "original_nz_row_indices"});
-    const char *lvl = family == GS_FAMILY_WARP_TOTAL ? "WARP_META" : "THREAD_META";
+    const char *lvl = family == GS_FAMILY_WARP_TOTAL ? "WARP_META" : family == GS_FAMILY_TBLOCK_TOTAL ? "TBLOCK_META" : "THREAD_META";
     if (family == GS_FAMILY_WARP_SEGMENT) deps.push_back({"WARP_META", "first_BMT_indices"});
     deps.push_back({lvl, "first_row_indices"}), deps.push_back({lvl, "first_nz_indices"});
     if (family == GS_FAMILY_THREAD_BITMAP)

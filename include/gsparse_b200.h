@@ -214,8 +214,8 @@ gs_status gs_upload_session_as(gs_ctx *ctx, const gsh_session *s, int half, int 
  * exactly as gs_upload_session_as would have stored the host pipeline's -- byte for byte the same device arrays (tests/
  * test_device_transform_gpu.py).  Families: GS_FAMILY_THREAD_TOTAL = sort_operator (sort_operator.cc:70-108: get_row_order_by_length,
  * reorder_{val,col,row}_by_index, remove_empty_row_in_end_of_sub_matrix) + fixed_interval_row_direction_thread_blocking_operator(1,
- * col pad to sparse_coarsen; ...thread_blocking_operator.cc:482-565); GS_FAMILY_WARP_TOTAL = fixed_interval_row_direction_warp_
- * blocking_operator(1), no sort, no pad; GS_FAMILY_THREAD_BITMAP = fixed_interval_nnz_direction_thread_blocking_operator(32, pad) +
+ * col pad to sparse_coarsen; ...thread_blocking_operator.cc:482-565); GS_FAMILY_WARP_TOTAL / GS_FAMILY_TBLOCK_TOTAL = fixed_interval_row_
+ * direction_{warp,tblock}_blocking_operator(1), no sort, no pad; GS_FAMILY_THREAD_BITMAP = fixed_interval_nnz_direction_thread_blocking_operator(32, pad) +
  * thread_bit_map_operator (thread_bit_map.cc, segment_{ptr,empty_flag,empty_row_indices}.cc); GS_FAMILY_WARP_SEGMENT = the same blocking +
  * thread_bit_map_operator at WARP level (a segment start forced at every VECTOR_WIDTH-th BMT) + warp_segment_reduce_operator (segment_offset.cc,
  * get_begin_BMTs_after_merge_thread.cc).  desc_out is what

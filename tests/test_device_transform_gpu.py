@@ -1,4 +1,4 @@
-"""the transform steps of four driver chains run as CUDA passes (csrc/device/transform.cu: binary searches, block
+"""the transform steps of five driver chains run as CUDA passes (csrc/device/transform.cu: binary searches, block
 scans, a stable LSD radix sort, warp ballots) instead of the host pipeline.  The bar is the host pipeline itself, which tests/test_golden.py pins
 byte for byte to the reference's dumps: every device array the chain registers must come out with the same dtype and the same bytes, the plan
 descriptor must be the one compile() gives, and a plan on the device-built arrays must pick the same kernel and produce the same C."""
@@ -33,7 +33,7 @@ def _desc_fields(d, strip_id):
                 grid=tuple(d.grid), block=tuple(d.block), rows=d.rows, cols=d.cols, nnz=d.origin_nnz, stored=d.stored_nnz, deps=deps)
 
 
-@pytest.mark.parametrize("family,S", [("thread_total", 2), ("thread_total", 8), ("warp_total", 1), ("thread_bit_map", 1), ("warp_segment", 1)])
+@pytest.mark.parametrize("family,S", [("thread_total", 2), ("thread_total", 8), ("warp_total", 1), ("thread_bit_map", 1), ("warp_segment", 1), ("block_total", 1), ("warp_total", 4)])
 @pytest.mark.parametrize("N,half", [(8, False), (32, True), (1, False)])
 def test_device_chain_equals_host_chain(engine, family, S, N, half):
     from generalsparse_b200 import api, synth
