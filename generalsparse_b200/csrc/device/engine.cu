@@ -698,8 +698,8 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
     GS_REQUIRE(ctx && desc_out && row_dev && col_dev && val_dev, "null argument");
     GS_REQUIRE(N >= 1 && sparse_coarsen >= 1 && coarsen >= 1, "N, sparse_coarsen and coarsen must be >= 1");
     GS_REQUIRE(as_id >= 0, "as_id must be >= 0");
-    if (family != GS_FAMILY_THREAD_TOTAL && family != GS_FAMILY_WARP_TOTAL && family != GS_FAMILY_TBLOCK_TOTAL && family != GS_FAMILY_THREAD_BITMAP && family != GS_FAMILY_WARP_SEGMENT)
-        return fail(GS_ERR_UNSUPPORTED, "gs_transform_device builds the thread_total, warp_total, block_total, thread_bit_map and warp_segment driver chains; the others are built on the host (gsh_session_run_family)");
+    if (family < GS_FAMILY_THREAD_TOTAL || family > GS_FAMILY_TBLOCK_BITMAP)
+        return fail(GS_ERR_UNSUPPORTED, "gs_transform_device builds the seven driver chains (the reference families); other operator sequences are built on the host (gsh_session_add_and_run)");
     CUDA_TRY(cudaSetDevice(ctx->device));
     ctx->join_async();
     const double bound = (double)gs::get_config().as_integer("PADDING_RATE_UP_BOUND");
@@ -730,6 +730,17 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
         y = 256 / x, grid_x = (unsigned)rows;
         d.sparse_coarsen = 1;
         e = gsd::transform_row_chain(m, false, 0, half != 0, "TBLOCK_META", bound, ctx->stream, out);
+    } else if (family == GS_FAMILY_WARP_BITMAP) { // token_test.cc:1253-1315
+        y = (unsigned)std::min(N / coarsen, 32);
+        GS_REQUIRE(y >= 1, "N / coarsen must be >= 1");
+        x = std::max(128 / y, 32u), grid_x = (unsigned)rows;
+        d.need_warp_reduction = 1;
+        e = gsd::transform_col_chain(m, 64, x, true, half != 0, bound, ctx->stream, out);
+    } else if (family == GS_FAMILY_TBLOCK_BITMAP) { // token_test.cc:1518-1582
+        x = (unsigned)std::min(N / coarsen, 32);
+        GS_REQUIRE(x >= 1, "N / coarsen must be >= 1");
+        y = 256 / x, grid_x = (unsigned)rows;
+        e = gsd::transform_col_chain(m, 64, y, false, half != 0, bound, ctx->stream, out); // (the driver hands the operator block[1] before grid_block_operator rounds its own copy)
     } else if (family == GS_FAMILY_WARP_SEGMENT) { // token_test.cc:1393-1455
         x = (unsigned)std::min(N, 32);
         y = 256 / x, grid_x = (unsigned)(nnz / 128 + 1);
@@ -749,7 +760,7 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
     }
     d.vector_width = (int)x;
     d.block[0] = x, d.block[1] = y % 2 ? y + 1 : y; // grid_block_operator.cc:13-33
-    const unsigned per = ((family == GS_FAMILY_WARP_TOTAL || family == GS_FAMILY_WARP_SEGMENT) ? d.block[1] : d.block[0]) * (unsigned)coarsen; // a WARP first_nz_indices exists
+    const unsigned per = ((family == GS_FAMILY_WARP_TOTAL || family == GS_FAMILY_WARP_SEGMENT || family == GS_FAMILY_WARP_BITMAP) ? d.block[1] : d.block[0]) * (unsigned)coarsen; // a WARP first_nz_indices exists
     d.grid[0] = grid_x, d.grid[1] = (unsigned)((N + per - 1) / per);
     d.has_row_permutation = out.has_perm, d.stored_nnz = out.stored_nnz;
     drop_arrays_of_id(ctx, as_id);
@@ -758,7 +769,15 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
     if (out.has_perm) deps.push_back({"GLOBAL_META", "original_nz_row_indices"});
     const char *lvl = family == GS_FAMILY_WARP_TOTAL ? "WARP_META" : family == GS_FAMILY_TBLOCK_TOTAL ? "TBLOCK_META" : "THREAD_META";
     if (family == GS_FAMILY_WARP_SEGMENT) deps.push_back({"WARP_META", "first_BMT_indices"});
-    deps.push_back({lvl, "first_row_indices"}), deps.push_back({lvl, "first_nz_indices"});
+    if (family == GS_FAMILY_WARP_BITMAP)
+        for (const auto &k : {std::pair<const char *, const char *>{"WARP_META", "first_row_indices"}, {"WARP_META", "first_nz_indices"}, {"WARP_META", "first_BMT_indices"}, {"WARP_META", "bit_map_of_thread"},
+                              {"THREAD_META", "first_row_indices_without_ending"}, {"THREAD_META", "first_nz_indices_relative_to_BMW"}})
+            deps.push_back(k);
+    else if (family == GS_FAMILY_TBLOCK_BITMAP)
+        for (const auto &k : {std::pair<const char *, const char *>{"TBLOCK_META", "first_BMT_indices"}, {"THREAD_META", "first_nz_indices"}, {"THREAD_META", "first_row_indices_without_ending"},
+                              {"THREAD_META", "bit_map_of_thread"}, {"THREAD_META", "segment_offset"}})
+            deps.push_back(k);
+    else deps.push_back({lvl, "first_row_indices"}), deps.push_back({lvl, "first_nz_indices"});
     if (family == GS_FAMILY_THREAD_BITMAP)
         for (const char *n : {"thread_bit_map", "segment_ptr", "segment_empty_flag", "segment_empty_row_indices"}) deps.push_back({"THREAD_META", n});
     if (family == GS_FAMILY_WARP_SEGMENT)

@@ -371,7 +371,7 @@ __global__ void __launch_bounds__(256) k_bmt_pass(const uint32_t *row_pad, uint3
 
 // segment_offset.cc: a BMT whose bit map is not zero gets the number of all-zero BMTs between it and the next non-zero one; the run that reaches
 // the end of the array is never written back (kept: the reference's loop ends without flushing it)
-__global__ void k_segment_offset(const uint64_t *bit_map, uint32_t n_bmt, uint32_t *out)
+template <typename W> __global__ void k_segment_offset(const W *bit_map, uint32_t n_bmt, uint32_t *out)
 {
     for (uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; b < n_bmt; b += (uint64_t)gridDim.x * blockDim.x) {
         uint32_t v = 0;
@@ -397,6 +397,41 @@ __global__ void k_pack_flags(const uint8_t *flag, uint32_t n_bmt, uint32_t size,
         uint64_t word = 0;
         for (uint32_t j = 0; j < size && w * size + j < n_bmt; j++) word |= (uint64_t)flag[w * size + j] << j;
         out[w] = word;
+    }
+}
+
+// ---- column direction (rows padded to whole BMTs of `c` non-zeros) ------------------------------------------------------------------------------
+// get_begin_{rows,nzs}_of_BMT_after_fixed_blocking_in_col_direction.cc: BMT b is non-zeros [c b, c b + c) and lies in the row of its first one;
+// get_begin_nzs_relative_to_parent_after_merge_thread.cc: the same offsets counted from the first BMT of the group of `m`
+__global__ void k_col_bmts(const uint32_t *row_pad, uint32_t n_bmt, uint32_t c, uint32_t m, uint32_t *bmt_row, uint32_t *first_nz, uint32_t *nz_rel)
+{
+    for (uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; b <= n_bmt; b += (uint64_t)gridDim.x * blockDim.x) {
+        first_nz[b] = (uint32_t)b * c;
+        if (b < n_bmt) {
+            bmt_row[b] = row_pad[b * c];
+            if (nz_rel) nz_rel[b] = (uint32_t)(b % m) * c;
+        }
+    }
+}
+// get_begin_rows_after_merge_thread.cc (sample_with_last): every m-th entry while another follows, then the last one
+__global__ void k_sample_with_last(const uint32_t *in, uint32_t n_in, uint32_t m, uint32_t *out, uint32_t n_out)
+{
+    for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_out; j += (uint64_t)gridDim.x * blockDim.x) out[j] = j + 1 < n_out ? in[j * m] : in[n_in - 1];
+}
+// parent_bit_map_of_thread.cc: a BMT starts a segment when its row differs from the BMT before it, and every m-th BMT does.  WARP level: m bits per
+// u64 word, first BMT in the LSB; TBLOCK level: one 0 / 1 per BMT
+__global__ void k_parent_bits(const uint32_t *bmt_row, uint32_t n_bmt, uint32_t m, uint64_t *words, uint32_t n_words, uint32_t *flags)
+{
+    const uint64_t n = words ? n_words : n_bmt;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        if (words) {
+            uint64_t w = 0;
+            for (uint32_t j = 0; j < m && i * m + j < n_bmt; j++) {
+                const uint64_t b = i * m + j;
+                if (j == 0 || bmt_row[b] != bmt_row[b - 1]) w |= 1ull << j;
+            }
+            words[i] = w;
+        } else flags[i] = (i == 0 || i % m == 0 || bmt_row[i] != bmt_row[i - 1]) ? 1u : 0u;
     }
 }
 
@@ -628,8 +663,86 @@ cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool warp_level
         const uint32_t g = n_bmt % size ? 1u : size;
         take(out, "WARP_META", "first_BMT_indices", first_bmt, n_w, GS_U32, n_bmt, n_bmt % size ? std::__gcd(size, n_bmt) : size, size == 1, n_bmt % size == 0, size);
         (void)g;
-        k_segment_offset<<<blocks_for(n_bmt, 256), 256, 0, s>>>(bit_map, n_bmt, seg_off);
+        k_segment_offset<uint64_t><<<blocks_for(n_bmt, 256), 256, 0, s>>>(bit_map, n_bmt, seg_off);
         k_group_starts<<<blocks_for(n_w, 256), 256, 0, s>>>(first_bmt, n_w, size, n_bmt);
+        TRY(cudaGetLastError());
+    }
+    return cudaStreamSynchronize(s);
+}
+
+} // namespace gsd
+
+namespace gsd {
+
+// fixed_interval_col_direction_thread_blocking_operator(64, pad to the column block) + thread_total_reduce_operator, then
+//   warp_level:  warp_bit_map_operator(C, relative nz, relative row) -- BMWs of `group` BMTs: WARP first_{row,nz,BMT}_indices, WARP bit_map_of_thread, THREAD
+//                first_nz_indices_relative_to_BMW, WARP first_row_indices_relative_to_BMW
+//   !warp_level: tblock_thread_bit_map_operator(C, group) -- BMTBs of `group` BMTs: TBLOCK first_BMT_indices, THREAD bit_map_of_thread, THREAD segment_offset
+cudaError_t transform_col_chain(const coo_dev &m, uint32_t col_block, uint32_t group, bool warp_level, bool half, double pad_bound, cudaStream_t s, transform_out &out)
+{
+    TRY(transform_row_chain(m, false, col_block, half, "ROW_TMP", pad_bound, s, out)); // (the padding refusal comes first, as on the host)
+    if (group < 1 || (warp_level && group > 64)) { // parent_bit_map_of_thread.cc packs VECTOR_WIDTH BMTs per u64 word
+        out.error = "parent_bit_map_of_thread: VECTOR_WIDTH must be in 1..64";
+        return cudaErrorInvalidValue;
+    }
+    // the row level of the padded stream is scaffolding here: the chain registers BMT-level arrays only
+    uint32_t *row_pad = nullptr;
+    for (size_t i = 0; i < out.arrays.size();) {
+        if (out.arrays[i].pos == "ROW_TMP") {
+            cudaFreeAsync(out.arrays[i].ptr, s);
+            out.arrays.erase(out.arrays.begin() + i);
+        } else {
+            if (out.arrays[i].name == "nz_row_indices") row_pad = (uint32_t *)out.arrays[i].ptr;
+            i++;
+        }
+    }
+    const uint32_t nnz_pad = (uint32_t)out.stored_nnz, n_bmt = nnz_pad / col_block;
+    if (!row_pad || n_bmt == 0 || nnz_pad % col_block) return cudaErrorInvalidValue;
+    uint32_t *bmt_row = nullptr, *first_nz = nullptr, *nz_rel = nullptr, *first_bmt = nullptr;
+    TRY(alloc_out(&bmt_row, n_bmt, s));
+    take(out, "THREAD_META", "first_row_indices_without_ending", bmt_row, n_bmt, GS_U32, m.rows - 1, 0);
+    // (the warp_bitmap chain registers the BMT offsets relative to their BMW only: the absolute ones are scratch there, as in the host's upload)
+    scratch sc(s);
+    if (warp_level) TRY(sc.get(&first_nz, (uint64_t)n_bmt + 1));
+    else {
+        TRY(alloc_out(&first_nz, (uint64_t)n_bmt + 1, s));
+        take(out, "THREAD_META", "first_nz_indices", first_nz, (uint64_t)n_bmt + 1, GS_U32, nnz_pad, col_block, false, true, col_block);
+    }
+    if (warp_level) {
+        TRY(alloc_out(&nz_rel, n_bmt, s));
+        take(out, "THREAD_META", "first_nz_indices_relative_to_BMW", nz_rel, n_bmt, GS_U32, (uint64_t)(std::min(group, n_bmt) - 1) * col_block, group > 1 ? col_block : 0);
+    }
+    k_col_bmts<<<blocks_for((uint64_t)n_bmt + 1, 256 * 4), 256, 0, s>>>(row_pad, n_bmt, col_block, group, bmt_row, first_nz, nz_rel);
+    TRY(cudaGetLastError());
+    const uint32_t n_g = (n_bmt + group - 1) / group + 1; // [0, group, ..., n_bmt]
+    TRY(alloc_out(&first_bmt, n_g, s));
+    take(out, warp_level ? "WARP_META" : "TBLOCK_META", "first_BMT_indices", first_bmt, n_g, GS_U32, n_bmt, n_bmt % group ? std::__gcd(group, n_bmt) : group, group == 1, n_bmt % group == 0, group);
+    k_group_starts<<<blocks_for(n_g, 256), 256, 0, s>>>(first_bmt, n_g, group, n_bmt);
+    TRY(cudaGetLastError());
+    if (warp_level) {
+        uint32_t *w_row = nullptr, *w_nz = nullptr, *row_rel = nullptr;
+        uint64_t *bits = nullptr;
+        const uint32_t n_wr = (n_bmt - 1 + group - 1) / group + 1; // sample_with_last over n_bmt entries: one entry fewer than the offsets when (n_bmt - 1) % group == 0
+        TRY(alloc_out(&w_row, n_wr, s));
+        take(out, "WARP_META", "first_row_indices", w_row, n_wr, GS_U32, m.rows - 1, 0);
+        TRY(alloc_out(&w_nz, n_g, s));
+        take(out, "WARP_META", "first_nz_indices", w_nz, n_g, GS_U32, nnz_pad, 0);
+        const uint32_t n_words = (n_bmt + group - 1) / group;
+        TRY(alloc_out(&bits, n_words, s));
+        take(out, "WARP_META", "bit_map_of_thread", bits, n_words, GS_U64, 0, 0);
+        k_sample_with_last<<<blocks_for(n_wr, 256), 256, 0, s>>>(bmt_row, n_bmt, group, w_row, n_wr);
+        k_sample_with_last<<<blocks_for(n_g, 256), 256, 0, s>>>(first_nz, n_bmt + 1, group, w_nz, n_g);
+        k_parent_bits<<<blocks_for(n_words, 256), 256, 0, s>>>(bmt_row, n_bmt, group, bits, n_words, nullptr);
+        TRY(cudaGetLastError());
+        (void)row_rel;
+    } else {
+        uint32_t *flags = nullptr, *seg_off = nullptr;
+        TRY(alloc_out(&flags, n_bmt, s));
+        take(out, "THREAD_META", "bit_map_of_thread", flags, n_bmt, GS_U32, 1, 0);
+        TRY(alloc_out(&seg_off, n_bmt, s));
+        take(out, "THREAD_META", "segment_offset", seg_off, n_bmt, GS_U32, 0, 0);
+        k_parent_bits<<<blocks_for(n_bmt, 256), 256, 0, s>>>(bmt_row, n_bmt, group, nullptr, 0, flags);
+        k_segment_offset<uint32_t><<<blocks_for(n_bmt, 256), 256, 0, s>>>(flags, n_bmt, seg_off);
         TRY(cudaGetLastError());
     }
     return cudaStreamSynchronize(s);

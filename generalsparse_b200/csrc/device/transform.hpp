@@ -51,4 +51,8 @@ cudaError_t transform_row_chain(const coo_dev &m, bool sort, uint32_t S, bool ha
 // warp_segment_reduce_operator adds THREAD segment_offset and WARP first_BMT_indices (BMWs of `size` BMTs)
 cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool warp_level, bool half, double pad_bound, cudaStream_t s, transform_out &out);
 
+// fixed_interval_col_direction_thread_blocking_operator(col_block, pad) + thread_total_reduce_operator + warp_bit_map_operator (warp_level: BMWs of
+// `group` BMTs) or tblock_thread_bit_map_operator (BMTBs of `group` BMTs): the warp_bitmap / block_bitmap driver chains
+cudaError_t transform_col_chain(const coo_dev &m, uint32_t col_block, uint32_t group, bool warp_level, bool half, double pad_bound, cudaStream_t s, transform_out &out);
+
 } // namespace gsd

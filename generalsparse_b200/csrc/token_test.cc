@@ -18,7 +18,7 @@
 //   --dump <dir>                      write every metadata array as text, one value per line (struct.cc:1991)
 //   --gpus G                          the matrix is cut into G nnz-balanced row blocks, one per GPU 0..G-1 (gs_exec_*: B replicated,
 //                                     C rows disjoint, no collective); --allgather: then replicate C on every GPU over NCCL and time it
-//   --device-transform                the driver's chain (default / warp_total / thread_bit_map / warp_segment family) is built by device passes from the loader's COO
+//   --device-transform                the driver's chain (any --family) is built by device passes from the loader's COO
 //                                     (gs_transform_host_coo) instead of the host transform steps; prints the device time
 //   --no-parity                       skip the host check (the reference always checks, code_generator.cc:631-638)
 //   --corrupt-check                   flip one element of the host copy of C before the check (shows that the check can fail)
@@ -197,7 +197,7 @@ int main(int argc, char **argv)
     gs_plan_desc desc;
     if (device_transform) {
         // the driver's chain built by device passes from the loader's COO (gs_transform_host_coo) -- no host transform steps
-        if (!ops.empty()) die("--device-transform builds the thread_total / warp_total / thread_bit_map / warp_segment driver chains, not --ops");
+        if (!ops.empty()) die("--device-transform builds the seven driver chains, not --ops");
         uint64_t nnz = 0, rows = 0, cols = 0;
         OK(gsh_metadata_info(ms, "GLOBAL_META_nz_row_indices_0", &nnz, nullptr, nullptr));
         OK(gsh_metadata_read_u64(ms, "GLOBAL_META_origin_row_num_-1", &rows, 1));

@@ -220,7 +220,9 @@ gs_status gs_upload_session_as(gs_ctx *ctx, const gsh_session *s, int half, int 
  * thread_bit_map_operator at WARP level (a segment start forced at every VECTOR_WIDTH-th BMT) + warp_segment_reduce_operator (segment_offset.cc,
  * get_begin_BMTs_after_merge_thread.cc).  desc_out is what
  * gsh_session_plan_desc would return after the driver's chain (token_test.cc:1003-1092, :1188-1249, :1319-1391, :1393-1455), launch shape
- * included.  GS_ERR_PADDING_RATE where the reference's padding assert fires; GS_ERR_UNSUPPORTED for the other families. */
+ * included.  GS_FAMILY_WARP_BITMAP / GS_FAMILY_TBLOCK_BITMAP = fixed_interval_col_direction_thread_blocking_operator(64, pad) +
+ * thread_total_reduce_operator + warp_bit_map_operator / tblock_thread_bit_map_operator (token_test.cc:1253-1315, :1518-1582).  GS_ERR_PADDING_RATE where
+ * the reference's padding assert fires; GS_ERR_UNSUPPORTED for families that are not one of the seven drivers'. */
 gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t cols, uint64_t nnz, const uint32_t *row_dev, const uint32_t *col_dev, const float *val_dev, int N,
                               int sparse_coarsen, int coarsen, int half, int as_id, gs_plan_desc *desc_out);
 /* the same from host arrays (H2D, then the device passes); ms_device = the device time of the passes alone (CUDA events), may be NULL */

@@ -1,4 +1,4 @@
-"""the transform steps of five driver chains run as CUDA passes (csrc/device/transform.cu: binary searches, block
+"""the transform steps of all seven driver chains run as CUDA passes (csrc/device/transform.cu: binary searches, block
 scans, a stable LSD radix sort, warp ballots) instead of the host pipeline.  The bar is the host pipeline itself, which tests/test_golden.py pins
 byte for byte to the reference's dumps: every device array the chain registers must come out with the same dtype and the same bytes, the plan
 descriptor must be the one compile() gives, and a plan on the device-built arrays must pick the same kernel and produce the same C."""
@@ -33,7 +33,7 @@ def _desc_fields(d, strip_id):
                 grid=tuple(d.grid), block=tuple(d.block), rows=d.rows, cols=d.cols, nnz=d.origin_nnz, stored=d.stored_nnz, deps=deps)
 
 
-@pytest.mark.parametrize("family,S", [("thread_total", 2), ("thread_total", 8), ("warp_total", 1), ("thread_bit_map", 1), ("warp_segment", 1), ("block_total", 1), ("warp_total", 4)])
+@pytest.mark.parametrize("family,S", [("thread_total", 2), ("thread_total", 8), ("warp_total", 1), ("thread_bit_map", 1), ("warp_segment", 1), ("block_total", 1), ("warp_total", 4), ("warp_bitmap", 1), ("block_bitmap", 4)])
 @pytest.mark.parametrize("N,half", [(8, False), (32, True), (1, False)])
 def test_device_chain_equals_host_chain(engine, family, S, N, half):
     from generalsparse_b200 import api, synth
@@ -72,7 +72,7 @@ def test_device_chain_equals_host_chain(engine, family, S, N, half):
             ph.set_dense(B), pd.set_dense(B)
             ph.run(1), pd.run(1)
             Ch, Cd = ph.output().astype(np.float32), pd.output().astype(np.float32)
-            if family in ("thread_bit_map", "warp_segment") or "merge" in pd.kernel_name or "nnz" in pd.kernel_name:  # atomics: the order of the adds is free
+            if family in ("thread_bit_map", "warp_segment", "warp_bitmap", "block_bitmap") or "merge" in pd.kernel_name or "nnz" in pd.kernel_name:  # atomics: the order of the adds is free
                 assert np.allclose(Ch, Cd, rtol=1e-2 if half else 1e-5, atol=1e-2 if half else 1e-5), (name, family, kernel)
             else:
                 assert np.array_equal(Ch, Cd), (name, family, kernel)
@@ -93,7 +93,7 @@ def test_device_chain_refusals(engine):
     with pytest.raises(api.GsError):  # a column id outside the matrix
         engine.transform_coo("warp_total", 4, 3, r, c, None, 8, 1, 1, as_id=82)
     with pytest.raises(api.GsError) as ei:
-        engine.transform_coo("warp_bitmap", 4, 4, r, c, None, 8, 1, 1, as_id=82)
+        engine.transform_coo("b200_merge", 4, 4, r, c, None, 8, 1, 1, as_id=82)
     assert ei.value.status == 3
 
 
