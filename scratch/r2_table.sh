@@ -13,6 +13,6 @@ for l in open("gpurun_out/r2_table.jsonl"):
     d=json.loads(l); r=d["roofline"]
     print("%-52s %-30s us %7.2f frac %.3f fmt/alg %.2f dep %.2f iso %.2f e2e %.2f parity %s" % (d["config"]["workload"][28:80], d["config"]["kernel"][:30], d["ms_per_step"]*1e3, r["frac"], r["format_over_algorithmic"], r["dependent_chain_ms_per_step"]*1e3, r["isolated_launch_ms"]*1e3, d["e2e"]["ms_per_step"]*1e3, d["parity"]["ok"]))
 PY
-for n in 64 128 256; do
+if [ -n "$R2_TABLE_NCU" ]; then for n in 64 128 256; do
   ncu --set full --clock-control none --import-source on -k regex:k_b200_sp24 -s 20 -c 1 -o gpurun_out/r2_sp24_nm24_n$n python bench.py --no-c4 --no-cpu-baseline --no-yardstick --steps 20 --warmup 5 --dense-n $n --pattern nm24 > gpurun_out/r2_sp24_ncu_n$n.log 2>&1; echo "ncu n$n rc=$?"
-done
+done; fi
