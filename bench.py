@@ -137,7 +137,7 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(inside[0][1]), "reasons": reasons, "samples": len(inside)}
 
 
-def device_transform_block(eng, sess, family, rows, cols, r, c, v, N, S, half, host_id, host_pipeline_s):
+def device_transform_block(eng, sess, family, rows, cols, r, c, v, N, S, half, host_id, host_pipeline_s, plan_kernel="auto"):
     """the chain's transform steps as device passes (gs_transform_host_coo) beside the host pipeline that built the timed plan:
     every array the chain registers must come out byte-equal; device_ms = CUDA events around the passes alone, wall_ms adds the H2D of the COO."""
     eng.transform_coo(family, rows, cols, r, c, v, N, S, 1, half=half, as_id=900)  # warm-up (allocations, module load)
@@ -151,7 +151,18 @@ def device_transform_block(eng, sess, family, rows, cols, r, c, v, N, S, half, h
         same = same and a.dtype == b.dtype and a.shape == b.shape and bool(np.array_equal(a.view(np.uint8), b.view(np.uint8)))
     hd = sess.plan_desc()
     same = same and (hd.stored_nnz, tuple(hd.grid), tuple(hd.block), hd.vector_width) == (dd.stored_nnz, tuple(dd.grid), tuple(dd.block), dd.vector_width)
-    return {"device_ms": dev_ms, "wall_ms_with_h2d_of_coo": wall * 1e3, "host_pipeline_s": host_pipeline_s, "arrays": len(keys), "identical_to_host_pipeline": bool(same),
+    # plan creation on the device-built chain: the kernel's own layout (the 2:4 image: csrc/device/sp24_build.cu) built by device passes, against
+    # the host builder (download of the chain's arrays, host build, upload) on the same arrays
+    plan_s = {}
+    for mode in ("0", "1", "1"):
+        os.environ["GS_SP24_DEVICE_BUILD"] = mode
+        t0 = time.perf_counter()
+        pp = eng.plan(dd, N, half=half, kernel=plan_kernel)
+        plan_s[mode] = time.perf_counter() - t0
+        pname = pp.kernel_name
+        del pp
+    os.environ.pop("GS_SP24_DEVICE_BUILD", None)
+    return {"plan_build_ms": plan_s["1"] * 1e3, "plan_build_host_builder_ms": plan_s["0"] * 1e3, "plan_kernel": pname.split("<")[0],"device_ms": dev_ms, "wall_ms_with_h2d_of_coo": wall * 1e3, "host_pipeline_s": host_pipeline_s, "arrays": len(keys), "identical_to_host_pipeline": bool(same),
             "speedup_vs_host_pipeline": host_pipeline_s * 1e3 / max(dev_ms, 1e-6)}
 
 
@@ -248,7 +259,7 @@ def c4_block(args, rank, world, local, dist):
     plan.set_dense(B)
     dtf = None
     if args.family in ("thread_bit_map", "warp_total", "thread_total"):
-        dtf = device_transform_block(eng, sess, args.family, my_rows, rows, r, c, v, N, 1, False, plan.desc.sub_matrix_id, host_pipeline_s)
+        dtf = device_transform_block(eng, sess, args.family, my_rows, rows, r, c, v, N, 1, False, plan.desc.sub_matrix_id, host_pipeline_s, c4_kernel)
     dev = torch.device("cuda", local)
     stream = torch.cuda.ExternalStream(eng.stream, device=dev)
     # C of this rank lands in place in a full-size C (rows x N): what the optional all-gather replicates
@@ -461,7 +472,7 @@ def main():
     parity = {"max_rel_err_vs_f64": -float(par[1].item()), "tolerance": "1e-2*|ref| + 1e-6*sum|a*b| + 2^-25", "ok": bool(par[0].item() > 0.5),
               "ranks_checked": world}
     del C, ref, absrow, err
-    dtf = device_transform_block(eng, sess, "thread_total", my_rows, COLS, r, c, v, N, 8, half, 0, host_pipeline_s)
+    dtf = device_transform_block(eng, sess, "thread_total", my_rows, COLS, r, c, v, N, 8, half, 0, host_pipeline_s, args.kernel)
 
     def barrier():
         if world > 1:

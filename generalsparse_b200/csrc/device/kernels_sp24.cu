@@ -1,6 +1,7 @@
 // Host side of the B200 2:4 kernel (GS_FAMILY_B200_SP24): builds the 2:4 image of a row-direction chain once per plan
 // (host/sp24_format.hpp), owns the device copies, the stream-K workspace and the launch.  Device code: b200_sp24.cuh.
 #include "b200_sp24.cuh"
+#include "sp24_build.hpp"
 #include "../host/sp24_format.hpp"
 
 #include <algorithm>
@@ -212,10 +213,43 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     pl->N = p.N, pl->K = p.a.cols, pl->n_rows = n_rows;
     if (!encoder()) return fail(cudaErrorNotSupported);
 
-    // the chain's arrays back to the host, once
-    std::vector<uint32_t> rp(n_rows + 1), rid(n_rows), perm, colw(p.a.nnz);
-    std::vector<uint16_t> val(p.a.nnz);
+    // ---- the image built on the device (sp24_build.cu) wherever the default form applies: one panel per unit and a remainder that is either
+    // empty or travels tile-local with the images.  The counts come first; the choices below are the host path's own rules on them.
     cudaError_t e;
+    const int fuse = env_int("GS_SP24_FUSED_REM", 2);
+    sp24_dev_image db;
+    bool on_device = false;
+    uint32_t dev_unit_bytes = 0;
+    if (group == 1 && env_int("GS_SP24_DEVICE_BUILD", 1)) {
+        if (sp24_dev_count(p, rowptr, n_rows, s, db) == cudaSuccess && !db.bad) {
+            if (db.rem_nnz == 0) on_device = true;
+            else if (allow_remainder && fuse >= 2 && p.N <= 64 && db.max_entries <= 0xffffu) {
+                dev_unit_bytes = (uint32_t)sp24::IMG_BYTES + gs::SP24_REM_HEADER + ((db.max_entries + 3u) & ~3u) * 4u;
+                b200_sp24_plan probe = *pl; // what pick_tiled would choose, without committing to it
+                probe.unit_bytes = dev_unit_bytes;
+                size_t rb = 0;
+                int st = 0;
+                if (p.N == 8) pick_tiled<16, 8>(&probe, rb, st);
+                else if (p.N == 16) pick_tiled<16, 16>(&probe, rb, st);
+                else if (p.N == 32) pick_tiled<32, 32>(&probe, rb, st);
+                else pick_tiled<64, 64>(&probe, rb, st);
+                const double content = (double)db.T * sp24::IMG_BYTES + 4.0 * (double)db.rem_nnz + (double)gs::SP24_REM_HEADER * (double)db.T;
+                on_device = rb <= TILED_SMEM_MAX && (double)db.T * dev_unit_bytes <= 1.10 * content; // else: owner-CTA gathers or a gather pass, built on the host
+            }
+        } else cudaGetLastError();
+        if (!on_device) db.release();
+    }
+    auto fail_dev = [&](cudaError_t e2) {
+        db.release();
+        return fail(e2);
+    };
+
+    // the chain's arrays back to the host, once (host path)
+    std::vector<uint32_t> rp, rid, perm, colw;
+    std::vector<uint16_t> val;
+    gs::sp24_image im;
+    if (!on_device) {
+    rp.resize(n_rows + 1), rid.resize(n_rows), colw.resize(p.a.nnz), val.resize(p.a.nnz);
     if ((e = cudaMemcpyAsync(rp.data(), rowptr, rp.size() * 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpyAsync(rid.data(), rowid, rid.size() * 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpyAsync(val.data(), p.a.val, val.size() * 2, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
@@ -234,22 +268,25 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     }
     if (rp[n_rows] > p.a.nnz) return fail(cudaErrorInvalidValue);
 
-    gs::sp24_image im;
     try {
         gs::build_sp24_image(rp.data(), colw.data(), val.data(), n_rows, p.a.cols, (uint32_t)group, im);
     } catch (...) {
         return fail(cudaErrorInvalidValue);
     }
-    pl->rem_nnz = im.rem_col.size();
-    if (pl->rem_nnz && !allow_remainder) return fail(cudaErrorInvalidValue); // not a 2:4 matrix
+    } // host path
+    const uint32_t im_n_panels = on_device ? db.n_panels : im.n_panels, im_k_tiles = on_device ? db.k_tiles : im.k_tiles;
+    const uint64_t im_bytes = on_device ? (uint64_t)db.T * sp24::IMG_BYTES : im.bytes.size(), im_nnz = on_device ? db.img_nnz : im.nnz;
+    pl->rem_nnz = on_device ? db.rem_nnz : im.rem_col.size();
+    if (pl->rem_nnz && !allow_remainder) return fail_dev(cudaErrorInvalidValue); // not a 2:4 matrix
     // The remainder is multiplied inside the 2:4 kernel (b200_sp24.cuh), no second launch.  GS_SP24_FUSED_REM: 2 (default) = from
     // tile-local blocks at N <= 64, as long as two CTAs still fit an SM and the padding to the largest block costs < 10 % of the
     // stream; 1 = gathers by the CTA that owns the panel (N <= 16); 0 = a separate gather launch.
-    const int fuse = env_int("GS_SP24_FUSED_REM", 2);
     gs::sp24_tiled tl;
+    const uint32_t tl_row_bytes = p.N == 64 ? 128u : p.N == 32 ? 64u : 32u;
     if (pl->rem_nnz && fuse >= 2 && p.N <= 64 && group == 1) {
-        try {
-            gs::localize_sp24_remainder(im, p.N == 64 ? 128u : p.N == 32 ? 64u : 32u, tl);
+        if (on_device) tl.unit_bytes = dev_unit_bytes;
+        else try {
+            gs::localize_sp24_remainder(im, tl_row_bytes, tl);
         } catch (...) {
             tl = gs::sp24_tiled();
         }
@@ -262,8 +299,9 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
             else if (p.N == 16) pick_tiled<16, 16>(pl, ring_bytes, stages);
             else if (p.N == 32) pick_tiled<32, 32>(pl, ring_bytes, stages);
             else pick_tiled<64, 64>(pl, ring_bytes, stages);
-            const double content = (double)im.bytes.size() + 4.0 * (double)pl->rem_nnz + (double)gs::SP24_REM_HEADER * (double)(im.bytes.size() / gs::SP24_TILE_BYTES);
-            pl->tiled = ring_bytes <= TILED_SMEM_MAX && (double)tl.bytes.size() <= 1.10 * content;
+            const double content = (double)im_bytes + 4.0 * (double)pl->rem_nnz + (double)gs::SP24_REM_HEADER * (double)(im_bytes / gs::SP24_TILE_BYTES);
+            const double tl_bytes = on_device ? (double)db.T * dev_unit_bytes : (double)tl.bytes.size();
+            pl->tiled = ring_bytes <= TILED_SMEM_MAX && tl_bytes <= 1.10 * content;
             if (pl->tiled) ctas = 2;
             else pl->fn = fn0, ring_bytes = ring0, stages = stages0, pl->unit_bytes = 0;
         }
@@ -275,11 +313,12 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
         else pick<16, 1, 16, 8>(pl->fn, pl->rem_fn, ring_bytes, stages, ctas);
         ring_bytes += 2 * sp24::SM_ROWS * p.N * 4; // the two remainder buffers behind the ring
     }
-    pl->n_panels = im.n_panels, pl->k_tiles = im.k_tiles, pl->n_tiles = im.n_panels / group * im.k_tiles, pl->nnz = im.nnz;
+    pl->n_panels = im_n_panels, pl->k_tiles = im_k_tiles, pl->n_tiles = im_n_panels / group * im_k_tiles, pl->nnz = im_nnz;
     pl->n_units_full = pl->n_tiles;
     // Tiles that hold nothing (banded, block-sparse matrices) are dropped from the stream when that saves at least a tenth of it; every
     // panel keeps one tile so that its rows of C are written.  GS_SP24_SKIP_EMPTY=0 keeps them all.
     gs::sp24_compact cp;
+    const void *dev_compact = nullptr; // device path: the kernel over a panel table, if the fill decides to drop the empty tiles
     if (group == 1 && env_int("GS_SP24_SKIP_EMPTY", 1)) {
         const void *cfn = nullptr; // the kernel over a panel table: same shape as the one picked above
         if (pl->tiled) {
@@ -296,16 +335,26 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
             case 128: cfn = (const void *)sp24::k_b200_sp24<128, 1, 128, 0, 0, true>; break;
             case 256: cfn = (const void *)sp24::k_b200_sp24<256, 1, 256, 0, 0, true>; break;
             }
-        if (cfn && gs::compact_sp24_units(pl->tiled ? tl.bytes.data() : im.bytes.data(), pl->tiled ? tl.unit_bytes : (size_t)sp24::IMG_BYTES, pl->tiled, im.n_panels, im.k_tiles, 0.9, cp)) {
+        if (on_device) dev_compact = cfn;
+        else if (cfn && gs::compact_sp24_units(pl->tiled ? tl.bytes.data() : im.bytes.data(), pl->tiled ? tl.unit_bytes : (size_t)sp24::IMG_BYTES, pl->tiled, im.n_panels, im.k_tiles, 0.9, cp)) {
             pl->fn = cfn;
             pl->n_tiles = (uint32_t)cp.unit_kt.size();
         }
     }
+    if (on_device) { // the fill: image, metadata, tile-local blocks, and the unit / panel tables when the empty tiles leave the stream
+        uint32_t n_units = 0;
+        if ((e = sp24_dev_fill(p, rowptr, n_rows, pl->tiled ? tl.unit_bytes : (uint32_t)sp24::IMG_BYTES, tl_row_bytes, dev_compact != nullptr, 0.9, s, db, &pl->img, &pl->panel_ptr, &pl->unit_kt, &n_units)) !=
+            cudaSuccess)
+            return fail_dev(e);
+        if (pl->panel_ptr) pl->fn = dev_compact, pl->n_tiles = n_units;
+        if ((e = sp24_dev_out_row(p, rowid, n_rows, im_n_panels, s, db, &pl->out_row)) != cudaSuccess) return fail_dev(e);
+        db.release();
+    }
     pl->grid = (uint32_t)std::min<uint64_t>((uint64_t)env_int("GS_TILE_CTAS", sm_count), pl->n_tiles);
     if (pl->grid == 0 || (int)pl->grid > sm_count * ctas) return fail(cudaErrorInvalidValue); // the split-panel hand-off needs every CTA resident
 
-    std::vector<uint32_t> orow((size_t)im.n_panels * sp24::SM_ROWS, 0xffffffffu);
-    for (uint32_t i = 0; i < n_rows; i++) {
+    std::vector<uint32_t> orow(on_device ? 0 : (size_t)im.n_panels * sp24::SM_ROWS, 0xffffffffu);
+    for (uint32_t i = 0; i < n_rows && !on_device; i++) {
         const uint32_t r = rid[i];
         if (p.a.perm && r >= perm.size()) return fail(cudaErrorInvalidValue);
         orow[i] = (p.a.perm ? perm[r] : r) + p.a.begin_row;
@@ -317,12 +366,14 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
         if (e2 != cudaSuccess) return e2;
         return bytes ? cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess;
     };
-    if (!cp.bytes.empty()) {
+    if (on_device) {
+        // the image, its tables and the row table are in place
+    } else if (!cp.bytes.empty()) {
         if ((e = up((void **)&pl->img, cp.bytes.data(), cp.bytes.size())) != cudaSuccess) return fail(e);
         if ((e = up((void **)&pl->panel_ptr, cp.panel_ptr.data(), cp.panel_ptr.size() * 4)) != cudaSuccess) return fail(e);
         if ((e = up((void **)&pl->unit_kt, cp.unit_kt.data(), cp.unit_kt.size() * 4)) != cudaSuccess) return fail(e);
     } else if ((e = pl->tiled ? up((void **)&pl->img, tl.bytes.data(), tl.bytes.size()) : up((void **)&pl->img, im.bytes.data(), im.bytes.size())) != cudaSuccess) return fail(e);
-    if ((e = up((void **)&pl->out_row, orow.data(), orow.size() * 4)) != cudaSuccess) return fail(e);
+    if (!on_device && (e = up((void **)&pl->out_row, orow.data(), orow.size() * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMalloc((void **)&pl->ws, (size_t)pl->grid * group * sp24::SM_ROWS * p.N * 4)) != cudaSuccess) return fail(e);
     const size_t n_flags = (size_t)pl->grid * 2 + pl->n_panels + (size_t)pl->n_panels * 4;
     if ((e = cudaMalloc((void **)&pl->flags, n_flags * 4)) != cudaSuccess) return fail(e);
