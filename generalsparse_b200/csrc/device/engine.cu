@@ -5,6 +5,7 @@
 #include "common.cuh"
 #include "nccl_dl.hpp"
 #include "transform.hpp"
+#include "sp24_build.hpp"
 #include "../host/arr_optimization.hpp"
 
 #include <algorithm>
@@ -415,30 +416,15 @@ struct auto_choice {
 };
 
 // 128 x 128 tiles of the row-level matrix that hold at least one entry (every row panel counts one at least): one pass over the
-// pattern on the host, at plan time
+// pattern, at plan time
 static uint64_t count_nonempty_tiles(const gs_plan *p, const char *lvl)
 {
     const gs_ctx *ctx = p->ctx;
     const int id = p->desc.sub_matrix_id;
     const dev_array *rp = find_arr(ctx, lvl, "first_nz_indices", id), *col = find_arr(ctx, "GLOBAL_META", "nz_col_indices", id);
     if (!rp || !col || rp->len < 2) return 0;
-    std::vector<uint32_t> h_rp(rp->len);
-    CUDA_TRY(cudaMemcpy(h_rp.data(), rp->ptr, rp->len * 4, cudaMemcpyDeviceToHost));
-    std::vector<unsigned char> h_col(col->len * dsize(col->dtype));
-    CUDA_TRY(cudaMemcpy(h_col.data(), col->ptr, h_col.size(), cudaMemcpyDeviceToHost));
-    const uint64_t kt = (p->desc.cols + 127) / 128, n_rows = rp->len - 1, panels = (n_rows + 127) / 128;
-    std::vector<bool> seen(panels * kt, false);
-    const bool u16 = col->dtype == GS_U16;
-    for (uint64_t r = 0; r < n_rows; r++) {
-        const uint64_t base = (r >> 7) * kt;
-        for (uint64_t i = h_rp[r]; i < h_rp[r + 1] && i < col->len; i++) seen[base + ((u16 ? ((const uint16_t *)h_col.data())[i] : ((const uint32_t *)h_col.data())[i]) >> 7)] = true;
-    }
-    uint64_t n = 0;
-    for (uint64_t pnl = 0; pnl < panels; pnl++) {
-        uint64_t here = 0;
-        for (uint64_t k = 0; k < kt; k++) here += seen[pnl * kt + k];
-        n += here ? here : 1;
-    }
+    uint64_t n = 0; // counted on the device (sp24_build.cu): the arrays stay where they are
+    CUDA_TRY(gsd::count_tiles128_dev(col->ptr, col->dtype == GS_U16, (const uint32_t *)rp->ptr, (uint32_t)(rp->len - 1), (uint32_t)p->desc.cols, col->len, ctx->stream, &n));
     return n;
 }
 

@@ -239,6 +239,32 @@ __global__ void k_sp24_out_row(const uint32_t *rowid, const uint32_t *perm, uint
     }
 }
 
+// the 128 x 128 tiles that hold a stored entry, for the cost model (engine.cu: auto_candidates)
+__global__ void k_tiles_seen(const void *col, uint32_t col_is_u16, const uint32_t *rowptr, uint32_t n_rows, uint32_t nnz, uint32_t k_tiles, unsigned char *seen)
+{
+    for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (uint64_t)gridDim.x * blockDim.x) {
+        uint32_t lo = 0, hi = n_rows;
+        while (hi - lo > 1) {
+            const uint32_t mid = lo + (hi - lo) / 2;
+            if (rowptr[mid] <= e) lo = mid;
+            else hi = mid;
+        }
+        if (e >= rowptr[lo + 1]) continue;
+        const uint32_t c = col_is_u16 ? (uint32_t)((const uint16_t *)col)[e] : ((const uint32_t *)col)[e];
+        if (c / COLS < k_tiles) seen[(size_t)(lo / ROWS) * k_tiles + c / COLS] = 1;
+    }
+}
+__global__ void k_tiles_count(const unsigned char *seen, uint32_t n_panels, uint32_t k_tiles, unsigned long long *out)
+{
+    unsigned long long n = 0;
+    for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_panels; p += (uint64_t)gridDim.x * blockDim.x) {
+        uint32_t here = 0;
+        for (uint32_t k = 0; k < k_tiles; k++) here += seen[p * k_tiles + k];
+        n += here ? here : 1; // every row panel keeps one tile
+    }
+    if (n) atomicAdd(out, n);
+}
+
 inline unsigned grid_for(uint64_t n, unsigned per) { return (unsigned)std::min<uint64_t>(std::max<uint64_t>(1, (n + per - 1) / per), 148u * 32u); }
 
 } // namespace
@@ -247,6 +273,28 @@ void sp24_dev_image::release()
 {
     cudaFree(tile_img), cudaFree(rem_cnt), cudaFree(tile_rem), cudaFree(keep), cudaFree(unit_of_tile), cudaFree(scal);
     tile_img = rem_cnt = tile_rem = keep = unit_of_tile = nullptr, scal = nullptr;
+}
+
+cudaError_t count_tiles128_dev(const void *col, bool col_is_u16, const uint32_t *rowptr, uint32_t n_rows, uint32_t n_cols, uint64_t nnz, cudaStream_t s, uint64_t *out)
+{
+    const uint32_t n_panels = (n_rows + ROWS - 1) / ROWS, k_tiles = (n_cols + COLS - 1) / COLS;
+    const uint64_t T = (uint64_t)n_panels * k_tiles;
+    if (T == 0 || nnz > 0xfffffff0ull) return cudaErrorInvalidValue;
+    unsigned char *seen = nullptr;
+    TRY(cudaMalloc((void **)&seen, T + 16));
+    cudaError_t e = cudaMemsetAsync(seen, 0, T + 16, s);
+    unsigned long long *cnt = (unsigned long long *)(seen + ((T + 7) & ~7ull)); // the spare bytes behind the flags
+    unsigned long long h = 0;
+    if (e == cudaSuccess) {
+        k_tiles_seen<<<grid_for(nnz, 256 * 4), 256, 0, s>>>(col, col_is_u16 ? 1u : 0u, rowptr, n_rows, (uint32_t)nnz, k_tiles, seen);
+        k_tiles_count<<<grid_for(n_panels, 128), 128, 0, s>>>(seen, n_panels, k_tiles, cnt);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&h, cnt, 8, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(seen);
+    *out = h;
+    return e;
 }
 
 cudaError_t sp24_dev_count(const launch_params &p, const uint32_t *rowptr, uint32_t n_rows, cudaStream_t s, sp24_dev_image &d)

@@ -23,4 +23,7 @@ cudaError_t sp24_dev_fill(const launch_params &p, const uint32_t *rowptr, uint32
                           sp24_dev_image &d, unsigned char **img, uint32_t **panel_ptr, uint32_t **unit_kt, uint32_t *n_units);
 cudaError_t sp24_dev_out_row(const launch_params &p, const uint32_t *rowid, uint32_t n_rows, uint32_t n_panels, cudaStream_t s, sp24_dev_image &d, uint32_t **out_row);
 
+// 128 x 128 tiles that hold a stored entry (every row panel counts at least one): what the cost model prices the 2:4 image by
+cudaError_t count_tiles128_dev(const void *col, bool col_is_u16, const uint32_t *rowptr, uint32_t n_rows, uint32_t n_cols, uint64_t nnz, cudaStream_t s, uint64_t *out);
+
 } // namespace gsd
