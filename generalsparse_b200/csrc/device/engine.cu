@@ -498,14 +498,17 @@ static std::vector<auto_choice> auto_candidates(const gs_plan *p)
         // r2_c5_sweep_narrow.md): the chunk kernel 110 K at N = 1, 83 K at 2, 137 K at 4 (the first width with a 16-byte row), 100 K at 8, 75 K at
         // 16, 68 K at 32, fp32 and fp16 alike (C1 stand-in: 100 / 89 / 77 K at N = 8 / 16 / 32); the group kernel 35.5 K at N = 64, 29 K at 128,
         // 5.5 K at 512, where fp16 values load 2 bytes per lane and run at about half of that
-        static const double mn[] = {1, 2, 4, 8, 16, 32, 64, 128, 256, 512}, mr[] = {110e3, 83e3, 137e3, 100e3, 75e3, 68e3, 35.5e3, 28.6e3, 13.9e3, 5.5e3};
+        static const double mn[] = {1, 2, 4, 8, 16, 32, 64, 128, 256, 512}, mr[] = {110e3, 83e3, 137e3, 100e3, 75e3, 68e3, 58e3, 28.6e3, 13.9e3, 5.5e3};
         double rate = mr[9];
         for (int i = 0; i < 10; i++)
             if (N <= mn[i]) {
                 rate = mr[i];
                 break;
             }
-        if (p->half && N >= 64) rate *= 0.5;
+        // the chunk variant also takes rows of B up to 256 bytes (fp32 N = 64: 727 us on the uniform matrix, 58 K per us; fp16 N = 64 / 128: 796 / 1 000 us)
+        if (p->half && N == 64) rate = 53e3;
+        else if (p->half && N == 128) rate = 42e3;
+        else if (p->half && N >= 256) rate *= 0.5;
         if (p->half && N <= 8) rate *= 0.75; // one lane per segment (C1 stand-in: 24.8 us against 17.8 in fp32)
         const double walk = nnz / rate;
         c.push_back({GS_FAMILY_B200_MERGE, std::max({(nnz * (idxb + vb) + bc) / (0.60 * bw), gather / (b_in_l2 ? l2_bw : 0.9 * bw), walk}) + 3.0});

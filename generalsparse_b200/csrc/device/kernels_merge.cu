@@ -35,7 +35,7 @@ struct b200_merge_plan {
     uint32_t n_zero = 0, max_sharers = 1;
     uint32_t cap = 0;        // no segment is longer
     bool stage = false;      // chunk kernel: the CTA's piece of the stream goes through shared memory
-    bool per_thread = false; // N <= 32: one lane per 16-byte chunk of B's row (k_b200_merge_chunk), else a group of 32 lanes
+    bool per_thread = false; // rows of B up to 256 bytes: one lane per 16-byte chunk of the row (k_b200_merge_chunk), else a group of 32 lanes
     char name[160] = {0};
 };
 
@@ -393,6 +393,9 @@ template <typename ColT, typename ValT, bool STAGE, bool TICKET> const void *pic
     case 8: return (const void *)k_b200_merge_chunk<ColT, ValT, 8, chunk_lanes<ValT>(8), STAGE, TICKET>;
     case 16: return (const void *)k_b200_merge_chunk<ColT, ValT, 16, chunk_lanes<ValT>(16), STAGE, TICKET>;
     case 32: return (const void *)k_b200_merge_chunk<ColT, ValT, 32, chunk_lanes<ValT>(32), STAGE, TICKET>;
+    // rows of B up to 256 bytes (fp32 N = 64, fp16 N = 64 / 128): 8 or 16 lanes per segment, unstaged (the staged form is for LG <= 4)
+    case 64: return STAGE ? nullptr : (const void *)k_b200_merge_chunk<ColT, ValT, 64, chunk_lanes<ValT>(64), false, TICKET>;
+    case 128: return (STAGE || sizeof(ValT) != 2) ? nullptr : (const void *)k_b200_merge_chunk<ColT, ValT, 128, (sizeof(ValT) == 2 ? 16 : 32), false, TICKET>;
     default: return nullptr;
     }
 }
@@ -478,14 +481,14 @@ cudaError_t b200_merge_prepare(const launch_params &p, const uint32_t *parts_dev
     if (parts[0] != 0 || parts[n_parts] > nnz || rowptr[n_rows] < parts[n_parts]) return fail(cudaErrorInvalidValue);
 
     // segments: the chain's parts, long ones cut into equal slices (GS_MERGE_CAP non-zeros at most)
-    const bool per_thread = p.N <= 32 && env_int("GS_MERGE_THREAD", 1) != 0;
+    const bool per_thread = (uint64_t)p.N * (p.a.val_is_f16 ? 2 : 4) <= (uint64_t)env_int("GS_MERGE_CHUNK_ROW_BYTES", 256) && env_int("GS_MERGE_THREAD", 1) != 0;
     const int LG = per_thread ? (p.a.val_is_f16 ? chunk_lanes<__half>(p.N) : chunk_lanes<float>(p.N)) : p.N < 32 ? p.N : 32;
     const uint32_t cap = (uint32_t)std::max(LG, env_int("GS_MERGE_CAP", per_thread ? (LG >= 4 ? 64 : 32) : LG == 32 ? 512 : 32 * LG)); // chunk kernel: every lane of a group walks the whole segment
     pl->per_thread = per_thread, pl->cap = cap;
     if (per_thread) { // staging needs 16-byte aligned streams and at most 48 KB for a CTA's piece
         const uint32_t elems = (128 / LG) * cap + 8;
         const uint64_t bytes = 4ull * (stage_words(elems, p.a.col_is_u16 ? 2 : 4) + stage_words(elems, p.a.val_is_f16 ? 2 : 4));
-        pl->stage = env_int("GS_MERGE_STAGE", LG <= 4) != 0 && bytes <= 48 * 1024 && (((uintptr_t)p.a.col | (uintptr_t)p.a.val) & 15) == 0;
+        pl->stage = env_int("GS_MERGE_STAGE", LG <= 4) != 0 && LG <= 8 && bytes <= 48 * 1024 && (((uintptr_t)p.a.col | (uintptr_t)p.a.val) & 15) == 0;
     }
     std::vector<uint32_t> seg_nz, seg_row;
     for (uint32_t i = 0; i < n_parts; i++) {
@@ -508,7 +511,11 @@ cudaError_t b200_merge_prepare(const launch_params &p, const uint32_t *parts_dev
     };
     if ((e = up(&pl->seg_nz, seg_nz)) != cudaSuccess || (e = up(&pl->seg_row, seg_row)) != cudaSuccess || (e = up(&pl->rowptr, rowptr)) != cudaSuccess) return fail(e);
     // ticket mode: who shares which row
-    if (p.a.begin_row == 0 && env_int("GS_MERGE_TICKET", 1) != 0) { // (a plan on a sub-matrix keeps the memset of the whole of C)
+    // tickets by default where they are needed (HALF: red.add would round every slice's partial to fp16) or measured at least as fast as memset +
+    // red.add (rows of B up to 128 bytes); wider fp32 rows keep red.add: the partial buffer costs 8 N bytes per segment there (C5 uniform, N = 128:
+    // 1 752 us with tickets against 1 493 with red.add)
+    const bool ticket_default = p.a.val_is_f16 || (per_thread && (uint64_t)p.N * 4 <= 128);
+    if (p.a.begin_row == 0 && env_int("GS_MERGE_TICKET", ticket_default ? 1 : 0) != 0) { // (a plan on a sub-matrix keeps the memset of the whole of C)
         const uint32_t n_seg = pl->n_seg;
         std::vector<uint32_t> head(n_seg), tail(n_seg), zero;
         auto seg_of = [&](uint32_t nz) { // the segment that holds stream position nz
