@@ -98,6 +98,7 @@ struct gs_plan {
     uint64_t chain_offset_bytes = 0; // the same for the chain's own family (desc.family): SURVEY.md 8(d)'s offset term, independent of the kernel chosen
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t ev_b = nullptr, ev_k = nullptr, ev_c = nullptr; // async round trip: B landed, kernel done, C read back
+    int last_async = -1;                                        // the launch stream the plan's previous gs_spmm_host_async used
     size_t esz() const { return half ? 2 : 4; }
 };
 
@@ -1129,7 +1130,8 @@ gs_status gs_spmm_host_async(gs_plan *p, const void *B_host, void *C_host)
     // launch stream; the split-panel flags count launches of one plan in order) has finished
     CUDA_TRY(cudaStreamWaitEvent(ls, p->ev_b, 0));
     CUDA_TRY(cudaStreamWaitEvent(ls, p->ev_c, 0));
-    CUDA_TRY(cudaStreamWaitEvent(ls, p->ev_k, 0));
+    if (p->last_async != which) CUDA_TRY(cudaStreamWaitEvent(ls, p->ev_k, 0)); // (stream order says so when the previous launch used this very stream)
+    p->last_async = which;
     enqueue(p, which);
     CUDA_TRY(cudaEventRecord(p->ev_k, ls));
     CUDA_TRY(cudaStreamWaitEvent(ctx->copy_out, p->ev_k, 0));
