@@ -13,6 +13,7 @@
 // (at most two) rows a segment shares with its neighbours go to C through red.global.add, and C is zeroed per launch, which also
 // covers empty rows.  Bound: HBM (A streamed once) while B's working set sits in L1/L2.
 #include "common.cuh"
+#include "transform.hpp"
 
 #include "../../../include/gsparse_b200.h"
 
@@ -423,10 +424,223 @@ template <typename ColT, typename ValT, bool TICKET> const void *pick_t(int N)
 }
 template <typename ColT, typename ValT> const void *pick(int N, bool ticket = false) { return ticket ? pick_t<ColT, ValT, true>(N) : pick_t<ColT, ValT, false>(N); }
 
+inline unsigned grid_1d(uint64_t n) { return (unsigned)std::min<uint64_t>(std::max<uint64_t>(1, (n + 255) / 256), 148u * 32u); }
+
 int env_int(const char *name, int dflt)
 {
     const char *v = getenv(name);
     return v && *v ? atoi(v) : dflt;
+}
+
+
+// ---- the plan built on the device -----------------------------------------------------------------------------------------------------------------
+// What b200_merge_prepare computes on the host -- segments, their rows, who shares which row, the rows without non-zeros -- from the chain's
+// arrays as they lie on the device: the host version downloads the parts and, for merge-path and balanced chains, the row id of every stored
+// non-zero (13.8 ms for the C1 stand-in, 139 ms for a 20 M-nnz block, against an 18 us / 0.5 ms kernel).  Same arrays, element for element
+// (tests/test_merge_kernel_gpu.py::test_plan_built_on_device_equals_host_built).
+__device__ __forceinline__ uint32_t upper_bound_u32(const uint32_t *a, uint32_t n, uint32_t x) // first index with a[i] > x
+{
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint32_t mid = lo + (hi - lo) / 2;
+        if (a[mid] <= x) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo;
+}
+__global__ void k_mp_check(const uint32_t *parts, uint32_t n_parts, const uint32_t *rows, uint32_t n_rows_ids, const uint32_t *part_rows, uint32_t *bad)
+{
+    const uint64_t n = max((uint64_t)n_parts, (uint64_t)n_rows_ids);
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        if (i < n_parts && parts[i + 1] < parts[i]) *bad = 1;
+        if (rows && i && i < n_rows_ids && rows[i] < rows[i - 1]) *bad = 1;
+        if (part_rows && i && i < n_parts && part_rows[i] < part_rows[i - 1]) *bad = 1;
+    }
+}
+// column-direction chunks: part i lies in row part_rows[i] (ascending); row r's non-zeros begin where its first part begins
+__global__ void k_mp_rowptr_from_part_rows(const uint32_t *parts, const uint32_t *part_rows, uint32_t n_parts, uint32_t n_rows, uint32_t *rowptr)
+{
+    for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r <= n_rows; r += (uint64_t)gridDim.x * blockDim.x) {
+        uint32_t lo = 0, hi = n_parts; // first part whose row is >= r
+        while (lo < hi) {
+            const uint32_t mid = lo + (hi - lo) / 2;
+            if (part_rows[mid] < r) lo = mid + 1;
+            else hi = mid;
+        }
+        rowptr[r] = parts[lo];
+    }
+}
+__global__ void k_mp_pieces(const uint32_t *parts, uint32_t n_parts, uint32_t cap, uint32_t *pieces)
+{
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_parts; i += (uint64_t)gridDim.x * blockDim.x) pieces[i] = (parts[i + 1] - parts[i] + cap - 1) / cap;
+}
+// segment s is slice q of the part that holds it: equal slices, the row of its first non-zero by binary search in the row pointer
+__global__ void k_mp_segments(const uint32_t *parts, const uint32_t *piece_off, uint32_t n_parts, const uint32_t *rowptr, uint32_t n_rows, uint32_t n_seg, uint32_t *seg_nz, uint32_t *seg_row)
+{
+    for (uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; s <= n_seg; s += (uint64_t)gridDim.x * blockDim.x) {
+        if (s == n_seg) {
+            seg_nz[s] = parts[n_parts];
+            continue;
+        }
+        const uint32_t i = upper_bound_u32(piece_off, n_parts + 1, (uint32_t)s) - 1, q = (uint32_t)s - piece_off[i], pieces = piece_off[i + 1] - piece_off[i];
+        const uint32_t a = parts[i], b = parts[i + 1], lo = a + (uint32_t)((uint64_t)(b - a) * q / pieces);
+        seg_nz[s] = lo, seg_row[s] = upper_bound_u32(rowptr, n_rows + 1, lo) - 1;
+    }
+}
+__global__ void k_mp_sharers(const uint32_t *seg_nz, const uint32_t *seg_row, uint32_t n_seg, const uint32_t *rowptr, uint32_t n_rows, uint32_t *head, uint32_t *tail, uint32_t *most)
+{
+    uint32_t mx = 1;
+    for (uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_seg; q += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t a = seg_nz[q], b = seg_nz[q + 1], f = seg_row[q], l = upper_bound_u32(rowptr, n_rows + 1, b - 1) - 1;
+        auto seg_of = [&](uint32_t nz) { // the segment that holds stream position nz
+            const uint32_t u = upper_bound_u32(seg_nz, n_seg + 1, nz);
+            return min(u ? u - 1 : 0u, n_seg - 1);
+        };
+        const uint32_t h = rowptr[f] < a ? seg_of(rowptr[f]) : (uint32_t)q, t = rowptr[l + 1] > b ? seg_of(rowptr[l + 1] - 1) : (uint32_t)q;
+        head[q] = h, tail[q] = t;
+        mx = max(mx, max((uint32_t)q - h, t - (uint32_t)q) + 1);
+    }
+    atomicMax(most, mx);
+}
+__global__ void k_mp_zero_flags(const uint32_t *rowptr, uint32_t n_rows, uint32_t rows_total, uint32_t parts_end, uint32_t *flag)
+{
+    for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < rows_total; r += (uint64_t)gridDim.x * blockDim.x)
+        flag[r] = r >= n_rows || rowptr[r + 1] == rowptr[r] || rowptr[r] >= parts_end;
+}
+__global__ void k_mp_zero_list(const uint32_t *flag, const uint32_t *off, uint32_t rows_total, uint32_t *list)
+{
+    for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < rows_total; r += (uint64_t)gridDim.x * blockDim.x)
+        if (flag[r]) list[off[r]] = (uint32_t)r;
+}
+
+struct merge_choice {
+    bool per_thread;
+    int LG;
+    uint32_t cap;
+};
+merge_choice choose(const launch_params &p)
+{
+    merge_choice c;
+    c.per_thread = (uint64_t)p.N * (p.a.val_is_f16 ? 2 : 4) <= (uint64_t)env_int("GS_MERGE_CHUNK_ROW_BYTES", 256) && env_int("GS_MERGE_THREAD", 1) != 0;
+    c.LG = c.per_thread ? (p.a.val_is_f16 ? chunk_lanes<__half>(p.N) : chunk_lanes<float>(p.N)) : p.N < 32 ? p.N : 32;
+    c.cap = (uint32_t)std::max(c.LG, env_int("GS_MERGE_CAP", c.per_thread ? (c.LG >= 4 ? 64 : 32) : c.LG == 32 ? 512 : 32 * c.LG)); // chunk kernel: every lane of a group walks the whole segment
+    return c;
+}
+
+#define MP_TRY(x)                                                                                                                                    \
+    do {                                                                                                                                             \
+        cudaError_t e_ = (x);                                                                                                                        \
+        if (e_ != cudaSuccess) return e_;                                                                                                            \
+    } while (0)
+
+// fills pl (the caller frees it on failure); cudaErrorNotSupported: let the host path decide (bad input is refused there with the same code as before)
+cudaError_t prepare_on_device(const launch_params &p, const uint32_t *parts, uint32_t n_parts, const uint32_t *nz_rows, const uint32_t *part_rows, bool parts_are_rows, b200_merge_plan *pl,
+                              cudaStream_t s)
+{
+    const uint32_t nnz = (uint32_t)p.a.nnz;
+    const merge_choice ch = choose(p);
+    struct tmp_bufs {
+        std::vector<void *> v;
+        ~tmp_bufs()
+        {
+            for (void *q : v) cudaFree(q);
+        }
+        cudaError_t get(uint32_t **q, uint64_t n)
+        {
+            cudaError_t e = cudaMalloc((void **)q, std::max<uint64_t>(n, 1) * 4 + 16);
+            if (e == cudaSuccess) v.push_back(*q);
+            return e;
+        }
+    } tmp;
+    uint32_t *scal = nullptr, h[4] = {0, 0, 0, 0}; // [0] bad input, [1] most sharers
+    MP_TRY(tmp.get(&scal, 4));
+    MP_TRY(cudaMemsetAsync(scal, 0, 16, s));
+    k_mp_check<<<grid_1d(std::max<uint64_t>(n_parts, nz_rows ? nnz : 0)), 256, 0, s>>>(parts, n_parts, nz_rows, nz_rows ? nnz : 0u, part_rows, scal);
+    uint32_t ends[2] = {0, 0}, last_row = 0;
+    MP_TRY(cudaMemcpyAsync(&ends[0], parts, 4, cudaMemcpyDeviceToHost, s));
+    MP_TRY(cudaMemcpyAsync(&ends[1], parts + n_parts, 4, cudaMemcpyDeviceToHost, s));
+    if (nz_rows) MP_TRY(cudaMemcpyAsync(&last_row, nz_rows + nnz - 1, 4, cudaMemcpyDeviceToHost, s));
+    else if (part_rows) MP_TRY(cudaMemcpyAsync(&last_row, part_rows + n_parts - 1, 4, cudaMemcpyDeviceToHost, s));
+    MP_TRY(cudaMemcpyAsync(h, scal, 4, cudaMemcpyDeviceToHost, s));
+    MP_TRY(cudaStreamSynchronize(s));
+    if (h[0] || ends[0] != 0 || ends[1] > nnz) return cudaErrorNotSupported;
+    uint32_t n_rows = 0;
+    if (nz_rows || part_rows) {
+        if (last_row >= 0xfffffff0u) return cudaErrorNotSupported;
+        n_rows = last_row + 1;
+    } else if (parts_are_rows) n_rows = n_parts;
+    else return cudaErrorNotSupported;
+    MP_TRY(cudaMalloc((void **)&pl->rowptr, ((size_t)n_rows + 1) * 4 + 16));
+    if (nz_rows) MP_TRY(rowptr_from_sorted_rows(nz_rows, nnz, n_rows, pl->rowptr, s));
+    else if (part_rows) {
+        k_mp_rowptr_from_part_rows<<<grid_1d((uint64_t)n_rows + 1), 256, 0, s>>>(parts, part_rows, n_parts, n_rows, pl->rowptr);
+        MP_TRY(cudaGetLastError());
+    } else MP_TRY(cudaMemcpyAsync(pl->rowptr, parts, ((size_t)n_rows + 1) * 4, cudaMemcpyDeviceToDevice, s));
+    uint32_t row_end = 0;
+    MP_TRY(cudaMemcpyAsync(&row_end, pl->rowptr + n_rows, 4, cudaMemcpyDeviceToHost, s));
+
+    // segments
+    pl->per_thread = ch.per_thread, pl->cap = ch.cap;
+    if (ch.per_thread) {
+        const uint32_t elems = (128 / ch.LG) * ch.cap + 8;
+        const uint64_t bytes = 4ull * (stage_words(elems, p.a.col_is_u16 ? 2 : 4) + stage_words(elems, p.a.val_is_f16 ? 2 : 4));
+        pl->stage = env_int("GS_MERGE_STAGE", ch.LG <= 4) != 0 && ch.LG <= 8 && bytes <= 48 * 1024 && (((uintptr_t)p.a.col | (uintptr_t)p.a.val) & 15) == 0;
+    }
+    uint32_t *piece_off = nullptr, n_seg = 0;
+    MP_TRY(tmp.get(&piece_off, (uint64_t)n_parts + 1));
+    k_mp_pieces<<<grid_1d(n_parts), 256, 0, s>>>(parts, n_parts, ch.cap, piece_off);
+    MP_TRY(cudaGetLastError());
+    MP_TRY(scan_exclusive_u32(piece_off, piece_off, n_parts, s));
+    MP_TRY(cudaMemcpyAsync(&n_seg, piece_off + n_parts, 4, cudaMemcpyDeviceToHost, s));
+    MP_TRY(cudaStreamSynchronize(s));
+    if (row_end < ends[1] || n_seg == 0) return cudaErrorNotSupported;
+    pl->n_seg = n_seg, pl->n_rows = n_rows, pl->N = p.N, pl->part_bytes = ((uint64_t)n_parts + 1) * 4;
+    MP_TRY(cudaMalloc((void **)&pl->seg_nz, ((size_t)n_seg + 1) * 4 + 16));
+    MP_TRY(cudaMalloc((void **)&pl->seg_row, (size_t)n_seg * 4 + 16));
+    k_mp_segments<<<grid_1d((uint64_t)n_seg + 1), 256, 0, s>>>(parts, piece_off, n_parts, pl->rowptr, n_rows, n_seg, pl->seg_nz, pl->seg_row);
+    MP_TRY(cudaGetLastError());
+
+    // tickets: who shares which row (the rule of b200_merge_prepare)
+    const bool ticket_default = p.a.val_is_f16 || (ch.per_thread && (uint64_t)p.N * 4 <= 128);
+    if (p.a.begin_row == 0 && env_int("GS_MERGE_TICKET", ticket_default ? 1 : 0) != 0) {
+        uint32_t *head = nullptr, *tail = nullptr;
+        MP_TRY(cudaMalloc((void **)&head, (size_t)n_seg * 4 + 16));
+        pl->head_s0 = head;
+        MP_TRY(cudaMalloc((void **)&tail, (size_t)n_seg * 4 + 16));
+        pl->tail_s1 = tail;
+        k_mp_sharers<<<grid_1d(n_seg), 256, 0, s>>>(pl->seg_nz, pl->seg_row, n_seg, pl->rowptr, n_rows, head, tail, scal + 1);
+        MP_TRY(cudaGetLastError());
+        MP_TRY(cudaMemcpyAsync(h, scal, 8, cudaMemcpyDeviceToHost, s));
+        MP_TRY(cudaStreamSynchronize(s));
+        pl->max_sharers = h[1] ? h[1] : 1;
+        if (pl->max_sharers <= (uint32_t)env_int("GS_MERGE_TICKET_MAX", 64) && (uint64_t)n_seg * 2 * p.N * sizeof(float) <= (uint64_t)env_int("GS_MERGE_TICKET_MB", 512) << 20) {
+            const uint32_t rows_total = std::max(n_rows, p.a.rows);
+            uint32_t *flag = nullptr, *off = nullptr, n_zero = 0;
+            MP_TRY(tmp.get(&flag, rows_total));
+            MP_TRY(tmp.get(&off, (uint64_t)rows_total + 1));
+            k_mp_zero_flags<<<grid_1d(rows_total), 256, 0, s>>>(pl->rowptr, n_rows, rows_total, ends[1], flag);
+            MP_TRY(cudaGetLastError());
+            MP_TRY(scan_exclusive_u32(flag, off, rows_total, s));
+            MP_TRY(cudaMemcpyAsync(&n_zero, off + rows_total, 4, cudaMemcpyDeviceToHost, s));
+            MP_TRY(cudaStreamSynchronize(s));
+            if (n_zero) {
+                MP_TRY(cudaMalloc((void **)&pl->zero_rows, (size_t)n_zero * 4 + 16));
+                k_mp_zero_list<<<grid_1d(rows_total), 256, 0, s>>>(flag, off, rows_total, pl->zero_rows);
+                MP_TRY(cudaGetLastError());
+            }
+            pl->n_zero = n_zero;
+            MP_TRY(cudaMalloc((void **)&pl->ticket, (size_t)n_seg * 4));
+            MP_TRY(cudaMemsetAsync(pl->ticket, 0, (size_t)n_seg * 4, s));
+            MP_TRY(cudaMalloc((void **)&pl->partial, (size_t)n_seg * 2 * p.N * sizeof(float)));
+        } else {
+            cudaFree(pl->head_s0), cudaFree(pl->tail_s1);
+            pl->head_s0 = pl->tail_s1 = nullptr;
+        }
+    }
+    MP_TRY(cudaStreamSynchronize(s));
+    snprintf(pl->name, sizeof pl->name, "k_b200_merge%s<N%d,%s,%s,%d lane%s/segment,%s%s%u segments of <=%u nnz from %u parts>", ch.per_thread ? "_chunk" : "", p.N, p.a.col_is_u16 ? "u16" : "u32",
+             p.a.val_is_f16 ? "f16" : "f32", ch.LG, ch.LG > 1 ? "s" : "", pl->stage ? "staged," : "", pl->ticket ? "tickets," : "", pl->n_seg, ch.cap, n_parts);
+    return cudaSuccess;
 }
 
 } // namespace
@@ -448,6 +662,17 @@ cudaError_t b200_merge_prepare(const launch_params &p, const uint32_t *parts_dev
         return e;
     };
     cudaError_t e;
+    if (env_int("GS_MERGE_DEVICE_PREPARE", 1) != 0) { // the plan built by device passes; anything it does not take goes through the host code below
+        e = prepare_on_device(p, parts_dev, n_parts, nz_rows_dev, part_rows_dev, parts_are_rows, pl, s);
+        if (e == cudaSuccess) {
+            *out = pl;
+            return cudaSuccess;
+        }
+        cudaGetLastError();
+        b200_merge_free(pl);
+        if (e != cudaErrorNotSupported) return e;
+        if (!(pl = new (std::nothrow) b200_merge_plan)) return cudaErrorMemoryAllocation;
+    }
     std::vector<uint32_t> parts(n_parts + 1), rowptr;
     if ((e = cudaMemcpyAsync(parts.data(), parts_dev, parts.size() * 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(e);
     const uint32_t nnz = (uint32_t)p.a.nnz;

@@ -501,6 +501,18 @@ int bit_width(uint32_t v)
 }
 } // namespace
 
+// exported for the other plan-time builders (kernels_merge.cu): out[i] = in[0] + ... + in[i - 1], i in [0, n]
+cudaError_t scan_exclusive_u32(const uint32_t *in, uint32_t *out, uint64_t n, cudaStream_t s)
+{
+    scratch sc(s);
+    return scan_exclusive(in, out, n, sc, s);
+}
+cudaError_t rowptr_from_sorted_rows(const uint32_t *row, uint32_t nnz, uint32_t rows, uint32_t *rowptr, cudaStream_t s)
+{
+    k_rowptr<<<blocks_for((uint64_t)rows + 1, 256), 256, 0, s>>>(row, nnz, rows, rowptr);
+    return cudaGetLastError();
+}
+
 cudaError_t transform_row_chain(const coo_dev &m, bool sort, uint32_t S, bool half, const char *level, double pad_bound, cudaStream_t s, transform_out &out)
 {
     scratch sc(s);

@@ -204,3 +204,46 @@ def test_chunk_kernel_hub_row_keeps_red_add(engine, monkeypatch):
     plan.run(2)
     ip = csr_from_coo(rows, r)
     _check(plan.output(), oracle_spmm_f64acc(rows, N, ip, c, vals, B), oracle_spmm_absrow(rows, N, ip, c, vals, B), False)
+
+
+@pytest.mark.parametrize("chain", sorted(CHAINS) + ["warp_bitmap", "thread_total"])
+@pytest.mark.parametrize("N,half", [(8, False), (32, True), (128, False), (2, False)])
+def test_plan_built_on_device_equals_host_built(engine, monkeypatch, chain, N, half):
+    """the range kernel's plan -- segments, their rows, who shares which row, the rows without non-zeros -- built by device passes (the default) against
+    the host code (GS_MERGE_DEVICE_PREPARE=0): the same kernel line (segment count, tickets or not), and the same C: bit for bit in ticket mode (the
+    order of every sum is fixed by the arrays), within fp32 rounding with red.add"""
+    from generalsparse_b200 import api, synth
+    for name, rows, cols, (r, c) in _mats():
+        vals = synth.synth_values(len(r), seed=9)
+        B = synth.synth_dense(cols, N, seed=9)
+        if half:
+            vals, B = vals.astype(np.float16).astype(np.float32), B.astype(np.float16).astype(np.float32)
+        api.config_set("DENSE_MATRIX_SIZE", N)
+        api.config_set("VECTOR_WIDTH", min(N, 32))
+        s = api.Session(api.MetaDataSet.from_coo(rows, cols, r, c, vals))
+        try:
+            if chain in CHAINS:
+                for op in CHAINS[chain](N):
+                    s.add_and_run(op[0], *op[1:])
+                s.compile()
+            else:
+                s.run_family(chain, N, 4 if chain == "thread_total" else 1, 1)
+        except api.GsError as e:
+            if e.status == 5:
+                continue  # the reference refuses the padding rate on this matrix
+            raise
+        engine.upload_session(s, half=half, as_id=75)
+        out = {}
+        for mode in ("0", "1"):
+            monkeypatch.setenv("GS_MERGE_DEVICE_PREPARE", mode)
+            plan = engine.plan(s, N, half=half, kernel="b200_merge", sub_matrix_id=75)
+            plan.set_dense(B)
+            plan.run(2)
+            out[mode] = (plan.output(), plan.kernel_name)
+            del plan
+        (Ch, kh), (Cd, kd) = out["0"], out["1"]
+        assert kh == kd, (name, chain, kh, kd)
+        if "tickets," in kd:
+            assert np.array_equal(Ch.view(np.uint8), Cd.view(np.uint8)), (name, chain, kd)
+        else:
+            assert np.allclose(Ch.astype(np.float32), Cd.astype(np.float32), rtol=1e-2 if half else 1e-5, atol=1e-2 if half else 1e-5), (name, chain, kd)
