@@ -141,9 +141,11 @@ def device_transform_block(eng, sess, family, rows, cols, r, c, v, N, S, half, h
     """the chain's transform steps as device passes (gs_transform_host_coo) beside the host pipeline that built the timed plan:
     every array the chain registers must come out byte-equal; device_ms = CUDA events around the passes alone, wall_ms adds the H2D of the COO."""
     eng.transform_coo(family, rows, cols, r, c, v, N, S, 1, half=half, as_id=900)  # warm-up (allocations, module load)
-    t0 = time.perf_counter()
-    dd, dev_ms = eng.transform_coo(family, rows, cols, r, c, v, N, S, 1, half=half, as_id=900)
-    wall = time.perf_counter() - t0
+    dev_ms, wall = 1e30, 1e30
+    for _ in range(3):  # best of three: the passes are a dozen small kernels with host round trips between them, a busy host core shows up at once
+        t0 = time.perf_counter()
+        dd, ms1 = eng.transform_coo(family, rows, cols, r, c, v, N, S, 1, half=half, as_id=900)
+        wall, dev_ms = min(wall, time.perf_counter() - t0), min(dev_ms, ms1)
     keys = [k[: k.rfind("_")] for k in sess.deps()]
     same = True
     for k in keys:
