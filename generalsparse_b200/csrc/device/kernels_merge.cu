@@ -523,7 +523,7 @@ merge_choice choose(const launch_params &p)
     merge_choice c;
     c.per_thread = (uint64_t)p.N * (p.a.val_is_f16 ? 2 : 4) <= (uint64_t)env_int("GS_MERGE_CHUNK_ROW_BYTES", 256) && env_int("GS_MERGE_THREAD", 1) != 0;
     c.LG = c.per_thread ? (p.a.val_is_f16 ? chunk_lanes<__half>(p.N) : chunk_lanes<float>(p.N)) : p.N < 32 ? p.N : 32;
-    c.cap = (uint32_t)std::max(c.LG, env_int("GS_MERGE_CAP", c.per_thread ? (c.LG >= 4 ? 64 : 32) : c.LG == 32 ? 512 : 32 * c.LG)); // chunk kernel: every lane of a group walks the whole segment
+    c.cap = (uint32_t)std::max(c.LG, env_int("GS_MERGE_CAP", c.per_thread ? (c.LG >= 4 ? 64 : c.LG == 2 ? 40 : 32) : c.LG == 32 ? 512 : 32 * c.LG)); // (C1 stand-in, cap 32 / 40 / 48 at two lanes: 18.3 / 16.0 / 17.7 us) // chunk kernel: every lane of a group walks the whole segment
     return c;
 }
 
@@ -708,7 +708,7 @@ cudaError_t b200_merge_prepare(const launch_params &p, const uint32_t *parts_dev
     // segments: the chain's parts, long ones cut into equal slices (GS_MERGE_CAP non-zeros at most)
     const bool per_thread = (uint64_t)p.N * (p.a.val_is_f16 ? 2 : 4) <= (uint64_t)env_int("GS_MERGE_CHUNK_ROW_BYTES", 256) && env_int("GS_MERGE_THREAD", 1) != 0;
     const int LG = per_thread ? (p.a.val_is_f16 ? chunk_lanes<__half>(p.N) : chunk_lanes<float>(p.N)) : p.N < 32 ? p.N : 32;
-    const uint32_t cap = (uint32_t)std::max(LG, env_int("GS_MERGE_CAP", per_thread ? (LG >= 4 ? 64 : 32) : LG == 32 ? 512 : 32 * LG)); // chunk kernel: every lane of a group walks the whole segment
+    const uint32_t cap = (uint32_t)std::max(LG, env_int("GS_MERGE_CAP", per_thread ? (LG >= 4 ? 64 : LG == 2 ? 40 : 32) : LG == 32 ? 512 : 32 * LG)); // chunk kernel: every lane of a group walks the whole segment
     pl->per_thread = per_thread, pl->cap = cap;
     if (per_thread) { // staging needs 16-byte aligned streams and at most 48 KB for a CTA's piece
         const uint32_t elems = (128 / LG) * cap + 8;
