@@ -137,7 +137,16 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(inside[0][1]), "reasons": reasons, "samples": len(inside)}
 
 
-def device_transform_block(eng, sess, family, rows, cols, r, c, v, N, S, half, host_id, host_pipeline_s, plan_kernel="auto"):
+def device_transform_block(*a, **kw):
+    """the block below, or what went wrong with it: a side measurement must not take the bench line down"""
+    try:
+        return _device_transform_block(*a, **kw)
+    except Exception as e:  # noqa: BLE001
+        os.environ.pop("GS_SP24_DEVICE_BUILD", None)
+        return {"error": "%s: %s" % (type(e).__name__, e)}
+
+
+def _device_transform_block(eng, sess, family, rows, cols, r, c, v, N, S, half, host_id, host_pipeline_s, plan_kernel="auto"):
     """the chain's transform steps as device passes (gs_transform_host_coo) beside the host pipeline that built the timed plan:
     every array the chain registers must come out byte-equal; device_ms = CUDA events around the passes alone, wall_ms adds the H2D of the COO."""
     eng.transform_coo(family, rows, cols, r, c, v, N, S, 1, half=half, as_id=900)  # warm-up (allocations, module load)
