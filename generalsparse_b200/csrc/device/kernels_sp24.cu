@@ -220,7 +220,8 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     sp24_dev_image db;
     bool on_device = false;
     uint32_t dev_unit_bytes = 0;
-    if (group == 1 && env_int("GS_SP24_DEVICE_BUILD", 1)) {
+    static thread_local bool force_host = false; // a device build that failed half-way (out of memory ...) is repeated on the host, once
+    if (group == 1 && !force_host && env_int("GS_SP24_DEVICE_BUILD", 1)) {
         if (sp24_dev_count(p, rowptr, n_rows, s, db) == cudaSuccess && !db.bad) {
             if (db.rem_nnz == 0) on_device = true;
             else if (allow_remainder && fuse >= 2 && p.N <= 64 && db.max_entries <= 0xffffu) {
@@ -343,11 +344,20 @@ cudaError_t b200_sp24_prepare(const launch_params &p, int sm_count, bool allow_r
     }
     if (on_device) { // the fill: image, metadata, tile-local blocks, and the unit / panel tables when the empty tiles leave the stream
         uint32_t n_units = 0;
-        if ((e = sp24_dev_fill(p, rowptr, n_rows, pl->tiled ? tl.unit_bytes : (uint32_t)sp24::IMG_BYTES, tl_row_bytes, dev_compact != nullptr, 0.9, s, db, &pl->img, &pl->panel_ptr, &pl->unit_kt, &n_units)) !=
-            cudaSuccess)
-            return fail_dev(e);
-        if (pl->panel_ptr) pl->fn = dev_compact, pl->n_tiles = n_units;
-        if ((e = sp24_dev_out_row(p, rowid, n_rows, im_n_panels, s, db, &pl->out_row)) != cudaSuccess) return fail_dev(e);
+        if (env_int("GS_SP24_DEVICE_BUILD", 1) == 2) e = cudaErrorMemoryAllocation; // (test hook: the fill "fails", the fallback below runs)
+        else e = sp24_dev_fill(p, rowptr, n_rows, pl->tiled ? tl.unit_bytes : (uint32_t)sp24::IMG_BYTES, tl_row_bytes, dev_compact != nullptr, 0.9, s, db, &pl->img, &pl->panel_ptr, &pl->unit_kt, &n_units);
+        if (e == cudaSuccess) {
+            if (pl->panel_ptr) pl->fn = dev_compact, pl->n_tiles = n_units;
+            e = sp24_dev_out_row(p, rowid, n_rows, im_n_panels, s, db, &pl->out_row);
+        }
+        if (e != cudaSuccess) { // the host builder takes over
+            cudaGetLastError();
+            fail_dev(e);
+            force_host = true;
+            e = b200_sp24_prepare(p, sm_count, allow_remainder, out, s);
+            force_host = false;
+            return e;
+        }
         db.release();
     }
     pl->grid = (uint32_t)std::min<uint64_t>((uint64_t)env_int("GS_TILE_CTAS", sm_count), pl->n_tiles);

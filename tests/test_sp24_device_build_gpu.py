@@ -75,3 +75,23 @@ def test_device_build_is_faster_than_host_build(engine, monkeypatch):
         del plan
     print("plan creation, C2 N=8: host builder %.3f s, device builder %.4f s (%s)" % (t["0"], t["1"], name))
     assert t["1"] < t["0"]
+
+
+def test_failed_device_build_falls_back_to_the_host_builder(engine, monkeypatch):
+    """GS_SP24_DEVICE_BUILD=2 makes the fill pass report an allocation failure after the counts were taken: the plan must come out of the host builder"""
+    from generalsparse_b200 import api, synth
+    from oracle.oracle_check import csr_from_coo, oracle_spmm_f32
+    rows, cols, N = 1000, 4096, 16
+    r, c = synth.synth_matrix("uniform", rows, cols, seed=83, density=0.3)
+    s = api.Session(api.MetaDataSet.from_coo(rows, cols, r, c, None)).run_family("thread_total", N, 8, 1)
+    engine.upload_session(s, half=True, as_id=92)
+    names = {}
+    for mode in ("0", "2"):
+        monkeypatch.setenv("GS_SP24_DEVICE_BUILD", mode)
+        plan = engine.plan(s, N, half=True, kernel="b200_sp24", sub_matrix_id=92)
+        plan.set_dense(np.ones((cols, N), np.float32))
+        plan.run(1)
+        assert np.array_equal(plan.output().astype(np.float32), oracle_spmm_f32(rows, N, csr_from_coo(rows, r), c, np.ones(len(r), np.float32), np.ones((cols, N), np.float32)))
+        names[mode] = plan.kernel_name
+        del plan
+    assert names["0"] == names["2"]
