@@ -668,9 +668,8 @@ cudaError_t b200_merge_prepare(const launch_params &p, const uint32_t *parts_dev
             *out = pl;
             return cudaSuccess;
         }
-        cudaGetLastError();
+        cudaGetLastError(); // input the passes do not take, or a pass that failed (out of memory ...): the host code decides
         b200_merge_free(pl);
-        if (e != cudaErrorNotSupported) return e;
         if (!(pl = new (std::nothrow) b200_merge_plan)) return cudaErrorMemoryAllocation;
     }
     std::vector<uint32_t> parts(n_parts + 1), rowptr;
