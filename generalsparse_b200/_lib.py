@@ -25,7 +25,7 @@ SYMBOLS = [
     "gs_comm_unique_id", "gs_comm_init", "gs_comm_allgather_rows", "gs_comm_destroy",
     "gs_exec_create", "gs_exec_destroy", "gs_exec_devices", "gs_exec_build", "gs_exec_row_cuts", "gs_exec_kernel_name", "gs_exec_set_dense", "gs_exec_run",
     "gsh_session_generate_final_program", "gs_execute_binary", "gsh_metadata_fit_model", "gs_plan_model_bytes",
-    "gs_transform_device", "gs_transform_host_coo", "gs_download_array", "gs_exec_build_on_device",
+    "gs_transform_device", "gs_transform_host_coo", "gs_download_array", "gs_exec_build_on_device", "gs_transform_device_merge_path",
     "gs_exec_get_output", "gs_exec_enable_allgather", "gs_exec_allgather_output", "gs_exec_get_replica",
 ]
 
@@ -90,6 +90,7 @@ def lib():
         "gs_transform_device": (i32, [vp, i32, u64, u64, u64, vp, vp, vp, i32, i32, i32, i32, i32, P(PlanDesc)]),
         "gs_transform_host_coo": (i32, [vp, i32, u64, u64, u64, vp, vp, vp, i32, i32, i32, i32, i32, P(PlanDesc), P(C.c_float)]),
         "gs_download_array": (i32, [vp, cp, vp, u64, P(u64), P(i32)]),
+        "gs_transform_device_merge_path": (i32, [vp, i32, C.c_uint32, i32, u64, u64, u64, vp, vp, vp, i32, i32, i32, i32, vp, vp, i32, i32, P(PlanDesc)]),
         "gs_plan_set_kernel": (i32, [vp, i32]), "gs_set_dense": (i32, [vp, vp, i32]), "gs_set_dense_device": (i32, [vp, vp]),
         "gs_launch": (i32, [vp]), "gs_run": (i32, [vp, i32, P(C.c_float)]), "gs_get_output": (i32, [vp, vp]),
         "gs_output_device": (vp, [vp]), "gs_spmm_host": (i32, [vp, vp, vp]),

@@ -250,6 +250,18 @@ class Engine:
                                         C.byref(desc)))
         return desc
 
+    def transform_coo_merge_path(self, level, work_size, rows, cols, r, c, vals, N, coarsen=1, vector_width=None, grid=(64, 1), block=(8, 4), sort=False, half=False, as_id=0):
+        """[sort_operator +] merge_path_{thread,warp,tblock}_operator(work_size) + the level's total reduction, built by device passes; level: 0 / 1 / 2
+        or "thread" / "warp" / "tblock"; grid / block / vector_width: the launch-shape hints of the chain's grid_block_operator"""
+        lv = {"thread": 0, "warp": 1, "tblock": 2}.get(level, level)
+        r32, c32 = np.ascontiguousarray(r, dtype=np.uint32), np.ascontiguousarray(c, dtype=np.uint32)
+        v32 = np.ones(len(r32), np.float32) if vals is None else np.ascontiguousarray(vals, dtype=np.float32)
+        g, b = np.asarray(grid, np.uint32), np.asarray(block, np.uint32)
+        desc = PlanDesc()
+        check(lib().gs_transform_device_merge_path(self._h, lv, work_size, int(sort), rows, cols, len(r32), _ptr(r32), _ptr(c32), _ptr(v32), 1, N, coarsen,
+                                                   min(N, 32) if vector_width is None else vector_width, _ptr(g), _ptr(b), int(half), as_id, C.byref(desc)))
+        return desc
+
     def download_array(self, key):
         """a device array of the context as numpy, in its device dtype"""
         n, dt = C.c_uint64(0), C.c_int32(0)

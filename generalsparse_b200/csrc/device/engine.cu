@@ -681,6 +681,18 @@ static void drop_arrays_of_id(gs_ctx *ctx, int id)
     }
 }
 
+static void register_built(gs_ctx *ctx, gsd::transform_out &out, int as_id)
+{
+    for (gsd::built_array &a : out.arrays) {
+        dev_array da;
+        da.ptr = a.ptr, da.len = a.len, da.dtype = a.dtype, da.max_value = a.max_value, da.align = a.align, da.iota = a.iota;
+        if (a.linear) da.model = (int)gs::LINEAR_COMPRESS, da.model_coefficient = a.linear_step, da.model_intercept = 0;
+        ctx->arrays[a.pos + "_" + a.name + "_" + std::to_string(as_id)] = da;
+        a.ptr = nullptr; // the context owns it now
+    }
+    out.arrays.clear();
+}
+
 gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t cols, uint64_t nnz, const uint32_t *row_dev, const uint32_t *col_dev, const float *val_dev, int N,
                               int sparse_coarsen, int coarsen, int half, int as_id, gs_plan_desc *desc_out)
 {
@@ -777,14 +789,62 @@ gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t c
         GS_REQUIRE(key.size() < 64, "key too long");
         strcpy(d.deps[d.n_deps++], key.c_str());
     }
-    for (gsd::built_array &a : out.arrays) {
-        dev_array da;
-        da.ptr = a.ptr, da.len = a.len, da.dtype = a.dtype, da.max_value = a.max_value, da.align = a.align, da.iota = a.iota;
-        if (a.linear) da.model = (int)gs::LINEAR_COMPRESS, da.model_coefficient = a.linear_step, da.model_intercept = 0;
-        ctx->arrays[a.pos + "_" + a.name + "_" + std::to_string(as_id)] = da;
-        a.ptr = nullptr; // the context owns it now
+    register_built(ctx, out, as_id);
+    *desc_out = d;
+    GS_API_END
+}
+
+gs_status gs_transform_device_merge_path(gs_ctx *ctx, int level, uint32_t work_size, int sort, uint64_t rows, uint64_t cols, uint64_t nnz, const uint32_t *row_dev, const uint32_t *col_dev,
+                                         const float *val_dev, int coo_on_host, int N, int coarsen, int vector_width, const uint32_t grid[2], const uint32_t block[2], int half, int as_id,
+                                         gs_plan_desc *desc_out)
+{
+    GS_API_BEGIN
+    GS_REQUIRE(ctx && desc_out && row_dev && col_dev && val_dev && grid && block && nnz > 0, "null argument");
+    GS_REQUIRE(level >= 0 && level <= 2 && work_size >= 1 && N >= 1 && coarsen >= 1 && as_id >= 0, "bad argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    ctx->join_async();
+    static const char *lv[3] = {"THREAD_META", "WARP_META", "TBLOCK_META"};
+    struct staged { // the COO brought over when it lies on the host
+        void *p[3] = {nullptr, nullptr, nullptr};
+        ~staged()
+        {
+            for (void *q : p) cudaFree(q);
+        }
+    } st;
+    if (coo_on_host) {
+        const void *src[3] = {row_dev, col_dev, val_dev};
+        for (int i = 0; i < 3; i++) {
+            CUDA_TRY(cudaMalloc(&st.p[i], nnz * 4));
+            CUDA_TRY(cudaMemcpyAsync(st.p[i], src[i], nnz * 4, cudaMemcpyHostToDevice, ctx->stream));
+        }
+        row_dev = (const uint32_t *)st.p[0], col_dev = (const uint32_t *)st.p[1], val_dev = (const float *)st.p[2];
     }
-    out.arrays.clear();
+    gsd::coo_dev m;
+    m.row = row_dev, m.col = col_dev, m.val = val_dev, m.rows = rows, m.cols = cols, m.nnz = nnz;
+    gsd::transform_out out;
+    const cudaError_t e = gsd::transform_merge_path_chain(m, sort != 0, work_size, lv[level], half != 0, (double)gs::get_config().as_integer("PADDING_RATE_UP_BOUND"), ctx->stream, out);
+    if (e != cudaSuccess) {
+        out.release();
+        cudaGetLastError();
+        if (!out.error.empty()) return fail(GS_ERR_INVALID, out.error);
+        return fail(GS_ERR_CUDA, std::string("device transform: ") + cudaGetErrorString(e));
+    }
+    // what compile() gives for a total reduction over blocks that are not one row each (operators.cc): the range kernel's family and its three arrays
+    gs_plan_desc d;
+    memset(&d, 0, sizeof d);
+    d.family = GS_FAMILY_B200_MERGE, d.sub_matrix_id = as_id, d.coarsen = coarsen, d.sparse_coarsen = 1, d.vector_width = vector_width;
+    d.rows = rows, d.cols = cols, d.origin_nnz = nnz, d.stored_nnz = out.stored_nnz, d.has_row_permutation = out.has_perm;
+    d.grid[0] = grid[0], d.grid[1] = grid[1], d.block[0] = block[0], d.block[1] = block[1];
+    std::vector<std::pair<const char *, const char *>> deps = {{"GLOBAL_META", "nz_col_indices"}, {"GLOBAL_META", "nz_vals"}};
+    if (out.has_perm) deps.push_back({"GLOBAL_META", "original_nz_row_indices"});
+    deps.push_back({"GLOBAL_META", "nz_row_indices"}), deps.push_back({lv[level], "first_nz_indices"}), deps.push_back({lv[level], "first_row_indices_without_ending"});
+    for (const auto &k : deps) {
+        const std::string key = std::string(k.first) + "_" + k.second + "_" + std::to_string(as_id);
+        GS_REQUIRE(key.size() < 64, "key too long");
+        strcpy(d.deps[d.n_deps++], key.c_str());
+    }
+    drop_arrays_of_id(ctx, as_id);
+    register_built(ctx, out, as_id);
     *desc_out = d;
     GS_API_END
 }

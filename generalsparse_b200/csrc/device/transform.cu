@@ -761,3 +761,84 @@ cudaError_t transform_col_chain(const coo_dev &m, uint32_t col_block, uint32_t g
 }
 
 } // namespace gsd
+
+namespace gsd {
+namespace {
+// merge path (get_begin_{rows,nzs}_of_level_after_merge_path.cc; csrc/host/steps.cc: merge_path_walk): the path visits the non-empty rows, row j (the
+// j-th non-empty one) ends at path position sum(len of rows 0..j) + j; part p starts at position p * work, in the first row whose end lies
+// beyond it, at non-zero position - j.  With incl[r] = sum over rows <= r of (len + 1 where len > 0) the end of a non-empty row r is incl[r] - 1,
+// incl only grows at non-empty rows, so the row of part p is the first r with incl[r] >= p * work + 2 -- one binary search per part.
+__global__ void k_mp_path_terms(const uint32_t *rowptr, uint32_t n_rows, uint32_t *term, uint32_t *nonempty)
+{
+    for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t l = rowptr[r + 1] - rowptr[r];
+        term[r] = l ? l + 1 : 0, nonempty[r] = l != 0;
+    }
+}
+__global__ void k_mp_parts(const uint32_t *excl /* n_rows + 1: excl[r + 1] = incl[r] */, const uint32_t *ordinal, uint32_t n_rows, uint32_t work, uint32_t n_parts, uint32_t nnz,
+                           uint32_t *part_row, uint32_t *part_nz)
+{
+    for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p <= n_parts; p += (uint64_t)gridDim.x * blockDim.x) {
+        if (p == n_parts) {
+            part_nz[p] = nnz; // the sentinel get_begin_nzs_of_level_after_merge_path.cc appends
+            continue;
+        }
+        const uint64_t pos = p * work;
+        uint32_t lo = 0, hi = n_rows; // first r with excl[r + 1] >= pos + 2
+        while (lo < hi) {
+            const uint32_t mid = lo + (hi - lo) / 2;
+            if ((uint64_t)excl[mid + 1] < pos + 2) lo = mid + 1;
+            else hi = mid;
+        }
+        part_row[p] = lo, part_nz[p] = (uint32_t)(pos - ordinal[lo]);
+    }
+}
+} // namespace
+
+// [sort_operator +] merge_path_{thread,warp,tblock}_operator(work): GLOBAL nz_* (sorted when asked), `level` first_row_indices_without_ending and
+// first_nz_indices (with the closing nnz)
+cudaError_t transform_merge_path_chain(const coo_dev &m, bool sort, uint32_t work, const char *level, bool half, double pad_bound, cudaStream_t s, transform_out &out)
+{
+    if (work < 1) {
+        out.error = "merge path: work_size must be >= 1";
+        return cudaErrorInvalidValue;
+    }
+    TRY(transform_row_chain(m, sort, 0, half, "ROW_TMP", pad_bound, s, out)); // the (sorted) stream and its row pointer; no padding
+    uint32_t *rowptr = nullptr;
+    for (size_t i = 0; i < out.arrays.size();) {
+        if (out.arrays[i].pos == "ROW_TMP") {
+            if (out.arrays[i].name == "first_nz_indices") rowptr = (uint32_t *)out.arrays[i].ptr;
+            else cudaFreeAsync(out.arrays[i].ptr, s);
+            out.arrays.erase(out.arrays.begin() + i);
+        } else i++;
+    }
+    if (!rowptr) return cudaErrorInvalidValue;
+    scratch sc(s);
+    sc.bufs.push_back(rowptr); // scaffolding: freed with the scratch
+    const uint32_t n_rows = (uint32_t)out.rows_kept, nnz = (uint32_t)out.stored_nnz;
+    uint32_t *term = nullptr, *ordinal = nullptr, total = 0;
+    TRY(sc.get(&term, (uint64_t)n_rows + 1));
+    TRY(sc.get(&ordinal, (uint64_t)n_rows + 1));
+    k_mp_path_terms<<<blocks_for(n_rows, 256 * 4), 256, 0, s>>>(rowptr, n_rows, term, ordinal);
+    TRY(cudaGetLastError());
+    TRY(scan_exclusive(term, term, n_rows, sc, s));
+    TRY(scan_exclusive(ordinal, ordinal, n_rows, sc, s));
+    TRY(cudaMemcpyAsync(&total, term + n_rows, 4, cudaMemcpyDeviceToHost, s));
+    TRY(cudaStreamSynchronize(s));
+    if (total < 2) { // no non-zero at all
+        out.error = "merge path over a matrix without non-zeros";
+        return cudaErrorInvalidValue;
+    }
+    const uint64_t count = (uint64_t)total - 1; // the first non-empty row carries no +1
+    const uint32_t n_parts = (uint32_t)((count + work - 1) / work);
+    uint32_t *part_row = nullptr, *part_nz = nullptr;
+    TRY(alloc_out(&part_row, n_parts, s));
+    take(out, level, "first_row_indices_without_ending", part_row, n_parts, GS_U32, n_rows ? n_rows - 1 : 0, 0);
+    TRY(alloc_out(&part_nz, (uint64_t)n_parts + 1, s));
+    take(out, level, "first_nz_indices", part_nz, (uint64_t)n_parts + 1, GS_U32, nnz, 0);
+    k_mp_parts<<<blocks_for((uint64_t)n_parts + 1, 256), 256, 0, s>>>(term, ordinal, n_rows, work, n_parts, nnz, part_row, part_nz);
+    TRY(cudaGetLastError());
+    return cudaStreamSynchronize(s);
+}
+
+} // namespace gsd

@@ -55,6 +55,9 @@ cudaError_t transform_nnz_chain(const coo_dev &m, uint32_t size, bool warp_level
 // `group` BMTs) or tblock_thread_bit_map_operator (BMTBs of `group` BMTs): the warp_bitmap / block_bitmap driver chains
 cudaError_t transform_col_chain(const coo_dev &m, uint32_t col_block, uint32_t group, bool warp_level, bool half, double pad_bound, cudaStream_t s, transform_out &out);
 
+// [sort_operator +] merge_path_{thread,warp,tblock}_operator(work): the (sorted) stream, `level` first_row_indices_without_ending and first_nz_indices
+cudaError_t transform_merge_path_chain(const coo_dev &m, bool sort, uint32_t work, const char *level, bool half, double pad_bound, cudaStream_t s, transform_out &out);
+
 // pieces the other plan-time builders reuse: exclusive scan (out has n + 1 entries, in == out allowed) and CSR offsets of ascending row ids
 cudaError_t scan_exclusive_u32(const uint32_t *in, uint32_t *out, uint64_t n, cudaStream_t s);
 cudaError_t rowptr_from_sorted_rows(const uint32_t *row, uint32_t nnz, uint32_t rows, uint32_t *rowptr, cudaStream_t s);

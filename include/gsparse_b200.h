@@ -225,6 +225,14 @@ gs_status gs_upload_session_as(gs_ctx *ctx, const gsh_session *s, int half, int 
  * the reference's padding assert fires; GS_ERR_UNSUPPORTED for families that are not one of the seven drivers'. */
 gs_status gs_transform_device(gs_ctx *ctx, int family, uint64_t rows, uint64_t cols, uint64_t nnz, const uint32_t *row_dev, const uint32_t *col_dev, const float *val_dev, int N,
                               int sparse_coarsen, int coarsen, int half, int as_id, gs_plan_desc *desc_out);
+/* the merge-path chains on the device: [sort_operator +] merge_path_{thread (level 0), warp (1), tblock (2)}_operator(work_size) + the level's total
+ * reduction (get_begin_{rows,nzs}_of_level_after_merge_path.cc: one binary search per part instead of the reference's walk from the first row).
+ * desc_out is what compile() gives for such a chain: GS_FAMILY_B200_MERGE over the level's first_nz_indices / first_row_indices_without_ending and
+ * GLOBAL nz_row_indices; grid / block / vector_width are the launch-shape hints the chain's grid_block_operator would have recorded.
+ * coo_on_host != 0: the three COO pointers are host arrays. */
+gs_status gs_transform_device_merge_path(gs_ctx *ctx, int level, uint32_t work_size, int sort, uint64_t rows, uint64_t cols, uint64_t nnz, const uint32_t *row_dev, const uint32_t *col_dev,
+                                         const float *val_dev, int coo_on_host, int N, int coarsen, int vector_width, const uint32_t grid[2], const uint32_t block[2], int half, int as_id,
+                                         gs_plan_desc *desc_out);
 /* the same from host arrays (H2D, then the device passes); ms_device = the device time of the passes alone (CUDA events), may be NULL */
 gs_status gs_transform_host_coo(gs_ctx *ctx, int family, uint64_t rows, uint64_t cols, uint64_t nnz, const uint32_t *row, const uint32_t *col, const float *val, int N,
                                 int sparse_coarsen, int coarsen, int half, int as_id, gs_plan_desc *desc_out, float *ms_device);

@@ -115,3 +115,41 @@ def test_device_chain_sort_is_stable_at_scale(engine):
     plen = (lens[expect[:kept]] + 1) // 2 * 2
     assert np.array_equal(fn, np.concatenate([[0], np.cumsum(plen)]).astype(np.uint32))
     assert dd.stored_nnz == plen.sum()
+
+
+@pytest.mark.parametrize("level,work,sort", [("thread", 33, False), ("thread", 7, True), ("warp", 300, False), ("tblock", 4096, False), ("thread", 1, False)])
+@pytest.mark.parametrize("N,half", [(8, False), (32, True)])
+def test_device_merge_path_chain_equals_host_chain(engine, level, work, sort, N, half):
+    """[sort_operator +] merge_path_{thread,warp,tblock}_operator(work) + the level's total reduction: the partition by one binary search per part on the
+    device against the host's two-pointer walk (itself pinned to the reference's rows x parts loop by the goldens): same arrays, same descriptor, same kernel, same C"""
+    from generalsparse_b200 import api, synth
+    red = {"thread": ("thread_total_reduce_operator", 0, 1, 1), "warp": ("warp_total_reduce_operator", 1), "tblock": ("tblock_total_reduce_operator", 1)}[level]
+    bx, by = min(N, 32), 4
+    for name, rows, cols, r, c in _mats():
+        vals = synth.synth_values(len(r), seed=9)
+        api.config_set("DENSE_MATRIX_SIZE", N)
+        api.config_set("VECTOR_WIDTH", min(N, 32))
+        s = api.Session(api.MetaDataSet.from_coo(rows, cols, r, c, vals))
+        for op in ([("sort_operator",)] if sort else []) + [("merge_path_%s_operator" % level, work), red, ("grid_block_operator", 64, bx, by, 1)]:
+            s.add_and_run(op[0], *op[1:])
+        s.compile()
+        hd = s.plan_desc()
+        engine.upload_session(s, half=half, as_id=84)
+        dd = engine.transform_coo_merge_path(level, work, rows, cols, r, c, vals, N, 1, min(N, 32), tuple(hd.grid), tuple(hd.block), sort=sort, half=half, as_id=85)
+        assert _desc_fields(hd, True) == _desc_fields(dd, True), (name, level)
+        for k in [k[: k.rfind("_")] for k in s.deps()]:
+            a, b = engine.download_array(k + "_84"), engine.download_array(k + "_85")
+            assert a.dtype == b.dtype and a.shape == b.shape and np.array_equal(a.view(np.uint8), b.view(np.uint8)), (name, level, k)
+        B = synth.synth_dense(cols, N, seed=9)
+        if half:
+            B = B.astype(np.float16).astype(np.float32)
+        ph, pd = engine.plan(s, N, half=half, sub_matrix_id=84), engine.plan(dd, N, half=half)
+        assert ph.kernel_name == pd.kernel_name and "k_b200_merge" in pd.kernel_name, (name, level)
+        ph.set_dense(B), pd.set_dense(B)
+        ph.run(1), pd.run(1)
+        if "tickets," in pd.kernel_name:
+            assert np.array_equal(ph.output().view(np.uint8), pd.output().view(np.uint8)), (name, level)
+        else:
+            tol = 1e-2 if half else 1e-5  # red.add: the order of the adds is free (fp16 partials when C is HALF)
+            assert np.allclose(ph.output().astype(np.float32), pd.output().astype(np.float32), rtol=tol, atol=tol), (name, level)
+        del ph, pd
